@@ -1,0 +1,180 @@
+/*
+ * metabuli_b200.h — C ABI of libmetabuli_b200.so: the B200-native replacement of Metabuli's
+ * classification hot path (query k-mer extraction -> k-mer sort -> diffIdx decode + AA merge join ->
+ * match sort -> per-read scoring / LCA).
+ *
+ * The reference has no FFI for this path; the path sits behind four C++ member calls made by
+ * Classifier::startClassify (src/commons/Classifier.cpp:105-119).  Each entry point below names
+ * the reference interface it replaces (paths relative to the reference tree).  INTEGRATION.md shows
+ * the binding a maintainer of the reference would add.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success and a negative
+ * MB_E* code on failure, with a message available from mb_last_error(); nothing throws or exits
+ * across the boundary.  The host owns host memory, the library owns device memory.  One context
+ * drives one GPU; a context is not re-entrant.  There is NO CPU fallback: mb_create fails when no
+ * CUDA device is usable.
+ */
+#ifndef METABULI_B200_H
+#define METABULI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MB_OK          0
+#define MB_E_CUDA     -1   /* CUDA runtime error (message has the call site)                */
+#define MB_E_ARG      -2   /* bad argument / call order                                     */
+#define MB_E_CAPACITY -3   /* caller buffer too small (required size reported by the call)  */
+#define MB_E_DATA     -4   /* malformed database / taxonomy (e.g. DB tax ID without species) */
+
+/* Query k-mer record: src/commons/Kmer.h:24-47 (16 bytes).
+ * qinfo (src/commons/Kmer.h:11-16): pos bits 0-31, sequenceID bits 32-60 (1-based read index within
+ * the batch), frame bits 61-63. */
+typedef struct {
+    uint64_t value;
+    uint64_t qinfo;
+} mb_kmer;
+
+/* Match record: the payload of src/commons/Match.h:9-25 without the vptr (24 bytes). */
+typedef struct {
+    uint64_t qinfo;
+    int32_t  targetId;        /* internal taxID of the DB k-mer (info & mask)            */
+    int32_t  speciesId;       /* taxId2speciesId[targetId] (KmerMatcher.cpp:56-120)      */
+    uint32_t dnaEncoding;     /* low 24 bits of the DB k-mer                             */
+    uint16_t rightEndHamming; /* 8 x 2-bit per-codon Hamming (KmerMatcher.h:386-416)     */
+    uint8_t  hamming;         /* Hamming sum (KmerMatcher.h:348-360)                     */
+    uint8_t  pad;
+} mb_match;
+
+/* src/commons/Kmer.h:111-119 — one entry of the DB `split` file. */
+typedef struct {
+    uint64_t ADkmer;
+    uint64_t diffIdxOffset;
+    uint64_t infoIdxOffset;
+} mb_split;
+
+/* The parameters of LocalParameters the path reads (defaults: src/workflow/classify.cpp:10-37;
+ * DB-side overrides: src/commons/common.cpp:88-133). */
+typedef struct {
+    int32_t device;           /* CUDA device ordinal                                           */
+    int32_t kmer_format;      /* 1 legacy base-21 metamer (OldMetamerScanner), 2 current       */
+    int32_t syncmer;          /* 0/1 (SyncmerScanner)                                          */
+    int32_t smer_len;         /* --smer-len (5)                                                */
+    int32_t seq_mode;         /* 1 single-end, 2 paired-end, 3 long read                       */
+    int32_t min_cons_cnt;     /* --min-cons-cnt (4)                                            */
+    int32_t min_cons_cnt_euk; /* --min-cons-cnt-euk (9)                                        */
+    float   min_score;        /* --min-score (0)                                               */
+    float   min_sp_score;     /* --min-sp-score (0)                                            */
+    float   tie_ratio;        /* --tie-ratio (0.95)                                            */
+    int32_t skip_redundancy;  /* db.parameters Skip_redundancy; 0 masks bit 31 of info         */
+    int32_t accession_level;  /* only 0 is supported on this path                              */
+    int32_t last_shard;       /* 1 when this context holds the END of the DB (the reference never
+                                 offers the final DB k-mer as a candidate, KmerMatcher.cpp:363-406) */
+    int32_t reserved[3];
+} mb_params;
+
+/* Per-read result: the fields of Query (src/commons/common.h:95-128) that reach the outputs. */
+typedef struct {
+    int32_t classification;   /* internal taxID, 0 = unclassified */
+    float   score;
+    int32_t is_classified;
+    int32_t query_length;     /* queryLength + queryLength2       */
+    int32_t hamming_dist;     /* reserved (always 0 without --em) */
+    int32_t taxcnt_begin;     /* range in the taxcnt arrays (Query::taxCnt in std::map order) */
+    int32_t taxcnt_end;
+    int32_t n_matches;        /* matches of this read (diagnostic) */
+} mb_read_result;
+
+/* CUDA-event timings (ms) and counters of the last batch, per phase. */
+typedef struct {
+    float    h2d_ms, extract_ms, sort_kmers_ms, match_ms, sort_matches_ms, score_ms, d2h_ms, total_ms;
+    uint64_t n_bases, n_kmers, n_matches, n_reads;
+    uint64_t db_words, db_kmers;
+    uint32_t kernel_launches;     /* kernels of this library launched for the last batch */
+    uint32_t match_retries;       /* reruns of the match kernel after a capacity miss     */
+} mb_phase_times;
+
+typedef struct mb_ctx mb_ctx;
+
+void        mb_default_params(mb_params *p);                 /* classify.cpp:10-37 */
+mb_ctx     *mb_create(const mb_params *p);                   /* NULL on failure; see mb_global_error() */
+void        mb_destroy(mb_ctx *ctx);
+const char *mb_last_error(const mb_ctx *ctx);
+const char *mb_global_error(void);                           /* failure of mb_create */
+int         mb_set_params(mb_ctx *ctx, const mb_params *p);  /* device / last_shard cannot change */
+
+/* ---- database (replaces the per-call fopen/fread/mmap of KmerMatcher::matchKmers, KmerMatcher.cpp:127-271) ----
+ * diffIdx: uint16 delta stream (IndexCreator.cpp:868-886); info: one uint32 per k-mer; splits: the
+ * `split` file.  The library keeps the compressed stream resident in HBM and builds a block index
+ * (k-mer ordinal + value before every 2048-word block, anchored on the stream start) so that every
+ * block decodes independently.  A SHARD (multi-GPU) is passed as a self-contained stream: the host
+ * cuts the DB at `split` entries and re-encodes the shard's first k-mer as a delta from 0
+ * (INTEGRATION.md), so the library never needs to know where a shard came from. */
+int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint32_t *info, size_t n_kmers);
+/* decode the resident shard on the GPU (parity tap for getNextTargetKmer, KmerMatcher.h:282-297) */
+int mb_decode_db(mb_ctx *ctx, uint64_t *values_out, size_t cap, size_t *n_out);
+
+/* ---- taxonomy (replaces TaxonomyWrapper lookups: NcbiTaxonomy.cpp:261-333, TaxonomyWrapper.cpp:479-498,
+ *      KmerMatcher::loadTaxIdList KmerMatcher.cpp:56-120) ----
+ * Dense arrays indexed by internal taxID 0..max_taxid, derived by the host from taxonomyDB/taxID_list:
+ *   parent[t]      internal parent taxID (root is its own parent); -1 when t does not exist
+ *   species_of[t]  taxId2speciesId (0 when t is not in the DB's taxon list)
+ *   species_rank_of[t]  getTaxIdAtRank(t, "species")
+ * node0_taxid: taxID stored in taxonomy node index 0 (lcaHelper short-circuits on node index 0);
+ * eukaryota_taxid: TaxonomyWrapper::getEukaryotaTaxID (0 if absent). */
+int mb_load_taxonomy(mb_ctx *ctx, const int32_t *parent, const int32_t *species_of, const int32_t *species_rank_of,
+                     int32_t max_taxid, int32_t node0_taxid, int32_t eukaryota_taxid);
+
+/* ---- the hot path ----
+ * Reads are passed packed: `bases` holds the raw sequence characters of all mates back to back;
+ * mate m (0/1) of read i starts at offsets[2*i+m] and has lens[2*i+m] characters (0 = absent).
+ * Replaces, for one batch (QuerySplit):
+ *   KmerExtractor::extractQueryKmers   src/commons/KmerExtractor.h:77-83
+ *   KmerMatcher::matchKmers            src/commons/KmerMatcher.h:228-230
+ *   KmerMatcher::sortMatches           src/commons/KmerMatcher.h:244
+ *   Classifier::assignTaxonomy         src/commons/Classifier.h:77-80
+ * results[n_reads]; taxcnt_id/taxcnt_n receive the per-read (internal taxID, count) lists; when
+ * taxcnt_cap is too small the call returns MB_E_CAPACITY and *taxcnt_used holds the required size. */
+int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
+                      uint32_t n_reads, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n,
+                      size_t taxcnt_cap, size_t *taxcnt_used);
+
+/* The same path in stages (each leaves its output resident on the device): */
+int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
+                   uint32_t n_reads);                                   /* H2D only                      */
+int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers);                     /* KmerExtractor.cpp:83-386      */
+int mb_sort_kmers(mb_ctx *ctx);                                         /* KmerExtractor.cpp:79          */
+int mb_match_kmers(mb_ctx *ctx, size_t *n_matches);                     /* KmerMatcher.cpp:123-481       */
+int mb_sort_matches(mb_ctx *ctx);                                       /* KmerMatcher.cpp:1071-1078     */
+int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used);                   /* Classifier.cpp:166-208        */
+int mb_fetch_results(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap);
+/* all device stages back to back on staged reads (no host copies) */
+int mb_classify_staged(mb_ctx *ctx, size_t *taxcnt_used);
+
+/* parity taps / multi-GPU exchange: copy the resident intermediate out, or replace it. */
+int mb_copy_kmers(mb_ctx *ctx, mb_kmer *out, size_t cap, size_t *n);
+int mb_copy_matches(mb_ctx *ctx, mb_match *out, size_t cap, size_t *n);
+int mb_set_kmers(mb_ctx *ctx, const mb_kmer *host_kmers, size_t n);          /* host -> device   */
+int mb_set_matches(mb_ctx *ctx, const mb_match *host_matches, size_t n);
+/* device-pointer forms used by the multi-GPU driver (pointers are CUDA device addresses on ctx's GPU) */
+int mb_kmers_device(mb_ctx *ctx, void **dptr, size_t *n);
+int mb_matches_device(mb_ctx *ctx, void **dptr, size_t *n);
+int mb_set_kmers_device(mb_ctx *ctx, const void *dptr, size_t n);            /* device -> device */
+int mb_set_matches_device(mb_ctx *ctx, const void *dptr, size_t n);
+/* multi-GPU bucketing: stable partition of the resident k-mers by the owner shard of their amino-acid
+ * part (owner = number of bounds[] <= value; bounds are the first values of shards 1..n_shards-1) and
+ * of the resident matches by home rank ((sequenceID-1) / reads_per_rank).  counts[n] receives sizes. */
+int mb_partition_kmers(mb_ctx *ctx, const uint64_t *bounds, int n_shards, uint64_t *counts);
+int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint64_t *counts);
+
+int mb_get_timings(mb_ctx *ctx, mb_phase_times *t);
+/* CUDA stream the library launches on (cudaStream_t as void*), for event timing by the caller */
+void *mb_stream(mb_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* METABULI_B200_H */

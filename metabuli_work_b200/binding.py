@@ -1,0 +1,328 @@
+"""ctypes binding of the C ABI (include/metabuli_b200.h) and of the host library (host/mb_host.h).
+
+No compute happens here; every call goes to the native libraries.  There is no fallback: a missing
+library raises at import time.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_CUDA = os.path.join(PKG, "libmetabuli_b200.so")
+LIB_HOST = os.path.join(PKG, "libmbhost.so")
+CLI = os.path.join(PKG, "metabuli")
+
+for _p in (LIB_CUDA, LIB_HOST):
+    if not os.path.exists(_p):
+        raise ImportError(f"{_p} is missing: run `python -m metabuli_work_b200.build` (there is no CPU fallback)")
+
+KMER_DT = np.dtype([("value", "<u8"), ("qinfo", "<u8")])
+MATCH_DT = np.dtype([("qinfo", "<u8"), ("targetId", "<i4"), ("speciesId", "<i4"), ("dnaEncoding", "<u4"),
+                     ("rightEndHamming", "<u2"), ("hamming", "u1"), ("pad", "u1")])
+RESULT_DT = np.dtype([("classification", "<i4"), ("score", "<f4"), ("is_classified", "<i4"), ("query_length", "<i4"),
+                      ("hamming_dist", "<i4"), ("taxcnt_begin", "<i4"), ("taxcnt_end", "<i4"), ("n_matches", "<i4")])
+assert KMER_DT.itemsize == 16 and MATCH_DT.itemsize == 24 and RESULT_DT.itemsize == 32
+
+MB_OK, MB_E_CUDA, MB_E_ARG, MB_E_CAPACITY, MB_E_DATA = 0, -1, -2, -3, -4
+
+
+class Params(C.Structure):
+    _fields_ = [("device", C.c_int32), ("kmer_format", C.c_int32), ("syncmer", C.c_int32), ("smer_len", C.c_int32),
+                ("seq_mode", C.c_int32), ("min_cons_cnt", C.c_int32), ("min_cons_cnt_euk", C.c_int32),
+                ("min_score", C.c_float), ("min_sp_score", C.c_float), ("tie_ratio", C.c_float),
+                ("skip_redundancy", C.c_int32), ("accession_level", C.c_int32), ("last_shard", C.c_int32),
+                ("reserved", C.c_int32 * 3)]
+
+
+class PhaseTimes(C.Structure):
+    _fields_ = [("h2d_ms", C.c_float), ("extract_ms", C.c_float), ("sort_kmers_ms", C.c_float), ("match_ms", C.c_float),
+                ("sort_matches_ms", C.c_float), ("score_ms", C.c_float), ("d2h_ms", C.c_float), ("total_ms", C.c_float),
+                ("n_bases", C.c_uint64), ("n_kmers", C.c_uint64), ("n_matches", C.c_uint64), ("n_reads", C.c_uint64),
+                ("db_words", C.c_uint64), ("db_kmers", C.c_uint64), ("kernel_launches", C.c_uint32),
+                ("match_retries", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+# every symbol include/metabuli_b200.h declares
+ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", "mb_global_error", "mb_set_params",
+               "mb_load_db", "mb_decode_db", "mb_load_taxonomy", "mb_classify_batch", "mb_stage_reads",
+               "mb_extract_kmers", "mb_sort_kmers", "mb_match_kmers", "mb_sort_matches", "mb_score_reads",
+               "mb_fetch_results", "mb_classify_staged", "mb_copy_kmers", "mb_copy_matches", "mb_set_kmers",
+               "mb_set_matches", "mb_kmers_device", "mb_matches_device", "mb_set_kmers_device", "mb_set_matches_device",
+               "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream"]
+
+_cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
+_host = C.CDLL(LIB_HOST)
+vp, sz, i32, u32, u64 = C.c_void_p, C.c_size_t, C.c_int32, C.c_uint32, C.c_uint64
+szp = C.POINTER(C.c_size_t)
+
+
+def _sig(lib, name, res, args):
+    f = getattr(lib, name)
+    f.restype = res
+    f.argtypes = args
+    return f
+
+
+_sig(_cuda, "mb_default_params", None, [C.POINTER(Params)])
+_sig(_cuda, "mb_create", vp, [C.POINTER(Params)])
+_sig(_cuda, "mb_destroy", None, [vp])
+_sig(_cuda, "mb_last_error", C.c_char_p, [vp])
+_sig(_cuda, "mb_global_error", C.c_char_p, [])
+_sig(_cuda, "mb_set_params", C.c_int, [vp, C.POINTER(Params)])
+_sig(_cuda, "mb_load_db", C.c_int, [vp, vp, sz, vp, sz])
+_sig(_cuda, "mb_decode_db", C.c_int, [vp, vp, sz, szp])
+_sig(_cuda, "mb_load_taxonomy", C.c_int, [vp, vp, vp, vp, i32, i32, i32])
+_sig(_cuda, "mb_classify_batch", C.c_int, [vp, vp, sz, vp, vp, u32, vp, vp, vp, sz, szp])
+_sig(_cuda, "mb_stage_reads", C.c_int, [vp, vp, sz, vp, vp, u32])
+_sig(_cuda, "mb_extract_kmers", C.c_int, [vp, szp])
+_sig(_cuda, "mb_sort_kmers", C.c_int, [vp])
+_sig(_cuda, "mb_match_kmers", C.c_int, [vp, szp])
+_sig(_cuda, "mb_sort_matches", C.c_int, [vp])
+_sig(_cuda, "mb_score_reads", C.c_int, [vp, szp])
+_sig(_cuda, "mb_fetch_results", C.c_int, [vp, vp, vp, vp, sz])
+_sig(_cuda, "mb_classify_staged", C.c_int, [vp, szp])
+_sig(_cuda, "mb_copy_kmers", C.c_int, [vp, vp, sz, szp])
+_sig(_cuda, "mb_copy_matches", C.c_int, [vp, vp, sz, szp])
+_sig(_cuda, "mb_set_kmers", C.c_int, [vp, vp, sz])
+_sig(_cuda, "mb_set_matches", C.c_int, [vp, vp, sz])
+_sig(_cuda, "mb_kmers_device", C.c_int, [vp, C.POINTER(vp), szp])
+_sig(_cuda, "mb_matches_device", C.c_int, [vp, C.POINTER(vp), szp])
+_sig(_cuda, "mb_set_kmers_device", C.c_int, [vp, vp, sz])
+_sig(_cuda, "mb_set_matches_device", C.c_int, [vp, vp, sz])
+_sig(_cuda, "mb_partition_kmers", C.c_int, [vp, vp, C.c_int, vp])
+_sig(_cuda, "mb_partition_matches", C.c_int, [vp, u32, C.c_int, vp])
+_sig(_cuda, "mb_get_timings", C.c_int, [vp, C.POINTER(PhaseTimes)])
+_sig(_cuda, "mb_stream", vp, [vp])
+
+_sig(_host, "mbh_last_error", C.c_char_p, [])
+_sig(_host, "mbh_open", vp, [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int])
+_sig(_host, "mbh_close", None, [vp])
+_sig(_host, "mbh_ctx", vp, [vp])
+_sig(_host, "mbh_params", None, [vp, C.POINTER(Params)])
+_sig(_host, "mbh_num_bounds", C.c_int, [vp])
+_sig(_host, "mbh_bounds", None, [vp, vp])
+_sig(_host, "mbh_original_taxid", i32, [vp, i32])
+_sig(_host, "mbh_rank", C.c_char_p, [vp, i32])
+_sig(_host, "mbh_db_kmers", u64, [vp])
+_sig(_host, "mbh_db_words", u64, [vp])
+_sig(_host, "mbh_classify_files", C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
+                                            C.c_float, C.c_float, u64])
+
+
+class MetabuliError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"[{code}] {msg}")
+        self.code = code
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def pack_reads(mates1, mates2=None):
+    """-> (bases uint8[], offsets uint64[2n], lens uint32[2n]) in the layout of mb_classify_batch."""
+    n = len(mates1)
+    lens = np.zeros(2 * n, dtype=np.uint32)
+    l1 = np.fromiter((len(s) for s in mates1), dtype=np.uint32, count=n)
+    lens[0::2] = l1
+    if mates2 is not None:
+        lens[1::2] = np.fromiter((len(s) for s in mates2), dtype=np.uint32, count=n)
+    offsets = np.zeros(2 * n, dtype=np.uint64)
+    if n:
+        offsets[1:] = np.cumsum(lens[:-1], dtype=np.uint64)
+    chunks = []
+    for i in range(n):
+        s = mates1[i]
+        chunks.append(s.encode() if isinstance(s, str) else s)
+        if mates2 is not None:
+            s = mates2[i]
+            chunks.append(s.encode() if isinstance(s, str) else s)
+    bases = np.frombuffer(b"".join(chunks), dtype=np.uint8).copy() if chunks else np.zeros(0, dtype=np.uint8)
+    return bases, offsets, lens
+
+
+class Classifier:
+    """One GPU context with a resident database: the Python mirror of the per-batch calls that
+    Classifier::startClassify makes (src/commons/Classifier.cpp:105-119)."""
+
+    def __init__(self, dbdir, device=0, seq_mode=2, min_score=0.0, min_sp_score=0.0, shard=0, n_shards=1):
+        self.h = _host.mbh_open(os.fsencode(dbdir), device, seq_mode, min_score, min_sp_score, shard, n_shards)
+        if not self.h:
+            raise MetabuliError(-1, _host.mbh_last_error().decode())
+        self.ctx = _host.mbh_ctx(self.h)
+        self.n_reads = 0
+
+    def close(self):
+        if self.h:
+            _host.mbh_close(self.h)
+            self.h = None
+
+    def _ck(self, rc):
+        if rc != MB_OK:
+            raise MetabuliError(rc, _cuda.mb_last_error(self.ctx).decode())
+
+    @property
+    def params(self):
+        p = Params()
+        _host.mbh_params(self.h, C.byref(p))
+        return p
+
+    def set_params(self, **kw):
+        p = self.params
+        for k, v in kw.items():
+            setattr(p, k, v)
+        self._ck(_cuda.mb_set_params(self.ctx, C.byref(p)))
+
+    def shard_bounds(self):
+        n = _host.mbh_num_bounds(self.h)
+        out = np.zeros(max(n, 1), dtype=np.uint64)
+        _host.mbh_bounds(self.h, _ptr(out))
+        return out[:n]
+
+    def db_kmers(self):
+        return _host.mbh_db_kmers(self.h)
+
+    def db_words(self):
+        return _host.mbh_db_words(self.h)
+
+    def original_taxid(self, t):
+        return _host.mbh_original_taxid(self.h, int(t))
+
+    def decode_db(self):
+        n = self.db_kmers()
+        out = np.zeros(n, dtype=np.uint64)
+        got = C.c_size_t(0)
+        self._ck(_cuda.mb_decode_db(self.ctx, _ptr(out), n, C.byref(got)))
+        return out[:got.value]
+
+    # ---- stages ----
+    def stage(self, bases, offsets, lens, bases_ptr=None):
+        self.n_reads = len(lens) // 2
+        self._keep = (bases, offsets, lens)
+        bp = bases_ptr if bases_ptr is not None else _ptr(bases)
+        self._ck(_cuda.mb_stage_reads(self.ctx, bp, len(bases), _ptr(offsets), _ptr(lens), self.n_reads))
+
+    def extract(self):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_extract_kmers(self.ctx, C.byref(n)))
+        return n.value
+
+    def sort_kmers(self):
+        self._ck(_cuda.mb_sort_kmers(self.ctx))
+
+    def match(self):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_match_kmers(self.ctx, C.byref(n)))
+        return n.value
+
+    def sort_matches(self):
+        self._ck(_cuda.mb_sort_matches(self.ctx))
+
+    def score(self):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_score_reads(self.ctx, C.byref(n)))
+        return n.value
+
+    def classify_staged(self):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_classify_staged(self.ctx, C.byref(n)))
+        return n.value
+
+    def fetch(self, used):
+        res = np.zeros(self.n_reads, dtype=RESULT_DT)
+        ids = np.zeros(used + 1, dtype=np.int32)
+        cnt = np.zeros(used + 1, dtype=np.int32)
+        self._ck(_cuda.mb_fetch_results(self.ctx, _ptr(res), _ptr(ids), _ptr(cnt), used + 1))
+        return res, ids[:used], cnt[:used]
+
+    def kmers(self):
+        n = C.c_size_t(0)
+        rc = _cuda.mb_copy_kmers(self.ctx, None, 0, C.byref(n))
+        if rc not in (MB_OK, MB_E_CAPACITY):
+            self._ck(rc)
+        out = np.zeros(n.value, dtype=KMER_DT)
+        self._ck(_cuda.mb_copy_kmers(self.ctx, _ptr(out), n.value, C.byref(n)))
+        return out
+
+    def matches(self):
+        n = C.c_size_t(0)
+        rc = _cuda.mb_copy_matches(self.ctx, None, 0, C.byref(n))
+        if rc not in (MB_OK, MB_E_CAPACITY):
+            self._ck(rc)
+        out = np.zeros(n.value, dtype=MATCH_DT)
+        self._ck(_cuda.mb_copy_matches(self.ctx, _ptr(out), n.value, C.byref(n)))
+        return out
+
+    def set_kmers(self, k):
+        k = np.ascontiguousarray(k, dtype=KMER_DT)
+        self._ck(_cuda.mb_set_kmers(self.ctx, _ptr(k), len(k)))
+
+    def set_matches(self, m):
+        m = np.ascontiguousarray(m, dtype=MATCH_DT)
+        self._ck(_cuda.mb_set_matches(self.ctx, _ptr(m), len(m)))
+
+    def kmers_device(self):
+        p, n = C.c_void_p(0), C.c_size_t(0)
+        self._ck(_cuda.mb_kmers_device(self.ctx, C.byref(p), C.byref(n)))
+        return p.value or 0, n.value
+
+    def matches_device(self):
+        p, n = C.c_void_p(0), C.c_size_t(0)
+        self._ck(_cuda.mb_matches_device(self.ctx, C.byref(p), C.byref(n)))
+        return p.value or 0, n.value
+
+    def set_kmers_device(self, dptr, n):
+        self._ck(_cuda.mb_set_kmers_device(self.ctx, C.c_void_p(dptr), n))
+
+    def set_matches_device(self, dptr, n):
+        self._ck(_cuda.mb_set_matches_device(self.ctx, C.c_void_p(dptr), n))
+
+    def partition_kmers(self, bounds):
+        bounds = np.ascontiguousarray(bounds, dtype=np.uint64)
+        counts = np.zeros(len(bounds) + 1, dtype=np.uint64)
+        self._ck(_cuda.mb_partition_kmers(self.ctx, _ptr(bounds), len(bounds) + 1, _ptr(counts)))
+        return counts
+
+    def partition_matches(self, reads_per_rank, n_ranks):
+        counts = np.zeros(n_ranks, dtype=np.uint64)
+        self._ck(_cuda.mb_partition_matches(self.ctx, reads_per_rank, n_ranks, _ptr(counts)))
+        return counts
+
+    def timings(self):
+        t = PhaseTimes()
+        self._ck(_cuda.mb_get_timings(self.ctx, C.byref(t)))
+        return t.as_dict()
+
+    def stream(self):
+        return _cuda.mb_stream(self.ctx)
+
+    # ---- whole path, host buffers in / host buffers out (mb_classify_batch) ----
+    def classify(self, bases, offsets, lens, bases_ptr=None):
+        self.n_reads = len(lens) // 2
+        res = np.zeros(self.n_reads, dtype=RESULT_DT)
+        cap = max(1024, 8 * self.n_reads)
+        while True:
+            ids = np.zeros(cap, dtype=np.int32)
+            cnt = np.zeros(cap, dtype=np.int32)
+            used = C.c_size_t(0)
+            bp = bases_ptr if bases_ptr is not None else _ptr(bases)
+            rc = _cuda.mb_classify_batch(self.ctx, bp, len(bases), _ptr(offsets), _ptr(lens), self.n_reads, _ptr(res),
+                                         _ptr(ids), _ptr(cnt), cap, C.byref(used))
+            if rc == MB_E_CAPACITY and used.value > cap:
+                cap = used.value
+                continue
+            self._ck(rc)
+            return res, ids[:used.value], cnt[:used.value]
+
+
+def classify_files(reads1, reads2, dbdir, outdir, jobid, seq_mode=2, device=0, min_score=0.0, min_sp_score=0.0, batch_reads=0):
+    rc = _host.mbh_classify_files(os.fsencode(reads1), os.fsencode(reads2 or ""), os.fsencode(dbdir), os.fsencode(outdir),
+                                  jobid.encode(), seq_mode, device, min_score, min_sp_score, batch_reads)
+    if rc != 0:
+        raise MetabuliError(rc, _host.mbh_last_error().decode())

@@ -1,0 +1,755 @@
+// mb_api.cu — the C ABI of libmetabuli_b200.so (include/metabuli_b200.h): context, HBM-resident
+// database / taxonomy, and the launch sequence of the classification hot path.
+//
+// Replaces the body of Classifier::startClassify's per-batch loop (src/commons/Classifier.cpp:81-150):
+//   extractQueryKmers -> matchKmers -> sortMatches -> assignTaxonomy.
+// Everything runs on one CUDA stream; the only host synchronisations per batch are four 8-byte
+// read-backs (k-mer count, match count, longest per-read match list, taxCnt size) that size the next
+// launch.  There is no CPU fallback anywhere in this file.
+#include "mb_common.cuh"
+#include "mb_extract.cuh"
+#include "mb_radix.cuh"
+#include "mb_match.cuh"
+#include "mb_score.cuh"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace mb;
+
+namespace {
+
+thread_local std::string g_global_err;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { p = nullptr; return e; }
+        cap = want;
+        return cudaSuccess;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+enum { EV_START, EV_H2D, EV_EXTRACT, EV_SORTK, EV_MATCH, EV_SORTM, EV_SCORE, EV_D2H, EV_COUNT };
+
+struct Counters {                 // device-side scalars, one allocation
+    unsigned long long match_count;
+    unsigned long long tc_count;
+    u32 error_flag;
+    u32 max_seg;
+    u32 score_ticket;
+    u32 radix_ticket;
+    u32 trivial[RS_MAX_PASSES];
+};
+
+} // namespace
+
+struct mb_ctx {
+    mb_params par;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    DevBuf tables;
+    // database
+    DevBuf words, info, blocks, blk_back, blk_cnt, blk_kidx, blk_vbefore;
+    u64 n_words = 0, n_db_kmers = 0;
+    u32 n_blocks = 0;
+    // taxonomy
+    DevBuf parent, depth, species_of, species_rank_of;
+    int32_t max_taxid = -1, node0 = 0, euk = 0;
+    // batch
+    DevBuf bases, offsets, lens;
+    u64 n_bases = 0;
+    u32 n_reads = 0;
+    u64 kmer_bound = 0;
+    u32 max_query_len = 0;
+    DevBuf tile_mate, tile_counts, tile_offsets;
+    DevBuf kmers_a, kmers_b;
+    u64 n_kmers = 0;
+    DevBuf hist, tile_state;
+    DevBuf qstart, matches_a, matches_b;
+    u64 n_matches = 0;
+    DevBuf seg_begin, seg_end, results, tc_id, tc_cnt, arena;
+    u64 tc_used = 0;
+    DevBuf counters;
+    void *pinned = nullptr;       // 256-byte pinned scratch for read-backs
+    cudaEvent_t ev[EV_COUNT];
+    bool ev_set[EV_COUNT];
+    mb_phase_times times;
+    u32 launches = 0;
+    bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
+
+    Counters *dcnt() const { return counters.as<Counters>(); }
+};
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            char buf_[512];                                                                          \
+            snprintf(buf_, sizeof(buf_), "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            ctx->err = buf_;                                                                         \
+            return MB_E_CUDA;                                                                        \
+        }                                                                                            \
+    } while (0)
+
+#define LAUNCH_CHECK()                                                                               \
+    do { ++ctx->launches; CK(cudaGetLastError()); } while (0)
+
+static int fail(mb_ctx *ctx, int code, const char *msg) { ctx->err = msg; return code; }
+
+static inline int bits_for(u64 v) { int b = 1; while (b < 63 && (v >> b)) ++b; return b; }
+
+static void mark(mb_ctx *ctx, int ev) {
+    cudaEventRecord(ctx->ev[ev], ctx->stream);
+    ctx->ev_set[ev] = true;
+}
+
+template <class T>
+static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
+    CK(cudaMemcpyAsync(ctx->pinned, dptr, sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    memcpy(out, ctx->pinned, sizeof(T));
+    return MB_OK;
+}
+
+// ---- radix sort driver --------------------------------------------------------------------------------
+template <typename Rec, typename Key, int ITEMS>
+static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes) {
+    if (n == 0 || n_passes == 0) return MB_OK;
+    if (n_passes > RS_MAX_PASSES) return fail(ctx, MB_E_ARG, "too many radix passes");
+    constexpr u64 TILE = (u64) RS_THREADS * ITEMS;
+    const u64 tiles = (n + TILE - 1) / TILE;
+    CK(b.ensure(n * sizeof(Rec)));
+    CK(ctx->hist.ensure(sizeof(u64) * RS_BINS * RS_MAX_PASSES));
+    CK(ctx->tile_state.ensure(tiles * RS_BINS * sizeof(u64)));
+    CK(cudaMemsetAsync(ctx->hist.p, 0, sizeof(u64) * RS_BINS * n_passes, ctx->stream));
+    CK(cudaMemsetAsync(&ctx->dcnt()->trivial, 0, sizeof(u32) * RS_MAX_PASSES, ctx->stream));
+    const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+    k_radix_hist<Rec, Key><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
+        a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>());
+    LAUNCH_CHECK();
+    k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial);
+    LAUNCH_CHECK();
+    constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        attr_set = true;
+    }
+    for (int p = 0; p < n_passes; ++p) {
+        CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * RS_BINS * sizeof(u64), ctx->stream));
+        CK(cudaMemsetAsync(&ctx->dcnt()->radix_ticket, 0, sizeof(u32), ctx->stream));
+        k_radix_pass<Rec, Key, ITEMS><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
+            a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
+            &ctx->dcnt()->radix_ticket);
+        LAUNCH_CHECK();
+        std::swap(a.p, b.p);
+        std::swap(a.cap, b.cap);
+    }
+    return MB_OK;
+}
+
+// stable multi-way partition = one radix pass whose digit is the destination rank
+template <typename Rec, typename Key, int ITEMS>
+static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_parts, uint64_t *counts) {
+    for (int i = 0; i < n_parts; ++i) counts[i] = 0;
+    if (n == 0) return MB_OK;
+    if (int rc = radix_sort<Rec, Key, ITEMS>(ctx, a, b, n, key, 1)) return rc;
+    // digit_base (exclusive scan of the histogram) is still in ctx->hist
+    std::vector<u64> base(RS_BINS);
+    CK(cudaMemcpyAsync(base.data(), ctx->hist.p, RS_BINS * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < n_parts; ++i) counts[i] = (i + 1 < RS_BINS ? base[i + 1] : n) - base[i];
+    counts[n_parts - 1] = n - base[n_parts - 1];
+    return MB_OK;
+}
+
+extern "C" {
+
+void mb_default_params(mb_params *p) {
+    memset(p, 0, sizeof(*p));
+    p->device = 0; p->kmer_format = 1; p->syncmer = 0; p->smer_len = 5; p->seq_mode = 2;
+    p->min_cons_cnt = 4; p->min_cons_cnt_euk = 9; p->min_score = 0.f; p->min_sp_score = 0.f; p->tie_ratio = 0.95f;
+    p->skip_redundancy = 0; p->accession_level = 0; p->last_shard = 1;
+}
+
+const char *mb_global_error(void) { return g_global_err.c_str(); }
+const char *mb_last_error(const mb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_global_err.c_str(); }
+
+static int check_params(const mb_params *p, std::string &err) {
+    if (p->kmer_format != 1 && p->kmer_format != 2) { err = "kmer_format must be 1 or 2"; return MB_E_ARG; }
+    if (p->seq_mode < 1 || p->seq_mode > 3) { err = "seq_mode must be 1, 2 or 3"; return MB_E_ARG; }
+    if (p->syncmer && (p->smer_len < 1 || p->smer_len > 7)) { err = "smer_len must be in 1..7"; return MB_E_ARG; }
+    if (p->accession_level != 0) { err = "accession_level != 0 is not on this path"; return MB_E_ARG; }
+    return MB_OK;
+}
+
+mb_ctx *mb_create(const mb_params *p) {
+    if (!p) { g_global_err = "null params"; return nullptr; }
+    if (check_params(p, g_global_err) != MB_OK) return nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        g_global_err = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (libmetabuli_b200 has no CPU fallback)";
+        return nullptr;
+    }
+    if (p->device < 0 || p->device >= n_dev) { g_global_err = "device ordinal out of range"; return nullptr; }
+    if ((e = cudaSetDevice(p->device)) != cudaSuccess) { g_global_err = cudaGetErrorString(e); return nullptr; }
+    mb_ctx *ctx = new mb_ctx();
+    ctx->par = *p;
+    memset(&ctx->times, 0, sizeof(ctx->times));
+    for (int i = 0; i < EV_COUNT; ++i) ctx->ev_set[i] = false;
+    bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < EV_COUNT; ++i) ok = cudaEventCreate(&ctx->ev[i]) == cudaSuccess;
+    ok = ok && cudaHostAlloc(&ctx->pinned, 256, cudaHostAllocDefault) == cudaSuccess;
+    ok = ok && ctx->tables.ensure(sizeof(Tables)) == cudaSuccess && ctx->counters.ensure(sizeof(Counters)) == cudaSuccess;
+    if (ok) {
+        Tables t;
+        build_tables(t);
+        ok = cudaMemcpy(ctx->tables.p, &t, sizeof(t), cudaMemcpyHostToDevice) == cudaSuccess &&
+             cudaMemset(ctx->counters.p, 0, sizeof(Counters)) == cudaSuccess;
+    }
+    if (!ok) {
+        g_global_err = std::string("context setup failed: ") + cudaGetErrorString(cudaGetLastError());
+        delete ctx;
+        return nullptr;
+    }
+    return ctx;
+}
+
+void mb_destroy(mb_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->par.device);
+    cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < EV_COUNT; ++i) cudaEventDestroy(ctx->ev[i]);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int mb_set_params(mb_ctx *ctx, const mb_params *p) {
+    if (!ctx || !p) return MB_E_ARG;
+    if (int rc = check_params(p, ctx->err)) return rc;
+    if (p->device != ctx->par.device) return fail(ctx, MB_E_ARG, "device cannot change");
+    const bool reshard = p->last_shard != ctx->par.last_shard;
+    if (reshard && ctx->n_words) return fail(ctx, MB_E_ARG, "last_shard cannot change after mb_load_db");
+    ctx->par = *p;
+    ctx->have_kmers = ctx->have_matches = ctx->have_results = false;
+    return MB_OK;
+}
+
+void *mb_stream(mb_ctx *ctx) { return ctx ? (void *) ctx->stream : nullptr; }
+
+// ---- database ---------------------------------------------------------------------------------------
+static DbView db_view(const mb_ctx *ctx, bool for_index) {
+    DbView v;
+    v.words = ctx->words.as<u16>();
+    v.n_words = ctx->n_words;
+    v.info = ctx->info.as<u32>();
+    v.n_kmers_eff = for_index ? ~0ull : (ctx->par.last_shard ? (ctx->n_db_kmers ? ctx->n_db_kmers - 1 : 0) : ctx->n_db_kmers);
+    v.info_mask = ~(((u32) (ctx->par.skip_redundancy == 0)) << 31);
+    v.species_of = ctx->species_of.as<int32_t>();
+    v.max_taxid = ctx->max_taxid;
+    return v;
+}
+
+int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint32_t *info, size_t n_kmers) {
+    if (!ctx || (!diffIdx && n_words) || (!info && n_kmers)) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    ctx->n_words = 0;
+    ctx->n_db_kmers = 0;
+    ctx->n_blocks = 0;
+    CK(ctx->words.ensure((n_words + DB_PAD) * sizeof(u16)));
+    CK(ctx->info.ensure((n_kmers + 16) * sizeof(u32)));
+    CK(cudaMemsetAsync(ctx->words.as<u16>() + n_words, 0, DB_PAD * sizeof(u16), ctx->stream));
+    CK(cudaMemcpyAsync(ctx->words.p, diffIdx, n_words * sizeof(u16), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->info.p, info, n_kmers * sizeof(u32), cudaMemcpyHostToDevice, ctx->stream));
+    ctx->n_words = n_words;
+    ctx->n_db_kmers = n_kmers;
+    const u32 nb = (u32) ((n_words + DB_W - 1) / DB_W);
+    ctx->n_blocks = nb;
+    if (nb == 0) { CK(cudaStreamSynchronize(ctx->stream)); return MB_OK; }
+    CK(ctx->blk_back.ensure(nb * sizeof(u32)));
+    CK(ctx->blk_cnt.ensure(nb * sizeof(u32)));
+    CK(ctx->blk_kidx.ensure(nb * sizeof(u64)));
+    CK(ctx->blk_vbefore.ensure(nb * sizeof(u64)));
+    CK(ctx->blocks.ensure(nb * sizeof(BlockIndex)));
+    DevBuf blk_sum;
+    CK(blk_sum.ensure(nb * sizeof(u64)));
+    const DbView v = db_view(ctx, true);
+    k_db_block_summary<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_cnt.as<u32>(), blk_sum.as<u64>());
+    LAUNCH_CHECK();
+    // The scan over blocks is a load-time step on a few MB: done on the host.
+    std::vector<u32> cnt(nb);
+    std::vector<u64> sum(nb), kidx(nb), vbefore(nb);
+    CK(cudaMemcpyAsync(cnt.data(), ctx->blk_cnt.p, nb * sizeof(u32), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(sum.data(), blk_sum.p, nb * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    u64 k = 0, s = 0;
+    for (u32 b = 0; b < nb; ++b) { kidx[b] = k; vbefore[b] = s; k += cnt[b]; s += sum[b]; }
+    if (k != n_kmers) {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "diffIdx holds %llu k-mers but info holds %llu entries", (unsigned long long) k, (unsigned long long) n_kmers);
+        ctx->n_words = 0; ctx->n_db_kmers = 0; ctx->n_blocks = 0;
+        return fail(ctx, MB_E_DATA, msg);
+    }
+    CK(cudaMemcpyAsync(ctx->blk_kidx.p, kidx.data(), nb * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->blk_vbefore.p, vbefore.data(), nb * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    k_db_block_own<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_kidx.as<u64>(),
+                                                        ctx->blk_vbefore.as<u64>(), ctx->blocks.as<BlockIndex>());
+    LAUNCH_CHECK();
+    std::vector<BlockIndex> bi(nb);
+    CK(cudaMemcpyAsync(bi.data(), ctx->blocks.p, nb * sizeof(BlockIndex), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    u64 next_aa = ~0ull;                      // blocks that own nothing take the next owner's AA (empty query slice)
+    for (u32 b = nb; b-- > 0;) {
+        if (bi[b].owns) next_aa = bi[b].own_aa; else bi[b].own_aa = next_aa;
+    }
+    CK(cudaMemcpyAsync(ctx->blocks.p, bi.data(), nb * sizeof(BlockIndex), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->times.db_words = n_words;
+    ctx->times.db_kmers = n_kmers;
+    return MB_OK;
+}
+
+int mb_decode_db(mb_ctx *ctx, uint64_t *values_out, size_t cap, size_t *n_out) {
+    if (!ctx || !n_out) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    *n_out = ctx->n_db_kmers;
+    if (cap < ctx->n_db_kmers) return fail(ctx, MB_E_CAPACITY, "values_out too small");
+    if (ctx->n_db_kmers == 0) return MB_OK;
+    DevBuf vals;
+    CK(vals.ensure(ctx->n_db_kmers * sizeof(u64)));
+    k_db_decode<<<ctx->n_blocks, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, true), ctx->n_blocks, ctx->blk_back.as<u32>(),
+                                                              ctx->blk_cnt.as<u32>(), ctx->blk_kidx.as<u64>(),
+                                                              ctx->blk_vbefore.as<u64>(), vals.as<u64>());
+    LAUNCH_CHECK();
+    CK(cudaMemcpyAsync(values_out, vals.p, ctx->n_db_kmers * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+// ---- taxonomy ---------------------------------------------------------------------------------------
+int mb_load_taxonomy(mb_ctx *ctx, const int32_t *parent, const int32_t *species_of, const int32_t *species_rank_of,
+                     int32_t max_taxid, int32_t node0_taxid, int32_t eukaryota_taxid) {
+    if (!ctx || !parent || !species_of || !species_rank_of || max_taxid < 0) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    const size_t n = (size_t) max_taxid + 1;
+    // depth by memoised parent walk (root: parent == self)
+    std::vector<int32_t> depth(n, -1);
+    std::vector<int32_t> chain;
+    for (size_t t = 0; t < n; ++t) {
+        if (parent[t] < 0 || depth[t] >= 0) continue;
+        chain.clear();
+        int32_t x = (int32_t) t;
+        while (depth[x] < 0) {
+            const int32_t p = parent[x];
+            if (p < 0 || p > max_taxid || parent[p] < 0) return fail(ctx, MB_E_DATA, "taxonomy: parent of an existing taxon does not exist");
+            chain.push_back(x);
+            if (p == x) { depth[x] = 0; chain.pop_back(); break; }
+            if (chain.size() > n) return fail(ctx, MB_E_DATA, "taxonomy: cycle in the parent array");
+            x = p;
+        }
+        int32_t d = depth[x];
+        for (size_t k = chain.size(); k-- > 0;) depth[chain[k]] = ++d;
+    }
+    CK(ctx->parent.ensure(n * 4)); CK(ctx->depth.ensure(n * 4));
+    CK(ctx->species_of.ensure(n * 4)); CK(ctx->species_rank_of.ensure(n * 4));
+    CK(cudaMemcpyAsync(ctx->parent.p, parent, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->depth.p, depth.data(), n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->species_of.p, species_of, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->species_rank_of.p, species_rank_of, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->max_taxid = max_taxid;
+    ctx->node0 = node0_taxid;
+    ctx->euk = eukaryota_taxid;
+    return MB_OK;
+}
+
+// ---- stages -----------------------------------------------------------------------------------------
+int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
+                   uint32_t n_reads) {
+    if (!ctx || (!bases && n_bases) || ((!offsets || !lens) && n_reads)) return MB_E_ARG;
+    if (n_reads >= (1u << 29)) return fail(ctx, MB_E_ARG, "at most 2^29-1 reads per batch (29-bit sequenceID, Kmer.h:11-16)");
+    CK(cudaSetDevice(ctx->par.device));
+    ctx->have_reads = ctx->have_kmers = ctx->have_matches = ctx->have_results = false;
+    // host pass over the lengths: layout check, k-mer slot bound (QueryIndexer.cpp:62-67), longest query
+    u64 bound = 0, prev_end = 0;
+    u32 max_q = 0;
+    const bool paired = ctx->par.seq_mode == 2;
+    for (u32 i = 0; i < n_reads; ++i) {
+        u32 ql = 0;
+        for (int mt = 0; mt < 2; ++mt) {
+            const u64 off = offsets[2 * i + mt];
+            const u32 len = lens[2 * i + mt];
+            if (off < prev_end || off + len > n_bases) return fail(ctx, MB_E_ARG, "mates must be packed back to back in increasing offset order");
+            prev_end = off + len;
+            if (mt == 1 && !paired) continue;
+            const int kn = query_kmer_number((int) len);
+            if (kn > 0) { bound += (u64) kn; ql += (u32) max_covered_length((int) len); }
+        }
+        max_q = std::max(max_q, ql);
+    }
+    mark(ctx, EV_START);
+    CK(ctx->bases.ensure(n_bases + 128));
+    CK(ctx->offsets.ensure((size_t) n_reads * 2 * sizeof(u64) + 16));
+    CK(ctx->lens.ensure((size_t) n_reads * 2 * sizeof(u32) + 16));
+    CK(cudaMemcpyAsync(ctx->bases.p, bases, n_bases, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(ctx->bases.as<u8>() + n_bases, 0, 128, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->offsets.p, offsets, (size_t) n_reads * 2 * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->lens.p, lens, (size_t) n_reads * 2 * sizeof(u32), cudaMemcpyHostToDevice, ctx->stream));
+    mark(ctx, EV_H2D);
+    ctx->n_bases = n_bases;
+    ctx->n_reads = n_reads;
+    ctx->kmer_bound = bound;
+    ctx->max_query_len = max_q + 8;
+    ctx->have_reads = true;
+    ctx->launches = 0;
+    ctx->times.match_retries = 0;
+    return MB_OK;
+}
+
+int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "mb_stage_reads first");
+    CK(cudaSetDevice(ctx->par.device));
+    ctx->have_kmers = ctx->kmers_sorted = ctx->have_matches = ctx->have_results = false;
+    ctx->n_kmers = 0;
+    const u32 n_tiles = (u32) ((ctx->n_bases + EX_TILE - 1) / EX_TILE);
+    if (n_tiles && ctx->n_reads) {
+        ExtractArgs a;
+        a.bases = ctx->bases.as<u8>(); a.n_bases = ctx->n_bases; a.offsets = ctx->offsets.as<u64>(); a.lens = ctx->lens.as<u32>();
+        a.n_mates = ctx->n_reads * 2; a.seq_mode = ctx->par.seq_mode; a.format = ctx->par.kmer_format;
+        a.syncmer = ctx->par.syncmer; a.smer_len = ctx->par.smer_len;
+        CK(ctx->tile_mate.ensure(((size_t) n_tiles + 1) * sizeof(u32)));
+        CK(ctx->tile_counts.ensure((size_t) n_tiles * sizeof(u32)));
+        CK(ctx->tile_offsets.ensure(((size_t) n_tiles + 1) * sizeof(u64)));
+        CK(ctx->kmers_a.ensure((ctx->kmer_bound + 1) * sizeof(mb_kmer)));
+        k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>());
+        LAUNCH_CHECK();
+        k_extract<false><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
+                                                                 ctx->tile_counts.as<u32>(), nullptr, nullptr);
+        LAUNCH_CHECK();
+        k_scan_counts<<<1, 1024, 0, ctx->stream>>>(ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(), n_tiles);
+        LAUNCH_CHECK();
+        k_extract<true><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
+                                                                ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(),
+                                                                ctx->kmers_a.as<mb_kmer>());
+        LAUNCH_CHECK();
+        u64 total = 0;
+        if (int rc = read_back(ctx, ctx->tile_offsets.as<u64>() + n_tiles, &total)) return rc;
+        if (total > ctx->kmer_bound) return fail(ctx, MB_E_DATA, "internal: extracted more k-mers than the slot bound");
+        ctx->n_kmers = total;
+    }
+    mark(ctx, EV_EXTRACT);
+    ctx->have_kmers = true;
+    if (n_kmers) *n_kmers = ctx->n_kmers;
+    return MB_OK;
+}
+
+int mb_sort_kmers(mb_ctx *ctx) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    CK(cudaSetDevice(ctx->par.device));
+    KmerKey key;
+    key.first_bit = 24;   // the join needs the amino-acid parts grouped in increasing order; 5 passes of 8 bits
+    if (int rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, 5)) return rc;
+    mark(ctx, EV_SORTK);
+    ctx->kmers_sorted = true;
+    return MB_OK;
+}
+
+int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_kmers || !ctx->kmers_sorted) return fail(ctx, MB_E_ARG, "sorted k-mers required");
+    if (ctx->max_taxid < 0) return fail(ctx, MB_E_ARG, "mb_load_taxonomy first");
+    CK(cudaSetDevice(ctx->par.device));
+    ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
+    ctx->n_matches = 0;
+    if (ctx->n_blocks && ctx->n_kmers) {
+        const u32 nb = ctx->n_blocks;
+        CK(ctx->qstart.ensure(((size_t) nb + 1) * sizeof(u64)));
+        k_match_partition<<<(nb + 1 + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
+                                                                       ctx->n_kmers, ctx->qstart.as<u64>());
+        LAUNCH_CHECK();
+        size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
+        for (int attempt = 0; attempt < 3; ++attempt) {
+            CK(ctx->matches_a.ensure(cap * sizeof(mb_match)));
+            cap = ctx->matches_a.cap / sizeof(mb_match);
+            CK(cudaMemsetAsync(&ctx->dcnt()->match_count, 0, sizeof(unsigned long long), ctx->stream));
+            CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
+            MatchOut mo;
+            mo.out = ctx->matches_a.as<mb_match>(); mo.cap = cap; mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag;
+            k_match<<<nb, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, false), ctx->blocks.as<BlockIndex>(), ctx->kmers_a.as<mb_kmer>(),
+                                                      ctx->qstart.as<u64>(), mo, ctx->tables.as<Tables>(), ctx->par.kmer_format);
+            LAUNCH_CHECK();
+            unsigned long long total = 0;
+            if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;
+            if (total <= cap) { ctx->n_matches = total; break; }
+            // capacity miss: the kernel counted everything but wrote only what fits; size exactly and rerun
+            ++ctx->times.match_retries;
+            cap = (size_t) total;
+            if (attempt == 2) return fail(ctx, MB_E_CAPACITY, "match buffer could not be sized");
+        }
+        u32 flag = 0;
+        if (int rc = read_back(ctx, &ctx->dcnt()->error_flag, &flag)) return rc;
+        if (flag) return fail(ctx, MB_E_DATA, "a DB k-mer carries a tax ID without species mapping (KmerMatcher.cpp:433-441)");
+    }
+    mark(ctx, EV_MATCH);
+    ctx->have_matches = true;
+    if (n_matches) *n_matches = ctx->n_matches;
+    return MB_OK;
+}
+
+static MatchKey match_key(const mb_ctx *ctx) {
+    MatchKey k;
+    // pos < queryLength + 3 (mate 2 offset, KmerExtractor.cpp:339-347)
+    k.pos_bits = bits_for((u64) ctx->max_query_len + 8);
+    k.sp_bits = bits_for((u64) std::max(ctx->max_taxid, 1));
+    k.seq_bits = bits_for((u64) ctx->n_reads + 1);
+    return k;
+}
+
+int mb_sort_matches(mb_ctx *ctx) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    CK(cudaSetDevice(ctx->par.device));
+    const MatchKey key = match_key(ctx);
+    const int passes = (key.total_bits() + 7) / 8;
+    if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes)) return rc;
+    mark(ctx, EV_SORTM);
+    ctx->matches_sorted = true;
+    return MB_OK;
+}
+
+int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_matches || !ctx->matches_sorted) return fail(ctx, MB_E_ARG, "sorted matches required");
+    if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "reads must be staged (lengths are needed)");
+    CK(cudaSetDevice(ctx->par.device));
+    const u32 nr = ctx->n_reads;
+    ctx->tc_used = 0;
+    if (nr) {
+        CK(ctx->seg_begin.ensure((size_t) nr * sizeof(u64)));
+        CK(ctx->seg_end.ensure((size_t) nr * sizeof(u64)));
+        CK(ctx->results.ensure((size_t) nr * sizeof(mb_read_result)));
+        CK(cudaMemsetAsync(ctx->seg_begin.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
+        CK(cudaMemsetAsync(ctx->seg_end.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
+        CK(cudaMemsetAsync(&ctx->dcnt()->max_seg, 0, sizeof(u32), ctx->stream));
+        CK(cudaMemsetAsync(&ctx->dcnt()->tc_count, 0, sizeof(unsigned long long), ctx->stream));
+        CK(cudaMemsetAsync(&ctx->dcnt()->score_ticket, 0, sizeof(u32), ctx->stream));
+        CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
+        u32 max_seg = 0;
+        if (ctx->n_matches) {
+            k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), &ctx->dcnt()->max_seg);
+            LAUNCH_CHECK();
+            k_segment_max<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), nr, &ctx->dcnt()->max_seg);
+            LAUNCH_CHECK();
+            if (int rc = read_back(ctx, &ctx->dcnt()->max_seg, &max_seg)) return rc;
+        }
+        ScoreCfg cfg;
+        cfg.format = ctx->par.kmer_format;
+        if (ctx->par.syncmer) { cfg.dna_shift = (8 - ctx->par.smer_len) * 3; cfg.max_codon_shift = 8 - ctx->par.smer_len; }
+        else { cfg.dna_shift = 3; cfg.max_codon_shift = 1; }
+        cfg.denominator = (ctx->par.seq_mode == 1 || ctx->par.seq_mode == 2) ? 100 : 1000;
+        cfg.min_cons_cnt = ctx->par.min_cons_cnt; cfg.min_cons_cnt_euk = ctx->par.min_cons_cnt_euk;
+        cfg.min_score = ctx->par.min_score; cfg.min_sp_score = ctx->par.min_sp_score; cfg.tie_ratio = ctx->par.tie_ratio;
+        TaxView tv;
+        tv.parent = ctx->parent.as<int32_t>(); tv.depth = ctx->depth.as<int32_t>(); tv.species_of = ctx->species_of.as<int32_t>();
+        tv.species_rank_of = ctx->species_rank_of.as<int32_t>(); tv.max_taxid = ctx->max_taxid; tv.node0_taxid = ctx->node0;
+        tv.eukaryota = ctx->euk;
+        ScoreArena arena;
+        arena.cap_n = (int) std::max<u32>(max_seg, 16);
+        arena.cap_b = (int) ((ctx->max_query_len + 3) / (u32) cfg.dna_shift + 2);
+        arena.cap_c = 4 * arena.cap_b + 64;
+        arena.slice_bytes = arena_slice_bytes(arena.cap_n, arena.cap_b, arena.cap_c);
+        // resident warps: enough to fill the machine, bounded by an 8-GB arena
+        const u64 budget = 8ull << 30;
+        u64 warps = std::min<u64>(148ull * 16 * (SC_THREADS / 32), std::max<u64>(budget / arena.slice_bytes, SC_THREADS / 32));
+        warps = std::min<u64>(warps, ((u64) nr + 3) / 4 + (SC_THREADS / 32));
+        const unsigned grid = (unsigned) std::max<u64>(1, warps / (SC_THREADS / 32));
+        CK(ctx->arena.ensure((size_t) grid * (SC_THREADS / 32) * arena.slice_bytes));
+        arena.base = ctx->arena.as<unsigned char>();
+        const size_t tc_cap = std::max<size_t>(ctx->n_matches, 16);
+        CK(ctx->tc_id.ensure(tc_cap * sizeof(int32_t)));
+        CK(ctx->tc_cnt.ensure(tc_cap * sizeof(int32_t)));
+        k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(),
+                                                    ctx->lens.as<u32>(), nr, ctx->par.seq_mode == 2 ? 1 : 0, cfg, tv, arena,
+                                                    ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(),
+                                                    (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag);
+        LAUNCH_CHECK();
+        unsigned long long used = 0;
+        if (int rc = read_back(ctx, &ctx->dcnt()->tc_count, &used)) return rc;
+        u32 flag = 0;
+        if (int rc = read_back(ctx, &ctx->dcnt()->error_flag, &flag)) return rc;
+        if (flag) {
+            char msg[128];
+            snprintf(msg, sizeof(msg), "scoring kernel reported internal error %u", flag);
+            return fail(ctx, MB_E_DATA, msg);
+        }
+        ctx->tc_used = used;
+    }
+    mark(ctx, EV_SCORE);
+    ctx->have_results = true;
+    if (taxcnt_used) *taxcnt_used = ctx->tc_used;
+    return MB_OK;
+}
+
+int mb_fetch_results(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap) {
+    if (!ctx || (!results && ctx->n_reads)) return MB_E_ARG;
+    if (!ctx->have_results) return fail(ctx, MB_E_ARG, "no results resident");
+    if (taxcnt_cap < ctx->tc_used) return fail(ctx, MB_E_CAPACITY, "taxcnt arrays too small");
+    CK(cudaSetDevice(ctx->par.device));
+    if (ctx->n_reads) CK(cudaMemcpyAsync(results, ctx->results.p, (size_t) ctx->n_reads * sizeof(mb_read_result), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->tc_used) {
+        CK(cudaMemcpyAsync(taxcnt_id, ctx->tc_id.p, ctx->tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(taxcnt_n, ctx->tc_cnt.p, ctx->tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    mark(ctx, EV_D2H);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+int mb_classify_staged(mb_ctx *ctx, size_t *taxcnt_used) {
+    if (int rc = mb_extract_kmers(ctx, nullptr)) return rc;
+    if (int rc = mb_sort_kmers(ctx)) return rc;
+    if (int rc = mb_match_kmers(ctx, nullptr)) return rc;
+    if (int rc = mb_sort_matches(ctx)) return rc;
+    return mb_score_reads(ctx, taxcnt_used);
+}
+
+int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
+                      uint32_t n_reads, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n,
+                      size_t taxcnt_cap, size_t *taxcnt_used) {
+    if (int rc = mb_stage_reads(ctx, bases, n_bases, offsets, lens, n_reads)) return rc;
+    size_t used = 0;
+    if (int rc = mb_classify_staged(ctx, &used)) return rc;
+    if (taxcnt_used) *taxcnt_used = used;
+    if (used > taxcnt_cap) return fail(ctx, MB_E_CAPACITY, "taxcnt arrays too small; *taxcnt_used holds the required size");
+    return mb_fetch_results(ctx, results, taxcnt_id, taxcnt_n, taxcnt_cap);
+}
+
+// ---- taps / exchange ----------------------------------------------------------------------------------
+int mb_copy_kmers(mb_ctx *ctx, mb_kmer *out, size_t cap, size_t *n) {
+    if (!ctx || !n) return MB_E_ARG;
+    if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    *n = ctx->n_kmers;
+    if (cap < ctx->n_kmers) return fail(ctx, MB_E_CAPACITY, "k-mer output too small");
+    CK(cudaSetDevice(ctx->par.device));
+    if (ctx->n_kmers) CK(cudaMemcpyAsync(out, ctx->kmers_a.p, ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+int mb_copy_matches(mb_ctx *ctx, mb_match *out, size_t cap, size_t *n) {
+    if (!ctx || !n) return MB_E_ARG;
+    if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    *n = ctx->n_matches;
+    if (cap < ctx->n_matches) return fail(ctx, MB_E_CAPACITY, "match output too small");
+    CK(cudaSetDevice(ctx->par.device));
+    if (ctx->n_matches) CK(cudaMemcpyAsync(out, ctx->matches_a.p, ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+static int set_kmers(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind kind) {
+    CK(cudaSetDevice(ctx->par.device));
+    CK(ctx->kmers_a.ensure((n + 1) * sizeof(mb_kmer)));
+    if (n) CK(cudaMemcpyAsync(ctx->kmers_a.p, src, n * sizeof(mb_kmer), kind, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_kmers = n;
+    ctx->have_kmers = true;
+    ctx->kmers_sorted = false;
+    ctx->have_matches = ctx->have_results = false;
+    return MB_OK;
+}
+static int set_matches(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind kind) {
+    CK(cudaSetDevice(ctx->par.device));
+    CK(ctx->matches_a.ensure((n + 1) * sizeof(mb_match)));
+    if (n) CK(cudaMemcpyAsync(ctx->matches_a.p, src, n * sizeof(mb_match), kind, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_matches = n;
+    ctx->have_matches = true;
+    ctx->matches_sorted = false;
+    ctx->have_results = false;
+    return MB_OK;
+}
+int mb_set_kmers(mb_ctx *ctx, const mb_kmer *k, size_t n) { return (!ctx || (!k && n)) ? MB_E_ARG : set_kmers(ctx, k, n, cudaMemcpyHostToDevice); }
+int mb_set_matches(mb_ctx *ctx, const mb_match *m, size_t n) { return (!ctx || (!m && n)) ? MB_E_ARG : set_matches(ctx, m, n, cudaMemcpyHostToDevice); }
+int mb_set_kmers_device(mb_ctx *ctx, const void *d, size_t n) { return (!ctx || (!d && n)) ? MB_E_ARG : set_kmers(ctx, d, n, cudaMemcpyDeviceToDevice); }
+int mb_set_matches_device(mb_ctx *ctx, const void *d, size_t n) { return (!ctx || (!d && n)) ? MB_E_ARG : set_matches(ctx, d, n, cudaMemcpyDeviceToDevice); }
+
+int mb_kmers_device(mb_ctx *ctx, void **dptr, size_t *n) {
+    if (!ctx || !dptr || !n) return MB_E_ARG;
+    if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    CK(cudaStreamSynchronize(ctx->stream));
+    *dptr = ctx->kmers_a.p; *n = ctx->n_kmers;
+    return MB_OK;
+}
+int mb_matches_device(mb_ctx *ctx, void **dptr, size_t *n) {
+    if (!ctx || !dptr || !n) return MB_E_ARG;
+    if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    CK(cudaStreamSynchronize(ctx->stream));
+    *dptr = ctx->matches_a.p; *n = ctx->n_matches;
+    return MB_OK;
+}
+
+int mb_partition_kmers(mb_ctx *ctx, const uint64_t *bounds, int n_shards, uint64_t *counts) {
+    if (!ctx || !counts || n_shards < 1 || n_shards > 9 || (!bounds && n_shards > 1)) return MB_E_ARG;
+    if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    CK(cudaSetDevice(ctx->par.device));
+    KmerOwnerKey key;
+    key.n_bounds = n_shards - 1;
+    for (int i = 0; i < 8; ++i) key.bounds[i] = i < n_shards - 1 ? bounds[i] : ~0ull;
+    return partition_by<mb_kmer, KmerOwnerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, n_shards, counts);
+}
+
+int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint64_t *counts) {
+    if (!ctx || !counts || n_ranks < 1 || n_ranks > 255 || reads_per_rank == 0) return MB_E_ARG;
+    if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MatchHomeKey key;
+    key.reads_per_rank = reads_per_rank;
+    return partition_by<mb_match, MatchHomeKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, n_ranks, counts);
+}
+
+int mb_get_timings(mb_ctx *ctx, mb_phase_times *t) {
+    if (!ctx || !t) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    mb_phase_times &o = ctx->times;
+    auto span = [&](int a, int b) -> float {
+        if (!ctx->ev_set[a] || !ctx->ev_set[b]) return 0.f;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->ev[a], ctx->ev[b]) != cudaSuccess) { cudaGetLastError(); return 0.f; }
+        return ms;
+    };
+    o.h2d_ms = span(EV_START, EV_H2D);
+    o.extract_ms = span(EV_H2D, EV_EXTRACT);
+    o.sort_kmers_ms = span(EV_EXTRACT, EV_SORTK);
+    o.match_ms = span(EV_SORTK, EV_MATCH);
+    o.sort_matches_ms = span(EV_MATCH, EV_SORTM);
+    o.score_ms = span(EV_SORTM, EV_SCORE);
+    o.d2h_ms = span(EV_SCORE, EV_D2H);
+    o.total_ms = span(EV_START, ctx->ev_set[EV_D2H] ? EV_D2H : EV_SCORE);
+    o.n_bases = ctx->n_bases; o.n_kmers = ctx->n_kmers; o.n_matches = ctx->n_matches; o.n_reads = ctx->n_reads;
+    o.db_words = ctx->n_words; o.db_kmers = ctx->n_db_kmers;
+    o.kernel_launches = ctx->launches;
+    *t = o;
+    return MB_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,190 @@
+// mb_common.cuh — shared types, lookup tables and small device helpers of libmetabuli_b200.
+//
+// Every table here restates a table of the reference (cited per item; paths relative to the
+// reference tree).  Functions marked MB_HD are pure per-element logic: they compile for the device
+// (product) and for the host (tests/emu only — a checker build that lets the CPU test-suite exercise
+// the exact device logic; the product never calls the host instantiation).
+#pragma once
+
+#include <stdint.h>
+#include <stddef.h>
+
+#if defined(__CUDACC__)
+#define MB_HD __host__ __device__ __forceinline__
+#else
+#define MB_HD inline
+#endif
+
+#include "../../include/metabuli_b200.h"
+
+namespace mb {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+typedef unsigned short u16;
+typedef unsigned char u8;
+
+// ---- qinfo bit layout: src/commons/Kmer.h:11-16 -------------------------------------------------
+MB_HD u64 make_qinfo(u32 seqId, u32 pos, u32 frame) {
+    return (u64) pos | ((u64) (seqId & 0x1FFFFFFFu) << 32) | ((u64) (frame & 7u) << 61);
+}
+MB_HD u32 qi_pos(u64 q) { return (u32) q; }
+MB_HD u32 qi_seq(u64 q) { return (u32) ((q >> 32) & 0x1FFFFFFFu); }
+MB_HD u32 qi_frame(u64 q) { return (u32) (q >> 61); }
+
+// ---- read-length arithmetic: src/commons/LocalUtil.h:45-59 ----------------------------------------
+MB_HD int max_covered_length(int len) {
+    int r = len % 3;
+    return r == 2 ? len - 2 : (r == 1 ? len - 4 : len - 3);
+}
+// slot bound of one mate; < 1 means the mate is "empty" (KmerExtractor.cpp:457-460)
+MB_HD int query_kmer_number(int len) { return (max_covered_length(len) / 3 - 8 + 1) * 6; }
+
+// ---- translation tables ---------------------------------------------------------------------------
+// Built on the host by build_tables() and copied to __constant__ memory.
+//   nuc[c]    : ASCII -> base code A0 C1 T2 G3, 4 = not a base.  Restates the atcg map
+//               (src/commons/common.cpp:13-23) followed by nuc2int (src/commons/GeneticCode.h:6).
+//   codonF[i] : i = b0 | b1<<2 | b2<<4 (three consecutive stored bases, little-endian) ->
+//               aa | cid<<5 of the forward codon b0 b1 b2 (GeneticCode.h:34-193: 21-letter alphabet
+//               ARNDCQEGHILKMFPSTWYVX, 3-bit codon ids)
+//   codonR[i] : same index -> reverse-strand codon comp(b2) comp(b1) comp(b0) (KmerScanner.h:94-98)
+//   ham4      : 8x8 codon-id Hamming table, 4 bits per cell (KmerMatcher.h:66-70 hammingLookup)
+struct Tables {
+    u8 nuc[256];
+    u8 codonF[64];
+    u8 codonR[64];
+    u64 ham4[4];
+};
+
+void build_tables(Tables &t);
+
+// hammingLookup[a][b], a/b 3-bit codon ids (KmerMatcher.h:66-70); cell (a,b) sits at nibble a*8+b
+MB_HD u32 ham_cell(const u64 (&h)[4], u32 a, u32 b) {
+    u32 idx = a * 8 + b;
+    u64 w = (idx & 32) ? ((idx & 16) ? h[3] : h[2]) : ((idx & 16) ? h[1] : h[0]);
+    return (u32) (w >> ((idx & 15) * 4)) & 15u;
+}
+
+// getHammingDistanceSum (KmerMatcher.h:348-360): sum over the 8 codon ids of the low 24 bits
+MB_HD u32 hamming_sum(const u64 (&h)[4], u64 q, u64 t) {
+    u32 s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += ham_cell(h, (u32) (q >> (3 * k)) & 7u, (u32) (t >> (3 * k)) & 7u);
+    return s;
+}
+
+// getHammings / getHammings_reverse (KmerMatcher.h:386-416) with the HAMMING_LUT0..7 cells
+// (KmerMatcher.h:72-158): field = hamming & 3 (so the cells holding 4 pack to 0), except that
+// HAMMING_LUT7 holds 1<<14 for query ids 4,5 against target ids 6,7.
+MB_HD u32 hamming_pack(const u64 (&h)[4], u64 q, u64 t, bool reverse) {
+    u32 out = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        u32 a = (u32) (q >> (3 * k)) & 7u, b = (u32) (t >> (3 * k)) & 7u;
+        int field = reverse ? 7 - k : k;
+        u32 v = ham_cell(h, a, b) & 3u;
+        if (field == 7 && (a == 4 || a == 5) && (b == 6 || b == 7)) v = 1;
+        out |= v << (2 * field);
+    }
+    return out;
+}
+
+// ---- metamer assembly from 24 stored bases --------------------------------------------------------
+// win48: 24 bases, base p at bits 2p..2p+1 (A0 C1 T2 G3).  Returns the metamer of the window on the
+// forward strand (reverse=false) or on the reverse strand (reverse=true).
+//   format 2 (MetamerScanner::next, KmerScanner.h:82-117): first translated codon most significant,
+//            AA 5 bits each << 24 | 3-bit codon ids.
+//   format 1 (OldMetamerScanner::next, KmerScanner.h:137-181): codons consumed from the far end, so
+//            the first translated codon is LEAST significant; AA part is a base-21 number.
+MB_HD u64 metamer_from_window(const u8 *codonF, const u8 *codonR, u64 win48, bool reverse, int format) {
+    u64 aa = 0, dna = 0;
+    if (format == 2) {
+        if (!reverse) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {           // j = codon index along the stored bases = translation order
+                u32 c = codonF[(win48 >> (6 * j)) & 63];
+                aa = (aa << 5) | (c & 31u);
+                dna = (dna << 3) | (c >> 5);
+            }
+        } else {
+#pragma unroll
+            for (int j = 7; j >= 0; --j) {          // translation order runs from the high end down
+                u32 c = codonR[(win48 >> (6 * j)) & 63];
+                aa = (aa << 5) | (c & 31u);
+                dna = (dna << 3) | (c >> 5);
+            }
+        }
+    } else {
+        if (!reverse) {
+#pragma unroll
+            for (int j = 7; j >= 0; --j) {          // highest stored codon most significant
+                u32 c = codonF[(win48 >> (6 * j)) & 63];
+                aa = aa * 21 + (c & 31u);
+                dna = (dna << 3) | (c >> 5);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {           // lowest stored codon most significant
+                u32 c = codonR[(win48 >> (6 * j)) & 63];
+                aa = aa * 21 + (c & 31u);
+                dna = (dna << 3) | (c >> 5);
+            }
+        }
+    }
+    return (aa << 24) | dna;
+}
+
+// Closed-syncmer test of SyncmerScanner::next (SyncmerScanner.h:36-102) on a format-2 metamer:
+// the leftmost minimum of the 8-s+1 amino-acid s-mers must sit at offset 0 or 8-s.
+MB_HD bool is_syncmer(u64 metamer, int s) {
+    const u64 aa = metamer >> 24;
+    const u64 mask = (1ull << (5 * s)) - 1;
+    const int last = 8 - s;
+    u64 best = (aa >> (5 * last)) & mask;           // s-mer at offset 0
+    int arg = 0;
+    for (int i = 1; i <= last; ++i) {
+        u64 v = (aa >> (5 * (last - i))) & mask;
+        if (v < best) { best = v; arg = i; }
+    }
+    return arg == 0 || arg == last;
+}
+
+// Device-resident taxonomy view (see mb_load_taxonomy in metabuli_b200.h)
+struct TaxView {
+    const int32_t *parent;         // -1 = taxon does not exist
+    const int32_t *depth;          // root 0
+    const int32_t *species_of;
+    const int32_t *species_rank_of;
+    int32_t max_taxid;
+    int32_t node0_taxid;
+    int32_t eukaryota;
+};
+
+MB_HD bool tax_exists(const TaxView &t, int32_t x) { return x >= 0 && x <= t.max_taxid && t.parent[x] >= 0; }
+
+// lowest common ancestor by depth-equalising parent walk == lcaHelper's Euler-tour RMQ on a tree
+// (NcbiTaxonomy.cpp:261-280), including its node-index-0 short circuit.
+MB_HD int32_t tax_lca_existing(const TaxView &t, int32_t a, int32_t b) {
+    if (a == t.node0_taxid || b == t.node0_taxid) return t.node0_taxid;
+    if (a == b) return a;
+    int da = t.depth[a], db = t.depth[b];
+    while (da > db) { a = t.parent[a]; --da; }
+    while (db > da) { b = t.parent[b]; --db; }
+    while (a != b) { a = t.parent[a]; b = t.parent[b]; }
+    return a;
+}
+// NcbiTaxonomy::LCA(TaxID, TaxID) (NcbiTaxonomy.cpp:303-310)
+MB_HD int32_t tax_lca(const TaxView &t, int32_t a, int32_t b) {
+    if (!tax_exists(t, a)) return b;
+    if (!tax_exists(t, b)) return a;
+    return tax_lca_existing(t, a, b);
+}
+// NcbiTaxonomy::IsAncestor (NcbiTaxonomy.cpp:282-300)
+MB_HD bool tax_is_ancestor(const TaxView &t, int32_t anc, int32_t child) {
+    if (anc == child) return true;
+    if (anc == 0 || child == 0) return false;
+    if (!tax_exists(t, child) || !tax_exists(t, anc)) return false;
+    return tax_lca_existing(t, child, anc) == anc;
+}
+
+} // namespace mb

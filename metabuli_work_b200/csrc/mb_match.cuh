@@ -1,0 +1,464 @@
+// mb_match.cuh — K3+K4: block-parallel diffIdx decode feeding the amino-acid merge join with the DNA
+// Hamming filter and match compaction.
+//
+// Replaces KmerMatcher::matchKmers (src/commons/KmerMatcher.cpp:123-481) with getNextTargetKmer
+// (KmerMatcher.h:282-297) and compareDna (KmerMatcher.cpp:1117-1146).
+//
+// What the reference computes, stated without its thread ranges: a query k-mer q is compared with
+// ALL DB k-mers whose amino-acid part (value >> 24) equals q's — except the very last k-mer of the
+// DB, which the `diffIdxPos != numOfDiffIdx` guards never offer (KmerMatcher.cpp:363-406) — and
+// every candidate whose codon-id Hamming sum is <= min(2*min_sum, 7) yields a Match.  The result
+// per query depends on nothing else, so the join parallelises over DB blocks.
+//
+// B200 design.  The compressed stream stays in HBM (about 9.7 B per k-mer with `info`).  At load
+// time a block index is built: for every 2048-word block the decode cursor (word, value before,
+// k-mer ordinal) of the first amino-acid group that STARTS in the block, and that group's AA.  A
+// group is owned by the block it starts in.  Per batch, a partition kernel binary-searches the
+// sorted query list once per block (merge-path style: block b joins queries [qstart[b],
+// qstart[b+1])); blocks without queries never touch their words.  A CTA then
+//   1. loads its block plus a 512-word overhang with 16-byte loads into shared memory,
+//   2. decodes it cooperatively: each thread assembles the deltas ending in its 10 words, a block
+//      scan of (count, 64-bit delta sum) turns them into absolute values in shared memory,
+//   3. joins its query slice, one query per thread: binary search of the AA part in the decoded
+//      block, a min pass and an emit pass over the group with the Hamming table held in registers,
+//   4. compacts matches with a block scan + ONE atomic reservation per 256 queries and writes them.
+// Groups longer than the overhang are re-decoded from their own start; groups longer than a whole
+// chunk take a streaming two-pass path.  Capacity misses are counted, never written out of bounds;
+// the host grows the buffer and reruns (the reference's retry, Classifier.cpp:127-131).
+#pragma once
+#include "mb_common.cuh"
+
+namespace mb {
+
+constexpr int DB_W = 2048;                 // words per block
+constexpr int DB_E = 512;                  // overhang words
+constexpr int DB_C = DB_W + DB_E;          // words decoded per chunk
+constexpr int MT_THREADS = 256;
+constexpr int DB_R = DB_C / MT_THREADS;    // words per thread (10: odd word stride, conflict-free)
+constexpr int DB_PAD = DB_C + 64;          // zero words the device stream is padded with
+
+static_assert(DB_C % MT_THREADS == 0, "chunk must divide among the threads");
+
+struct BlockIndex {      // per 2048-word block: cursor of the first AA group starting in it
+    u64 word;            // first word of that group's first k-mer
+    u64 vbefore;         // value of the preceding k-mer (0 at the stream start)
+    u64 kidx;            // ordinal of that k-mer
+    u64 own_aa;          // its AA part; for a block that owns nothing: the next owning block's AA
+    u32 owns;            // 1 when a group starts in this block
+    u32 pad;
+};
+
+struct DbView {
+    const u16 *words;        // padded with DB_PAD zero words
+    u64 n_words;
+    const u32 *info;
+    u64 n_kmers_eff;         // candidates are ordinals < n_kmers_eff (drops the final k-mer on the last shard)
+    u32 info_mask;           // KmerMatcher.cpp:204-205
+    const int32_t *species_of;
+    int32_t max_taxid;
+};
+
+struct DbCursor { u64 word, vbefore, kidx; };
+
+struct MatchSmem {
+    __align__(16) u16 w[DB_C + 16];
+    u64 vals[DB_C];
+    u16 wend[DB_C];
+    u64 scan_sum[MT_THREADS / 32];
+    u32 scan_cnt[MT_THREADS / 32];
+    u32 n;
+    int last_start;
+    int own_end;
+    u32 group_end;
+    u64 reserve_base;
+    u32 warp_tot[MT_THREADS / 32];
+};
+
+// Decode up to DB_C words starting at cursor c (which must sit on the first word of a k-mer).
+// Leaves values / terminator word offsets in shared memory, returns the number of k-mers decoded.
+__device__ __forceinline__ u32 decode_chunk(const DbView &db, const DbCursor &c, MatchSmem &s) {
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u64 wbase = c.word & ~7ull;
+    const u32 pad = (u32) (c.word - wbase);
+    // 16-byte loads; the stream is zero padded so reads past n_words are harmless (no terminators)
+    const uint4 *src = reinterpret_cast<const uint4 *>(db.words + wbase);
+    uint4 *dst = reinterpret_cast<uint4 *>(s.w);
+    for (u32 i = tid; i < (DB_C + 16) / 8; i += MT_THREADS) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (wbase + (u64) i * 8 < db.n_words) v = __ldg(src + i);
+        dst[i] = v;
+    }
+    __syncthreads();
+    const u16 *w = s.w + pad;
+    const u32 l0 = tid * DB_R;
+    // words of an unfinished delta in front of this thread's run (at most 4 for a valid stream)
+    u32 st = l0;
+    while (st > 0 && l0 - st < 4 && !(w[st - 1] & 0x8000u)) --st;
+    u64 carry = 0;
+    for (u32 k = st; k < l0; ++k) carry = (carry | w[k]) << 15;
+    // pass 1: count and sum the deltas terminating in my run (getNextTargetKmer, KmerMatcher.h:282-297)
+    u32 cnt = 0;
+    u64 sum = 0, diff = carry;
+#pragma unroll
+    for (int i = 0; i < DB_R; ++i) {
+        const u32 frag = w[l0 + i];
+        const bool in_range = c.word + l0 + i < db.n_words;
+        if ((frag & 0x8000u) && in_range) { diff |= (frag & 0x7FFFu); sum += diff; ++cnt; diff = 0; }
+        else diff = (diff | frag) << 15;
+    }
+    // block exclusive scan of (cnt, sum)
+    u32 icnt = cnt;
+    u64 isum = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 tc = __shfl_up_sync(0xFFFFFFFFu, icnt, d);
+        const u64 ts = __shfl_up_sync(0xFFFFFFFFu, isum, d);
+        if (lane >= (u32) d) { icnt += tc; isum += ts; }
+    }
+    if (lane == 31) { s.scan_cnt[warp] = icnt; s.scan_sum[warp] = isum; }
+    __syncthreads();
+    u32 cbase = 0, ctot = 0;
+    u64 sbase = 0;
+#pragma unroll
+    for (int k = 0; k < MT_THREADS / 32; ++k) {
+        const u32 tc = s.scan_cnt[k];
+        const u64 ts = s.scan_sum[k];
+        if ((u32) k < warp) { cbase += tc; sbase += ts; }
+        ctot += tc;
+    }
+    u32 pos = cbase + icnt - cnt;
+    u64 run = c.vbefore + sbase + isum - sum;
+    // pass 2: absolute values
+    diff = carry;
+#pragma unroll
+    for (int i = 0; i < DB_R; ++i) {
+        const u32 frag = w[l0 + i];
+        const bool in_range = c.word + l0 + i < db.n_words;
+        if ((frag & 0x8000u) && in_range) {
+            diff |= (frag & 0x7FFFu);
+            run += diff;
+            s.vals[pos] = run;
+            s.wend[pos] = (u16) (l0 + i);
+            ++pos;
+            diff = 0;
+        } else diff = (diff | frag) << 15;
+    }
+    // candidates stop at n_kmers_eff
+    u64 room = db.n_kmers_eff > c.kidx ? db.n_kmers_eff - c.kidx : 0;
+    if ((u64) ctot > room) ctot = (u32) room;
+    __syncthreads();
+    return ctot;
+}
+
+// first index in vals[0, n) whose AA part is >= aa
+__device__ __forceinline__ u32 lower_bound_aa(const u64 *vals, u32 n, u64 aa) {
+    u32 lo = 0, hi = n;
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if ((vals[mid] >> 24) < aa) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+struct MatchOut {
+    mb_match *out;
+    u64 cap;
+    unsigned long long *counter;   // total matches produced (may exceed cap)
+    u32 *error_flag;               // set when a DB tax ID has no species (KmerMatcher.cpp:433-441)
+};
+
+// Block-cooperative: thread t emits its `cnt` matches (entries [lo,hi) of s.vals with dist <= maxh).
+__device__ __forceinline__ void emit_matches(const DbView &db, const DbCursor &c, MatchSmem &s, const MatchOut &mo,
+                                             const u64 (&ham)[4], bool active, const mb_kmer &q, u32 lo, u32 hi,
+                                             u32 maxh, u32 cnt, int format) {
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    u32 incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= (u32) d) incl += t;
+    }
+    if (lane == 31) s.warp_tot[warp] = incl;
+    __syncthreads();
+    u32 wb = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < MT_THREADS / 32; ++k) {
+        const u32 t = s.warp_tot[k];
+        if ((u32) k < warp) wb += t;
+        total += t;
+    }
+    if (tid == 0 && total) s.reserve_base = atomicAdd(mo.counter, (unsigned long long) total);
+    __syncthreads();
+    if (active && cnt) {
+        u64 o = s.reserve_base + wb + incl - cnt;
+        const u32 frame = qi_frame(q.qinfo);
+        // KmerMatcher.cpp:1137-1143: getHammings for (frame<3) == (format==2), else getHammings_reverse
+        const bool rev = ((frame < 3) != (format == 2));
+        for (u32 j = lo; j < hi; ++j) {
+            const u64 t = s.vals[j];
+            const u32 d = hamming_sum(ham, q.value, t);
+            if (d > maxh) continue;
+            if (o < mo.cap) {
+                const int32_t tax = (int32_t) (__ldg(db.info + c.kidx + j) & db.info_mask);
+                int32_t sp = 0;
+                if (tax >= 0 && tax <= db.max_taxid) sp = __ldg(db.species_of + tax);
+                if (sp == 0 || tax == 0) *mo.error_flag = 1;
+                mb_match m;
+                m.qinfo = q.qinfo;
+                m.targetId = tax;
+                m.speciesId = sp;
+                m.dnaEncoding = (u32) (t & 0xFFFFFFull);
+                m.rightEndHamming = (u16) hamming_pack(ham, q.value, t, rev);
+                m.hamming = (u8) d;
+                m.pad = 0;
+                // 24-byte record as three 8-byte stores
+                u64 *p = reinterpret_cast<u64 *>(mo.out + o);
+                p[0] = m.qinfo;
+                p[1] = (u64) (u32) m.targetId | ((u64) (u32) m.speciesId << 32);
+                p[2] = (u64) m.dnaEncoding | ((u64) m.rightEndHamming << 32) | ((u64) m.hamming << 48);
+            }
+            ++o;
+        }
+    }
+    __syncthreads();
+}
+
+// Streaming two-pass join for an amino-acid group that does not fit one chunk: for every batch of
+// 256 queries of that group the group is decoded twice from its start cursor (minimum, then emit).
+__device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, MatchSmem &s, const MatchOut &mo,
+                                         const u64 (&ham)[4], const mb_kmer *__restrict__ q, u64 qcur, u64 qend,
+                                         u64 gaa, int format) {
+    const u32 tid = threadIdx.x;
+    while (true) {
+        const u64 qi = qcur + tid;
+        mb_kmer qk;
+        qk.value = 0; qk.qinfo = 0;
+        bool mine = false;
+        if (qi < qend) { qk = q[qi]; mine = (qk.value >> 24) == gaa; }
+        const int taken = __syncthreads_count(mine);
+        if (taken == 0) break;
+        u32 mind = 255, maxh = 0;
+        for (int phase = 0; phase < 2; ++phase) {
+            DbCursor g = c;
+            while (true) {
+                const u32 n = decode_chunk(db, g, s);
+                if (n == 0) break;
+                if (tid == 0) s.group_end = n;
+                __syncthreads();
+                for (u32 j = tid; j < n; j += MT_THREADS)
+                    if ((s.vals[j] >> 24) != gaa) atomicMin(&s.group_end, j);
+                __syncthreads();
+                const u32 ge = s.group_end;
+                const bool finished = ge < n || (g.kidx + n == db.n_kmers_eff);
+                if (phase == 0) {
+                    if (mine)
+                        for (u32 j = 0; j < ge; ++j) {
+                            const u32 d = hamming_sum(ham, qk.value, s.vals[j]);
+                            mind = d < mind ? d : mind;
+                        }
+                    __syncthreads();
+                } else {
+                    u32 cnt = 0;
+                    if (mine)
+                        for (u32 j = 0; j < ge; ++j) cnt += hamming_sum(ham, qk.value, s.vals[j]) <= maxh ? 1u : 0u;
+                    emit_matches(db, g, s, mo, ham, mine, qk, 0, ge, maxh, cnt, format);
+                }
+                if (finished) break;
+                const u64 nw = g.word + (u64) s.wend[n - 1] + 1;
+                const u64 nv = s.vals[n - 1];
+                __syncthreads();
+                g.word = nw; g.vbefore = nv; g.kidx += n;
+            }
+            if (phase == 0) maxh = mind * 2 < 7 ? mind * 2 : 7;
+        }
+        qcur += (u64) taken;
+        if (taken < MT_THREADS) break;
+    }
+}
+
+__global__ void __launch_bounds__(MT_THREADS)
+k_match(DbView db, const BlockIndex *__restrict__ blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
+        MatchOut mo, const Tables *__restrict__ tables, int format) {
+    __shared__ MatchSmem s;
+    const u32 tid = threadIdx.x;
+    const u32 b = blockIdx.x;
+    const BlockIndex bi = blocks[b];
+    if (!bi.owns) return;
+    u64 qcur = qstart[b];
+    const u64 qend = qstart[b + 1];
+    if (qcur >= qend) return;                      // no query falls into this block's AA range
+    u64 ham[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ham[i] = tables->ham4[i];
+
+    const u64 tile_end = (u64) (b + 1) * DB_W;     // groups starting at or after this word belong to later blocks
+    DbCursor c{bi.word, bi.vbefore, bi.kidx};
+
+    while (true) {
+        const u32 n = decode_chunk(db, c, s);
+        if (n == 0) break;
+        if (tid == 0) { s.last_start = 0; s.own_end = (int) n; }
+        __syncthreads();
+        const u64 own_limit = tile_end > c.word ? tile_end - c.word : 0;   // local word offset of the block end
+        for (u32 j = tid + 1; j < n; j += MT_THREADS) {
+            if ((s.vals[j] >> 24) != (s.vals[j - 1] >> 24)) {
+                atomicMax(&s.last_start, (int) j);
+                // first word of k-mer j is the word after the previous terminator
+                if ((u64) s.wend[j - 1] + 1 >= own_limit) atomicMin(&s.own_end, (int) j);
+            }
+        }
+        __syncthreads();
+        const bool db_end = (c.kidx + n == db.n_kmers_eff);
+        u32 proc_end = db_end ? n : (u32) s.last_start;     // the last group may continue past the chunk
+        if ((u32) s.own_end < proc_end) proc_end = (u32) s.own_end;
+        const u32 own_end = (u32) s.own_end;
+        __syncthreads();
+
+        if (proc_end == 0) {
+            // One group fills the whole chunk and is not known to be complete: streaming path.  The
+            // group is owned (the cursor always sits on a group starting inside this block) and, being
+            // longer than a block plus overhang, it is the last one this block owns.
+            giant_group(db, c, s, mo, ham, q, qcur, qend, s.vals[0] >> 24, format);
+            break;
+        }
+
+        // ---- fast path: all groups in [0, proc_end) are complete and owned ----
+        const u64 limit_aa = proc_end < n ? (s.vals[proc_end] >> 24) : ~0ull;
+        while (true) {
+            const u64 qi = qcur + tid;
+            mb_kmer qk;
+            qk.value = 0; qk.qinfo = 0;
+            bool mine = false;
+            if (qi < qend) { qk = q[qi]; mine = (qk.value >> 24) < limit_aa; }
+            const int taken = __syncthreads_count(mine);
+            u32 lo = 0, hi = 0, maxh = 0, cnt = 0;
+            if (mine) {
+                const u64 aa = qk.value >> 24;
+                lo = lower_bound_aa(s.vals, proc_end, aa);
+                hi = lo;
+                u32 mind = 255;
+                while (hi < proc_end && (s.vals[hi] >> 24) == aa) {
+                    const u32 d = hamming_sum(ham, qk.value, s.vals[hi]);
+                    mind = d < mind ? d : mind;
+                    ++hi;
+                }
+                if (hi > lo) {
+                    maxh = mind * 2 < 7 ? mind * 2 : 7;        // KmerMatcher.cpp:1126
+                    for (u32 j = lo; j < hi; ++j) cnt += hamming_sum(ham, qk.value, s.vals[j]) <= maxh ? 1u : 0u;
+                }
+            }
+            emit_matches(db, c, s, mo, ham, mine, qk, lo, hi, maxh, cnt, format);
+            qcur += (u64) taken;
+            if (taken < MT_THREADS) break;
+        }
+        if (proc_end >= n && db_end) break;                        // end of the stream
+        if (proc_end >= own_end) break;                            // the next group starts in a later block
+        // continue from the first group that was not processed (it starts inside this block)
+        c.word += (u64) s.wend[proc_end - 1] + 1;
+        c.vbefore = s.vals[proc_end - 1];
+        c.kidx += proc_end;
+        if (qcur >= qend) break;
+        __syncthreads();
+    }
+}
+
+// ---- load-time block index ---------------------------------------------------------------------------
+// pass A: per block, how many words in front of the block belong to the first k-mer ending in it, how
+// many k-mers end in it and the sum of their deltas.
+__global__ void __launch_bounds__(MT_THREADS)
+k_db_block_summary(DbView db, u32 n_blocks, u32 *__restrict__ blk_back, u32 *__restrict__ blk_cnt, u64 *__restrict__ blk_sum) {
+    __shared__ MatchSmem s;
+    __shared__ u32 s_back;
+    __shared__ u32 s_cnt;
+    const u32 b = blockIdx.x, tid = threadIdx.x;
+    if (b >= n_blocks) return;
+    const u64 w0 = (u64) b * DB_W;
+    if (tid == 0) {
+        u32 back = 0;
+        while (back < 4 && w0 > back && !(db.words[w0 - back - 1] & 0x8000u)) ++back;
+        s_back = back;
+        s_cnt = 0;
+    }
+    __syncthreads();
+    const u32 back = s_back;
+    DbCursor c{w0 - back, 0, 0};
+    const u32 n = decode_chunk(db, c, s);
+    const u32 limit = DB_W + back;                 // local offset of the block end
+    // entries are ordered: count those whose terminator lies inside the block
+    for (u32 j = tid; j < n; j += MT_THREADS)
+        if (s.wend[j] < limit && (j + 1 == n || s.wend[j + 1] >= limit)) s_cnt = j + 1;
+    __syncthreads();
+    if (tid == 0) {
+        const u32 cnt = s_cnt;
+        blk_back[b] = back;
+        blk_cnt[b] = cnt;
+        blk_sum[b] = cnt ? s.vals[cnt - 1] : 0;
+    }
+}
+
+// pass B (after the host scanned counts and sums into kidx/vbefore per block): first group starting in the block
+__global__ void __launch_bounds__(MT_THREADS)
+k_db_block_own(DbView db, u32 n_blocks, const u32 *__restrict__ blk_back, const u64 *__restrict__ blk_kidx,
+               const u64 *__restrict__ blk_vbefore, BlockIndex *__restrict__ out) {
+    __shared__ MatchSmem s;
+    __shared__ u32 s_first;
+    const u32 b = blockIdx.x, tid = threadIdx.x;
+    if (b >= n_blocks) return;
+    const u32 back = blk_back[b];
+    DbCursor c{(u64) b * DB_W - back, blk_vbefore[b], blk_kidx[b]};
+    if (tid == 0) s_first = 0xFFFFFFFFu;
+    const u32 n = decode_chunk(db, c, s);
+    const u32 lo = back, hi = DB_W + back;         // local word range of the block
+    for (u32 j = tid; j < n; j += MT_THREADS) {
+        const u32 first_word = j == 0 ? 0u : (u32) s.wend[j - 1] + 1u;
+        if (first_word < lo || first_word >= hi) continue;
+        const bool starts = (j == 0) ? (c.kidx == 0 || (s.vals[0] >> 24) != (c.vbefore >> 24))
+                                     : ((s.vals[j] >> 24) != (s.vals[j - 1] >> 24));
+        if (starts) atomicMin(&s_first, j);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        BlockIndex bi;
+        const u32 j = s_first;
+        if (j == 0xFFFFFFFFu) { bi.word = 0; bi.vbefore = 0; bi.kidx = 0; bi.own_aa = ~0ull; bi.owns = 0; }
+        else {
+            bi.word = c.word + (j == 0 ? 0u : (u32) s.wend[j - 1] + 1u);
+            bi.vbefore = j == 0 ? c.vbefore : s.vals[j - 1];
+            bi.kidx = c.kidx + j;
+            bi.own_aa = s.vals[j] >> 24;
+            bi.owns = 1;
+        }
+        bi.pad = 0;
+        out[b] = bi;
+    }
+}
+
+// plain decode of the resident stream (parity tap): values of the k-mers ending in each block
+__global__ void __launch_bounds__(MT_THREADS)
+k_db_decode(DbView db, u32 n_blocks, const u32 *__restrict__ blk_back, const u32 *__restrict__ blk_cnt,
+            const u64 *__restrict__ blk_kidx, const u64 *__restrict__ blk_vbefore, u64 *__restrict__ values) {
+    __shared__ MatchSmem s;
+    const u32 b = blockIdx.x, tid = threadIdx.x;
+    if (b >= n_blocks) return;
+    DbCursor c{(u64) b * DB_W - blk_back[b], blk_vbefore[b], blk_kidx[b]};
+    decode_chunk(db, c, s);
+    const u32 cnt = blk_cnt[b];
+    for (u32 j = tid; j < cnt; j += MT_THREADS) values[c.kidx + j] = s.vals[j];
+}
+
+// ---- per-batch partition: first query whose AA part is >= the block's first owned AA ------------------
+__global__ void k_match_partition(const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, u64 nq,
+                                  u64 *__restrict__ qstart) {
+    const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > n_blocks) return;
+    if (b == n_blocks) { qstart[b] = nq; return; }
+    const u64 aa = blocks[b].own_aa;
+    u64 lo = 0, hi = nq;
+    while (lo < hi) {
+        const u64 mid = (lo + hi) >> 1;
+        if ((__ldg(&q[mid].value) >> 24) < aa) lo = mid + 1; else hi = mid;
+    }
+    qstart[b] = lo;
+}
+
+} // namespace mb

@@ -1,0 +1,211 @@
+// mb_radix.cuh — K2/K5: hand-written LSD radix sort (8-bit digits, one read + one write per pass).
+//
+// Replaces SORT_PARALLEL(..., Kmer::compareQueryKmer) (src/commons/KmerExtractor.cpp:79, Kmer.h:89-94)
+// and KmerMatcher::sortMatches / compareMatches (src/commons/KmerMatcher.cpp:1071-1078,1149-1166), and
+// serves as the stable multi-way partition of the multi-GPU exchange.
+//
+// B200 design ("one-sweep"): the digit histograms of ALL passes are taken in one read of the input;
+// each pass is then a single kernel in which a CTA ranks a tile of records (warp-level match_any
+// multisplit, stable), publishes its per-digit counts, resolves its global offsets by decoupled
+// look-back over the preceding tiles, stages the tile in digit order in shared memory and writes
+// runs to HBM.  Traffic per pass is exactly one read and one write of the records.  Tiles are
+// handed out by an atomic ticket so a tile only ever waits on tiles that are already running.
+#pragma once
+#include "mb_common.cuh"
+
+namespace mb {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_BINS = 256;
+constexpr int RS_MAX_PASSES = 16;
+
+constexpr u64 RS_FLAG_AGG = 1ull << 62;   // tile aggregate published
+constexpr u64 RS_FLAG_INC = 2ull << 62;   // inclusive prefix published
+constexpr u64 RS_VALUE_MASK = (1ull << 62) - 1;
+
+// ---- key functors: digit(record, pass) in [0,256) -------------------------------------------------
+struct KmerKey {            // sort by the amino-acid part and then the DNA part of Kmer::value
+    int first_bit;          // 24 = order the 40 AA bits only (all the join needs); 0 = full value
+    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const { return (u32) (r.value >> (first_bit + 8 * pass)) & 255u; }
+};
+
+struct KmerOwnerKey {       // multi-GPU bucketing: owner shard = number of bounds <= value
+    u64 bounds[8];
+    int n_bounds;
+    __device__ __forceinline__ u32 digit(const mb_kmer &r, int) const {
+        u32 o = 0;
+        for (int i = 0; i < n_bounds; ++i) o += (r.value >= bounds[i]) ? 1u : 0u;
+        return o;
+    }
+};
+
+// compareMatches order: (sequenceID, speciesId, frame, pos, hamming, dnaEncoding), packed into one
+// integer with per-batch field widths so that only the significant bytes are sorted.
+struct MatchKey {
+    int pos_bits, sp_bits, seq_bits;
+    __device__ __forceinline__ unsigned __int128 key(const mb_match &m) const {
+        unsigned __int128 k = qi_seq(m.qinfo);
+        k = (k << sp_bits) | (u32) m.speciesId;
+        k = (k << 3) | qi_frame(m.qinfo);
+        k = (k << pos_bits) | qi_pos(m.qinfo);
+        k = (k << 3) | (m.hamming & 7u);
+        k = (k << 24) | (m.dnaEncoding & 0xFFFFFFu);
+        return k;
+    }
+    __device__ __forceinline__ u32 digit(const mb_match &m, int pass) const { return (u32) (key(m) >> (8 * pass)) & 255u; }
+    int total_bits() const { return 24 + 3 + pos_bits + 3 + sp_bits + seq_bits; }
+};
+
+struct MatchHomeKey {       // multi-GPU: home rank of a match = (sequenceID-1) / reads_per_rank
+    u32 reads_per_rank;
+    __device__ __forceinline__ u32 digit(const mb_match &m, int) const { return (qi_seq(m.qinfo) - 1u) / reads_per_rank; }
+};
+
+// ---- histogram of every pass in one read -----------------------------------------------------------
+template <typename Rec, typename Key>
+__global__ void __launch_bounds__(RS_THREADS)
+k_radix_hist(const Rec *__restrict__ in, u64 n, Key key, int n_passes, u64 *__restrict__ hist /*[n_passes][256]*/) {
+    extern __shared__ u32 s_hist[]; // n_passes * 256
+    for (int i = threadIdx.x; i < n_passes * RS_BINS; i += RS_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    const u64 stride = (u64) gridDim.x * RS_THREADS;
+    for (u64 i = (u64) blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+        const Rec r = in[i];
+        for (int p = 0; p < n_passes; ++p) atomicAdd(&s_hist[p * RS_BINS + key.digit(r, p)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_passes * RS_BINS; i += RS_THREADS) {
+        const u32 v = s_hist[i];
+        if (v) atomicAdd(reinterpret_cast<unsigned long long *>(hist + i), (unsigned long long) v);
+    }
+}
+
+// exclusive scan of each pass' histogram (one CTA per pass, 256 threads); also flags trivial passes
+__global__ void __launch_bounds__(RS_BINS) k_radix_scan_hist(u64 *__restrict__ hist, u64 n, u32 *__restrict__ trivial) {
+    __shared__ u64 s[RS_BINS];
+    const int p = blockIdx.x, d = threadIdx.x;
+    const u64 v = hist[p * RS_BINS + d];
+    s[d] = v;
+    __syncthreads();
+    // simple Hillis-Steele over 256 entries
+    for (int off = 1; off < RS_BINS; off <<= 1) {
+        u64 t = d >= off ? s[d - off] : 0;
+        __syncthreads();
+        s[d] += t;
+        __syncthreads();
+    }
+    hist[p * RS_BINS + d] = s[d] - v;
+    if (v == n && n > 0) trivial[p] = 1; // every record shares this digit: the pass is the identity
+}
+
+// ---- one pass -----------------------------------------------------------------------------------
+template <typename Rec, typename Key, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS)
+k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, int pass,
+             const u64 *__restrict__ digit_base /*[256] exclusive*/, u64 *tile_state /*[tiles][256]*/,
+             u32 *ticket) {
+    constexpr int TILE = RS_THREADS * ITEMS;
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    Rec *s_rec = reinterpret_cast<Rec *>(s_raw);                                   // TILE records
+    u32 *s_whist = reinterpret_cast<u32 *>(s_raw + sizeof(Rec) * TILE);            // [RS_WARPS][256]
+    u32 *s_binstart = s_whist + RS_WARPS * RS_BINS;                                // [256]
+    u64 *s_gbase = reinterpret_cast<u64 *>(s_binstart + RS_BINS);                  // [256]
+    __shared__ u32 s_tile;
+    __shared__ u32 s_scan[RS_WARPS];
+
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    for (int i = tid; i < RS_WARPS * RS_BINS; i += RS_THREADS) s_whist[i] = 0;
+    __syncthreads();
+    const u32 tile = s_tile;
+    const u64 tile_base = (u64) tile * TILE;
+
+    // warp-striped load: item j of lane l is record tile_base + warp*32*ITEMS + j*32 + l
+    Rec rec[ITEMS];
+    u32 dig[ITEMS];
+    u32 rank[ITEMS];
+    const u64 wbase = tile_base + (u64) warp * 32 * ITEMS;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u64 idx = wbase + (u64) j * 32 + lane;
+        if (idx < n) { rec[j] = in[idx]; dig[j] = key.digit(rec[j], pass); }
+        else dig[j] = 0xFFFFFFFFu;
+    }
+    // stable ranking inside the warp: items are ordered by (j, lane) == memory order
+    u32 *wh = s_whist + warp * RS_BINS;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u32 d = dig[j];
+        const u32 peers = __match_any_sync(0xFFFFFFFFu, d);
+        u32 pre = 0;
+        if (d != 0xFFFFFFFFu) pre = wh[d];
+        __syncwarp();
+        if (d != 0xFFFFFFFFu && lane == (u32) (__ffs(peers) - 1)) wh[d] = pre + __popc(peers);
+        __syncwarp();
+        rank[j] = pre + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+
+    // per digit (thread == digit): exclusive scan over the warps, tile count, look-back
+    {
+        const u32 d = tid;
+        u32 sum = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) {
+            const u32 t = s_whist[w * RS_BINS + d];
+            s_whist[w * RS_BINS + d] = sum;
+            sum += t;
+        }
+        volatile u64 *state = tile_state;
+        state[(u64) tile * RS_BINS + d] = (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | sum;
+        u64 excl = 0;
+        if (tile > 0) {
+            long long p = (long long) tile - 1;
+            while (true) {
+                u64 s = state[(u64) p * RS_BINS + d];
+                if ((s >> 62) == 0) continue;            // not published yet: spin (the tile is running)
+                excl += s & RS_VALUE_MASK;
+                if (s & RS_FLAG_INC) break;
+                --p;
+            }
+            state[(u64) tile * RS_BINS + d] = RS_FLAG_INC | (excl + sum);
+        }
+        // block exclusive scan of the tile's digit counts
+        u32 incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= (u32) o) incl += t;
+        }
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        u32 wb = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) if ((u32) w < warp) wb += s_scan[w];
+        const u32 start = wb + incl - sum;
+        s_binstart[d] = start;
+        s_gbase[d] = digit_base[d] + excl - start;   // out index = s_gbase[digit] + position in the staged tile
+    }
+    __syncthreads();
+
+    // stage the tile in digit order
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u32 d = dig[j];
+        if (d != 0xFFFFFFFFu) s_rec[s_binstart[d] + s_whist[warp * RS_BINS + d] + rank[j]] = rec[j];
+    }
+    __syncthreads();
+    const u32 valid = (u32) (n - tile_base < (u64) TILE ? n - tile_base : (u64) TILE);
+    for (u32 i = tid; i < valid; i += RS_THREADS) {
+        const Rec r = s_rec[i];
+        out[s_gbase[key.digit(r, pass)] + i] = r;
+    }
+}
+
+template <typename Rec, int ITEMS>
+constexpr size_t radix_pass_smem() {
+    return sizeof(Rec) * RS_THREADS * ITEMS + sizeof(u32) * (RS_WARPS * RS_BINS + RS_BINS) + sizeof(u64) * RS_BINS;
+}
+
+} // namespace mb

@@ -1,0 +1,565 @@
+// mb_score.cuh — K6: per-read scoring, best-species selection, LCA and sub-species assignment.
+//
+// Replaces Classifier::assignTaxonomy (src/commons/Classifier.cpp:166-208) and
+// Taxonomer::chooseBestTaxon with everything below it (src/commons/Taxonomer.cpp:130-699):
+// getBestSpeciesMatches, getMatchPaths, combineMatchPaths / trimMatchPath, filterRedundantMatches,
+// lowerRankClassification / getSpeciesCladeCounts / BFS, and the Match score accessors
+// (src/commons/Match.h:32-86).
+//
+// The per-read logic is written once as score_read(), a pure function over the read's slice of the
+// sorted match list and a scratch arena.  On the GPU one warp owns one read at a time (reads are
+// handed out by an atomic ticket, so long and short reads balance); the taxonomy (parent / depth /
+// species tables, a few MB) stays L2-resident and LCA is a depth-equalising parent walk, which on a
+// tree equals the reference's Euler-tour RMQ.  All partial scores are multiples of 0.5 and the only
+// rounding operations (one division by the read length, the tie average) are IEEE fp32 operations
+// performed in the reference's order, so scores come out bit-identical.
+#pragma once
+#include "mb_common.cuh"
+
+namespace mb {
+
+struct ScoreCfg {
+    int format;            // Kmer_format
+    int dna_shift;         // Taxonomer.cpp:34-43: 3, or 3*(8-s) with syncmers
+    int max_codon_shift;   // 1, or 8-s with syncmers
+    int denominator;       // Taxonomer.cpp:44-48: 100 short reads, 1000 long reads
+    int min_cons_cnt, min_cons_cnt_euk;
+    float min_score, min_sp_score, tie_ratio;
+};
+
+struct PathRec {           // Taxonomer.h:35-58 MatchPath
+    int start, end;
+    float score;
+    int ham, depth;
+    int sm, em;            // indices of the first / last match of the path
+};
+
+struct ReadScratch {
+    PathRec *local;        // [cap_n] one per match of the current (species, frame) group
+    PathRec *paths;        // [cap_n]
+    PathRec *combined;     // [cap_n]
+    u8 *linked;            // [cap_n]
+    int32_t *sp_id;        // [cap_n] species with a score, in match order
+    float *sp_score;       // [cap_n]
+    int32_t *bucket_tax;   // [cap_b] filterRedundantMatches buckets
+    u8 *bucket_ham;        // [cap_b] 255 = empty
+    int32_t *tc_id;        // [cap_b] taxCnt in ascending taxID order
+    int32_t *tc_cnt;       // [cap_b]
+    int32_t *cl_id;        // [cap_c] clade table of lowerRankClassification
+    int32_t *cl_cnt;       // [cap_c]
+    int32_t *cl_parent;    // [cap_c] index into cl_* of the parent, -1 for the root
+    int cap_n, cap_b, cap_c;
+};
+
+// Match::getScore pieces (Match.h:32-44): a codon with Hamming 0 scores 3, else 2 - 0.5*h
+MB_HD float codon_score(u32 h) { return h == 0 ? 3.0f : 2.0f - 0.5f * (float) h; }
+MB_HD float match_score(const mb_match &m) {
+    float s = 0.f;
+    for (int k = 0; k < 8; ++k) s += codon_score((m.rightEndHamming >> (2 * k)) & 3u);
+    return s;
+}
+// Match::getRightPartScore / getLeftPartScore / get*PartHammingDist (Match.h:46-86)
+MB_HD float right_part_score(const mb_match &m, int range) {
+    float s = 0.f;
+    for (int k = 0; k < range; ++k) s += codon_score((m.rightEndHamming >> (2 * k)) & 3u);
+    return s;
+}
+MB_HD float left_part_score(const mb_match &m, int range) {
+    float s = 0.f;
+    for (int k = 0; k < range; ++k) s += codon_score((m.rightEndHamming >> (14 - 2 * k)) & 3u);
+    return s;
+}
+MB_HD int right_part_ham(const mb_match &m, int range) {
+    int s = 0;
+    for (int k = 0; k < range; ++k) s += (m.rightEndHamming >> (2 * k)) & 3;
+    return s;
+}
+MB_HD int left_part_ham(const mb_match &m, int range) {
+    int s = 0;
+    for (int k = 0; k < range; ++k) s += (m.rightEndHamming >> (14 - 2 * k)) & 3;
+    return s;
+}
+
+// Taxonomer::isConsecutive / isConsecutive2 (Taxonomer.cpp:671-699): DNA overlap of two matches
+// `shift` codons apart; which end overlaps depends on the metamer format.
+MB_HD bool dna_consecutive(const mb_match &a, const mb_match &b, int shift, int format) {
+    const u32 keep = (1u << (24 - 3 * shift)) - 1u;
+    if (format == 2) return (a.dnaEncoding & keep) == (b.dnaEncoding >> (3 * shift));
+    return (a.dnaEncoding >> (3 * shift)) == (b.dnaEncoding & keep);
+}
+
+MB_HD void path_init(PathRec &p, const mb_match *m, int i) {
+    p.start = (int) qi_pos(m[i].qinfo);
+    p.end = p.start + 23;
+    p.score = match_score(m[i]);
+    p.ham = m[i].hamming;
+    p.depth = 1;
+    p.sm = i;
+    p.em = i;
+}
+
+// Taxonomer::getMatchPaths (Taxonomer.cpp:487-648): matches [b,e) share species and frame and are
+// ordered by (pos, hamming, dnaEncoding).  Appends to scr.paths[n_paths...].
+MB_HD void match_paths(const mb_match *m, int b, int e, int min_depth, const ScoreCfg &cfg, ReadScratch &scr, int &n_paths) {
+    const bool forward = qi_frame(m[b].qinfo) < 3;
+    PathRec *local = scr.local;
+    u8 *linked = scr.linked;
+    for (int i = 0; i < e - b; ++i) linked[i] = 0;
+    int i = b;
+    u32 cur_pos = qi_pos(m[b].qinfo);
+    const int cur_b0 = i;
+    while (i < e && qi_pos(m[i].qinfo) == cur_pos) { path_init(local[i - b], m, i); ++i; }
+    int cur_b = cur_b0, cur_e = i;
+    while (i < e) {
+        const u32 next_pos = qi_pos(m[i].qinfo);
+        const int next_b = i;
+        while (i < e && qi_pos(m[i].qinfo) == next_pos) { path_init(local[i - b], m, i); ++i; }
+        const int next_e = i;
+        const int shift = (int) ((next_pos - cur_pos) / 3);
+        if (shift > 0 && shift <= cfg.max_codon_shift) {
+            for (int nx = next_b; nx < next_e; ++nx) {
+                // calScoreIncrement / calHammingDistIncrement (Taxonomer.cpp:650-669)
+                float inc = 0.f;
+                int hinc = 0;
+                for (int k = 0; k < shift; ++k) {
+                    const u32 h = (m[nx].rightEndHamming >> (2 * k)) & 3u;
+                    inc += codon_score(h);
+                    hinc += (int) h;
+                }
+                int best = -1;
+                float best_score = 0.f;
+                for (int c = cur_b; c < cur_e; ++c) {
+                    const bool ok = forward ? dna_consecutive(m[c], m[nx], shift, cfg.format)
+                                            : dna_consecutive(m[nx], m[c], shift, cfg.format);
+                    if (ok) {
+                        linked[c - b] = 1;
+                        if (local[c - b].score > best_score) { best = c; best_score = local[c - b].score; }
+                    }
+                }
+                if (best >= 0) {
+                    const PathRec &bp = local[best - b];
+                    PathRec &t = local[nx - b];
+                    t.start = bp.start;
+                    t.score = bp.score + inc;
+                    t.ham = bp.ham + hinc;
+                    t.depth = bp.depth + shift;
+                    t.sm = bp.sm;
+                }
+            }
+        }
+        for (int c = cur_b; c < cur_e; ++c)
+            if (!linked[c - b] && local[c - b].depth >= min_depth) scr.paths[n_paths++] = local[c - b];
+        if (i == e)
+            for (int nx = next_b; nx < next_e; ++nx)
+                if (local[nx - b].depth >= min_depth) scr.paths[n_paths++] = local[nx - b];
+        cur_b = next_b; cur_e = next_e; cur_pos = next_pos;
+    }
+}
+
+// comparator of combineMatchPaths (Taxonomer.cpp:417-426)
+MB_HD bool path_before(const PathRec &a, const PathRec &b) {
+    if (a.score != b.score) return a.score > b.score;
+    if (a.ham != b.ham) return a.ham < b.ham;
+    return a.start > b.start;
+}
+
+// The reference sorts the paths with std::sort.  Its comparator can tie, so the order of tied
+// paths is whatever libstdc++'s introsort leaves; to stay bit-exact this is the same algorithm
+// (bits/stl_algo.h: __introsort_loop with median-of-three + __final_insertion_sort, threshold 16).
+MB_HD void path_swap(PathRec &a, PathRec &b) { PathRec t = a; a = b; b = t; }
+MB_HD void path_unguarded_linear_insert(PathRec *last) {
+    PathRec val = *last;
+    PathRec *next = last - 1;
+    while (path_before(val, *next)) { *last = *next; last = next; --next; }
+    *last = val;
+}
+MB_HD void path_insertion_sort(PathRec *first, PathRec *last) {
+    if (first == last) return;
+    for (PathRec *i = first + 1; i != last; ++i) {
+        if (path_before(*i, *first)) {
+            PathRec val = *i;
+            for (PathRec *p = i; p != first; --p) *p = *(p - 1);
+            *first = val;
+        } else path_unguarded_linear_insert(i);
+    }
+}
+MB_HD void path_adjust_heap(PathRec *first, long hole, long len, PathRec value) {
+    const long top = hole;
+    long child = hole;
+    while (child < (len - 1) / 2) {
+        child = 2 * (child + 1);
+        if (path_before(first[child], first[child - 1])) --child;
+        first[hole] = first[child];
+        hole = child;
+    }
+    if ((len & 1) == 0 && child == (len - 2) / 2) {
+        child = 2 * (child + 1);
+        first[hole] = first[child - 1];
+        hole = child - 1;
+    }
+    long parent = (hole - 1) / 2;                       // __push_heap
+    while (hole > top && path_before(first[parent], value)) {
+        first[hole] = first[parent];
+        hole = parent;
+        parent = (hole - 1) / 2;
+    }
+    first[hole] = value;
+}
+MB_HD void path_heap_sort(PathRec *first, PathRec *last) { // __partial_sort(first, last, last)
+    const long len = last - first;
+    if (len >= 2)
+        for (long parent = (len - 2) / 2;; --parent) {   // __make_heap
+            path_adjust_heap(first, parent, len, first[parent]);
+            if (parent == 0) break;
+        }
+    while (last - first > 1) {                           // __sort_heap
+        --last;
+        PathRec value = *last;
+        *last = *first;
+        path_adjust_heap(first, 0, last - first, value);
+    }
+}
+MB_HD void path_sort(PathRec *first, PathRec *last) {
+    const long n = last - first;
+    if (n <= 1) return;
+    if (n > 16) {
+        // explicit stack for the recursion on the right part
+        PathRec *stk_first[64];
+        PathRec *stk_last[64];
+        int stk_depth[64];
+        int sp = 0;
+        int lg = 0;
+        for (long t = n; t > 1; t >>= 1) ++lg;
+        stk_first[sp] = first; stk_last[sp] = last; stk_depth[sp] = 2 * lg; ++sp;
+        while (sp > 0) {
+            --sp;
+            PathRec *f = stk_first[sp], *l = stk_last[sp];
+            int depth = stk_depth[sp];
+            while (l - f > 16) {
+                if (depth == 0) { path_heap_sort(f, l); break; }
+                --depth;
+                // __move_median_to_first(f, f+1, mid, l-1)
+                PathRec *a = f + 1, *bm = f + (l - f) / 2, *c = l - 1;
+                if (path_before(*a, *bm)) {
+                    if (path_before(*bm, *c)) path_swap(*f, *bm);
+                    else if (path_before(*a, *c)) path_swap(*f, *c);
+                    else path_swap(*f, *a);
+                } else if (path_before(*a, *c)) path_swap(*f, *a);
+                else if (path_before(*bm, *c)) path_swap(*f, *c);
+                else path_swap(*f, *bm);
+                // __unguarded_partition(f+1, l, pivot = f)
+                PathRec *lo = f + 1, *hi = l;
+                while (true) {
+                    while (path_before(*lo, *f)) ++lo;
+                    --hi;
+                    while (path_before(*f, *hi)) --hi;
+                    if (!(lo < hi)) break;
+                    path_swap(*lo, *hi);
+                    ++lo;
+                }
+                // recurse on [lo, l), continue with [f, lo)
+                if (sp < 64) { stk_first[sp] = lo; stk_last[sp] = l; stk_depth[sp] = depth; ++sp; }
+                l = lo;
+            }
+        }
+        path_insertion_sort(first, first + 16);
+        for (PathRec *i = first + 16; i != last; ++i) path_unguarded_linear_insert(i);
+    } else path_insertion_sort(first, last);
+}
+
+// Taxonomer::combineMatchPaths + trimMatchPath (Taxonomer.cpp:410-485) over scr.paths[0, n_paths)
+MB_HD float combine_paths(const mb_match *m, ReadScratch &scr, int n_paths, int read_length) {
+    PathRec *paths = scr.paths, *comb = scr.combined;
+    path_sort(paths, paths + n_paths);
+    int n_comb = 0;
+    float score = 0.f;
+    for (int i = 0; i < n_paths; ++i) {
+        PathRec cand = paths[i];
+        if (n_comb == 0) { comb[n_comb++] = cand; score += cand.score; continue; }
+        bool rejected = false;
+        for (int j = 0; j < n_comb; ++j) {
+            const PathRec &kept = comb[j];
+            if (cand.end < kept.start || kept.end < cand.start) continue;
+            const int lo = cand.start > kept.start ? cand.start : kept.start;
+            const int hi = cand.end < kept.end ? cand.end : kept.end;
+            const int overlap = hi - lo + 1;
+            if (overlap == cand.end - cand.start + 1 || overlap >= 24) { rejected = true; break; }
+            if (cand.start < kept.start) {
+                cand.end = kept.start - 1;
+                int h = cand.ham - right_part_ham(m[cand.em], overlap / 3);
+                cand.ham = h > 0 ? h : 0;
+                cand.score = cand.score - right_part_score(m[cand.em], overlap / 3) - (float) (overlap % 3);
+            } else {
+                cand.start = kept.end + 1;
+                int h = cand.ham - left_part_ham(m[cand.sm], overlap / 3);
+                cand.ham = h > 0 ? h : 0;
+                cand.score = cand.score - left_part_score(m[cand.sm], overlap / 3) - (float) (overlap % 3);
+            }
+        }
+        if (!rejected) { comb[n_comb++] = cand; score += cand.score; }
+    }
+    return score / (float) read_length;
+}
+
+struct BestSpecies { int32_t tax; float score; bool lca; int rb, re; };
+
+// Taxonomer::getBestSpeciesMatches (Taxonomer.cpp:316-408); matches [b,e) belong to one read
+MB_HD BestSpecies best_species(const mb_match *m, int b, int e, int query_length, const ScoreCfg &cfg,
+                               const TaxView &tax, ReadScratch &scr) {
+    BestSpecies out;
+    out.tax = 0; out.score = 0.f; out.lca = false; out.rb = 0; out.re = 0;
+    int n_sp = 0, meaningful = 0;
+    float best_sp = 0.f;
+    int i = b;
+    while (i < e) {
+        const int32_t species = m[i].speciesId;
+        const int sp_begin = i;
+        int n_paths = 0;
+        int min_depth = cfg.min_cons_cnt;
+        if (tax_is_ancestor(tax, tax.eukaryota, species)) min_depth = cfg.min_cons_cnt_euk;
+        while (i < e && m[i].speciesId == species) {
+            const u32 frame = qi_frame(m[i].qinfo);
+            const int fb = i;
+            while (i < e && m[i].speciesId == species && qi_frame(m[i].qinfo) == frame) ++i;
+            if (i - fb > 1) match_paths(m, fb, i, min_depth, cfg, scr, n_paths);
+        }
+        if (n_paths > 0) {
+            float score = combine_paths(m, scr, n_paths, query_length);
+            score = score < 1.0f ? score : 1.0f;
+            if (score < cfg.min_score) continue;
+            scr.sp_id[n_sp] = species;
+            scr.sp_score[n_sp] = score;
+            ++n_sp;
+            if (score > 0.f) ++meaningful;
+            if (score > best_sp) { best_sp = score; out.rb = sp_begin; out.re = i; }
+        }
+    }
+    if (meaningful == 0) { out.score = 0.f; return out; }
+    // species within tie_ratio of the best (Taxonomer.cpp:388-402)
+    int n_top = 0;
+    int32_t lca = 0;
+    bool have = false;
+    int32_t single = 0;
+    const float cut = best_sp * cfg.tie_ratio;
+    for (int k = 0; k < n_sp; ++k) {
+        if (scr.sp_score[k] >= cut) {
+            const int32_t t = scr.sp_id[k];
+            if (n_top == 0) single = t;
+            ++n_top;
+            out.score += scr.sp_score[k];
+            // NcbiTaxonomy::LCA(vector) (NcbiTaxonomy.cpp:313-333): fold over the existing taxa
+            if (tax_exists(tax, t)) {
+                if (!have) { lca = t; have = true; }
+                else lca = tax_lca_existing(tax, lca, t);
+            }
+        }
+    }
+    if (n_top > 1) {
+        out.lca = true;
+        out.tax = have ? lca : 0;
+        out.score /= (float) n_top;
+        return out;
+    }
+    out.tax = single;
+    return out;
+}
+
+// Scores one read.  Returns the number of taxCnt entries left in scr.tc_id / scr.tc_cnt.
+MB_HD int score_read(const mb_match *m, int b, int e, int query_length, const ScoreCfg &cfg, const TaxView &tax,
+                     ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
+    r.classification = 0; r.score = 0.f; r.is_classified = 0; r.query_length = query_length;
+    r.hamming_dist = 0; r.taxcnt_begin = 0; r.taxcnt_end = 0; r.n_matches = e - b;
+    if (e <= b) return 0;
+    const BestSpecies best = best_species(m, b, e, query_length, cfg, tax, scr);
+    // Taxonomer::chooseBestTaxon (Taxonomer.cpp:130-202), em == false
+    if (best.score == 0.f || best.score < cfg.min_score) { r.score = best.score; return 0; }
+    if (best.lca) { r.is_classified = 1; r.classification = best.tax; r.score = best.score; return 0; }
+
+    // filterRedundantMatches (Taxonomer.cpp:205-241)
+    const int max_q = (query_length + 3) / cfg.dna_shift;
+    if (max_q + 1 > scr.cap_b) { *error_flag = 2; return 0; }
+    for (int k = 0; k <= max_q; ++k) { scr.bucket_ham[k] = 255; scr.bucket_tax[k] = 0; }
+    for (int i = best.rb; i < best.re; ++i) {
+        const int qd = (int) (qi_pos(m[i].qinfo) / (u32) cfg.dna_shift);
+        if (qd > max_q) continue;
+        const u8 h = m[i].hamming;
+        if (scr.bucket_ham[qd] == 255 || h < scr.bucket_ham[qd]) { scr.bucket_tax[qd] = m[i].targetId; scr.bucket_ham[qd] = h; }
+        else if (h == scr.bucket_ham[qd]) scr.bucket_tax[qd] = tax_lca(tax, scr.bucket_tax[qd], m[i].targetId);
+    }
+    int n_tc = 0;                                   // taxCnt as a sorted array (std::map order)
+    for (int k = 0; k <= max_q; ++k) {
+        if (scr.bucket_ham[k] == 255) continue;
+        const int32_t t = scr.bucket_tax[k];
+        int p = 0;
+        while (p < n_tc && scr.tc_id[p] < t) ++p;
+        if (p < n_tc && scr.tc_id[p] == t) { ++scr.tc_cnt[p]; continue; }
+        for (int z = n_tc; z > p; --z) { scr.tc_id[z] = scr.tc_id[z - 1]; scr.tc_cnt[z] = scr.tc_cnt[z - 1]; }
+        scr.tc_id[p] = t; scr.tc_cnt[p] = 1;
+        ++n_tc;
+    }
+    r.is_classified = 1;
+    r.score = best.score;
+    if (best.score < cfg.min_sp_score) {
+        // parent of the species-rank ancestor (Taxonomer.cpp:186-190)
+        int32_t sp = 0;
+        if (best.tax > 1 && tax_exists(tax, best.tax)) sp = tax.species_rank_of[best.tax];
+        r.classification = (sp != 0 && tax_exists(tax, sp)) ? tax.parent[sp] : 0;
+        return n_tc;
+    }
+    // lowerRankClassification / getSpeciesCladeCounts / BFS (Taxonomer.cpp:252-314), accessionLevel != 2
+    const int32_t species = best.tax;
+    int n_cl = 0;
+    bool overflow = false;
+    for (int k = 0; k < n_tc && !overflow; ++k) {
+        int32_t t = scr.tc_id[k];
+        const int cnt = scr.tc_cnt[k];
+        if (t == 0 || !tax_exists(tax, t)) continue;
+        int child_slot = -1;
+        int guard = 0;
+        while (true) {
+            int slot = 0;
+            while (slot < n_cl && scr.cl_id[slot] != t) ++slot;
+            if (slot == n_cl) {
+                if (n_cl >= scr.cap_c) { overflow = true; break; }
+                scr.cl_id[slot] = t; scr.cl_cnt[slot] = 0; scr.cl_parent[slot] = -1;
+                ++n_cl;
+            }
+            scr.cl_cnt[slot] += cnt;
+            if (child_slot >= 0) scr.cl_parent[child_slot] = slot;
+            child_slot = slot;
+            if (t == species || guard++ >= 1000) break;
+            const int32_t p = tax.parent[t];
+            if (p == t || !tax_exists(tax, p)) break;
+            t = p;
+        }
+    }
+    if (overflow) { *error_flag = 3; r.classification = species; return n_tc; }
+    int root = 0;
+    while (root < n_cl && scr.cl_id[root] != species) ++root;
+    if (root == n_cl) { r.classification = species; return n_tc; }
+    const int floor_cnt = (query_length - 1) / cfg.denominator;
+    int cur = root;
+    while (true) {
+        int max_cnt = floor_cnt, nb = 0, pick = -1, n_children = 0;
+        for (int k = 0; k < n_cl; ++k) {
+            if (scr.cl_parent[k] != cur) continue;
+            ++n_children;
+            const int cnt = scr.cl_cnt[k];
+            if (cnt > max_cnt) { nb = 1; pick = k; max_cnt = cnt; }
+            else if (cnt == max_cnt) { ++nb; pick = k; }
+        }
+        if (n_children == 0 || nb != 1) break;
+        cur = pick;
+    }
+    r.classification = scr.cl_id[cur];
+    return n_tc;
+}
+
+#if defined(__CUDACC__)
+// ---- segmentation of the sorted match list by read (Classifier.cpp:174-185) ----------------------------
+__global__ void k_segment_matches(const mb_match *__restrict__ m, u64 n, u32 n_reads, u64 *__restrict__ seg_begin,
+                                  u64 *__restrict__ seg_end, u32 *__restrict__ max_len) {
+    const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 s = qi_seq(m[i].qinfo);
+    if (s == 0 || s > n_reads) return;
+    const bool first = i == 0 || qi_seq(m[i - 1].qinfo) != s;
+    const bool last = i + 1 == n || qi_seq(m[i + 1].qinfo) != s;
+    if (first) seg_begin[s - 1] = i;
+    if (last) {
+        seg_end[s - 1] = i + 1;
+    }
+}
+__global__ void k_segment_max(const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end, u32 n_reads, u32 *__restrict__ max_len) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    u32 len = 0;
+    if (i < n_reads) len = (u32) (seg_end[i] - seg_begin[i]);
+    for (int d = 16; d > 0; d >>= 1) { const u32 o = __shfl_xor_sync(0xFFFFFFFFu, len, d); len = o > len ? o : len; }
+    if ((threadIdx.x & 31) == 0 && len) atomicMax(max_len, len);
+}
+
+struct ScoreArena {        // one slice per resident warp
+    unsigned char *base;
+    u64 slice_bytes;
+    int cap_n, cap_b, cap_c;
+};
+
+__host__ __device__ inline u64 arena_slice_bytes(int cap_n, int cap_b, int cap_c) {
+    u64 b = 0;
+    b += (u64) cap_n * sizeof(PathRec) * 3;
+    b += (u64) cap_n * (sizeof(int32_t) + sizeof(float));
+    b += (u64) cap_b * sizeof(int32_t) * 3;
+    b += (u64) cap_c * sizeof(int32_t) * 3;
+    b += (u64) cap_n + (u64) cap_b;
+    return (b + 255) & ~255ull;
+}
+
+__device__ __forceinline__ void arena_carve(const ScoreArena &a, u64 slot, ReadScratch &s) {
+    unsigned char *p = a.base + slot * a.slice_bytes;
+    s.local = reinterpret_cast<PathRec *>(p); p += (u64) a.cap_n * sizeof(PathRec);
+    s.paths = reinterpret_cast<PathRec *>(p); p += (u64) a.cap_n * sizeof(PathRec);
+    s.combined = reinterpret_cast<PathRec *>(p); p += (u64) a.cap_n * sizeof(PathRec);
+    s.sp_id = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_n * sizeof(int32_t);
+    s.sp_score = reinterpret_cast<float *>(p); p += (u64) a.cap_n * sizeof(float);
+    s.bucket_tax = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_b * sizeof(int32_t);
+    s.tc_id = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_b * sizeof(int32_t);
+    s.tc_cnt = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_b * sizeof(int32_t);
+    s.cl_id = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_c * sizeof(int32_t);
+    s.cl_cnt = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_c * sizeof(int32_t);
+    s.cl_parent = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_c * sizeof(int32_t);
+    s.linked = p; p += a.cap_n;
+    s.bucket_ham = p;
+    s.cap_n = a.cap_n; s.cap_b = a.cap_b; s.cap_c = a.cap_c;
+}
+
+constexpr int SC_THREADS = 128;
+
+// One warp per read at a time; reads are handed out in chunks by an atomic ticket.
+__global__ void __launch_bounds__(SC_THREADS)
+k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
+        const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
+        mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
+        u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag) {
+    const u32 lane = threadIdx.x & 31;
+    const u64 slot = (u64) blockIdx.x * (SC_THREADS / 32) + (threadIdx.x >> 5);
+    ReadScratch scr;
+    arena_carve(arena, slot, scr);
+    constexpr u32 CHUNK = 4;
+    while (true) {
+        u32 r0 = 0;
+        if (lane == 0) r0 = atomicAdd(ticket, CHUNK);
+        r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
+        if (r0 >= n_reads) break;
+        if (lane == 0) {
+            const u32 r1 = r0 + CHUNK < n_reads ? r0 + CHUNK : n_reads;
+            for (u32 r = r0; r < r1; ++r) {
+                // queryLength = max covered length of each mate (KmerExtractor.cpp:452,476)
+                int ql = max_covered_length((int) lens[2 * r]);
+                if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
+                const u64 b = seg_begin[r], e = seg_end[r];
+                mb_read_result res;
+                int n_tc = 0;
+                if (e > b && (e - b) <= (u64) arena.cap_n) {
+                    n_tc = score_read(m + b, 0, (int) (e - b), ql, cfg, tax, scr, res, error_flag);
+                } else {
+                    if (e > b) *error_flag = 4;
+                    res.classification = 0; res.score = 0.f; res.is_classified = 0; res.query_length = ql;
+                    res.hamming_dist = 0; res.taxcnt_begin = 0; res.taxcnt_end = 0; res.n_matches = (int32_t) (e - b);
+                }
+                if (n_tc > 0) {
+                    const u64 o = atomicAdd(tc_counter, (unsigned long long) n_tc);
+                    if (o + (u64) n_tc <= tc_cap) {
+                        for (int k = 0; k < n_tc; ++k) { tc_id_out[o + k] = scr.tc_id[k]; tc_cnt_out[o + k] = scr.tc_cnt[k]; }
+                        res.taxcnt_begin = (int32_t) o;
+                        res.taxcnt_end = (int32_t) (o + n_tc);
+                    } else *error_flag = 5;
+                }
+                results[r] = res;
+            }
+        }
+        __syncwarp();
+    }
+}
+#endif // __CUDACC__
+
+} // namespace mb

@@ -1,0 +1,298 @@
+// mb_host.cpp — host side of the B200 classifier (see mb_host.h).  File:line citations are relative to
+// the reference tree.
+#include "mb_host.h"
+
+#include <zlib.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+
+namespace mbh {
+
+// ------------------------------------------------------------------------------------------------------
+// taxonomyDB
+// ------------------------------------------------------------------------------------------------------
+namespace {
+
+bool readFile(const std::string &path, std::vector<char> &out, std::string &err) {
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) { err = "cannot open " + path; return false; }
+    fseek(f, 0, SEEK_END);
+    long sz = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    out.resize((size_t) sz);
+    size_t got = sz ? fread(out.data(), 1, (size_t) sz, f) : 0;
+    fclose(f);
+    if (got != (size_t) sz) { err = "short read on " + path; return false; }
+    return true;
+}
+
+// MathUtil::flog2 (lib/mmseqs/src/commons/MathUtil.h:107-119): the width of the sparse table M in the
+// serialized taxonomy is floor(flog2(2*maxNodes)) + 1, computed with this approximation.
+float flog2Approx(float x) {
+    if (x <= 0) return -128;
+    int32_t bits;
+    memcpy(&bits, &x, 4);
+    float e = (float) (((bits & 0x7F800000) >> 23) - 0x7f);
+    bits = (bits & 0x007FFFFF) | 0x3f800000;
+    memcpy(&x, &bits, 4);
+    x -= 1.0f;
+    x *= (1.441740 + x * (-0.7077702 + x * (0.4123442 + x * (-0.1903190 + x * 0.0440047))));
+    return x + e;
+}
+
+} // namespace
+
+bool Taxonomy::load(const std::string &path, std::string &err) {
+    std::vector<char> blob;
+    if (!readFile(path, blob, err)) return false;
+    const char *p = blob.data();
+    const char *end = p + blob.size();
+    auto need = [&](size_t n) { return (size_t) (end - p) >= n; };
+    if (!need(12)) { err = "taxonomyDB truncated"; return false; }
+    int32_t version;
+    memcpy(&version, p, 4); p += 4;
+    if (version != 2) { err = "taxonomyDB: unsupported serialization version"; return false; }
+    uint64_t flag;
+    memcpy(&flag, p, 8);
+    internalIds_ = false;
+    if (flag == 1) { internalIds_ = true; p += 8; }          // TaxonomyWrapper.cpp:372-378
+    if (!need(12)) { err = "taxonomyDB truncated"; return false; }
+    uint64_t maxNodes;
+    memcpy(&maxNodes, p, 8); p += 8;
+    memcpy(&maxTaxID_, p, 4); p += 4;
+    const size_t nT = (size_t) maxTaxID_ + 1;
+    if (!need(maxNodes * sizeof(TaxNodeRec) + nT * 4 * (internalIds_ ? 2 : 1))) { err = "taxonomyDB truncated"; return false; }
+    nodes_.resize(maxNodes);
+    memcpy(nodes_.data(), p, maxNodes * sizeof(TaxNodeRec)); p += maxNodes * sizeof(TaxNodeRec);
+    D_.resize(nT);
+    memcpy(D_.data(), p, nT * 4); p += nT * 4;
+    internal2org_.clear();
+    if (internalIds_) { internal2org_.resize(nT); memcpy(internal2org_.data(), p, nT * 4); p += nT * 4; }
+    // E, L (2N each), H (N) and the sparse table M are only needed for the reference's RMQ LCA; the GPU
+    // uses parent/depth arrays, so they are skipped.
+    const size_t dim = maxNodes * 2;
+    const size_t k = (size_t) ((int) flog2Approx((float) dim)) + 1;
+    const size_t skip = (dim * 2 + maxNodes + dim * k) * 4;
+    if (!need(skip + 16)) { err = "taxonomyDB truncated (tables)"; return false; }
+    p += skip;
+    // StringBlock<unsigned int> (lib/mmseqs/src/commons/StringBlock.h:116-145)
+    uint64_t byteCap;
+    uint32_t entryCap, entryCnt;
+    memcpy(&byteCap, p, 8); p += 8;
+    memcpy(&entryCap, p, 4); p += 4;
+    memcpy(&entryCnt, p, 4); p += 4;
+    if (!need(byteCap + (size_t) entryCnt * 4)) { err = "taxonomyDB truncated (strings)"; return false; }
+    strData_.assign(p, p + byteCap); p += byteCap;
+    strOffsets_.resize(entryCnt);
+    memcpy(strOffsets_.data(), p, (size_t) entryCnt * 4);
+    (void) entryCap;
+    eukaryota_ = 0;                                           // TaxonomyWrapper.h:90-100
+    for (const TaxNodeRec &n : nodes_) {
+        if (n.nameIdx == 0) continue;
+        if (strcmp(str(n.nameIdx), "Eukaryota") == 0) { eukaryota_ = n.taxId; break; }
+    }
+    return true;
+}
+
+int Taxonomy::rankIndex(const char *r) {
+    static const std::map<std::string, int> ranks = {
+        {"forma", 1}, {"varietas", 2}, {"subspecies", 3}, {"species", 4}, {"species subgroup", 5},
+        {"species group", 6}, {"subgenus", 7}, {"genus", 8}, {"subtribe", 9}, {"tribe", 10},
+        {"subfamily", 11}, {"family", 12}, {"superfamily", 13}, {"parvorder", 14}, {"infraorder", 15},
+        {"suborder", 16}, {"order", 17}, {"superorder", 18}, {"infraclass", 19}, {"subclass", 20},
+        {"class", 21}, {"superclass", 22}, {"subphylum", 23}, {"phylum", 24}, {"superphylum", 25},
+        {"subkingdom", 26}, {"kingdom", 27}, {"superkingdom", 28}, {"domain", 28}};
+    auto it = ranks.find(r);
+    return it == ranks.end() ? -1 : it->second;
+}
+
+int32_t Taxonomy::atRank(int32_t t, const char *rank) const {
+    if (t == 0 || !exists(t) || t == 1) return 0;
+    const int want = rankIndex(rank);
+    const TaxNodeRec *cur = &nodes_[D_[t]];
+    int steps = 0;
+    while (steps < 30 && rankIndex(str(cur->rankIdx)) < want) {
+        cur = &nodes_[D_[cur->parentTaxId]];
+        ++steps;
+    }
+    return steps == 30 ? t : cur->taxId;
+}
+
+void Taxonomy::denseParents(std::vector<int32_t> &parent, std::vector<int32_t> &speciesRankOf) const {
+    const size_t n = (size_t) maxTaxID_ + 1;
+    parent.assign(n, -1);
+    speciesRankOf.assign(n, 0);
+    // rank index per node once, then the <= 30-step walk of getTaxIdAtRank per taxon
+    std::vector<int> nodeRank(nodes_.size());
+    for (size_t i = 0; i < nodes_.size(); ++i) nodeRank[i] = rankIndex(str(nodes_[i].rankIdx));
+    const int want = rankIndex("species");
+    for (size_t t = 0; t < n; ++t) {
+        if (D_[t] == -1) continue;
+        const TaxNodeRec &nd = nodes_[D_[t]];
+        parent[t] = nd.parentTaxId;
+        if (t <= 1) continue;
+        int idx = D_[t], steps = 0;
+        while (steps < 30 && nodeRank[idx] < want) { idx = D_[nodes_[idx].parentTaxId]; ++steps; }
+        speciesRankOf[t] = steps == 30 ? (int32_t) t : nodes_[idx].taxId;
+    }
+    if (n > 0 && D_[0] != -1 && parent[0] < 0) parent[0] = 0;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// database directory
+// ------------------------------------------------------------------------------------------------------
+static DbParameters readDbParameters(const std::string &dir) {
+    DbParameters p;
+    std::ifstream f(dir + "/db.parameters");
+    if (!f.is_open()) return p;
+    p.present = true;
+    std::string line;
+    while (std::getline(f, line)) {
+        const size_t tab = line.find('\t');
+        if (tab == std::string::npos) continue;
+        const std::string k = line.substr(0, tab), v = line.substr(tab + 1);
+        if (k == "Reduced_alphabet") p.reducedAA = atoi(v.c_str());
+        else if (k == "Accession_level") p.accessionLevel = atoi(v.c_str());
+        else if (k == "DB_name") p.dbName = v;
+        else if (k == "Creation_date") p.dbDate = v;
+        else if (k == "Skip_redundancy") { if (v == "1") p.skipRedundancy = 1; }
+        else if (k == "Syncmer") { if (v == "1") p.syncmer = 1; }
+        else if (k == "S-mer_len") p.smerLen = atoi(v.c_str());   // never written by the builder (it writes Syncmer_len)
+        else if (k == "Kmer_format") p.kmerFormat = atoi(v.c_str());
+    }
+    return p;
+}
+
+Database::~Database() { if (ctx_) mb_destroy(ctx_); }
+
+bool Database::open(const std::string &dir, Options &opt, int shard, int nShards, std::string &err) {
+    // loadDbParameters (common.cpp:88-133): DB-side values win where the reference lets them
+    const DbParameters dp = readDbParameters(dir);
+    int skipRedundancy = 0;
+    if (dp.present) {
+        if (dp.reducedAA) opt.reducedAA = dp.reducedAA;
+        if (dp.skipRedundancy) skipRedundancy = 1;
+        if (dp.syncmer && !opt.syncmer) opt.syncmer = 1;
+        if (dp.smerLen > 0) opt.smerLen = dp.smerLen;
+        if (dp.kmerFormat > 0) opt.kmerFormat = dp.kmerFormat;
+        if (dp.accessionLevel == 0 && opt.accessionLevel == 1) opt.accessionLevel = 0;
+        if (dp.accessionLevel == 1 && opt.accessionLevel == 0) opt.accessionLevel = 2;
+    }
+    if (opt.reducedAA) { err = "reduced amino-acid alphabet databases are outside this path (ReducedKmerMatcher)"; return false; }
+    if (opt.accessionLevel != 0) { err = "accession-level classification is outside this path"; return false; }
+    if (opt.em) { err = "--em is outside this path"; return false; }
+    if (opt.maskMode) { err = "--mask 1 (tantan masking) is not implemented on this path yet"; return false; }
+
+    const std::string taxPath = opt.taxonomyPath.empty() ? dir + "/taxonomyDB" : opt.taxonomyPath + "/taxonomyDB";
+    if (!tax_.load(taxPath, err)) return false;
+
+    std::vector<char> words, info, splitBytes;
+    if (!readFile(dir + "/diffIdx", words, err) || !readFile(dir + "/info", info, err) || !readFile(dir + "/split", splitBytes, err)) return false;
+    const uint16_t *w = reinterpret_cast<const uint16_t *>(words.data());
+    const uint32_t *inf = reinterpret_cast<const uint32_t *>(info.data());
+    const size_t nWords = words.size() / 2, nKmers = info.size() / 4;
+    const mb_split *splits = reinterpret_cast<const mb_split *>(splitBytes.data());
+    const size_t nSplits = splitBytes.size() / sizeof(mb_split);
+
+    // usable split entries (KmerMatcher.cpp:157-164): entry 0 plus every later entry with a real ADkmer
+    std::vector<mb_split> cuts;
+    for (size_t i = 0; i < nSplits; ++i)
+        if (i == 0 || (splits[i].ADkmer != 0 && splits[i].ADkmer != UINT64_MAX)) cuts.push_back(splits[i]);
+
+    // Shard boundaries: nShards-1 split entries spread evenly over the usable ones.  Shard g starts at the
+    // k-mer ADkmer of its boundary entry; that k-mer's delta occupies the words just before diffIdxOffset.
+    struct Cut { uint64_t value; size_t wordStart; size_t wordAfter; size_t kIndex; };
+    std::vector<Cut> cutPoints;       // one per boundary
+    bounds_.clear();
+    if (nShards > 1) {
+        if ((size_t) nShards > cuts.size()) { err = "more shards than usable split entries"; return false; }
+        for (int g = 1; g < nShards; ++g) {
+            const mb_split &s = cuts[(size_t) g * cuts.size() / (size_t) nShards];
+            if (s.diffIdxOffset == 0 || s.diffIdxOffset > nWords || s.infoIdxOffset == 0) { err = "split entry out of range"; return false; }
+            size_t start = (size_t) s.diffIdxOffset - 1;       // terminator word of ADkmer's delta
+            while (start > 0 && !(w[start - 1] & 0x8000u)) --start;
+            cutPoints.push_back({s.ADkmer, start, (size_t) s.diffIdxOffset, (size_t) s.infoIdxOffset - 1});
+            bounds_.push_back(s.ADkmer);
+        }
+    }
+    size_t wBegin = 0, wEnd = nWords, kBegin = 0, kEnd = nKmers;
+    std::vector<uint16_t> shardWords;
+    if (nShards > 1) {
+        if (shard > 0) { wBegin = cutPoints[shard - 1].wordAfter; kBegin = cutPoints[shard - 1].kIndex; }
+        if (shard + 1 < nShards) { wEnd = cutPoints[shard].wordStart; kEnd = cutPoints[shard].kIndex; }
+        if (shard > 0) {
+            // re-encode the shard's first k-mer as a delta from 0 (IndexCreator.cpp:868-886) so that the
+            // shard is a self-contained stream
+            uint64_t v = cutPoints[shard - 1].value;
+            uint16_t tmp[5];
+            int idx = 3;
+            tmp[4] = (uint16_t) (0x8000u | (v & 0x7FFFu));
+            v >>= 15;
+            while (v) { tmp[idx--] = (uint16_t) (v & 0x7FFFu); v >>= 15; }
+            for (int k = idx + 1; k <= 4; ++k) shardWords.push_back(tmp[k]);
+        }
+        shardWords.insert(shardWords.end(), w + wBegin, w + wEnd);
+    }
+
+    mb_default_params(&par_);
+    par_.device = opt.device;
+    par_.kmer_format = opt.kmerFormat;
+    par_.syncmer = opt.syncmer;
+    par_.smer_len = opt.smerLen;
+    par_.seq_mode = opt.seqMode;
+    par_.min_cons_cnt = opt.minConsCnt;
+    par_.min_cons_cnt_euk = opt.minConsCntEuk;
+    par_.min_score = opt.minScore;
+    par_.min_sp_score = opt.minSpScore;
+    par_.tie_ratio = opt.tieRatio;
+    par_.skip_redundancy = skipRedundancy;
+    par_.accession_level = 0;
+    par_.last_shard = (shard + 1 == nShards) ? 1 : 0;
+    ctx_ = mb_create(&par_);
+    if (!ctx_) { err = mb_global_error(); return false; }
+
+    // taxonomy tables; taxId2speciesId as KmerMatcher::loadTaxIdList builds it (KmerMatcher.cpp:56-120)
+    std::vector<int32_t> parent, speciesRankOf, speciesOf((size_t) tax_.maxTaxId() + 1, 0);
+    tax_.denseParents(parent, speciesRankOf);
+    {
+        std::ifstream f(dir + "/taxID_list");
+        if (!f.is_open()) { err = "cannot open " + dir + "/taxID_list"; return false; }
+        std::string line;
+        while (std::getline(f, line)) {
+            if (line.empty()) continue;
+            const int32_t taxId = (int32_t) strtoul(line.c_str(), nullptr, 10);
+            const TaxNodeRec *n = tax_.node(taxId);
+            if (!n) continue;
+            const int32_t sp = tax_.atRank(taxId, "species");
+            if (taxId != n->taxId) speciesOf[taxId] = sp;
+            int guard = 0;
+            while (n->taxId != sp && guard++ < 1000) {
+                speciesOf[n->taxId] = sp;
+                const TaxNodeRec *pn = tax_.node(n->parentTaxId);
+                if (!pn || pn == n) break;
+                n = pn;
+            }
+            if (sp >= 0 && sp <= tax_.maxTaxId()) speciesOf[sp] = sp;
+        }
+    }
+    if (mb_load_taxonomy(ctx_, parent.data(), speciesOf.data(), speciesRankOf.data(), tax_.maxTaxId(), tax_.node0TaxId(), tax_.eukaryota()) != MB_OK) {
+        err = mb_last_error(ctx_);
+        return false;
+    }
+    int rc;
+    if (nShards > 1) rc = mb_load_db(ctx_, shardWords.data(), shardWords.size(), inf + kBegin, kEnd - kBegin);
+    else rc = mb_load_db(ctx_, w, nWords, inf, nKmers);
+    if (rc != MB_OK) { err = mb_last_error(ctx_); return false; }
+    nKmers_ = kEnd - kBegin;
+    nWords_ = nShards > 1 ? shardWords.size() : nWords;
+    return true;
+}
+
+} // namespace mbh

@@ -60,3 +60,59 @@ def check_results_against_golden(rows, res, ids, cnt):
                 and row[5] == bits and row[6] == tc):
             bad.append(i)
     return bad
+
+
+# ---- host emulation of the device logic (tests/emu) ----------------------------------------------------
+import ctypes as C
+import subprocess
+
+EMU_DIR = os.path.join(HERE, "emu")
+ROOT = os.path.dirname(HERE)
+
+
+def emu_lib():
+    so = os.path.join(EMU_DIR, "libemu.so")
+    srcs = [os.path.join(EMU_DIR, "emu.cpp")] + [os.path.join(ROOT, "metabuli_work_b200", "csrc", f)
+                                                 for f in ("mb_common.cuh", "mb_score.cuh", "mb_tables.cu")]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["/usr/bin/g++", "-O2", "-std=gnu++17", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", so,
+                               srcs[0], "-x", "c++", srcs[3]])
+    L = C.CDLL(so)
+    vp, sz, i32, u32 = C.c_void_p, C.c_size_t, C.c_int32, C.c_uint32
+    L.emu_extract.restype = sz
+    L.emu_extract.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, u32, vp, sz]
+    L.emu_hamming.argtypes = [vp, vp, vp, sz, vp, vp]
+    L.emu_lca.restype = i32
+    L.emu_lca.argtypes = [vp, vp, i32, i32, i32, i32]
+    L.emu_score.restype = C.c_int64
+    L.emu_score.argtypes = [vp, sz, vp, u32, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                            C.c_float, vp, vp, vp, vp, i32, i32, i32, vp, vp, vp, sz]
+    return L
+
+
+def dense_taxonomy(db):
+    """Dense arrays of mb_load_taxonomy derived from the ORACLE's taxonomy (test side)."""
+    L = orc.lib()
+    mx = L.orc_tax_max_taxid(db.h)
+    parent = np.full(mx + 1, -1, dtype=np.int32)
+    species_of = np.zeros(mx + 1, dtype=np.int32)
+    species_rank_of = np.zeros(mx + 1, dtype=np.int32)
+    for t in range(mx + 1):
+        if t == 0:
+            continue
+        if L.orc_tax_rank(db.h, t) == b"" and L.orc_tax_name(db.h, t) == b"":
+            continue
+        parent[t] = L.orc_tax_parent(db.h, t)
+        species_of[t] = L.orc_tax_species_of(db.h, t)
+        species_rank_of[t] = L.orc_tax_at_rank(db.h, t, b"species")
+    depth = np.full(mx + 1, -1, dtype=np.int32)
+    for t in range(mx + 1):
+        if parent[t] < 0:
+            continue
+        d, x = 0, t
+        while parent[x] != x and d < 1000:
+            x = parent[x]
+            d += 1
+        depth[t] = d
+    node0 = 1
+    return parent, depth, species_of, species_rank_of, mx, node0, L.orc_tax_eukaryota(db.h)

@@ -1,0 +1,104 @@
+"""CPU checks of the per-element DEVICE logic (MB_HD functions in metabuli_work_b200/csrc/*.cuh),
+instantiated for the host by tests/emu/emu.cpp, against the oracle.  These run without a GPU; the
+kernels themselves (tiling, scans, atomics) are covered by the -m gpu tests."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import helpers
+import orc
+
+CASES = ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single"]
+RES_DT = np.dtype([("classification", "<i4"), ("score", "<f4"), ("is_classified", "<i4"), ("query_length", "<i4"),
+                   ("hamming_dist", "<i4"), ("taxcnt_begin", "<i4"), ("taxcnt_end", "<i4"), ("n_matches", "<i4")])
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return helpers.emu_lib()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_window_extraction_logic(golden, emu, case):
+    meta = golden.cases[case]
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=meta["seq_mode"])
+    _, s1, s2 = golden.reads(case)
+    b = orc.Batch(s1, s2)
+    want = orc.sort_kmers(orc.extract(p, b))
+    out = np.zeros(len(want) + 1024, dtype=orc.KMER_DT)
+    n = emu.emu_extract(p.kmer_format, p.syncmer, p.smer_len, p.seq_mode, _ptr(b.seqs), _ptr(b.off), _ptr(b.len), b.n, _ptr(out), len(out))
+    assert n == len(want)
+    got = orc.sort_kmers(out[:n].copy())
+    assert np.array_equal(got, want)
+    db.close()
+
+
+@pytest.mark.parametrize("case", ["plain_paired", "legacy_paired", "sync_long"])
+def test_hamming_tables(golden, emu, case):
+    """hamming / rightEndHamming of every oracle match recomputed by the device functions."""
+    meta = golden.cases[case]
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=meta["seq_mode"])
+    _, s1, s2 = golden.reads(case)
+    k = orc.sort_kmers(orc.extract(p, orc.Batch(s1, s2)))
+    m = orc.match(db, p, k)
+    order = np.argsort(k["qinfo"], kind="stable")
+    idx = order[np.searchsorted(k["qinfo"][order], m["qinfo"])]
+    q = np.ascontiguousarray(k["value"][idx])
+    t = np.ascontiguousarray(m["dnaEncoding"].astype(np.uint64))
+    frame = (m["qinfo"] >> np.uint64(61)).astype(np.int64)
+    rev = np.ascontiguousarray(((frame < 3) != (p.kmer_format == 2)).astype(np.uint8))
+    s = np.zeros(len(m), dtype=np.uint8)
+    pk = np.zeros(len(m), dtype=np.uint16)
+    emu.emu_hamming(_ptr(q), _ptr(t), _ptr(rev), len(m), _ptr(s), _ptr(pk))
+    assert np.array_equal(s, m["hamming"])
+    assert np.array_equal(pk, m["rightEndHamming"])
+    db.close()
+
+
+def test_hamming_lut_quirk(emu):
+    """HAMMING_LUT7 holds 1<<14 for query codon ids 4,5 against target ids 6,7 (KmerMatcher.h:148-157)."""
+    q = np.array([4 << 21, 5 << 21, 6 << 21], dtype=np.uint64)
+    t = np.array([6 << 21, 7 << 21, 4 << 21], dtype=np.uint64)
+    rev = np.zeros(3, dtype=np.uint8)
+    s = np.zeros(3, dtype=np.uint8)
+    pk = np.zeros(3, dtype=np.uint16)
+    emu.emu_hamming(_ptr(q), _ptr(t), _ptr(rev), 3, _ptr(s), _ptr(pk))
+    assert list(s) == [4, 4, 4]
+    assert list(pk) == [1 << 14, 1 << 14, 0]
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("min_sp", [0.0, 0.9])
+def test_score_read_logic(golden, emu, case, min_sp):
+    meta = golden.cases[case]
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=meta["seq_mode"], min_sp_score=min_sp)
+    _, s1, s2 = golden.reads(case)
+    b = orc.Batch(s1, s2)
+    k, m, res, ids, cnt = orc.classify(db, p, b)
+    parent, depth, sp_of, sp_rank, mx, node0, euk = helpers.dense_taxonomy(db)
+    out = np.zeros(b.n, dtype=RES_DT)
+    tid = np.zeros(len(m) + 16, dtype=np.int32)
+    tcn = np.zeros(len(m) + 16, dtype=np.int32)
+    used = emu.emu_score(_ptr(m), len(m), _ptr(b.len), b.n, p.seq_mode, p.kmer_format, p.syncmer, p.smer_len, p.min_cons_cnt,
+                         p.min_cons_cnt_euk, p.min_score, p.min_sp_score, p.tie_ratio, _ptr(parent), _ptr(depth), _ptr(sp_of),
+                         _ptr(sp_rank), mx, node0, euk, _ptr(out), _ptr(tid), _ptr(tcn), len(tid))
+    assert used >= 0
+    bad = []
+    for i in range(b.n):
+        a, o = res[i], out[i]
+        tc_a = helpers.taxcnt_string(ids, cnt, int(a["taxcnt_begin"]), int(a["taxcnt_end"]))
+        tc_o = helpers.taxcnt_string(tid, tcn, int(o["taxcnt_begin"]), int(o["taxcnt_end"]))
+        if not (a["classification"] == o["classification"] and a["is_classified"] == o["is_classified"]
+                and np.float32(a["score"]).view(np.uint32) == np.float32(o["score"]).view(np.uint32)
+                and a["query_length"] == o["query_length"] and tc_a == tc_o):
+            bad.append(i)
+    assert bad == []
+    db.close()
