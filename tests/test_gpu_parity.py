@@ -1,0 +1,274 @@
+"""GPU parity tests (run on the B200 box with -m gpu): every stage of the CUDA path, called through the
+C ABI, against the oracle on the same inputs, and against the reference-generated golden fixtures."""
+import os
+import shutil
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import helpers
+import orc
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single"]
+
+
+@pytest.fixture(scope="module")
+def mb():
+    import metabuli_work_b200.binding as b
+    return b
+
+
+def canon_k(k):
+    return orc.sort_kmers(np.ascontiguousarray(k).view(orc.KMER_DT).copy())
+
+
+def as_orc_matches(m):
+    out = np.zeros(len(m), dtype=orc.MATCH_DT)
+    for f in ("qinfo", "targetId", "speciesId", "dnaEncoding", "rightEndHamming", "hamming"):
+        out[f] = m[f]
+    return out
+
+
+def compare_results(res_gpu, ids_gpu, cnt_gpu, res_o, ids_o, cnt_o):
+    bad = []
+    for i in range(len(res_o)):
+        a, o = res_o[i], res_gpu[i]
+        tc_a = helpers.taxcnt_string(ids_o, cnt_o, int(a["taxcnt_begin"]), int(a["taxcnt_end"]))
+        tc_o = helpers.taxcnt_string(ids_gpu, cnt_gpu, int(o["taxcnt_begin"]), int(o["taxcnt_end"]))
+        if not (a["classification"] == o["classification"] and a["is_classified"] == o["is_classified"]
+                and np.float32(a["score"]).view(np.uint32) == np.float32(o["score"]).view(np.uint32)
+                and a["query_length"] == o["query_length"] and tc_a == tc_o):
+            bad.append(i)
+    return bad
+
+
+def run_all_stages(mb, dbdir, seq_mode, s1, s2, **kw):
+    """Returns dict of GPU intermediates and the oracle's, after asserting stage-by-stage parity."""
+    db = orc.Db(dbdir)
+    p = db.params(seq_mode=seq_mode, **kw)
+    batch = orc.Batch(s1, s2)
+    ok, om, ores, oids, ocnt = orc.classify(db, p, batch, threads=4)
+    clf = mb.Classifier(dbdir, seq_mode=seq_mode, min_score=kw.get("min_score", 0.0), min_sp_score=kw.get("min_sp_score", 0.0))
+    try:
+        # K3 tap: decode of the resident stream
+        v, _ = db.decode()
+        assert np.array_equal(clf.decode_db(), v)
+        bases, offsets, lens = mb.pack_reads(s1, s2)
+        clf.stage(bases, offsets, lens)
+        n = clf.extract()
+        assert n == len(ok)
+        assert np.array_equal(canon_k(clf.kmers()), ok)                      # K1
+        clf.sort_kmers()
+        ks = clf.kmers()
+        aa = ks["value"] >> np.uint64(24)
+        assert np.all(aa[1:] >= aa[:-1])                                      # K2: grouped by amino-acid part
+        assert np.array_equal(canon_k(ks), ok)
+        nm = clf.match()
+        assert nm == len(om)
+        gm = orc.sort_matches(as_orc_matches(clf.matches()))
+        assert np.array_equal(gm, om)                                         # K3+K4
+        clf.sort_matches()
+        assert np.array_equal(as_orc_matches(clf.matches()), om)              # K5: exact compareMatches order
+        used = clf.score()
+        res, ids, cnt = clf.fetch(used)
+        assert compare_results(res, ids, cnt, ores, oids, ocnt) == []         # K6
+        # the one-call path with host buffers
+        res2, ids2, cnt2 = clf.classify(bases, offsets, lens)
+        assert compare_results(res2, ids2, cnt2, ores, oids, ocnt) == []
+        t = clf.timings()
+        assert t["kernel_launches"] > 0 and t["n_kmers"] == len(ok) and t["n_matches"] == len(om)
+        return res, ids, cnt
+    finally:
+        clf.close()
+        db.close()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_case_all_stages(golden, mb, case):
+    meta = golden.cases[case]
+    _, s1, s2 = golden.reads(case)
+    res, ids, cnt = run_all_stages(mb, golden.dbdir(case), meta["seq_mode"], s1, s2)
+    # and directly against the reference-generated fixture
+    assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
+
+
+def test_min_sp_score_branch(golden, mb):
+    _, s1, s2 = golden.reads("plain_paired")
+    run_all_stages(mb, golden.dbdir("plain_paired"), 2, s1, s2, min_sp_score=0.9)
+
+
+def test_min_score_branch(golden, mb):
+    _, s1, s2 = golden.reads("sync_paired")
+    run_all_stages(mb, golden.dbdir("sync_paired"), 2, s1, s2, min_score=0.3)
+
+
+def test_edge_reads(golden, mb):
+    """Empty batch, reads shorter than one k-mer, all-N reads, N every few bases, lower case, ragged mates."""
+    rng = np.random.default_rng(5)
+    _, g1, g2 = golden.reads("plain_paired")
+    s1 = [b"", b"ACGT", b"N" * 150, g1[0], g1[1].lower(), g1[2][:26], g1[3][:27], g1[4][:28], g1[5][:29], g1[6]]
+    s2 = [b"", g2[1], g2[2], b"ACGTAC", g2[1], g2[2][:150], g2[3][:31], g2[4][:30], b"", bytes(g2[6][:75]) + b"NNN" + bytes(g2[6][78:])]
+    x = bytearray(g1[7])
+    for i in range(0, len(x), 29):
+        x[i] = ord("N")
+    s1.append(bytes(x))
+    s2.append(g2[7])
+    run_all_stages(mb, golden.dbdir("plain_paired"), 2, s1, s2)
+    run_all_stages(mb, golden.dbdir("sync_paired"), 2, s1, s2)
+    run_all_stages(mb, golden.dbdir("legacy_paired"), 1, s1, None)
+    clf = mb.Classifier(golden.dbdir("plain_paired"), seq_mode=2)
+    bases, offsets, lens = mb.pack_reads([], [])
+    res, ids, cnt = clf.classify(bases, offsets, lens)
+    assert len(res) == 0
+    clf.close()
+
+
+def _craft_db(golden, tmp, values, taxids):
+    src = golden.dbdir("plain_paired")
+    os.makedirs(tmp, exist_ok=True)
+    for f in ("taxonomyDB", "taxID_list", "db.parameters"):
+        shutil.copy(os.path.join(src, f), tmp)
+    v = np.ascontiguousarray(values, dtype=np.uint64)
+    t = np.ascontiguousarray(taxids, dtype=np.uint32)
+    assert orc.lib().orc_write_db_files(tmp.encode(), orc._ptr(v), orc._ptr(t), len(v), 64, 2) == 0
+    return tmp
+
+
+def test_skewed_groups(golden, mb, tmp_path):
+    """Amino-acid groups longer than the 512-word overhang and longer than a whole chunk (streaming path),
+    groups straddling block boundaries, and the 'last k-mer of the DB is never a candidate' rule."""
+    rng = np.random.default_rng(11)
+    src_db = orc.Db(golden.dbdir("plain_paired"))
+    base_v, base_t = src_db.decode()
+    src_db.close()
+    taxa = np.unique(base_t)
+    _, s1, s2 = golden.reads("plain_paired")
+    p = orc.default_params(kmer_format=2, seq_mode=2)
+    qk = orc.extract(p, orc.Batch(s1[:200], s2[:200]))
+    aa_pool = np.unique(qk["value"] >> np.uint64(24))
+    vals = [base_v]
+    for aa, size in zip(rng.choice(aa_pool, 6, replace=False), (600, 1500, 4000, 9000, 300, 2600)):
+        dna = rng.choice(1 << 24, size=size, replace=False).astype(np.uint64)
+        vals.append((np.uint64(aa) << np.uint64(24)) | dna)
+    v = np.unique(np.concatenate(vals))
+    t = rng.choice(taxa, size=len(v)).astype(np.uint32)
+    # make the LAST DB k-mer share its AA with a query so that the exclusion rule matters
+    last_aa = int(aa_pool[-1])
+    tail = (np.uint64(last_aa) << np.uint64(24)) | np.arange(5, dtype=np.uint64)
+    keep = (v >> np.uint64(24)) < np.uint64(last_aa)
+    v = np.concatenate([v[keep], tail])
+    t = np.concatenate([t[keep], rng.choice(taxa, size=5).astype(np.uint32)])
+    dbdir = _craft_db(golden, str(tmp_path / "skew"), v, t)
+    run_all_stages(mb, dbdir, 2, s1[:200], s2[:200])
+
+
+def test_medium_random(mb, tmp_path):
+    """A larger seeded case built on the box: 54 genomes x 60 kb, 20k pairs + long reads (multi-tile sort,
+    hundreds of DB blocks), plain and syncmer."""
+    import synth
+    work = str(tmp_path / "med")
+    subprocess.check_call([sys.executable, os.path.join(helpers.HERE, "golden", "make_inputs.py"), work, "--seed", "77", "--families", "3",
+                           "--genera", "3", "--species", "3", "--strains", "2", "--genome-len", "60000", "--pairs", "20000",
+                           "--long-reads", "30"])
+    _, s1 = orc.read_fastx(os.path.join(work, "reads_1.fq"))
+    _, s2 = orc.read_fastx(os.path.join(work, "reads_2.fq"))
+    _, sl = orc.read_fastx(os.path.join(work, "long.fa"))
+    for sync in (0, 1):
+        dbdir = os.path.join(work, f"db{sync}")
+        synth.build_db(work, dbdir, syncmer=sync, kmer_format=2)
+        run_all_stages(mb, dbdir, 2, s1, s2)
+        run_all_stages(mb, dbdir, 3, sl, None)
+
+
+def test_cli_files_byte_identical(golden, mb, tmp_path):
+    """`metabuli classify` outputs vs the oracle's writers (Reporter.cpp:38-83,175-253) byte for byte."""
+    case = "plain_paired"
+    data = helpers.DATA
+    out = str(tmp_path)
+    subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
+                           out, "job", "--batch-reads", "150"])
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=2)
+    names, s1, s2 = golden.reads(case)
+    k, m, res, ids, cnt = orc.classify(db, p, orc.Batch(s1, s2))
+    orc.write_classifications(db, os.path.join(out, "ref_classifications.tsv"), names, res, ids, cnt)
+    orc.write_report(db, os.path.join(out, "ref_report.tsv"), res)
+    for f in ("classifications.tsv", "report.tsv"):
+        a = open(os.path.join(out, "job_" + f), "rb").read()
+        b = open(os.path.join(out, "ref_" + f), "rb").read()
+        assert a == b, f
+    # long-read mode through the library entry point
+    mb.classify_files(os.path.join(data, "long.fa"), None, golden.dbdir("sync_long"), out, "jobl", seq_mode=3)
+    db2 = orc.Db(golden.dbdir("sync_long"))
+    p2 = db2.params(seq_mode=3)
+    names, s1, _ = golden.reads("sync_long")
+    k, m, res, ids, cnt = orc.classify(db2, p2, orc.Batch(s1, None))
+    orc.write_classifications(db2, os.path.join(out, "refl_classifications.tsv"), names, res, ids, cnt)
+    assert open(os.path.join(out, "jobl_classifications.tsv"), "rb").read() == open(os.path.join(out, "refl_classifications.tsv"), "rb").read()
+
+
+def test_sharded_db_matches_union(golden, mb):
+    """DB cut at split boundaries into 3 self-contained shards: the union of the shards' matches equals
+    the whole-DB match list, including the last-k-mer rule on the last shard only."""
+    case = "plain_paired"
+    _, s1, s2 = golden.reads(case)
+    bases, offsets, lens = mb.pack_reads(s1, s2)
+    whole = mb.Classifier(golden.dbdir(case), seq_mode=2)
+    whole.stage(bases, offsets, lens)
+    whole.extract()
+    whole.sort_kmers()
+    kmers = whole.kmers()
+    whole.match()
+    want = orc.sort_matches(as_orc_matches(whole.matches()))
+    whole.close()
+    parts = []
+    total_k = 0
+    for g in range(3):
+        sh = mb.Classifier(golden.dbdir(case), seq_mode=2, shard=g, n_shards=3)
+        total_k += sh.db_kmers()
+        bounds = sh.shard_bounds()
+        assert len(bounds) == 2
+        owner = np.searchsorted(bounds, kmers["value"], side="right")
+        sh.set_kmers(kmers[owner == g])
+        sh.sort_kmers()
+        sh.match()
+        parts.append(as_orc_matches(sh.matches()))
+        sh.close()
+    got = orc.sort_matches(np.concatenate(parts))
+    assert np.array_equal(got, want)
+    db = orc.Db(golden.dbdir(case))
+    assert total_k == db.num_kmers()
+    db.close()
+
+
+def test_partition_kernels(golden, mb):
+    case = "plain_paired"
+    _, s1, s2 = golden.reads(case)
+    bases, offsets, lens = mb.pack_reads(s1, s2)
+    clf = mb.Classifier(golden.dbdir(case), seq_mode=2)
+    clf.stage(bases, offsets, lens)
+    clf.extract()
+    k0 = clf.kmers()
+    qs = np.quantile(k0["value"].astype(np.float64), [0.25, 0.5, 0.75]).astype(np.uint64)
+    counts = clf.partition_kmers(qs)
+    k1 = clf.kmers()
+    owner0 = np.searchsorted(qs, k0["value"], side="right")
+    assert np.array_equal(counts, np.bincount(owner0, minlength=4).astype(np.uint64))
+    # stable partition
+    want = np.concatenate([k0[owner0 == g] for g in range(4)])
+    assert np.array_equal(k1, want)
+    clf.sort_kmers()
+    clf.match()
+    m0 = clf.matches()
+    rpr = (len(s1) + 2) // 3
+    counts = clf.partition_matches(rpr, 3)
+    m1 = clf.matches()
+    home = ((m0["qinfo"] >> np.uint64(32)) & np.uint64(0x1FFFFFFF)).astype(np.int64) - 1
+    home //= rpr
+    assert np.array_equal(counts, np.bincount(home, minlength=3).astype(np.uint64))
+    assert np.array_equal(m1, np.concatenate([m0[home == g] for g in range(3)]))
+    clf.close()
