@@ -1,0 +1,271 @@
+"""Synthetic workload of BASELINE.json configs[1] for bench.py (bench infrastructure, not product):
+1M synthetic 2x150 paired reads vs a 10k-genome synthetic SYNCMER database.
+
+Everything is generated on the GPU box at run time from a seed (there is no network and nothing this
+large can travel): a 7-rank taxonomy, 10 000 genomes of 200-500 kb that diverge along it, the database
+(pseudo-genes -> syncmer metamers through the library's own extraction kernel -> (value, species)
+de-duplication with LCA -> 15-bit delta stream + info, the on-disk format of IndexCreator.cpp:811-886),
+and Illumina-like read pairs (1 % substitutions, 2 % random pairs).  torch is used as plumbing for the
+random numbers, sorting and gathers of this SET-UP; the timed region only runs the library.
+"""
+import ctypes as C
+import time
+
+import numpy as np
+import torch
+
+CODE2ASCII = np.frombuffer(b"ACTG", dtype=np.uint8)   # library base codes: A0 C1 T2 G3
+
+
+class Taxonomy:
+    """root(1) > domain(2) > phylum(3) > class(4) > order(5) > F families > G genera > S species > T strains.
+    Internal tax IDs are dense; dense arrays are what mb_load_taxonomy takes."""
+
+    def __init__(self, F, G, S, T):
+        self.F, self.G, self.S, self.T = F, G, S, T
+        ids = [(0, -1, ""), (1, 1, "no rank"), (2, 1, "superkingdom"), (3, 2, "phylum"), (4, 3, "class"), (5, 4, "order")]
+        names = {1: "root", 2: "Bacteria", 3: "Synthphyla", 4: "Synthclassia", 5: "Synthorderales"}
+        nxt = 6
+        self.family, self.genus, self.species, self.strain = [], [], [], []
+        for f in range(F):
+            fam = nxt; nxt += 1
+            ids.append((fam, 5, "family")); names[fam] = f"Fam{f}"
+            self.family.append(fam)
+            for g in range(G):
+                gen = nxt; nxt += 1
+                ids.append((gen, fam, "genus")); names[gen] = f"Gen{f}_{g}"
+                self.genus.append(gen)
+                for s in range(S):
+                    sp = nxt; nxt += 1
+                    ids.append((sp, gen, "species")); names[sp] = f"Gen{f}_{g} sp{s}"
+                    self.species.append(sp)
+                    for t in range(T):
+                        st = nxt; nxt += 1
+                        ids.append((st, sp, "no rank")); names[st] = f"Gen{f}_{g} sp{s} str{t}"
+                        self.strain.append(st)
+        self.nodes = ids
+        self.names = names
+        n = nxt
+        self.parent = np.full(n, -1, dtype=np.int32)
+        self.rank = [""] * n
+        for t, p, r in ids[1:]:
+            self.parent[t] = p
+            self.rank[t] = r
+        # getTaxIdAtRank(t, "species") (TaxonomyWrapper.cpp:479-498): walk up while the rank is below species
+        self.species_rank_of = np.zeros(n, dtype=np.int32)
+        order = {"no rank": -1, "species": 4, "genus": 8, "family": 12, "order": 17, "class": 21, "phylum": 24, "superkingdom": 28}
+        for t in range(2, n):
+            cur, steps = t, 0
+            while steps < 30 and order[self.rank[cur]] < 4:
+                cur = self.parent[cur]
+                steps += 1
+            self.species_rank_of[t] = t if steps == 30 else cur
+        # taxId2speciesId for the DB's taxa (strains) and their ancestors up to species (KmerMatcher.cpp:56-120)
+        self.species_of = np.zeros(n, dtype=np.int32)
+        for st in self.strain:
+            sp = self.parent[st]
+            self.species_of[st] = sp
+            self.species_of[sp] = sp
+        self.genome_tax = np.array(self.strain, dtype=np.int64)
+        self.genome_species = self.parent[self.genome_tax].astype(np.int64)
+
+
+def _mutate(seq, rate, gen):
+    """Substitute a fraction `rate` of the codes (uint8 0..3) with a different base, in place, chunked by rows."""
+    rows = max(1, (1 << 28) // max(1, seq.shape[-1]))
+    flat = seq.view(-1, seq.shape[-1])
+    thr = int(rate * 65536)
+    for r0 in range(0, flat.shape[0], rows):
+        blk = flat[r0:r0 + rows]
+        r = torch.randint(0, 65536 * 4, blk.shape, generator=gen, device=blk.device, dtype=torch.int32)
+        hit = (r >> 2) < thr
+        shift = (r & 3).clamp_(max=2).to(torch.uint8) + 1
+        blk.copy_(torch.where(hit, (blk + shift) & 3, blk))
+    return seq
+
+
+def make_genomes(tax, seed, len_min, len_max, device):
+    """-> (codes uint8[total] packed genomes on `device`, starts int64[n+1] on the host)."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    L = len_max
+    root = torch.randint(0, 4, (1, L), generator=gen, device=device, dtype=torch.uint8)
+    fam = _mutate(root.repeat(tax.F, 1), 0.25, gen)
+    genus = _mutate(fam.repeat_interleave(tax.G, dim=0), 0.10, gen)
+    del fam
+    species = _mutate(genus.repeat_interleave(tax.S, dim=0), 0.06, gen)
+    del genus
+    n = len(tax.strain)
+    lens = torch.randint(len_min, len_max + 1, (n,), generator=gen, device=device, dtype=torch.int64)
+    starts = torch.zeros(n + 1, dtype=torch.int64, device=device)
+    starts[1:] = torch.cumsum(lens, 0)
+    total = int(starts[-1].item())
+    codes = torch.empty(total, dtype=torch.uint8, device=device)
+    rows = max(1, (1 << 29) // L)
+    pos = torch.arange(L, device=device)
+    for g0 in range(0, n, rows):
+        g1 = min(n, g0 + rows)
+        sp_idx = torch.arange(g0, g1, device=device) // tax.T
+        blk = _mutate(species[sp_idx].clone(), 0.01, gen)
+        keep = pos.unsqueeze(0) < lens[g0:g1].unsqueeze(1)
+        codes[int(starts[g0].item()):int(starts[g1].item())] = blk[keep]
+    return codes, starts.cpu().numpy()
+
+
+def _encode_deltas(values_sorted_u):
+    """values as int64 holding the uint64 bit pattern, ascending in UNSIGNED order -> uint16 numpy delta stream
+    (IndexCreator::getDiffIdx, IndexCreator.cpp:868-886): 15-bit groups, most significant first, last flagged."""
+    v = values_sorted_u
+    d = torch.empty_like(v)
+    d[0] = v[0]
+    d[1:] = v[1:] - v[:-1]
+    def lsr(x, k):                                      # logical shift right on int64 bit patterns
+        return (x >> k) & ((1 << (64 - k)) - 1) if k else x
+
+    nw = torch.ones_like(d)
+    for k in (15, 30, 45, 60):
+        nw += (lsr(d, k) != 0).to(torch.int64)
+    end = torch.cumsum(nw, 0)
+    total = int(end[-1].item())
+    words = torch.zeros(total, dtype=torch.int32, device=v.device)
+    for j in range(5):
+        m = nw > j
+        idx = end[m] - 1 - j
+        w = (lsr(d[m], 15 * j) & 0x7FFF).to(torch.int32)
+        if j == 0:
+            w |= 0x8000
+        words[idx] = w
+    return words.cpu().numpy().astype(np.uint16)
+
+
+FLIP = -(1 << 63)
+
+
+def build_db(mb, tax, codes, starts, device, genomes_per_chunk=400, block=1500, log=None):
+    """-> dict(values int64 tensor (uint64 bit patterns, unsigned-ascending), info int64 tensor).  K-mers come from the
+    library's extraction kernel run over the genomes as long reads; one (strand, frame) is kept per 1.5-kb
+    block, the density of a gene-finder driven build."""
+    ex = mb.RawContext(device=device.index or 0, kmer_format=2, syncmer=1, smer_len=5, seq_mode=3)
+    n = len(starts) - 1
+    vals, taxs = [], []
+    ascii_lut = torch.from_numpy(CODE2ASCII.copy()).to(device)
+    t0 = time.time()
+    for g0 in range(0, n, genomes_per_chunk):
+        g1 = min(n, g0 + genomes_per_chunk)
+        a, b = int(starts[g0]), int(starts[g1])
+        host = ascii_lut[codes[a:b].long()].cpu().numpy()
+        lens = np.zeros(2 * (g1 - g0), dtype=np.uint32)
+        lens[0::2] = (starts[g0 + 1:g1 + 1] - starts[g0:g1]).astype(np.uint32)
+        offs = np.zeros(2 * (g1 - g0), dtype=np.uint64)
+        offs[0::2] = (starts[g0:g1] - a).astype(np.uint64)
+        offs[1::2] = (starts[g0 + 1:g1 + 1] - a).astype(np.uint64)
+        ex.stage(host, offs, lens)
+        nk = ex.extract()
+        buf = torch.empty((nk, 2), dtype=torch.int64, device=device)
+        ex.export_kmers_device(buf.data_ptr(), nk)
+        q = buf[:, 1]
+        pos = q & 0xFFFFFFFF
+        seq = (q >> 32) & 0x1FFFFFFF
+        frame = (q >> 61) & 7
+        genome = seq - 1 + g0
+        chosen = ((genome * 7919 + (pos // block) * 104729) >> 3) % 6
+        keep = frame == chosen
+        vals.append(buf[:, 0][keep].clone())
+        taxs.append(genome[keep].clone())
+        del buf
+    ex.close()
+    v = torch.cat(vals)
+    g = torch.cat(taxs)
+    del vals, taxs
+    gtax = torch.from_numpy(tax.genome_tax).to(device)[g]
+    gsp = torch.from_numpy(tax.genome_species).to(device)[g]
+    del g
+    # order (value unsigned, species, taxid): Kmer.h:77-87
+    o1 = torch.argsort(gsp * (1 << 24) + gtax, stable=True)
+    v, gtax, gsp = v[o1], gtax[o1], gsp[o1]
+    o2 = torch.argsort(v ^ FLIP, stable=True)
+    v, gtax, gsp = v[o2], gtax[o2], gsp[o2]
+    del o1, o2
+    # one entry per (value, species); tax id = LCA of the group's tax ids = the strain if unique, else the species
+    first = torch.ones(len(v), dtype=torch.bool, device=device)
+    first[1:] = (v[1:] != v[:-1]) | (gsp[1:] != gsp[:-1])
+    gid = torch.cumsum(first.to(torch.int64), 0) - 1
+    ng = int(gid[-1].item()) + 1
+    tmin = torch.full((ng,), 1 << 40, dtype=torch.int64, device=device).scatter_reduce_(0, gid, gtax, "amin")
+    tmax = torch.zeros(ng, dtype=torch.int64, device=device).scatter_reduce_(0, gid, gtax, "amax")
+    out_v = v[first]
+    out_sp = gsp[first]
+    out_t = torch.where(tmin == tmax, tmin, out_sp)
+    if log:
+        log(f"db: {len(out_v)} k-mers from {n} genomes in {time.time() - t0:.1f}s")
+    return {"values": out_v, "info": out_t}
+
+
+def shard_db(db, shard, n_shards):
+    """Cut at amino-acid group boundaries nearest to equal k-mer counts (what the `split` table encodes,
+    IndexCreator.cpp:811-866) -> (words uint16 numpy, info uint32 numpy, bounds uint64 numpy[n_shards-1], n_kmers)."""
+    v, t = db["values"], db["info"]
+    n = len(v)
+    cuts = [0]
+    aa = v >> 24
+    for g in range(1, n_shards):
+        i = g * n // n_shards
+        # first index >= i that starts a new AA group
+        win = aa[i - 1:i + (1 << 16)]
+        ch = torch.nonzero(win[1:] != win[:-1])
+        i = i + int(ch[0].item()) if len(ch) else n
+        cuts.append(i)
+    cuts.append(n)
+    bounds = np.array([int(v[c].item()) & 0xFFFFFFFFFFFFFFFF for c in cuts[1:-1]], dtype=np.uint64)
+    a, b = cuts[shard], cuts[shard + 1]
+    words = _encode_deltas(v[a:b])
+    info = t[a:b].to(torch.int32).cpu().numpy().astype(np.uint32)
+    return words, info, bounds, b - a
+
+
+def make_reads(codes, starts, n_pairs, seed, device, read_len=150, sub_rate=0.01, random_frac=0.02):
+    """-> (bases uint8 numpy [n_pairs*2*read_len] ASCII, offsets uint64[2n], lens uint32[2n], genome index int64[n])."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    n = len(starts) - 1
+    st = torch.from_numpy(starts).to(device)
+    g = torch.randint(0, n, (n_pairs,), generator=gen, device=device)
+    glen = st[g + 1] - st[g]
+    insert = torch.randint(300, 501, (n_pairs,), generator=gen, device=device)
+    off = (torch.rand(n_pairs, generator=gen, device=device, dtype=torch.float64) * (glen - insert).double()).long()
+    base = st[g] + off
+    ar = torch.arange(read_len, device=device)
+    m1 = codes[(base.unsqueeze(1) + ar.unsqueeze(0))]
+    m2 = codes[(base + insert - 1).unsqueeze(1) - ar.unsqueeze(0)] ^ 2          # reverse complement of the far end
+    flip = torch.rand(n_pairs, generator=gen, device=device) < 0.5
+    r1 = torch.where(flip.unsqueeze(1), m2, m1)
+    r2 = torch.where(flip.unsqueeze(1), m1, m2)
+    pair = torch.cat([r1, r2], dim=1)
+    _mutate(pair, sub_rate, gen)
+    rnd = torch.rand(n_pairs, generator=gen, device=device) < random_frac
+    noise = torch.randint(0, 4, pair.shape, generator=gen, device=device, dtype=torch.uint8)
+    pair = torch.where(rnd.unsqueeze(1), noise, pair)
+    ascii_lut = torch.from_numpy(CODE2ASCII.copy()).to(device)
+    bases = ascii_lut[pair.long()].reshape(-1).cpu().numpy()
+    offsets = (np.arange(2 * n_pairs, dtype=np.uint64) * np.uint64(read_len))
+    lens = np.full(2 * n_pairs, read_len, dtype=np.uint32)
+    return bases, offsets, lens, g.cpu().numpy()
+
+
+def write_fastq_pair(path1, path2, bases, read_len, n_pairs):
+    b = bases[:n_pairs * 2 * read_len].reshape(n_pairs, 2, read_len)
+    qual = b"I" * read_len
+    with open(path1, "wb") as f1, open(path2, "wb") as f2:
+        for i in range(n_pairs):
+            f1.write(b"@r%d/1\n" % i + b[i, 0].tobytes() + b"\n+\n" + qual + b"\n")
+            f2.write(b"@r%d/2\n" % i + b[i, 1].tobytes() + b"\n+\n" + qual + b"\n")
+
+
+def write_taxdump(tax, outdir):
+    import os
+    os.makedirs(outdir, exist_ok=True)
+    with open(f"{outdir}/nodes.dmp", "w") as fn, open(f"{outdir}/names.dmp", "w") as fm:
+        for t, p, r in tax.nodes[1:]:
+            fn.write(f"{t}\t|\t{p}\t|\t{r}\t|\t\t|\t0\t|\n")
+            fm.write(f"{t}\t|\t{tax.names[t]}\t|\t\t|\tscientific name\t|\n")
+    open(f"{outdir}/merged.dmp", "w").close()

@@ -164,6 +164,12 @@ int mb_kmers_device(mb_ctx *ctx, void **dptr, size_t *n);
 int mb_matches_device(mb_ctx *ctx, void **dptr, size_t *n);
 int mb_set_kmers_device(mb_ctx *ctx, const void *dptr, size_t n);            /* device -> device */
 int mb_set_matches_device(mb_ctx *ctx, const void *dptr, size_t n);
+/* device -> caller-owned device buffer (e.g. a torch tensor that feeds an NCCL all-to-all) */
+int mb_export_kmers_device(mb_ctx *ctx, void *dst_dptr, size_t cap, size_t *n);
+int mb_export_matches_device(mb_ctx *ctx, void *dst_dptr, size_t cap, size_t *n);
+/* multi-GPU: sequenceIDs written by extraction become base + 1-based local read index, so k-mers and
+ * matches of different home ranks can share one owner GPU; scoring maps them back to local reads. */
+int mb_set_read_id_base(mb_ctx *ctx, uint32_t base);
 /* multi-GPU bucketing: stable partition of the resident k-mers by the owner shard of their amino-acid
  * part (owner = number of bounds[] <= value; bounds are the first values of shards 1..n_shards-1) and
  * of the resident matches by home rank ((sequenceID-1) / reads_per_rank).  counts[n] receives sizes. */

@@ -52,7 +52,8 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_extract_kmers", "mb_sort_kmers", "mb_match_kmers", "mb_sort_matches", "mb_score_reads",
                "mb_fetch_results", "mb_classify_staged", "mb_copy_kmers", "mb_copy_matches", "mb_set_kmers",
                "mb_set_matches", "mb_kmers_device", "mb_matches_device", "mb_set_kmers_device", "mb_set_matches_device",
-               "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream"]
+               "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream",
+               "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -93,6 +94,9 @@ _sig(_cuda, "mb_kmers_device", C.c_int, [vp, C.POINTER(vp), szp])
 _sig(_cuda, "mb_matches_device", C.c_int, [vp, C.POINTER(vp), szp])
 _sig(_cuda, "mb_set_kmers_device", C.c_int, [vp, vp, sz])
 _sig(_cuda, "mb_set_matches_device", C.c_int, [vp, vp, sz])
+_sig(_cuda, "mb_export_kmers_device", C.c_int, [vp, vp, sz, szp])
+_sig(_cuda, "mb_export_matches_device", C.c_int, [vp, vp, sz, szp])
+_sig(_cuda, "mb_set_read_id_base", C.c_int, [vp, u32])
 _sig(_cuda, "mb_partition_kmers", C.c_int, [vp, vp, C.c_int, vp])
 _sig(_cuda, "mb_partition_matches", C.c_int, [vp, u32, C.c_int, vp])
 _sig(_cuda, "mb_get_timings", C.c_int, [vp, C.POINTER(PhaseTimes)])
@@ -147,52 +151,22 @@ def pack_reads(mates1, mates2=None):
     return bases, offsets, lens
 
 
-class Classifier:
-    """One GPU context with a resident database: the Python mirror of the per-batch calls that
-    Classifier::startClassify makes (src/commons/Classifier.cpp:105-119)."""
+class Context:
+    """Methods shared by every owner of an mb_ctx: the per-batch calls that Classifier::startClassify makes
+    (src/commons/Classifier.cpp:105-119), one Python method per C-ABI entry point."""
 
-    def __init__(self, dbdir, device=0, seq_mode=2, min_score=0.0, min_sp_score=0.0, shard=0, n_shards=1):
-        self.h = _host.mbh_open(os.fsencode(dbdir), device, seq_mode, min_score, min_sp_score, shard, n_shards)
-        if not self.h:
-            raise MetabuliError(-1, _host.mbh_last_error().decode())
-        self.ctx = _host.mbh_ctx(self.h)
-        self.n_reads = 0
-
-    def close(self):
-        if self.h:
-            _host.mbh_close(self.h)
-            self.h = None
+    ctx = None
+    n_reads = 0
 
     def _ck(self, rc):
         if rc != MB_OK:
             raise MetabuliError(rc, _cuda.mb_last_error(self.ctx).decode())
-
-    @property
-    def params(self):
-        p = Params()
-        _host.mbh_params(self.h, C.byref(p))
-        return p
 
     def set_params(self, **kw):
         p = self.params
         for k, v in kw.items():
             setattr(p, k, v)
         self._ck(_cuda.mb_set_params(self.ctx, C.byref(p)))
-
-    def shard_bounds(self):
-        n = _host.mbh_num_bounds(self.h)
-        out = np.zeros(max(n, 1), dtype=np.uint64)
-        _host.mbh_bounds(self.h, _ptr(out))
-        return out[:n]
-
-    def db_kmers(self):
-        return _host.mbh_db_kmers(self.h)
-
-    def db_words(self):
-        return _host.mbh_db_words(self.h)
-
-    def original_taxid(self, t):
-        return _host.mbh_original_taxid(self.h, int(t))
 
     def decode_db(self):
         n = self.db_kmers()
@@ -283,6 +257,19 @@ class Classifier:
     def set_matches_device(self, dptr, n):
         self._ck(_cuda.mb_set_matches_device(self.ctx, C.c_void_p(dptr), n))
 
+    def export_kmers_device(self, dptr, cap):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_export_kmers_device(self.ctx, C.c_void_p(dptr), cap, C.byref(n)))
+        return n.value
+
+    def export_matches_device(self, dptr, cap):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_export_matches_device(self.ctx, C.c_void_p(dptr), cap, C.byref(n)))
+        return n.value
+
+    def set_read_id_base(self, base):
+        self._ck(_cuda.mb_set_read_id_base(self.ctx, base))
+
     def partition_kmers(self, bounds):
         bounds = np.ascontiguousarray(bounds, dtype=np.uint64)
         counts = np.zeros(len(bounds) + 1, dtype=np.uint64)
@@ -319,6 +306,89 @@ class Classifier:
                 continue
             self._ck(rc)
             return res, ids[:used.value], cnt[:used.value]
+
+
+class Classifier(Context):
+    """A database directory opened through the C++ host library (host/mb_host.h): parses taxonomyDB,
+    taxID_list, db.parameters, cuts the shard and makes everything resident on the GPU."""
+
+    def __init__(self, dbdir, device=0, seq_mode=2, min_score=0.0, min_sp_score=0.0, shard=0, n_shards=1):
+        self.h = _host.mbh_open(os.fsencode(dbdir), device, seq_mode, min_score, min_sp_score, shard, n_shards)
+        if not self.h:
+            raise MetabuliError(-1, _host.mbh_last_error().decode())
+        self.ctx = _host.mbh_ctx(self.h)
+        self.n_reads = 0
+
+    def close(self):
+        if self.h:
+            _host.mbh_close(self.h)
+            self.h = None
+
+    @property
+    def params(self):
+        p = Params()
+        _host.mbh_params(self.h, C.byref(p))
+        return p
+
+    def shard_bounds(self):
+        n = _host.mbh_num_bounds(self.h)
+        out = np.zeros(max(n, 1), dtype=np.uint64)
+        _host.mbh_bounds(self.h, _ptr(out))
+        return out[:n]
+
+    def db_kmers(self):
+        return _host.mbh_db_kmers(self.h)
+
+    def db_words(self):
+        return _host.mbh_db_words(self.h)
+
+    def original_taxid(self, t):
+        return _host.mbh_original_taxid(self.h, int(t))
+
+
+class RawContext(Context):
+    """An mb_ctx created straight from arrays (mb_create / mb_load_taxonomy / mb_load_db): what a host that
+    already holds the database in memory would do.  bench.py uses it for the synthetic workload."""
+
+    def __init__(self, **kw):
+        p = Params()
+        _cuda.mb_default_params(C.byref(p))
+        for k, v in kw.items():
+            setattr(p, k, v)
+        self._params = p
+        self.ctx = _cuda.mb_create(C.byref(p))
+        if not self.ctx:
+            raise MetabuliError(-1, _cuda.mb_global_error().decode())
+        self._n_db = 0
+        self._n_words = 0
+
+    def close(self):
+        if self.ctx:
+            _cuda.mb_destroy(self.ctx)
+            self.ctx = None
+
+    @property
+    def params(self):
+        return self._params
+
+    def load_taxonomy(self, parent, species_of, species_rank_of, node0_taxid=1, eukaryota_taxid=0):
+        parent = np.ascontiguousarray(parent, dtype=np.int32)
+        species_of = np.ascontiguousarray(species_of, dtype=np.int32)
+        species_rank_of = np.ascontiguousarray(species_rank_of, dtype=np.int32)
+        self._ck(_cuda.mb_load_taxonomy(self.ctx, _ptr(parent), _ptr(species_of), _ptr(species_rank_of), len(parent) - 1,
+                                        node0_taxid, eukaryota_taxid))
+
+    def load_db(self, words, info):
+        words = np.ascontiguousarray(words, dtype=np.uint16)
+        info = np.ascontiguousarray(info, dtype=np.uint32)
+        self._ck(_cuda.mb_load_db(self.ctx, _ptr(words), len(words), _ptr(info), len(info)))
+        self._n_db, self._n_words = len(info), len(words)
+
+    def db_kmers(self):
+        return self._n_db
+
+    def db_words(self):
+        return self._n_words
 
 
 def classify_files(reads1, reads2, dbdir, outdir, jobid, seq_mode=2, device=0, min_score=0.0, min_sp_score=0.0, batch_reads=0):

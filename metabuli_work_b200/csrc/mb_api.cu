@@ -72,6 +72,7 @@ struct mb_ctx {
     DevBuf bases, offsets, lens;
     u64 n_bases = 0;
     u32 n_reads = 0;
+    u32 seq_base = 0;
     u64 kmer_bound = 0;
     u32 max_query_len = 0;
     DevBuf tile_mate, tile_counts, tile_offsets;
@@ -382,7 +383,7 @@ int mb_load_taxonomy(mb_ctx *ctx, const int32_t *parent, const int32_t *species_
 int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
                    uint32_t n_reads) {
     if (!ctx || (!bases && n_bases) || ((!offsets || !lens) && n_reads)) return MB_E_ARG;
-    if (n_reads >= (1u << 29)) return fail(ctx, MB_E_ARG, "at most 2^29-1 reads per batch (29-bit sequenceID, Kmer.h:11-16)");
+    if ((uint64_t) n_reads + ctx->seq_base >= (1u << 29)) return fail(ctx, MB_E_ARG, "at most 2^29-1 reads per batch (29-bit sequenceID, Kmer.h:11-16)");
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_reads = ctx->have_kmers = ctx->have_matches = ctx->have_results = false;
     // host pass over the lengths: layout check, k-mer slot bound (QueryIndexer.cpp:62-67), longest query
@@ -432,7 +433,7 @@ int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
         ExtractArgs a;
         a.bases = ctx->bases.as<u8>(); a.n_bases = ctx->n_bases; a.offsets = ctx->offsets.as<u64>(); a.lens = ctx->lens.as<u32>();
         a.n_mates = ctx->n_reads * 2; a.seq_mode = ctx->par.seq_mode; a.format = ctx->par.kmer_format;
-        a.syncmer = ctx->par.syncmer; a.smer_len = ctx->par.smer_len;
+        a.syncmer = ctx->par.syncmer; a.smer_len = ctx->par.smer_len; a.seq_base = ctx->seq_base;
         CK(ctx->tile_mate.ensure(((size_t) n_tiles + 1) * sizeof(u32)));
         CK(ctx->tile_counts.ensure((size_t) n_tiles * sizeof(u32)));
         CK(ctx->tile_offsets.ensure(((size_t) n_tiles + 1) * sizeof(u64)));
@@ -519,6 +520,7 @@ static MatchKey match_key(const mb_ctx *ctx) {
     k.pos_bits = bits_for((u64) ctx->max_query_len + 8);
     k.sp_bits = bits_for((u64) std::max(ctx->max_taxid, 1));
     k.seq_bits = bits_for((u64) ctx->n_reads + 1);
+    k.seq_base = ctx->seq_base;
     return k;
 }
 
@@ -554,7 +556,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         u32 max_seg = 0;
         if (ctx->n_matches) {
             k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
-                ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), &ctx->dcnt()->max_seg);
+                ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seq_base, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>());
             LAUNCH_CHECK();
             k_segment_max<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), nr, &ctx->dcnt()->max_seg);
             LAUNCH_CHECK();
@@ -691,6 +693,33 @@ int mb_set_kmers(mb_ctx *ctx, const mb_kmer *k, size_t n) { return (!ctx || (!k 
 int mb_set_matches(mb_ctx *ctx, const mb_match *m, size_t n) { return (!ctx || (!m && n)) ? MB_E_ARG : set_matches(ctx, m, n, cudaMemcpyHostToDevice); }
 int mb_set_kmers_device(mb_ctx *ctx, const void *d, size_t n) { return (!ctx || (!d && n)) ? MB_E_ARG : set_kmers(ctx, d, n, cudaMemcpyDeviceToDevice); }
 int mb_set_matches_device(mb_ctx *ctx, const void *d, size_t n) { return (!ctx || (!d && n)) ? MB_E_ARG : set_matches(ctx, d, n, cudaMemcpyDeviceToDevice); }
+
+int mb_export_kmers_device(mb_ctx *ctx, void *dst, size_t cap, size_t *n) {
+    if (!ctx || !n) return MB_E_ARG;
+    if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    *n = ctx->n_kmers;
+    if (cap < ctx->n_kmers) return fail(ctx, MB_E_CAPACITY, "k-mer output too small");
+    CK(cudaSetDevice(ctx->par.device));
+    if (ctx->n_kmers) CK(cudaMemcpyAsync(dst, ctx->kmers_a.p, ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+int mb_export_matches_device(mb_ctx *ctx, void *dst, size_t cap, size_t *n) {
+    if (!ctx || !n) return MB_E_ARG;
+    if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    *n = ctx->n_matches;
+    if (cap < ctx->n_matches) return fail(ctx, MB_E_CAPACITY, "match output too small");
+    CK(cudaSetDevice(ctx->par.device));
+    if (ctx->n_matches) CK(cudaMemcpyAsync(dst, ctx->matches_a.p, ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+int mb_set_read_id_base(mb_ctx *ctx, uint32_t base) {
+    if (!ctx) return MB_E_ARG;
+    if ((uint64_t) base + ctx->n_reads >= (1u << 29)) return fail(ctx, MB_E_ARG, "read id base + batch size exceeds the 29-bit sequenceID");
+    ctx->seq_base = base;
+    return MB_OK;
+}
 
 int mb_kmers_device(mb_ctx *ctx, void **dptr, size_t *n) {
     if (!ctx || !dptr || !n) return MB_E_ARG;

@@ -30,6 +30,7 @@ struct ExtractArgs {
     const u32 *lens;       // [2*n_reads]
     u32 n_mates;           // 2*n_reads
     int seq_mode, format, syncmer, smer_len;
+    u32 seq_base;          // added to the 1-based read index (multi-GPU: ids unique across home ranks)
 };
 
 // largest mate index m with offsets[m] <= g, searching [lo, hi] (offsets are non-decreasing)
@@ -142,7 +143,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
             if ((int) (x + 24) > (int) (x % 3) + used) continue;
             if ((ambw >> i) & 0xFFFFFFu) continue;          // an ambiguous base: no window may cover it
             const u64 win = (w >> (2 * i)) & 0xFFFFFFFFFFFFull;
-            const u32 seqId = (m >> 1) + 1;
+            const u32 seqId = a.seq_base + (m >> 1) + 1;
             // forward strand: frame = begin = x % 3 (KmerExtractor.cpp:369-373)
             {
                 const u64 v = metamer_from_window(s_codonF, s_codonR, win, false, a.format);

@@ -44,8 +44,9 @@ struct KmerOwnerKey {       // multi-GPU bucketing: owner shard = number of boun
 // integer with per-batch field widths so that only the significant bytes are sorted.
 struct MatchKey {
     int pos_bits, sp_bits, seq_bits;
+    u32 seq_base;          // ids of this batch are seq_base+1 .. seq_base+n_reads
     __device__ __forceinline__ unsigned __int128 key(const mb_match &m) const {
-        unsigned __int128 k = qi_seq(m.qinfo);
+        unsigned __int128 k = (u32) (qi_seq(m.qinfo) - seq_base);
         k = (k << sp_bits) | (u32) m.speciesId;
         k = (k << 3) | qi_frame(m.qinfo);
         k = (k << pos_bits) | qi_pos(m.qinfo);

@@ -457,18 +457,17 @@ MB_HD int score_read(const mb_match *m, int b, int e, int query_length, const Sc
 
 #if defined(__CUDACC__)
 // ---- segmentation of the sorted match list by read (Classifier.cpp:174-185) ----------------------------
-__global__ void k_segment_matches(const mb_match *__restrict__ m, u64 n, u32 n_reads, u64 *__restrict__ seg_begin,
-                                  u64 *__restrict__ seg_end, u32 *__restrict__ max_len) {
+__global__ void k_segment_matches(const mb_match *__restrict__ m, u64 n, u32 n_reads, u32 seq_base, u64 *__restrict__ seg_begin,
+                                  u64 *__restrict__ seg_end) {
     const u64 i = (u64) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const u32 s = qi_seq(m[i].qinfo);
-    if (s == 0 || s > n_reads) return;
-    const bool first = i == 0 || qi_seq(m[i - 1].qinfo) != s;
-    const bool last = i + 1 == n || qi_seq(m[i + 1].qinfo) != s;
+    const u32 sg = qi_seq(m[i].qinfo);
+    if (sg <= seq_base || sg - seq_base > n_reads) return;       // not a read of this batch
+    const u32 s = sg - seq_base;
+    const bool first = i == 0 || qi_seq(m[i - 1].qinfo) != sg;
+    const bool last = i + 1 == n || qi_seq(m[i + 1].qinfo) != sg;
     if (first) seg_begin[s - 1] = i;
-    if (last) {
-        seg_end[s - 1] = i + 1;
-    }
+    if (last) seg_end[s - 1] = i + 1;
 }
 __global__ void k_segment_max(const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end, u32 n_reads, u32 *__restrict__ max_len) {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
