@@ -68,6 +68,18 @@ class Taxonomy:
             self.species_of[sp] = sp
         self.genome_tax = np.array(self.strain, dtype=np.int64)
         self.genome_species = self.parent[self.genome_tax].astype(np.int64)
+        self.n = n
+
+    def use_internal_ids(self, ext2int):
+        """The DB stores the INTERNAL tax IDs the reference's TaxonomyWrapper assigned (tax_map.tsv written by
+        oracle/_ref/ref_mkdb); order and `info` must use them."""
+        m = np.zeros(self.n, dtype=np.int64)
+        for e, i in ext2int.items():
+            if e < self.n:
+                m[e] = i
+        self.genome_tax = m[self.genome_tax]
+        self.genome_species = m[self.genome_species]
+        self.int_of = m
 
 
 def _mutate(seq, rate, gen):
@@ -135,7 +147,7 @@ def _encode_deltas(values_sorted_u):
         if j == 0:
             w |= 0x8000
         words[idx] = w
-    return words.cpu().numpy().astype(np.uint16)
+    return words.to(torch.int16).cpu().numpy().view(np.uint16), end
 
 
 FLIP = -(1 << 63)
@@ -218,7 +230,7 @@ def shard_db(db, shard, n_shards):
     cuts.append(n)
     bounds = np.array([int(v[c].item()) & 0xFFFFFFFFFFFFFFFF for c in cuts[1:-1]], dtype=np.uint64)
     a, b = cuts[shard], cuts[shard + 1]
-    words = _encode_deltas(v[a:b])
+    words, _ = _encode_deltas(v[a:b])
     info = t[a:b].to(torch.int32).cpu().numpy().astype(np.uint32)
     return words, info, bounds, b - a
 
@@ -269,3 +281,53 @@ def write_taxdump(tax, outdir):
             fn.write(f"{t}\t|\t{p}\t|\t{r}\t|\t\t|\t0\t|\n")
             fm.write(f"{t}\t|\t{tax.names[t]}\t|\t\t|\tscientific name\t|\n")
     open(f"{outdir}/merged.dmp", "w").close()
+
+
+def write_db_dir(dbdir, db, tax, split_num=4096, syncmer=1, smer_len=5):
+    """Writes diffIdx / info / split / taxID_list / db.parameters of a Metabuli database directory (taxonomyDB comes
+    from ref_mkdb).  Format: IndexCreator::writeTargetFilesAndSplits + getDiffIdx (IndexCreator.cpp:811-886) and
+    writeDbParameters (:1245-1266)."""
+    import os
+    v, t = db["values"], db["info"]
+    n = len(v)
+    words, end = _encode_deltas(v)
+    words.tofile(os.path.join(dbdir, "diffIdx"))
+    t.to(torch.int32).cpu().numpy().astype(np.uint32).tofile(os.path.join(dbdir, "info"))
+    # split table: after the k-th equal-count boundary, the first k-mer whose amino-acid part differs
+    aa = v >> 24
+    change = torch.nonzero(aa[1:] != aa[:-1]).flatten() + 1          # indices that start a new AA group
+    size = n // (split_num - 1)
+    splits = np.zeros((split_num, 3), dtype=np.uint64)
+    si = 1
+    bidx = (torch.arange(1, split_num, device=v.device, dtype=torch.int64) * size - 1).clamp_(max=n - 1)
+    nxt = torch.searchsorted(change, bidx, right=True)                # first group start > boundary index
+    has = nxt < len(change)
+    j = torch.where(has, change[nxt.clamp(max=max(len(change) - 1, 0))] if len(change) else bidx, torch.full_like(bidx, -1))
+    bidx_h, j_h = bidx.cpu().numpy(), j.cpu().numpy()
+    jv = v[j.clamp(min=0)].cpu().numpy().astype(np.uint64)
+    je = end[j.clamp(min=0)].cpu().numpy().astype(np.uint64)
+    for k in range(split_num - 1):
+        if size == 0:
+            break
+        jk = int(j_h[k])
+        if jk < 0:
+            break
+        # a later boundary reached before this one resolved overwrites it (single `pending` state)
+        if k + 1 < split_num - 1 and jk > int(bidx_h[k + 1]):
+            continue
+        if si < split_num:
+            splits[si] = (jv[k], je[k], jk + 1)
+            si += 1
+    splits.tofile(os.path.join(dbdir, "split"))
+    with open(os.path.join(dbdir, "taxID_list"), "w") as f:
+        for x in sorted(set(int(x) for x in tax.genome_tax)):
+            f.write(f"{x}\n")
+    with open(os.path.join(dbdir, "db.parameters"), "w") as f:
+        f.write("DB_name\tsynthetic\nCreation_date\t2026-01-01\n")
+        f.write("Metabuli commit used to create the DB\tsynthetic\n")
+        f.write("Reduced_alphabet\t0\nAccession_level\t0\nMask_mode\t0\nMask_prob\t0.900000\nSkip_redundancy\t1\n")
+        f.write(f"Syncmer\t{syncmer}\n")
+        if syncmer:
+            f.write(f"Syncmer_len\t{smer_len}\n")
+        f.write("Kmer_format\t2\n")
+    return len(words)

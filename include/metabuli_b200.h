@@ -177,6 +177,15 @@ int mb_partition_kmers(mb_ctx *ctx, const uint64_t *bounds, int n_shards, uint64
 int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint64_t *counts);
 
 int mb_get_timings(mb_ctx *ctx, mb_phase_times *t);
+/* Per-kernel timing of the last batch: with profiling on, every kernel launch of the hot path is
+ * bracketed by a CUDA event pair on the launching stream; the table sums them per kernel. */
+typedef struct {
+    char     name[32];
+    float    ms;              /* summed over the launches of the last batch */
+    uint32_t launches;
+} mb_kernel_time;
+int mb_set_profile(mb_ctx *ctx, int on);
+int mb_get_kernel_times(mb_ctx *ctx, mb_kernel_time *out, size_t cap, size_t *n);   /* *n = table size */
 /* CUDA stream the library launches on (cudaStream_t as void*), for event timing by the caller */
 void *mb_stream(mb_ctx *ctx);
 

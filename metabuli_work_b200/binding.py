@@ -46,6 +46,10 @@ class PhaseTimes(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class KernelTime(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("ms", C.c_float), ("launches", C.c_uint32)]
+
+
 # every symbol include/metabuli_b200.h declares
 ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", "mb_global_error", "mb_set_params",
                "mb_load_db", "mb_decode_db", "mb_load_taxonomy", "mb_classify_batch", "mb_stage_reads",
@@ -53,7 +57,8 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_fetch_results", "mb_classify_staged", "mb_copy_kmers", "mb_copy_matches", "mb_set_kmers",
                "mb_set_matches", "mb_kmers_device", "mb_matches_device", "mb_set_kmers_device", "mb_set_matches_device",
                "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream",
-               "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base"]
+               "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
+               "mb_get_kernel_times"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -101,6 +106,8 @@ _sig(_cuda, "mb_partition_kmers", C.c_int, [vp, vp, C.c_int, vp])
 _sig(_cuda, "mb_partition_matches", C.c_int, [vp, u32, C.c_int, vp])
 _sig(_cuda, "mb_get_timings", C.c_int, [vp, C.POINTER(PhaseTimes)])
 _sig(_cuda, "mb_stream", vp, [vp])
+_sig(_cuda, "mb_set_profile", C.c_int, [vp, C.c_int])
+_sig(_cuda, "mb_get_kernel_times", C.c_int, [vp, C.POINTER(KernelTime), sz, szp])
 
 _sig(_host, "mbh_last_error", C.c_char_p, [])
 _sig(_host, "mbh_open", vp, [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int])
@@ -215,6 +222,10 @@ class Context:
         self._ck(_cuda.mb_fetch_results(self.ctx, _ptr(res), _ptr(ids), _ptr(cnt), used + 1))
         return res, ids[:used], cnt[:used]
 
+    def fetch_into(self, res, ids, cnt):
+        """mb_fetch_results into caller-owned (e.g. pinned) arrays."""
+        self._ck(_cuda.mb_fetch_results(self.ctx, _ptr(res), _ptr(ids), _ptr(cnt), len(ids)))
+
     def kmers(self):
         n = C.c_size_t(0)
         rc = _cuda.mb_copy_kmers(self.ctx, None, 0, C.byref(n))
@@ -289,6 +300,16 @@ class Context:
     def stream(self):
         return _cuda.mb_stream(self.ctx)
 
+    def set_profile(self, on):
+        self._ck(_cuda.mb_set_profile(self.ctx, int(on)))
+
+    def kernel_times(self):
+        """-> {kernel name: (ms summed over the launches of the last batch, launches)}"""
+        arr = (KernelTime * 64)()
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_get_kernel_times(self.ctx, arr, 64, C.byref(n)))
+        return {arr[i].name.decode(): (arr[i].ms, arr[i].launches) for i in range(n.value) if arr[i].launches}
+
     # ---- whole path, host buffers in / host buffers out (mb_classify_batch) ----
     def classify(self, bases, offsets, lens, bases_ptr=None):
         self.n_reads = len(lens) // 2
@@ -306,6 +327,17 @@ class Context:
                 continue
             self._ck(rc)
             return res, ids[:used.value], cnt[:used.value]
+
+
+    def classify_into(self, bases_ptr, n_bases, offsets, lens, res, ids, cnt):
+        """mb_classify_batch with caller-owned (e.g. pinned) buffers; returns the number of taxCnt entries.
+        Raises MetabuliError(MB_E_CAPACITY) when ids/cnt are too small."""
+        self.n_reads = len(lens) // 2
+        used = C.c_size_t(0)
+        rc = _cuda.mb_classify_batch(self.ctx, bases_ptr, n_bases, _ptr(offsets), _ptr(lens), self.n_reads, _ptr(res),
+                                     _ptr(ids), _ptr(cnt), len(ids), C.byref(used))
+        self._ck(rc)
+        return used.value
 
 
 class Classifier(Context):

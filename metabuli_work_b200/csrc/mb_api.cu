@@ -54,6 +54,16 @@ struct Counters {                 // device-side scalars, one allocation
     u32 trivial[RS_MAX_PASSES];
 };
 
+// kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
+enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
+       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SCORE,
+       KID_COUNT };
+const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract<write>",
+                                          "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
+                                          "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
+                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_score"};
+struct KSample { int kid; cudaEvent_t a, b; };
+
 } // namespace
 
 struct mb_ctx {
@@ -89,6 +99,9 @@ struct mb_ctx {
     bool ev_set[EV_COUNT];
     mb_phase_times times;
     u32 launches = 0;
+    bool profile = false;             // mb_set_profile: bracket every kernel launch with an event pair
+    std::vector<KSample> samples;     // event pairs of the current batch
+    size_t n_samples = 0;
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
 
     Counters *dcnt() const { return counters.as<Counters>(); }
@@ -105,8 +118,32 @@ struct mb_ctx {
         }                                                                                            \
     } while (0)
 
-#define LAUNCH_CHECK()                                                                               \
-    do { ++ctx->launches; CK(cudaGetLastError()); } while (0)
+// one kernel launch: bracketed by profiling events, counted, checked
+#define KL(kid, ...)                                                                                 \
+    do {                                                                                             \
+        { KTimer kt_(ctx, kid); __VA_ARGS__; }                                                       \
+        ++ctx->launches;                                                                             \
+        CK(cudaGetLastError());                                                                      \
+    } while (0)
+
+// Brackets one kernel launch with events on the launching stream when profiling is on.
+struct KTimer {
+    mb_ctx *c;
+    KSample *s = nullptr;
+    KTimer(mb_ctx *ctx, int kid) : c(ctx) {
+        if (!c->profile || kid < 0) return;
+        if (c->n_samples == c->samples.size()) {
+            KSample n;
+            n.kid = kid;
+            if (cudaEventCreate(&n.a) != cudaSuccess || cudaEventCreate(&n.b) != cudaSuccess) return;
+            c->samples.push_back(n);
+        }
+        s = &c->samples[c->n_samples++];
+        s->kid = kid;
+        cudaEventRecord(s->a, c->stream);
+    }
+    ~KTimer() { if (s) cudaEventRecord(s->b, c->stream); }
+};
 
 static int fail(mb_ctx *ctx, int code, const char *msg) { ctx->err = msg; return code; }
 
@@ -127,7 +164,7 @@ static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
 
 // ---- radix sort driver --------------------------------------------------------------------------------
 template <typename Rec, typename Key, int ITEMS>
-static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes) {
+static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes, int kid_base) {
     if (n == 0 || n_passes == 0) return MB_OK;
     if (n_passes > RS_MAX_PASSES) return fail(ctx, MB_E_ARG, "too many radix passes");
     constexpr u64 TILE = (u64) RS_THREADS * ITEMS;
@@ -138,11 +175,9 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     CK(cudaMemsetAsync(ctx->hist.p, 0, sizeof(u64) * RS_BINS * n_passes, ctx->stream));
     CK(cudaMemsetAsync(&ctx->dcnt()->trivial, 0, sizeof(u32) * RS_MAX_PASSES, ctx->stream));
     const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
-    k_radix_hist<Rec, Key><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
-        a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>());
-    LAUNCH_CHECK();
-    k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial);
-    LAUNCH_CHECK();
+    KL(kid_base + 0, k_radix_hist<Rec, Key><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
+        a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>()));
+    KL(kid_base + 1, k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial));
     constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
     static bool attr_set = false;
     if (!attr_set) {
@@ -152,10 +187,9 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     for (int p = 0; p < n_passes; ++p) {
         CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * RS_BINS * sizeof(u64), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->radix_ticket, 0, sizeof(u32), ctx->stream));
-        k_radix_pass<Rec, Key, ITEMS><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
+        KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
             a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
-            &ctx->dcnt()->radix_ticket);
-        LAUNCH_CHECK();
+            &ctx->dcnt()->radix_ticket));
         std::swap(a.p, b.p);
         std::swap(a.cap, b.cap);
     }
@@ -167,7 +201,7 @@ template <typename Rec, typename Key, int ITEMS>
 static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_parts, uint64_t *counts) {
     for (int i = 0; i < n_parts; ++i) counts[i] = 0;
     if (n == 0) return MB_OK;
-    if (int rc = radix_sort<Rec, Key, ITEMS>(ctx, a, b, n, key, 1)) return rc;
+    if (int rc = radix_sort<Rec, Key, ITEMS>(ctx, a, b, n, key, 1, -100)) return rc;
     // digit_base (exclusive scan of the histogram) is still in ctx->hist
     std::vector<u64> base(RS_BINS);
     CK(cudaMemcpyAsync(base.data(), ctx->hist.p, RS_BINS * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
@@ -235,6 +269,7 @@ void mb_destroy(mb_ctx *ctx) {
     cudaSetDevice(ctx->par.device);
     cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < EV_COUNT; ++i) cudaEventDestroy(ctx->ev[i]);
+    for (auto &k : ctx->samples) { cudaEventDestroy(k.a); cudaEventDestroy(k.b); }
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -290,8 +325,7 @@ int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint3
     DevBuf blk_sum;
     CK(blk_sum.ensure(nb * sizeof(u64)));
     const DbView v = db_view(ctx, true);
-    k_db_block_summary<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_cnt.as<u32>(), blk_sum.as<u64>());
-    LAUNCH_CHECK();
+    KL(-1, k_db_block_summary<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_cnt.as<u32>(), blk_sum.as<u64>()));
     // The scan over blocks is a load-time step on a few MB: done on the host.
     std::vector<u32> cnt(nb);
     std::vector<u64> sum(nb), kidx(nb), vbefore(nb);
@@ -308,9 +342,8 @@ int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint3
     }
     CK(cudaMemcpyAsync(ctx->blk_kidx.p, kidx.data(), nb * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->blk_vbefore.p, vbefore.data(), nb * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
-    k_db_block_own<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_kidx.as<u64>(),
-                                                        ctx->blk_vbefore.as<u64>(), ctx->blocks.as<BlockIndex>());
-    LAUNCH_CHECK();
+    KL(-1, k_db_block_own<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_kidx.as<u64>(),
+                                                        ctx->blk_vbefore.as<u64>(), ctx->blocks.as<BlockIndex>()));
     std::vector<BlockIndex> bi(nb);
     CK(cudaMemcpyAsync(bi.data(), ctx->blocks.p, nb * sizeof(BlockIndex), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -333,10 +366,9 @@ int mb_decode_db(mb_ctx *ctx, uint64_t *values_out, size_t cap, size_t *n_out) {
     if (ctx->n_db_kmers == 0) return MB_OK;
     DevBuf vals;
     CK(vals.ensure(ctx->n_db_kmers * sizeof(u64)));
-    k_db_decode<<<ctx->n_blocks, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, true), ctx->n_blocks, ctx->blk_back.as<u32>(),
+    KL(-1, k_db_decode<<<ctx->n_blocks, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, true), ctx->n_blocks, ctx->blk_back.as<u32>(),
                                                               ctx->blk_cnt.as<u32>(), ctx->blk_kidx.as<u64>(),
-                                                              ctx->blk_vbefore.as<u64>(), vals.as<u64>());
-    LAUNCH_CHECK();
+                                                              ctx->blk_vbefore.as<u64>(), vals.as<u64>()));
     CK(cudaMemcpyAsync(values_out, vals.p, ctx->n_db_kmers * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
@@ -418,6 +450,7 @@ int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_
     ctx->max_query_len = max_q + 8;
     ctx->have_reads = true;
     ctx->launches = 0;
+    ctx->n_samples = 0;
     ctx->times.match_retries = 0;
     return MB_OK;
 }
@@ -438,17 +471,13 @@ int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
         CK(ctx->tile_counts.ensure((size_t) n_tiles * sizeof(u32)));
         CK(ctx->tile_offsets.ensure(((size_t) n_tiles + 1) * sizeof(u64)));
         CK(ctx->kmers_a.ensure((ctx->kmer_bound + 1) * sizeof(mb_kmer)));
-        k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>());
-        LAUNCH_CHECK();
-        k_extract<false><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
-                                                                 ctx->tile_counts.as<u32>(), nullptr, nullptr);
-        LAUNCH_CHECK();
-        k_scan_counts<<<1, 1024, 0, ctx->stream>>>(ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(), n_tiles);
-        LAUNCH_CHECK();
-        k_extract<true><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
+        KL(KID_TILE_MATE, k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>()));
+        KL(KID_EXTRACT_COUNT, k_extract<false><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
+                                                                 ctx->tile_counts.as<u32>(), nullptr, nullptr));
+        KL(KID_EXTRACT_SCAN, k_scan_counts<<<1, 1024, 0, ctx->stream>>>(ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(), n_tiles));
+        KL(KID_EXTRACT_WRITE, k_extract<true><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
                                                                 ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(),
-                                                                ctx->kmers_a.as<mb_kmer>());
-        LAUNCH_CHECK();
+                                                                ctx->kmers_a.as<mb_kmer>()));
         u64 total = 0;
         if (int rc = read_back(ctx, ctx->tile_offsets.as<u64>() + n_tiles, &total)) return rc;
         if (total > ctx->kmer_bound) return fail(ctx, MB_E_DATA, "internal: extracted more k-mers than the slot bound");
@@ -466,7 +495,7 @@ int mb_sort_kmers(mb_ctx *ctx) {
     CK(cudaSetDevice(ctx->par.device));
     KmerKey key;
     key.first_bit = 24;   // the join needs the amino-acid parts grouped in increasing order; 5 passes of 8 bits
-    if (int rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, 5)) return rc;
+    if (int rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, 5, KID_KSORT_HIST)) return rc;
     mark(ctx, EV_SORTK);
     ctx->kmers_sorted = true;
     return MB_OK;
@@ -482,9 +511,8 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
     if (ctx->n_blocks && ctx->n_kmers) {
         const u32 nb = ctx->n_blocks;
         CK(ctx->qstart.ensure(((size_t) nb + 1) * sizeof(u64)));
-        k_match_partition<<<(nb + 1 + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
-                                                                       ctx->n_kmers, ctx->qstart.as<u64>());
-        LAUNCH_CHECK();
+        KL(KID_MATCH_PARTITION, k_match_partition<<<(nb + 1 + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
+                                                                       ctx->n_kmers, ctx->qstart.as<u64>()));
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
         for (int attempt = 0; attempt < 3; ++attempt) {
             CK(ctx->matches_a.ensure(cap * sizeof(mb_match)));
@@ -493,9 +521,8 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
             CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
             MatchOut mo;
             mo.out = ctx->matches_a.as<mb_match>(); mo.cap = cap; mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag;
-            k_match<<<nb, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, false), ctx->blocks.as<BlockIndex>(), ctx->kmers_a.as<mb_kmer>(),
-                                                      ctx->qstart.as<u64>(), mo, ctx->tables.as<Tables>(), ctx->par.kmer_format);
-            LAUNCH_CHECK();
+            KL(KID_MATCH, k_match<<<nb, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, false), ctx->blocks.as<BlockIndex>(), ctx->kmers_a.as<mb_kmer>(),
+                                                      ctx->qstart.as<u64>(), mo, ctx->tables.as<Tables>(), ctx->par.kmer_format));
             unsigned long long total = 0;
             if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;
             if (total <= cap) { ctx->n_matches = total; break; }
@@ -530,7 +557,7 @@ int mb_sort_matches(mb_ctx *ctx) {
     CK(cudaSetDevice(ctx->par.device));
     const MatchKey key = match_key(ctx);
     const int passes = (key.total_bits() + 7) / 8;
-    if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes)) return rc;
+    if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST)) return rc;
     mark(ctx, EV_SORTM);
     ctx->matches_sorted = true;
     return MB_OK;
@@ -555,11 +582,9 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
         u32 max_seg = 0;
         if (ctx->n_matches) {
-            k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
-                ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seq_base, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>());
-            LAUNCH_CHECK();
-            k_segment_max<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), nr, &ctx->dcnt()->max_seg);
-            LAUNCH_CHECK();
+            KL(KID_SEGMENT, k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seq_base, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>()));
+            KL(KID_SEGMENT_MAX, k_segment_max<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), nr, &ctx->dcnt()->max_seg));
             if (int rc = read_back(ctx, &ctx->dcnt()->max_seg, &max_seg)) return rc;
         }
         ScoreCfg cfg;
@@ -588,11 +613,10 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         const size_t tc_cap = std::max<size_t>(ctx->n_matches, 16);
         CK(ctx->tc_id.ensure(tc_cap * sizeof(int32_t)));
         CK(ctx->tc_cnt.ensure(tc_cap * sizeof(int32_t)));
-        k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(),
+        KL(KID_SCORE, k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(),
                                                     ctx->lens.as<u32>(), nr, ctx->par.seq_mode == 2 ? 1 : 0, cfg, tv, arena,
                                                     ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(),
-                                                    (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag);
-        LAUNCH_CHECK();
+                                                    (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag));
         unsigned long long used = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->tc_count, &used)) return rc;
         u32 flag = 0;
@@ -778,6 +802,33 @@ int mb_get_timings(mb_ctx *ctx, mb_phase_times *t) {
     o.db_words = ctx->n_words; o.db_kmers = ctx->n_db_kmers;
     o.kernel_launches = ctx->launches;
     *t = o;
+    return MB_OK;
+}
+
+int mb_set_profile(mb_ctx *ctx, int on) {
+    if (!ctx) return MB_E_ARG;
+    ctx->profile = on != 0;
+    ctx->n_samples = 0;
+    return MB_OK;
+}
+
+int mb_get_kernel_times(mb_ctx *ctx, mb_kernel_time *out, size_t cap, size_t *n) {
+    if (!ctx || !n || (!out && cap)) return MB_E_ARG;
+    *n = KID_COUNT;
+    if (cap < (size_t) KID_COUNT) return fail(ctx, MB_E_CAPACITY, "kernel time table needs KID_COUNT entries");
+    CK(cudaSetDevice(ctx->par.device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < KID_COUNT; ++k) {
+        memset(&out[k], 0, sizeof(out[k]));
+        strncpy(out[k].name, KID_NAMES[k], sizeof(out[k].name) - 1);
+    }
+    for (size_t i = 0; i < ctx->n_samples; ++i) {
+        const KSample &s = ctx->samples[i];
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.a, s.b) != cudaSuccess) { cudaGetLastError(); continue; }
+        out[s.kid].ms += ms;
+        out[s.kid].launches += 1;
+    }
     return MB_OK;
 }
 

@@ -17,8 +17,9 @@
  * LocalParameters cannot be constructed without the MMseqs2 Parameters machinery (generated
  * code again), so a zeroed object is fabricated and only the fields the path reads are set.
  *
- * usage: ref_harness DBDIR OUTPREFIX SEQMODE THREADS READS1 [READS2] [--dump] [--reps N]
+ * usage: ref_harness DBDIR OUTPREFIX SEQMODE THREADS READS1 [READS2] [--dump] [--reps N] [--skip-reps W]
  *                    [--max-reads N] [--min-score F] [--min-sp-score F]
+ * (--skip-reps W: the first W of the N repetitions are warm-up and stay out of the reported means)
  * writes OUTPREFIX.results.tsv and, with --dump, OUTPREFIX.kmers.bin / OUTPREFIX.matches.bin;
  * prints one JSON line with per-phase wall times.
  */
@@ -70,16 +71,18 @@ int main(int argc, char **argv) {
     int argi = 6;
     if (seqMode == 2) { reads2 = argv[argi++]; }
     bool dump = false;
-    int reps = 1;
+    int reps = 1, skipReps = 0;
     size_t maxReads = SIZE_MAX;
     float minScore = 0.f, minSpScore = 0.f;
     for (; argi < argc; ++argi) {
         if (!strcmp(argv[argi], "--dump")) dump = true;
         else if (!strcmp(argv[argi], "--reps")) reps = atoi(argv[++argi]);
+        else if (!strcmp(argv[argi], "--skip-reps")) skipReps = atoi(argv[++argi]);
         else if (!strcmp(argv[argi], "--max-reads")) maxReads = strtoull(argv[++argi], nullptr, 10);
         else if (!strcmp(argv[argi], "--min-score")) minScore = (float) atof(argv[++argi]);
         else if (!strcmp(argv[argi], "--min-sp-score")) minSpScore = (float) atof(argv[++argi]);
     }
+    if (skipReps >= reps) skipReps = reps - 1;
     omp_set_num_threads(threads);
 
     LocalParameters &par = *fabricate_parameters();
@@ -147,6 +150,7 @@ int main(int argc, char **argv) {
     Buffer<Kmer> kmerBuffer(16);
     Buffer<Match> matchBuffer(16);
     for (int rep = 0; rep < reps; ++rep) {
+        if (rep == skipReps) tExtract = tSortK = tMatch = tSortM = tScore = 0;   /* warm-up repetitions end here */
         /* ---- extraction: KmerExtractor.cpp:442-494 (lengths, empties), :312-386 (six frames) ---- */
         t0 = now_s();
         size_t slots = 0;
@@ -289,7 +293,7 @@ int main(int argc, char **argv) {
     printf("\n{\"harness\": \"reference\", \"reads\": %zu, \"kmers\": %zu, \"matches\": %zu, \"threads\": %d, \"reps\": %d, "
            "\"parse_s\": %.6f, \"extract_s\": %.6f, \"sort_kmers_s\": %.6f, \"match_s\": %.6f, \"sort_matches_s\": %.6f, "
            "\"score_s\": %.6f}\n",
-           nReads, nKmers, nMatches, threads, reps, tParse, tExtract / reps, tSortK / reps, tMatch / reps, tSortM / reps,
-           tScore / reps);
+           nReads, nKmers, nMatches, threads, reps - skipReps, tParse, tExtract / (reps - skipReps), tSortK / (reps - skipReps),
+           tMatch / (reps - skipReps), tSortM / (reps - skipReps), tScore / (reps - skipReps));
     return 0;
 }
