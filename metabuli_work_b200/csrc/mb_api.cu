@@ -51,6 +51,7 @@ struct Counters {                 // device-side scalars, one allocation
     u32 max_seg;
     u32 score_ticket;
     u32 radix_ticket;
+    u32 match_ticket;
     u32 trivial[RS_MAX_PASSES];
 };
 
@@ -92,6 +93,7 @@ struct mb_ctx {
     DevBuf qstart, matches_a, matches_b;
     u64 n_matches = 0;
     DevBuf seg_begin, seg_end, results, tc_id, tc_cnt, arena;
+    DevBuf sc_local, sc_paths, sc_comb, sc_linked, sc_spid, sc_spscore;   // per-match scoring scratch
     u64 tc_used = 0;
     DevBuf counters;
     void *pinned = nullptr;       // 256-byte pinned scratch for read-backs
@@ -513,6 +515,11 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
         CK(ctx->qstart.ensure(((size_t) nb + 1) * sizeof(u64)));
         KL(KID_MATCH_PARTITION, k_match_partition<<<(nb + 1 + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
                                                                        ctx->n_kmers, ctx->qstart.as<u64>()));
+        static bool match_attr_set = false;
+        if (!match_attr_set) {
+            CK(cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            match_attr_set = true;
+        }
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
         for (int attempt = 0; attempt < 3; ++attempt) {
             CK(ctx->matches_a.ensure(cap * sizeof(mb_match)));
@@ -521,8 +528,11 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
             CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
             MatchOut mo;
             mo.out = ctx->matches_a.as<mb_match>(); mo.cap = cap; mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag;
-            KL(KID_MATCH, k_match<<<nb, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, false), ctx->blocks.as<BlockIndex>(), ctx->kmers_a.as<mb_kmer>(),
-                                                      ctx->qstart.as<u64>(), mo, ctx->tables.as<Tables>(), ctx->par.kmer_format));
+            CK(cudaMemsetAsync(&ctx->dcnt()->match_ticket, 0, sizeof(u32), ctx->stream));
+            const unsigned grid = (unsigned) std::min<u64>(nb, 148ull * 3);     // persistent: 3 CTAs per SM (70 KB smem each)
+            KL(KID_MATCH, k_match<<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
+                              db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), ctx->qstart.as<u64>(), mo,
+                              ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket));
             unsigned long long total = 0;
             if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;
             if (total <= cap) { ctx->n_matches = total; break; }
@@ -576,16 +586,12 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         CK(ctx->results.ensure((size_t) nr * sizeof(mb_read_result)));
         CK(cudaMemsetAsync(ctx->seg_begin.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
         CK(cudaMemsetAsync(ctx->seg_end.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
-        CK(cudaMemsetAsync(&ctx->dcnt()->max_seg, 0, sizeof(u32), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->tc_count, 0, sizeof(unsigned long long), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->score_ticket, 0, sizeof(u32), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
-        u32 max_seg = 0;
         if (ctx->n_matches) {
             KL(KID_SEGMENT, k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seq_base, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>()));
-            KL(KID_SEGMENT_MAX, k_segment_max<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), nr, &ctx->dcnt()->max_seg));
-            if (int rc = read_back(ctx, &ctx->dcnt()->max_seg, &max_seg)) return rc;
         }
         ScoreCfg cfg;
         cfg.format = ctx->par.kmer_format;
@@ -599,17 +605,25 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         tv.species_rank_of = ctx->species_rank_of.as<int32_t>(); tv.max_taxid = ctx->max_taxid; tv.node0_taxid = ctx->node0;
         tv.eukaryota = ctx->euk;
         ScoreArena arena;
-        arena.cap_n = (int) std::max<u32>(max_seg, 16);
         arena.cap_b = (int) ((ctx->max_query_len + 3) / (u32) cfg.dna_shift + 2);
         arena.cap_c = 4 * arena.cap_b + 64;
-        arena.slice_bytes = arena_slice_bytes(arena.cap_n, arena.cap_b, arena.cap_c);
-        // resident warps: enough to fill the machine, bounded by an 8-GB arena
-        const u64 budget = 8ull << 30;
-        u64 warps = std::min<u64>(148ull * 16 * (SC_THREADS / 32), std::max<u64>(budget / arena.slice_bytes, SC_THREADS / 32));
-        warps = std::min<u64>(warps, ((u64) nr + 3) / 4 + (SC_THREADS / 32));
-        const unsigned grid = (unsigned) std::max<u64>(1, warps / (SC_THREADS / 32));
-        CK(ctx->arena.ensure((size_t) grid * (SC_THREADS / 32) * arena.slice_bytes));
+        arena.slice_bytes = arena_slice_bytes(arena.cap_b, arena.cap_c);
+        // one thread per read; resident threads fill the machine, bounded by a 4-GB arena of per-thread slices
+        const u64 budget = 4ull << 30;
+        u64 threads = std::min<u64>(148ull * 2048, std::max<u64>(budget / arena.slice_bytes, SC_THREADS));
+        threads = std::min<u64>(threads, (u64) nr + SC_THREADS);
+        const unsigned grid = (unsigned) std::max<u64>(1, threads / SC_THREADS);
+        CK(ctx->arena.ensure((size_t) grid * SC_THREADS * arena.slice_bytes));
         arena.base = ctx->arena.as<unsigned char>();
+        const size_t nm = std::max<size_t>(ctx->n_matches, 1);
+        CK(ctx->sc_local.ensure(nm * sizeof(PathRec)));
+        CK(ctx->sc_paths.ensure(nm * sizeof(PathRec)));
+        CK(ctx->sc_comb.ensure(nm * sizeof(PathRec)));
+        CK(ctx->sc_linked.ensure(nm));
+        CK(ctx->sc_spid.ensure(nm * sizeof(int32_t)));
+        CK(ctx->sc_spscore.ensure(nm * sizeof(float)));
+        arena.local = ctx->sc_local.as<PathRec>(); arena.paths = ctx->sc_paths.as<PathRec>(); arena.combined = ctx->sc_comb.as<PathRec>();
+        arena.linked = ctx->sc_linked.as<u8>(); arena.sp_id = ctx->sc_spid.as<int32_t>(); arena.sp_score = ctx->sc_spscore.as<float>();
         const size_t tc_cap = std::max<size_t>(ctx->n_matches, 16);
         CK(ctx->tc_id.ensure(tc_cap * sizeof(int32_t)));
         CK(ctx->tc_cnt.ensure(tc_cap * sizeof(int32_t)));

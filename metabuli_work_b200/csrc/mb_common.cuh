@@ -49,11 +49,17 @@ MB_HD int query_kmer_number(int len) { return (max_covered_length(len) / 3 - 8 +
 //               ARNDCQEGHILKMFPSTWYVX, 3-bit codon ids)
 //   codonR[i] : same index -> reverse-strand codon comp(b2) comp(b1) comp(b0) (KmerScanner.h:94-98)
 //   ham4      : 8x8 codon-id Hamming table, 4 bits per cell (KmerMatcher.h:66-70 hammingLookup)
+//   lut2      : the same table for two codons at a time: index = qpair << 6 | tpair, where a pair is six bits
+//               of the DNA part (codon 2j in the low three bits); cell = sum of the two Hamming cells (<= 8)
+//   lutp      : per pair, the two 2-bit fields of getHammings (low nibble: v0 | v1 << 2) and of
+//               getHammings_reverse (high nibble: v1 | v0 << 2), v = cell & 3 (KmerMatcher.h:72-158, 386-416)
 struct Tables {
     u8 nuc[256];
     u8 codonF[64];
     u8 codonR[64];
     u64 ham4[4];
+    u8 lut2[4096];
+    u8 lutp[4096];
 };
 
 void build_tables(Tables &t);
@@ -86,6 +92,27 @@ MB_HD u32 hamming_pack(const u64 (&h)[4], u64 q, u64 t, bool reverse) {
         if (field == 7 && (a == 4 || a == 5) && (b == 6 || b == 7)) v = 1;
         out |= v << (2 * field);
     }
+    return out;
+}
+
+// The same two functions through the two-codon tables (4 lookups instead of 8 cell extractions).
+MB_HD u32 hamming_sum_lut(const u8 *lut2, u64 q, u64 t) {
+    u32 s = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) s += lut2[(((u32) (q >> (6 * j)) & 63u) << 6) | ((u32) (t >> (6 * j)) & 63u)];
+    return s;
+}
+MB_HD u32 hamming_pack_lut(const u8 *lutp, u64 q, u64 t, bool reverse) {
+    u32 out = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const u32 p = lutp[(((u32) (q >> (6 * j)) & 63u) << 6) | ((u32) (t >> (6 * j)) & 63u)];
+        out |= reverse ? ((p >> 4) << (4 * (3 - j))) : ((p & 15u) << (4 * j));
+    }
+    // HAMMING_LUT7 quirk: field 7 (codon 7, or codon 0 when reversed) holds 1 for query ids 4,5 vs target ids 6,7
+    const int kq = reverse ? 0 : 7;
+    const u32 a = (u32) (q >> (3 * kq)) & 7u, b = (u32) (t >> (3 * kq)) & 7u;
+    if ((a == 4 || a == 5) && (b == 6 || b == 7)) out |= 1u << 14;
     return out;
 }
 

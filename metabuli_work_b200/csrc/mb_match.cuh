@@ -19,9 +19,13 @@
 //   1. loads its block plus a 512-word overhang with 16-byte loads into shared memory,
 //   2. decodes it cooperatively: each thread assembles the deltas ending in its 10 words, a block
 //      scan of (count, 64-bit delta sum) turns them into absolute values in shared memory,
-//   3. joins its query slice, one query per thread: binary search of the AA part in the decoded
-//      block, a min pass and an emit pass over the group with the Hamming table held in registers,
-//   4. compacts matches with a block scan + ONE atomic reservation per 256 queries and writes them.
+//   3. joins its query slice, one query per thread, warps running independently (32 queries per ticket,
+//      no block barrier): binary search of the AA part in the decoded block, ONE Hamming evaluation per
+//      candidate through a two-codon table in shared memory (distances cached in a packed register),
+//   4. compacts matches per warp: records are staged in a per-warp shared-memory buffer and flushed with
+//      one atomic reservation and coalesced 8-byte stores when the buffer fills.
+// The kernel is persistent (one CTA per resident slot, DB blocks handed out by an atomic ticket), so the
+// tables are loaded into shared memory once per CTA and staged matches survive from block to block.
 // Groups longer than the overhang are re-decoded from their own start; groups longer than a whole
 // chunk take a streaming two-pass path.  Capacity misses are counted, never written out of bounds;
 // the host grows the buffer and reruns (the reference's retry, Classifier.cpp:127-131).
@@ -60,6 +64,8 @@ struct DbView {
 
 struct DbCursor { u64 word, vbefore, kidx; };
 
+constexpr int MT_STAGE = 160;              // matches staged per warp before a flush
+
 struct MatchSmem {
     __align__(16) u16 w[DB_C + 16];
     u64 vals[DB_C];
@@ -72,6 +78,17 @@ struct MatchSmem {
     u32 group_end;
     u64 reserve_base;
     u32 warp_tot[MT_THREADS / 32];
+    u32 qnext;                             // next 32-query ticket of the current chunk
+    u32 cur_block;                         // DB block this CTA is working on (persistent loop)
+    u64 qadv;
+};
+
+// the part of the shared memory that lives for the whole (persistent) kernel
+struct MatchTables {
+    u8 lut2[4096];
+    u8 lutp[4096];
+    u64 stage[MT_THREADS / 32][MT_STAGE * 3];
+    u32 fill[MT_THREADS / 32];
 };
 
 // Decode up to DB_C words starting at cursor c (which must sit on the first word of a k-mer).
@@ -167,67 +184,101 @@ struct MatchOut {
     u32 *error_flag;               // set when a DB tax ID has no species (KmerMatcher.cpp:433-441)
 };
 
-// Block-cooperative: thread t emits its `cnt` matches (entries [lo,hi) of s.vals with dist <= maxh).
-__device__ __forceinline__ void emit_matches(const DbView &db, const DbCursor &c, MatchSmem &s, const MatchOut &mo,
-                                             const u64 (&ham)[4], bool active, const mb_kmer &q, u32 lo, u32 hi,
-                                             u32 maxh, u32 cnt, int format) {
-    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// One match record (Match.h:9-25 payload) from query q and DB k-mer ordinal `kidx` with value t, distance d.
+__device__ __forceinline__ void make_match(const DbView &db, const MatchOut &mo, const u8 *lutp, const mb_kmer &q, u64 t, u64 kidx,
+                                           u32 d, int format, u64 (&rec)[3]) {
+    const int32_t tax = (int32_t) (__ldg(db.info + kidx) & db.info_mask);
+    int32_t sp = 0;
+    if (tax >= 0 && tax <= db.max_taxid) sp = __ldg(db.species_of + tax);
+    if (sp == 0 || tax == 0) *mo.error_flag = 1;
+    // KmerMatcher.cpp:1137-1143: getHammings for (frame<3) == (format==2), else getHammings_reverse
+    const bool rev = ((qi_frame(q.qinfo) < 3) != (format == 2));
+    const u32 pack = d ? hamming_pack_lut(lutp, q.value, t, rev) : 0u;       // distance 0 <=> every field 0
+    rec[0] = q.qinfo;
+    rec[1] = (u64) (u32) tax | ((u64) (u32) sp << 32);
+    rec[2] = (t & 0xFFFFFFull) | ((u64) pack << 32) | ((u64) d << 48);
+}
+
+// Flush the warp's staged matches: one reservation, coalesced 8-byte stores.  Warp-synchronous.
+__device__ __forceinline__ void warp_flush(const MatchOut &mo, u64 *stage, u32 &fill) {
+    const u32 lane = threadIdx.x & 31;
+    __syncwarp();
+    if (fill) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(mo.counter, (unsigned long long) fill);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        u64 *dst = reinterpret_cast<u64 *>(mo.out) + base * 3;
+        const u32 words = fill * 3;
+        if (base + fill <= mo.cap) {
+            for (u32 i = lane; i < words; i += 32) dst[i] = stage[i];
+        } else {
+            for (u32 i = lane; i < words; i += 32)
+                if (base + i / 3 < mo.cap) dst[i] = stage[i];
+        }
+    }
+    fill = 0;
+    __syncwarp();
+}
+
+// Warp-level emission: lane l adds `cnt` matches (entries [lo,hi) of s.vals whose distance is <= maxh; the
+// distances of the first 16 entries are cached 4 bits each in dpack).
+__device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, const MatchSmem &s, MatchTables &tb, const MatchOut &mo,
+                                          bool active, const mb_kmer &q, u32 lo, u32 hi, u32 maxh, u32 cnt, u64 dpack, int format,
+                                          u32 &fill) {
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     u32 incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
         if (lane >= (u32) d) incl += t;
     }
-    if (lane == 31) s.warp_tot[warp] = incl;
-    __syncthreads();
-    u32 wb = 0, total = 0;
-#pragma unroll
-    for (int k = 0; k < MT_THREADS / 32; ++k) {
-        const u32 t = s.warp_tot[k];
-        if ((u32) k < warp) wb += t;
-        total += t;
+    const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (total == 0) return;
+    u64 *stage = tb.stage[warp];
+    if (total > MT_STAGE) {
+        // more than the staging buffer holds (a few very long groups): reserve and write straight to HBM
+        warp_flush(mo, stage, fill);
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(mo.counter, (unsigned long long) total);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (active && cnt) {
+            u64 o = base + incl - cnt;
+            for (u32 j = lo; j < hi; ++j) {
+                const u64 t = s.vals[j];
+                const u32 d = (j - lo < 16) ? (u32) (dpack >> (4 * (j - lo))) & 15u : hamming_sum_lut(tb.lut2, q.value, t);
+                if (d > maxh) continue;
+                if (o < mo.cap) {
+                    u64 rec[3];
+                    make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
+                    u64 *p = reinterpret_cast<u64 *>(mo.out + o);
+                    p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
+                }
+                ++o;
+            }
+        }
+        return;
     }
-    if (tid == 0 && total) s.reserve_base = atomicAdd(mo.counter, (unsigned long long) total);
-    __syncthreads();
+    if (fill + total > MT_STAGE) warp_flush(mo, stage, fill);
     if (active && cnt) {
-        u64 o = s.reserve_base + wb + incl - cnt;
-        const u32 frame = qi_frame(q.qinfo);
-        // KmerMatcher.cpp:1137-1143: getHammings for (frame<3) == (format==2), else getHammings_reverse
-        const bool rev = ((frame < 3) != (format == 2));
+        u32 o = fill + incl - cnt;
         for (u32 j = lo; j < hi; ++j) {
             const u64 t = s.vals[j];
-            const u32 d = hamming_sum(ham, q.value, t);
+            const u32 d = (j - lo < 16) ? (u32) (dpack >> (4 * (j - lo))) & 15u : hamming_sum_lut(tb.lut2, q.value, t);
             if (d > maxh) continue;
-            if (o < mo.cap) {
-                const int32_t tax = (int32_t) (__ldg(db.info + c.kidx + j) & db.info_mask);
-                int32_t sp = 0;
-                if (tax >= 0 && tax <= db.max_taxid) sp = __ldg(db.species_of + tax);
-                if (sp == 0 || tax == 0) *mo.error_flag = 1;
-                mb_match m;
-                m.qinfo = q.qinfo;
-                m.targetId = tax;
-                m.speciesId = sp;
-                m.dnaEncoding = (u32) (t & 0xFFFFFFull);
-                m.rightEndHamming = (u16) hamming_pack(ham, q.value, t, rev);
-                m.hamming = (u8) d;
-                m.pad = 0;
-                // 24-byte record as three 8-byte stores
-                u64 *p = reinterpret_cast<u64 *>(mo.out + o);
-                p[0] = m.qinfo;
-                p[1] = (u64) (u32) m.targetId | ((u64) (u32) m.speciesId << 32);
-                p[2] = (u64) m.dnaEncoding | ((u64) m.rightEndHamming << 32) | ((u64) m.hamming << 48);
-            }
+            u64 rec[3];
+            make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
+            stage[o * 3] = rec[0]; stage[o * 3 + 1] = rec[1]; stage[o * 3 + 2] = rec[2];
             ++o;
         }
     }
-    __syncthreads();
+    fill += total;
+    __syncwarp();
 }
 
 // Streaming two-pass join for an amino-acid group that does not fit one chunk: for every batch of
 // 256 queries of that group the group is decoded twice from its start cursor (minimum, then emit).
-__device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, MatchSmem &s, const MatchOut &mo,
-                                         const u64 (&ham)[4], const mb_kmer *__restrict__ q, u64 qcur, u64 qend,
-                                         u64 gaa, int format) {
+__device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, MatchSmem &s, MatchTables &tb, const MatchOut &mo,
+                                         const mb_kmer *__restrict__ q, u64 qcur, u64 qend, u64 gaa, int format, u32 &fill) {
     const u32 tid = threadIdx.x;
     while (true) {
         const u64 qi = qcur + tid;
@@ -253,16 +304,21 @@ __device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, Ma
                 if (phase == 0) {
                     if (mine)
                         for (u32 j = 0; j < ge; ++j) {
-                            const u32 d = hamming_sum(ham, qk.value, s.vals[j]);
+                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, s.vals[j]);
                             mind = d < mind ? d : mind;
                         }
-                    __syncthreads();
                 } else {
                     u32 cnt = 0;
+                    u64 dpack = 0;
                     if (mine)
-                        for (u32 j = 0; j < ge; ++j) cnt += hamming_sum(ham, qk.value, s.vals[j]) <= maxh ? 1u : 0u;
-                    emit_matches(db, g, s, mo, ham, mine, qk, 0, ge, maxh, cnt, format);
+                        for (u32 j = 0; j < ge; ++j) {
+                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, s.vals[j]);
+                            if (j < 16) dpack |= (u64) (d < 15 ? d : 15) << (4 * j);
+                            cnt += d <= maxh ? 1u : 0u;
+                        }
+                    warp_emit(db, g, s, tb, mo, mine, qk, 0, ge, maxh, cnt, dpack, format, fill);
                 }
+                __syncthreads();
                 if (finished) break;
                 const u64 nw = g.word + (u64) s.wend[n - 1] + 1;
                 const u64 nv = s.vals[n - 1];
@@ -276,91 +332,135 @@ __device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, Ma
     }
 }
 
-__global__ void __launch_bounds__(MT_THREADS)
-k_match(DbView db, const BlockIndex *__restrict__ blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
-        MatchOut mo, const Tables *__restrict__ tables, int format) {
-    __shared__ MatchSmem s;
-    const u32 tid = threadIdx.x;
-    const u32 b = blockIdx.x;
-    const BlockIndex bi = blocks[b];
-    if (!bi.owns) return;
-    u64 qcur = qstart[b];
-    const u64 qend = qstart[b + 1];
-    if (qcur >= qend) return;                      // no query falls into this block's AA range
-    u64 ham[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) ham[i] = tables->ham4[i];
+// first index in q[lo, hi) whose AA part is >= aa
+__device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, u64 lo, u64 hi, u64 aa) {
+    while (lo < hi) {
+        const u64 mid = (lo + hi) >> 1;
+        if ((__ldg(&q[mid].value) >> 24) < aa) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
 
-    const u64 tile_end = (u64) (b + 1) * DB_W;     // groups starting at or after this word belong to later blocks
-    DbCursor c{bi.word, bi.vbefore, bi.kidx};
+__global__ void __launch_bounds__(MT_THREADS)
+k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
+        MatchOut mo, const Tables *__restrict__ tables, int format, u32 *block_ticket) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    MatchSmem &s = *reinterpret_cast<MatchSmem *>(smem_raw);
+    MatchTables &tb = *reinterpret_cast<MatchTables *>(smem_raw + ((sizeof(MatchSmem) + 15) & ~(size_t) 15));
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const uint4 *src2 = reinterpret_cast<const uint4 *>(tables->lut2);
+        const uint4 *srcp = reinterpret_cast<const uint4 *>(tables->lutp);
+        uint4 *d2 = reinterpret_cast<uint4 *>(tb.lut2);
+        uint4 *dp = reinterpret_cast<uint4 *>(tb.lutp);
+        for (u32 i = tid; i < 4096 / 16; i += MT_THREADS) { d2[i] = __ldg(src2 + i); dp[i] = __ldg(srcp + i); }
+    }
+    u32 fill = 0;                                   // matches staged by this warp (warp-uniform)
 
     while (true) {
-        const u32 n = decode_chunk(db, c, s);
-        if (n == 0) break;
-        if (tid == 0) { s.last_start = 0; s.own_end = (int) n; }
+        __syncthreads();                            // previous block is done with the shared arrays
+        if (tid == 0) s.cur_block = atomicAdd(block_ticket, 1u);
         __syncthreads();
-        const u64 own_limit = tile_end > c.word ? tile_end - c.word : 0;   // local word offset of the block end
-        for (u32 j = tid + 1; j < n; j += MT_THREADS) {
-            if ((s.vals[j] >> 24) != (s.vals[j - 1] >> 24)) {
-                atomicMax(&s.last_start, (int) j);
-                // first word of k-mer j is the word after the previous terminator
-                if ((u64) s.wend[j - 1] + 1 >= own_limit) atomicMin(&s.own_end, (int) j);
-            }
-        }
-        __syncthreads();
-        const bool db_end = (c.kidx + n == db.n_kmers_eff);
-        u32 proc_end = db_end ? n : (u32) s.last_start;     // the last group may continue past the chunk
-        if ((u32) s.own_end < proc_end) proc_end = (u32) s.own_end;
-        const u32 own_end = (u32) s.own_end;
-        __syncthreads();
+        const u32 b = s.cur_block;
+        if (b >= n_blocks) break;
+        const BlockIndex bi = blocks[b];
+        if (!bi.owns) continue;
+        u64 qcur = qstart[b];
+        const u64 qend = qstart[b + 1];
+        if (qcur >= qend) continue;                 // no query falls into this block's AA range
 
-        if (proc_end == 0) {
-            // One group fills the whole chunk and is not known to be complete: streaming path.  The
-            // group is owned (the cursor always sits on a group starting inside this block) and, being
-            // longer than a block plus overhang, it is the last one this block owns.
-            giant_group(db, c, s, mo, ham, q, qcur, qend, s.vals[0] >> 24, format);
-            break;
-        }
+        const u64 tile_end = (u64) (b + 1) * DB_W;  // groups starting at or after this word belong to later blocks
+        DbCursor c{bi.word, bi.vbefore, bi.kidx};
 
-        // ---- fast path: all groups in [0, proc_end) are complete and owned ----
-        const u64 limit_aa = proc_end < n ? (s.vals[proc_end] >> 24) : ~0ull;
         while (true) {
-            const u64 qi = qcur + tid;
-            mb_kmer qk;
-            qk.value = 0; qk.qinfo = 0;
-            bool mine = false;
-            if (qi < qend) { qk = q[qi]; mine = (qk.value >> 24) < limit_aa; }
-            const int taken = __syncthreads_count(mine);
-            u32 lo = 0, hi = 0, maxh = 0, cnt = 0;
-            if (mine) {
-                const u64 aa = qk.value >> 24;
-                lo = lower_bound_aa(s.vals, proc_end, aa);
-                hi = lo;
-                u32 mind = 255;
-                while (hi < proc_end && (s.vals[hi] >> 24) == aa) {
-                    const u32 d = hamming_sum(ham, qk.value, s.vals[hi]);
-                    mind = d < mind ? d : mind;
-                    ++hi;
-                }
-                if (hi > lo) {
-                    maxh = mind * 2 < 7 ? mind * 2 : 7;        // KmerMatcher.cpp:1126
-                    for (u32 j = lo; j < hi; ++j) cnt += hamming_sum(ham, qk.value, s.vals[j]) <= maxh ? 1u : 0u;
+            const u32 n = decode_chunk(db, c, s);
+            if (n == 0) break;
+            if (tid == 0) { s.last_start = 0; s.own_end = (int) n; s.qnext = 0; }
+            __syncthreads();
+            const u64 own_limit = tile_end > c.word ? tile_end - c.word : 0;   // local word offset of the block end
+            for (u32 j = tid + 1; j < n; j += MT_THREADS) {
+                if ((s.vals[j] >> 24) != (s.vals[j - 1] >> 24)) {
+                    atomicMax(&s.last_start, (int) j);
+                    // first word of k-mer j is the word after the previous terminator
+                    if ((u64) s.wend[j - 1] + 1 >= own_limit) atomicMin(&s.own_end, (int) j);
                 }
             }
-            emit_matches(db, c, s, mo, ham, mine, qk, lo, hi, maxh, cnt, format);
-            qcur += (u64) taken;
-            if (taken < MT_THREADS) break;
+            __syncthreads();
+            const bool db_end = (c.kidx + n == db.n_kmers_eff);
+            u32 proc_end = db_end ? n : (u32) s.last_start;     // the last group may continue past the chunk
+            if ((u32) s.own_end < proc_end) proc_end = (u32) s.own_end;
+            const u32 own_end = (u32) s.own_end;
+
+            if (proc_end == 0) {
+                // One group fills the whole chunk and is not known to be complete: streaming path.  The
+                // group is owned (the cursor always sits on a group starting inside this block) and, being
+                // longer than a block plus overhang, it is the last one this block owns.
+                const u64 gaa = s.vals[0] >> 24;
+                __syncthreads();
+                giant_group(db, c, s, tb, mo, q, qcur, qend, gaa, format, fill);
+                break;
+            }
+
+            // ---- fast path: all groups in [0, proc_end) are complete and owned.  Warps run on their own. ----
+            const u64 limit_aa = proc_end < n ? (s.vals[proc_end] >> 24) : ~0ull;
+            while (true) {
+                u32 base = 0;
+                if (lane == 0) base = atomicAdd(&s.qnext, 32u);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (qcur + base >= qend) break;
+                const u64 qi = qcur + base + lane;
+                mb_kmer qk;
+                qk.value = 0; qk.qinfo = 0;
+                bool mine = false;
+                if (qi < qend) {
+                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(q + qi));
+                    qk.value = v.x; qk.qinfo = v.y;
+                    mine = (qk.value >> 24) < limit_aa;
+                }
+                const u32 mine_mask = __ballot_sync(0xFFFFFFFFu, mine);
+                u32 lo = 0, hi = 0, maxh = 0, cnt = 0;
+                u64 dpack = 0;
+                if (mine) {
+                    const u64 aa = qk.value >> 24;
+                    lo = lower_bound_aa(s.vals, proc_end, aa);
+                    hi = lo;
+                    u32 mind = 255;
+                    while (hi < proc_end) {
+                        const u64 t = s.vals[hi];
+                        if ((t >> 24) != aa) break;
+                        const u32 d = hamming_sum_lut(tb.lut2, qk.value, t);
+                        if (hi - lo < 16) dpack |= (u64) (d < 15 ? d : 15) << (4 * (hi - lo));
+                        mind = d < mind ? d : mind;
+                        ++hi;
+                    }
+                    if (hi > lo) {
+                        maxh = mind * 2 < 7 ? mind * 2 : 7;        // KmerMatcher.cpp:1126
+                        const u32 n16 = hi - lo < 16 ? hi - lo : 16;
+                        for (u32 j = 0; j < n16; ++j) cnt += ((u32) (dpack >> (4 * j)) & 15u) <= maxh ? 1u : 0u;
+                        for (u32 j = lo + 16; j < hi; ++j) cnt += hamming_sum_lut(tb.lut2, qk.value, s.vals[j]) <= maxh ? 1u : 0u;
+                    }
+                }
+                warp_emit(db, c, s, tb, mo, mine, qk, lo, hi, maxh, cnt, dpack, format, fill);
+                if (mine_mask != 0xFFFFFFFFu) break;               // queries are sorted: the rest belongs to later groups
+            }
+            __syncthreads();
+            if (proc_end >= n && db_end) break;                        // end of the stream
+            if (proc_end >= own_end) break;                            // the next group starts in a later block
+            // continue from the first group that was not processed (it starts inside this block)
+            if (tid == 0) s.qadv = query_lower_bound(q, qcur, qend, limit_aa);
+            const u64 nw = c.word + (u64) s.wend[proc_end - 1] + 1;
+            const u64 nv = s.vals[proc_end - 1];
+            __syncthreads();
+            qcur = s.qadv;
+            c.word = nw; c.vbefore = nv; c.kidx += proc_end;
+            if (qcur >= qend) break;
+            __syncthreads();
         }
-        if (proc_end >= n && db_end) break;                        // end of the stream
-        if (proc_end >= own_end) break;                            // the next group starts in a later block
-        // continue from the first group that was not processed (it starts inside this block)
-        c.word += (u64) s.wend[proc_end - 1] + 1;
-        c.vbefore = s.vals[proc_end - 1];
-        c.kidx += proc_end;
-        if (qcur >= qend) break;
-        __syncthreads();
     }
+    warp_flush(mo, tb.stage[warp], fill);
 }
+
+constexpr size_t match_smem_bytes() { return ((sizeof(MatchSmem) + 15) & ~(size_t) 15) + sizeof(MatchTables); }
 
 // ---- load-time block index ---------------------------------------------------------------------------
 // pass A: per block, how many words in front of the block belong to the first k-mer ending in it, how

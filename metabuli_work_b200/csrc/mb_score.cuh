@@ -477,84 +477,88 @@ __global__ void k_segment_max(const u64 *__restrict__ seg_begin, const u64 *__re
     if ((threadIdx.x & 31) == 0 && len) atomicMax(max_len, len);
 }
 
-struct ScoreArena {        // one slice per resident warp
+struct ScoreArena {
+    // per-thread slices (filterRedundantMatches buckets, taxCnt, clade table): slot-indexed
     unsigned char *base;
     u64 slice_bytes;
-    int cap_n, cap_b, cap_c;
+    int cap_b, cap_c;
+    // per-match scratch, indexed from the read's first match (a read never needs more entries than it has matches)
+    PathRec *local, *paths, *combined;
+    u8 *linked;
+    int32_t *sp_id;
+    float *sp_score;
 };
 
-__host__ __device__ inline u64 arena_slice_bytes(int cap_n, int cap_b, int cap_c) {
+__host__ __device__ inline u64 arena_slice_bytes(int cap_b, int cap_c) {
     u64 b = 0;
-    b += (u64) cap_n * sizeof(PathRec) * 3;
-    b += (u64) cap_n * (sizeof(int32_t) + sizeof(float));
     b += (u64) cap_b * sizeof(int32_t) * 3;
     b += (u64) cap_c * sizeof(int32_t) * 3;
-    b += (u64) cap_n + (u64) cap_b;
-    return (b + 255) & ~255ull;
+    b += (u64) cap_b;
+    return (b + 15) & ~15ull;
 }
 
-__device__ __forceinline__ void arena_carve(const ScoreArena &a, u64 slot, ReadScratch &s) {
+__device__ __forceinline__ void arena_carve(const ScoreArena &a, u64 slot, u64 first_match, int n_matches, ReadScratch &s) {
     unsigned char *p = a.base + slot * a.slice_bytes;
-    s.local = reinterpret_cast<PathRec *>(p); p += (u64) a.cap_n * sizeof(PathRec);
-    s.paths = reinterpret_cast<PathRec *>(p); p += (u64) a.cap_n * sizeof(PathRec);
-    s.combined = reinterpret_cast<PathRec *>(p); p += (u64) a.cap_n * sizeof(PathRec);
-    s.sp_id = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_n * sizeof(int32_t);
-    s.sp_score = reinterpret_cast<float *>(p); p += (u64) a.cap_n * sizeof(float);
     s.bucket_tax = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_b * sizeof(int32_t);
     s.tc_id = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_b * sizeof(int32_t);
     s.tc_cnt = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_b * sizeof(int32_t);
     s.cl_id = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_c * sizeof(int32_t);
     s.cl_cnt = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_c * sizeof(int32_t);
     s.cl_parent = reinterpret_cast<int32_t *>(p); p += (u64) a.cap_c * sizeof(int32_t);
-    s.linked = p; p += a.cap_n;
     s.bucket_ham = p;
-    s.cap_n = a.cap_n; s.cap_b = a.cap_b; s.cap_c = a.cap_c;
+    s.local = a.local + first_match;
+    s.paths = a.paths + first_match;
+    s.combined = a.combined + first_match;
+    s.linked = a.linked + first_match;
+    s.sp_id = a.sp_id + first_match;
+    s.sp_score = a.sp_score + first_match;
+    s.cap_n = n_matches; s.cap_b = a.cap_b; s.cap_c = a.cap_c;
 }
 
 constexpr int SC_THREADS = 128;
 
-// One warp per read at a time; reads are handed out in chunks by an atomic ticket.
+// One THREAD per read: a warp takes 32 consecutive reads by an atomic ticket, lane i scores read r0+i.
+// The per-read logic is sequential and branchy (DP over positions, introsort, greedy combine), so the
+// parallelism of this kernel is across reads; the lanes of a warp walk neighbouring slices of the sorted
+// match list.
 __global__ void __launch_bounds__(SC_THREADS)
 k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
         const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
         mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
         u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag) {
     const u32 lane = threadIdx.x & 31;
-    const u64 slot = (u64) blockIdx.x * (SC_THREADS / 32) + (threadIdx.x >> 5);
-    ReadScratch scr;
-    arena_carve(arena, slot, scr);
-    constexpr u32 CHUNK = 4;
+    const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
     while (true) {
         u32 r0 = 0;
-        if (lane == 0) r0 = atomicAdd(ticket, CHUNK);
+        if (lane == 0) r0 = atomicAdd(ticket, 32u);
         r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
         if (r0 >= n_reads) break;
-        if (lane == 0) {
-            const u32 r1 = r0 + CHUNK < n_reads ? r0 + CHUNK : n_reads;
-            for (u32 r = r0; r < r1; ++r) {
-                // queryLength = max covered length of each mate (KmerExtractor.cpp:452,476)
-                int ql = max_covered_length((int) lens[2 * r]);
-                if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
-                const u64 b = seg_begin[r], e = seg_end[r];
-                mb_read_result res;
-                int n_tc = 0;
-                if (e > b && (e - b) <= (u64) arena.cap_n) {
-                    n_tc = score_read(m + b, 0, (int) (e - b), ql, cfg, tax, scr, res, error_flag);
-                } else {
-                    if (e > b) *error_flag = 4;
-                    res.classification = 0; res.score = 0.f; res.is_classified = 0; res.query_length = ql;
-                    res.hamming_dist = 0; res.taxcnt_begin = 0; res.taxcnt_end = 0; res.n_matches = (int32_t) (e - b);
-                }
-                if (n_tc > 0) {
-                    const u64 o = atomicAdd(tc_counter, (unsigned long long) n_tc);
-                    if (o + (u64) n_tc <= tc_cap) {
-                        for (int k = 0; k < n_tc; ++k) { tc_id_out[o + k] = scr.tc_id[k]; tc_cnt_out[o + k] = scr.tc_cnt[k]; }
-                        res.taxcnt_begin = (int32_t) o;
-                        res.taxcnt_end = (int32_t) (o + n_tc);
-                    } else *error_flag = 5;
-                }
-                results[r] = res;
+        const u32 r = r0 + lane;
+        if (r < n_reads) {
+            // queryLength = max covered length of each mate (KmerExtractor.cpp:452,476)
+            int ql = max_covered_length((int) lens[2 * r]);
+            if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
+            const u64 b = seg_begin[r], e = seg_end[r];
+            mb_read_result res;
+            int n_tc = 0;
+            ReadScratch scr;
+            if (e > b && (e - b) < 0x7FFFFFFFull) {
+                arena_carve(arena, slot, b, (int) (e - b), scr);
+                n_tc = score_read(m + b, 0, (int) (e - b), ql, cfg, tax, scr, res, error_flag);
+            } else {
+                if (e > b) *error_flag = 4;
+                res.classification = 0; res.score = 0.f; res.is_classified = 0; res.query_length = ql;
+                res.hamming_dist = 0; res.taxcnt_begin = 0; res.taxcnt_end = 0; res.n_matches = (int32_t) (e - b);
             }
+            if (n_tc > 0) {
+                const u64 o = atomicAdd(tc_counter, (unsigned long long) n_tc);
+                if (o + (u64) n_tc <= tc_cap) {
+                    for (int k = 0; k < n_tc; ++k) { tc_id_out[o + k] = scr.tc_id[k]; tc_cnt_out[o + k] = scr.tc_cnt[k]; }
+                    res.taxcnt_begin = (int32_t) o;
+                    res.taxcnt_end = (int32_t) (o + n_tc);
+                } else *error_flag = 5;
+            }
+            results[r] = res;
         }
         __syncwarp();
     }

@@ -52,6 +52,13 @@ void build_tables(Tables &t) {
             const int idx = a * 8 + b;
             t.ham4[idx >> 4] |= (u64) H[a][b] << ((idx & 15) * 4);
         }
+    for (int qp = 0; qp < 64; ++qp)
+        for (int tp = 0; tp < 64; ++tp) {
+            const int c0 = H[qp & 7][tp & 7], c1 = H[qp >> 3][tp >> 3];
+            const int v0 = c0 & 3, v1 = c1 & 3;
+            t.lut2[qp << 6 | tp] = (u8) (c0 + c1);
+            t.lutp[qp << 6 | tp] = (u8) ((v0 | v1 << 2) | ((v1 | v0 << 2) << 4));
+        }
 }
 
 } // namespace mb

@@ -1,0 +1,26 @@
+"""Summarise an ncu --page raw --csv dump (stdin): the metrics DESIGN.md / profiles cite, per launch."""
+import csv, sys
+rows = list(csv.reader(sys.stdin))
+hdr, units = rows[0], rows[1]
+want = ['Kernel Name', 'gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
+        'sm__warps_active.avg.pct_of_peak_sustained_active', 'launch__registers_per_thread', 'launch__occupancy_limit_registers',
+        'launch__occupancy_limit_shared_mem', 'launch__occupancy_limit_warps', 'smsp__inst_executed.sum',
+        'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'smsp__issue_active.avg.pct_of_peak_sustained_active',
+        'smsp__thread_inst_executed_per_inst_executed.ratio', 'launch__grid_size',
+        'l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum', 'l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum',
+        'l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum', 'l1tex__t_requests_pipe_lsu_mem_global_op_st.sum',
+        'lts__t_sector_hit_rate.pct']
+want += [h for h in hdr if 'warp_issue_stalled' in h and h.endswith('_per_warp_active.pct')]
+for r in rows[2:]:
+    print('-----')
+    for w in want:
+        if w in hdr:
+            i = hdr.index(w)
+            v = r[i]
+            try:
+                if 'stalled' in w and float(v) < 3:
+                    continue
+            except ValueError:
+                pass
+            print(w.replace('smsp__warp_issue_stalled_', 'stall_').replace('_per_warp_active.pct', ''), v, units[i])

@@ -67,6 +67,15 @@ void emu_hamming(const uint64_t *q, const uint64_t *t, const uint8_t *reverse, s
     }
 }
 
+// the two-codon table forms the match kernel uses
+void emu_hamming_lut(const uint64_t *q, const uint64_t *t, const uint8_t *reverse, size_t n, uint8_t *sum, uint16_t *packed) {
+    init();
+    for (size_t i = 0; i < n; ++i) {
+        sum[i] = (uint8_t) hamming_sum_lut(g_t.lut2, q[i], t[i]);
+        packed[i] = (uint16_t) hamming_pack_lut(g_t.lutp, q[i], t[i], reverse[i] != 0);
+    }
+}
+
 int32_t emu_lca(const int32_t *parent, const int32_t *depth, int32_t max_taxid, int32_t node0, int32_t a, int32_t b) {
     TaxView tv;
     tv.parent = parent; tv.depth = depth; tv.species_of = nullptr; tv.species_rank_of = nullptr;

@@ -82,6 +82,7 @@ def emu_lib():
     L.emu_extract.restype = sz
     L.emu_extract.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, u32, vp, sz]
     L.emu_hamming.argtypes = [vp, vp, vp, sz, vp, vp]
+    L.emu_hamming_lut.argtypes = [vp, vp, vp, sz, vp, vp]
     L.emu_lca.restype = i32
     L.emu_lca.argtypes = [vp, vp, i32, i32, i32, i32]
     L.emu_score.restype = C.c_int64

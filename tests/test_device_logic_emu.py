@@ -59,7 +59,26 @@ def test_hamming_tables(golden, emu, case):
     emu.emu_hamming(_ptr(q), _ptr(t), _ptr(rev), len(m), _ptr(s), _ptr(pk))
     assert np.array_equal(s, m["hamming"])
     assert np.array_equal(pk, m["rightEndHamming"])
+    s2, pk2 = np.zeros_like(s), np.zeros_like(pk)
+    emu.emu_hamming_lut(_ptr(q), _ptr(t), _ptr(rev), len(m), _ptr(s2), _ptr(pk2))
+    assert np.array_equal(s2, m["hamming"])
+    assert np.array_equal(pk2, m["rightEndHamming"])
     db.close()
+
+
+def test_hamming_two_codon_tables_exhaustive(emu):
+    """The two-codon tables of the match kernel equal the cell-by-cell functions on random 24-bit pairs, both orientations."""
+    rng = np.random.default_rng(3)
+    n = 200000
+    q = rng.integers(0, 1 << 24, size=n, dtype=np.uint64)
+    t = rng.integers(0, 1 << 24, size=n, dtype=np.uint64)
+    for r in (0, 1):
+        rev = np.full(n, r, dtype=np.uint8)
+        s1, p1 = np.zeros(n, dtype=np.uint8), np.zeros(n, dtype=np.uint16)
+        s2, p2 = np.zeros(n, dtype=np.uint8), np.zeros(n, dtype=np.uint16)
+        emu.emu_hamming(_ptr(q), _ptr(t), _ptr(rev), n, _ptr(s1), _ptr(p1))
+        emu.emu_hamming_lut(_ptr(q), _ptr(t), _ptr(rev), n, _ptr(s2), _ptr(p2))
+        assert np.array_equal(s1, s2) and np.array_equal(p1, p2)
 
 
 def test_hamming_lut_quirk(emu):
