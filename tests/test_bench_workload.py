@@ -1,0 +1,44 @@
+"""bench_workload.py writes the bench database straight in the on-disk format; its writer must agree byte for byte
+with the oracle's restatement of IndexCreator::writeTargetFilesAndSplits / getDiffIdx (which the reference reader pins)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+@pytest.mark.parametrize("n,split", [(50000, 64), (5000, 4096), (300000, 4096)])
+def test_db_writer_matches_oracle_writer(tmp_path, n, split):
+    import bench_workload as W
+    rng = np.random.default_rng(n)
+    aa = np.sort(rng.integers(0, 1 << 40, size=n // 3, dtype=np.uint64))
+    v = np.unique((rng.choice(aa, size=n) << np.uint64(24)) | rng.integers(0, 1 << 24, size=n, dtype=np.uint64))
+    v = np.sort(np.concatenate([v, v[::7]]))                      # repeated values: one entry per (value, species)
+    t = rng.integers(1, 100, size=len(v)).astype(np.uint32)
+    d1, d2 = str(tmp_path / "a"), str(tmp_path / "b")
+    os.makedirs(d1), os.makedirs(d2)
+    assert orc.lib().orc_write_db_files(d1.encode(), orc._ptr(v), orc._ptr(t), len(v), split, 2) == 0
+
+    class Tax:
+        genome_tax = np.array([5, 6])
+    db = {"values": torch.from_numpy(v.view(np.int64)), "info": torch.from_numpy(t.astype(np.int64))}
+    W.write_db_dir(d2, db, Tax(), split_num=split)
+    for f in ("diffIdx", "info", "split"):
+        assert open(os.path.join(d1, f), "rb").read() == open(os.path.join(d2, f), "rb").read(), f
+
+
+def test_taxonomy_tables_follow_reference_rules():
+    import bench
+    import bench_workload as W
+    tax = W.Taxonomy(*bench.taxonomy_shape(100))
+    assert len(tax.strain) == 100 and len(tax.species) == 100
+    for st in tax.strain[:10]:
+        sp = tax.parent[st]
+        assert tax.rank[sp] == "species" and tax.species_rank_of[st] == sp and tax.species_of[st] == sp
+    assert tax.species_rank_of[tax.genus[0]] == tax.genus[0]      # above species: the taxon itself (TaxonomyWrapper.cpp:479-498)
