@@ -11,6 +11,7 @@
 #include "mb_radix.cuh"
 #include "mb_match.cuh"
 #include "mb_score.cuh"
+#include "mb_segsort.cuh"
 
 #include <cuda_runtime.h>
 
@@ -52,17 +53,19 @@ struct Counters {                 // device-side scalars, one allocation
     u32 score_ticket;
     u32 radix_ticket;
     u32 match_ticket;
+    u32 seg_ticket;
+    u32 seg_too_long;
     u32 trivial[RS_MAX_PASSES];
 };
 
 // kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
-       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SCORE,
+       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE,
        KID_COUNT };
 const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract<write>",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
-                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_score"};
+                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score"};
 struct KSample { int kid; cudaEvent_t a, b; };
 
 } // namespace
@@ -105,6 +108,7 @@ struct mb_ctx {
     std::vector<KSample> samples;     // event pairs of the current batch
     size_t n_samples = 0;
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
+    bool segments_valid = false;      // seg_begin/seg_end describe matches_a
 
     Counters *dcnt() const { return counters.as<Counters>(); }
 };
@@ -509,6 +513,7 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
     if (ctx->max_taxid < 0) return fail(ctx, MB_E_ARG, "mb_load_taxonomy first");
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
+    ctx->segments_valid = false;
     ctx->n_matches = 0;
     if (ctx->n_blocks && ctx->n_kmers) {
         const u32 nb = ctx->n_blocks;
@@ -561,13 +566,61 @@ static MatchKey match_key(const mb_ctx *ctx) {
     return k;
 }
 
+// per-read segments [seg_begin, seg_end) of the match list (which must be grouped by read): Classifier.cpp:174-185
+static int compute_segments(mb_ctx *ctx) {
+    const u32 nr = ctx->n_reads;
+    CK(ctx->seg_begin.ensure((size_t) std::max<u32>(nr, 1) * sizeof(u64)));
+    CK(ctx->seg_end.ensure((size_t) std::max<u32>(nr, 1) * sizeof(u64)));
+    if (nr) {
+        CK(cudaMemsetAsync(ctx->seg_begin.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
+        CK(cudaMemsetAsync(ctx->seg_end.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
+    }
+    if (ctx->n_matches && nr)
+        KL(KID_SEGMENT, k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
+            ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seq_base, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>()));
+    ctx->segments_valid = true;
+    return MB_OK;
+}
+
 int mb_sort_matches(mb_ctx *ctx) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
     CK(cudaSetDevice(ctx->par.device));
     const MatchKey key = match_key(ctx);
-    const int passes = (key.total_bits() + 7) / 8;
-    if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST)) return rc;
+    ctx->segments_valid = false;
+    bool done = false;
+    SegKey sk;
+    sk.pos_bits = key.pos_bits; sk.sp_bits = key.sp_bits;
+    // Short reads: group by read with radix passes on the sequence ID alone, then order every read's segment in
+    // shared memory (mb_segsort.cuh).  Long reads have segments of thousands of matches: full-key radix sort.
+    if (ctx->par.seq_mode != 3 && sk.total_bits() <= 64 && ctx->have_reads && ctx->n_matches && ctx->n_reads) {
+        MatchSeqKey qk;
+        qk.seq_base = ctx->seq_base;
+        const int seq_passes = (key.seq_bits + 7) / 8;
+        if (int rc = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST)) return rc;
+        if (int rc = compute_segments(ctx)) return rc;
+        CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
+        CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 2 * sizeof(u32), ctx->stream));
+        static bool attr_set = false;
+        if (!attr_set) {
+            CK(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
+            attr_set = true;
+        }
+        const unsigned grid = (unsigned) std::min<u64>(148ull * 2, ((u64) ctx->n_reads + 63) / 64);
+        KL(KID_SEGSORT, k_sort_segments<<<grid, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+            ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
+            &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long));
+        u32 too_long = 0;
+        if (int rc = read_back(ctx, &ctx->dcnt()->seg_too_long, &too_long)) return rc;
+        std::swap(ctx->matches_a.p, ctx->matches_b.p);
+        std::swap(ctx->matches_a.cap, ctx->matches_b.cap);
+        done = too_long == 0;      // otherwise some read has more matches than a segment buffer: fall through
+    }
+    if (!done) {
+        ctx->segments_valid = false;
+        const int passes = (key.total_bits() + 7) / 8;
+        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST)) return rc;
+    }
     mark(ctx, EV_SORTM);
     ctx->matches_sorted = true;
     return MB_OK;
@@ -581,18 +634,12 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
     const u32 nr = ctx->n_reads;
     ctx->tc_used = 0;
     if (nr) {
-        CK(ctx->seg_begin.ensure((size_t) nr * sizeof(u64)));
-        CK(ctx->seg_end.ensure((size_t) nr * sizeof(u64)));
         CK(ctx->results.ensure((size_t) nr * sizeof(mb_read_result)));
-        CK(cudaMemsetAsync(ctx->seg_begin.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
-        CK(cudaMemsetAsync(ctx->seg_end.p, 0, (size_t) nr * sizeof(u64), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->tc_count, 0, sizeof(unsigned long long), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->score_ticket, 0, sizeof(u32), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
-        if (ctx->n_matches) {
-            KL(KID_SEGMENT, k_segment_matches<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
-                ctx->matches_a.as<mb_match>(), ctx->n_matches, nr, ctx->seq_base, ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>()));
-        }
+        if (!ctx->segments_valid)
+            if (int rc = compute_segments(ctx)) return rc;
         ScoreCfg cfg;
         cfg.format = ctx->par.kmer_format;
         if (ctx->par.syncmer) { cfg.dna_shift = (8 - ctx->par.smer_len) * 3; cfg.max_codon_shift = 8 - ctx->par.smer_len; }
@@ -724,6 +771,7 @@ static int set_matches(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind ki
     ctx->n_matches = n;
     ctx->have_matches = true;
     ctx->matches_sorted = false;
+    ctx->segments_valid = false;
     ctx->have_results = false;
     return MB_OK;
 }
