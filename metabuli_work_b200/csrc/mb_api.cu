@@ -603,13 +603,19 @@ int mb_sort_matches(mb_ctx *ctx) {
         CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 2 * sizeof(u32), ctx->stream));
         static bool attr_set = false;
         if (!attr_set) {
-            CK(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_sort_segments<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_sort_segments<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
             attr_set = true;
         }
         const unsigned grid = (unsigned) std::min<u64>(148ull * 2, ((u64) ctx->n_reads + 63) / 64);
-        KL(KID_SEGSORT, k_sort_segments<<<grid, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
-            ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
-            &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long));
+        if (sk.total_bits() <= 55)
+            KL(KID_SEGSORT, k_sort_segments<true><<<grid, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
+                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long));
+        else
+            KL(KID_SEGSORT, k_sort_segments<false><<<grid, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
+                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long));
         u32 too_long = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->seg_too_long, &too_long)) return rc;
         std::swap(ctx->matches_a.p, ctx->matches_b.p);

@@ -26,14 +26,122 @@ struct SegKey {                                 // the compareMatches key below 
         k = (k << 24) | (dna & 0xFFFFFFu);
         return k;
     }
-    int total_bits() const { return sp_bits + 3 + pos_bits + 3 + 24; }
+    __host__ __device__ int total_bits() const { return sp_bits + 3 + pos_bits + 3 + 24; }
 };
+
+// branch-free selects (the compiler otherwise turns the conditional exchanges into divergent branches)
+__device__ __forceinline__ u64 sel64(bool p, u64 a, u64 b) {
+    u64 r;
+    asm("{.reg .pred q; setp.ne.u32 q, %3, 0; selp.b64 %0, %1, %2, q;}" : "=l"(r) : "l"(a), "l"(b), "r"((u32) p));
+    return r;
+}
+__device__ __forceinline__ u32 sel32(bool p, u32 a, u32 b) {
+    u32 r;
+    asm("{.reg .pred q; setp.ne.u32 q, %3, 0; selp.b32 %0, %1, %2, q;}" : "=r"(r) : "r"(a), "r"(b), "r"((u32) p));
+    return r;
+}
+
+// Bitonic sort of the first n_pad (a power of two <= ITEMS*32) elements held in registers by one warp; element
+// e = i*32 + lane (striped), so partners less than 32 apart are exchanged with shuffles and the others are
+// register-to-register.  PACKED keys carry the source index in their low 9 bits (possible when the compareMatches
+// key needs at most 55 bits): one 64-bit compare per exchange; otherwise ties on the key are broken by src[].
+// Either way the order is total and equals a stable sort of the input order.  The stage loops stay rolled (a fully
+// unrolled network is larger than the instruction cache); only the per-register loop is unrolled.
+template <int ITEMS, int DJ, bool PACKED>
+__device__ __forceinline__ void bitonic_in_lane(u64 (&k)[ITEMS], u32 (&src)[ITEMS], int kk) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        if ((i & DJ) == 0 && (i | DJ) < ITEMS) {
+            const int p = i | DJ;
+            {
+                const bool up = ((i * 32) & kk) == 0;
+                const u64 a = k[i], c = k[p];
+                const bool a_gt = PACKED ? a > c : (a > c || (a == c && src[i] > src[p]));
+                const bool sw = a_gt == up;
+                k[i] = sel64(sw, c, a);
+                k[p] = sel64(sw, a, c);
+                if (!PACKED) { const u32 sa = src[i], sc = src[p]; src[i] = sel32(sw, sc, sa); src[p] = sel32(sw, sa, sc); }
+            }
+        }
+    }
+}
+
+template <int ITEMS, bool PACKED>
+__device__ __forceinline__ void warp_bitonic(u64 (&k)[ITEMS], u32 (&src)[ITEMS], int n_pad) {
+    const u32 lane = threadIdx.x & 31;
+#pragma unroll 1
+    for (int kk = 2; kk <= n_pad; kk <<= 1) {
+#pragma unroll 1
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+            if (j < 32) {
+                const bool lower = (lane & j) == 0;
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i) {
+                    {
+                        const u64 ok = __shfl_xor_sync(0xFFFFFFFFu, k[i], j);
+                        const bool up = kk < 32 ? (lane & kk) == 0 : ((i * 32) & kk) == 0;   // kk == 32: bit 5 of e = bit 0 of i
+                        bool other_less = ok < k[i];
+                        if (!PACKED) {
+                            const u32 os = __shfl_xor_sync(0xFFFFFFFFu, src[i], j);
+                            other_less = other_less || (ok == k[i] && os < src[i]);
+                            const bool take = (lower == up) == other_less;
+                            src[i] = sel32(take, os, src[i]);
+                            k[i] = sel64(take, ok, k[i]);
+                        } else {
+                            const bool take = (lower == up) == other_less;      // packed keys never tie
+                            k[i] = sel64(take, ok, k[i]);
+                        }
+                    }
+                }
+            } else {
+                switch (j >> 5) {
+                    case 1: bitonic_in_lane<ITEMS, 1, PACKED>(k, src, kk); break;
+                    case 2: bitonic_in_lane<ITEMS, 2, PACKED>(k, src, kk); break;
+                    case 4: bitonic_in_lane<ITEMS, 4, PACKED>(k, src, kk); break;
+                    default: bitonic_in_lane<ITEMS, 8, PACKED>(k, src, kk); break;
+                }
+            }
+        }
+    }
+}
+
+// Sort one segment of n <= ITEMS*32 records with the register network and write it in order.
+template <int ITEMS, bool PACKED>
+__device__ __forceinline__ void sort_segment_regs(const u64 *__restrict__ in64, u64 *__restrict__ out64, u64 b, u32 n, const SegKey &sk) {
+    const u32 lane = threadIdx.x & 31;
+    u64 k[ITEMS];
+    u32 src[ITEMS];
+    int n_pad = 32;
+    while ((u32) n_pad < n) n_pad <<= 1;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const u32 e = i * 32 + lane;
+        k[i] = ~0ull;
+        src[i] = e;
+        if (e < n) {
+            const u64 w0 = __ldg(in64 + (b + e) * 3), w1 = __ldg(in64 + (b + e) * 3 + 1), w2 = __ldg(in64 + (b + e) * 3 + 2);
+            const u64 key = sk.key(w0, (u32) (w1 >> 32), (u32) w2, (u32) (w2 >> 48));
+            k[i] = PACKED ? ((key << 9) | e) : key;
+        }
+    }
+    warp_bitonic<ITEMS, PACKED>(k, src, n_pad);
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const u32 e = i * 32 + lane;
+        if (e < n) {
+            const u64 s = b + (PACKED ? (u32) (k[i] & 511u) : src[i]);
+            const u64 w0 = __ldg(in64 + s * 3), w1 = __ldg(in64 + s * 3 + 1), w2 = __ldg(in64 + s * 3 + 2);
+            out64[(b + e) * 3] = w0; out64[(b + e) * 3 + 1] = w1; out64[(b + e) * 3 + 2] = w2;
+        }
+    }
+}
 
 constexpr size_t segsort_smem_bytes() { return (size_t) SS_WARPS * SS_CAP * (sizeof(u64) + sizeof(u16)); }
 
 // One warp per read segment [seg_begin[r], seg_end[r]) of `in` (grouped by read); sorted records go to the same
 // range of `out`.  Segments longer than SS_CAP are copied unsorted and counted in *too_long (the host then takes
 // the full radix path).
+template <bool PACKED>
 __global__ void __launch_bounds__(SS_THREADS)
 k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, const u64 *__restrict__ seg_begin,
                 const u64 *__restrict__ seg_end, u32 n_reads, SegKey sk, u32 *ticket, u32 *too_long) {
@@ -58,36 +166,12 @@ k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, con
                 for (u64 i = lane; i < (u64) n * 3; i += 32) out64[b * 3 + i] = in64[b * 3 + i];
                 continue;
             }
-            if (n <= 32) {
-                // register path: one record per lane, bitonic network over the warp with shuffles
-                u64 k = ~0ull;
-                u64 w0 = 0, w1 = 0, w2 = 0;
-                if (lane < n) {
-                    w0 = __ldg(in64 + (b + lane) * 3); w1 = __ldg(in64 + (b + lane) * 3 + 1); w2 = __ldg(in64 + (b + lane) * 3 + 2);
-                    k = sk.key(w0, (u32) (w1 >> 32), (u32) w2, (u32) (w2 >> 48));
-                }
-                u32 src = lane;
-#pragma unroll
-                for (int kk = 2; kk <= 32; kk <<= 1) {
-#pragma unroll
-                    for (int j = kk >> 1; j > 0; j >>= 1) {
-                        const u64 ok = __shfl_xor_sync(0xFFFFFFFFu, k, j);
-                        const u32 os = __shfl_xor_sync(0xFFFFFFFFu, src, j);
-                        const bool up = (lane & kk) == 0;
-                        const bool lower = (lane & j) == 0;
-                        const bool other_less = ok < k || (ok == k && os < src);
-                        // the lower lane keeps the smaller element when the run ascends, the larger when it descends
-                        const bool take = (lower == up) ? other_less : !other_less;
-                        if (take) { k = ok; src = os; }
-                    }
-                }
-                // lane now holds the element of rank `lane`; fetch its record from the lane that loaded it
-                const u64 s0 = __shfl_sync(0xFFFFFFFFu, w0, src), s1 = __shfl_sync(0xFFFFFFFFu, w1, src), s2 = __shfl_sync(0xFFFFFFFFu, w2, src);
-                if (lane < n) { out64[(b + lane) * 3] = s0; out64[(b + lane) * 3 + 1] = s1; out64[(b + lane) * 3 + 2] = s2; }
-                continue;
-            }
-            u32 n_pad = 64;
-            while (n_pad < n) n_pad <<= 1;
+            if (n <= 32) { sort_segment_regs<1, PACKED>(in64, out64, b, n, sk); continue; }
+            if (n <= 64) { sort_segment_regs<2, PACKED>(in64, out64, b, n, sk); continue; }
+            if (n <= 128) { sort_segment_regs<4, PACKED>(in64, out64, b, n, sk); continue; }
+            if (n <= 256) { sort_segment_regs<8, PACKED>(in64, out64, b, n, sk); continue; }
+            if (n <= 512) { sort_segment_regs<16, PACKED>(in64, out64, b, n, sk); continue; }
+            u32 n_pad = 1024;
             for (u32 i = lane; i < n_pad; i += 32) {
                 u64 k = ~0ull;
                 if (i < n) {
