@@ -55,17 +55,19 @@ struct Counters {                 // device-side scalars, one allocation
     u32 match_ticket;
     u32 seg_ticket;
     u32 seg_too_long;
+    u32 slow_count;
+    u32 slow_ticket;
     u32 trivial[RS_MAX_PASSES];
 };
 
 // kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
-       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE,
+       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE_FAST, KID_SCORE,
        KID_COUNT };
 const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract<write>",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
-                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score"};
+                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score_fast", "k_score"};
 struct KSample { int kid; cudaEvent_t a, b; };
 
 } // namespace
@@ -96,6 +98,7 @@ struct mb_ctx {
     DevBuf qstart, matches_a, matches_b;
     u64 n_matches = 0;
     DevBuf seg_begin, seg_end, results, tc_id, tc_cnt, arena;
+    DevBuf slow_list;
     DevBuf sc_local, sc_paths, sc_comb, sc_linked, sc_spid, sc_spscore;   // per-match scoring scratch
     u64 tc_used = 0;
     DevBuf counters;
@@ -680,10 +683,25 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         const size_t tc_cap = std::max<size_t>(ctx->n_matches, 16);
         CK(ctx->tc_id.ensure(tc_cap * sizeof(int32_t)));
         CK(ctx->tc_cnt.ensure(tc_cap * sizeof(int32_t)));
-        KL(KID_SCORE, k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(),
-                                                    ctx->lens.as<u32>(), nr, ctx->par.seq_mode == 2 ? 1 : 0, cfg, tv, arena,
-                                                    ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(),
-                                                    (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag));
+        const int paired = ctx->par.seq_mode == 2 ? 1 : 0;
+        if (ctx->par.seq_mode != 3) {
+            // short reads: streaming scorer first; what it cannot hold goes to the general kernel through slow_list
+            CK(ctx->slow_list.ensure((size_t) nr * sizeof(u32)));
+            CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 2 * sizeof(u32), ctx->stream));
+            KL(KID_SCORE_FAST, k_score_fast<<<grid, SC_THREADS, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
+                ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
+                &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
+            KL(KID_SCORE, k_score<<<std::min<unsigned>(grid, 148u * 4), SC_THREADS, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
+                ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
+                &ctx->dcnt()->slow_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
+        } else {
+            KL(KID_SCORE, k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
+                ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
+                &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag, nullptr, nullptr));
+        }
         unsigned long long used = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->tc_count, &used)) return rc;
         u32 flag = 0;

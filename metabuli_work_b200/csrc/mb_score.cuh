@@ -364,13 +364,10 @@ MB_HD BestSpecies best_species(const mb_match *m, int b, int e, int query_length
     return out;
 }
 
-// Scores one read.  Returns the number of taxCnt entries left in scr.tc_id / scr.tc_cnt.
-MB_HD int score_read(const mb_match *m, int b, int e, int query_length, const ScoreCfg &cfg, const TaxView &tax,
-                     ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
-    r.classification = 0; r.score = 0.f; r.is_classified = 0; r.query_length = query_length;
-    r.hamming_dist = 0; r.taxcnt_begin = 0; r.taxcnt_end = 0; r.n_matches = e - b;
-    if (e <= b) return 0;
-    const BestSpecies best = best_species(m, b, e, query_length, cfg, tax, scr);
+// Everything of Taxonomer::chooseBestTaxon after getBestSpeciesMatches.  Returns the number of taxCnt entries left
+// in scr.tc_id / scr.tc_cnt.
+MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_length, const ScoreCfg &cfg, const TaxView &tax,
+                      ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
     // Taxonomer::chooseBestTaxon (Taxonomer.cpp:130-202), em == false
     if (best.score == 0.f || best.score < cfg.min_score) { r.score = best.score; return 0; }
     if (best.lca) { r.is_classified = 1; r.classification = best.tax; r.score = best.score; return 0; }
@@ -455,6 +452,215 @@ MB_HD int score_read(const mb_match *m, int b, int e, int query_length, const Sc
     return n_tc;
 }
 
+MB_HD void result_init(mb_read_result &r, int query_length, int n_matches) {
+    r.classification = 0; r.score = 0.f; r.is_classified = 0; r.query_length = query_length;
+    r.hamming_dist = 0; r.taxcnt_begin = 0; r.taxcnt_end = 0; r.n_matches = n_matches;
+}
+
+// Scores one read (general form: any number of matches, paths and species; scratch sized by the match count).
+MB_HD int score_read(const mb_match *m, int b, int e, int query_length, const ScoreCfg &cfg, const TaxView &tax,
+                     ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
+    result_init(r, query_length, e - b);
+    if (e <= b) return 0;
+    const BestSpecies best = best_species(m, b, e, query_length, cfg, tax, scr);
+    return finish_read(m, best, query_length, cfg, tax, scr, r, error_flag);
+}
+
+// ---- streaming form -------------------------------------------------------------------------------------
+// The same computation as best_species() + match_paths() + combine_paths(), restated as ONE loop over the read's
+// sorted matches with a bounded state, so that the 32 reads a warp scores in parallel run the same instruction
+// stream (the nested while-loops of the general form serialise the lanes).  State: the two position groups of
+// the path DP (Taxonomer.cpp:487-648 only ever links a position group to the one before it), the paths of the
+// current species and the species that scored.  When a bound is exceeded the read is left to the general form.
+constexpr int SF_G = 4;      // matches per (species, frame, position) group
+constexpr int SF_P = 16;     // paths per species: also the size below which std::sort is a plain insertion sort
+constexpr int SF_S = 16;     // species with a score per read
+
+struct FastGroup {
+    PathRec p[SF_G];
+    u32 dna[SF_G];
+    u32 linked;              // bit k: entry k was extended
+    int n;
+    u32 pos;
+};
+
+struct FastState {
+    FastGroup g[2];
+    PathRec paths[SF_P];
+    PathRec comb[SF_P];
+    int32_t sp_id[SF_S];
+    float sp_score[SF_S];
+};
+
+// combineMatchPaths on at most SF_P paths (insertion sort == libstdc++ std::sort for n <= 16)
+MB_HD float combine_paths_small(const mb_match *m, PathRec *paths, PathRec *comb, int n_paths, int read_length) {
+    ReadScratch tmp;
+    tmp.paths = paths; tmp.combined = comb;
+    return combine_paths(m, tmp, n_paths, read_length);
+}
+
+MB_HD bool best_species_fast(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, FastState &st,
+                             BestSpecies &out) {
+    out.tax = 0; out.score = 0.f; out.lca = false; out.rb = 0; out.re = 0;
+    int n_sp = 0, meaningful = 0, n_paths = 0;
+    float best_sp = 0.f;
+    int32_t species = 0;
+    u32 frame = 0;
+    int sp_begin = 0, min_depth = cfg.min_cons_cnt;
+    int cur = 0;                 // st.g[cur] = previous position group, st.g[cur ^ 1] = the group being filled
+    bool have_cur = false, started = false, forward = true, overflow = false;
+
+    for (int i = 0; i <= n; ++i) {
+        const bool at_end = i == n;
+        u64 qinfo = 0;
+        int32_t sp = 0;
+        u32 dna = 0, reh = 0, ham = 0;
+        if (!at_end) {
+            const u64 *w = reinterpret_cast<const u64 *>(m + i);
+            const u64 w0 = w[0], w1 = w[1], w2 = w[2];
+            qinfo = w0; sp = (int32_t) (w1 >> 32); dna = (u32) w2 & 0xFFFFFFu; reh = (u32) (w2 >> 32) & 0xFFFFu; ham = (u32) (w2 >> 48) & 0xFFu;
+        }
+        const u32 fr = qi_frame(qinfo), pos = qi_pos(qinfo);
+        const bool new_species = at_end || i == 0 || sp != species;
+        const bool new_frame = new_species || fr != frame;
+        if (new_frame && i > 0) {
+            // ---- end of a (species, frame) group: the last transition's emissions (Taxonomer.cpp:631-646) ----
+            if (have_cur) {
+                const FastGroup &a = st.g[cur], &b = st.g[cur ^ 1];
+                for (int c = 0; c < a.n; ++c)
+                    if (!((a.linked >> c) & 1u) && a.p[c].depth >= min_depth) {
+                        if (n_paths < SF_P) st.paths[n_paths] = a.p[c]; else overflow = true;
+                        ++n_paths;
+                    }
+                for (int c = 0; c < b.n; ++c)
+                    if (b.p[c].depth >= min_depth) {
+                        if (n_paths < SF_P) st.paths[n_paths] = b.p[c]; else overflow = true;
+                        ++n_paths;
+                    }
+            }
+            if (new_species) {
+                // ---- end of a species (Taxonomer.cpp:357-376) ----
+                if (n_paths > 0 && !overflow) {
+                    float score = combine_paths_small(m, st.paths, st.comb, n_paths, query_length);
+                    score = score < 1.0f ? score : 1.0f;
+                    if (!(score < cfg.min_score)) {
+                        if (n_sp < SF_S) { st.sp_id[n_sp] = species; st.sp_score[n_sp] = score; } else overflow = true;
+                        ++n_sp;
+                        if (score > 0.f) ++meaningful;
+                        if (score > best_sp) { best_sp = score; out.rb = sp_begin; out.re = i; }
+                    }
+                }
+                n_paths = 0;
+            }
+        }
+        if (at_end || overflow) break;
+        if (new_species) {
+            species = sp; sp_begin = i;
+            min_depth = tax_is_ancestor(tax, tax.eukaryota, species) ? cfg.min_cons_cnt_euk : cfg.min_cons_cnt;
+        }
+        if (new_frame) {
+            frame = fr; forward = fr < 3;
+            have_cur = false; started = false;
+            st.g[0].n = 0; st.g[1].n = 0; st.g[0].linked = 0; st.g[1].linked = 0;
+            cur = 0;
+        }
+        FastGroup *fill = &st.g[cur ^ 1];
+        if (!started) { started = true; fill->pos = pos; }
+        if (pos != fill->pos) {
+            // the group being filled is complete: emit the unlinked paths of the group before it, then rotate
+            if (have_cur) {
+                const FastGroup &a = st.g[cur];
+                for (int c = 0; c < a.n; ++c)
+                    if (!((a.linked >> c) & 1u) && a.p[c].depth >= min_depth) {
+                        if (n_paths < SF_P) st.paths[n_paths] = a.p[c]; else overflow = true;
+                        ++n_paths;
+                    }
+            }
+            cur ^= 1;
+            have_cur = true;
+            fill = &st.g[cur ^ 1];
+            fill->n = 0; fill->linked = 0; fill->pos = pos;
+        }
+        // path_init (Taxonomer.h:39-46)
+        PathRec t;
+        t.start = (int) pos; t.end = (int) pos + 23; t.ham = (int) ham; t.depth = 1; t.sm = i; t.em = i;
+        {
+            float sc = 0.f;
+            for (int k = 0; k < 8; ++k) sc += codon_score((reh >> (2 * k)) & 3u);
+            t.score = sc;
+        }
+        if (have_cur) {
+            FastGroup &a = st.g[cur];
+            const int shift = (int) ((pos - a.pos) / 3);
+            if (shift > 0 && shift <= cfg.max_codon_shift) {
+                float inc = 0.f;
+                int hinc = 0;
+                for (int k = 0; k < shift; ++k) {
+                    const u32 h = (reh >> (2 * k)) & 3u;
+                    inc += codon_score(h);
+                    hinc += (int) h;
+                }
+                const u32 keep = (1u << (24 - 3 * shift)) - 1u;
+                int best = -1;
+                float best_score = 0.f;
+                for (int c = 0; c < a.n; ++c) {
+                    // isConsecutive(cur, next) forward, isConsecutive(next, cur) reverse (Taxonomer.cpp:671-699)
+                    const u32 x = forward ? a.dna[c] : dna, y = forward ? dna : a.dna[c];
+                    const bool ok = cfg.format == 2 ? (x & keep) == (y >> (3 * shift)) : (x >> (3 * shift)) == (y & keep);
+                    if (ok) {
+                        a.linked |= 1u << c;
+                        if (a.p[c].score > best_score) { best = c; best_score = a.p[c].score; }
+                    }
+                }
+                if (best >= 0) {
+                    const PathRec &bp = a.p[best];
+                    t.start = bp.start; t.score = bp.score + inc; t.ham = bp.ham + hinc; t.depth = bp.depth + shift; t.sm = bp.sm;
+                }
+            }
+        }
+        if (fill->n < SF_G) { fill->p[fill->n] = t; fill->dna[fill->n] = dna; } else overflow = true;
+        ++fill->n;
+    }
+    if (overflow) return false;
+    if (meaningful == 0) { out.score = 0.f; return true; }
+    // species within tie_ratio of the best (Taxonomer.cpp:388-402)
+    int n_top = 0;
+    int32_t lca = 0;
+    bool have = false;
+    int32_t single = 0;
+    const float cut = best_sp * cfg.tie_ratio;
+    for (int k = 0; k < n_sp; ++k) {
+        if (st.sp_score[k] >= cut) {
+            const int32_t t = st.sp_id[k];
+            if (n_top == 0) single = t;
+            ++n_top;
+            out.score += st.sp_score[k];
+            if (tax_exists(tax, t)) {
+                if (!have) { lca = t; have = true; }
+                else lca = tax_lca_existing(tax, lca, t);
+            }
+        }
+    }
+    if (n_top > 1) {
+        out.lca = true;
+        out.tax = have ? lca : 0;
+        out.score /= (float) n_top;
+        return true;
+    }
+    out.tax = single;
+    return true;
+}
+
+// Streaming scorer.  Returns -1 when a bound of the streaming state was exceeded (the caller then uses score_read).
+MB_HD int score_read_fast(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, FastState &st,
+                          ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
+    result_init(r, query_length, n);
+    if (n <= 0) return 0;
+    BestSpecies best;
+    if (!best_species_fast(m, n, query_length, cfg, tax, st, best)) return -1;
+    return finish_read(m, best, query_length, cfg, tax, scr, r, error_flag);
+}
+
 #if defined(__CUDACC__)
 // ---- segmentation of the sorted match list by read (Classifier.cpp:174-185) ----------------------------
 __global__ void k_segment_matches(const mb_match *__restrict__ m, u64 n, u32 n_reads, u32 seq_base, u64 *__restrict__ seg_begin,
@@ -517,24 +723,39 @@ __device__ __forceinline__ void arena_carve(const ScoreArena &a, u64 slot, u64 f
 
 constexpr int SC_THREADS = 128;
 
-// One THREAD per read: a warp takes 32 consecutive reads by an atomic ticket, lane i scores read r0+i.
-// The per-read logic is sequential and branchy (DP over positions, introsort, greedy combine), so the
-// parallelism of this kernel is across reads; the lanes of a warp walk neighbouring slices of the sorted
-// match list.
+// Shared tail of both scoring kernels: copy the read's taxCnt list out and store the result.
+__device__ __forceinline__ void store_result(mb_read_result &res, int n_tc, const ReadScratch &scr, u32 r, mb_read_result *__restrict__ results,
+                                             int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out, u64 tc_cap,
+                                             unsigned long long *tc_counter, u32 *error_flag) {
+    if (n_tc > 0) {
+        const u64 o = atomicAdd(tc_counter, (unsigned long long) n_tc);
+        if (o + (u64) n_tc <= tc_cap) {
+            for (int k = 0; k < n_tc; ++k) { tc_id_out[o + k] = scr.tc_id[k]; tc_cnt_out[o + k] = scr.tc_cnt[k]; }
+            res.taxcnt_begin = (int32_t) o;
+            res.taxcnt_end = (int32_t) (o + n_tc);
+        } else *error_flag = 5;
+    }
+    results[r] = res;
+}
+
+// General form, one THREAD per read.  With `list` == nullptr a warp takes 32 consecutive reads by an atomic ticket;
+// otherwise the reads are list[0 .. *list_count) (the reads the streaming kernel left over).
 __global__ void __launch_bounds__(SC_THREADS)
 k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
         const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
         mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
-        u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag) {
+        u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag, const u32 *__restrict__ list,
+        const u32 *__restrict__ list_count) {
     const u32 lane = threadIdx.x & 31;
     const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
+    const u32 total = list ? *list_count : n_reads;
     while (true) {
         u32 r0 = 0;
         if (lane == 0) r0 = atomicAdd(ticket, 32u);
         r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
-        if (r0 >= n_reads) break;
-        const u32 r = r0 + lane;
-        if (r < n_reads) {
+        if (r0 >= total) break;
+        if (r0 + lane < total) {
+            const u32 r = list ? list[r0 + lane] : r0 + lane;
             // queryLength = max covered length of each mate (KmerExtractor.cpp:452,476)
             int ql = max_covered_length((int) lens[2 * r]);
             if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
@@ -547,18 +768,43 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
                 n_tc = score_read(m + b, 0, (int) (e - b), ql, cfg, tax, scr, res, error_flag);
             } else {
                 if (e > b) *error_flag = 4;
-                res.classification = 0; res.score = 0.f; res.is_classified = 0; res.query_length = ql;
-                res.hamming_dist = 0; res.taxcnt_begin = 0; res.taxcnt_end = 0; res.n_matches = (int32_t) (e - b);
+                result_init(res, ql, (int32_t) (e - b));
             }
-            if (n_tc > 0) {
-                const u64 o = atomicAdd(tc_counter, (unsigned long long) n_tc);
-                if (o + (u64) n_tc <= tc_cap) {
-                    for (int k = 0; k < n_tc; ++k) { tc_id_out[o + k] = scr.tc_id[k]; tc_cnt_out[o + k] = scr.tc_cnt[k]; }
-                    res.taxcnt_begin = (int32_t) o;
-                    res.taxcnt_end = (int32_t) (o + n_tc);
-                } else *error_flag = 5;
+            store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
+        }
+        __syncwarp();
+    }
+}
+
+// Streaming form, one THREAD per read (score_read_fast): the 32 reads of a warp advance through their match lists in
+// lock step.  Reads that exceed a bound of the streaming state are appended to `list` for k_score.
+__global__ void __launch_bounds__(SC_THREADS)
+k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
+             const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
+             mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
+             u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag, u32 *__restrict__ list, u32 *list_count) {
+    const u32 lane = threadIdx.x & 31;
+    const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
+    while (true) {
+        u32 r0 = 0;
+        if (lane == 0) r0 = atomicAdd(ticket, 32u);
+        r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
+        if (r0 >= n_reads) break;
+        const u32 r = r0 + lane;
+        if (r < n_reads) {
+            int ql = max_covered_length((int) lens[2 * r]);
+            if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
+            const u64 b = seg_begin[r], e = seg_end[r];
+            mb_read_result res;
+            ReadScratch scr;
+            int n_tc = -1;
+            if ((e - b) < 0x7FFFFFFFull) {
+                FastState st;
+                arena_carve(arena, slot, 0, 0, scr);
+                n_tc = score_read_fast(m + b, (int) (e - b), ql, cfg, tax, st, scr, res, error_flag);
             }
-            results[r] = res;
+            if (n_tc < 0) list[atomicAdd(list_count, 1u)] = r;
+            else store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
         }
         __syncwarp();
     }

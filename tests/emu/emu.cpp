@@ -83,6 +83,11 @@ int32_t emu_lca(const int32_t *parent, const int32_t *depth, int32_t max_taxid, 
     return tax_lca(tv, a, b);
 }
 
+static int g_fast = 0;
+static long g_fallbacks = 0;
+void emu_set_fast(int on) { g_fast = on; g_fallbacks = 0; }
+long emu_fast_fallbacks() { return g_fallbacks; }
+
 // score all reads of a sorted match list with score_read (mb_score.cuh), like k_score does per warp
 int64_t emu_score(const mb_match *m, size_t n, const uint32_t *lens, uint32_t n_reads, int seq_mode, int format, int syncmer,
                   int smer_len, int min_cons_cnt, int min_cons_cnt_euk, float min_score, float min_sp_score, float tie_ratio,
@@ -127,7 +132,14 @@ int64_t emu_score(const mb_match *m, size_t n, const uint32_t *lens, uint32_t n_
     for (uint32_t r = 0; r < n_reads; ++r) {
         int ql = max_covered_length((int) lens[2 * r]);
         if (seq_mode == 2) ql += max_covered_length((int) lens[2 * r + 1]);
-        const int n_tc = score_read(m + sb[r], 0, (int) (se[r] - sb[r]), ql, cfg, tv, scr, res[r], &err);
+        int n_tc = -1;
+        if (g_fast) {
+            // the streaming form k_score_fast runs; reads it cannot hold fall back to the general form, as on the device
+            FastState st;
+            n_tc = score_read_fast(m + sb[r], (int) (se[r] - sb[r]), ql, cfg, tv, st, scr, res[r], &err);
+            if (n_tc < 0) ++g_fallbacks;
+        }
+        if (n_tc < 0) n_tc = score_read(m + sb[r], 0, (int) (se[r] - sb[r]), ql, cfg, tv, scr, res[r], &err);
         if (n_tc > 0) {
             if (used + (size_t) n_tc > tc_cap) return -1;
             for (int k = 0; k < n_tc; ++k) { tc_id[used + k] = scr.tc_id[k]; tc_cnt[used + k] = scr.tc_cnt[k]; }

@@ -88,6 +88,8 @@ def emu_lib():
     L.emu_score.restype = C.c_int64
     L.emu_score.argtypes = [vp, sz, vp, u32, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
                             C.c_float, vp, vp, vp, vp, i32, i32, i32, vp, vp, vp, sz]
+    L.emu_set_fast.argtypes = [C.c_int]
+    L.emu_fast_fallbacks.restype = C.c_long
     return L
 
 

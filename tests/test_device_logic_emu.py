@@ -95,7 +95,8 @@ def test_hamming_lut_quirk(emu):
 
 @pytest.mark.parametrize("case", CASES)
 @pytest.mark.parametrize("min_sp", [0.0, 0.9])
-def test_score_read_logic(golden, emu, case, min_sp):
+@pytest.mark.parametrize("fast", [0, 1])
+def test_score_read_logic(golden, emu, case, min_sp, fast):
     meta = golden.cases[case]
     db = orc.Db(golden.dbdir(case))
     p = db.params(seq_mode=meta["seq_mode"], min_sp_score=min_sp)
@@ -106,6 +107,7 @@ def test_score_read_logic(golden, emu, case, min_sp):
     out = np.zeros(b.n, dtype=RES_DT)
     tid = np.zeros(len(m) + 16, dtype=np.int32)
     tcn = np.zeros(len(m) + 16, dtype=np.int32)
+    emu.emu_set_fast(fast)
     used = emu.emu_score(_ptr(m), len(m), _ptr(b.len), b.n, p.seq_mode, p.kmer_format, p.syncmer, p.smer_len, p.min_cons_cnt,
                          p.min_cons_cnt_euk, p.min_score, p.min_sp_score, p.tie_ratio, _ptr(parent), _ptr(depth), _ptr(sp_of),
                          _ptr(sp_rank), mx, node0, euk, _ptr(out), _ptr(tid), _ptr(tcn), len(tid))
@@ -120,4 +122,7 @@ def test_score_read_logic(golden, emu, case, min_sp):
                 and a["query_length"] == o["query_length"] and tc_a == tc_o):
             bad.append(i)
     assert bad == []
+    if fast and meta["seq_mode"] != 3:
+        assert emu.emu_fast_fallbacks() * 5 < b.n        # the streaming form holds the typical short read
+    emu.emu_set_fast(0)
     db.close()
