@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -57,6 +58,7 @@ struct Counters {                 // device-side scalars, one allocation
     u32 seg_too_long;
     u32 slow_count;
     u32 slow_ticket;
+    u32 fast_overflow[8];     // reads the compact scorer left to the general kernel, by reason
     u32 trivial[RS_MAX_PASSES];
 };
 
@@ -666,7 +668,9 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         arena.slice_bytes = arena_slice_bytes(arena.cap_b, arena.cap_c);
         // one thread per read; resident threads fill the machine, bounded by a 4-GB arena of per-thread slices
         const u64 budget = 4ull << 30;
-        u64 threads = std::min<u64>(148ull * 2048, std::max<u64>(budget / arena.slice_bytes, SC_THREADS));
+        u64 resident = 148ull * 2048;
+        if (const char *ev = getenv("MB_SCORE_THREADS_PER_SM")) resident = 148ull * (u64) std::max(128, atoi(ev));   // tuning knob
+        u64 threads = std::min<u64>(resident, std::max<u64>(budget / arena.slice_bytes, SC_THREADS));
         threads = std::min<u64>(threads, (u64) nr + SC_THREADS);
         const unsigned grid = (unsigned) std::max<u64>(1, threads / SC_THREADS);
         CK(ctx->arena.ensure((size_t) grid * SC_THREADS * arena.slice_bytes));
@@ -687,12 +691,18 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         if (ctx->par.seq_mode != 3) {
             // short reads: streaming scorer first; what it cannot hold goes to the general kernel through slow_list
             CK(ctx->slow_list.ensure((size_t) nr * sizeof(u32)));
-            CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 2 * sizeof(u32), ctx->stream));
-            KL(KID_SCORE_FAST, k_score_fast<<<grid, SC_THREADS, 0, ctx->stream>>>(
+            CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 10 * sizeof(u32), ctx->stream));
+            const size_t fast_smem = (size_t) SC_THREADS * SC_STRIDE * sizeof(u32);
+            static bool fast_attr = false;
+            if (!fast_attr) {
+                CK(cudaFuncSetAttribute(k_score_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) fast_smem));
+                fast_attr = true;
+            }
+            KL(KID_SCORE_FAST, k_score_fast<<<grid, SC_THREADS, fast_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
                 ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
-                &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
-            KL(KID_SCORE, k_score<<<std::min<unsigned>(grid, 148u * 4), SC_THREADS, 0, ctx->stream>>>(
+                &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count, ctx->dcnt()->fast_overflow));
+            KL(KID_SCORE, k_score<<<std::min<unsigned>(grid, 148u * 8), SC_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
                 ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
                 &ctx->dcnt()->slow_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
@@ -704,6 +714,13 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         }
         unsigned long long used = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->tc_count, &used)) return rc;
+        if (getenv("MB_DEBUG_SCORE") && ctx->par.seq_mode != 3) {
+            u32 why[8];
+            CK(cudaMemcpyAsync(why, ctx->dcnt()->fast_overflow, sizeof(why), cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            fprintf(stderr, "[mb] compact scorer left over: group %u, paths/read %u, species/read %u, paths/species %u, field %u, size %u (of %u reads)\n",
+                    why[1], why[2], why[3], why[4], why[5], why[6], nr);
+        }
         u32 flag = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->error_flag, &flag)) return rc;
         if (flag) {

@@ -15,6 +15,7 @@
 // performed in the reference's order, so scores come out bit-identical.
 #pragma once
 #include "mb_common.cuh"
+#include <string.h>
 
 namespace mb {
 
@@ -466,92 +467,138 @@ MB_HD int score_read(const mb_match *m, int b, int e, int query_length, const Sc
     return finish_read(m, best, query_length, cfg, tax, scr, r, error_flag);
 }
 
-// ---- streaming form -------------------------------------------------------------------------------------
-// The same computation as best_species() + match_paths() + combine_paths(), restated as ONE loop over the read's
-// sorted matches with a bounded state, so that the 32 reads a warp scores in parallel run the same instruction
-// stream (the nested while-loops of the general form serialise the lanes).  State: the two position groups of
-// the path DP (Taxonomer.cpp:487-648 only ever links a position group to the one before it), the paths of the
-// current species and the species that scored.  When a bound is exceeded the read is left to the general form.
-constexpr int SF_G = 4;      // matches per (species, frame, position) group
-constexpr int SF_P = 16;     // paths per species: also the size below which std::sort is a plain insertion sort
-constexpr int SF_S = 16;     // species with a score per read
+constexpr int SF_P = 16;     // paths per species: the size up to which std::sort is a plain insertion sort
 
-struct FastGroup {
-    PathRec p[SF_G];
-    u32 dna[SF_G];
-    u32 linked;              // bit k: entry k was extended
-    int n;
-    u32 pos;
-};
+// ---- compact streaming form ---------------------------------------------------------------------------------
+// The streaming state packed into 32-bit words so that it lives in SHARED memory on the device (one odd-strided
+// slice per thread: bank-conflict free, no local-memory traffic).  Scores are kept in half units as integers: every
+// partial score of the reference is a multiple of 0.5 far below 2^23, so its float sums are exact and equal to
+// these integer sums; the only rounding operations (division by the read length, tie average) stay in fp32.
+// Two phases per read so that the lanes of a warp stay together: (1) one loop over the matches runs the path DP and
+// collects the paths of every species, (2) one loop over the species that have paths sorts and combines them.
+constexpr int SC_G = 4;                          // matches per (species, frame, position) group
+constexpr int SC_NP = 40;                        // paths per read
+constexpr int SC_NS = 16;                        // species with paths per read
+constexpr int SC_W_GROUP = 0;                    // 2 groups x SC_G entries x 3 words
+constexpr int SC_W_PATH = 2 * SC_G * 3;          // SC_NP paths x 3 words
+constexpr int SC_W_SPEC = SC_W_PATH + SC_NP * 3; // SC_NS species x 2 words: id | paths << 24, then begin | end << 16 (later the score)
+constexpr int SC_WORDS = SC_W_SPEC + SC_NS * 2;
+constexpr int SC_STRIDE = SC_WORDS + 1;          // odd: lanes touching the same word hit different banks
 
-struct FastState {
-    FastGroup g[2];
-    PathRec paths[SF_P];
-    PathRec comb[SF_P];
-    int32_t sp_id[SF_S];
-    float sp_score[SF_S];
-};
-
-// combineMatchPaths on at most SF_P paths (insertion sort == libstdc++ std::sort for n <= 16)
-MB_HD float combine_paths_small(const mb_match *m, PathRec *paths, PathRec *comb, int n_paths, int read_length) {
-    ReadScratch tmp;
-    tmp.paths = paths; tmp.combined = comb;
-    return combine_paths(m, tmp, n_paths, read_length);
+// half-unit score and Hamming sum of the lowest `cnt` 2-bit fields of r (codon score 3 / 1.5 / 1 / 0.5 for h = 0..3)
+MB_HD void fields_score(u32 r, int cnt, int &score2, int &ham) {
+    r &= (cnt >= 16) ? 0xFFFFFFFFu : ((1u << (2 * cnt)) - 1u);
+    const u32 lo = r & 0x55555555u, hi = (r >> 1) & 0x55555555u;
+#if defined(__CUDA_ARCH__)
+    const int n1 = __popc(lo & ~hi), n2 = __popc(hi & ~lo), n3 = __popc(hi & lo);
+#else
+    const int n1 = __builtin_popcount(lo & ~hi), n2 = __builtin_popcount(hi & ~lo), n3 = __builtin_popcount(hi & lo);
+#endif
+    const int n0 = cnt - n1 - n2 - n3;
+    score2 = 6 * n0 + 3 * n1 + 2 * n2 + n3;
+    ham = n1 + 2 * n2 + 3 * n3;
 }
 
-MB_HD bool best_species_fast(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, FastState &st,
-                             BestSpecies &out) {
+// packed path (3 words): w0 = start | end << 16, w1 = (score2 & 0xFFFF) | ham << 16, w2 = sm | em << 16
+MB_HD int pk_score2(u32 w1) { return (int) (short) (w1 & 0xFFFFu); }
+MB_HD int pk_ham(u32 w1) { return (int) (w1 >> 16); }
+// comparator of combineMatchPaths (Taxonomer.cpp:417-426) on packed paths: score desc, hamming asc, start desc
+MB_HD bool pk_before(u32 a0, u32 a1, u32 b0, u32 b1) {
+    const int sa = pk_score2(a1), sb = pk_score2(b1);
+    if (sa != sb) return sa > sb;
+    const int ha = pk_ham(a1), hb = pk_ham(b1);
+    if (ha != hb) return ha < hb;
+    return (a0 & 0xFFFFu) > (b0 & 0xFFFFu);
+}
+
+
+MB_HD u32 f2u_hd(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    u32 u; memcpy(&u, &f, 4); return u;
+#endif
+}
+MB_HD float u2f_hd(u32 u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+// one group entry that is a finished path -> packed path list
+MB_HD void emit_path(u32 *w, int &n_paths, int &overflow, u32 e0, u32 e1, u32 end_pos, u32 em) {
+    if (n_paths < SC_NP) {
+        u32 *pp = w + SC_W_PATH + n_paths * 3;
+        pp[0] = (e0 & 0xFFFFu) | (end_pos << 16);
+        pp[1] = (e1 & 0xFFFu) | (((e1 >> 12) & 0xFFFu) << 16);
+        pp[2] = (e0 >> 16) | (em << 16);
+    } else overflow = 2;
+    ++n_paths;
+}
+
+// Returns false when a bound of the compact state is exceeded (the caller then uses the general form).
+// (reason codes: 1 position group, 2 paths per read, 3 species per read, 4 paths per species, 5 field width, 6 read size)
+MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, u32 *w,
+                               BestSpecies &out) {
     out.tax = 0; out.score = 0.f; out.lca = false; out.rb = 0; out.re = 0;
-    int n_sp = 0, meaningful = 0, n_paths = 0;
-    float best_sp = 0.f;
+    if (n > 60000 || query_length > 60000) return 6;
+    int n_paths = 0, n_spp = 0, sp_paths0 = 0;
     int32_t species = 0;
     u32 frame = 0;
     int sp_begin = 0, min_depth = cfg.min_cons_cnt;
-    int cur = 0;                 // st.g[cur] = previous position group, st.g[cur ^ 1] = the group being filled
-    bool have_cur = false, started = false, forward = true, overflow = false;
+    // group `cur` = previous position group (na entries from match ia0 at pos_a), cur ^ 1 = the group being filled
+    int cur = 0, na = 0, nb = 0, ia0 = 0, ib0 = 0;
+    u32 pos_a = 0, pos_b = 0;
+    bool have_cur = false, started = false, forward = true;
+    int overflow = 0;
 
+    // ---- phase 1: path DP over the matches (Taxonomer.cpp:487-648); the next record is loaded one step ahead ----
+    const u64 *mw = reinterpret_cast<const u64 *>(m);
+    u64 nx0 = mw[0], nx1 = mw[1], nx2 = mw[2];
     for (int i = 0; i <= n; ++i) {
         const bool at_end = i == n;
+        const u64 w0 = nx0, w1 = nx1, w2 = nx2;
+        if (i + 1 < n) { nx0 = mw[(i + 1) * 3]; nx1 = mw[(i + 1) * 3 + 1]; nx2 = mw[(i + 1) * 3 + 2]; }
         u64 qinfo = 0;
         int32_t sp = 0;
         u32 dna = 0, reh = 0, ham = 0;
         if (!at_end) {
-            const u64 *w = reinterpret_cast<const u64 *>(m + i);
-            const u64 w0 = w[0], w1 = w[1], w2 = w[2];
             qinfo = w0; sp = (int32_t) (w1 >> 32); dna = (u32) w2 & 0xFFFFFFu; reh = (u32) (w2 >> 32) & 0xFFFFu; ham = (u32) (w2 >> 48) & 0xFFu;
         }
         const u32 fr = qi_frame(qinfo), pos = qi_pos(qinfo);
         const bool new_species = at_end || i == 0 || sp != species;
         const bool new_frame = new_species || fr != frame;
-        if (new_frame && i > 0) {
-            // ---- end of a (species, frame) group: the last transition's emissions (Taxonomer.cpp:631-646) ----
-            if (have_cur) {
-                const FastGroup &a = st.g[cur], &b = st.g[cur ^ 1];
-                for (int c = 0; c < a.n; ++c)
-                    if (!((a.linked >> c) & 1u) && a.p[c].depth >= min_depth) {
-                        if (n_paths < SF_P) st.paths[n_paths] = a.p[c]; else overflow = true;
-                        ++n_paths;
-                    }
-                for (int c = 0; c < b.n; ++c)
-                    if (b.p[c].depth >= min_depth) {
-                        if (n_paths < SF_P) st.paths[n_paths] = b.p[c]; else overflow = true;
-                        ++n_paths;
-                    }
+        const bool rotate = !new_frame && started && pos != pos_b;
+        if (have_cur && (rotate || (new_frame && i > 0))) {
+            // paths of the previous group that were not extended (Taxonomer.cpp:631-640)
+            const u32 *ga = w + SC_W_GROUP + cur * SC_G * 3;
+            for (int c = 0; c < na; ++c) {
+                const u32 e1 = ga[c * 3 + 1], e2 = ga[c * 3 + 2];
+                if (!(e2 >> 24) && (int) (e1 >> 24) >= min_depth) emit_path(w, n_paths, overflow, ga[c * 3], e1, pos_a + 23u, (u32) (ia0 + c));
             }
-            if (new_species) {
-                // ---- end of a species (Taxonomer.cpp:357-376) ----
-                if (n_paths > 0 && !overflow) {
-                    float score = combine_paths_small(m, st.paths, st.comb, n_paths, query_length);
-                    score = score < 1.0f ? score : 1.0f;
-                    if (!(score < cfg.min_score)) {
-                        if (n_sp < SF_S) { st.sp_id[n_sp] = species; st.sp_score[n_sp] = score; } else overflow = true;
-                        ++n_sp;
-                        if (score > 0.f) ++meaningful;
-                        if (score > best_sp) { best_sp = score; out.rb = sp_begin; out.re = i; }
-                    }
+            if (new_frame) {
+                // the last group of the (species, frame) group: every path that is long enough (Taxonomer.cpp:641-646)
+                const u32 *gb = w + SC_W_GROUP + (cur ^ 1) * SC_G * 3;
+                for (int c = 0; c < nb; ++c) {
+                    const u32 e1 = gb[c * 3 + 1];
+                    if ((int) (e1 >> 24) >= min_depth) emit_path(w, n_paths, overflow, gb[c * 3], e1, pos_b + 23u, (u32) (ib0 + c));
                 }
-                n_paths = 0;
             }
+        }
+        if (new_species && i > 0) {
+            // species with paths are scored in phase 2
+            if (n_paths > sp_paths0) {
+                if (n_spp >= SC_NS || (u32) species >= (1u << 24)) overflow = 3;
+                else if (n_paths - sp_paths0 > SF_P) overflow = 4;
+                else {
+                    u32 *sw = w + SC_W_SPEC + n_spp * 2;
+                    sw[0] = (u32) species | ((u32) (n_paths - sp_paths0) << 24);
+                    sw[1] = (u32) sp_begin | ((u32) i << 16);
+                }
+                ++n_spp;
+            }
+            sp_paths0 = n_paths;
         }
         if (at_end || overflow) break;
         if (new_species) {
@@ -561,80 +608,137 @@ MB_HD bool best_species_fast(const mb_match *m, int n, int query_length, const S
         if (new_frame) {
             frame = fr; forward = fr < 3;
             have_cur = false; started = false;
-            st.g[0].n = 0; st.g[1].n = 0; st.g[0].linked = 0; st.g[1].linked = 0;
-            cur = 0;
+            na = 0; nb = 0; cur = 0;
         }
-        FastGroup *fill = &st.g[cur ^ 1];
-        if (!started) { started = true; fill->pos = pos; }
-        if (pos != fill->pos) {
-            // the group being filled is complete: emit the unlinked paths of the group before it, then rotate
-            if (have_cur) {
-                const FastGroup &a = st.g[cur];
-                for (int c = 0; c < a.n; ++c)
-                    if (!((a.linked >> c) & 1u) && a.p[c].depth >= min_depth) {
-                        if (n_paths < SF_P) st.paths[n_paths] = a.p[c]; else overflow = true;
-                        ++n_paths;
-                    }
-            }
+        if (!started) { started = true; pos_b = pos; ib0 = i; }
+        if (pos != pos_b) {                      // == rotate
             cur ^= 1;
             have_cur = true;
-            fill = &st.g[cur ^ 1];
-            fill->n = 0; fill->linked = 0; fill->pos = pos;
+            na = nb; pos_a = pos_b; ia0 = ib0;
+            nb = 0; pos_b = pos; ib0 = i;
         }
-        // path_init (Taxonomer.h:39-46)
-        PathRec t;
-        t.start = (int) pos; t.end = (int) pos + 23; t.ham = (int) ham; t.depth = 1; t.sm = i; t.em = i;
-        {
-            float sc = 0.f;
-            for (int k = 0; k < 8; ++k) sc += codon_score((reh >> (2 * k)) & 3u);
-            t.score = sc;
-        }
+        // path_init (Taxonomer.h:39-46): start = pos, score of the 8 codons, depth 1, sm = em = i
+        int t_score2, t_ham8;
+        fields_score(reh, 8, t_score2, t_ham8);
+        u32 t_start = pos, t_sm = (u32) i;
+        int t_ham = (int) ham, t_depth = 1;
         if (have_cur) {
-            FastGroup &a = st.g[cur];
-            const int shift = (int) ((pos - a.pos) / 3);
+            const int shift = (int) ((pos - pos_a) / 3);
             if (shift > 0 && shift <= cfg.max_codon_shift) {
-                float inc = 0.f;
-                int hinc = 0;
-                for (int k = 0; k < shift; ++k) {
-                    const u32 h = (reh >> (2 * k)) & 3u;
-                    inc += codon_score(h);
-                    hinc += (int) h;
-                }
+                int inc2, hinc;
+                fields_score(reh, shift, inc2, hinc);     // calScoreIncrement / calHammingDistIncrement (Taxonomer.cpp:650-669)
                 const u32 keep = (1u << (24 - 3 * shift)) - 1u;
-                int best = -1;
-                float best_score = 0.f;
-                for (int c = 0; c < a.n; ++c) {
+                u32 *ga = w + SC_W_GROUP + cur * SC_G * 3;
+                int best = -1, best_score2 = 0;
+                for (int c = 0; c < na; ++c) {
+                    const u32 e2 = ga[c * 3 + 2];
+                    const u32 adna = e2 & 0xFFFFFFu;
                     // isConsecutive(cur, next) forward, isConsecutive(next, cur) reverse (Taxonomer.cpp:671-699)
-                    const u32 x = forward ? a.dna[c] : dna, y = forward ? dna : a.dna[c];
+                    const u32 x = forward ? adna : dna, y = forward ? dna : adna;
                     const bool ok = cfg.format == 2 ? (x & keep) == (y >> (3 * shift)) : (x >> (3 * shift)) == (y & keep);
                     if (ok) {
-                        a.linked |= 1u << c;
-                        if (a.p[c].score > best_score) { best = c; best_score = a.p[c].score; }
+                        ga[c * 3 + 2] = e2 | (1u << 24);
+                        const int s2 = (int) (ga[c * 3 + 1] & 0xFFFu);
+                        if (s2 > best_score2) { best = c; best_score2 = s2; }
                     }
                 }
                 if (best >= 0) {
-                    const PathRec &bp = a.p[best];
-                    t.start = bp.start; t.score = bp.score + inc; t.ham = bp.ham + hinc; t.depth = bp.depth + shift; t.sm = bp.sm;
+                    const u32 e0 = ga[best * 3], e1 = ga[best * 3 + 1];
+                    t_start = e0 & 0xFFFFu; t_sm = e0 >> 16;
+                    t_score2 = (int) (e1 & 0xFFFu) + inc2;
+                    t_ham = (int) ((e1 >> 12) & 0xFFFu) + hinc;
+                    t_depth = (int) (e1 >> 24) + shift;
                 }
             }
         }
-        if (fill->n < SF_G) { fill->p[fill->n] = t; fill->dna[fill->n] = dna; } else overflow = true;
-        ++fill->n;
+        if (nb >= SC_G) overflow = 1;
+        else if (t_score2 >= 4096 || t_ham >= 4096 || t_depth >= 256) overflow = 5;
+        else {
+            u32 *gb = w + SC_W_GROUP + (cur ^ 1) * SC_G * 3 + nb * 3;
+            gb[0] = t_start | (t_sm << 16);
+            gb[1] = (u32) t_score2 | ((u32) t_ham << 12) | ((u32) t_depth << 24);
+            gb[2] = dna;
+        }
+        ++nb;
     }
-    if (overflow) return false;
-    if (meaningful == 0) { out.score = 0.f; return true; }
+    if (overflow) return overflow;
+
+    // ---- phase 2: per species with paths, combineMatchPaths (Taxonomer.cpp:410-485) ----
+    int meaningful = 0;
+    float best_sp = 0.f;
+    u32 *comb = w + SC_W_GROUP;                  // kept paths (start | end << 16): the DP groups are dead now
+    int p0 = 0;
+    for (int s = 0; s < n_spp; ++s) {
+        u32 *sw = w + SC_W_SPEC + s * 2;
+        const int pc = (int) (sw[0] >> 24);
+        u32 *pp = w + SC_W_PATH + p0 * 3;
+        p0 += pc;
+        // std::sort on <= 16 elements is libstdc++'s __insertion_sort (bits/stl_algo.h)
+        for (int k = 1; k < pc; ++k) {
+            const u32 v0 = pp[k * 3], v1 = pp[k * 3 + 1], v2 = pp[k * 3 + 2];
+            int j = k;
+            if (pk_before(v0, v1, pp[0], pp[1])) {
+                for (; j > 0; --j) { pp[j * 3] = pp[(j - 1) * 3]; pp[j * 3 + 1] = pp[(j - 1) * 3 + 1]; pp[j * 3 + 2] = pp[(j - 1) * 3 + 2]; }
+            } else {
+                while (pk_before(v0, v1, pp[(j - 1) * 3], pp[(j - 1) * 3 + 1])) {
+                    pp[j * 3] = pp[(j - 1) * 3]; pp[j * 3 + 1] = pp[(j - 1) * 3 + 1]; pp[j * 3 + 2] = pp[(j - 1) * 3 + 2];
+                    --j;
+                }
+            }
+            pp[j * 3] = v0; pp[j * 3 + 1] = v1; pp[j * 3 + 2] = v2;
+        }
+        int n_comb = 0, sum2 = 0;
+        for (int k = 0; k < pc; ++k) {
+            int c_start = (int) (pp[k * 3] & 0xFFFFu), c_end = (int) (pp[k * 3] >> 16);
+            int c_score2 = pk_score2(pp[k * 3 + 1]), c_ham = pk_ham(pp[k * 3 + 1]);
+            const int c_sm = (int) (pp[k * 3 + 2] & 0xFFFFu), c_em = (int) (pp[k * 3 + 2] >> 16);
+            bool rejected = false;
+            for (int j = 0; j < n_comb; ++j) {
+                const int k_start = (int) (comb[j] & 0xFFFFu), k_end = (int) (comb[j] >> 16);
+                if (c_end < k_start || k_end < c_start) continue;
+                const int lo = c_start > k_start ? c_start : k_start;
+                const int hi = c_end < k_end ? c_end : k_end;
+                const int overlap = hi - lo + 1;
+                if (overlap == c_end - c_start + 1 || overlap >= 24) { rejected = true; break; }
+                int part2, part_ham;
+                if (c_start < k_start) {         // trim the right end: Match::getRightPartScore / getRightPartHammingDist
+                    c_end = k_start - 1;
+                    fields_score((u32) m[c_em].rightEndHamming, overlap / 3, part2, part_ham);
+                } else {                         // trim the left end: the top overlap/3 fields (Match.h:46-86)
+                    c_start = k_end + 1;
+                    const int range = overlap / 3;
+                    fields_score(range ? ((u32) m[c_sm].rightEndHamming >> (16 - 2 * range)) : 0u, range, part2, part_ham);
+                }
+                const int h = c_ham - part_ham;
+                c_ham = h > 0 ? h : 0;
+                c_score2 = c_score2 - part2 - 2 * (overlap % 3);
+            }
+            if (!rejected) { comb[n_comb++] = (u32) c_start | ((u32) c_end << 16); sum2 += c_score2; }
+        }
+        float score = ((float) sum2 * 0.5f) / (float) query_length;
+        score = score < 1.0f ? score : 1.0f;
+        const u32 range = sw[1];
+        if (score < cfg.min_score) { sw[1] = 0xFFFFFFFFu; continue; }     // not recorded (Taxonomer.cpp:361)
+        sw[1] = f2u_hd(score);
+        if (score > 0.f) ++meaningful;
+        if (score > best_sp) { best_sp = score; out.rb = (int) (range & 0xFFFFu); out.re = (int) (range >> 16); }
+    }
+    if (meaningful == 0) { out.score = 0.f; return 0; }
     // species within tie_ratio of the best (Taxonomer.cpp:388-402)
     int n_top = 0;
     int32_t lca = 0;
     bool have = false;
     int32_t single = 0;
     const float cut = best_sp * cfg.tie_ratio;
-    for (int k = 0; k < n_sp; ++k) {
-        if (st.sp_score[k] >= cut) {
-            const int32_t t = st.sp_id[k];
+    for (int s = 0; s < n_spp; ++s) {
+        const u32 *sw = w + SC_W_SPEC + s * 2;
+        if (sw[1] == 0xFFFFFFFFu) continue;
+        const float sc = u2f_hd(sw[1]);
+        if (sc >= cut) {
+            const int32_t t = (int32_t) (sw[0] & 0xFFFFFFu);
             if (n_top == 0) single = t;
             ++n_top;
-            out.score += st.sp_score[k];
+            out.score += sc;
             if (tax_exists(tax, t)) {
                 if (!have) { lca = t; have = true; }
                 else lca = tax_lca_existing(tax, lca, t);
@@ -645,19 +749,20 @@ MB_HD bool best_species_fast(const mb_match *m, int n, int query_length, const S
         out.lca = true;
         out.tax = have ? lca : 0;
         out.score /= (float) n_top;
-        return true;
+        return 0;
     }
     out.tax = single;
-    return true;
+    return 0;
 }
 
-// Streaming scorer.  Returns -1 when a bound of the streaming state was exceeded (the caller then uses score_read).
-MB_HD int score_read_fast(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, FastState &st,
-                          ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
+// Compact streaming scorer.  Returns -(reason) when a bound of the state was exceeded (the caller then uses score_read).
+MB_HD int score_read_compact(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, u32 *w,
+                             ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
     result_init(r, query_length, n);
     if (n <= 0) return 0;
     BestSpecies best;
-    if (!best_species_fast(m, n, query_length, cfg, tax, st, best)) return -1;
+    const int why = best_species_compact(m, n, query_length, cfg, tax, w, best);
+    if (why) return -why;
     return finish_read(m, best, query_length, cfg, tax, scr, r, error_flag);
 }
 
@@ -749,12 +854,15 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
     const u32 lane = threadIdx.x & 31;
     const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
     const u32 total = list ? *list_count : n_reads;
+    // Left-over reads are few and heavy, and the general form diverges completely between lanes: one read per WARP
+    // (lane 0 works) finishes them sooner than 32 per warp.  The full-batch form takes 32 consecutive reads per warp.
+    const u32 per_ticket = list ? 1u : 32u;
     while (true) {
         u32 r0 = 0;
-        if (lane == 0) r0 = atomicAdd(ticket, 32u);
+        if (lane == 0) r0 = atomicAdd(ticket, per_ticket);
         r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
         if (r0 >= total) break;
-        if (r0 + lane < total) {
+        if (lane < per_ticket && r0 + lane < total) {
             const u32 r = list ? list[r0 + lane] : r0 + lane;
             // queryLength = max covered length of each mate (KmerExtractor.cpp:452,476)
             int ql = max_covered_length((int) lens[2 * r]);
@@ -776,13 +884,14 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
     }
 }
 
-// Streaming form, one THREAD per read (score_read_fast): the 32 reads of a warp advance through their match lists in
+// Compact streaming form, one THREAD per read (score_read_compact): the 32 reads of a warp advance through their match lists in
 // lock step.  Reads that exceed a bound of the streaming state are appended to `list` for k_score.
 __global__ void __launch_bounds__(SC_THREADS)
 k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
              const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
              mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
-             u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag, u32 *__restrict__ list, u32 *list_count) {
+             u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag, u32 *__restrict__ list, u32 *list_count, u32 *overflow_reasons) {
+    extern __shared__ u32 sc_state[];            // SC_THREADS slices of SC_STRIDE words
     const u32 lane = threadIdx.x & 31;
     const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
     while (true) {
@@ -799,11 +908,10 @@ k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, 
             ReadScratch scr;
             int n_tc = -1;
             if ((e - b) < 0x7FFFFFFFull) {
-                FastState st;
                 arena_carve(arena, slot, 0, 0, scr);
-                n_tc = score_read_fast(m + b, (int) (e - b), ql, cfg, tax, st, scr, res, error_flag);
+                n_tc = score_read_compact(m + b, (int) (e - b), ql, cfg, tax, sc_state + threadIdx.x * SC_STRIDE, scr, res, error_flag);
             }
-            if (n_tc < 0) list[atomicAdd(list_count, 1u)] = r;
+            if (n_tc < 0) { list[atomicAdd(list_count, 1u)] = r; atomicAdd(overflow_reasons + (n_tc < -7 ? 7 : -n_tc), 1u); }
             else store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
         }
         __syncwarp();
