@@ -58,18 +58,19 @@ struct Counters {                 // device-side scalars, one allocation
     u32 seg_too_long;
     u32 slow_count;
     u32 slow_ticket;
+    u32 finish_ticket;
     u32 fast_overflow[8];     // reads the compact scorer left to the general kernel, by reason
     u32 trivial[RS_MAX_PASSES];
 };
 
 // kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
-       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE_FAST, KID_SCORE,
+       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE_FAST, KID_SCORE_FINISH, KID_SCORE,
        KID_COUNT };
 const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract<write>",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
-                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score_fast", "k_score"};
+                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score_fast", "k_score_finish", "k_score"};
 struct KSample { int kid; cudaEvent_t a, b; };
 
 } // namespace
@@ -100,7 +101,7 @@ struct mb_ctx {
     DevBuf qstart, matches_a, matches_b;
     u64 n_matches = 0;
     DevBuf seg_begin, seg_end, results, tc_id, tc_cnt, arena;
-    DevBuf slow_list;
+    DevBuf slow_list, best_recs;
     DevBuf sc_local, sc_paths, sc_comb, sc_linked, sc_spid, sc_spscore;   // per-match scoring scratch
     u64 tc_used = 0;
     DevBuf counters;
@@ -691,17 +692,29 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         if (ctx->par.seq_mode != 3) {
             // short reads: streaming scorer first; what it cannot hold goes to the general kernel through slow_list
             CK(ctx->slow_list.ensure((size_t) nr * sizeof(u32)));
-            CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 10 * sizeof(u32), ctx->stream));
+            CK(ctx->best_recs.ensure((size_t) nr * sizeof(BestRec)));
+            CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 11 * sizeof(u32), ctx->stream));
             const size_t fast_smem = (size_t) SC_THREADS * SC_STRIDE * sizeof(u32);
+            // buckets of k_score_finish: cap_b taxa + cap_b bytes per thread, odd word stride
+            int bucket_stride = arena.cap_b + (arena.cap_b + 3) / 4;
+            bucket_stride |= 1;
+            const size_t fin_smem = (size_t) SC_THREADS * bucket_stride * sizeof(u32);
+            if (fin_smem > 200 * 1024) return fail(ctx, MB_E_ARG, "reads too long for seq-mode 1/2 scoring: use --seq-mode 3");
             static bool fast_attr = false;
             if (!fast_attr) {
                 CK(cudaFuncSetAttribute(k_score_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) fast_smem));
+                CK(cudaFuncSetAttribute(k_score_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
                 fast_attr = true;
             }
-            KL(KID_SCORE_FAST, k_score_fast<<<grid, SC_THREADS, fast_smem, ctx->stream>>>(
+            const unsigned fast_grid = (unsigned) std::min<u64>(148ull * 2, ((u64) nr + SC_THREADS - 1) / SC_THREADS);
+            KL(KID_SCORE_FAST, k_score_fast<<<fast_grid, SC_THREADS, fast_smem, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv,
+                ctx->best_recs.as<BestRec>(), &ctx->dcnt()->score_ticket, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count,
+                ctx->dcnt()->fast_overflow));
+            KL(KID_SCORE_FINISH, k_score_finish<<<grid, SC_THREADS, fin_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
-                ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
-                &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count, ctx->dcnt()->fast_overflow));
+                ctx->best_recs.as<BestRec>(), bucket_stride, ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(),
+                ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->finish_ticket, &ctx->dcnt()->error_flag));
             KL(KID_SCORE, k_score<<<std::min<unsigned>(grid, 148u * 8), SC_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
                 ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,

@@ -884,16 +884,22 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
     }
 }
 
-// Compact streaming form, one THREAD per read (score_read_compact): the 32 reads of a warp advance through their match lists in
-// lock step.  Reads that exceed a bound of the streaming state are appended to `list` for k_score.
+// What k_score_fast hands to k_score_finish: the outcome of getBestSpeciesMatches for one read.
+struct BestRec {
+    int32_t tax;
+    float score;
+    u32 range;             // rb | re << 16 : the best species' matches inside the read's segment
+    u32 state;             // 0 = left to the general kernel, 1 = no match, 2 = best species, 3 = LCA of tied species
+};
+
+// Compact streaming form, one THREAD per read (best_species_compact): the 32 reads of a warp advance through their match
+// lists in lock step.  Reads that exceed a bound of the streaming state are appended to `list` for k_score.
 __global__ void __launch_bounds__(SC_THREADS)
 k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
-             const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
-             mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
-             u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag, u32 *__restrict__ list, u32 *list_count, u32 *overflow_reasons) {
+             const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, BestRec *__restrict__ best_out,
+             u32 *ticket, u32 *__restrict__ list, u32 *list_count, u32 *overflow_reasons) {
     extern __shared__ u32 sc_state[];            // SC_THREADS slices of SC_STRIDE words
     const u32 lane = threadIdx.x & 31;
-    const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
     while (true) {
         u32 r0 = 0;
         if (lane == 0) r0 = atomicAdd(ticket, 32u);
@@ -904,15 +910,65 @@ k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, 
             int ql = max_covered_length((int) lens[2 * r]);
             if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
             const u64 b = seg_begin[r], e = seg_end[r];
-            mb_read_result res;
-            ReadScratch scr;
-            int n_tc = -1;
-            if ((e - b) < 0x7FFFFFFFull) {
-                arena_carve(arena, slot, 0, 0, scr);
-                n_tc = score_read_compact(m + b, (int) (e - b), ql, cfg, tax, sc_state + threadIdx.x * SC_STRIDE, scr, res, error_flag);
+            BestRec rec;
+            rec.tax = 0; rec.score = 0.f; rec.range = 0; rec.state = 1;
+            if (e > b) {
+                BestSpecies best;
+                const int why = (e - b) < 0x7FFFFFFFull ? best_species_compact(m + b, (int) (e - b), ql, cfg, tax, sc_state + threadIdx.x * SC_STRIDE, best) : 6;
+                if (why) {
+                    rec.state = 0;
+                    list[atomicAdd(list_count, 1u)] = r;
+                    atomicAdd(overflow_reasons + (why > 7 ? 7 : why), 1u);
+                } else {
+                    rec.tax = best.tax; rec.score = best.score; rec.range = (u32) best.rb | ((u32) best.re << 16);
+                    rec.state = best.lca ? 3u : 2u;
+                }
             }
-            if (n_tc < 0) { list[atomicAdd(list_count, 1u)] = r; atomicAdd(overflow_reasons + (n_tc < -7 ? 7 : -n_tc), 1u); }
-            else store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
+            best_out[r] = rec;
+        }
+        __syncwarp();
+    }
+}
+
+// Second half for the reads k_score_fast scored: chooseBestTaxon after getBestSpeciesMatches (finish_read).  The
+// redundancy buckets live in shared memory (cap_b entries per thread), so this kernel runs at high occupancy.
+__global__ void __launch_bounds__(SC_THREADS)
+k_score_finish(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
+               const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
+               const BestRec *__restrict__ best_in, int bucket_stride, mb_read_result *__restrict__ results,
+               int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out, u64 tc_cap, unsigned long long *tc_counter,
+               u32 *ticket, u32 *error_flag) {
+    extern __shared__ u32 fin_buckets[];         // SC_THREADS slices of bucket_stride words: cap_b taxa, then cap_b bytes
+    const u32 lane = threadIdx.x & 31;
+    const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
+    while (true) {
+        u32 r0 = 0;
+        if (lane == 0) r0 = atomicAdd(ticket, 32u);
+        r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
+        if (r0 >= n_reads) break;
+        const u32 r = r0 + lane;
+        if (r < n_reads) {
+            const BestRec rec = best_in[r];
+            if (rec.state != 0) {
+                int ql = max_covered_length((int) lens[2 * r]);
+                if (paired) ql += max_covered_length((int) lens[2 * r + 1]);
+                const u64 b = seg_begin[r], e = seg_end[r];
+                mb_read_result res;
+                ReadScratch scr;
+                arena_carve(arena, slot, 0, 0, scr);
+                u32 *mine = fin_buckets + (size_t) threadIdx.x * bucket_stride;
+                scr.bucket_tax = reinterpret_cast<int32_t *>(mine);
+                scr.bucket_ham = reinterpret_cast<u8 *>(mine + arena.cap_b);
+                result_init(res, ql, (int) (e - b));
+                int n_tc = 0;
+                if (rec.state != 1) {
+                    BestSpecies best;
+                    best.tax = rec.tax; best.score = rec.score; best.lca = rec.state == 3;
+                    best.rb = (int) (rec.range & 0xFFFFu); best.re = (int) (rec.range >> 16);
+                    n_tc = finish_read(m + b, best, ql, cfg, tax, scr, res, error_flag);
+                }
+                store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
+            }
         }
         __syncwarp();
     }
