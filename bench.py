@@ -283,7 +283,10 @@ def algorithmic_bytes(t, sizeof_match=24):
         "k_tile_first_mate": 8 * (nb // 2048 + 1),
         "k_extract<count>": nb,                                   # 1 B/base read
         "k_scan_counts": 12 * (nb // 2048 + 1),
-        "k_extract<write>": nb + 16 * nk,                         # bases read + 16 B/k-mer written
+        "k_extract": nb + 16 * nk,                                # bases read + 16 B/k-mer written (single pass)
+        "k_sort_segments": 2 * sizeof_match * nm,                 # one read + one write of the grouped matches
+        "k_score_fast": sizeof_match * nm + 16 * nr,
+        "k_score_finish": sizeof_match * nm // 2 + 48 * nr,       # the best species' matches (about half) + results
         "k_radix_hist<kmer>": 16 * nk,
         "k_radix_scan_hist<kmer>": 5 * 256 * 16,
         "k_radix_pass<kmer>": 32 * nk,                            # one read + one write of the records

@@ -73,7 +73,10 @@ typedef struct {
     int32_t accession_level;  /* only 0 is supported on this path                              */
     int32_t last_shard;       /* 1 when this context holds the END of the DB (the reference never
                                  offers the final DB k-mer as a candidate, KmerMatcher.cpp:363-406) */
-    int32_t reserved[3];
+    int32_t kmer_sort_bits;   /* leading amino-acid bits the query k-mer sort orders: 24, 32 or 40 (0 = default 32).
+                                 The join only needs the queries of a DB block to be contiguous, not ordered, so
+                                 fewer bits = fewer radix passes; blocks re-check the full amino-acid part.        */
+    int32_t reserved[2];
 } mb_params;
 
 /* Per-read result: the fields of Query (src/commons/common.h:95-128) that reach the outputs. */

@@ -32,7 +32,7 @@ class Params(C.Structure):
                 ("seq_mode", C.c_int32), ("min_cons_cnt", C.c_int32), ("min_cons_cnt_euk", C.c_int32),
                 ("min_score", C.c_float), ("min_sp_score", C.c_float), ("tie_ratio", C.c_float),
                 ("skip_redundancy", C.c_int32), ("accession_level", C.c_int32), ("last_shard", C.c_int32),
-                ("reserved", C.c_int32 * 3)]
+                ("kmer_sort_bits", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class PhaseTimes(C.Structure):

@@ -49,6 +49,7 @@ enum { EV_START, EV_H2D, EV_EXTRACT, EV_SORTK, EV_MATCH, EV_SORTM, EV_SCORE, EV_
 struct Counters {                 // device-side scalars, one allocation
     unsigned long long match_count;
     unsigned long long tc_count;
+    unsigned long long kmer_count;
     u32 error_flag;
     u32 max_seg;
     u32 score_ticket;
@@ -67,7 +68,7 @@ struct Counters {                 // device-side scalars, one allocation
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
        KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE_FAST, KID_SCORE_FINISH, KID_SCORE,
        KID_COUNT };
-const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract<write>",
+const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
                                           "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score_fast", "k_score_finish", "k_score"};
@@ -92,6 +93,7 @@ struct mb_ctx {
     u64 n_bases = 0;
     u32 n_reads = 0;
     u32 seq_base = 0;
+    int sort_shift = 0;               // low amino-acid bits the resident k-mer order ignores
     u64 kmer_bound = 0;
     u32 max_query_len = 0;
     DevBuf tile_mate, tile_counts, tile_offsets;
@@ -239,6 +241,9 @@ static int check_params(const mb_params *p, std::string &err) {
     if (p->kmer_format != 1 && p->kmer_format != 2) { err = "kmer_format must be 1 or 2"; return MB_E_ARG; }
     if (p->seq_mode < 1 || p->seq_mode > 3) { err = "seq_mode must be 1, 2 or 3"; return MB_E_ARG; }
     if (p->syncmer && (p->smer_len < 1 || p->smer_len > 7)) { err = "smer_len must be in 1..7"; return MB_E_ARG; }
+    if (p->kmer_sort_bits != 0 && p->kmer_sort_bits != 24 && p->kmer_sort_bits != 32 && p->kmer_sort_bits != 40) {
+        err = "kmer_sort_bits must be 0, 24, 32 or 40"; return MB_E_ARG;
+    }
     if (p->accession_level != 0) { err = "accession_level != 0 is not on this path"; return MB_E_ARG; }
     return MB_OK;
 }
@@ -473,6 +478,8 @@ int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_kmers = ctx->kmers_sorted = ctx->have_matches = ctx->have_results = false;
     ctx->n_kmers = 0;
+    ctx->n_samples = 0;               // the per-kernel table covers one pass of the device stages
+    ctx->launches = 0;
     const u32 n_tiles = (u32) ((ctx->n_bases + EX_TILE - 1) / EX_TILE);
     if (n_tiles && ctx->n_reads) {
         ExtractArgs a;
@@ -480,18 +487,23 @@ int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
         a.n_mates = ctx->n_reads * 2; a.seq_mode = ctx->par.seq_mode; a.format = ctx->par.kmer_format;
         a.syncmer = ctx->par.syncmer; a.smer_len = ctx->par.smer_len; a.seq_base = ctx->seq_base;
         CK(ctx->tile_mate.ensure(((size_t) n_tiles + 1) * sizeof(u32)));
-        CK(ctx->tile_counts.ensure((size_t) n_tiles * sizeof(u32)));
-        CK(ctx->tile_offsets.ensure(((size_t) n_tiles + 1) * sizeof(u64)));
         CK(ctx->kmers_a.ensure((ctx->kmer_bound + 1) * sizeof(mb_kmer)));
+        CK(cudaMemsetAsync(&ctx->dcnt()->kmer_count, 0, sizeof(unsigned long long), ctx->stream));
         KL(KID_TILE_MATE, k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>()));
-        KL(KID_EXTRACT_COUNT, k_extract<false><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
-                                                                 ctx->tile_counts.as<u32>(), nullptr, nullptr));
-        KL(KID_EXTRACT_SCAN, k_scan_counts<<<1, 1024, 0, ctx->stream>>>(ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(), n_tiles));
-        KL(KID_EXTRACT_WRITE, k_extract<true><<<n_tiles, EX_THREADS, 0, ctx->stream>>>(a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(),
-                                                                ctx->tile_counts.as<u32>(), ctx->tile_offsets.as<u64>(),
-                                                                ctx->kmers_a.as<mb_kmer>()));
-        u64 total = 0;
-        if (int rc = read_back(ctx, ctx->tile_offsets.as<u64>() + n_tiles, &total)) return rc;
+        static bool ex_attr = false;
+        if (!ex_attr) {
+            CK(cudaFuncSetAttribute(k_extract<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_extract<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
+            ex_attr = true;
+        }
+        if (a.format == 2)
+            KL(KID_EXTRACT_WRITE, k_extract<true><<<n_tiles, EX_THREADS, extract_smem_bytes(), ctx->stream>>>(
+                a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(), ctx->kmers_a.as<mb_kmer>(), &ctx->dcnt()->kmer_count, ctx->kmer_bound));
+        else
+            KL(KID_EXTRACT_WRITE, k_extract<false><<<n_tiles, EX_THREADS, extract_smem_bytes(), ctx->stream>>>(
+                a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(), ctx->kmers_a.as<mb_kmer>(), &ctx->dcnt()->kmer_count, ctx->kmer_bound));
+        unsigned long long total = 0;
+        if (int rc = read_back(ctx, &ctx->dcnt()->kmer_count, &total)) return rc;
         if (total > ctx->kmer_bound) return fail(ctx, MB_E_DATA, "internal: extracted more k-mers than the slot bound");
         ctx->n_kmers = total;
     }
@@ -505,9 +517,20 @@ int mb_sort_kmers(mb_ctx *ctx) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
     CK(cudaSetDevice(ctx->par.device));
+    // The join needs the queries of one DB block contiguous, not ordered (every query binary-searches the decoded
+    // block): ordering the leading `bits` of the 40 amino-acid bits takes bits/8 passes instead of 5.
+    static const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;      // tuning knob
+    const int bits = env_bits ? env_bits : (ctx->par.kmer_sort_bits ? ctx->par.kmer_sort_bits : 32);
+    ctx->sort_shift = 40 - bits;
     KmerKey key;
-    key.first_bit = 24;   // the join needs the amino-acid parts grouped in increasing order; 5 passes of 8 bits
-    if (int rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, 5, KID_KSORT_HIST)) return rc;
+    key.first_bit = 24 + ctx->sort_shift;
+    const int passes = bits / 8;
+    static const int k_items = getenv("MB_KSORT_ITEMS") ? atoi(getenv("MB_KSORT_ITEMS")) : 16;     // tuning knob
+    int rc = 0;
+    if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST);
+    else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST);
+    else rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST);
+    if (rc) return rc;
     mark(ctx, EV_SORTK);
     ctx->kmers_sorted = true;
     return MB_OK;
@@ -523,9 +546,10 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
     ctx->n_matches = 0;
     if (ctx->n_blocks && ctx->n_kmers) {
         const u32 nb = ctx->n_blocks;
-        CK(ctx->qstart.ensure(((size_t) nb + 1) * sizeof(u64)));
-        KL(KID_MATCH_PARTITION, k_match_partition<<<(nb + 1 + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
-                                                                       ctx->n_kmers, ctx->qstart.as<u64>()));
+        CK(ctx->qstart.ensure(((size_t) nb + 1) * 2 * sizeof(u64)));
+        u64 *qstart = ctx->qstart.as<u64>(), *qend = qstart + nb + 1;
+        KL(KID_MATCH_PARTITION, k_match_partition<<<(nb + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
+                                                                   ctx->n_kmers, ctx->sort_shift, qstart, qend));
         static bool match_attr_set = false;
         if (!match_attr_set) {
             CK(cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
@@ -542,7 +566,7 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
             CK(cudaMemsetAsync(&ctx->dcnt()->match_ticket, 0, sizeof(u32), ctx->stream));
             const unsigned grid = (unsigned) std::min<u64>(nb, 148ull * 3);     // persistent: 3 CTAs per SM (70 KB smem each)
             KL(KID_MATCH, k_match<<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
-                              db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), ctx->qstart.as<u64>(), mo,
+                              db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
                               ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket));
             unsigned long long total = 0;
             if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;
@@ -603,7 +627,13 @@ int mb_sort_matches(mb_ctx *ctx) {
         MatchSeqKey qk;
         qk.seq_base = ctx->seq_base;
         const int seq_passes = (key.seq_bits + 7) / 8;
-        if (int rc = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST)) return rc;
+        static const int m_items = getenv("MB_MSORT_ITEMS") ? atoi(getenv("MB_MSORT_ITEMS")) : 8;     // tuning knob
+        int rcs = 0;
+        if (m_items == 4) rcs = radix_sort<mb_match, MatchSeqKey, 4>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
+        else if (m_items == 6) rcs = radix_sort<mb_match, MatchSeqKey, 6>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
+        else if (m_items == 12) rcs = radix_sort<mb_match, MatchSeqKey, 12>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
+        else rcs = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
+        if (rcs) return rcs;
         if (int rc = compute_segments(ctx)) return rc;
         CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
         CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 2 * sizeof(u32), ctx->stream));

@@ -50,23 +50,39 @@ __global__ void k_tile_first_mate(ExtractArgs a, u32 n_tiles, u32 *__restrict__ 
     tile_mate[t] = (t == n_tiles || a.n_mates == 0) ? (a.n_mates ? a.n_mates - 1 : 0) : mate_of(a.offsets, 0, a.n_mates - 1, g);
 }
 
-template <bool WRITE>
+constexpr size_t extract_smem_bytes() { return (size_t) EX_TILE * 2 * sizeof(mb_kmer); }   // every window, both strands
+
+// ONE pass: a CTA extracts the k-mers of its 2048 window starts into a shared-memory staging buffer (slots handed out
+// by warp-aggregated atomics on a shared counter), reserves its output range with one global atomic and copies the
+// buffer out with coalesced 16-byte stores.  The query buffer is unordered by contract (the reference fills it from
+// many threads, KmerExtractor.cpp:83-386, and sorts afterwards), so no prefix sum over tiles is needed.
+//
+// FMT2 (current metamer format): the three codon phases of a thread's 32 staged bases are translated ONCE into packed
+// streams (5-bit amino acids, 3-bit codon ids; 10 codons per phase); the metamer of every window is then a bit-field
+// of its phase's stream — forward strand with the first codon most significant, reverse strand with the stream built
+// in the opposite order (MetamerScanner::next, KmerScanner.h:82-117).  The legacy base-21 format keeps the
+// per-window translation.
+template <bool FMT2>
 __global__ void __launch_bounds__(EX_THREADS)
-k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__restrict__ tables,
-          u32 *__restrict__ tile_counts, const u64 *__restrict__ tile_offsets, mb_kmer *__restrict__ out) {
+k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__restrict__ tables, mb_kmer *__restrict__ out,
+          unsigned long long *__restrict__ out_count, u64 out_cap) {
+    extern __shared__ __align__(16) unsigned char ex_raw[];
+    ulonglong2 *s_out = reinterpret_cast<ulonglong2 *>(ex_raw);          // EX_TILE * 2 records
     __shared__ u16 s_code[EX_THREADS + 4];
     __shared__ u8 s_amb[EX_THREADS + 4];
     __shared__ u8 s_nuc[256];
     __shared__ u8 s_codonF[64];
     __shared__ u8 s_codonR[64];
-    __shared__ u32 s_warp[EX_THREADS / 32];
+    __shared__ u32 s_fill;
+    __shared__ unsigned long long s_base;
 
-    const u32 tid = threadIdx.x;
+    const u32 tid = threadIdx.x, lane = tid & 31;
     const u32 tile = blockIdx.x;
     const u64 g0 = (u64) tile * EX_TILE;
 
     s_nuc[tid] = tables->nuc[tid];
     if (tid < 64) { s_codonF[tid] = tables->codonF[tid]; s_codonR[tid] = tables->codonR[tid]; }
+    if (tid == 0) s_fill = 0;
     __syncthreads();
 
     // stage 8 bases per thread (+ 4 halo groups by the first threads)
@@ -91,6 +107,28 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
     const u64 w = (u64) s_code[tid] | ((u64) s_code[tid + 1] << 16) | ((u64) s_code[tid + 2] << 32) | ((u64) s_code[tid + 3] << 48);
     const u32 ambw = (u32) s_amb[tid] | ((u32) s_amb[tid + 1] << 8) | ((u32) s_amb[tid + 2] << 16) | ((u32) s_amb[tid + 3] << 24);
 
+    // packed codon streams of the three phases (FMT2)
+    u64 aaF[3], aaR[3];
+    u32 dnaF[3], dnaR[3];
+    if (FMT2) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            u64 af = 0, ar = 0;
+            u32 df = 0, dr = 0;
+#pragma unroll
+            for (int k = 0; k < 10; ++k) {
+                const int p = r + 3 * k;                                  // <= 29: bases p..p+2 lie inside the 32 staged bases
+                const u32 six = (u32) (w >> (2 * p)) & 63u;
+                const u32 cf = s_codonF[six], cr = s_codonR[six];
+                af = (af << 5) | (cf & 31u);
+                df = (df << 3) | (cf >> 5);
+                ar |= (u64) (cr & 31u) << (5 * k);
+                dr |= (cr >> 5) << (3 * k);
+            }
+            aaF[r] = af; dnaF[r] = df; aaR[r] = ar; dnaR[r] = dr;
+        }
+    }
+
     // mate of the first window start of this thread
     const u64 gfirst = g0 + (u64) tid * EX_PER_THREAD;
     u32 m = 0;
@@ -102,17 +140,16 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
         moff = __ldg(a.offsets + m);
         mlen = __ldg(a.lens + m);
     }
-
-    mb_kmer local[2 * EX_PER_THREAD];
-    int cnt = 0;
     const bool paired = a.seq_mode == 2;
     bool have_meta = false, usable = false;
     u32 pos_offset = 0;
     int used = 0;
 
-    if (any) {
 #pragma unroll
-        for (int i = 0; i < EX_PER_THREAD; ++i) {
+    for (int i = 0; i < EX_PER_THREAD; ++i) {
+        bool ok = false;
+        u32 x = 0;
+        if (any) {
             const u64 g = gfirst + i;
             // advance to the mate that owns base g (mates are back to back, zero-length ones share an offset)
             while (m + 1 < a.n_mates && __ldg(a.offsets + m + 1) <= g) {
@@ -121,76 +158,65 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
                 mlen = __ldg(a.lens + m);
                 have_meta = false;
             }
-            if (g < moff || g >= moff + mlen) continue;
-            if (!have_meta) {
-                have_meta = true;
-                // KmerExtractor.cpp:261-279, 457-460: a mate whose slot bound is < 1 is empty; in paired
-                // mode one empty mate drops the pair; other modes use mate 0 only.
-                const bool self_ok = query_kmer_number((int) mlen) >= 1;
-                if (paired) {
-                    const u32 sib = __ldg(a.lens + (m ^ 1u));
-                    usable = self_ok && query_kmer_number((int) sib) >= 1;
-                    pos_offset = (m & 1u) ? (u32) max_covered_length((int) sib) + 3u : 0u;
-                } else {
-                    usable = self_ok && (m & 1u) == 0;
-                    pos_offset = 0;
+            if (g >= moff && g < moff + mlen) {
+                if (!have_meta) {
+                    have_meta = true;
+                    // KmerExtractor.cpp:261-279, 457-460: a mate whose slot bound is < 1 is empty; in paired
+                    // mode one empty mate drops the pair; other modes use mate 0 only.
+                    const bool self_ok = query_kmer_number((int) mlen) >= 1;
+                    if (paired) {
+                        const u32 sib = __ldg(a.lens + (m ^ 1u));
+                        usable = self_ok && query_kmer_number((int) sib) >= 1;
+                        pos_offset = (m & 1u) ? (u32) max_covered_length((int) sib) + 3u : 0u;
+                    } else {
+                        usable = self_ok && (m & 1u) == 0;
+                        pos_offset = 0;
+                    }
+                    used = max_covered_length((int) mlen);
                 }
-                used = max_covered_length((int) mlen);
+                x = (u32) (g - moff);
+                // window [x, x+23] must end inside the frame segment [x%3, x%3 + used - 1]; an ambiguous base
+                // inside the window: the scanners restart after it, so no window may cover it
+                ok = usable && (int) (x + 24) <= (int) (x % 3) + used && !((ambw >> i) & 0xFFFFFFu);
             }
-            if (!usable) continue;
-            const u32 x = (u32) (g - moff);
-            // window [x, x+23] must end inside the frame segment [x%3, x%3 + used - 1]
-            if ((int) (x + 24) > (int) (x % 3) + used) continue;
-            if ((ambw >> i) & 0xFFFFFFu) continue;          // an ambiguous base: no window may cover it
+        }
+        u64 vf, vr;
+        if (FMT2) {
+            const int r = i % 3, k0 = i / 3;
+            vf = (((aaF[r] >> (5 * (2 - k0))) & 0xFFFFFFFFFFull) << 24) | ((dnaF[r] >> (3 * (2 - k0))) & 0xFFFFFFu);
+            vr = (((aaR[r] >> (5 * k0)) & 0xFFFFFFFFFFull) << 24) | ((dnaR[r] >> (3 * k0)) & 0xFFFFFFu);
+        } else {
             const u64 win = (w >> (2 * i)) & 0xFFFFFFFFFFFFull;
-            const u32 seqId = a.seq_base + (m >> 1) + 1;
-            // forward strand: frame = begin = x % 3 (KmerExtractor.cpp:369-373)
-            {
-                const u64 v = metamer_from_window(s_codonF, s_codonR, win, false, a.format);
-                if (a.format == 1 || !a.syncmer || is_syncmer(v, a.smer_len)) {
-                    local[cnt].value = v;
-                    local[cnt].qinfo = make_qinfo(seqId, x + pos_offset, x % 3);
-                    ++cnt;
-                }
-            }
-            // reverse strand: begin = (L%3 - frame%3) mod 3 and begin == x%3  =>  frame = 3 + (L - x) mod 3
-            {
-                const u64 v = metamer_from_window(s_codonF, s_codonR, win, true, a.format);
-                if (a.format == 1 || !a.syncmer || is_syncmer(v, a.smer_len)) {
-                    const u32 fr = 3u + (u32) (((int) (mlen % 3) - (int) (x % 3) + 3) % 3);
-                    local[cnt].value = v;
-                    local[cnt].qinfo = make_qinfo(seqId, x + pos_offset, fr);
-                    ++cnt;
-                }
+            vf = metamer_from_window(s_codonF, s_codonR, win, false, 1);
+            vr = metamer_from_window(s_codonF, s_codonR, win, true, 1);
+        }
+        const u32 seqId = a.seq_base + (m >> 1) + 1;
+        const u32 xm = x % 3;
+        // forward strand: frame = begin = x % 3 (KmerExtractor.cpp:369-373)
+        // reverse strand: begin = (L%3 - frame%3) mod 3 and begin == x%3  =>  frame = 3 + (L - x) mod 3
+        const u32 fr_rev = 3u + (u32) (((int) (mlen % 3) - (int) xm + 3) % 3);
+#pragma unroll
+        for (int strand = 0; strand < 2; ++strand) {
+            const u64 v = strand ? vr : vf;
+            const bool emit = ok && (!FMT2 || !a.syncmer || is_syncmer(v, a.smer_len));
+            const u32 mask = __ballot_sync(0xFFFFFFFFu, emit);
+            if (mask) {
+                u32 base = 0;
+                if (lane == (u32) (__ffs(mask) - 1)) base = atomicAdd(&s_fill, (u32) __popc(mask));
+                base = __shfl_sync(0xFFFFFFFFu, base, __ffs(mask) - 1);
+                if (emit) s_out[base + __popc(mask & ((1u << lane) - 1u))] = make_ulonglong2(v, make_qinfo(seqId, x + pos_offset, strand ? fr_rev : xm));
             }
         }
     }
-
-    // block-wide exclusive scan of cnt
-    const u32 lane = tid & 31, warp = tid >> 5;
-    u32 incl = (u32) cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        u32 v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= (u32) d) incl += v;
-    }
-    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    u32 wbase = 0, total = 0;
-#pragma unroll
-    for (int k = 0; k < EX_THREADS / 32; ++k) {
-        const u32 v = s_warp[k];
-        if ((u32) k < warp) wbase += v;
-        total += v;
-    }
-    if (!WRITE) {
-        if (tid == 0) tile_counts[tile] = total;
-        return;
-    }
-    const u64 base = tile_offsets[tile] + wbase + (incl - (u32) cnt);
-    for (int k = 0; k < cnt; ++k) {
-        // 16-byte vector store
-        *reinterpret_cast<ulonglong2 *>(out + base + k) = make_ulonglong2(local[k].value, local[k].qinfo);
+    const u32 total = s_fill;
+    if (tid == 0 && total) s_base = atomicAdd(out_count, (unsigned long long) total);
+    __syncthreads();
+    if (total) {
+        const u64 base = s_base;
+        ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(out);
+        for (u32 k = tid; k < total; k += EX_THREADS)
+            if (base + k < out_cap) dst[base + k] = s_out[k];
     }
 }
 

@@ -280,14 +280,13 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
 __device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, MatchSmem &s, MatchTables &tb, const MatchOut &mo,
                                          const mb_kmer *__restrict__ q, u64 qcur, u64 qend, u64 gaa, int format, u32 &fill) {
     const u32 tid = threadIdx.x;
-    while (true) {
+    for (; qcur < qend; qcur += MT_THREADS) {
         const u64 qi = qcur + tid;
         mb_kmer qk;
         qk.value = 0; qk.qinfo = 0;
         bool mine = false;
         if (qi < qend) { qk = q[qi]; mine = (qk.value >> 24) == gaa; }
-        const int taken = __syncthreads_count(mine);
-        if (taken == 0) break;
+        if (__syncthreads_count(mine) == 0) continue;
         u32 mind = 255, maxh = 0;
         for (int phase = 0; phase < 2; ++phase) {
             DbCursor g = c;
@@ -327,8 +326,6 @@ __device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, Ma
             }
             if (phase == 0) maxh = mind * 2 < 7 ? mind * 2 : 7;
         }
-        qcur += (u64) taken;
-        if (taken < MT_THREADS) break;
     }
 }
 
@@ -343,7 +340,7 @@ __device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, 
 
 __global__ void __launch_bounds__(MT_THREADS)
 k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
-        MatchOut mo, const Tables *__restrict__ tables, int format, u32 *block_ticket) {
+        const u64 *__restrict__ qend_of, MatchOut mo, const Tables *__restrict__ tables, int format, u32 *block_ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     MatchSmem &s = *reinterpret_cast<MatchSmem *>(smem_raw);
     MatchTables &tb = *reinterpret_cast<MatchTables *>(smem_raw + ((sizeof(MatchSmem) + 15) & ~(size_t) 15));
@@ -365,8 +362,8 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
         if (b >= n_blocks) break;
         const BlockIndex bi = blocks[b];
         if (!bi.owns) continue;
-        u64 qcur = qstart[b];
-        const u64 qend = qstart[b + 1];
+        const u64 qcur = qstart[b];
+        const u64 qend = qend_of[b];
         if (qcur >= qend) continue;                 // no query falls into this block's AA range
 
         const u64 tile_end = (u64) (b + 1) * DB_W;  // groups starting at or after this word belong to later blocks
@@ -401,8 +398,9 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 break;
             }
 
-            // ---- fast path: all groups in [0, proc_end) are complete and owned.  Warps run on their own. ----
-            const u64 limit_aa = proc_end < n ? (s.vals[proc_end] >> 24) : ~0ull;
+            // ---- fast path: all groups in [0, proc_end) are complete and owned.  Warps run on their own; every query
+            // of the block's range is looked up (the range is not ordered below the sorted bits, and it also holds
+            // queries of the neighbouring blocks: those find no group of their amino-acid part here). ----
             while (true) {
                 u32 base = 0;
                 if (lane == 0) base = atomicAdd(&s.qnext, 32u);
@@ -415,9 +413,8 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 if (qi < qend) {
                     const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(q + qi));
                     qk.value = v.x; qk.qinfo = v.y;
-                    mine = (qk.value >> 24) < limit_aa;
+                    mine = true;
                 }
-                const u32 mine_mask = __ballot_sync(0xFFFFFFFFu, mine);
                 u32 lo = 0, hi = 0, maxh = 0, cnt = 0;
                 u64 dpack = 0;
                 if (mine) {
@@ -441,20 +438,15 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                     }
                 }
                 warp_emit(db, c, s, tb, mo, mine, qk, lo, hi, maxh, cnt, dpack, format, fill);
-                if (mine_mask != 0xFFFFFFFFu) break;               // queries are sorted: the rest belongs to later groups
             }
             __syncthreads();
             if (proc_end >= n && db_end) break;                        // end of the stream
             if (proc_end >= own_end) break;                            // the next group starts in a later block
             // continue from the first group that was not processed (it starts inside this block)
-            if (tid == 0) s.qadv = query_lower_bound(q, qcur, qend, limit_aa);
             const u64 nw = c.word + (u64) s.wend[proc_end - 1] + 1;
             const u64 nv = s.vals[proc_end - 1];
             __syncthreads();
-            qcur = s.qadv;
             c.word = nw; c.vbefore = nv; c.kidx += proc_end;
-            if (qcur >= qend) break;
-            __syncthreads();
         }
     }
     warp_flush(mo, tb.stage[warp], fill);
@@ -546,19 +538,26 @@ k_db_decode(DbView db, u32 n_blocks, const u32 *__restrict__ blk_back, const u32
     for (u32 j = tid; j < cnt; j += MT_THREADS) values[c.kidx + j] = s.vals[j];
 }
 
-// ---- per-batch partition: first query whose AA part is >= the block's first owned AA ------------------
-__global__ void k_match_partition(const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, u64 nq,
-                                  u64 *__restrict__ qstart) {
-    const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b > n_blocks) return;
-    if (b == n_blocks) { qstart[b] = nq; return; }
-    const u64 aa = blocks[b].own_aa;
+// ---- per-batch partition: the query range a block has to look at ------------------------------------------
+// The queries are ordered by T(aa) = aa >> shift only.  Block b owns the amino-acid groups [own_aa(b), own_aa(b+1)),
+// so it scans the queries with T(own_aa(b)) <= T(aa) <= T(own_aa(b+1)): the buckets at both ends are shared with the
+// neighbouring blocks, which is harmless because a query only finds its group in the block that owns it.
+__device__ __forceinline__ u64 query_lower_bound_t(const mb_kmer *__restrict__ q, u64 nq, int shift, u64 t) {
     u64 lo = 0, hi = nq;
     while (lo < hi) {
         const u64 mid = (lo + hi) >> 1;
-        if ((__ldg(&q[mid].value) >> 24) < aa) lo = mid + 1; else hi = mid;
+        if (((__ldg(&q[mid].value) >> 24) >> shift) < t) lo = mid + 1; else hi = mid;
     }
-    qstart[b] = lo;
+    return lo;
+}
+__global__ void k_match_partition(const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, u64 nq, int shift,
+                                  u64 *__restrict__ qstart, u64 *__restrict__ qend) {
+    const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    if (!blocks[b].owns) { qstart[b] = 0; qend[b] = 0; return; }
+    qstart[b] = query_lower_bound_t(q, nq, shift, blocks[b].own_aa >> shift);
+    const u64 nxt = b + 1 < n_blocks ? blocks[b + 1].own_aa : ~0ull;
+    qend[b] = nxt == ~0ull ? nq : query_lower_bound_t(q, nq, shift, (nxt >> shift) + (shift ? 1 : 0));
 }
 
 } // namespace mb

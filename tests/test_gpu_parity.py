@@ -46,7 +46,7 @@ def compare_results(res_gpu, ids_gpu, cnt_gpu, res_o, ids_o, cnt_o):
     return bad
 
 
-def run_all_stages(mb, dbdir, seq_mode, s1, s2, **kw):
+def run_all_stages(mb, dbdir, seq_mode, s1, s2, sort_bits=0, **kw):
     """Returns dict of GPU intermediates and the oracle's, after asserting stage-by-stage parity."""
     db = orc.Db(dbdir)
     p = db.params(seq_mode=seq_mode, **kw)
@@ -54,6 +54,8 @@ def run_all_stages(mb, dbdir, seq_mode, s1, s2, **kw):
     ok, om, ores, oids, ocnt = orc.classify(db, p, batch, threads=4)
     clf = mb.Classifier(dbdir, seq_mode=seq_mode, min_score=kw.get("min_score", 0.0), min_sp_score=kw.get("min_sp_score", 0.0))
     try:
+        if sort_bits:
+            clf.set_params(kmer_sort_bits=sort_bits)
         # K3 tap: decode of the resident stream
         v, _ = db.decode()
         assert np.array_equal(clf.decode_db(), v)
@@ -64,8 +66,8 @@ def run_all_stages(mb, dbdir, seq_mode, s1, s2, **kw):
         assert np.array_equal(canon_k(clf.kmers()), ok)                      # K1
         clf.sort_kmers()
         ks = clf.kmers()
-        aa = ks["value"] >> np.uint64(24)
-        assert np.all(aa[1:] >= aa[:-1])                                      # K2: grouped by amino-acid part
+        t = ks["value"] >> np.uint64(24 + 40 - (sort_bits or 32))
+        assert np.all(t[1:] >= t[:-1])                                        # K2: ordered by the leading amino-acid bits
         assert np.array_equal(canon_k(ks), ok)
         nm = clf.match()
         assert nm == len(om)
@@ -94,6 +96,15 @@ def test_golden_case_all_stages(golden, mb, case):
     res, ids, cnt = run_all_stages(mb, golden.dbdir(case), meta["seq_mode"], s1, s2)
     # and directly against the reference-generated fixture
     assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
+
+
+@pytest.mark.parametrize("bits", [24, 40])
+def test_kmer_sort_bits(golden, mb, bits):
+    """The join result does not depend on how many leading amino-acid bits the query sort orders."""
+    _, s1, s2 = golden.reads("sync_paired")
+    run_all_stages(mb, golden.dbdir("sync_paired"), 2, s1, s2, sort_bits=bits)
+    _, sl, _ = golden.reads("plain_long")
+    run_all_stages(mb, golden.dbdir("plain_long"), 3, sl, None, sort_bits=bits)
 
 
 def test_min_sp_score_branch(golden, mb):
