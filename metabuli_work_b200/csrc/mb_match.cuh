@@ -89,6 +89,7 @@ struct MatchTables {
     u8 lutp[4096];
     u64 stage[MT_THREADS / 32][MT_STAGE * 3];
     u32 fill[MT_THREADS / 32];
+    u32 qmin[MT_THREADS / 32][32];           // per query of the warp's ticket: smallest distance in its group
 };
 
 // Decode up to DB_C words starting at cursor c (which must sit on the first word of a k-mer).
@@ -415,29 +416,93 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                     qk.value = v.x; qk.qinfo = v.y;
                     mine = true;
                 }
-                u32 lo = 0, hi = 0, maxh = 0, cnt = 0;
-                u64 dpack = 0;
+                // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
+                u32 lo = 0, ncand = 0;
                 if (mine) {
                     const u64 aa = qk.value >> 24;
                     lo = lower_bound_aa(s.vals, proc_end, aa);
-                    hi = lo;
-                    u32 mind = 255;
-                    while (hi < proc_end) {
-                        const u64 t = s.vals[hi];
-                        if ((t >> 24) != aa) break;
-                        const u32 d = hamming_sum_lut(tb.lut2, qk.value, t);
-                        if (hi - lo < 16) dpack |= (u64) (d < 15 ? d : 15) << (4 * (hi - lo));
-                        mind = d < mind ? d : mind;
-                        ++hi;
-                    }
-                    if (hi > lo) {
-                        maxh = mind * 2 < 7 ? mind * 2 : 7;        // KmerMatcher.cpp:1126
-                        const u32 n16 = hi - lo < 16 ? hi - lo : 16;
-                        for (u32 j = 0; j < n16; ++j) cnt += ((u32) (dpack >> (4 * j)) & 15u) <= maxh ? 1u : 0u;
-                        for (u32 j = lo + 16; j < hi; ++j) cnt += hamming_sum_lut(tb.lut2, qk.value, s.vals[j]) <= maxh ? 1u : 0u;
-                    }
+                    u32 hi = lo;
+                    while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
+                    ncand = hi - lo;
                 }
-                warp_emit(db, c, s, tb, mo, mine, qk, lo, hi, maxh, cnt, dpack, format, fill);
+                // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
+                // whose exclusive prefix of ncand is the largest one <= p
+                u32 incl = ncand;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                    if (lane >= (u32) d) incl += t;
+                }
+                const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                if (total == 0) continue;
+                const u32 excl = incl - ncand;
+                const u32 q24 = (u32) qk.value & 0xFFFFFFu;
+                u32 *qmin = tb.qmin[warp];
+                qmin[lane] = 255;
+                __syncwarp();
+                const u32 rounds = (total + 31) / 32;
+                u32 d_first = 0, owner_first = 0, j_first = 0;           // pair of round 0 is kept for the emit pass
+                for (u32 r = 0; r < rounds; ++r) {
+                    const u32 p = r * 32 + lane;
+                    u32 owner = 0;
+#pragma unroll
+                    for (int st = 16; st > 0; st >>= 1) {
+                        const u32 e = __shfl_sync(0xFFFFFFFFu, excl, (owner + st) & 31);
+                        if (owner + st < 32 && e <= p) owner += st;
+                    }
+                    // lanes with ncand == 0 share their prefix with the next lane: the search lands on the LAST lane
+                    // with excl <= p, which is the one that owns p (its range is non-empty) when p < total
+                    const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
+                    const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo, owner);
+                    const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
+                    u32 dd = 255, j = 0;
+                    if (p < total) {
+                        j = o_lo + (p - o_excl);
+                        dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
+                        atomicMin(&qmin[owner], dd);
+                    }
+                    if (r == 0) { d_first = dd; owner_first = owner; j_first = j; }
+                }
+                __syncwarp();
+                // (3) emit: distance <= min(2 * min, 7) (KmerMatcher.cpp:1126); one staging slot per surviving pair
+                u64 *stage = tb.stage[warp];
+                for (u32 r = 0; r < rounds; ++r) {
+                    const u32 p = r * 32 + lane;
+                    u32 owner, dd, j;
+                    if (r == 0) { owner = owner_first; dd = d_first; j = j_first; }
+                    else {
+                        owner = 0;
+#pragma unroll
+                        for (int st = 16; st > 0; st >>= 1) {
+                            const u32 e = __shfl_sync(0xFFFFFFFFu, excl, (owner + st) & 31);
+                            if (owner + st < 32 && e <= p) owner += st;
+                        }
+                        const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
+                        const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo, owner);
+                        const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
+                        dd = 255; j = 0;
+                        if (p < total) { j = o_lo + (p - o_excl); dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]); }
+                    }
+                    const u32 mind = qmin[owner];
+                    const u32 maxh = mind * 2 < 7 ? mind * 2 : 7;
+                    const bool ok = p < total && dd <= maxh;
+                    const u32 okmask = __ballot_sync(0xFFFFFFFFu, ok);
+                    // the owner's full query record (value and qinfo) for the match
+                    mb_kmer oq;
+                    oq.value = __shfl_sync(0xFFFFFFFFu, qk.value, owner);
+                    oq.qinfo = __shfl_sync(0xFFFFFFFFu, qk.qinfo, owner);
+                    if (okmask == 0) continue;
+                    const u32 nok = (u32) __popc(okmask);
+                    if (fill + nok > MT_STAGE) warp_flush(mo, stage, fill);
+                    if (ok) {
+                        u64 rec[3];
+                        make_match(db, mo, tb.lutp, oq, s.vals[j], c.kidx + j, dd, format, rec);
+                        const u32 o = fill + (u32) __popc(okmask & ((1u << lane) - 1u));
+                        stage[o * 3] = rec[0]; stage[o * 3 + 1] = rec[1]; stage[o * 3 + 2] = rec[2];
+                    }
+                    fill += nok;
+                    __syncwarp();
+                }
             }
             __syncthreads();
             if (proc_end >= n && db_end) break;                        // end of the stream
