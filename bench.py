@@ -314,7 +314,10 @@ def ncu_traffic(kernel):
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         with open(p) as f:
-            return json.load(f).get(kernel)
+            ks = json.load(f).get("kernels", {})
+        for name, v in ks.items():                   # ncu names carry template arguments: match on the base name
+            if name == kernel or name.split("<")[0] == kernel.split("<")[0] and (("kmer" in name) == ("kmer" in kernel)):
+                return int(v["dram_bytes_per_launch"])
     return None
 
 
