@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--cpu-pairs", type=int, default=0, help="read pairs of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--check", action="store_true", help="compare a sample of the GPU results with the oracle")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="multi-GPU: producers write into peer memory (fused) or bucket + NCCL all-to-all (nccl)")
     ap.add_argument("--keep", action="store_true", help="keep the generated workload in --workdir")
     return ap.parse_args()
 
@@ -348,7 +350,7 @@ def run_b200(a):
     clf = mb.Classifier(dbdir, device=local, seq_mode=2, shard=rank, n_shards=world)
     log(f"rank {rank}: shard {rank}/{world} resident ({clf.db_kmers()} k-mers, {clf.db_words()} words) in {time.time() - t0:.1f}s")
     clf.set_profile(True)
-    sharded = ShardedClassifier(DeviceEngine(clf, device), clf.shard_bounds(), n_pairs, rank, world) if world > 1 else None
+    sharded = ShardedClassifier(DeviceEngine(clf, device), clf.shard_bounds(), n_pairs, rank, world, fused=a.exchange == "fused") if world > 1 else None
 
     # pinned host buffers (inputs and results of the end-to-end leg)
     pin_bases = torch.from_numpy(bases).pin_memory()
@@ -469,6 +471,7 @@ def run_b200(a):
                                f"({meta['db_kmers']} k-mers, {meta['species']} species), seq-mode 2, s=5",
                    "pairs_per_gpu": n_pairs, "db_kmers": meta["db_kmers"], "db_words": meta["db_words"], "genomes": meta["genomes"],
                    "db_sharding": f"{world} k-mer-range shard(s), one per GPU" if world > 1 else "whole DB on one GPU",
+                   "exchange": (a.exchange if world > 1 else None),
                    "l2": "inputs larger than L2 (k-mer buffer and DB stream are GBs vs 126 MB L2); no flush needed",
                    "seed": a.seed},
         "clocks": clocks,

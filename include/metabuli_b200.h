@@ -179,6 +179,38 @@ int mb_set_read_id_base(mb_ctx *ctx, uint32_t base);
 int mb_partition_kmers(mb_ctx *ctx, const uint64_t *bounds, int n_shards, uint64_t *counts);
 int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint64_t *counts);
 
+/* multi-GPU, fused form: the producing kernels route their records straight into the destination GPU's
+ * receive buffer through peer memory (NVLink P2P stores + one remote atomic reservation per run), so the
+ * bucketing passes and the all-to-all collectives above disappear.  Extraction sends every k-mer to the
+ * shard that owns its value; the join sends every match to its read's home rank.
+ *   mb_peer_alloc    allocate this context's fixed-capacity receive side and describe it
+ *   mb_ipc_export/open/close  CUDA IPC plumbing for one-process-per-GPU (handles travel by any host channel)
+ *   mb_peer_attach   give the context the receive sides of ALL ranks (device addresses valid in this process;
+ *                    entry `rank` is its own) plus the routing rules
+ *   mb_extract_kmers_routed / mb_match_kmers_routed   the producers; *n_emitted = records this rank produced
+ *   mb_take_routed_kmers / mb_take_routed_matches     after a cross-rank barrier: adopt what arrived as the
+ *                    resident k-mers / matches (MB_E_CAPACITY when more arrived than the buffer holds; the
+ *                    count is still returned so that the caller can re-allocate on every rank and redo)
+ * Between producer and take the CALLER must synchronise all ranks (every producer call returns only after
+ * its kernel has finished, so a host barrier is enough). */
+#define MB_MAX_RANKS 16
+typedef struct {
+    void    *kmers;           /* mb_kmer[kmer_cap]   receive buffer                        */
+    void    *matches;         /* mb_match[match_cap] receive buffer                        */
+    void    *counters;        /* uint64[2]: k-mers arrived, matches arrived                */
+    uint64_t kmer_cap, match_cap;
+} mb_peer_mem;
+int mb_peer_alloc(mb_ctx *ctx, size_t kmer_cap, size_t match_cap, mb_peer_mem *out);
+int mb_ipc_export(mb_ctx *ctx, const void *dptr, unsigned char handle[64]);
+int mb_ipc_open(mb_ctx *ctx, const unsigned char handle[64], void **dptr);
+int mb_ipc_close(mb_ctx *ctx, void *dptr);
+int mb_peer_attach(mb_ctx *ctx, uint32_t rank, uint32_t n_ranks, const mb_peer_mem *peers, const uint64_t *bounds,
+                   uint32_t reads_per_rank);
+int mb_extract_kmers_routed(mb_ctx *ctx, size_t *n_emitted);
+int mb_take_routed_kmers(mb_ctx *ctx, size_t *n);
+int mb_match_kmers_routed(mb_ctx *ctx, size_t *n_emitted);
+int mb_take_routed_matches(mb_ctx *ctx, size_t *n);
+
 int mb_get_timings(mb_ctx *ctx, mb_phase_times *t);
 /* Per-kernel timing of the last batch: with profiling on, every kernel launch of the hot path is
  * bracketed by a CUDA event pair on the launching stream; the table sums them per kernel. */

@@ -50,6 +50,12 @@ class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms", C.c_float), ("launches", C.c_uint32)]
 
 
+class PeerMem(C.Structure):
+    """mb_peer_mem: one rank's receive side (device addresses valid in the process that holds the struct)."""
+    _fields_ = [("kmers", C.c_void_p), ("matches", C.c_void_p), ("counters", C.c_void_p), ("kmer_cap", C.c_uint64),
+                ("match_cap", C.c_uint64)]
+
+
 # every symbol include/metabuli_b200.h declares
 ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", "mb_global_error", "mb_set_params",
                "mb_load_db", "mb_decode_db", "mb_load_taxonomy", "mb_classify_batch", "mb_stage_reads",
@@ -58,7 +64,8 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_set_matches", "mb_kmers_device", "mb_matches_device", "mb_set_kmers_device", "mb_set_matches_device",
                "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream",
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
-               "mb_get_kernel_times"]
+               "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
+               "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -108,6 +115,15 @@ _sig(_cuda, "mb_get_timings", C.c_int, [vp, C.POINTER(PhaseTimes)])
 _sig(_cuda, "mb_stream", vp, [vp])
 _sig(_cuda, "mb_set_profile", C.c_int, [vp, C.c_int])
 _sig(_cuda, "mb_get_kernel_times", C.c_int, [vp, C.POINTER(KernelTime), sz, szp])
+_sig(_cuda, "mb_peer_alloc", C.c_int, [vp, sz, sz, C.POINTER(PeerMem)])
+_sig(_cuda, "mb_ipc_export", C.c_int, [vp, vp, vp])
+_sig(_cuda, "mb_ipc_open", C.c_int, [vp, vp, C.POINTER(vp)])
+_sig(_cuda, "mb_ipc_close", C.c_int, [vp, vp])
+_sig(_cuda, "mb_peer_attach", C.c_int, [vp, u32, u32, C.POINTER(PeerMem), vp, u32])
+_sig(_cuda, "mb_extract_kmers_routed", C.c_int, [vp, szp])
+_sig(_cuda, "mb_take_routed_kmers", C.c_int, [vp, szp])
+_sig(_cuda, "mb_match_kmers_routed", C.c_int, [vp, szp])
+_sig(_cuda, "mb_take_routed_matches", C.c_int, [vp, szp])
 
 _sig(_host, "mbh_last_error", C.c_char_p, [])
 _sig(_host, "mbh_open", vp, [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int])
@@ -291,6 +307,59 @@ class Context:
         counts = np.zeros(n_ranks, dtype=np.uint64)
         self._ck(_cuda.mb_partition_matches(self.ctx, reads_per_rank, n_ranks, _ptr(counts)))
         return counts
+
+    # ---- multi-GPU, fused form: producers write into the destination rank's receive buffer over peer memory ----
+    def peer_alloc(self, kmer_cap, match_cap):
+        m = PeerMem()
+        self._ck(_cuda.mb_peer_alloc(self.ctx, int(kmer_cap), int(match_cap), C.byref(m)))
+        return m
+
+    def ipc_export(self, dptr):
+        h = (C.c_ubyte * 64)()
+        self._ck(_cuda.mb_ipc_export(self.ctx, C.c_void_p(dptr), h))
+        return bytes(h)
+
+    def ipc_open(self, handle):
+        h = (C.c_ubyte * 64).from_buffer_copy(handle)
+        p = C.c_void_p(0)
+        self._ck(_cuda.mb_ipc_open(self.ctx, h, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, dptr):
+        self._ck(_cuda.mb_ipc_close(self.ctx, C.c_void_p(dptr)))
+
+    def peer_attach(self, rank, peers, bounds, reads_per_rank):
+        """peers: list of PeerMem, one per rank, addresses valid in this process (entry `rank` = own peer_alloc)."""
+        arr = (PeerMem * len(peers))(*peers)
+        bounds = np.ascontiguousarray(bounds, dtype=np.uint64)
+        self._ck(_cuda.mb_peer_attach(self.ctx, rank, len(peers), arr, _ptr(bounds) if len(bounds) else None, int(reads_per_rank)))
+
+    def extract_routed(self):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_extract_kmers_routed(self.ctx, C.byref(n)))
+        return n.value
+
+    def take_routed_kmers(self):
+        """-> (k-mers that arrived, overflowed?)"""
+        n = C.c_size_t(0)
+        rc = _cuda.mb_take_routed_kmers(self.ctx, C.byref(n))
+        if rc == MB_E_CAPACITY:
+            return n.value, True
+        self._ck(rc)
+        return n.value, False
+
+    def match_routed(self):
+        n = C.c_size_t(0)
+        self._ck(_cuda.mb_match_kmers_routed(self.ctx, C.byref(n)))
+        return n.value
+
+    def take_routed_matches(self):
+        n = C.c_size_t(0)
+        rc = _cuda.mb_take_routed_matches(self.ctx, C.byref(n))
+        if rc == MB_E_CAPACITY:
+            return n.value, True
+        self._ck(rc)
+        return n.value, False
 
     def timings(self):
         t = PhaseTimes()

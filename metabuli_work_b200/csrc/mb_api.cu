@@ -117,6 +117,16 @@ struct mb_ctx {
     size_t n_samples = 0;
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
     bool segments_valid = false;      // seg_begin/seg_end describe matches_a
+    // multi-GPU routing (mb_peer_*): this context's receive side and the routing table of all ranks
+    DevBuf peer_kmers, peer_matches, peer_cnt, route_dev;
+    u64 peer_kmer_cap = 0, peer_match_cap = 0;
+    Route route;
+    bool routed = false;
+    const void *kmers_src = nullptr;   // resident k-mers live in the receive buffer until the sort reads them
+    const void *matches_src = nullptr; // same for matches
+
+    const mb_kmer *kmers_now() const { return kmers_src ? (const mb_kmer *) kmers_src : kmers_a.as<mb_kmer>(); }
+    const mb_match *matches_now() const { return matches_src ? (const mb_match *) matches_src : matches_a.as<mb_match>(); }
 
     Counters *dcnt() const { return counters.as<Counters>(); }
 };
@@ -178,9 +188,16 @@ static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
 
 // ---- radix sort driver --------------------------------------------------------------------------------
 template <typename Rec, typename Key, int ITEMS>
-static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes, int kid_base) {
-    if (n == 0 || n_passes == 0) return MB_OK;
+static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes, int kid_base, const void *src = nullptr) {
+    // src: the records are in a read-only buffer outside the ping-pong pair (a peer receive buffer); the histogram and
+    // the first pass read it, the result ends up in `a` like always
+    if (n == 0) return MB_OK;
+    if (n_passes == 0) {
+        if (src) { CK(a.ensure(n * sizeof(Rec))); CK(cudaMemcpyAsync(a.p, src, n * sizeof(Rec), cudaMemcpyDeviceToDevice, ctx->stream)); }
+        return MB_OK;
+    }
     if (n_passes > RS_MAX_PASSES) return fail(ctx, MB_E_ARG, "too many radix passes");
+    if (src) CK(a.ensure(n * sizeof(Rec)));
     constexpr u64 TILE = (u64) RS_THREADS * ITEMS;
     const u64 tiles = (n + TILE - 1) / TILE;
     CK(b.ensure(n * sizeof(Rec)));
@@ -190,7 +207,7 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     CK(cudaMemsetAsync(&ctx->dcnt()->trivial, 0, sizeof(u32) * RS_MAX_PASSES, ctx->stream));
     const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
     KL(kid_base + 0, k_radix_hist<Rec, Key><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
-        a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>()));
+        src ? (const Rec *) src : a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>()));
     KL(kid_base + 1, k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial));
     constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
     static const int radix_dbg = getenv("MB_RADIX_DBG") ? atoi(getenv("MB_RADIX_DBG")) : 0;     // timing experiments only
@@ -203,7 +220,7 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
         CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * RS_BINS * sizeof(u64), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->radix_ticket, 0, sizeof(u32), ctx->stream));
         KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
-            a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
+            (p == 0 && src) ? (const Rec *) src : a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
             &ctx->dcnt()->radix_ticket, radix_dbg));
         std::swap(a.p, b.p);
         std::swap(a.cap, b.cap);
@@ -213,10 +230,10 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
 
 // stable multi-way partition = one radix pass whose digit is the destination rank
 template <typename Rec, typename Key, int ITEMS>
-static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_parts, uint64_t *counts) {
+static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_parts, uint64_t *counts, const void *src) {
     for (int i = 0; i < n_parts; ++i) counts[i] = 0;
     if (n == 0) return MB_OK;
-    if (int rc = radix_sort<Rec, Key, ITEMS>(ctx, a, b, n, key, 1, -100)) return rc;
+    if (int rc = radix_sort<Rec, Key, ITEMS>(ctx, a, b, n, key, 1, -100, src)) return rc;
     // digit_base (exclusive scan of the histogram) is still in ctx->hist
     std::vector<u64> base(RS_BINS);
     CK(cudaMemcpyAsync(base.data(), ctx->hist.p, RS_BINS * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
@@ -473,12 +490,14 @@ int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_
     return MB_OK;
 }
 
-int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
+static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "mb_stage_reads first");
+    if (routed && !ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_kmers = ctx->kmers_sorted = ctx->have_matches = ctx->have_results = false;
     ctx->n_kmers = 0;
+    ctx->kmers_src = nullptr;
     ctx->n_samples = 0;               // the per-kernel table covers one pass of the device stages
     ctx->launches = 0;
     const u32 n_tiles = (u32) ((ctx->n_bases + EX_TILE - 1) / EX_TILE);
@@ -488,31 +507,40 @@ int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) {
         a.n_mates = ctx->n_reads * 2; a.seq_mode = ctx->par.seq_mode; a.format = ctx->par.kmer_format;
         a.syncmer = ctx->par.syncmer; a.smer_len = ctx->par.smer_len; a.seq_base = ctx->seq_base;
         CK(ctx->tile_mate.ensure(((size_t) n_tiles + 1) * sizeof(u32)));
-        CK(ctx->kmers_a.ensure((ctx->kmer_bound + 1) * sizeof(mb_kmer)));
+        if (!routed) CK(ctx->kmers_a.ensure((ctx->kmer_bound + 1) * sizeof(mb_kmer)));
         CK(cudaMemsetAsync(&ctx->dcnt()->kmer_count, 0, sizeof(unsigned long long), ctx->stream));
         KL(KID_TILE_MATE, k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>()));
         static bool ex_attr = false;
         if (!ex_attr) {
-            CK(cudaFuncSetAttribute(k_extract<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
-            CK(cudaFuncSetAttribute(k_extract<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_extract<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_extract<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_extract<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_extract<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
             ex_attr = true;
         }
-        if (a.format == 2)
-            KL(KID_EXTRACT_WRITE, k_extract<true><<<n_tiles, EX_THREADS, extract_smem_bytes(), ctx->stream>>>(
-                a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(), ctx->kmers_a.as<mb_kmer>(), &ctx->dcnt()->kmer_count, ctx->kmer_bound));
-        else
-            KL(KID_EXTRACT_WRITE, k_extract<false><<<n_tiles, EX_THREADS, extract_smem_bytes(), ctx->stream>>>(
-                a, ctx->tile_mate.as<u32>(), ctx->tables.as<Tables>(), ctx->kmers_a.as<mb_kmer>(), &ctx->dcnt()->kmer_count, ctx->kmer_bound));
+        mb_kmer *out = routed ? nullptr : ctx->kmers_a.as<mb_kmer>();
+        const Route *rt = routed ? ctx->route_dev.as<Route>() : nullptr;
+        const u32 *tm = ctx->tile_mate.as<u32>();
+        const Tables *tb = ctx->tables.as<Tables>();
+        unsigned long long *cnt = &ctx->dcnt()->kmer_count;
+        const size_t sm = extract_smem_bytes();
+        if (a.format == 2 && !routed) KL(KID_EXTRACT_WRITE, k_extract<true, false><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
+        else if (a.format == 2) KL(KID_EXTRACT_WRITE, k_extract<true, true><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
+        else if (!routed) KL(KID_EXTRACT_WRITE, k_extract<false, false><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
+        else KL(KID_EXTRACT_WRITE, k_extract<false, true><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
         unsigned long long total = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->kmer_count, &total)) return rc;
         if (total > ctx->kmer_bound) return fail(ctx, MB_E_DATA, "internal: extracted more k-mers than the slot bound");
         ctx->n_kmers = total;
     }
     mark(ctx, EV_EXTRACT);
-    ctx->have_kmers = true;
     if (n_kmers) *n_kmers = ctx->n_kmers;
+    if (routed) ctx->n_kmers = 0;            // they left for their owners; mb_take_routed_kmers brings this rank's share
+    else ctx->have_kmers = true;
     return MB_OK;
 }
+int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers) { return extract_impl(ctx, n_kmers, false); }
+int mb_extract_kmers_routed(mb_ctx *ctx, size_t *n_emitted) { return extract_impl(ctx, n_emitted, true); }
 
 int mb_sort_kmers(mb_ctx *ctx) {
     if (!ctx) return MB_E_ARG;
@@ -528,18 +556,21 @@ int mb_sort_kmers(mb_ctx *ctx) {
     const int passes = bits / 8;
     static const int k_items = getenv("MB_KSORT_ITEMS") ? atoi(getenv("MB_KSORT_ITEMS")) : 16;     // tuning knob
     int rc = 0;
-    if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST);
-    else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST);
-    else rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST);
+    if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, ctx->kmers_src);
+    else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, ctx->kmers_src);
+    else rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, ctx->kmers_src);
     if (rc) return rc;
+    ctx->kmers_src = nullptr;
     mark(ctx, EV_SORTK);
     ctx->kmers_sorted = true;
     return MB_OK;
 }
 
-int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
+static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_kmers || !ctx->kmers_sorted) return fail(ctx, MB_E_ARG, "sorted k-mers required");
+    if (routed && !ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
+    ctx->matches_src = nullptr;
     if (ctx->max_taxid < 0) return fail(ctx, MB_E_ARG, "mb_load_taxonomy first");
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
@@ -558,20 +589,24 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
         }
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
         for (int attempt = 0; attempt < 3; ++attempt) {
-            CK(ctx->matches_a.ensure(cap * sizeof(mb_match)));
-            cap = ctx->matches_a.cap / sizeof(mb_match);
+            if (!routed) {
+                CK(ctx->matches_a.ensure(cap * sizeof(mb_match)));
+                cap = ctx->matches_a.cap / sizeof(mb_match);
+            }
             CK(cudaMemsetAsync(&ctx->dcnt()->match_count, 0, sizeof(unsigned long long), ctx->stream));
             CK(cudaMemsetAsync(&ctx->dcnt()->error_flag, 0, sizeof(u32), ctx->stream));
             MatchOut mo;
-            mo.out = ctx->matches_a.as<mb_match>(); mo.cap = cap; mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag;
+            mo.out = routed ? nullptr : ctx->matches_a.as<mb_match>(); mo.cap = routed ? 0 : cap;
+            mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag; mo.route = nullptr;
             CK(cudaMemsetAsync(&ctx->dcnt()->match_ticket, 0, sizeof(u32), ctx->stream));
             const unsigned grid = (unsigned) std::min<u64>(nb, 148ull * 3);     // persistent: 3 CTAs per SM (70 KB smem each)
             KL(KID_MATCH, k_match<<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
                               db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
-                              ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket));
+                              ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket,
+                              routed ? ctx->route_dev.as<Route>() : nullptr));
             unsigned long long total = 0;
             if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;
-            if (total <= cap) { ctx->n_matches = total; break; }
+            if (routed || total <= cap) { ctx->n_matches = total; break; }
             // capacity miss: the kernel counted everything but wrote only what fits; size exactly and rerun
             ++ctx->times.match_retries;
             cap = (size_t) total;
@@ -582,10 +617,13 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) {
         if (flag) return fail(ctx, MB_E_DATA, "a DB k-mer carries a tax ID without species mapping (KmerMatcher.cpp:433-441)");
     }
     mark(ctx, EV_MATCH);
-    ctx->have_matches = true;
     if (n_matches) *n_matches = ctx->n_matches;
+    if (routed) ctx->n_matches = 0;          // they left for their home ranks; mb_take_routed_matches brings this rank's
+    else ctx->have_matches = true;
     return MB_OK;
 }
+int mb_match_kmers(mb_ctx *ctx, size_t *n_matches) { return match_impl(ctx, n_matches, false); }
+int mb_match_kmers_routed(mb_ctx *ctx, size_t *n_emitted) { return match_impl(ctx, n_emitted, true); }
 
 static MatchKey match_key(const mb_ctx *ctx) {
     MatchKey k;
@@ -630,11 +668,12 @@ int mb_sort_matches(mb_ctx *ctx) {
         const int seq_passes = (key.seq_bits + 7) / 8;
         static const int m_items = getenv("MB_MSORT_ITEMS") ? atoi(getenv("MB_MSORT_ITEMS")) : 12;    // tuning knob
         int rcs = 0;
-        if (m_items == 4) rcs = radix_sort<mb_match, MatchSeqKey, 4>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
-        else if (m_items == 6) rcs = radix_sort<mb_match, MatchSeqKey, 6>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
-        else if (m_items == 12) rcs = radix_sort<mb_match, MatchSeqKey, 12>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
-        else rcs = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST);
+        if (m_items == 4) rcs = radix_sort<mb_match, MatchSeqKey, 4>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
+        else if (m_items == 6) rcs = radix_sort<mb_match, MatchSeqKey, 6>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
+        else if (m_items == 12) rcs = radix_sort<mb_match, MatchSeqKey, 12>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
+        else rcs = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
         if (rcs) return rcs;
+        ctx->matches_src = nullptr;
         if (int rc = compute_segments(ctx)) return rc;
         CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
         CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 2 * sizeof(u32), ctx->stream));
@@ -662,7 +701,8 @@ int mb_sort_matches(mb_ctx *ctx) {
     if (!done) {
         ctx->segments_valid = false;
         const int passes = (key.total_bits() + 7) / 8;
-        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST)) return rc;
+        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST, ctx->matches_src)) return rc;
+        ctx->matches_src = nullptr;
     }
     mark(ctx, EV_SORTM);
     ctx->matches_sorted = true;
@@ -821,7 +861,7 @@ int mb_copy_kmers(mb_ctx *ctx, mb_kmer *out, size_t cap, size_t *n) {
     *n = ctx->n_kmers;
     if (cap < ctx->n_kmers) return fail(ctx, MB_E_CAPACITY, "k-mer output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_kmers) CK(cudaMemcpyAsync(out, ctx->kmers_a.p, ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->n_kmers) CK(cudaMemcpyAsync(out, ctx->kmers_now(), ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -832,7 +872,7 @@ int mb_copy_matches(mb_ctx *ctx, mb_match *out, size_t cap, size_t *n) {
     *n = ctx->n_matches;
     if (cap < ctx->n_matches) return fail(ctx, MB_E_CAPACITY, "match output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_matches) CK(cudaMemcpyAsync(out, ctx->matches_a.p, ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->n_matches) CK(cudaMemcpyAsync(out, ctx->matches_now(), ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -843,6 +883,7 @@ static int set_kmers(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind kind
     if (n) CK(cudaMemcpyAsync(ctx->kmers_a.p, src, n * sizeof(mb_kmer), kind, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_kmers = n;
+    ctx->kmers_src = nullptr;
     ctx->have_kmers = true;
     ctx->kmers_sorted = false;
     ctx->have_matches = ctx->have_results = false;
@@ -854,6 +895,7 @@ static int set_matches(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind ki
     if (n) CK(cudaMemcpyAsync(ctx->matches_a.p, src, n * sizeof(mb_match), kind, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_matches = n;
+    ctx->matches_src = nullptr;
     ctx->have_matches = true;
     ctx->matches_sorted = false;
     ctx->segments_valid = false;
@@ -871,7 +913,7 @@ int mb_export_kmers_device(mb_ctx *ctx, void *dst, size_t cap, size_t *n) {
     *n = ctx->n_kmers;
     if (cap < ctx->n_kmers) return fail(ctx, MB_E_CAPACITY, "k-mer output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_kmers) CK(cudaMemcpyAsync(dst, ctx->kmers_a.p, ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->n_kmers) CK(cudaMemcpyAsync(dst, ctx->kmers_now(), ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -881,7 +923,7 @@ int mb_export_matches_device(mb_ctx *ctx, void *dst, size_t cap, size_t *n) {
     *n = ctx->n_matches;
     if (cap < ctx->n_matches) return fail(ctx, MB_E_CAPACITY, "match output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_matches) CK(cudaMemcpyAsync(dst, ctx->matches_a.p, ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->n_matches) CK(cudaMemcpyAsync(dst, ctx->matches_now(), ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -896,14 +938,14 @@ int mb_kmers_device(mb_ctx *ctx, void **dptr, size_t *n) {
     if (!ctx || !dptr || !n) return MB_E_ARG;
     if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
     CK(cudaStreamSynchronize(ctx->stream));
-    *dptr = ctx->kmers_a.p; *n = ctx->n_kmers;
+    *dptr = (void *) ctx->kmers_now(); *n = ctx->n_kmers;
     return MB_OK;
 }
 int mb_matches_device(mb_ctx *ctx, void **dptr, size_t *n) {
     if (!ctx || !dptr || !n) return MB_E_ARG;
     if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
     CK(cudaStreamSynchronize(ctx->stream));
-    *dptr = ctx->matches_a.p; *n = ctx->n_matches;
+    *dptr = (void *) ctx->matches_now(); *n = ctx->n_matches;
     return MB_OK;
 }
 
@@ -914,7 +956,9 @@ int mb_partition_kmers(mb_ctx *ctx, const uint64_t *bounds, int n_shards, uint64
     KmerOwnerKey key;
     key.n_bounds = n_shards - 1;
     for (int i = 0; i < 8; ++i) key.bounds[i] = i < n_shards - 1 ? bounds[i] : ~0ull;
-    return partition_by<mb_kmer, KmerOwnerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, n_shards, counts);
+    const int rc = partition_by<mb_kmer, KmerOwnerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, n_shards, counts, ctx->kmers_src);
+    if (rc == MB_OK) ctx->kmers_src = nullptr;
+    return rc;
 }
 
 int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint64_t *counts) {
@@ -923,7 +967,125 @@ int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint
     CK(cudaSetDevice(ctx->par.device));
     MatchHomeKey key;
     key.reads_per_rank = reads_per_rank;
-    return partition_by<mb_match, MatchHomeKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, n_ranks, counts);
+    const int rc = partition_by<mb_match, MatchHomeKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, n_ranks, counts, ctx->matches_src);
+    if (rc == MB_OK) ctx->matches_src = nullptr;
+    return rc;
+}
+
+// ---- multi-GPU: peer-routed producers --------------------------------------------------------------------
+static cudaError_t alloc_fixed(DevBuf &b, size_t bytes) {
+    if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+    cudaError_t e = cudaMalloc(&b.p, bytes);
+    if (e != cudaSuccess) { b.p = nullptr; return e; }
+    b.cap = bytes;
+    return cudaSuccess;
+}
+
+int mb_peer_alloc(mb_ctx *ctx, size_t kmer_cap, size_t match_cap, mb_peer_mem *out) {
+    if (!ctx || !out || !kmer_cap || !match_cap) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->routed = false;
+    ctx->kmers_src = ctx->matches_src = nullptr;
+    CK(alloc_fixed(ctx->peer_kmers, kmer_cap * sizeof(mb_kmer)));
+    CK(alloc_fixed(ctx->peer_matches, match_cap * sizeof(mb_match)));
+    CK(alloc_fixed(ctx->peer_cnt, 256));
+    CK(cudaMemsetAsync(ctx->peer_cnt.p, 0, 256, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->peer_kmer_cap = kmer_cap; ctx->peer_match_cap = match_cap;
+    out->kmers = ctx->peer_kmers.p; out->matches = ctx->peer_matches.p; out->counters = ctx->peer_cnt.p;
+    out->kmer_cap = kmer_cap; out->match_cap = match_cap;
+    return MB_OK;
+}
+
+int mb_ipc_export(mb_ctx *ctx, const void *dptr, unsigned char handle[64]) {
+    if (!ctx || !dptr || !handle) return MB_E_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    CK(cudaSetDevice(ctx->par.device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, const_cast<void *>(dptr)));
+    memcpy(handle, &h, 64);
+    return MB_OK;
+}
+int mb_ipc_open(mb_ctx *ctx, const unsigned char handle[64], void **dptr) {
+    if (!ctx || !dptr || !handle) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    CK(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return MB_OK;
+}
+int mb_ipc_close(mb_ctx *ctx, void *dptr) {
+    if (!ctx || !dptr) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaIpcCloseMemHandle(dptr));
+    return MB_OK;
+}
+
+int mb_peer_attach(mb_ctx *ctx, uint32_t rank, uint32_t n_ranks, const mb_peer_mem *peers, const uint64_t *bounds,
+                   uint32_t reads_per_rank) {
+    if (!ctx || !peers || n_ranks < 1 || n_ranks > MB_MAX_RANKS || rank >= n_ranks || (!bounds && n_ranks > 1) || !reads_per_rank)
+        return MB_E_ARG;
+    if (!ctx->peer_kmers.p || peers[rank].kmers != ctx->peer_kmers.p || peers[rank].matches != ctx->peer_matches.p ||
+        peers[rank].counters != ctx->peer_cnt.p)
+        return fail(ctx, MB_E_ARG, "peers[rank] must be this context's own mb_peer_alloc result");
+    CK(cudaSetDevice(ctx->par.device));
+    Route &r = ctx->route;
+    memset(&r, 0, sizeof(r));
+    r.n = n_ranks; r.rank = rank; r.reads_per_rank = reads_per_rank;
+    for (uint32_t i = 0; i < MB_MAX_RANKS; ++i) r.bounds[i] = (i + 1 < n_ranks) ? bounds[i] : ~0ull;
+    for (uint32_t i = 0; i < n_ranks; ++i) {
+        if (!peers[i].kmers || !peers[i].matches || !peers[i].counters) return fail(ctx, MB_E_ARG, "peer receive side missing");
+        r.kmers[i] = peers[i].kmers; r.matches[i] = peers[i].matches;
+        r.counters[i] = reinterpret_cast<unsigned long long *>(peers[i].counters);
+        r.kmer_cap[i] = peers[i].kmer_cap; r.match_cap[i] = peers[i].match_cap;
+    }
+    CK(ctx->route_dev.ensure(sizeof(Route)));
+    CK(cudaMemcpyAsync(ctx->route_dev.p, &r, sizeof(Route), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->routed = true;
+    return MB_OK;
+}
+
+// read this rank's arrival counter `which` (0 k-mers, 1 matches) and clear it for the next batch
+static int take_counter(mb_ctx *ctx, int which, unsigned long long *n) {
+    unsigned long long *c = ctx->peer_cnt.as<unsigned long long>() + which;
+    if (int rc = read_back(ctx, c, n)) return rc;
+    CK(cudaMemsetAsync(c, 0, sizeof(unsigned long long), ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+int mb_take_routed_kmers(mb_ctx *ctx, size_t *n) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
+    CK(cudaSetDevice(ctx->par.device));
+    unsigned long long got = 0;
+    if (int rc = take_counter(ctx, 0, &got)) return rc;
+    if (n) *n = (size_t) got;
+    ctx->have_kmers = ctx->kmers_sorted = ctx->have_matches = ctx->have_results = false;
+    if (got > ctx->peer_kmer_cap) return fail(ctx, MB_E_CAPACITY, "more k-mers arrived than the receive buffer holds");
+    ctx->n_kmers = got;
+    ctx->kmers_src = ctx->peer_kmers.p;
+    ctx->have_kmers = true;
+    return MB_OK;
+}
+
+int mb_take_routed_matches(mb_ctx *ctx, size_t *n) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
+    CK(cudaSetDevice(ctx->par.device));
+    unsigned long long got = 0;
+    if (int rc = take_counter(ctx, 1, &got)) return rc;
+    if (n) *n = (size_t) got;
+    ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
+    ctx->segments_valid = false;
+    if (got > ctx->peer_match_cap) return fail(ctx, MB_E_CAPACITY, "more matches arrived than the receive buffer holds");
+    ctx->n_matches = got;
+    ctx->matches_src = ctx->peer_matches.p;
+    ctx->have_matches = true;
+    return MB_OK;
 }
 
 int mb_get_timings(mb_ctx *ctx, mb_phase_times *t) {

@@ -32,6 +32,27 @@ MB_HD u32 qi_pos(u64 q) { return (u32) q; }
 MB_HD u32 qi_seq(u64 q) { return (u32) ((q >> 32) & 0x1FFFFFFFu); }
 MB_HD u32 qi_frame(u64 q) { return (u32) (q >> 61); }
 
+// ---- multi-GPU routing (mb_peer_attach): where the producers send their records ---------------------
+// k-mers go to the shard that owns their value (owner = number of bounds <= value; bounds = first value of shards
+// 1..n-1, i.e. the `split` cut points of KmerMatcher.cpp:127-271); matches go to the home rank of their read.
+struct Route {
+    u32 n, rank, reads_per_rank, pad;
+    u64 bounds[MB_MAX_RANKS];
+    void *kmers[MB_MAX_RANKS];
+    void *matches[MB_MAX_RANKS];
+    unsigned long long *counters[MB_MAX_RANKS];      // [0] k-mers arrived, [1] matches arrived
+    u64 kmer_cap[MB_MAX_RANKS], match_cap[MB_MAX_RANKS];
+};
+MB_HD u32 route_owner(const Route &r, u64 value) {
+    u32 d = 0;
+    for (u32 i = 0; i + 1 < r.n; ++i) d += r.bounds[i] <= value ? 1u : 0u;
+    return d;
+}
+MB_HD u32 route_home(const Route &r, u32 seq) {
+    const u32 h = (seq - 1u) / r.reads_per_rank;
+    return h < r.n ? h : r.n - 1u;
+}
+
 // ---- read-length arithmetic: src/commons/LocalUtil.h:45-59 ----------------------------------------
 MB_HD int max_covered_length(int len) {
     int r = len % 3;

@@ -62,10 +62,14 @@ constexpr size_t extract_smem_bytes() { return (size_t) EX_TILE * 2 * sizeof(mb_
 // of its phase's stream — forward strand with the first codon most significant, reverse strand with the stream built
 // in the opposite order (MetamerScanner::next, KmerScanner.h:82-117).  The legacy base-21 format keeps the
 // per-window translation.
-template <bool FMT2>
+//
+// ROUTED (multi-GPU, mb_extract_kmers_routed): the staged k-mers of half a tile are grouped by owner shard in shared
+// memory (second half of the staging area), one reservation per owner on the OWNER's arrival counter (remote atomic
+// over NVLink), then every owner's run is written with coalesced 16-byte peer stores.
+template <bool FMT2, bool ROUTED>
 __global__ void __launch_bounds__(EX_THREADS)
 k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__restrict__ tables, mb_kmer *__restrict__ out,
-          unsigned long long *__restrict__ out_count, u64 out_cap) {
+          unsigned long long *__restrict__ out_count, u64 out_cap, const Route *__restrict__ route_g) {
     extern __shared__ __align__(16) unsigned char ex_raw[];
     ulonglong2 *s_out = reinterpret_cast<ulonglong2 *>(ex_raw);          // EX_TILE * 2 records
     __shared__ u16 s_code[EX_THREADS + 4];
@@ -75,8 +79,15 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
     __shared__ u8 s_codonR[64];
     __shared__ u32 s_fill;
     __shared__ unsigned long long s_base;
+    __shared__ Route s_route;
+    __shared__ u32 s_dcnt[MB_MAX_RANKS], s_dloc[MB_MAX_RANKS + 1];
+    __shared__ unsigned long long s_dbase[MB_MAX_RANKS];
 
     const u32 tid = threadIdx.x, lane = tid & 31;
+    if (ROUTED) {
+        for (u32 i = tid; i < sizeof(Route) / 8; i += EX_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
+        if (tid < MB_MAX_RANKS) s_dcnt[tid] = 0;
+    }
     const u32 tile = blockIdx.x;
     const u64 g0 = (u64) tile * EX_TILE;
 
@@ -146,7 +157,9 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
     int used = 0;
 
 #pragma unroll
-    for (int i = 0; i < EX_PER_THREAD; ++i) {
+    for (int half = 0; half < (ROUTED ? 2 : 1); ++half) {
+#pragma unroll
+    for (int i = half * (EX_PER_THREAD / 2); i < (ROUTED ? (half + 1) * (EX_PER_THREAD / 2) : EX_PER_THREAD); ++i) {
         bool ok = false;
         u32 x = 0;
         if (any) {
@@ -208,6 +221,56 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
             }
         }
     }
+    if (ROUTED) {
+        // ---- group the <= EX_TILE staged records by owner, reserve, write runs to the owners ----
+        __syncthreads();
+        const u32 total = s_fill;
+        const u32 nr = s_route.n;
+        constexpr int PER = EX_TILE / EX_THREADS;
+        u32 pos[PER];
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+            const u32 k = tid + j * EX_THREADS;
+            const u32 d = k < total ? route_owner(s_route, s_out[k].x) : 0xFFFFFFFFu;
+            pos[j] = 0;
+            for (u32 dd = 0; dd < nr; ++dd) {
+                const u32 mask = __ballot_sync(0xFFFFFFFFu, d == dd);
+                if (!mask) continue;
+                u32 base = 0;
+                if (lane == (u32) (__ffs(mask) - 1)) base = atomicAdd(&s_dcnt[dd], (u32) __popc(mask));
+                base = __shfl_sync(0xFFFFFFFFu, base, __ffs(mask) - 1);
+                if (d == dd) pos[j] = (dd << 16) | (base + __popc(mask & ((1u << lane) - 1u)));
+            }
+        }
+        __syncthreads();
+        if (tid < nr) s_dbase[tid] = s_dcnt[tid] ? atomicAdd(s_route.counters[tid], (unsigned long long) s_dcnt[tid]) : 0ull;
+        if (tid == 32) {
+            u32 acc = 0;
+            for (u32 dd = 0; dd < nr; ++dd) { s_dloc[dd] = acc; acc += s_dcnt[dd]; }
+            s_dloc[nr] = acc;
+            if (total) atomicAdd(out_count, (unsigned long long) total);          // local statistic: k-mers this rank produced
+        }
+        __syncthreads();
+        ulonglong2 *s_ord = s_out + EX_TILE;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+            const u32 k = tid + j * EX_THREADS;
+            if (k < total) s_ord[s_dloc[pos[j] >> 16] + (pos[j] & 0xFFFFu)] = s_out[k];
+        }
+        __syncthreads();
+        for (u32 k = tid; k < total; k += EX_THREADS) {
+            u32 d = 0;
+            while (d + 1 < nr && s_dloc[d + 1] <= k) ++d;
+            const u64 idx = s_dbase[d] + (k - s_dloc[d]);
+            if (idx < s_route.kmer_cap[d]) reinterpret_cast<ulonglong2 *>(s_route.kmers[d])[idx] = s_ord[k];
+        }
+        __syncthreads();
+        if (tid == 0) s_fill = 0;
+        if (tid < MB_MAX_RANKS) s_dcnt[tid] = 0;
+        __syncthreads();
+    }
+    }   // half
+    if (!ROUTED) {
     __syncthreads();
     const u32 total = s_fill;
     if (tid == 0 && total) s_base = atomicAdd(out_count, (unsigned long long) total);
@@ -217,6 +280,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
         ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(out);
         for (u32 k = tid; k < total; k += EX_THREADS)
             if (base + k < out_cap) dst[base + k] = s_out[k];
+    }
     }
 }
 

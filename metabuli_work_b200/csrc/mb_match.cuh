@@ -183,6 +183,7 @@ struct MatchOut {
     u64 cap;
     unsigned long long *counter;   // total matches produced (may exceed cap)
     u32 *error_flag;               // set when a DB tax ID has no species (KmerMatcher.cpp:433-441)
+    const Route *route;            // multi-GPU: matches go to their read's home rank (shared-memory copy), else nullptr
 };
 
 // One match record (Match.h:9-25 payload) from query q and DB k-mer ordinal `kidx` with value t, distance d.
@@ -200,11 +201,73 @@ __device__ __forceinline__ void make_match(const DbView &db, const MatchOut &mo,
     rec[2] = (t & 0xFFFFFFull) | ((u64) pack << 32) | ((u64) d << 48);
 }
 
+// Routed flush (mb_match_kmers_routed): the staged matches are grouped by home rank inside the staging buffer, one
+// reservation per home on the HOME's arrival counter (remote atomic over NVLink, lanes 0..n-1 in parallel), then each
+// home's run leaves with coalesced 8-byte peer stores.  Warp-synchronous.
+__device__ __noinline__ void warp_flush_routed(const MatchOut &mo, u64 *stage, u32 fill) {
+    const Route &r = *mo.route;
+    const u32 lane = threadIdx.x & 31;
+    constexpr int PER = (MT_STAGE + 31) / 32;
+    u64 w0[PER], w1[PER], w2[PER];
+    u32 d[PER], rank[PER];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        const u32 i = lane + 32 * j;
+        d[j] = 0xFFFFFFFFu; rank[j] = 0;
+        if (i < fill) { w0[j] = stage[i * 3]; w1[j] = stage[i * 3 + 1]; w2[j] = stage[i * 3 + 2]; d[j] = route_home(r, qi_seq(w0[j])); }
+    }
+    u32 mycnt = 0;                                  // lane dd: matches of this flush for home dd
+    for (u32 dd = 0; dd < r.n; ++dd) {
+        u32 run = 0;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+            const u32 mask = __ballot_sync(0xFFFFFFFFu, d[j] == dd);
+            if (d[j] == dd) rank[j] = run + __popc(mask & ((1u << lane) - 1u));
+            run += __popc(mask);
+        }
+        if (lane == dd) mycnt = run;
+    }
+    u32 incl = mycnt;
+#pragma unroll
+    for (int k = 1; k < 32; k <<= 1) {
+        const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, k);
+        if (lane >= (u32) k) incl += t;
+    }
+    const u32 excl = incl - mycnt;
+    unsigned long long base = 0;
+    if (lane < r.n && mycnt) base = atomicAdd(r.counters[lane] + 1, (unsigned long long) mycnt);
+    if (lane == 0) atomicAdd(mo.counter, (unsigned long long) fill);             // local statistic: matches this rank produced
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        const u32 e = __shfl_sync(0xFFFFFFFFu, excl, d[j] & 31u);
+        if (d[j] != 0xFFFFFFFFu) { const u32 o = (e + rank[j]) * 3; stage[o] = w0[j]; stage[o + 1] = w1[j]; stage[o + 2] = w2[j]; }
+    }
+    __syncwarp();
+    for (u32 dd = 0; dd < r.n; ++dd) {
+        const u32 cnt = __shfl_sync(0xFFFFFFFFu, mycnt, dd);
+        const u32 ex = __shfl_sync(0xFFFFFFFFu, excl, dd);
+        const unsigned long long b = __shfl_sync(0xFFFFFFFFu, base, dd);
+        if (!cnt) continue;
+        u64 *dst = reinterpret_cast<u64 *>(r.matches[dd]) + b * 3;
+        const u64 *src = stage + ex * 3;
+        const u64 cap = r.match_cap[dd];
+        if (b + cnt <= cap) {
+            for (u32 i = lane; i < cnt * 3; i += 32) dst[i] = src[i];
+        } else {
+            for (u32 i = lane; i < cnt * 3; i += 32)
+                if (b + i / 3 < cap) dst[i] = src[i];
+        }
+    }
+}
+
 // Flush the warp's staged matches: one reservation, coalesced 8-byte stores.  Warp-synchronous.
 __device__ __forceinline__ void warp_flush(const MatchOut &mo, u64 *stage, u32 &fill) {
     const u32 lane = threadIdx.x & 31;
     __syncwarp();
-    if (fill) {
+    if (fill && mo.route) {
+        warp_flush_routed(mo, stage, fill);
+    } else if (fill) {
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(mo.counter, (unsigned long long) fill);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
@@ -248,7 +311,16 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
                 const u64 t = s.vals[j];
                 const u32 d = (j - lo < 16) ? (u32) (dpack >> (4 * (j - lo))) & 15u : hamming_sum_lut(tb.lut2, q.value, t);
                 if (d > maxh) continue;
-                if (o < mo.cap) {
+                if (mo.route) {                                   // rare path: one reservation per record at its home
+                    u64 rec[3];
+                    make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
+                    const u32 h = route_home(*mo.route, qi_seq(rec[0]));
+                    const unsigned long long slot = atomicAdd(mo.route->counters[h] + 1, 1ull);
+                    if (slot < mo.route->match_cap[h]) {
+                        u64 *p = reinterpret_cast<u64 *>(mo.route->matches[h]) + slot * 3;
+                        p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
+                    }
+                } else if (o < mo.cap) {
                     u64 rec[3];
                     make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
                     u64 *p = reinterpret_cast<u64 *>(mo.out + o);
@@ -339,10 +411,18 @@ __device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, 
     return lo;
 }
 
-__global__ void __launch_bounds__(MT_THREADS)
+__global__ void __launch_bounds__(MT_THREADS, 3)
 k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
-        const u64 *__restrict__ qend_of, MatchOut mo, const Tables *__restrict__ tables, int format, u32 *block_ticket) {
+        const u64 *__restrict__ qend_of, MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *block_ticket,
+        const Route *__restrict__ route_g) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ Route s_route;
+    MatchOut mo = mo_in;
+    mo.route = nullptr;
+    if (route_g) {                                  // multi-GPU: matches leave for their home rank (warp_flush_routed)
+        for (u32 i = threadIdx.x; i < sizeof(Route) / 8; i += MT_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
+        mo.route = &s_route;
+    }
     MatchSmem &s = *reinterpret_cast<MatchSmem *>(smem_raw);
     MatchTables &tb = *reinterpret_cast<MatchTables *>(smem_raw + ((sizeof(MatchSmem) + 15) & ~(size_t) 15));
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -84,8 +84,46 @@ class OracleEngine:
     def fetch(self, used):
         return self.res, self.ids, self.cnt
 
+    # ---- fused form: on the device the producers write into peer memory; here an all-to-all stands in for the peer
+    # stores, so that the control flow of ShardedClassifier (barriers, takes, overflow agreement, regrow) is what runs
+    def peer_setup(self, group, rank, world, bounds, reads_per_rank, kmer_cap, match_cap):
+        self.g = dict(group=group, rank=rank, world=world, bounds=np.asarray(bounds, dtype=np.uint64), rpr=reads_per_rank,
+                      kmer_cap=kmer_cap, match_cap=match_cap)
+        self.setups = getattr(self, "setups", 0) + 1
 
-def _worker(rank, world, port, dbdir, s1, s2, seq_mode, bounds, per_rank, outdir):
+    def sync_tensor(self):
+        return torch.zeros(1, dtype=torch.int64)
+
+    def extract_routed(self):
+        from metabuli_work_b200.exchange import _all_to_all_records
+        n = self.extract()
+        counts = self.partition_kmers(self.g["bounds"])
+        self._arrived_k, _ = _all_to_all_records(self.export_kmers(), counts, 2, self.g["group"])
+        return n
+
+    def take_kmers(self):
+        n = self._arrived_k.shape[0]
+        if n > self.g["kmer_cap"]:
+            return n, True
+        self.import_kmers(self._arrived_k)
+        return n, False
+
+    def match_routed(self):
+        from metabuli_work_b200.exchange import _all_to_all_records
+        n = self.match()
+        counts = self.partition_matches(self.g["rpr"], self.g["world"])
+        self._arrived_m, _ = _all_to_all_records(self.export_matches(), counts, 3, self.g["group"])
+        return n
+
+    def take_matches(self):
+        n = self._arrived_m.shape[0]
+        if n > self.g["match_cap"]:
+            return n, True
+        self.import_matches(self._arrived_m)
+        return n, False
+
+
+def _worker(rank, world, port, dbdir, s1, s2, seq_mode, bounds, per_rank, outdir, fused):
     sys.path.insert(0, ROOT)
     from metabuli_work_b200.exchange import ShardedClassifier
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -95,7 +133,7 @@ def _worker(rank, world, port, dbdir, s1, s2, seq_mode, bounds, per_rank, outdir
         a, b = rank * per_rank, min(len(s1), (rank + 1) * per_rank)
         batch = orc.Batch(s1[a:b], None if s2 is None else s2[a:b])
         eng = OracleEngine(dbdir, seq_mode)
-        sc = ShardedClassifier(eng, bounds, per_rank)
+        sc = ShardedClassifier(eng, bounds, per_rank, fused=fused, match_cap=16 if fused else None)
         sc.stage(batch, None, batch.len)
         used = sc.classify_staged()
         res, ids, cnt = sc.fetch(used)
@@ -104,13 +142,14 @@ def _worker(rank, world, port, dbdir, s1, s2, seq_mode, bounds, per_rank, outdir
         with open(os.path.join(outdir, f"tc{rank}.txt"), "w") as f:
             f.write("\n".join(tc))
         np.save(os.path.join(outdir, f"stats{rank}.npy"), np.array([sc.stats["kmers_extracted"], sc.stats["kmers_owned"],
-                                                                  sc.stats["matches_owned"], sc.stats["matches_home"]]))
+                                                                  sc.stats["matches_owned"], sc.stats["matches_home"], sc.regrows]))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("case,world", [("plain_paired", 2), ("sync_paired", 3), ("sync_long", 2)])
-def test_sharded_equals_single(golden, tmp_path, case, world):
+@pytest.mark.parametrize("case,world,fused", [("plain_paired", 2, False), ("sync_paired", 3, False), ("sync_long", 2, False),
+                                              ("plain_paired", 2, True), ("sync_paired", 3, True)])
+def test_sharded_equals_single(golden, tmp_path, case, world, fused):
     meta = golden.cases[case]
     dbdir = golden.dbdir(case)
     _, s1, s2 = golden.reads(case)
@@ -130,7 +169,7 @@ def test_sharded_equals_single(golden, tmp_path, case, world):
     k, m, res, ids, cnt = orc.classify(db, p, orc.Batch(s1, s2))
     db.close()
     port = 29600 + (os.getpid() % 300)
-    mp.spawn(_worker, args=(world, port, dbdir, s1, s2, meta["seq_mode"], bounds, per_rank, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, dbdir, s1, s2, meta["seq_mode"], bounds, per_rank, str(tmp_path), fused), nprocs=world, join=True)
     got_res = np.concatenate([np.load(tmp_path / f"res{r}.npy") for r in range(world)])
     got_tc = []
     for r in range(world):
@@ -147,3 +186,5 @@ def test_sharded_equals_single(golden, tmp_path, case, world):
     assert st[:, 0].sum() == st[:, 1].sum() == len(k)          # every k-mer reached exactly one owner
     assert st[:, 2].sum() == st[:, 3].sum() == len(m)          # every match came home
     assert (st[:, 1] > 0).all()                                # the shards really split the work
+    if fused:
+        assert (st[:, 4] >= 1).all()                           # the 16-record match buffer overflowed and was regrown

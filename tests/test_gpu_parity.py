@@ -283,3 +283,69 @@ def test_partition_kernels(golden, mb):
     assert np.array_equal(counts, np.bincount(home, minlength=3).astype(np.uint64))
     assert np.array_equal(m1, np.concatenate([m0[home == g] for g in range(3)]))
     clf.close()
+
+
+@pytest.mark.parametrize("case,world", [("plain_paired", 3), ("sync_paired", 2), ("legacy_paired", 2)])
+def test_routed_producers_one_gpu(golden, mb, case, world):
+    """The fused multi-GPU form on ONE GPU: `world` contexts (one DB shard each, a slice of the reads each) wired to each
+    other's receive buffers by plain device pointers — the same kernels write the same "peer" stores, only the NVLink
+    hop is missing.  k-mers must arrive at the shard that owns them, matches at their read's home context, and every
+    context's results must equal the single-context oracle run of its reads."""
+    meta = golden.cases[case]
+    dbdir = golden.dbdir(case)
+    _, s1, s2 = golden.reads(case)
+    n = len(s1)
+    per = (n + world - 1) // world
+    db = orc.Db(dbdir)
+    p = db.params(seq_mode=meta["seq_mode"])
+    ok, om, ores, oids, ocnt = orc.classify(db, p, orc.Batch(s1, s2), threads=4)
+    db.close()
+    ctxs = [mb.Classifier(dbdir, seq_mode=meta["seq_mode"], shard=g, n_shards=world) for g in range(world)]
+    try:
+        bounds = ctxs[0].shard_bounds()
+        assert len(bounds) == world - 1
+        mem = [c.peer_alloc(len(ok) + 64, len(om) + 64) for c in ctxs]
+        for g, c in enumerate(ctxs):
+            c.peer_attach(g, mem, bounds, per)
+        emitted = 0
+        for g, c in enumerate(ctxs):
+            a, b = g * per, min(n, (g + 1) * per)
+            bases, offsets, lens = mb.pack_reads(s1[a:b], None if s2 is None else s2[a:b])
+            c.set_read_id_base(g * per)
+            c.stage(bases, offsets, lens)
+            emitted += c.extract_routed()
+        assert emitted == len(ok)
+        owner = np.searchsorted(bounds, ok["value"], side="right")
+        m_emitted = 0
+        for g, c in enumerate(ctxs):
+            got, over = c.take_routed_kmers()
+            assert not over and got == int((owner == g).sum())
+            assert np.array_equal(canon_k(c.kmers()), ok[owner == g])         # the right k-mers reached shard g
+            c.sort_kmers()
+            m_emitted += c.match_routed()
+        assert m_emitted == len(om)
+        home = (((om["qinfo"] >> np.uint64(32)) & np.uint64(0x1FFFFFFF)).astype(np.int64) - 1) // per
+        for g, c in enumerate(ctxs):
+            got, over = c.take_routed_matches()
+            assert not over and got == int((home == g).sum())
+            assert np.array_equal(orc.sort_matches(as_orc_matches(c.matches())), om[home == g])
+            c.sort_matches()
+            used = c.score()
+            res, ids, cnt = c.fetch(used)
+            a, b = g * per, min(n, (g + 1) * per)
+            sub = ores[a:b]
+            assert compare_results(res, ids, cnt, sub, oids, ocnt) == []
+        # a receive buffer that is too small is reported, not overrun
+        small = [c.peer_alloc(len(ok) + 64, 8) for c in ctxs]
+        for g, c in enumerate(ctxs):
+            c.peer_attach(g, small, bounds, per)
+        for c in ctxs:
+            c.extract_routed()
+        for c in ctxs:
+            c.take_routed_kmers()
+            c.sort_kmers()
+            c.match_routed()
+        assert any(c.take_routed_matches()[1] for c in ctxs)
+    finally:
+        for c in ctxs:
+            c.close()
