@@ -118,15 +118,12 @@ struct mb_ctx {
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
     bool segments_valid = false;      // seg_begin/seg_end describe matches_a
     // multi-GPU routing (mb_peer_*): this context's receive side and the routing table of all ranks
-    DevBuf peer_kmers, peer_matches, peer_cnt, route_dev;
+    DevBuf peer_kmers, peer_matches, peer_cnt, route_dev, sent_cnt;
     u64 peer_kmer_cap = 0, peer_match_cap = 0;
     Route route;
+    unsigned long long *peer_counters[MB_MAX_RANKS] = {};   // every rank's arrival counters (peer addresses)
     bool routed = false;
-    const void *kmers_src = nullptr;   // resident k-mers live in the receive buffer until the sort reads them
-    const void *matches_src = nullptr; // same for matches
-
-    const mb_kmer *kmers_now() const { return kmers_src ? (const mb_kmer *) kmers_src : kmers_a.as<mb_kmer>(); }
-    const mb_match *matches_now() const { return matches_src ? (const mb_match *) matches_src : matches_a.as<mb_match>(); }
+    SegIn kmers_seg = {}, matches_seg = {};    // n > 0: the resident k-mers / matches still lie in the receive regions
 
     Counters *dcnt() const { return counters.as<Counters>(); }
 };
@@ -188,16 +185,24 @@ static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
 
 // ---- radix sort driver --------------------------------------------------------------------------------
 template <typename Rec, typename Key, int ITEMS>
-static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes, int kid_base, const void *src = nullptr) {
-    // src: the records are in a read-only buffer outside the ping-pong pair (a peer receive buffer); the histogram and
-    // the first pass read it, the result ends up in `a` like always
+static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes, int kid_base, SegIn *seg_in = nullptr) {
+    // seg_in (n > 0): the records lie in the regions of a peer receive buffer, outside the ping-pong pair; the histogram
+    // and the first pass read them there, the result ends up in `a` like always and *seg_in is cleared
+    SegIn seg = {};
+    if (seg_in && seg_in->n) { seg = *seg_in; seg_in->n = 0; }
     if (n == 0) return MB_OK;
     if (n_passes == 0) {
-        if (src) { CK(a.ensure(n * sizeof(Rec))); CK(cudaMemcpyAsync(a.p, src, n * sizeof(Rec), cudaMemcpyDeviceToDevice, ctx->stream)); }
+        if (seg.n) {
+            CK(a.ensure(n * sizeof(Rec)));
+            for (u32 r = 0; r < seg.n; ++r)
+                if (seg.prefix[r + 1] > seg.prefix[r])
+                    CK(cudaMemcpyAsync(a.as<Rec>() + seg.prefix[r], seg.base[r], (seg.prefix[r + 1] - seg.prefix[r]) * sizeof(Rec),
+                                       cudaMemcpyDeviceToDevice, ctx->stream));
+        }
         return MB_OK;
     }
     if (n_passes > RS_MAX_PASSES) return fail(ctx, MB_E_ARG, "too many radix passes");
-    if (src) CK(a.ensure(n * sizeof(Rec)));
+    if (seg.n) CK(a.ensure(n * sizeof(Rec)));
     constexpr u64 TILE = (u64) RS_THREADS * ITEMS;
     const u64 tiles = (n + TILE - 1) / TILE;
     CK(b.ensure(n * sizeof(Rec)));
@@ -206,22 +211,33 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     CK(cudaMemsetAsync(ctx->hist.p, 0, sizeof(u64) * RS_BINS * n_passes, ctx->stream));
     CK(cudaMemsetAsync(&ctx->dcnt()->trivial, 0, sizeof(u32) * RS_MAX_PASSES, ctx->stream));
     const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
-    KL(kid_base + 0, k_radix_hist<Rec, Key><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
-        src ? (const Rec *) src : a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>()));
+    if (seg.n)
+        KL(kid_base + 0, k_radix_hist<Rec, Key, true><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
+            a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>(), seg));
+    else
+        KL(kid_base + 0, k_radix_hist<Rec, Key, false><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
+            a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>(), seg));
     KL(kid_base + 1, k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial));
     constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
     static const int radix_dbg = getenv("MB_RADIX_DBG") ? atoi(getenv("MB_RADIX_DBG")) : 0;     // timing experiments only
     static bool attr_set = false;
     if (!attr_set) {
-        CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         attr_set = true;
     }
     for (int p = 0; p < n_passes; ++p) {
         CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * RS_BINS * sizeof(u64), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->radix_ticket, 0, sizeof(u32), ctx->stream));
-        KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
-            (p == 0 && src) ? (const Rec *) src : a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
-            &ctx->dcnt()->radix_ticket, radix_dbg));
+        if (seg.n)
+            KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS, true><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
+                a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
+                &ctx->dcnt()->radix_ticket, radix_dbg, seg));
+        else
+            KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS, false><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
+                a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
+                &ctx->dcnt()->radix_ticket, radix_dbg, seg));
+        seg.n = 0;
         std::swap(a.p, b.p);
         std::swap(a.cap, b.cap);
     }
@@ -230,7 +246,7 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
 
 // stable multi-way partition = one radix pass whose digit is the destination rank
 template <typename Rec, typename Key, int ITEMS>
-static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_parts, uint64_t *counts, const void *src) {
+static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_parts, uint64_t *counts, SegIn *src) {
     for (int i = 0; i < n_parts; ++i) counts[i] = 0;
     if (n == 0) return MB_OK;
     if (int rc = radix_sort<Rec, Key, ITEMS>(ctx, a, b, n, key, 1, -100, src)) return rc;
@@ -243,7 +259,24 @@ static int partition_by(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key
     return MB_OK;
 }
 
+// records that still lie in the regions of a receive buffer are gathered into the ordinary resident buffer
+template <typename Rec>
+static int materialize(mb_ctx *ctx, SegIn &seg, DevBuf &a, u64 n) {
+    if (!seg.n) return MB_OK;
+    CK(a.ensure((n + 1) * sizeof(Rec)));
+    for (u32 r = 0; r < seg.n; ++r)
+        if (seg.prefix[r + 1] > seg.prefix[r])
+            CK(cudaMemcpyAsync(a.as<Rec>() + seg.prefix[r], seg.base[r], (seg.prefix[r + 1] - seg.prefix[r]) * sizeof(Rec),
+                               cudaMemcpyDeviceToDevice, ctx->stream));
+    seg.n = 0;
+    return MB_OK;
+}
+#define MATERIALIZE_K() do { if (int rc_ = materialize<mb_kmer>(ctx, ctx->kmers_seg, ctx->kmers_a, ctx->n_kmers)) return rc_; } while (0)
+#define MATERIALIZE_M() do { if (int rc_ = materialize<mb_match>(ctx, ctx->matches_seg, ctx->matches_a, ctx->n_matches)) return rc_; } while (0)
+
 extern "C" {
+
+static int publish_sent(mb_ctx *ctx, int which);
 
 void mb_default_params(mb_params *p) {
     memset(p, 0, sizeof(*p));
@@ -497,7 +530,7 @@ static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_kmers = ctx->kmers_sorted = ctx->have_matches = ctx->have_results = false;
     ctx->n_kmers = 0;
-    ctx->kmers_src = nullptr;
+    ctx->kmers_seg.n = 0;
     ctx->n_samples = 0;               // the per-kernel table covers one pass of the device stages
     ctx->launches = 0;
     const u32 n_tiles = (u32) ((ctx->n_bases + EX_TILE - 1) / EX_TILE);
@@ -508,6 +541,7 @@ static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
         a.syncmer = ctx->par.syncmer; a.smer_len = ctx->par.smer_len; a.seq_base = ctx->seq_base;
         CK(ctx->tile_mate.ensure(((size_t) n_tiles + 1) * sizeof(u32)));
         if (!routed) CK(ctx->kmers_a.ensure((ctx->kmer_bound + 1) * sizeof(mb_kmer)));
+        else CK(cudaMemsetAsync(ctx->route.sent_k, 0, MB_MAX_RANKS * sizeof(unsigned long long), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->kmer_count, 0, sizeof(unsigned long long), ctx->stream));
         KL(KID_TILE_MATE, k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>()));
         static bool ex_attr = false;
@@ -528,6 +562,7 @@ static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
         else if (a.format == 2) KL(KID_EXTRACT_WRITE, k_extract<true, true><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
         else if (!routed) KL(KID_EXTRACT_WRITE, k_extract<false, false><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
         else KL(KID_EXTRACT_WRITE, k_extract<false, true><<<n_tiles, EX_THREADS, sm, ctx->stream>>>(a, tm, tb, out, cnt, ctx->kmer_bound, rt));
+        if (routed) { if (int rc = publish_sent(ctx, 0)) return rc; }
         unsigned long long total = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->kmer_count, &total)) return rc;
         if (total > ctx->kmer_bound) return fail(ctx, MB_E_DATA, "internal: extracted more k-mers than the slot bound");
@@ -556,11 +591,10 @@ int mb_sort_kmers(mb_ctx *ctx) {
     const int passes = bits / 8;
     static const int k_items = getenv("MB_KSORT_ITEMS") ? atoi(getenv("MB_KSORT_ITEMS")) : 16;     // tuning knob
     int rc = 0;
-    if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, ctx->kmers_src);
-    else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, ctx->kmers_src);
-    else rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, ctx->kmers_src);
+    if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+    else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+    else rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
     if (rc) return rc;
-    ctx->kmers_src = nullptr;
     mark(ctx, EV_SORTK);
     ctx->kmers_sorted = true;
     return MB_OK;
@@ -570,7 +604,7 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_kmers || !ctx->kmers_sorted) return fail(ctx, MB_E_ARG, "sorted k-mers required");
     if (routed && !ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
-    ctx->matches_src = nullptr;
+    ctx->matches_seg.n = 0;
     if (ctx->max_taxid < 0) return fail(ctx, MB_E_ARG, "mb_load_taxonomy first");
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
@@ -584,7 +618,8 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
                                                                    ctx->n_kmers, ctx->sort_shift, qstart, qend));
         static bool match_attr_set = false;
         if (!match_attr_set) {
-            CK(cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
             match_attr_set = true;
         }
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
@@ -599,11 +634,17 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
             mo.out = routed ? nullptr : ctx->matches_a.as<mb_match>(); mo.cap = routed ? 0 : cap;
             mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag; mo.route = nullptr;
             CK(cudaMemsetAsync(&ctx->dcnt()->match_ticket, 0, sizeof(u32), ctx->stream));
+            if (routed) CK(cudaMemsetAsync(ctx->route.sent_m, 0, MB_MAX_RANKS * sizeof(unsigned long long), ctx->stream));
             const unsigned grid = (unsigned) std::min<u64>(nb, 148ull * 3);     // persistent: 3 CTAs per SM (70 KB smem each)
-            KL(KID_MATCH, k_match<<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
-                              db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
-                              ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket,
-                              routed ? ctx->route_dev.as<Route>() : nullptr));
+            if (!routed)
+                KL(KID_MATCH, k_match<false><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
+                                  db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
+                                  ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, nullptr));
+            else
+                KL(KID_MATCH, k_match<true><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
+                                  db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
+                                  ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, ctx->route_dev.as<Route>()));
+            if (routed) { if (int rc = publish_sent(ctx, 1)) return rc; }
             unsigned long long total = 0;
             if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;
             if (routed || total <= cap) { ctx->n_matches = total; break; }
@@ -668,12 +709,11 @@ int mb_sort_matches(mb_ctx *ctx) {
         const int seq_passes = (key.seq_bits + 7) / 8;
         static const int m_items = getenv("MB_MSORT_ITEMS") ? atoi(getenv("MB_MSORT_ITEMS")) : 12;    // tuning knob
         int rcs = 0;
-        if (m_items == 4) rcs = radix_sort<mb_match, MatchSeqKey, 4>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
-        else if (m_items == 6) rcs = radix_sort<mb_match, MatchSeqKey, 6>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
-        else if (m_items == 12) rcs = radix_sort<mb_match, MatchSeqKey, 12>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
-        else rcs = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, ctx->matches_src);
+        if (m_items == 4) rcs = radix_sort<mb_match, MatchSeqKey, 4>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, &ctx->matches_seg);
+        else if (m_items == 6) rcs = radix_sort<mb_match, MatchSeqKey, 6>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, &ctx->matches_seg);
+        else if (m_items == 12) rcs = radix_sort<mb_match, MatchSeqKey, 12>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, &ctx->matches_seg);
+        else rcs = radix_sort<mb_match, MatchSeqKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, qk, seq_passes, KID_MSORT_HIST, &ctx->matches_seg);
         if (rcs) return rcs;
-        ctx->matches_src = nullptr;
         if (int rc = compute_segments(ctx)) return rc;
         CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
         CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 2 * sizeof(u32), ctx->stream));
@@ -701,8 +741,7 @@ int mb_sort_matches(mb_ctx *ctx) {
     if (!done) {
         ctx->segments_valid = false;
         const int passes = (key.total_bits() + 7) / 8;
-        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST, ctx->matches_src)) return rc;
-        ctx->matches_src = nullptr;
+        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST, &ctx->matches_seg)) return rc;
     }
     mark(ctx, EV_SORTM);
     ctx->matches_sorted = true;
@@ -858,10 +897,12 @@ int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint
 int mb_copy_kmers(mb_ctx *ctx, mb_kmer *out, size_t cap, size_t *n) {
     if (!ctx || !n) return MB_E_ARG;
     if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MATERIALIZE_K();
     *n = ctx->n_kmers;
     if (cap < ctx->n_kmers) return fail(ctx, MB_E_CAPACITY, "k-mer output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_kmers) CK(cudaMemcpyAsync(out, ctx->kmers_now(), ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->n_kmers) CK(cudaMemcpyAsync(out, ctx->kmers_a.p, ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -869,10 +910,12 @@ int mb_copy_kmers(mb_ctx *ctx, mb_kmer *out, size_t cap, size_t *n) {
 int mb_copy_matches(mb_ctx *ctx, mb_match *out, size_t cap, size_t *n) {
     if (!ctx || !n) return MB_E_ARG;
     if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MATERIALIZE_M();
     *n = ctx->n_matches;
     if (cap < ctx->n_matches) return fail(ctx, MB_E_CAPACITY, "match output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_matches) CK(cudaMemcpyAsync(out, ctx->matches_now(), ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->n_matches) CK(cudaMemcpyAsync(out, ctx->matches_a.p, ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -883,7 +926,7 @@ static int set_kmers(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind kind
     if (n) CK(cudaMemcpyAsync(ctx->kmers_a.p, src, n * sizeof(mb_kmer), kind, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_kmers = n;
-    ctx->kmers_src = nullptr;
+    ctx->kmers_seg.n = 0;
     ctx->have_kmers = true;
     ctx->kmers_sorted = false;
     ctx->have_matches = ctx->have_results = false;
@@ -895,7 +938,7 @@ static int set_matches(mb_ctx *ctx, const void *src, size_t n, cudaMemcpyKind ki
     if (n) CK(cudaMemcpyAsync(ctx->matches_a.p, src, n * sizeof(mb_match), kind, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_matches = n;
-    ctx->matches_src = nullptr;
+    ctx->matches_seg.n = 0;
     ctx->have_matches = true;
     ctx->matches_sorted = false;
     ctx->segments_valid = false;
@@ -910,20 +953,24 @@ int mb_set_matches_device(mb_ctx *ctx, const void *d, size_t n) { return (!ctx |
 int mb_export_kmers_device(mb_ctx *ctx, void *dst, size_t cap, size_t *n) {
     if (!ctx || !n) return MB_E_ARG;
     if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MATERIALIZE_K();
     *n = ctx->n_kmers;
     if (cap < ctx->n_kmers) return fail(ctx, MB_E_CAPACITY, "k-mer output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_kmers) CK(cudaMemcpyAsync(dst, ctx->kmers_now(), ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->n_kmers) CK(cudaMemcpyAsync(dst, ctx->kmers_a.p, ctx->n_kmers * sizeof(mb_kmer), cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
 int mb_export_matches_device(mb_ctx *ctx, void *dst, size_t cap, size_t *n) {
     if (!ctx || !n) return MB_E_ARG;
     if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MATERIALIZE_M();
     *n = ctx->n_matches;
     if (cap < ctx->n_matches) return fail(ctx, MB_E_CAPACITY, "match output too small");
     CK(cudaSetDevice(ctx->par.device));
-    if (ctx->n_matches) CK(cudaMemcpyAsync(dst, ctx->matches_now(), ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->n_matches) CK(cudaMemcpyAsync(dst, ctx->matches_a.p, ctx->n_matches * sizeof(mb_match), cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
@@ -937,15 +984,19 @@ int mb_set_read_id_base(mb_ctx *ctx, uint32_t base) {
 int mb_kmers_device(mb_ctx *ctx, void **dptr, size_t *n) {
     if (!ctx || !dptr || !n) return MB_E_ARG;
     if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MATERIALIZE_K();
     CK(cudaStreamSynchronize(ctx->stream));
-    *dptr = (void *) ctx->kmers_now(); *n = ctx->n_kmers;
+    *dptr = ctx->kmers_a.p; *n = ctx->n_kmers;
     return MB_OK;
 }
 int mb_matches_device(mb_ctx *ctx, void **dptr, size_t *n) {
     if (!ctx || !dptr || !n) return MB_E_ARG;
     if (!ctx->have_matches) return fail(ctx, MB_E_ARG, "no matches resident");
+    CK(cudaSetDevice(ctx->par.device));
+    MATERIALIZE_M();
     CK(cudaStreamSynchronize(ctx->stream));
-    *dptr = (void *) ctx->matches_now(); *n = ctx->n_matches;
+    *dptr = ctx->matches_a.p; *n = ctx->n_matches;
     return MB_OK;
 }
 
@@ -956,9 +1007,7 @@ int mb_partition_kmers(mb_ctx *ctx, const uint64_t *bounds, int n_shards, uint64
     KmerOwnerKey key;
     key.n_bounds = n_shards - 1;
     for (int i = 0; i < 8; ++i) key.bounds[i] = i < n_shards - 1 ? bounds[i] : ~0ull;
-    const int rc = partition_by<mb_kmer, KmerOwnerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, n_shards, counts, ctx->kmers_src);
-    if (rc == MB_OK) ctx->kmers_src = nullptr;
-    return rc;
+    return partition_by<mb_kmer, KmerOwnerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, n_shards, counts, &ctx->kmers_seg);
 }
 
 int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint64_t *counts) {
@@ -967,9 +1016,7 @@ int mb_partition_matches(mb_ctx *ctx, uint32_t reads_per_rank, int n_ranks, uint
     CK(cudaSetDevice(ctx->par.device));
     MatchHomeKey key;
     key.reads_per_rank = reads_per_rank;
-    const int rc = partition_by<mb_match, MatchHomeKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, n_ranks, counts, ctx->matches_src);
-    if (rc == MB_OK) ctx->matches_src = nullptr;
-    return rc;
+    return partition_by<mb_match, MatchHomeKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, n_ranks, counts, &ctx->matches_seg);
 }
 
 // ---- multi-GPU: peer-routed producers --------------------------------------------------------------------
@@ -986,11 +1033,11 @@ int mb_peer_alloc(mb_ctx *ctx, size_t kmer_cap, size_t match_cap, mb_peer_mem *o
     CK(cudaSetDevice(ctx->par.device));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->routed = false;
-    ctx->kmers_src = ctx->matches_src = nullptr;
+    ctx->kmers_seg.n = 0; ctx->matches_seg.n = 0;
     CK(alloc_fixed(ctx->peer_kmers, kmer_cap * sizeof(mb_kmer)));
     CK(alloc_fixed(ctx->peer_matches, match_cap * sizeof(mb_match)));
-    CK(alloc_fixed(ctx->peer_cnt, 256));
-    CK(cudaMemsetAsync(ctx->peer_cnt.p, 0, 256, ctx->stream));
+    CK(alloc_fixed(ctx->peer_cnt, 2 * MB_MAX_RANKS * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->peer_cnt.p, 0, ctx->peer_cnt.cap, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->peer_kmer_cap = kmer_cap; ctx->peer_match_cap = match_cap;
     out->kmers = ctx->peer_kmers.p; out->matches = ctx->peer_matches.p; out->counters = ctx->peer_cnt.p;
@@ -1023,6 +1070,8 @@ int mb_ipc_close(mb_ctx *ctx, void *dptr) {
     return MB_OK;
 }
 
+// Receive-buffer geometry: rank d's buffer of `cap` records is cut into n_ranks equal regions, region s is written by
+// source rank s only, so a source reserves slots with its own local counters and no remote atomic is ever needed.
 int mb_peer_attach(mb_ctx *ctx, uint32_t rank, uint32_t n_ranks, const mb_peer_mem *peers, const uint64_t *bounds,
                    uint32_t reads_per_rank) {
     if (!ctx || !peers || n_ranks < 1 || n_ranks > MB_MAX_RANKS || rank >= n_ranks || (!bounds && n_ranks > 1) || !reads_per_rank)
@@ -1031,16 +1080,21 @@ int mb_peer_attach(mb_ctx *ctx, uint32_t rank, uint32_t n_ranks, const mb_peer_m
         peers[rank].counters != ctx->peer_cnt.p)
         return fail(ctx, MB_E_ARG, "peers[rank] must be this context's own mb_peer_alloc result");
     CK(cudaSetDevice(ctx->par.device));
+    CK(ctx->sent_cnt.ensure(2 * MB_MAX_RANKS * sizeof(unsigned long long)));
     Route &r = ctx->route;
     memset(&r, 0, sizeof(r));
-    r.n = n_ranks; r.rank = rank; r.reads_per_rank = reads_per_rank;
+    r.n = n_ranks; r.rank = rank; r.reads_per_rank = reads_per_rank; r.inv_reads_per_rank = 1.0f / (float) reads_per_rank;
     for (uint32_t i = 0; i < MB_MAX_RANKS; ++i) r.bounds[i] = (i + 1 < n_ranks) ? bounds[i] : ~0ull;
     for (uint32_t i = 0; i < n_ranks; ++i) {
         if (!peers[i].kmers || !peers[i].matches || !peers[i].counters) return fail(ctx, MB_E_ARG, "peer receive side missing");
-        r.kmers[i] = peers[i].kmers; r.matches[i] = peers[i].matches;
-        r.counters[i] = reinterpret_cast<unsigned long long *>(peers[i].counters);
-        r.kmer_cap[i] = peers[i].kmer_cap; r.match_cap[i] = peers[i].match_cap;
+        const u64 kreg = peers[i].kmer_cap / n_ranks, mreg = peers[i].match_cap / n_ranks;
+        r.kmers[i] = reinterpret_cast<mb_kmer *>(peers[i].kmers) + (u64) rank * kreg;
+        r.matches[i] = reinterpret_cast<mb_match *>(peers[i].matches) + (u64) rank * mreg;
+        r.kmer_cap[i] = kreg; r.match_cap[i] = mreg;
+        ctx->peer_counters[i] = reinterpret_cast<unsigned long long *>(peers[i].counters);
     }
+    r.sent_k = ctx->sent_cnt.as<unsigned long long>();
+    r.sent_m = r.sent_k + MB_MAX_RANKS;
     CK(ctx->route_dev.ensure(sizeof(Route)));
     CK(cudaMemcpyAsync(ctx->route_dev.p, &r, sizeof(Route), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -1048,12 +1102,41 @@ int mb_peer_attach(mb_ctx *ctx, uint32_t rank, uint32_t n_ranks, const mb_peer_m
     return MB_OK;
 }
 
-// read this rank's arrival counter `which` (0 k-mers, 1 matches) and clear it for the next batch
-static int take_counter(mb_ctx *ctx, int which, unsigned long long *n) {
-    unsigned long long *c = ctx->peer_cnt.as<unsigned long long>() + which;
-    if (int rc = read_back(ctx, c, n)) return rc;
-    CK(cudaMemsetAsync(c, 0, sizeof(unsigned long long), ctx->stream));
+// after a routed producer kernel: tell every destination how many records this rank put into its region there
+// (`which`: 0 k-mers, 1 matches); stream ordered behind the kernel, 8-byte peer copies
+static int publish_sent(mb_ctx *ctx, int which) {
+    const Route &r = ctx->route;
+    const unsigned long long *sent = which ? r.sent_m : r.sent_k;
+    for (u32 d = 0; d < r.n; ++d)
+        CK(cudaMemcpyAsync(ctx->peer_counters[d] + which * MB_MAX_RANKS + r.rank, sent + d, sizeof(unsigned long long), cudaMemcpyDefault,
+                           ctx->stream));
+    return MB_OK;
+}
+
+struct Arrived { unsigned long long v[MB_MAX_RANKS]; };
+
+// read this rank's arrival counters `which` (0 k-mers, 1 matches), clear them for the next batch and describe the
+// filled part of the regions; *total = records that arrived, or (overflow) n_ranks x the fullest region's demand
+static int take_regions(mb_ctx *ctx, int which, size_t rec_bytes, void *buf, u64 cap, SegIn &seg, unsigned long long *total, bool *over) {
+    Arrived a;
+    Arrived *dev = reinterpret_cast<Arrived *>(ctx->peer_cnt.as<unsigned long long>() + which * MB_MAX_RANKS);
+    if (int rc = read_back(ctx, dev, &a)) return rc;
+    CK(cudaMemsetAsync(dev, 0, sizeof(Arrived), ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    const u32 n = ctx->route.n;
+    const u64 region = cap / n;
+    unsigned long long sum = 0, worst = 0;
+    seg.n = n;
+    for (u32 s = 0; s < n; ++s) {
+        seg.prefix[s] = sum;
+        seg.base[s] = reinterpret_cast<const unsigned char *>(buf) + (size_t) s * region * rec_bytes;
+        sum += a.v[s];
+        worst = std::max(worst, a.v[s]);
+    }
+    seg.prefix[n] = sum;
+    *over = worst > region;
+    *total = *over ? worst * n : sum;
+    if (*over) seg.n = 0;
     return MB_OK;
 }
 
@@ -1062,12 +1145,13 @@ int mb_take_routed_kmers(mb_ctx *ctx, size_t *n) {
     if (!ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
     CK(cudaSetDevice(ctx->par.device));
     unsigned long long got = 0;
-    if (int rc = take_counter(ctx, 0, &got)) return rc;
-    if (n) *n = (size_t) got;
+    bool over = false;
     ctx->have_kmers = ctx->kmers_sorted = ctx->have_matches = ctx->have_results = false;
-    if (got > ctx->peer_kmer_cap) return fail(ctx, MB_E_CAPACITY, "more k-mers arrived than the receive buffer holds");
+    if (int rc = take_regions(ctx, 0, sizeof(mb_kmer), ctx->peer_kmers.p, ctx->peer_kmer_cap, ctx->kmers_seg, &got, &over)) return rc;
+    if (n) *n = (size_t) got;
+    if (over) return fail(ctx, MB_E_CAPACITY, "more k-mers arrived from one rank than its region of the receive buffer holds");
     ctx->n_kmers = got;
-    ctx->kmers_src = ctx->peer_kmers.p;
+    if (got == 0) ctx->kmers_seg.n = 0;
     ctx->have_kmers = true;
     return MB_OK;
 }
@@ -1077,13 +1161,14 @@ int mb_take_routed_matches(mb_ctx *ctx, size_t *n) {
     if (!ctx->routed) return fail(ctx, MB_E_ARG, "mb_peer_attach first");
     CK(cudaSetDevice(ctx->par.device));
     unsigned long long got = 0;
-    if (int rc = take_counter(ctx, 1, &got)) return rc;
-    if (n) *n = (size_t) got;
+    bool over = false;
     ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
     ctx->segments_valid = false;
-    if (got > ctx->peer_match_cap) return fail(ctx, MB_E_CAPACITY, "more matches arrived than the receive buffer holds");
+    if (int rc = take_regions(ctx, 1, sizeof(mb_match), ctx->peer_matches.p, ctx->peer_match_cap, ctx->matches_seg, &got, &over)) return rc;
+    if (n) *n = (size_t) got;
+    if (over) return fail(ctx, MB_E_CAPACITY, "more matches arrived from one rank than its region of the receive buffer holds");
     ctx->n_matches = got;
-    ctx->matches_src = ctx->peer_matches.p;
+    if (got == 0) ctx->matches_seg.n = 0;
     ctx->have_matches = true;
     return MB_OK;
 }

@@ -36,21 +36,45 @@ MB_HD u32 qi_frame(u64 q) { return (u32) (q >> 61); }
 // k-mers go to the shard that owns their value (owner = number of bounds <= value; bounds = first value of shards
 // 1..n-1, i.e. the `split` cut points of KmerMatcher.cpp:127-271); matches go to the home rank of their read.
 struct Route {
-    u32 n, rank, reads_per_rank, pad;
+    u32 n, rank, reads_per_rank;
+    float inv_reads_per_rank;
     u64 bounds[MB_MAX_RANKS];
-    void *kmers[MB_MAX_RANKS];
-    void *matches[MB_MAX_RANKS];
-    unsigned long long *counters[MB_MAX_RANKS];      // [0] k-mers arrived, [1] matches arrived
-    u64 kmer_cap[MB_MAX_RANKS], match_cap[MB_MAX_RANKS];
+    void *kmers[MB_MAX_RANKS];                 // start of THIS rank's region inside rank d's k-mer receive buffer
+    void *matches[MB_MAX_RANKS];               // same for matches
+    u64 kmer_cap[MB_MAX_RANKS], match_cap[MB_MAX_RANKS];     // region capacities (records)
+    unsigned long long *sent_k, *sent_m;       // LOCAL per-destination counters [MB_MAX_RANKS]: slots reserved so far
 };
+// A record array that lives in up to MB_MAX_RANKS pieces (the per-source regions of a receive buffer): element idx of the
+// concatenation.  n == 0: not segmented.
+struct SegIn {
+    u32 n, pad;
+    u64 prefix[MB_MAX_RANKS + 1];
+    const void *base[MB_MAX_RANKS];
+};
+template <typename Rec>
+__device__ __forceinline__ const Rec *seg_ptr(const SegIn &s, const Rec *in, u64 idx) {
+    if (s.n == 0) return in + idx;
+    u32 r = 0;
+    while (r + 1 < s.n && idx >= s.prefix[r + 1]) ++r;
+    return reinterpret_cast<const Rec *>(s.base[r]) + (idx - s.prefix[r]);
+}
 MB_HD u32 route_owner(const Route &r, u64 value) {
     u32 d = 0;
     for (u32 i = 0; i + 1 < r.n; ++i) d += r.bounds[i] <= value ? 1u : 0u;
     return d;
 }
 MB_HD u32 route_home(const Route &r, u32 seq) {
+#ifdef __CUDA_ARCH__
+    // (seq-1) / reads_per_rank without the integer-division sequence: float estimate, exact correction (x < 2^29)
+    const u32 x = seq - 1u;
+    u32 q = (u32) (__uint2float_rz(x) * r.inv_reads_per_rank);
+    if (q * r.reads_per_rank > x) --q;
+    else if ((q + 1u) * r.reads_per_rank <= x) ++q;
+    return q < r.n ? q : r.n - 1u;
+#else
     const u32 h = (seq - 1u) / r.reads_per_rank;
     return h < r.n ? h : r.n - 1u;
+#endif
 }
 
 // ---- read-length arithmetic: src/commons/LocalUtil.h:45-59 ----------------------------------------

@@ -64,8 +64,9 @@ constexpr size_t extract_smem_bytes() { return (size_t) EX_TILE * 2 * sizeof(mb_
 // per-window translation.
 //
 // ROUTED (multi-GPU, mb_extract_kmers_routed): the staged k-mers of half a tile are grouped by owner shard in shared
-// memory (second half of the staging area), one reservation per owner on the OWNER's arrival counter (remote atomic
-// over NVLink), then every owner's run is written with coalesced 16-byte peer stores.
+// memory (second half of the staging area), one reservation per owner on this rank's LOCAL per-owner counter (every
+// source owns a fixed region of every owner's receive buffer, so no remote atomic is needed), then every owner's run is
+// written with coalesced 16-byte peer stores over NVLink.
 template <bool FMT2, bool ROUTED>
 __global__ void __launch_bounds__(EX_THREADS)
 k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__restrict__ tables, mb_kmer *__restrict__ out,
@@ -81,12 +82,13 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
     __shared__ unsigned long long s_base;
     __shared__ Route s_route;
     __shared__ u32 s_dcnt[MB_MAX_RANKS], s_dloc[MB_MAX_RANKS + 1];
+    __shared__ u32 s_wcnt[EX_THREADS / 32][MB_MAX_RANKS];
     __shared__ unsigned long long s_dbase[MB_MAX_RANKS];
 
     const u32 tid = threadIdx.x, lane = tid & 31;
     if (ROUTED) {
         for (u32 i = tid; i < sizeof(Route) / 8; i += EX_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
-        if (tid < MB_MAX_RANKS) s_dcnt[tid] = 0;
+        if (tid < MB_MAX_RANKS * (EX_THREADS / 32)) (&s_wcnt[0][0])[tid] = 0;
     }
     const u32 tile = blockIdx.x;
     const u64 g0 = (u64) tile * EX_TILE;
@@ -227,24 +229,30 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
         const u32 total = s_fill;
         const u32 nr = s_route.n;
         constexpr int PER = EX_TILE / EX_THREADS;
+        constexpr int NW = EX_THREADS / 32;
+        const u32 warp = tid >> 5;
         u32 pos[PER];
+        // rank of every record among the records of its warp with the same owner: one shared-memory atomic per record
+        // on a per-warp counter (cost independent of the number of ranks)
 #pragma unroll
         for (int j = 0; j < PER; ++j) {
             const u32 k = tid + j * EX_THREADS;
-            const u32 d = k < total ? route_owner(s_route, s_out[k].x) : 0xFFFFFFFFu;
             pos[j] = 0;
-            for (u32 dd = 0; dd < nr; ++dd) {
-                const u32 mask = __ballot_sync(0xFFFFFFFFu, d == dd);
-                if (!mask) continue;
-                u32 base = 0;
-                if (lane == (u32) (__ffs(mask) - 1)) base = atomicAdd(&s_dcnt[dd], (u32) __popc(mask));
-                base = __shfl_sync(0xFFFFFFFFu, base, __ffs(mask) - 1);
-                if (d == dd) pos[j] = (dd << 16) | (base + __popc(mask & ((1u << lane) - 1u)));
+            if (k < total) {
+                const u32 d = route_owner(s_route, s_out[k].x);
+                pos[j] = (d << 16) | atomicAdd(&s_wcnt[warp][d], 1u);
             }
         }
         __syncthreads();
-        if (tid < nr) s_dbase[tid] = s_dcnt[tid] ? atomicAdd(s_route.counters[tid], (unsigned long long) s_dcnt[tid]) : 0ull;
-        if (tid == 32) {
+        if (tid < nr) {                                       // per owner: offsets of the warps' runs, total, reservation
+            u32 acc = 0;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) { const u32 c = s_wcnt[w][tid]; s_wcnt[w][tid] = acc; acc += c; }
+            s_dcnt[tid] = acc;
+            s_dbase[tid] = acc ? atomicAdd(s_route.sent_k + tid, (unsigned long long) acc) : 0ull;
+        }
+        __syncthreads();
+        if (tid == 0) {
             u32 acc = 0;
             for (u32 dd = 0; dd < nr; ++dd) { s_dloc[dd] = acc; acc += s_dcnt[dd]; }
             s_dloc[nr] = acc;
@@ -255,7 +263,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
 #pragma unroll
         for (int j = 0; j < PER; ++j) {
             const u32 k = tid + j * EX_THREADS;
-            if (k < total) s_ord[s_dloc[pos[j] >> 16] + (pos[j] & 0xFFFFu)] = s_out[k];
+            if (k < total) { const u32 d = pos[j] >> 16; s_ord[s_dloc[d] + s_wcnt[warp][d] + (pos[j] & 0xFFFFu)] = s_out[k]; }
         }
         __syncthreads();
         for (u32 k = tid; k < total; k += EX_THREADS) {
@@ -266,7 +274,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
         }
         __syncthreads();
         if (tid == 0) s_fill = 0;
-        if (tid < MB_MAX_RANKS) s_dcnt[tid] = 0;
+        if (tid < MB_MAX_RANKS * (EX_THREADS / 32)) (&s_wcnt[0][0])[tid] = 0;
         __syncthreads();
     }
     }   // half

@@ -202,8 +202,8 @@ __device__ __forceinline__ void make_match(const DbView &db, const MatchOut &mo,
 }
 
 // Routed flush (mb_match_kmers_routed): the staged matches are grouped by home rank inside the staging buffer, one
-// reservation per home on the HOME's arrival counter (remote atomic over NVLink, lanes 0..n-1 in parallel), then each
-// home's run leaves with coalesced 8-byte peer stores.  Warp-synchronous.
+// reservation per home on this rank's LOCAL per-home counter (lanes 0..n-1 in parallel; every source owns a fixed region
+// of every home's receive buffer), then each home's run leaves with coalesced 8-byte peer stores.  Warp-synchronous.
 __device__ __noinline__ void warp_flush_routed(const MatchOut &mo, u64 *stage, u32 fill) {
     const Route &r = *mo.route;
     const u32 lane = threadIdx.x & 31;
@@ -235,7 +235,7 @@ __device__ __noinline__ void warp_flush_routed(const MatchOut &mo, u64 *stage, u
     }
     const u32 excl = incl - mycnt;
     unsigned long long base = 0;
-    if (lane < r.n && mycnt) base = atomicAdd(r.counters[lane] + 1, (unsigned long long) mycnt);
+    if (lane < r.n && mycnt) base = atomicAdd(r.sent_m + lane, (unsigned long long) mycnt);
     if (lane == 0) atomicAdd(mo.counter, (unsigned long long) fill);             // local statistic: matches this rank produced
     __syncwarp();
 #pragma unroll
@@ -262,10 +262,11 @@ __device__ __noinline__ void warp_flush_routed(const MatchOut &mo, u64 *stage, u
 }
 
 // Flush the warp's staged matches: one reservation, coalesced 8-byte stores.  Warp-synchronous.
+template <bool ROUTED>
 __device__ __forceinline__ void warp_flush(const MatchOut &mo, u64 *stage, u32 &fill) {
     const u32 lane = threadIdx.x & 31;
     __syncwarp();
-    if (fill && mo.route) {
+    if (ROUTED && fill) {
         warp_flush_routed(mo, stage, fill);
     } else if (fill) {
         unsigned long long base = 0;
@@ -286,6 +287,7 @@ __device__ __forceinline__ void warp_flush(const MatchOut &mo, u64 *stage, u32 &
 
 // Warp-level emission: lane l adds `cnt` matches (entries [lo,hi) of s.vals whose distance is <= maxh; the
 // distances of the first 16 entries are cached 4 bits each in dpack).
+template <bool ROUTED>
 __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, const MatchSmem &s, MatchTables &tb, const MatchOut &mo,
                                           bool active, const mb_kmer &q, u32 lo, u32 hi, u32 maxh, u32 cnt, u64 dpack, int format,
                                           u32 &fill) {
@@ -301,7 +303,7 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
     u64 *stage = tb.stage[warp];
     if (total > MT_STAGE) {
         // more than the staging buffer holds (a few very long groups): reserve and write straight to HBM
-        warp_flush(mo, stage, fill);
+        warp_flush<ROUTED>(mo, stage, fill);
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(mo.counter, (unsigned long long) total);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
@@ -311,11 +313,11 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
                 const u64 t = s.vals[j];
                 const u32 d = (j - lo < 16) ? (u32) (dpack >> (4 * (j - lo))) & 15u : hamming_sum_lut(tb.lut2, q.value, t);
                 if (d > maxh) continue;
-                if (mo.route) {                                   // rare path: one reservation per record at its home
+                if (ROUTED) {                                     // rare path: one reservation per record at its home
                     u64 rec[3];
                     make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
                     const u32 h = route_home(*mo.route, qi_seq(rec[0]));
-                    const unsigned long long slot = atomicAdd(mo.route->counters[h] + 1, 1ull);
+                    const unsigned long long slot = atomicAdd(mo.route->sent_m + h, 1ull);
                     if (slot < mo.route->match_cap[h]) {
                         u64 *p = reinterpret_cast<u64 *>(mo.route->matches[h]) + slot * 3;
                         p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
@@ -331,7 +333,7 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
         }
         return;
     }
-    if (fill + total > MT_STAGE) warp_flush(mo, stage, fill);
+    if (fill + total > MT_STAGE) warp_flush<ROUTED>(mo, stage, fill);
     if (active && cnt) {
         u32 o = fill + incl - cnt;
         for (u32 j = lo; j < hi; ++j) {
@@ -350,6 +352,7 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
 
 // Streaming two-pass join for an amino-acid group that does not fit one chunk: for every batch of
 // 256 queries of that group the group is decoded twice from its start cursor (minimum, then emit).
+template <bool ROUTED>
 __device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, MatchSmem &s, MatchTables &tb, const MatchOut &mo,
                                          const mb_kmer *__restrict__ q, u64 qcur, u64 qend, u64 gaa, int format, u32 &fill) {
     const u32 tid = threadIdx.x;
@@ -388,7 +391,7 @@ __device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, Ma
                             if (j < 16) dpack |= (u64) (d < 15 ? d : 15) << (4 * j);
                             cnt += d <= maxh ? 1u : 0u;
                         }
-                    warp_emit(db, g, s, tb, mo, mine, qk, 0, ge, maxh, cnt, dpack, format, fill);
+                    warp_emit<ROUTED>(db, g, s, tb, mo, mine, qk, 0, ge, maxh, cnt, dpack, format, fill);
                 }
                 __syncthreads();
                 if (finished) break;
@@ -411,6 +414,7 @@ __device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, 
     return lo;
 }
 
+template <bool ROUTED>
 __global__ void __launch_bounds__(MT_THREADS, 3)
 k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
         const u64 *__restrict__ qend_of, MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *block_ticket,
@@ -419,7 +423,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
     __shared__ Route s_route;
     MatchOut mo = mo_in;
     mo.route = nullptr;
-    if (route_g) {                                  // multi-GPU: matches leave for their home rank (warp_flush_routed)
+    if (ROUTED) {                                   // multi-GPU: matches leave for their home rank (warp_flush_routed)
         for (u32 i = threadIdx.x; i < sizeof(Route) / 8; i += MT_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
         mo.route = &s_route;
     }
@@ -475,7 +479,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 // longer than a block plus overhang, it is the last one this block owns.
                 const u64 gaa = s.vals[0] >> 24;
                 __syncthreads();
-                giant_group(db, c, s, tb, mo, q, qcur, qend, gaa, format, fill);
+                giant_group<ROUTED>(db, c, s, tb, mo, q, qcur, qend, gaa, format, fill);
                 break;
             }
 
@@ -573,7 +577,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                     oq.qinfo = __shfl_sync(0xFFFFFFFFu, qk.qinfo, owner);
                     if (okmask == 0) continue;
                     const u32 nok = (u32) __popc(okmask);
-                    if (fill + nok > MT_STAGE) warp_flush(mo, stage, fill);
+                    if (fill + nok > MT_STAGE) warp_flush<ROUTED>(mo, stage, fill);
                     if (ok) {
                         u64 rec[3];
                         make_match(db, mo, tb.lutp, oq, s.vals[j], c.kidx + j, dd, format, rec);
@@ -594,7 +598,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
             c.word = nw; c.vbefore = nv; c.kidx += proc_end;
         }
     }
-    warp_flush(mo, tb.stage[warp], fill);
+    warp_flush<ROUTED>(mo, tb.stage[warp], fill);
 }
 
 constexpr size_t match_smem_bytes() { return ((sizeof(MatchSmem) + 15) & ~(size_t) 15) + sizeof(MatchTables); }

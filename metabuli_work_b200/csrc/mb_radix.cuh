@@ -64,15 +64,16 @@ struct MatchHomeKey {       // multi-GPU: home rank of a match = (sequenceID-1) 
 };
 
 // ---- histogram of every pass in one read -----------------------------------------------------------
-template <typename Rec, typename Key>
+template <typename Rec, typename Key, bool SEG>
 __global__ void __launch_bounds__(RS_THREADS)
-k_radix_hist(const Rec *__restrict__ in, u64 n, Key key, int n_passes, u64 *__restrict__ hist /*[n_passes][256]*/) {
+k_radix_hist(const Rec *__restrict__ in, u64 n, Key key, int n_passes, u64 *__restrict__ hist /*[n_passes][256]*/,
+             const __grid_constant__ SegIn seg) {
     extern __shared__ u32 s_hist[]; // n_passes * 256
     for (int i = threadIdx.x; i < n_passes * RS_BINS; i += RS_THREADS) s_hist[i] = 0;
     __syncthreads();
     const u64 stride = (u64) gridDim.x * RS_THREADS;
     for (u64 i = (u64) blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
-        const Rec r = in[i];
+        const Rec r = SEG ? *seg_ptr(seg, in, i) : in[i];
         for (int p = 0; p < n_passes; ++p) atomicAdd(&s_hist[p * RS_BINS + key.digit(r, p)], 1u);
     }
     __syncthreads();
@@ -101,11 +102,11 @@ __global__ void __launch_bounds__(RS_BINS) k_radix_scan_hist(u64 *__restrict__ h
 }
 
 // ---- one pass -----------------------------------------------------------------------------------
-template <typename Rec, typename Key, int ITEMS>
+template <typename Rec, typename Key, int ITEMS, bool SEG>
 __global__ void __launch_bounds__(RS_THREADS)
 k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, int pass,
              const u64 *__restrict__ digit_base /*[256] exclusive*/, u64 *tile_state /*[tiles][256]*/,
-             u32 *ticket, int dbg) {
+             u32 *ticket, int dbg, const __grid_constant__ SegIn seg) {
     constexpr int TILE = RS_THREADS * ITEMS;
     extern __shared__ __align__(16) unsigned char s_raw[];
     Rec *s_rec = reinterpret_cast<Rec *>(s_raw);                                   // TILE records
@@ -127,11 +128,30 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
     u32 dig[ITEMS];
     u32 rank[ITEMS];
     const u64 wbase = tile_base + (u64) warp * 32 * ITEMS;
+    // SEG: the input lies in a few regions (SegIn); a tile that falls inside one region — all but n-1 tiles — reads
+    // through one rebased pointer, so that its loads stay one independent batch
+    const Rec *in_eff = in;
+    bool split = false;
+    if (SEG) {
+        u32 r = 0;
+        while (r + 1 < seg.n && tile_base >= seg.prefix[r + 1]) ++r;
+        in_eff = reinterpret_cast<const Rec *>(seg.base[r]) - seg.prefix[r];
+        split = r + 1 < seg.n && tile_base + TILE > seg.prefix[r + 1];
+    }
+    if (SEG && split) {
 #pragma unroll
-    for (int j = 0; j < ITEMS; ++j) {
-        const u64 idx = wbase + (u64) j * 32 + lane;
-        if (idx < n) { rec[j] = in[idx]; dig[j] = key.digit(rec[j], pass); }
-        else dig[j] = 0xFFFFFFFFu;
+        for (int j = 0; j < ITEMS; ++j) {
+            const u64 idx = wbase + (u64) j * 32 + lane;
+            if (idx < n) { rec[j] = *seg_ptr(seg, in, idx); dig[j] = key.digit(rec[j], pass); }
+            else dig[j] = 0xFFFFFFFFu;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const u64 idx = wbase + (u64) j * 32 + lane;
+            if (idx < n) { rec[j] = in_eff[idx]; dig[j] = key.digit(rec[j], pass); }
+            else dig[j] = 0xFFFFFFFFu;
+        }
     }
     // early counts: the tile's digit histogram is published BEFORE the ranking, so that by the time this tile looks
     // back its predecessors (which started earlier) have long published theirs

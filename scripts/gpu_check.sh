@@ -2,7 +2,7 @@
 # parity tests + the configs[1] bench with the oracle check; usage: bash scripts/gpu_check.sh <tag> [bench args]
 TAG=${1:-chk}; shift
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest_rc=$?"
+timeout 400 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest_rc=$?"
 tail -4 gpurun_out/${TAG}_pytest.log
 timeout 1500 python bench.py --steps 3 --warmup 3 --check --no-cpu-baseline "$@" > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench_rc=$?"
 tail -3 gpurun_out/${TAG}_bench.err

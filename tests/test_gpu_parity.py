@@ -304,7 +304,7 @@ def test_routed_producers_one_gpu(golden, mb, case, world):
     try:
         bounds = ctxs[0].shard_bounds()
         assert len(bounds) == world - 1
-        mem = [c.peer_alloc(len(ok) + 64, len(om) + 64) for c in ctxs]
+        mem = [c.peer_alloc(world * (len(ok) + 64), world * (len(om) + 64)) for c in ctxs]      # a region per source rank
         for g, c in enumerate(ctxs):
             c.peer_attach(g, mem, bounds, per)
         emitted = 0
@@ -336,7 +336,7 @@ def test_routed_producers_one_gpu(golden, mb, case, world):
             sub = ores[a:b]
             assert compare_results(res, ids, cnt, sub, oids, ocnt) == []
         # a receive buffer that is too small is reported, not overrun
-        small = [c.peer_alloc(len(ok) + 64, 8) for c in ctxs]
+        small = [c.peer_alloc(world * (len(ok) + 64), 8) for c in ctxs]
         for g, c in enumerate(ctxs):
             c.peer_attach(g, small, bounds, per)
         for c in ctxs:
