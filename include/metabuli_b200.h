@@ -148,6 +148,13 @@ int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint
 /* The same path in stages (each leaves its output resident on the device): */
 int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
                    uint32_t n_reads);                                   /* H2D only                      */
+/* Overlap the host->device copy of the NEXT batch with the device work of the current one: the copy is
+ * enqueued on a second stream into a second set of buffers; a following mb_stage_reads (or
+ * mb_classify_batch) with the SAME arguments adopts the copied batch instead of copying again.  The
+ * host buffers must stay unchanged until then (pinned memory for a truly asynchronous copy).
+ * Typical loop: stage(cur) -> prefetch(next) -> classify_staged -> fetch_results.                    */
+int mb_prefetch_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
+                      uint32_t n_reads);
 int mb_extract_kmers(mb_ctx *ctx, size_t *n_kmers);                     /* KmerExtractor.cpp:83-386      */
 int mb_sort_kmers(mb_ctx *ctx);                                         /* KmerExtractor.cpp:79          */
 int mb_match_kmers(mb_ctx *ctx, size_t *n_matches);                     /* KmerMatcher.cpp:123-481       */

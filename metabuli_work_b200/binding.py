@@ -65,7 +65,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream",
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
-               "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
+               "mb_prefetch_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -91,6 +91,7 @@ _sig(_cuda, "mb_decode_db", C.c_int, [vp, vp, sz, szp])
 _sig(_cuda, "mb_load_taxonomy", C.c_int, [vp, vp, vp, vp, i32, i32, i32])
 _sig(_cuda, "mb_classify_batch", C.c_int, [vp, vp, sz, vp, vp, u32, vp, vp, vp, sz, szp])
 _sig(_cuda, "mb_stage_reads", C.c_int, [vp, vp, sz, vp, vp, u32])
+_sig(_cuda, "mb_prefetch_reads", C.c_int, [vp, vp, sz, vp, vp, u32])
 _sig(_cuda, "mb_extract_kmers", C.c_int, [vp, szp])
 _sig(_cuda, "mb_sort_kmers", C.c_int, [vp])
 _sig(_cuda, "mb_match_kmers", C.c_int, [vp, szp])
@@ -204,6 +205,12 @@ class Context:
         self._keep = (bases, offsets, lens)
         bp = bases_ptr if bases_ptr is not None else _ptr(bases)
         self._ck(_cuda.mb_stage_reads(self.ctx, bp, len(bases), _ptr(offsets), _ptr(lens), self.n_reads))
+
+    def prefetch(self, bases, offsets, lens, bases_ptr=None):
+        """Start the host->device copy of the NEXT batch on the copy stream; a later stage() with the same arrays adopts it."""
+        self._keep_next = (bases, offsets, lens)
+        bp = bases_ptr if bases_ptr is not None else _ptr(bases)
+        self._ck(_cuda.mb_prefetch_reads(self.ctx, bp, len(bases), _ptr(offsets), _ptr(lens), len(lens) // 2))
 
     def extract(self):
         n = C.c_size_t(0)

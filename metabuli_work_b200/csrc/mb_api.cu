@@ -42,6 +42,10 @@ struct DevBuf {
         return cudaSuccess;
     }
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+    void swap(DevBuf &o) { std::swap(p, o.p); std::swap(cap, o.cap); }
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
 };
 
 enum { EV_START, EV_H2D, EV_EXTRACT, EV_SORTK, EV_MATCH, EV_SORTM, EV_SCORE, EV_D2H, EV_COUNT };
@@ -89,7 +93,15 @@ struct mb_ctx {
     DevBuf parent, depth, species_of, species_rank_of;
     int32_t max_taxid = -1, node0 = 0, euk = 0;
     // batch
-    DevBuf bases, offsets, lens;
+    DevBuf bases, offsets, lens, stage_info;
+    // mb_prefetch_reads: the next batch, copied on a second stream while the current one is being classified
+    DevBuf pf_bases, pf_offsets, pf_lens, pf_info;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t pf_done = nullptr;
+    bool pf_pending = false;
+    const void *pf_host[3] = {nullptr, nullptr, nullptr};
+    u64 pf_n_bases = 0;
+    u32 pf_n_reads = 0;
     u64 n_bases = 0;
     u32 n_reads = 0;
     u32 seq_base = 0;
@@ -339,6 +351,8 @@ void mb_destroy(mb_ctx *ctx) {
     for (int i = 0; i < EV_COUNT; ++i) cudaEventDestroy(ctx->ev[i]);
     for (auto &k : ctx->samples) { cudaEventDestroy(k.a); cudaEventDestroy(k.b); }
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    if (ctx->pf_done) cudaEventDestroy(ctx->pf_done);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -480,42 +494,72 @@ int mb_load_taxonomy(mb_ctx *ctx, const int32_t *parent, const int32_t *species_
 }
 
 // ---- stages -----------------------------------------------------------------------------------------
+// copies + device-side validation of one batch into (bases, offsets, lens, info) on stream `st`
+static int enqueue_batch(mb_ctx *ctx, cudaStream_t st, DevBuf &d_bases, DevBuf &d_off, DevBuf &d_len, DevBuf &d_info,
+                         const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens, uint32_t n_reads) {
+    CK(d_bases.ensure(n_bases + 128));
+    CK(d_off.ensure((size_t) n_reads * 2 * sizeof(u64) + 16));
+    CK(d_len.ensure((size_t) n_reads * 2 * sizeof(u32) + 16));
+    CK(d_info.ensure(sizeof(StageInfo)));
+    if (n_bases) CK(cudaMemcpyAsync(d_bases.p, bases, n_bases, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(d_bases.as<u8>() + n_bases, 0, 128, st));
+    CK(cudaMemsetAsync(d_info.p, 0, sizeof(StageInfo), st));
+    if (n_reads) {
+        CK(cudaMemcpyAsync(d_off.p, offsets, (size_t) n_reads * 2 * sizeof(u64), cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(d_len.p, lens, (size_t) n_reads * 2 * sizeof(u32), cudaMemcpyHostToDevice, st));
+        k_validate_reads<<<(n_reads + 255) / 256, 256, 0, st>>>(d_off.as<u64>(), d_len.as<u32>(), n_reads, n_bases, ctx->par.seq_mode == 2,
+                                                                 d_info.as<StageInfo>());
+        CK(cudaGetLastError());
+    }
+    return MB_OK;
+}
+
+int mb_prefetch_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
+                      uint32_t n_reads) {
+    if (!ctx || (!bases && n_bases) || ((!offsets || !lens) && n_reads)) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->pf_done, cudaEventDisableTiming));
+    }
+    if (ctx->pf_pending) CK(cudaStreamSynchronize(ctx->copy_stream));          // an unclaimed prefetch is overwritten
+    ctx->pf_pending = false;
+    if (int rc = enqueue_batch(ctx, ctx->copy_stream, ctx->pf_bases, ctx->pf_offsets, ctx->pf_lens, ctx->pf_info, bases, n_bases, offsets, lens, n_reads))
+        return rc;
+    CK(cudaEventRecord(ctx->pf_done, ctx->copy_stream));
+    ctx->pf_host[0] = bases; ctx->pf_host[1] = offsets; ctx->pf_host[2] = lens;
+    ctx->pf_n_bases = n_bases; ctx->pf_n_reads = n_reads;
+    ctx->pf_pending = true;
+    return MB_OK;
+}
+
 int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
                    uint32_t n_reads) {
     if (!ctx || (!bases && n_bases) || ((!offsets || !lens) && n_reads)) return MB_E_ARG;
     if ((uint64_t) n_reads + ctx->seq_base >= (1u << 29)) return fail(ctx, MB_E_ARG, "at most 2^29-1 reads per batch (29-bit sequenceID, Kmer.h:11-16)");
     CK(cudaSetDevice(ctx->par.device));
     ctx->have_reads = ctx->have_kmers = ctx->have_matches = ctx->have_results = false;
-    // host pass over the lengths: layout check, k-mer slot bound (QueryIndexer.cpp:62-67), longest query
-    u64 bound = 0, prev_end = 0;
-    u32 max_q = 0;
-    const bool paired = ctx->par.seq_mode == 2;
-    for (u32 i = 0; i < n_reads; ++i) {
-        u32 ql = 0;
-        for (int mt = 0; mt < 2; ++mt) {
-            const u64 off = offsets[2 * i + mt];
-            const u32 len = lens[2 * i + mt];
-            if (off < prev_end || off + len > n_bases) return fail(ctx, MB_E_ARG, "mates must be packed back to back in increasing offset order");
-            prev_end = off + len;
-            if (mt == 1 && !paired) continue;
-            const int kn = query_kmer_number((int) len);
-            if (kn > 0) { bound += (u64) kn; ql += (u32) max_covered_length((int) len); }
-        }
-        max_q = std::max(max_q, ql);
-    }
     mark(ctx, EV_START);
-    CK(ctx->bases.ensure(n_bases + 128));
-    CK(ctx->offsets.ensure((size_t) n_reads * 2 * sizeof(u64) + 16));
-    CK(ctx->lens.ensure((size_t) n_reads * 2 * sizeof(u32) + 16));
-    CK(cudaMemcpyAsync(ctx->bases.p, bases, n_bases, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemsetAsync(ctx->bases.as<u8>() + n_bases, 0, 128, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->offsets.p, offsets, (size_t) n_reads * 2 * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->lens.p, lens, (size_t) n_reads * 2 * sizeof(u32), cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->pf_pending && ctx->pf_host[0] == bases && ctx->pf_host[1] == offsets && ctx->pf_host[2] == lens &&
+        ctx->pf_n_bases == n_bases && ctx->pf_n_reads == n_reads) {
+        // this batch was prefetched: adopt its buffers, order the work stream behind the copy
+        ctx->bases.swap(ctx->pf_bases); ctx->offsets.swap(ctx->pf_offsets);
+        ctx->lens.swap(ctx->pf_lens); ctx->stage_info.swap(ctx->pf_info);
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->pf_done, 0));
+        ctx->pf_pending = false;
+    } else {
+        if (int rc = enqueue_batch(ctx, ctx->stream, ctx->bases, ctx->offsets, ctx->lens, ctx->stage_info, bases, n_bases, offsets, lens, n_reads))
+            return rc;
+    }
     mark(ctx, EV_H2D);
+    // layout check, k-mer slot bound (QueryIndexer.cpp:62-67) and longest query were computed on the device
+    StageInfo info;
+    if (int rc = read_back(ctx, ctx->stage_info.as<StageInfo>(), &info)) return rc;
+    if (info.bad) return fail(ctx, MB_E_ARG, "mates must be packed back to back in increasing offset order");
     ctx->n_bases = n_bases;
     ctx->n_reads = n_reads;
-    ctx->kmer_bound = bound;
-    ctx->max_query_len = max_q + 8;
+    ctx->kmer_bound = info.bound;
+    ctx->max_query_len = info.max_q + 8;
     ctx->have_reads = true;
     ctx->launches = 0;
     ctx->n_samples = 0;

@@ -51,6 +51,7 @@ struct SegIn {
     u64 prefix[MB_MAX_RANKS + 1];
     const void *base[MB_MAX_RANKS];
 };
+#ifdef __CUDACC__
 template <typename Rec>
 __device__ __forceinline__ const Rec *seg_ptr(const SegIn &s, const Rec *in, u64 idx) {
     if (s.n == 0) return in + idx;
@@ -58,6 +59,7 @@ __device__ __forceinline__ const Rec *seg_ptr(const SegIn &s, const Rec *in, u64
     while (r + 1 < s.n && idx >= s.prefix[r + 1]) ++r;
     return reinterpret_cast<const Rec *>(s.base[r]) + (idx - s.prefix[r]);
 }
+#endif
 MB_HD u32 route_owner(const Route &r, u64 value) {
     u32 d = 0;
     for (u32 i = 0; i + 1 < r.n; ++i) d += r.bounds[i] <= value ? 1u : 0u;

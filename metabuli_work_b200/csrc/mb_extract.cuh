@@ -50,6 +50,40 @@ __global__ void k_tile_first_mate(ExtractArgs a, u32 n_tiles, u32 *__restrict__ 
     tile_mate[t] = (t == n_tiles || a.n_mates == 0) ? (a.n_mates ? a.n_mates - 1 : 0) : mate_of(a.offsets, 0, a.n_mates - 1, g);
 }
 
+// Layout check and sizing of a staged batch, on the device (one thread per read): mates back to back in increasing
+// offset order inside the base buffer; k-mer slot bound (QueryIndexer.cpp:62-67); longest query.
+struct StageInfo { unsigned long long bound; u32 max_q; u32 bad; };
+__global__ void __launch_bounds__(256) k_validate_reads(const u64 *__restrict__ offsets, const u32 *__restrict__ lens, u32 n_reads,
+                                                        u64 n_bases, int paired, StageInfo *__restrict__ info) {
+    const u32 i = blockIdx.x * 256 + threadIdx.x;
+    unsigned long long bound = 0;
+    u32 ql = 0, bad = 0;
+    if (i < n_reads) {
+        u64 prev_end = i ? offsets[2 * i - 1] + lens[2 * i - 1] : 0;
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            const u64 off = offsets[2 * i + mt];
+            const u32 len = lens[2 * i + mt];
+            if (off < prev_end || off + len > n_bases) bad = 1;
+            prev_end = off + len;
+            if (mt == 1 && !paired) continue;
+            const int kn = query_kmer_number((int) len);
+            if (kn > 0) { bound += (unsigned long long) kn; ql += (u32) max_covered_length((int) len); }
+        }
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        bound += __shfl_xor_sync(0xFFFFFFFFu, bound, d);
+        ql = max(ql, __shfl_xor_sync(0xFFFFFFFFu, ql, d));
+        bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, d);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (bound) atomicAdd(&info->bound, bound);
+        if (ql) atomicMax(&info->max_q, ql);
+        if (bad) atomicOr(&info->bad, 1u);
+    }
+}
+
 constexpr size_t extract_smem_bytes() { return (size_t) EX_TILE * 2 * sizeof(mb_kmer); }   // every window, both strands
 
 // ONE pass: a CTA extracts the k-mers of its 2048 window starts into a shared-memory staging buffer (slots handed out

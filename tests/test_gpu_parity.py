@@ -349,3 +349,40 @@ def test_routed_producers_one_gpu(golden, mb, case, world):
     finally:
         for c in ctxs:
             c.close()
+
+
+def test_prefetch_overlap(golden, mb):
+    """mb_prefetch_reads: the next batch is copied on the second stream while the current one is classified; the
+    following stage() with the same arrays adopts it.  Results must equal the plain path, also when a prefetch is
+    never claimed or is replaced."""
+    case = "sync_paired"
+    _, s1, s2 = golden.reads(case)
+    half = len(s1) // 2
+    A = mb.pack_reads(s1[:half], s2[:half])
+    B = mb.pack_reads(s1[half:], s2[half:])
+    clf = mb.Classifier(golden.dbdir(case), seq_mode=2)
+    try:
+        want = {}
+        for name, (b, o, l) in (("A", A), ("B", B)):
+            want[name] = clf.classify(b, o, l)
+        clf.stage(*A)
+        clf.prefetch(*B)                        # overlaps the work on A
+        ra = clf.fetch(clf.classify_staged())
+        clf.stage(*B)                           # adopted, no second copy
+        clf.prefetch(*A)
+        rb = clf.fetch(clf.classify_staged())
+        clf.prefetch(*B)                        # replaces the unclaimed prefetch of A
+        clf.stage(*A)                           # not the prefetched batch: ordinary copy
+        ra2 = clf.fetch(clf.classify_staged())
+        clf.stage(*B)                           # still pending, adopted now
+        rb2 = clf.fetch(clf.classify_staged())
+        for got, name in ((ra, "A"), (rb, "B"), (ra2, "A"), (rb2, "B")):
+            assert compare_results(*got, *want[name]) == [], name           # (taxCnt ranges are handed out by atomics)
+        # a malformed layout is caught by the device-side check
+        b, o, l = A
+        o2 = o.copy()
+        o2[1], o2[2] = o[2], o[1]
+        with pytest.raises(mb.MetabuliError):
+            clf.stage(b, o2, l)
+    finally:
+        clf.close()
