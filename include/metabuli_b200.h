@@ -73,7 +73,9 @@ typedef struct {
     int32_t accession_level;  /* only 0 is supported on this path                              */
     int32_t last_shard;       /* 1 when this context holds the END of the DB (the reference never
                                  offers the final DB k-mer as a candidate, KmerMatcher.cpp:363-406) */
-    int32_t kmer_sort_bits;   /* leading amino-acid bits the query k-mer sort orders: 24, 32 or 40 (0 = default 32).
+    int32_t kmer_sort_bits;   /* leading amino-acid bits the query k-mer sort orders: 24, 32 or 40; 21 (format 2 only) =
+                                 the re-coded key: five leading residues as a base-21 number plus two bits of the
+                                 sixth, 24 bits in all.  0 = default (21 for format 2, 32 for format 1).
                                  The join only needs the queries of a DB block to be contiguous, not ordered, so
                                  fewer bits = fewer radix passes; blocks re-check the full amino-acid part.        */
     int32_t reserved[2];

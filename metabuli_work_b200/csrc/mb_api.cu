@@ -105,7 +105,7 @@ struct mb_ctx {
     u64 n_bases = 0;
     u32 n_reads = 0;
     u32 seq_base = 0;
-    int sort_shift = 0;               // low amino-acid bits the resident k-mer order ignores
+    SortT sort_t{0, 0};               // the function of the amino-acid part the resident k-mers are ordered by
     u64 kmer_bound = 0;
     u32 max_query_len = 0;
     DevBuf tile_mate, tile_counts, tile_offsets;
@@ -304,9 +304,10 @@ static int check_params(const mb_params *p, std::string &err) {
     if (p->kmer_format != 1 && p->kmer_format != 2) { err = "kmer_format must be 1 or 2"; return MB_E_ARG; }
     if (p->seq_mode < 1 || p->seq_mode > 3) { err = "seq_mode must be 1, 2 or 3"; return MB_E_ARG; }
     if (p->syncmer && (p->smer_len < 1 || p->smer_len > 7)) { err = "smer_len must be in 1..7"; return MB_E_ARG; }
-    if (p->kmer_sort_bits != 0 && p->kmer_sort_bits != 24 && p->kmer_sort_bits != 32 && p->kmer_sort_bits != 40) {
-        err = "kmer_sort_bits must be 0, 24, 32 or 40"; return MB_E_ARG;
+    if (p->kmer_sort_bits != 0 && p->kmer_sort_bits != 21 && p->kmer_sort_bits != 24 && p->kmer_sort_bits != 32 && p->kmer_sort_bits != 40) {
+        err = "kmer_sort_bits must be 0, 21, 24, 32 or 40"; return MB_E_ARG;
     }
+    if (p->kmer_sort_bits == 21 && p->kmer_format != 2) { err = "kmer_sort_bits 21 (re-coded key) needs kmer_format 2"; return MB_E_ARG; }
     if (p->accession_level != 0) { err = "accession_level != 0 is not on this path"; return MB_E_ARG; }
     return MB_OK;
 }
@@ -625,14 +626,20 @@ int mb_sort_kmers(mb_ctx *ctx) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_kmers) return fail(ctx, MB_E_ARG, "no k-mers resident");
     CK(cudaSetDevice(ctx->par.device));
-    // The join needs the queries of one DB block contiguous, not ordered (every query binary-searches the decoded
-    // block): ordering the leading `bits` of the 40 amino-acid bits takes bits/8 passes instead of 5.
+    // The join needs the queries of one DB block contiguous, not ordered (every query looks its group up in the decoded
+    // block): ordering the leading `bits` of the 40 amino-acid bits takes bits/8 passes instead of 5, and for format 2
+    // the re-coded 24-bit key (SortT mode 1, mb_common.cuh; kmer_sort_bits 21) resolves 5.6 residues in 3 passes.
     static const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;      // tuning knob
-    const int bits = env_bits ? env_bits : (ctx->par.kmer_sort_bits ? ctx->par.kmer_sort_bits : 32);
-    ctx->sort_shift = 40 - bits;
+    int bits = env_bits ? env_bits : ctx->par.kmer_sort_bits;
+    if (bits == 0 || (bits == 21 && ctx->par.kmer_format != 2)) bits = ctx->par.kmer_format == 2 ? 21 : 32;
+    if (bits != 21 && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 24, 32 or 40");
+    const bool packed = bits == 21;
+    ctx->sort_t.mode = packed ? 1 : 0;
+    ctx->sort_t.shift = packed ? 0 : 40 - bits;
     KmerKey key;
-    key.first_bit = 24 + ctx->sort_shift;
-    const int passes = bits / 8;
+    key.first_bit = 24 + ctx->sort_t.shift;
+    key.packed = packed ? 1 : 0;
+    const int passes = packed ? 3 : bits / 8;
     static const int k_items = getenv("MB_KSORT_ITEMS") ? atoi(getenv("MB_KSORT_ITEMS")) : 16;     // tuning knob
     int rc = 0;
     if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
@@ -659,7 +666,7 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
         CK(ctx->qstart.ensure(((size_t) nb + 1) * 2 * sizeof(u64)));
         u64 *qstart = ctx->qstart.as<u64>(), *qend = qstart + nb + 1;
         KL(KID_MATCH_PARTITION, k_match_partition<<<(nb + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
-                                                                   ctx->n_kmers, ctx->sort_shift, qstart, qend));
+                                                                   ctx->n_kmers, ctx->sort_t, qstart, qend));
         static bool match_attr_set = false;
         if (!match_attr_set) {
             CK(cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));

@@ -79,6 +79,63 @@ MB_HD u32 route_home(const Route &r, u32 seq) {
 #endif
 }
 
+// ---- order key of the query k-mer sort ---------------------------------------------------------------
+// The join only needs the queries of one DB block contiguous (mb_match.cuh), so the sort orders a monotone function T of the
+// 40-bit amino-acid part instead of all of it.  mode 0: T = aa >> shift (the leading 40-shift bits).  mode 1 (format 2 only):
+// the 5-bit codes of a format-2 metamer take 21 values (GeneticCode.h:34-193), so the five leading residues are re-coded
+// as one base-21 number (21^5 < 2^22) and the sixth residue adds two more bits: a 24-bit key — three 8-bit radix passes —
+// that resolves as much as the leading 27 raw bits would.  Monotone for codes <= 20, which is all the translation tables emit.
+struct SortT { int mode, shift; };
+MB_HD u32 sort_t_packed(u64 value) {
+    const u32 hi = (u32) (value >> 32);          // amino-acid bits 8..39
+    u32 t = hi >> 27;
+    t = t * 21u + ((hi >> 22) & 31u);
+    t = t * 21u + ((hi >> 17) & 31u);
+    t = t * 21u + ((hi >> 12) & 31u);
+    t = t * 21u + ((hi >> 7) & 31u);
+    return (t << 2) | ((((hi >> 2) & 31u) * 49u) >> 8);
+}
+MB_HD u64 sort_t(const SortT &k, u64 value) { return k.mode ? (u64) sort_t_packed(value) : (value >> 24) >> k.shift; }
+MB_HD bool sort_t_lossy(const SortT &k) { return k.mode != 0 || k.shift != 0; }
+
+// ---- bucket index of a decoded DB block (k_match) ------------------------------------------------------
+// A decoded block holds n ascending values; their amino-acid parts span [aa0, aa_last].  Instead of a binary search over
+// the whole block, a query looks its group up through MB_NBUCKET equal-width buckets of that span: bstart[b] = first
+// index whose bucket is >= b (b = 0..MB_NBUCKET), so the group of `aa` lies in [bstart[b], bstart[b+1]) — a handful of
+// entries — and a short binary search finishes.
+constexpr int MB_NBUCKET_LOG = 10;
+constexpr int MB_NBUCKET = 1 << MB_NBUCKET_LOG;
+MB_HD int bucket_shift(u64 aa0, u64 aa_last) {          // smallest shift with (aa_last - aa0) >> shift < MB_NBUCKET
+    u64 range = aa_last - aa0;
+    int sh = 0;
+    while ((range >> sh) >= (u64) MB_NBUCKET) ++sh;
+    return sh;
+}
+MB_HD u32 bucket_of(u64 aa, u64 aa0, int shift) { return (u32) ((aa - aa0) >> shift); }
+// first index in vals[lo, hi) whose amino-acid part is >= aa
+MB_HD u32 lower_bound_aa_range(const u64 *vals, u32 lo, u32 hi, u64 aa) {
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if ((vals[mid] >> 24) < aa) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+// candidate range [lo, lo + ncand) of a query with amino-acid part aa among vals[0, proc_end)
+template <typename BS>
+MB_HD u32 bucket_lookup(const u64 *vals, const BS *bstart, u32 proc_end, u64 aa0, u64 aa_last, int shift, u64 aa, u32 &ncand) {
+    ncand = 0;
+    if (aa < aa0 || aa > aa_last) return 0;
+    const u32 b = bucket_of(aa, aa0, shift);
+    u32 lo = bstart[b], hi = bstart[b + 1];
+    if (lo > proc_end) lo = proc_end;
+    if (hi > proc_end) hi = proc_end;
+    lo = lower_bound_aa_range(vals, lo, hi, aa);
+    u32 e = lo;
+    while (e < proc_end && (vals[e] >> 24) == aa) ++e;
+    ncand = e - lo;
+    return lo;
+}
+
 // ---- read-length arithmetic: src/commons/LocalUtil.h:45-59 ----------------------------------------
 MB_HD int max_covered_length(int len) {
     int r = len % 3;
@@ -210,7 +267,26 @@ MB_HD u64 metamer_from_window(const u8 *codonF, const u8 *codonR, u64 win48, boo
 
 // Closed-syncmer test of SyncmerScanner::next (SyncmerScanner.h:36-102) on a format-2 metamer:
 // the leftmost minimum of the 8-s+1 amino-acid s-mers must sit at offset 0 or 8-s.
+template <int S>
+MB_HD bool is_syncmer_fixed(u64 metamer) {         // s known at compile time: constant shifts, 32-bit s-mers (5*S <= 30)
+    const u64 aa = metamer >> 24;
+    constexpr u32 mask = (1u << (5 * S)) - 1u;
+    constexpr int last = 8 - S;
+    const u32 v0 = (u32) (aa >> (5 * last)) & mask, vl = (u32) aa & mask;
+    u32 mid = 0xFFFFFFFFu;                          // smallest s-mer strictly between the two ends
+#pragma unroll
+    for (int i = 1; i < last; ++i) {
+        const u32 v = (u32) (aa >> (5 * (last - i))) & mask;
+        mid = v < mid ? v : mid;
+    }
+    // leftmost minimum at offset 0: v0 <= every other one; at offset `last`: vl < every other one
+    const u32 rest0 = mid < vl ? mid : vl, restl = mid < v0 ? mid : v0;
+    return v0 <= rest0 || vl < restl;
+}
 MB_HD bool is_syncmer(u64 metamer, int s) {
+    if (s == 5) return is_syncmer_fixed<5>(metamer);        // the default --smer-len (LocalParameters.cpp)
+    if (s == 6) return is_syncmer_fixed<6>(metamer);
+    if (s == 4) return is_syncmer_fixed<4>(metamer);
     const u64 aa = metamer >> 24;
     const u64 mask = (1ull << (5 * s)) - 1;
     const int last = 8 - s;

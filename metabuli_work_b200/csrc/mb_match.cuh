@@ -20,12 +20,16 @@
 //   2. decodes it cooperatively: each thread assembles the deltas ending in its 10 words, a block
 //      scan of (count, 64-bit delta sum) turns them into absolute values in shared memory,
 //   3. joins its query slice, one query per thread, warps running independently (32 queries per ticket,
-//      no block barrier): binary search of the AA part in the decoded block, ONE Hamming evaluation per
-//      candidate through a two-codon table in shared memory (distances cached in a packed register),
+//      no block barrier): the AA part is looked up through a 1024-bucket index of the decoded block (built
+//      in the same sweep that finds the group boundaries), ONE Hamming evaluation per candidate through a
+//      two-codon table in shared memory,
 //   4. compacts matches per warp: records are staged in a per-warp shared-memory buffer and flushed with
 //      one atomic reservation and coalesced 8-byte stores when the buffer fills.
 // The kernel is persistent (one CTA per resident slot, DB blocks handed out by an atomic ticket), so the
-// tables are loaded into shared memory once per CTA and staged matches survive from block to block.
+// tables are loaded into shared memory once per CTA and staged matches survive from block to block.  Tickets
+// are drawn one block ahead: while a CTA joins block b, one of its warps pulls the words, the info entries and
+// the query slice of its NEXT block into L2 (prefetch.global.L2), and the query loads of the ticket loop are
+// software-pipelined, so the join itself waits on L2, not on HBM.
 // Groups longer than the overhang are re-decoded from their own start; groups longer than a whole
 // chunk take a streaming two-pass path.  Capacity misses are counted, never written out of bounds;
 // the host grows the buffer and reruns (the reference's retry, Classifier.cpp:127-131).
@@ -79,8 +83,9 @@ struct MatchSmem {
     u64 reserve_base;
     u32 warp_tot[MT_THREADS / 32];
     u32 qnext;                             // next 32-query ticket of the current chunk
-    u32 cur_block;                         // DB block this CTA is working on (persistent loop)
+    u32 tick[2];                           // persistent loop: DB block tickets, fetched one block ahead
     u64 qadv;
+    u16 bstart[MB_NBUCKET + 2];            // bucket index of the decoded chunk (bucket_lookup, mb_common.cuh)
 };
 
 // the part of the shared memory that lives for the whole (persistent) kernel
@@ -168,14 +173,34 @@ __device__ __forceinline__ u32 decode_chunk(const DbView &db, const DbCursor &c,
     return ctot;
 }
 
-// first index in vals[0, n) whose AA part is >= aa
-__device__ __forceinline__ u32 lower_bound_aa(const u64 *vals, u32 n, u64 aa) {
-    u32 lo = 0, hi = n;
-    while (lo < hi) {
-        const u32 mid = (lo + hi) >> 1;
-        if ((vals[mid] >> 24) < aa) lo = mid + 1; else hi = mid;
-    }
-    return lo;
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// One warp warms L2 with what DB block nb will touch: its words, its info entries and its query slice.  Also asks for
+// the index entries that some CTA will read `ahead` tickets from now.  Every address stays inside its allocation.
+__device__ __forceinline__ void prefetch_block(const DbView &db, const BlockIndex *__restrict__ blocks, u32 n_blocks,
+                                               const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
+                                               const u64 *__restrict__ qend_of, u32 nb, u32 ahead) {
+    const u32 lane = threadIdx.x & 31;
+    if (nb >= n_blocks) return;
+    if (lane == 0 && nb + ahead < n_blocks) { prefetch_l2(blocks + nb + ahead); prefetch_l2(qstart + nb + ahead); prefetch_l2(qend_of + nb + ahead); }
+    if (!blocks[nb].owns) return;
+    const u64 qs = qstart[nb], qe = qend_of[nb];
+    if (qs >= qe) return;
+    const u64 word = blocks[nb].word & ~7ull, kidx = blocks[nb].kidx;
+    u64 nk = DB_W / 2;
+    if (nb + 1 < n_blocks && blocks[nb + 1].owns && blocks[nb + 1].kidx > kidx) nk = blocks[nb + 1].kidx - kidx;
+    if (nk > (u64) DB_C) nk = DB_C;
+    if (kidx + nk > db.n_kmers_eff) nk = db.n_kmers_eff > kidx ? db.n_kmers_eff - kidx : 0;
+    const char *w = reinterpret_cast<const char *>(db.words + word);
+    u64 wbytes = (db.n_words + DB_PAD - word) * 2;
+    if (wbytes > (u64) (DB_C + 16) * 2) wbytes = (u64) (DB_C + 16) * 2;
+    for (u64 o = (u64) lane * 128; o < wbytes; o += 32 * 128) prefetch_l2(w + o);
+    const char *inf = reinterpret_cast<const char *>(db.info + kidx);
+    for (u64 o = (u64) lane * 128; o < nk * 4; o += 32 * 128) prefetch_l2(inf + o);
+    u64 qn = qe - qs;
+    if (qn > 8192) qn = 8192;
+    const char *qp = reinterpret_cast<const char *>(q + qs);
+    for (u64 o = (u64) lane * 128; o < qn * 16; o += 32 * 128) prefetch_l2(qp + o);
 }
 
 struct MatchOut {
@@ -439,17 +464,23 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
     }
     u32 fill = 0;                                   // matches staged by this warp (warp-uniform)
 
-    while (true) {
-        __syncthreads();                            // previous block is done with the shared arrays
-        if (tid == 0) s.cur_block = atomicAdd(block_ticket, 1u);
-        __syncthreads();
-        const u32 b = s.cur_block;
-        if (b >= n_blocks) break;
+    // Block tickets are drawn one block ahead: tick[it & 1] is the block of iteration `it`, tick[(it + 1) & 1] the next one
+    // (known from the start, so that it can be prefetched).  Thread 0 draws the ticket after that at the start of the
+    // iteration, keeps it in a register and publishes it in the slot of the current block just before the closing barrier.
+    if (tid == 0) { s.tick[0] = atomicAdd(block_ticket, 1u); s.tick[1] = atomicAdd(block_ticket, 1u); }
+    __syncthreads();
+    u32 b = s.tick[0];
+    for (u32 it = 0; b < n_blocks; ++it) {
+        const u32 nb = s.tick[(it + 1) & 1];
+        u32 drawn = 0;
+        if (tid == 0) drawn = atomicAdd(block_ticket, 1u);
+        if (warp == MT_THREADS / 32 - 1) prefetch_block(db, blocks, n_blocks, q, qstart, qend_of, nb, gridDim.x);
+        do {
         const BlockIndex bi = blocks[b];
-        if (!bi.owns) continue;
+        if (!bi.owns) break;
         const u64 qcur = qstart[b];
         const u64 qend = qend_of[b];
-        if (qcur >= qend) continue;                 // no query falls into this block's AA range
+        if (qcur >= qend) break;                    // no query falls into this block's AA range
 
         const u64 tile_end = (u64) (b + 1) * DB_W;  // groups starting at or after this word belong to later blocks
         DbCursor c{bi.word, bi.vbefore, bi.kidx};
@@ -457,14 +488,33 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
         while (true) {
             const u32 n = decode_chunk(db, c, s);
             if (n == 0) break;
-            if (tid == 0) { s.last_start = 0; s.own_end = (int) n; s.qnext = 0; }
+            if (tid == 0) { s.last_start = 0; s.own_end = (int) n; s.qnext = 0; s.bstart[0] = 0; }
+            // bucket index over the amino-acid span of the chunk (bucket_lookup)
+            const u64 aa0 = s.vals[0] >> 24, aal = s.vals[n - 1] >> 24;
+            int bsh = 64 - __clzll((long long) (aal - aa0)) - MB_NBUCKET_LOG;
+            bsh = bsh > 0 ? bsh : 0;
             __syncthreads();
             const u64 own_limit = tile_end > c.word ? tile_end - c.word : 0;   // local word offset of the block end
-            for (u32 j = tid + 1; j < n; j += MT_THREADS) {
-                if ((s.vals[j] >> 24) != (s.vals[j - 1] >> 24)) {
-                    atomicMax(&s.last_start, (int) j);
-                    // first word of k-mer j is the word after the previous terminator
-                    if ((u64) s.wend[j - 1] + 1 >= own_limit) atomicMin(&s.own_end, (int) j);
+            {
+                // one sweep over the group boundaries: last group start, first group that starts in a later block, and
+                // bstart[] of every bucket that begins between two neighbours
+                int lmax = 0, lmin = (int) n;
+                for (u32 j = tid + 1; j < n; j += MT_THREADS) {
+                    const u64 a = s.vals[j] >> 24, pa = s.vals[j - 1] >> 24;
+                    if (a != pa) {
+                        lmax = (int) j;
+                        // first word of k-mer j is the word after the previous terminator
+                        if ((u64) s.wend[j - 1] + 1 >= own_limit && (int) j < lmin) lmin = (int) j;
+                        const u32 bj = bucket_of(a, aa0, bsh), bp = bucket_of(pa, aa0, bsh);
+                        for (u32 bb = bp + 1; bb <= bj; ++bb) s.bstart[bb] = (u16) j;
+                    }
+                }
+                for (u32 bb = bucket_of(aal, aa0, bsh) + 1 + tid; bb <= (u32) MB_NBUCKET; bb += MT_THREADS) s.bstart[bb] = (u16) n;
+                lmax = __reduce_max_sync(0xFFFFFFFFu, lmax);
+                lmin = __reduce_min_sync(0xFFFFFFFFu, lmin);
+                if (lane == 0) {
+                    if (lmax) atomicMax(&s.last_start, lmax);
+                    if (lmin < (int) n) atomicMin(&s.own_end, lmin);
                 }
             }
             __syncthreads();
@@ -485,30 +535,26 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
 
             // ---- fast path: all groups in [0, proc_end) are complete and owned.  Warps run on their own; every query
             // of the block's range is looked up (the range is not ordered below the sorted bits, and it also holds
-            // queries of the neighbouring blocks: those find no group of their amino-acid part here). ----
-            while (true) {
-                u32 base = 0;
-                if (lane == 0) base = atomicAdd(&s.qnext, 32u);
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (qcur + base >= qend) break;
-                const u64 qi = qcur + base + lane;
+            // queries of the neighbouring blocks: those find no group of their amino-acid part here).  The query
+            // record of the NEXT ticket is requested before the current one is processed. ----
+            u32 base = 0;
+            if (lane == 0) base = atomicAdd(&s.qnext, 32u);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            ulonglong2 v_next = make_ulonglong2(0, 0);
+            if (qcur + base + lane < qend) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qcur + base + lane));
+            while (qcur + base < qend) {
                 mb_kmer qk;
-                qk.value = 0; qk.qinfo = 0;
-                bool mine = false;
-                if (qi < qend) {
-                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(q + qi));
-                    qk.value = v.x; qk.qinfo = v.y;
-                    mine = true;
+                qk.value = v_next.x; qk.qinfo = v_next.y;
+                const bool mine = qcur + base + lane < qend;
+                {
+                    u32 base_n = 0;
+                    if (lane == 0) base_n = atomicAdd(&s.qnext, 32u);
+                    base = __shfl_sync(0xFFFFFFFFu, base_n, 0);
+                    if (qcur + base + lane < qend) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qcur + base + lane));
                 }
                 // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
                 u32 lo = 0, ncand = 0;
-                if (mine) {
-                    const u64 aa = qk.value >> 24;
-                    lo = lower_bound_aa(s.vals, proc_end, aa);
-                    u32 hi = lo;
-                    while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
-                    ncand = hi - lo;
-                }
+                if (mine) lo = bucket_lookup(s.vals, s.bstart, proc_end, aa0, aal, bsh, qk.value >> 24, ncand);
                 // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
                 // whose exclusive prefix of ncand is the largest one <= p
                 u32 incl = ncand;
@@ -525,7 +571,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 qmin[lane] = 255;
                 __syncwarp();
                 const u32 rounds = (total + 31) / 32;
-                u32 d_first = 0, owner_first = 0, j_first = 0;           // pair of round 0 is kept for the emit pass
+                u32 pk0 = 255, pk1 = 255;           // pairs of rounds 0 and 1 are kept for the emit pass: dd | owner << 8 | j << 16
                 for (u32 r = 0; r < rounds; ++r) {
                     const u32 p = r * 32 + lane;
                     u32 owner = 0;
@@ -545,7 +591,9 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                         dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
                         atomicMin(&qmin[owner], dd);
                     }
-                    if (r == 0) { d_first = dd; owner_first = owner; j_first = j; }
+                    const u32 pk = dd | (owner << 8) | (j << 16);
+                    if (r == 0) pk0 = pk;
+                    else if (r == 1) pk1 = pk;
                 }
                 __syncwarp();
                 // (3) emit: distance <= min(2 * min, 7) (KmerMatcher.cpp:1126); one staging slot per surviving pair
@@ -553,7 +601,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 for (u32 r = 0; r < rounds; ++r) {
                     const u32 p = r * 32 + lane;
                     u32 owner, dd, j;
-                    if (r == 0) { owner = owner_first; dd = d_first; j = j_first; }
+                    if (r < 2) { const u32 pk = r == 0 ? pk0 : pk1; dd = pk & 255u; owner = (pk >> 8) & 31u; j = pk >> 16; }
                     else {
                         owner = 0;
 #pragma unroll
@@ -597,6 +645,10 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
             __syncthreads();
             c.word = nw; c.vbefore = nv; c.kidx += proc_end;
         }
+        } while (false);
+        if (tid == 0) s.tick[it & 1] = drawn;
+        __syncthreads();                            // this block is done with the shared arrays; the new ticket is visible
+        b = nb;
     }
     warp_flush<ROUTED>(mo, tb.stage[warp], fill);
 }
@@ -688,25 +740,25 @@ k_db_decode(DbView db, u32 n_blocks, const u32 *__restrict__ blk_back, const u32
 }
 
 // ---- per-batch partition: the query range a block has to look at ------------------------------------------
-// The queries are ordered by T(aa) = aa >> shift only.  Block b owns the amino-acid groups [own_aa(b), own_aa(b+1)),
+// The queries are ordered by T(aa) only (SortT, mb_common.cuh: leading bits or the re-coded 24-bit key).  Block b owns the amino-acid groups [own_aa(b), own_aa(b+1)),
 // so it scans the queries with T(own_aa(b)) <= T(aa) <= T(own_aa(b+1)): the buckets at both ends are shared with the
 // neighbouring blocks, which is harmless because a query only finds its group in the block that owns it.
-__device__ __forceinline__ u64 query_lower_bound_t(const mb_kmer *__restrict__ q, u64 nq, int shift, u64 t) {
+__device__ __forceinline__ u64 query_lower_bound_t(const mb_kmer *__restrict__ q, u64 nq, const SortT &st, u64 t) {
     u64 lo = 0, hi = nq;
     while (lo < hi) {
         const u64 mid = (lo + hi) >> 1;
-        if (((__ldg(&q[mid].value) >> 24) >> shift) < t) lo = mid + 1; else hi = mid;
+        if (sort_t(st, __ldg(&q[mid].value)) < t) lo = mid + 1; else hi = mid;
     }
     return lo;
 }
-__global__ void k_match_partition(const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, u64 nq, int shift,
+__global__ void k_match_partition(const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, u64 nq, SortT st,
                                   u64 *__restrict__ qstart, u64 *__restrict__ qend) {
     const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_blocks) return;
     if (!blocks[b].owns) { qstart[b] = 0; qend[b] = 0; return; }
-    qstart[b] = query_lower_bound_t(q, nq, shift, blocks[b].own_aa >> shift);
+    qstart[b] = query_lower_bound_t(q, nq, st, sort_t(st, blocks[b].own_aa << 24));
     const u64 nxt = b + 1 < n_blocks ? blocks[b + 1].own_aa : ~0ull;
-    qend[b] = nxt == ~0ull ? nq : query_lower_bound_t(q, nq, shift, (nxt >> shift) + (shift ? 1 : 0));
+    qend[b] = nxt == ~0ull ? nq : query_lower_bound_t(q, nq, st, sort_t(st, nxt << 24) + (sort_t_lossy(st) ? 1 : 0));
 }
 
 } // namespace mb

@@ -27,7 +27,11 @@ constexpr u64 RS_VALUE_MASK = (1ull << 62) - 1;
 // ---- key functors: digit(record, pass) in [0,256) -------------------------------------------------
 struct KmerKey {            // sort by the amino-acid part and then the DNA part of Kmer::value
     int first_bit;          // 24 = order the 40 AA bits only (all the join needs); 0 = full value
-    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const { return (u32) (r.value >> (first_bit + 8 * pass)) & 255u; }
+    int packed;             // 1: digits of the 24-bit re-coded key sort_t_packed (mb_common.cuh)
+    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const {
+        if (packed) return (sort_t_packed(r.value) >> (8 * pass)) & 255u;
+        return (u32) (r.value >> (first_bit + 8 * pass)) & 255u;
+    }
 };
 
 struct KmerOwnerKey {       // multi-GPU bucketing: owner shard = number of bounds <= value

@@ -378,7 +378,9 @@ MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_leng
     if (max_q + 1 > scr.cap_b) { *error_flag = 2; return 0; }
     for (int k = 0; k <= max_q; ++k) { scr.bucket_ham[k] = 255; scr.bucket_tax[k] = 0; }
     for (int i = best.rb; i < best.re; ++i) {
-        const int qd = (int) (qi_pos(m[i].qinfo) / (u32) cfg.dna_shift);
+        // dna_shift is 3 (plain) or 9 (syncmers, s = 5) in practice: constant divisions instead of the general sequence
+        const u32 pos_i = qi_pos(m[i].qinfo);
+        const int qd = (int) (cfg.dna_shift == 3 ? pos_i / 3u : cfg.dna_shift == 9 ? pos_i / 9u : pos_i / (u32) cfg.dna_shift);
         if (qd > max_q) continue;
         const u8 h = m[i].hamming;
         if (scr.bucket_ham[qd] == 255 || h < scr.bucket_ham[qd]) { scr.bucket_tax[qd] = m[i].targetId; scr.bucket_ham[qd] = h; }

@@ -159,6 +159,15 @@ k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, con
         const u32 r1 = r0 + 8 < n_reads ? r0 + 8 : n_reads;
         for (u32 r = r0; r < r1; ++r) {
             const u64 b = seg_begin[r], e = seg_end[r];
+            // the records of the NEXT read are pulled into L2 while this one is sorted (a warp otherwise waits on HBM
+            // at the start of every segment)
+            if (r + 1 < n_reads) {
+                const u64 nb = seg_begin[r + 1], ne = seg_end[r + 1];
+                const char *pb = reinterpret_cast<const char *>(in64 + nb * 3);
+                const u64 bytes = (ne - nb) * sizeof(mb_match);
+                for (u64 o = (u64) lane * 128; o < bytes && o < 16384; o += 32 * 128)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + o));
+            }
             const u32 n = (u32) (e - b);
             if (n == 0) continue;
             if (n > SS_CAP) {

@@ -43,6 +43,21 @@ class Golden:
         return rows
 
 
+def kmer_sort_key(values, sort_bits, kmer_format):
+    """The key mb_sort_kmers orders by (SortT, csrc/mb_common.cuh): leading amino-acid bits, or for format 2 by default
+    (kmer_sort_bits 21) the five leading residues as a base-21 number plus two bits of the sixth."""
+    values = np.asarray(values, dtype=np.uint64)
+    if not sort_bits:
+        sort_bits = 21 if kmer_format == 2 else 32
+    if sort_bits != 21:
+        return values >> np.uint64(24 + 40 - sort_bits)
+    hi = (values >> np.uint64(32)).astype(np.uint64)
+    t = hi >> np.uint64(27)
+    for sh in (22, 17, 12, 7):
+        t = t * np.uint64(21) + ((hi >> np.uint64(sh)) & np.uint64(31))
+    return (t << np.uint64(2)) | ((((hi >> np.uint64(2)) & np.uint64(31)) * np.uint64(49)) >> np.uint64(8))
+
+
 def taxcnt_string(ids, cnt, b, e):
     s = " ".join(f"{a}:{c}" for a, c in zip(ids[b:e], cnt[b:e]))
     return s + " " if s else s
@@ -89,6 +104,9 @@ def emu_lib():
     L.emu_score.argtypes = [vp, sz, vp, u32, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
                             C.c_float, vp, vp, vp, vp, i32, i32, i32, vp, vp, vp, sz]
     L.emu_set_fast.argtypes = [C.c_int]
+    L.emu_is_syncmer.argtypes = [vp, sz, C.c_int, vp]
+    L.emu_sort_t.argtypes = [C.c_int, C.c_int, vp, sz, vp]
+    L.emu_bucket_lookup.argtypes = [vp, u32, u32, vp, sz, vp, vp]
     L.emu_fast_fallbacks.restype = C.c_long
     return L
 

@@ -126,3 +126,90 @@ def test_score_read_logic(golden, emu, case, min_sp, fast):
         assert emu.emu_fast_fallbacks() * 5 < b.n        # the streaming form holds the typical short read
     emu.emu_set_fast(0)
     db.close()
+
+
+@pytest.mark.parametrize("case", ["plain_paired", "sync_paired", "sync_long"])
+def test_sort_key_recoded(golden, emu, case):
+    """The re-coded 24-bit sort key (format 2) is monotone over ascending metamers of queries AND of the database (the
+    partition of k_match relies on it), fits 24 bits and equals the numpy restatement used by the GPU tests."""
+    meta = golden.cases[case]
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=meta["seq_mode"])
+    assert p.kmer_format == 2
+    _, s1, s2 = golden.reads(case)
+    k = orc.sort_kmers(orc.extract(p, orc.Batch(s1, s2)))
+    dbv, _ = db.decode()
+    for values in (np.ascontiguousarray(k["value"]), np.ascontiguousarray(dbv)):
+        out = np.zeros(len(values), dtype=np.uint64)
+        emu.emu_sort_t(1, 0, _ptr(values), len(values), _ptr(out))
+        assert np.all(out[1:] >= out[:-1])
+        assert int(out.max()) < (1 << 24)
+        assert np.array_equal(out, helpers.kmer_sort_key(values, 21, 2))
+        # it must separate at least as well as the leading 25 raw bits... and never split equal amino-acid parts
+        aa = values >> np.uint64(24)
+        same = aa[1:] == aa[:-1]
+        assert np.all(out[1:][same] == out[:-1][same])
+    # plain leading-bits mode
+    v = np.ascontiguousarray(k["value"])
+    out = np.zeros(len(v), dtype=np.uint64)
+    emu.emu_sort_t(0, 8, _ptr(v), len(v), _ptr(out))
+    assert np.array_equal(out, v >> np.uint64(32))
+    db.close()
+
+
+@pytest.mark.parametrize("case", ["plain_paired", "sync_paired", "legacy_paired"])
+def test_block_bucket_lookup(golden, emu, case):
+    """k_match's bucket index of a decoded block finds exactly the amino-acid group a binary search finds, for chunks
+    cut anywhere in the database, with proc_end cutting the chunk short, and for queries outside the chunk's span."""
+    meta = golden.cases[case]
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=meta["seq_mode"])
+    _, s1, s2 = golden.reads(case)
+    k = orc.extract(p, orc.Batch(s1, s2))
+    dbv, _ = db.decode()
+    dbv = np.ascontiguousarray(dbv)
+    rng = np.random.default_rng(11)
+    qv = np.ascontiguousarray(k["value"][rng.integers(0, len(k), 4000)])
+    for trial in range(12):
+        n = int(rng.integers(1, 2560))
+        a = int(rng.integers(0, max(1, len(dbv) - n)))
+        vals = np.ascontiguousarray(dbv[a:a + n])
+        n = len(vals)
+        proc_end = n if trial % 3 == 0 else int(rng.integers(1, n + 1))
+        # queries: random k-mers of the reads, the chunk's own values (guaranteed hits) and its two ends
+        qs = np.concatenate([qv, vals[rng.integers(0, n, 500)], vals[:1], vals[-1:], vals[:1] - np.uint64(1 << 24), vals[-1:] + np.uint64(1 << 24)])
+        qs = np.ascontiguousarray(qs)
+        lo = np.zeros(len(qs), dtype=np.uint32)
+        nc = np.zeros(len(qs), dtype=np.uint32)
+        emu.emu_bucket_lookup(_ptr(vals), n, proc_end, _ptr(qs), len(qs), _ptr(lo), _ptr(nc))
+        aa = vals[:proc_end] >> np.uint64(24)
+        qa = qs >> np.uint64(24)
+        want_lo = np.searchsorted(aa, qa, side="left")
+        want_hi = np.searchsorted(aa, qa, side="right")
+        want_n = want_hi - want_lo
+        assert np.array_equal(nc, want_n.astype(np.uint32))
+        hit = want_n > 0
+        assert np.array_equal(lo[hit], want_lo[hit].astype(np.uint32))
+    db.close()
+
+
+@pytest.mark.parametrize("s", [3, 4, 5, 6, 7])
+def test_syncmer_predicate(emu, s):
+    """is_syncmer (compile-time forms for s = 4, 5, 6 and the loop) against the definition of SyncmerScanner.h:36-102:
+    the LEFTMOST minimum of the 8-s+1 amino-acid s-mers sits at offset 0 or 8-s.  Low-entropy residues force ties."""
+    rng = np.random.default_rng(s)
+    n = 20000
+    aa = np.zeros(n, dtype=np.uint64)
+    for i in range(8):
+        hi = 21 if i % 2 == 0 else 3
+        aa = (aa << np.uint64(5)) | rng.integers(0, hi, n).astype(np.uint64)
+    aa[: n // 4] = (aa[: n // 4] & np.uint64(0x1F)) * np.uint64(0x0842108421)      # one residue repeated eight times
+    values = np.ascontiguousarray((aa << np.uint64(24)) | rng.integers(0, 1 << 24, n).astype(np.uint64))
+    out = np.zeros(n, dtype=np.uint8)
+    emu.emu_is_syncmer(_ptr(values), n, s, _ptr(out))
+    last = 8 - s
+    mask = np.uint64((1 << (5 * s)) - 1)
+    smers = np.stack([(aa >> np.uint64(5 * (last - i))) & mask for i in range(last + 1)], axis=1)
+    arg = np.argmin(smers, axis=1)                  # numpy returns the first minimum
+    want = ((arg == 0) | (arg == last)).astype(np.uint8)
+    assert np.array_equal(out, want)

@@ -66,8 +66,8 @@ def run_all_stages(mb, dbdir, seq_mode, s1, s2, sort_bits=0, **kw):
         assert np.array_equal(canon_k(clf.kmers()), ok)                      # K1
         clf.sort_kmers()
         ks = clf.kmers()
-        t = ks["value"] >> np.uint64(24 + 40 - (sort_bits or 32))
-        assert np.all(t[1:] >= t[:-1])                                        # K2: ordered by the leading amino-acid bits
+        t = helpers.kmer_sort_key(ks["value"], sort_bits, int(p.kmer_format))
+        assert np.all(t[1:] >= t[:-1])                                        # K2: ordered by the sort's key (leading AA bits / re-coded)
         assert np.array_equal(canon_k(ks), ok)
         nm = clf.match()
         assert nm == len(om)
@@ -98,7 +98,7 @@ def test_golden_case_all_stages(golden, mb, case):
     assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
 
 
-@pytest.mark.parametrize("bits", [24, 40])
+@pytest.mark.parametrize("bits", [24, 32, 40])
 def test_kmer_sort_bits(golden, mb, bits):
     """The join result does not depend on how many leading amino-acid bits the query sort orders."""
     _, s1, s2 = golden.reads("sync_paired")
