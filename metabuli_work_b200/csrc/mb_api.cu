@@ -638,11 +638,16 @@ int mb_sort_kmers(mb_ctx *ctx) {
     ctx->sort_t.shift = packed ? 0 : 40 - bits;
     KmerKey key;
     key.first_bit = 24 + ctx->sort_t.shift;
-    key.packed = packed ? 1 : 0;
     const int passes = packed ? 3 : bits / 8;
     static const int k_items = getenv("MB_KSORT_ITEMS") ? atoi(getenv("MB_KSORT_ITEMS")) : 16;     // tuning knob
     int rc = 0;
-    if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+    if (packed) {
+        KmerKeyPacked pk;
+        if (k_items == 8) rc = radix_sort<mb_kmer, KmerKeyPacked, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+        else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKeyPacked, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+        else rc = radix_sort<mb_kmer, KmerKeyPacked, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+    }
+    else if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
     else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
     else rc = radix_sort<mb_kmer, KmerKey, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
     if (rc) return rc;
@@ -669,8 +674,10 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
                                                                    ctx->n_kmers, ctx->sort_t, qstart, qend));
         static bool match_attr_set = false;
         if (!match_attr_set) {
-            CK(cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
-            CK(cudaFuncSetAttribute(k_match<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
             match_attr_set = true;
         }
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
@@ -686,15 +693,24 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
             mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag; mo.route = nullptr;
             CK(cudaMemsetAsync(&ctx->dcnt()->match_ticket, 0, sizeof(u32), ctx->stream));
             if (routed) CK(cudaMemsetAsync(ctx->route.sent_m, 0, MB_MAX_RANKS * sizeof(unsigned long long), ctx->stream));
-            const unsigned grid = (unsigned) std::min<u64>(nb, 148ull * 3);     // persistent: 3 CTAs per SM (70 KB smem each)
-            if (!routed)
-                KL(KID_MATCH, k_match<false><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
-                                  db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
-                                  ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, nullptr));
-            else
-                KL(KID_MATCH, k_match<true><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>(
-                                  db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo,
-                                  ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, ctx->route_dev.as<Route>()));
+            // persistent: as many CTAs as are resident at once (4 per SM: 55 KB shared memory, 64 registers)
+            static int match_ctas = 0;
+            if (!match_ctas) {
+                int per_sm = 0, sms = 148;
+                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_match<false, false>, MT_THREADS, match_smem_bytes()));
+                CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
+                static const int env_ctas = getenv("MB_MATCH_CTAS_PER_SM") ? atoi(getenv("MB_MATCH_CTAS_PER_SM")) : 0;     // tuning knob
+                if (env_ctas > 0 && env_ctas < per_sm) per_sm = env_ctas;
+                match_ctas = std::max(1, per_sm) * sms;
+            }
+            const unsigned grid = (unsigned) std::min<u64>(nb, (u64) match_ctas);
+            static const int buckets = getenv("MB_MATCH_LOOKUP") ? atoi(getenv("MB_MATCH_LOOKUP")) : 0;   // tuning knob: 1 = bucket index
+#define MB_LAUNCH_MATCH(R, B, ROUTE) KL(KID_MATCH, (k_match<R, B><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>( \
+                db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo, \
+                ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, ROUTE)))
+            if (!routed) { if (buckets) MB_LAUNCH_MATCH(false, true, nullptr); else MB_LAUNCH_MATCH(false, false, nullptr); }
+            else { if (buckets) MB_LAUNCH_MATCH(true, true, ctx->route_dev.as<Route>()); else MB_LAUNCH_MATCH(true, false, ctx->route_dev.as<Route>()); }
+#undef MB_LAUNCH_MATCH
             if (routed) { if (int rc = publish_sent(ctx, 1)) return rc; }
             unsigned long long total = 0;
             if (int rc = read_back(ctx, &ctx->dcnt()->match_count, &total)) return rc;

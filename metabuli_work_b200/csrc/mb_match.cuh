@@ -68,7 +68,7 @@ struct DbView {
 
 struct DbCursor { u64 word, vbefore, kidx; };
 
-constexpr int MT_STAGE = 160;              // matches staged per warp before a flush
+constexpr int MT_STAGE = 64;               // matches staged per warp before a flush
 
 struct MatchSmem {
     __align__(16) u16 w[DB_C + 16];
@@ -439,8 +439,8 @@ __device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, 
     return lo;
 }
 
-template <bool ROUTED>
-__global__ void __launch_bounds__(MT_THREADS, 3)
+template <bool ROUTED, bool BUCKETS>
+__global__ void __launch_bounds__(MT_THREADS, 4)
 k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
         const u64 *__restrict__ qend_of, MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *block_ticket,
         const Route *__restrict__ route_g) {
@@ -505,11 +505,14 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                         lmax = (int) j;
                         // first word of k-mer j is the word after the previous terminator
                         if ((u64) s.wend[j - 1] + 1 >= own_limit && (int) j < lmin) lmin = (int) j;
-                        const u32 bj = bucket_of(a, aa0, bsh), bp = bucket_of(pa, aa0, bsh);
-                        for (u32 bb = bp + 1; bb <= bj; ++bb) s.bstart[bb] = (u16) j;
+                        if (BUCKETS) {
+                            const u32 bj = bucket_of(a, aa0, bsh), bp = bucket_of(pa, aa0, bsh);
+                            for (u32 bb = bp + 1; bb <= bj; ++bb) s.bstart[bb] = (u16) j;
+                        }
                     }
                 }
-                for (u32 bb = bucket_of(aal, aa0, bsh) + 1 + tid; bb <= (u32) MB_NBUCKET; bb += MT_THREADS) s.bstart[bb] = (u16) n;
+                if (BUCKETS)
+                    for (u32 bb = bucket_of(aal, aa0, bsh) + 1 + tid; bb <= (u32) MB_NBUCKET; bb += MT_THREADS) s.bstart[bb] = (u16) n;
                 lmax = __reduce_max_sync(0xFFFFFFFFu, lmax);
                 lmin = __reduce_min_sync(0xFFFFFFFFu, lmin);
                 if (lane == 0) {
@@ -554,7 +557,16 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 }
                 // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
                 u32 lo = 0, ncand = 0;
-                if (mine) lo = bucket_lookup(s.vals, s.bstart, proc_end, aa0, aal, bsh, qk.value >> 24, ncand);
+                if (mine) {
+                    if (BUCKETS) lo = bucket_lookup(s.vals, s.bstart, proc_end, aa0, aal, bsh, qk.value >> 24, ncand);
+                    else {
+                        const u64 aa = qk.value >> 24;
+                        lo = lower_bound_aa_range(s.vals, 0, proc_end, aa);
+                        u32 hi = lo;
+                        while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
+                        ncand = hi - lo;
+                    }
+                }
                 // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
                 // whose exclusive prefix of ncand is the largest one <= p
                 u32 incl = ncand;

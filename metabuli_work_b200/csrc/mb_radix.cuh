@@ -27,11 +27,10 @@ constexpr u64 RS_VALUE_MASK = (1ull << 62) - 1;
 // ---- key functors: digit(record, pass) in [0,256) -------------------------------------------------
 struct KmerKey {            // sort by the amino-acid part and then the DNA part of Kmer::value
     int first_bit;          // 24 = order the 40 AA bits only (all the join needs); 0 = full value
-    int packed;             // 1: digits of the 24-bit re-coded key sort_t_packed (mb_common.cuh)
-    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const {
-        if (packed) return (sort_t_packed(r.value) >> (8 * pass)) & 255u;
-        return (u32) (r.value >> (first_bit + 8 * pass)) & 255u;
-    }
+    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const { return (u32) (r.value >> (first_bit + 8 * pass)) & 255u; }
+};
+struct KmerKeyPacked {      // digits of the 24-bit re-coded key sort_t_packed (mb_common.cuh), format 2 only
+    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const { return (sort_t_packed(r.value) >> (8 * pass)) & 255u; }
 };
 
 struct KmerOwnerKey {       // multi-GPU bucketing: owner shard = number of bounds <= value
@@ -142,20 +141,24 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
         in_eff = reinterpret_cast<const Rec *>(seg.base[r]) - seg.prefix[r];
         split = r + 1 < seg.n && tile_base + TILE > seg.prefix[r + 1];
     }
+    // all loads first (one independent batch per thread), digits afterwards
     if (SEG && split) {
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const u64 idx = wbase + (u64) j * 32 + lane;
-            if (idx < n) { rec[j] = *seg_ptr(seg, in, idx); dig[j] = key.digit(rec[j], pass); }
-            else dig[j] = 0xFFFFFFFFu;
+            if (idx < n) rec[j] = *seg_ptr(seg, in, idx);
         }
     } else {
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const u64 idx = wbase + (u64) j * 32 + lane;
-            if (idx < n) { rec[j] = in_eff[idx]; dig[j] = key.digit(rec[j], pass); }
-            else dig[j] = 0xFFFFFFFFu;
+            if (idx < n) rec[j] = in_eff[idx];
         }
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u64 idx = wbase + (u64) j * 32 + lane;
+        dig[j] = idx < n ? key.digit(rec[j], pass) : 0xFFFFFFFFu;
     }
     // early counts: the tile's digit histogram is published BEFORE the ranking, so that by the time this tile looks
     // back its predecessors (which started earlier) have long published theirs

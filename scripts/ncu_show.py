@@ -11,16 +11,11 @@ want = ['Kernel Name', 'gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__
         'l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum', 'l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum',
         'l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum', 'l1tex__t_requests_pipe_lsu_mem_global_op_st.sum',
         'lts__t_sector_hit_rate.pct']
-want += [h for h in hdr if 'warp_issue_stalled' in h and h.endswith('_per_warp_active.pct')]
+want += [h for h in hdr if 'issue_stalled' in h and ('per_warp_active' in h or 'pcsamp' in h) and 'not_issued' not in h]
 for r in rows[2:]:
     print('-----')
     for w in want:
         if w in hdr:
             i = hdr.index(w)
             v = r[i]
-            try:
-                if 'stalled' in w and float(v) < 3:
-                    continue
-            except ValueError:
-                pass
-            print(w.replace('smsp__warp_issue_stalled_', 'stall_').replace('_per_warp_active.pct', ''), v, units[i])
+            print(w.replace('smsp__warp_issue_stalled_', 'stall_').replace('smsp__pcsamp_warps_issue_stalled_', 'samples_stall_').replace('_per_warp_active.pct', ''), v, units[i])
