@@ -871,7 +871,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
             CK(ctx->slow_list.ensure((size_t) nr * sizeof(u32)));
             CK(ctx->best_recs.ensure((size_t) nr * sizeof(BestRec)));
             CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 11 * sizeof(u32), ctx->stream));
-            const size_t fast_smem = (size_t) SC_THREADS * SC_STRIDE * sizeof(u32);
+            const size_t fast_smem = (size_t) SC_THREADS * SC_GSTRIDE * sizeof(u32);
             // buckets of k_score_finish: cap_b taxa + cap_b bytes per thread, odd word stride
             int bucket_stride = arena.cap_b + (arena.cap_b + 3) / 4;
             bucket_stride |= 1;
@@ -883,7 +883,17 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
                 CK(cudaFuncSetAttribute(k_score_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
                 fast_attr = true;
             }
-            const unsigned fast_grid = (unsigned) std::min<u64>(148ull * 2, ((u64) nr + SC_THREADS - 1) / SC_THREADS);
+            // persistent: every resident slot (the DP state is 100 B of shared memory per thread; registers set the limit)
+            static int fast_ctas = 0;
+            if (!fast_ctas) {
+                int per_sm = 0, sms = 148;
+                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast, SC_THREADS, fast_smem));
+                CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
+                static const int env_ctas = getenv("MB_SCORE_CTAS_PER_SM") ? atoi(getenv("MB_SCORE_CTAS_PER_SM")) : 0;      // tuning knob
+                if (env_ctas > 0 && env_ctas < per_sm) per_sm = env_ctas;
+                fast_ctas = std::max(1, per_sm) * sms;
+            }
+            const unsigned fast_grid = (unsigned) std::min<u64>((u64) fast_ctas, ((u64) nr + SC_THREADS - 1) / SC_THREADS);
             KL(KID_SCORE_FAST, k_score_fast<<<fast_grid, SC_THREADS, fast_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv,
                 ctx->best_recs.as<BestRec>(), &ctx->dcnt()->score_ticket, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count,

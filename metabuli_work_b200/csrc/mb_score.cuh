@@ -481,11 +481,12 @@ constexpr int SF_P = 16;     // paths per species: the size up to which std::sor
 constexpr int SC_G = 4;                          // matches per (species, frame, position) group
 constexpr int SC_NP = 40;                        // paths per read
 constexpr int SC_NS = 16;                        // species with paths per read
-constexpr int SC_W_GROUP = 0;                    // 2 groups x SC_G entries x 3 words
-constexpr int SC_W_PATH = 2 * SC_G * 3;          // SC_NP paths x 3 words
-constexpr int SC_W_SPEC = SC_W_PATH + SC_NP * 3; // SC_NS species x 2 words: id | paths << 24, then begin | end << 16 (later the score)
-constexpr int SC_WORDS = SC_W_SPEC + SC_NS * 2;
-constexpr int SC_STRIDE = SC_WORDS + 1;          // odd: lanes touching the same word hit different banks
+constexpr int SC_GWORDS = 2 * SC_G * 3;          // DP state `w`: 2 groups x SC_G entries x 3 words (shared memory on the device)
+constexpr int SC_GSTRIDE = SC_GWORDS + 1;        // odd: lanes touching the same word hit different banks
+constexpr int SC_W_SPEC = SC_NP * 3;             // path list `wp`: SC_NP paths x 3 words, then SC_NS species x 2 words:
+constexpr int SC_PWORDS = SC_W_SPEC + SC_NS * 2; // id | paths << 24, then begin | end << 16 (later the score).  Touched a few
+                                                 // times per read only, so it lives in per-thread local memory (L1) and the
+                                                 // kernel keeps 25 words of shared memory per thread instead of 177.
 
 // half-unit score and Hamming sum of the lowest `cnt` 2-bit fields of r (codon score 3 / 1.5 / 1 / 0.5 for h = 0..3)
 MB_HD void fields_score(u32 r, int cnt, int &score2, int &ham) {
@@ -529,9 +530,9 @@ MB_HD float u2f_hd(u32 u) {
 #endif
 }
 // one group entry that is a finished path -> packed path list
-MB_HD void emit_path(u32 *w, int &n_paths, int &overflow, u32 e0, u32 e1, u32 end_pos, u32 em) {
+MB_HD void emit_path(u32 *wp, int &n_paths, int &overflow, u32 e0, u32 e1, u32 end_pos, u32 em) {
     if (n_paths < SC_NP) {
-        u32 *pp = w + SC_W_PATH + n_paths * 3;
+        u32 *pp = wp + n_paths * 3;
         pp[0] = (e0 & 0xFFFFu) | (end_pos << 16);
         pp[1] = (e1 & 0xFFFu) | (((e1 >> 12) & 0xFFFu) << 16);
         pp[2] = (e0 >> 16) | (em << 16);
@@ -541,7 +542,7 @@ MB_HD void emit_path(u32 *w, int &n_paths, int &overflow, u32 e0, u32 e1, u32 en
 
 // Returns false when a bound of the compact state is exceeded (the caller then uses the general form).
 // (reason codes: 1 position group, 2 paths per read, 3 species per read, 4 paths per species, 5 field width, 6 read size)
-MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, u32 *w,
+MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, u32 *w, u32 *wp,
                                BestSpecies &out) {
     out.tax = 0; out.score = 0.f; out.lca = false; out.rb = 0; out.re = 0;
     if (n > 60000 || query_length > 60000) return 6;
@@ -559,6 +560,7 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
     const u64 *mw = reinterpret_cast<const u64 *>(m);
     u64 nx0 = mw[0], nx1 = mw[1], nx2 = mw[2];
     for (int i = 0; i <= n; ++i) {
+        if (overflow) break;                     // nothing below may run with a group count past SC_G
         const bool at_end = i == n;
         const u64 w0 = nx0, w1 = nx1, w2 = nx2;
         if (i + 1 < n) { nx0 = mw[(i + 1) * 3]; nx1 = mw[(i + 1) * 3 + 1]; nx2 = mw[(i + 1) * 3 + 2]; }
@@ -574,17 +576,17 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
         const bool rotate = !new_frame && started && pos != pos_b;
         if (have_cur && (rotate || (new_frame && i > 0))) {
             // paths of the previous group that were not extended (Taxonomer.cpp:631-640)
-            const u32 *ga = w + SC_W_GROUP + cur * SC_G * 3;
+            const u32 *ga = w + cur * SC_G * 3;
             for (int c = 0; c < na; ++c) {
                 const u32 e1 = ga[c * 3 + 1], e2 = ga[c * 3 + 2];
-                if (!(e2 >> 24) && (int) (e1 >> 24) >= min_depth) emit_path(w, n_paths, overflow, ga[c * 3], e1, pos_a + 23u, (u32) (ia0 + c));
+                if (!(e2 >> 24) && (int) (e1 >> 24) >= min_depth) emit_path(wp, n_paths, overflow, ga[c * 3], e1, pos_a + 23u, (u32) (ia0 + c));
             }
             if (new_frame) {
                 // the last group of the (species, frame) group: every path that is long enough (Taxonomer.cpp:641-646)
-                const u32 *gb = w + SC_W_GROUP + (cur ^ 1) * SC_G * 3;
+                const u32 *gb = w + (cur ^ 1) * SC_G * 3;
                 for (int c = 0; c < nb; ++c) {
                     const u32 e1 = gb[c * 3 + 1];
-                    if ((int) (e1 >> 24) >= min_depth) emit_path(w, n_paths, overflow, gb[c * 3], e1, pos_b + 23u, (u32) (ib0 + c));
+                    if ((int) (e1 >> 24) >= min_depth) emit_path(wp, n_paths, overflow, gb[c * 3], e1, pos_b + 23u, (u32) (ib0 + c));
                 }
             }
         }
@@ -594,7 +596,7 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
                 if (n_spp >= SC_NS || (u32) species >= (1u << 24)) overflow = 3;
                 else if (n_paths - sp_paths0 > SF_P) overflow = 4;
                 else {
-                    u32 *sw = w + SC_W_SPEC + n_spp * 2;
+                    u32 *sw = wp + SC_W_SPEC + n_spp * 2;
                     sw[0] = (u32) species | ((u32) (n_paths - sp_paths0) << 24);
                     sw[1] = (u32) sp_begin | ((u32) i << 16);
                 }
@@ -630,7 +632,7 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
                 int inc2, hinc;
                 fields_score(reh, shift, inc2, hinc);     // calScoreIncrement / calHammingDistIncrement (Taxonomer.cpp:650-669)
                 const u32 keep = (1u << (24 - 3 * shift)) - 1u;
-                u32 *ga = w + SC_W_GROUP + cur * SC_G * 3;
+                u32 *ga = w + cur * SC_G * 3;
                 int best = -1, best_score2 = 0;
                 for (int c = 0; c < na; ++c) {
                     const u32 e2 = ga[c * 3 + 2];
@@ -656,7 +658,7 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
         if (nb >= SC_G) overflow = 1;
         else if (t_score2 >= 4096 || t_ham >= 4096 || t_depth >= 256) overflow = 5;
         else {
-            u32 *gb = w + SC_W_GROUP + (cur ^ 1) * SC_G * 3 + nb * 3;
+            u32 *gb = w + (cur ^ 1) * SC_G * 3 + nb * 3;
             gb[0] = t_start | (t_sm << 16);
             gb[1] = (u32) t_score2 | ((u32) t_ham << 12) | ((u32) t_depth << 24);
             gb[2] = dna;
@@ -668,12 +670,12 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
     // ---- phase 2: per species with paths, combineMatchPaths (Taxonomer.cpp:410-485) ----
     int meaningful = 0;
     float best_sp = 0.f;
-    u32 *comb = w + SC_W_GROUP;                  // kept paths (start | end << 16): the DP groups are dead now
+    u32 *comb = w;                 // kept paths (start | end << 16): the DP groups are dead now
     int p0 = 0;
     for (int s = 0; s < n_spp; ++s) {
-        u32 *sw = w + SC_W_SPEC + s * 2;
+        u32 *sw = wp + SC_W_SPEC + s * 2;
         const int pc = (int) (sw[0] >> 24);
-        u32 *pp = w + SC_W_PATH + p0 * 3;
+        u32 *pp = wp + p0 * 3;
         p0 += pc;
         // std::sort on <= 16 elements is libstdc++'s __insertion_sort (bits/stl_algo.h)
         for (int k = 1; k < pc; ++k) {
@@ -733,7 +735,7 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
     int32_t single = 0;
     const float cut = best_sp * cfg.tie_ratio;
     for (int s = 0; s < n_spp; ++s) {
-        const u32 *sw = w + SC_W_SPEC + s * 2;
+        const u32 *sw = wp + SC_W_SPEC + s * 2;
         if (sw[1] == 0xFFFFFFFFu) continue;
         const float sc = u2f_hd(sw[1]);
         if (sc >= cut) {
@@ -758,12 +760,12 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
 }
 
 // Compact streaming scorer.  Returns -(reason) when a bound of the state was exceeded (the caller then uses score_read).
-MB_HD int score_read_compact(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, u32 *w,
+MB_HD int score_read_compact(const mb_match *m, int n, int query_length, const ScoreCfg &cfg, const TaxView &tax, u32 *w, u32 *wp,
                              ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
     result_init(r, query_length, n);
     if (n <= 0) return 0;
     BestSpecies best;
-    const int why = best_species_compact(m, n, query_length, cfg, tax, w, best);
+    const int why = best_species_compact(m, n, query_length, cfg, tax, w, wp, best);
     if (why) return -why;
     return finish_read(m, best, query_length, cfg, tax, scr, r, error_flag);
 }
@@ -900,7 +902,8 @@ __global__ void __launch_bounds__(SC_THREADS)
 k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
              const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, BestRec *__restrict__ best_out,
              u32 *ticket, u32 *__restrict__ list, u32 *list_count, u32 *overflow_reasons) {
-    extern __shared__ u32 sc_state[];            // SC_THREADS slices of SC_STRIDE words
+    extern __shared__ u32 sc_state[];            // SC_THREADS slices of SC_GSTRIDE words
+    u32 wp[SC_PWORDS];                           // path / species lists of this thread's read (local memory)
     const u32 lane = threadIdx.x & 31;
     while (true) {
         u32 r0 = 0;
@@ -916,7 +919,7 @@ k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, 
             rec.tax = 0; rec.score = 0.f; rec.range = 0; rec.state = 1;
             if (e > b) {
                 BestSpecies best;
-                const int why = (e - b) < 0x7FFFFFFFull ? best_species_compact(m + b, (int) (e - b), ql, cfg, tax, sc_state + threadIdx.x * SC_STRIDE, best) : 6;
+                const int why = (e - b) < 0x7FFFFFFFull ? best_species_compact(m + b, (int) (e - b), ql, cfg, tax, sc_state + threadIdx.x * SC_GSTRIDE, wp, best) : 6;
                 if (why) {
                     rec.state = 0;
                     list[atomicAdd(list_count, 1u)] = r;

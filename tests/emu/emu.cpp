@@ -135,8 +135,8 @@ int64_t emu_score(const mb_match *m, size_t n, const uint32_t *lens, uint32_t n_
         int n_tc = -1;
         if (g_fast) {
             // the streaming form k_score_fast runs; reads it cannot hold fall back to the general form, as on the device
-            u32 state[SC_STRIDE];
-            n_tc = score_read_compact(m + sb[r], (int) (se[r] - sb[r]), ql, cfg, tv, state, scr, res[r], &err);
+            u32 state[SC_GSTRIDE], paths[SC_PWORDS];
+            n_tc = score_read_compact(m + sb[r], (int) (se[r] - sb[r]), ql, cfg, tv, state, paths, scr, res[r], &err);
             if (n_tc < 0) ++g_fallbacks;
         }
         if (n_tc < 0) n_tc = score_read(m + sb[r], 0, (int) (se[r] - sb[r]), ql, cfg, tv, scr, res[r], &err);
