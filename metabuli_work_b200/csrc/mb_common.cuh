@@ -325,6 +325,7 @@ MB_HD int32_t tax_lca_existing(const TaxView &t, int32_t a, int32_t b) {
 }
 // NcbiTaxonomy::LCA(TaxID, TaxID) (NcbiTaxonomy.cpp:303-310)
 MB_HD int32_t tax_lca(const TaxView &t, int32_t a, int32_t b) {
+    if (a == b) return a;                      // every branch below returns a (== b) in this case; saves the table loads
     if (!tax_exists(t, a)) return b;
     if (!tax_exists(t, b)) return a;
     return tax_lca_existing(t, a, b);

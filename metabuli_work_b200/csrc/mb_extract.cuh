@@ -86,9 +86,9 @@ __global__ void __launch_bounds__(256) k_validate_reads(const u64 *__restrict__ 
 
 constexpr size_t extract_smem_bytes() { return (size_t) EX_TILE * 2 * sizeof(mb_kmer); }   // every window, both strands
 
-// ONE pass: a CTA extracts the k-mers of its 2048 window starts into a shared-memory staging buffer (slots handed out
-// by warp-aggregated atomics on a shared counter), reserves its output range with one global atomic and copies the
-// buffer out with coalesced 16-byte stores.  The query buffer is unordered by contract (the reference fills it from
+// ONE pass: a CTA extracts the k-mers of its 2048 window starts into a shared-memory staging buffer (one region per
+// warp, slots = running count + ballot rank), every warp reserves its output range with one global atomic and copies
+// its region out with coalesced 16-byte stores.  The query buffer is unordered by contract (the reference fills it from
 // many threads, KmerExtractor.cpp:83-386, and sorts afterwards), so no prefix sum over tiles is needed.
 //
 // FMT2 (current metamer format): the three codon phases of a thread's 32 staged bases are translated ONCE into packed
@@ -112,8 +112,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
     __shared__ u8 s_nuc[256];
     __shared__ u8 s_codonF[64];
     __shared__ u8 s_codonR[64];
-    __shared__ u32 s_fill;
-    __shared__ unsigned long long s_base;
+    __shared__ u32 s_wfill[EX_THREADS / 32];
     __shared__ Route s_route;
     __shared__ u32 s_dcnt[MB_MAX_RANKS], s_dloc[MB_MAX_RANKS + 1];
     __shared__ u32 s_wcnt[EX_THREADS / 32][MB_MAX_RANKS];
@@ -129,7 +128,6 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
 
     s_nuc[tid] = tables->nuc[tid];
     if (tid < 64) { s_codonF[tid] = tables->codonF[tid]; s_codonR[tid] = tables->codonR[tid]; }
-    if (tid == 0) s_fill = 0;
     __syncthreads();
 
     // stage 8 bases per thread (+ 4 halo groups by the first threads)
@@ -181,12 +179,19 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
     u32 m = 0;
     u64 moff = 0;
     u32 mlen = 0;
+    u64 next_off = ~0ull;                        // offset of mate m + 1: the mate changes when a window start reaches it
     const bool any = gfirst < a.n_bases && a.n_mates > 0;
     if (any) {
         m = mate_of(a.offsets, tile_mate[tile], tile_mate[tile + 1], gfirst);
         moff = __ldg(a.offsets + m);
         mlen = __ldg(a.lens + m);
+        if (m + 1 < a.n_mates) next_off = __ldg(a.offsets + m + 1);
     }
+    // staging: every warp owns a fixed region of the buffer (as many records as its lanes can emit), so a slot is the
+    // warp's running count plus the lane's rank in the ballot: no shared-memory atomics
+    constexpr u32 RW = (ROUTED ? EX_PER_THREAD / 2 : EX_PER_THREAD) * 2 * 32;
+    const u32 wbase = (tid >> 5) * RW;
+    u32 wfill = 0;
     const bool paired = a.seq_mode == 2;
     bool have_meta = false, usable = false;
     u32 pos_offset = 0;
@@ -201,10 +206,11 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
         if (any) {
             const u64 g = gfirst + i;
             // advance to the mate that owns base g (mates are back to back, zero-length ones share an offset)
-            while (m + 1 < a.n_mates && __ldg(a.offsets + m + 1) <= g) {
+            while (g >= next_off) {
                 ++m;
-                moff = __ldg(a.offsets + m);
+                moff = next_off;
                 mlen = __ldg(a.lens + m);
+                next_off = m + 1 < a.n_mates ? __ldg(a.offsets + m + 1) : ~0ull;
                 have_meta = false;
             }
             if (g >= moff && g < moff + mlen) {
@@ -249,22 +255,23 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
             const u64 v = strand ? vr : vf;
             const bool emit = ok && (!FMT2 || !a.syncmer || is_syncmer(v, a.smer_len));
             const u32 mask = __ballot_sync(0xFFFFFFFFu, emit);
-            if (mask) {
-                u32 base = 0;
-                if (lane == (u32) (__ffs(mask) - 1)) base = atomicAdd(&s_fill, (u32) __popc(mask));
-                base = __shfl_sync(0xFFFFFFFFu, base, __ffs(mask) - 1);
-                if (emit) s_out[base + __popc(mask & ((1u << lane) - 1u))] = make_ulonglong2(v, make_qinfo(seqId, x + pos_offset, strand ? fr_rev : xm));
-            }
+            if (emit) s_out[wbase + wfill + __popc(mask & ((1u << lane) - 1u))] = make_ulonglong2(v, make_qinfo(seqId, x + pos_offset, strand ? fr_rev : xm));
+            wfill += __popc(mask);
         }
     }
     if (ROUTED) {
         // ---- group the <= EX_TILE staged records by owner, reserve, write runs to the owners ----
+        if (lane == 0) s_wfill[tid >> 5] = wfill;
+        wfill = 0;
         __syncthreads();
-        const u32 total = s_fill;
         const u32 nr = s_route.n;
-        constexpr int PER = EX_TILE / EX_THREADS;
+        constexpr int PER = EX_TILE / EX_THREADS;          // == number of warps: pass j handles warp j's region, RW == EX_THREADS
         constexpr int NW = EX_THREADS / 32;
+        static_assert(PER == NW && RW == EX_THREADS || !ROUTED, "routed grouping walks one staging region per pass");
         const u32 warp = tid >> 5;
+        u32 total = 0;
+#pragma unroll
+        for (int j = 0; j < NW; ++j) total += s_wfill[j];
         u32 pos[PER];
         // rank of every record among the records of its warp with the same owner: one shared-memory atomic per record
         // on a per-warp counter (cost independent of the number of ranks)
@@ -272,7 +279,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
         for (int j = 0; j < PER; ++j) {
             const u32 k = tid + j * EX_THREADS;
             pos[j] = 0;
-            if (k < total) {
+            if (tid < s_wfill[j]) {
                 const u32 d = route_owner(s_route, s_out[k].x);
                 pos[j] = (d << 16) | atomicAdd(&s_wcnt[warp][d], 1u);
             }
@@ -297,7 +304,7 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
 #pragma unroll
         for (int j = 0; j < PER; ++j) {
             const u32 k = tid + j * EX_THREADS;
-            if (k < total) { const u32 d = pos[j] >> 16; s_ord[s_dloc[d] + s_wcnt[warp][d] + (pos[j] & 0xFFFFu)] = s_out[k]; }
+            if (tid < s_wfill[j]) { const u32 d = pos[j] >> 16; s_ord[s_dloc[d] + s_wcnt[warp][d] + (pos[j] & 0xFFFFu)] = s_out[k]; }
         }
         __syncthreads();
         for (u32 k = tid; k < total; k += EX_THREADS) {
@@ -307,22 +314,20 @@ k_extract(ExtractArgs a, const u32 *__restrict__ tile_mate, const Tables *__rest
             if (idx < s_route.kmer_cap[d]) reinterpret_cast<ulonglong2 *>(s_route.kmers[d])[idx] = s_ord[k];
         }
         __syncthreads();
-        if (tid == 0) s_fill = 0;
         if (tid < MB_MAX_RANKS * (EX_THREADS / 32)) (&s_wcnt[0][0])[tid] = 0;
         __syncthreads();
     }
     }   // half
     if (!ROUTED) {
-    __syncthreads();
-    const u32 total = s_fill;
-    if (tid == 0 && total) s_base = atomicAdd(out_count, (unsigned long long) total);
-    __syncthreads();
-    if (total) {
-        const u64 base = s_base;
+        // every warp reserves the output range of its own region (one global atomic per warp) and copies it out with
+        // coalesced 16-byte stores; no block barrier is needed
+        __syncwarp();
+        unsigned long long base = 0;
+        if (lane == 0 && wfill) base = atomicAdd(out_count, (unsigned long long) wfill);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
         ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(out);
-        for (u32 k = tid; k < total; k += EX_THREADS)
-            if (base + k < out_cap) dst[base + k] = s_out[k];
-    }
+        for (u32 k = lane; k < wfill; k += 32)
+            if (base + k < out_cap) dst[base + k] = s_out[wbase + k];
     }
 }
 

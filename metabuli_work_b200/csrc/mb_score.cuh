@@ -377,14 +377,28 @@ MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_leng
     const int max_q = (query_length + 3) / cfg.dna_shift;
     if (max_q + 1 > scr.cap_b) { *error_flag = 2; return 0; }
     for (int k = 0; k <= max_q; ++k) { scr.bucket_ham[k] = 255; scr.bucket_tax[k] = 0; }
-    for (int i = best.rb; i < best.re; ++i) {
-        // dna_shift is 3 (plain) or 9 (syncmers, s = 5) in practice: constant divisions instead of the general sequence
-        const u32 pos_i = qi_pos(m[i].qinfo);
-        const int qd = (int) (cfg.dna_shift == 3 ? pos_i / 3u : cfg.dna_shift == 9 ? pos_i / 9u : pos_i / (u32) cfg.dna_shift);
-        if (qd > max_q) continue;
-        const u8 h = m[i].hamming;
-        if (scr.bucket_ham[qd] == 255 || h < scr.bucket_ham[qd]) { scr.bucket_tax[qd] = m[i].targetId; scr.bucket_ham[qd] = h; }
-        else if (h == scr.bucket_ham[qd]) scr.bucket_tax[qd] = tax_lca(tax, scr.bucket_tax[qd], m[i].targetId);
+    {
+        // the record of the next match is requested while the current one is bucketed (one thread per read: every load
+        // is a round trip to L1/L2 that nothing else hides)
+        const u64 *mw = reinterpret_cast<const u64 *>(m);
+        u64 n0 = 0, n1 = 0, n2 = 0;
+        if (best.rb < best.re) { n0 = mw[best.rb * 3]; n1 = mw[best.rb * 3 + 1]; n2 = mw[best.rb * 3 + 2]; }
+        for (int i = best.rb; i < best.re; ++i) {
+            const u64 w0 = n0, w1 = n1, w2 = n2;
+            if (i + 1 < best.re) { n0 = mw[(i + 1) * 3]; n1 = mw[(i + 1) * 3 + 1]; n2 = mw[(i + 1) * 3 + 2]; }
+            // dna_shift is 3 (plain) or 9 (syncmers, s = 5) in practice: constant divisions instead of the general sequence
+            const u32 pos_i = qi_pos(w0);
+            const int qd = (int) (cfg.dna_shift == 3 ? pos_i / 3u : cfg.dna_shift == 9 ? pos_i / 9u : pos_i / (u32) cfg.dna_shift);
+            if (qd > max_q) continue;
+            const u8 h = (u8) (w2 >> 48);
+            const int32_t target = (int32_t) (u32) w1;
+            const u8 bh = scr.bucket_ham[qd];
+            if (bh == 255 || h < bh) { scr.bucket_tax[qd] = target; scr.bucket_ham[qd] = h; }
+            else if (h == bh) {
+                const int32_t cur_tax = scr.bucket_tax[qd];
+                if (cur_tax != target) scr.bucket_tax[qd] = tax_lca(tax, cur_tax, target);
+            }
+        }
     }
     int n_tc = 0;                                   // taxCnt as a sorted array (std::map order)
     for (int k = 0; k <= max_q; ++k) {
