@@ -66,6 +66,20 @@ struct MatchHomeKey {       // multi-GPU: home rank of a match = (sequenceID-1) 
     __device__ __forceinline__ u32 digit(const mb_match &m, int) const { return (qi_seq(m.qinfo) - 1u) / reads_per_rank; }
 };
 
+// ---- record moves ------------------------------------------------------------------------------------
+// 16-byte records travel as one 128-bit access (their arrays are 16-byte aligned: cudaMalloc bases, region sizes in
+// whole records); other sizes as 64-bit words.
+template <typename Rec>
+__device__ __forceinline__ void rec_load(Rec &dst, const Rec *src) {
+    if constexpr (sizeof(Rec) == 16) *reinterpret_cast<ulonglong2 *>(&dst) = *reinterpret_cast<const ulonglong2 *>(src);
+    else dst = *src;
+}
+template <typename Rec>
+__device__ __forceinline__ void rec_store(Rec *dst, const Rec &src) {
+    if constexpr (sizeof(Rec) == 16) *reinterpret_cast<ulonglong2 *>(dst) = *reinterpret_cast<const ulonglong2 *>(&src);
+    else *dst = src;
+}
+
 // ---- histogram of every pass in one read -----------------------------------------------------------
 template <typename Rec, typename Key, bool SEG>
 __global__ void __launch_bounds__(RS_THREADS)
@@ -116,6 +130,7 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
     u32 *s_whist = reinterpret_cast<u32 *>(s_raw + sizeof(Rec) * TILE);            // [RS_WARPS][256]
     u32 *s_binstart = s_whist + RS_WARPS * RS_BINS;                                // [256]
     u64 *s_gbase = reinterpret_cast<u64 *>(s_binstart + RS_BINS);                  // [256]
+    u8 *s_dig = reinterpret_cast<u8 *>(s_gbase + RS_BINS);                         // [TILE] digit of every staged record
     __shared__ u32 s_tile;
     __shared__ u32 s_scan[RS_WARPS];
 
@@ -146,13 +161,13 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const u64 idx = wbase + (u64) j * 32 + lane;
-            if (idx < n) rec[j] = *seg_ptr(seg, in, idx);
+            if (idx < n) rec_load(rec[j], seg_ptr(seg, in, idx));
         }
     } else {
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             const u64 idx = wbase + (u64) j * 32 + lane;
-            if (idx < n) rec[j] = in_eff[idx];
+            if (idx < n) rec_load(rec[j], in_eff + idx);
         }
     }
 #pragma unroll
@@ -248,24 +263,43 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
     }
     __syncthreads();
 
-    // stage the tile in digit order
+    // stage the tile in digit order; the digit of every staged record is kept beside it
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         const u32 d = dig[j];
-        if (d != 0xFFFFFFFFu) s_rec[s_binstart[d] + s_whist[warp * RS_BINS + d] + rank[j]] = rec[j];
+        if (d != 0xFFFFFFFFu) {
+            const u32 pos = s_binstart[d] + s_whist[warp * RS_BINS + d] + rank[j];
+            rec_store(s_rec + pos, rec[j]);
+            s_dig[pos] = (u8) d;
+        }
     }
     __syncthreads();
     const u32 valid = (u32) (n - tile_base < (u64) TILE ? n - tile_base : (u64) TILE);
-    for (u32 i = tid; i < valid; i += RS_THREADS) {
-        const Rec r = s_rec[i];
-        if (dbg == 2) out[tile_base + i] = r; else
-        out[s_gbase[key.digit(r, pass)] + i] = r;
+    if constexpr (sizeof(Rec) == 16) {
+        // one 128-bit store per record: a warp writes 512 contiguous bytes of a run
+        for (u32 i = tid; i < valid; i += RS_THREADS) {
+            Rec r;
+            rec_load(r, s_rec + i);
+            rec_store(dbg == 2 ? out + tile_base + i : out + s_gbase[s_dig[i]] + i, r);
+        }
+    } else {
+        // other record sizes leave word by word: consecutive lanes write consecutive 8-byte words of a run (a record-wise
+        // store of a 24-byte struct is three strided stores that each touch every sector of the span)
+        constexpr u32 W = sizeof(Rec) / 8;
+        static_assert(sizeof(Rec) % 8 == 0, "records are whole 64-bit words");
+        const u64 *s_w = reinterpret_cast<const u64 *>(s_rec);
+        u64 *out_w = reinterpret_cast<u64 *>(out);
+        for (u32 wi = tid; wi < valid * W; wi += RS_THREADS) {
+            const u32 r = wi / W, c = wi - r * W;
+            const u64 dst = dbg == 2 ? tile_base + r : s_gbase[s_dig[r]] + r;
+            out_w[dst * W + c] = s_w[wi];
+        }
     }
 }
 
 template <typename Rec, int ITEMS>
 constexpr size_t radix_pass_smem() {
-    return sizeof(Rec) * RS_THREADS * ITEMS + sizeof(u32) * (RS_WARPS * RS_BINS + RS_BINS) + sizeof(u64) * RS_BINS;
+    return sizeof(Rec) * RS_THREADS * ITEMS + sizeof(u32) * (RS_WARPS * RS_BINS + RS_BINS) + sizeof(u64) * RS_BINS + RS_THREADS * ITEMS;
 }
 
 } // namespace mb
