@@ -61,6 +61,8 @@ struct Counters {                 // device-side scalars, one allocation
     u32 match_ticket;
     u32 seg_ticket;
     u32 seg_too_long;
+    u32 seg_long_count;
+    u32 seg_long_ticket;
     u32 slow_count;
     u32 slow_ticket;
     u32 finish_ticket;
@@ -70,12 +72,12 @@ struct Counters {                 // device-side scalars, one allocation
 
 // kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
-       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SCORE_FAST, KID_SCORE_FINISH, KID_SCORE,
+       KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SEGSORT_LONG, KID_SCORE_FAST, KID_SCORE_FINISH, KID_SCORE,
        KID_COUNT };
 const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
-                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_score_fast", "k_score_finish", "k_score"};
+                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_sort_segments_long", "k_score_fast", "k_score_finish", "k_score"};
 struct KSample { int kid; cudaEvent_t a, b; };
 
 } // namespace
@@ -91,6 +93,7 @@ struct mb_ctx {
     u32 n_blocks = 0;
     // taxonomy
     DevBuf parent, depth, species_of, species_rank_of;
+    DevBuf seg_long;                  // reads whose segment goes to k_sort_segments_long
     int32_t max_taxid = -1, node0 = 0, euk = 0;
     // batch
     DevBuf bases, offsets, lens, stage_info;
@@ -98,6 +101,8 @@ struct mb_ctx {
     DevBuf pf_bases, pf_offsets, pf_lens, pf_info;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t pf_done = nullptr;
+    cudaStream_t side_stream = nullptr;          // the leftover scorer runs beside k_score_finish
+    cudaEvent_t side_fork = nullptr, side_join = nullptr;
     bool pf_pending = false;
     const void *pf_host[3] = {nullptr, nullptr, nullptr};
     u64 pf_n_bases = 0;
@@ -152,6 +157,12 @@ struct mb_ctx {
     } while (0)
 
 // one kernel launch: bracketed by profiling events, counted, checked
+#define KL_ON(kid, strm, ...)                                                                        \
+    do {                                                                                             \
+        { KTimer kt_(ctx, kid, strm); __VA_ARGS__; }                                                 \
+        ++ctx->launches;                                                                             \
+        CK(cudaGetLastError());                                                                      \
+    } while (0)
 #define KL(kid, ...)                                                                                 \
     do {                                                                                             \
         { KTimer kt_(ctx, kid); __VA_ARGS__; }                                                       \
@@ -163,7 +174,8 @@ struct mb_ctx {
 struct KTimer {
     mb_ctx *c;
     KSample *s = nullptr;
-    KTimer(mb_ctx *ctx, int kid) : c(ctx) {
+    cudaStream_t st;
+    KTimer(mb_ctx *ctx, int kid, cudaStream_t on = nullptr) : c(ctx), st(on ? on : ctx->stream) {
         if (!c->profile || kid < 0) return;
         if (c->n_samples == c->samples.size()) {
             KSample n;
@@ -173,9 +185,9 @@ struct KTimer {
         }
         s = &c->samples[c->n_samples++];
         s->kid = kid;
-        cudaEventRecord(s->a, c->stream);
+        cudaEventRecord(s->a, st);
     }
-    ~KTimer() { if (s) cudaEventRecord(s->b, c->stream); }
+    ~KTimer() { if (s) cudaEventRecord(s->b, st); }
 };
 
 static int fail(mb_ctx *ctx, int code, const char *msg) { ctx->err = msg; return code; }
@@ -354,6 +366,9 @@ void mb_destroy(mb_ctx *ctx) {
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     if (ctx->pf_done) cudaEventDestroy(ctx->pf_done);
+    if (ctx->side_stream) { cudaStreamSynchronize(ctx->side_stream); cudaStreamDestroy(ctx->side_stream); }
+    if (ctx->side_fork) cudaEventDestroy(ctx->side_fork);
+    if (ctx->side_join) cudaEventDestroy(ctx->side_join);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -783,22 +798,29 @@ int mb_sort_matches(mb_ctx *ctx) {
         if (rcs) return rcs;
         if (int rc = compute_segments(ctx)) return rc;
         CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
-        CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 2 * sizeof(u32), ctx->stream));
-        static bool attr_set = false;
-        if (!attr_set) {
-            CK(cudaFuncSetAttribute(k_sort_segments<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
-            CK(cudaFuncSetAttribute(k_sort_segments<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
-            attr_set = true;
+        CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 4 * sizeof(u32), ctx->stream));
+        CK(ctx->seg_long.ensure((size_t) ctx->n_reads * sizeof(u32)));
+        static int seg_ctas = 0;
+        if (!seg_ctas) {
+            CK(cudaFuncSetAttribute(k_sort_segments_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
+            int per_sm = 0, sms = 148;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sort_segments<true>, SS_THREADS, 0));
+            CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
+            seg_ctas = std::max(1, per_sm) * sms;
         }
-        const unsigned grid = (unsigned) std::min<u64>(148ull * 2, ((u64) ctx->n_reads + 63) / 64);
+        const unsigned grid = (unsigned) std::min<u64>((u64) seg_ctas, ((u64) ctx->n_reads + 63) / 64);
         if (sk.total_bits() <= 55)
-            KL(KID_SEGSORT, k_sort_segments<true><<<grid, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+            KL(KID_SEGSORT, k_sort_segments<true><<<grid, SS_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
-                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long));
+                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
         else
-            KL(KID_SEGSORT, k_sort_segments<false><<<grid, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+            KL(KID_SEGSORT, k_sort_segments<false><<<grid, SS_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
-                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long));
+                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
+        // segments of 513..1024 matches (rare with short reads): shared-memory network, one warp each
+        KL(KID_SEGSORT_LONG, k_sort_segments_long<<<148, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+            ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), sk,
+            &ctx->dcnt()->seg_long_ticket, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
         u32 too_long = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->seg_too_long, &too_long)) return rc;
         std::swap(ctx->matches_a.p, ctx->matches_b.p);
@@ -851,7 +873,10 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         u64 threads = std::min<u64>(resident, std::max<u64>(budget / arena.slice_bytes, SC_THREADS));
         threads = std::min<u64>(threads, (u64) nr + SC_THREADS);
         const unsigned grid = (unsigned) std::max<u64>(1, threads / SC_THREADS);
-        CK(ctx->arena.ensure((size_t) grid * SC_THREADS * arena.slice_bytes));
+        // short reads: the leftover scorer runs beside k_score_finish on a second stream, with its own slices behind the
+        // first `grid` blocks' worth
+        const unsigned slow_grid = std::min<unsigned>(grid, 148u * 8);
+        CK(ctx->arena.ensure((size_t) (grid + slow_grid) * SC_THREADS * arena.slice_bytes));
         arena.base = ctx->arena.as<unsigned char>();
         const size_t nm = std::max<size_t>(ctx->n_matches, 1);
         CK(ctx->sc_local.ensure(nm * sizeof(PathRec)));
@@ -862,6 +887,8 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         CK(ctx->sc_spscore.ensure(nm * sizeof(float)));
         arena.local = ctx->sc_local.as<PathRec>(); arena.paths = ctx->sc_paths.as<PathRec>(); arena.combined = ctx->sc_comb.as<PathRec>();
         arena.linked = ctx->sc_linked.as<u8>(); arena.sp_id = ctx->sc_spid.as<int32_t>(); arena.sp_score = ctx->sc_spscore.as<float>();
+        ScoreArena arena_slow = arena;
+        arena_slow.base = arena.base + (size_t) grid * SC_THREADS * arena.slice_bytes;
         const size_t tc_cap = std::max<size_t>(ctx->n_matches, 16);
         CK(ctx->tc_id.ensure(tc_cap * sizeof(int32_t)));
         CK(ctx->tc_cnt.ensure(tc_cap * sizeof(int32_t)));
@@ -898,14 +925,29 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv,
                 ctx->best_recs.as<BestRec>(), &ctx->dcnt()->score_ticket, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count,
                 ctx->dcnt()->fast_overflow));
+            if (!ctx->side_stream) {
+                CK(cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&ctx->side_fork, cudaEventDisableTiming));
+                CK(cudaEventCreateWithFlags(&ctx->side_join, cudaEventDisableTiming));
+            }
+            // the few reads the streaming scorer left over are long single-thread jobs; they can run on a side stream while
+            // k_score_finish finishes everybody else (disjoint reads, disjoint scratch, shared atomic counters)
+            // (measured on B200: beside k_score_finish the leftover kernel slows from 0.95 to 4.8 ms — its scratch is
+            // evicted from L1 by the streaming kernel — so the two are serialised by default; MB_SCORE_SIDE_STREAM=1 overlaps)
+            static const bool side = getenv("MB_SCORE_SIDE_STREAM") != nullptr;                // tuning knob
+            cudaStream_t slow_stream = side ? ctx->side_stream : ctx->stream;
+            CK(cudaEventRecord(ctx->side_fork, ctx->stream));
+            CK(cudaStreamWaitEvent(slow_stream, ctx->side_fork, 0));
+            KL_ON(KID_SCORE, slow_stream, k_score<<<slow_grid, SC_THREADS, 0, slow_stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena_slow,
+                ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
+                &ctx->dcnt()->slow_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
+            CK(cudaEventRecord(ctx->side_join, slow_stream));
             KL(KID_SCORE_FINISH, k_score_finish<<<grid, SC_THREADS, fin_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
                 ctx->best_recs.as<BestRec>(), bucket_stride, ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(),
                 ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->finish_ticket, &ctx->dcnt()->error_flag));
-            KL(KID_SCORE, k_score<<<std::min<unsigned>(grid, 148u * 8), SC_THREADS, 0, ctx->stream>>>(
-                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
-                ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
-                &ctx->dcnt()->slow_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
+            CK(cudaStreamWaitEvent(ctx->stream, ctx->side_join, 0));
         } else {
             KL(KID_SCORE, k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,

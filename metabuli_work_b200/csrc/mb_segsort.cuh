@@ -139,16 +139,15 @@ __device__ __forceinline__ void sort_segment_regs(const u64 *__restrict__ in64, 
 constexpr size_t segsort_smem_bytes() { return (size_t) SS_WARPS * SS_CAP * (sizeof(u64) + sizeof(u16)); }
 
 // One warp per read segment [seg_begin[r], seg_end[r]) of `in` (grouped by read); sorted records go to the same
-// range of `out`.  Segments longer than SS_CAP are copied unsorted and counted in *too_long (the host then takes
-// the full radix path).
+// range of `out`.  Segments of up to 512 records are sorted in registers here; those of 513..SS_CAP are appended to
+// `long_list` for k_sort_segments_long (keeping this kernel free of shared memory: 3 CTAs per SM instead of 2);
+// longer ones are copied unsorted and counted in *too_long (the host then takes the full radix path).
 template <bool PACKED>
-__global__ void __launch_bounds__(SS_THREADS)
+__global__ void __launch_bounds__(SS_THREADS, 3)
 k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, const u64 *__restrict__ seg_begin,
-                const u64 *__restrict__ seg_end, u32 n_reads, SegKey sk, u32 *ticket, u32 *too_long) {
-    extern __shared__ __align__(16) unsigned char ss_raw[];
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    u64 *keys = reinterpret_cast<u64 *>(ss_raw) + (size_t) warp * SS_CAP;
-    u16 *idx = reinterpret_cast<u16 *>(ss_raw + (size_t) SS_WARPS * SS_CAP * sizeof(u64)) + (size_t) warp * SS_CAP;
+                const u64 *__restrict__ seg_end, u32 n_reads, SegKey sk, u32 *ticket, u32 *too_long, u32 *__restrict__ long_list,
+                u32 *long_count) {
+    const u32 lane = threadIdx.x & 31;
     const u64 *in64 = reinterpret_cast<const u64 *>(in);
     u64 *out64 = reinterpret_cast<u64 *>(out);
     while (true) {
@@ -180,38 +179,62 @@ k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, con
             if (n <= 128) { sort_segment_regs<4, PACKED>(in64, out64, b, n, sk); continue; }
             if (n <= 256) { sort_segment_regs<8, PACKED>(in64, out64, b, n, sk); continue; }
             if (n <= 512) { sort_segment_regs<16, PACKED>(in64, out64, b, n, sk); continue; }
-            u32 n_pad = 1024;
-            for (u32 i = lane; i < n_pad; i += 32) {
-                u64 k = ~0ull;
-                if (i < n) {
-                    const u64 w0 = __ldg(in64 + (b + i) * 3), w1 = __ldg(in64 + (b + i) * 3 + 1), w2 = __ldg(in64 + (b + i) * 3 + 2);
-                    k = sk.key(w0, (u32) (w1 >> 32), (u32) w2, (u32) (w2 >> 48));
-                }
-                keys[i] = k;
-                idx[i] = (u16) i;
-            }
-            __syncwarp();
-            for (u32 kk = 2; kk <= n_pad; kk <<= 1) {
-                for (u32 j = kk >> 1; j > 0; j >>= 1) {
-                    for (u32 t = lane; t < n_pad / 2; t += 32) {
-                        const u32 i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-                        const u32 p = i | j;
-                        const u64 a = keys[i], c = keys[p];
-                        const u16 ia = idx[i], ic = idx[p];
-                        const bool up = (i & kk) == 0;
-                        const bool a_gt = a > c || (a == c && ia > ic);
-                        if (a_gt == up) { keys[i] = c; keys[p] = a; idx[i] = ic; idx[p] = ia; }
-                    }
-                    __syncwarp();
-                }
-            }
-            for (u32 i = lane; i < n; i += 32) {
-                const u64 s = b + idx[i];
-                const u64 w0 = __ldg(in64 + s * 3), w1 = __ldg(in64 + s * 3 + 1), w2 = __ldg(in64 + s * 3 + 2);
-                out64[(b + i) * 3] = w0; out64[(b + i) * 3 + 1] = w1; out64[(b + i) * 3 + 2] = w2;
-            }
-            __syncwarp();
+            if (lane == 0) long_list[atomicAdd(long_count, 1u)] = r;
         }
+    }
+}
+
+// The segments of 513..SS_CAP records k_sort_segments left over: one warp each, bitonic network in shared memory.
+__global__ void __launch_bounds__(SS_THREADS)
+k_sort_segments_long(const mb_match *__restrict__ in, mb_match *__restrict__ out, const u64 *__restrict__ seg_begin,
+                     const u64 *__restrict__ seg_end, SegKey sk, u32 *ticket, const u32 *__restrict__ long_list,
+                     const u32 *__restrict__ long_count) {
+    extern __shared__ __align__(16) unsigned char ss_raw[];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    u64 *keys = reinterpret_cast<u64 *>(ss_raw) + (size_t) warp * SS_CAP;
+    u16 *idx = reinterpret_cast<u16 *>(ss_raw + (size_t) SS_WARPS * SS_CAP * sizeof(u64)) + (size_t) warp * SS_CAP;
+    const u64 *in64 = reinterpret_cast<const u64 *>(in);
+    u64 *out64 = reinterpret_cast<u64 *>(out);
+    const u32 total = *long_count;
+    while (true) {
+        u32 t = 0;
+        if (lane == 0) t = atomicAdd(ticket, 1u);
+        t = __shfl_sync(0xFFFFFFFFu, t, 0);
+        if (t >= total) break;
+        const u32 r = long_list[t];
+        const u64 b = seg_begin[r];
+        const u32 n = (u32) (seg_end[r] - b);
+        const u32 n_pad = 1024;
+        for (u32 i = lane; i < n_pad; i += 32) {
+            u64 k = ~0ull;
+            if (i < n) {
+                const u64 w0 = __ldg(in64 + (b + i) * 3), w1 = __ldg(in64 + (b + i) * 3 + 1), w2 = __ldg(in64 + (b + i) * 3 + 2);
+                k = sk.key(w0, (u32) (w1 >> 32), (u32) w2, (u32) (w2 >> 48));
+            }
+            keys[i] = k;
+            idx[i] = (u16) i;
+        }
+        __syncwarp();
+        for (u32 kk = 2; kk <= n_pad; kk <<= 1) {
+            for (u32 j = kk >> 1; j > 0; j >>= 1) {
+                for (u32 tt = lane; tt < n_pad / 2; tt += 32) {
+                    const u32 i = ((tt & ~(j - 1)) << 1) | (tt & (j - 1));
+                    const u32 p = i | j;
+                    const u64 a = keys[i], c = keys[p];
+                    const u16 ia = idx[i], ic = idx[p];
+                    const bool up = (i & kk) == 0;
+                    const bool a_gt = a > c || (a == c && ia > ic);
+                    if (a_gt == up) { keys[i] = c; keys[p] = a; idx[i] = ic; idx[p] = ia; }
+                }
+                __syncwarp();
+            }
+        }
+        for (u32 i = lane; i < n; i += 32) {
+            const u64 s = b + idx[i];
+            const u64 w0 = __ldg(in64 + s * 3), w1 = __ldg(in64 + s * 3 + 1), w2 = __ldg(in64 + s * 3 + 2);
+            out64[(b + i) * 3] = w0; out64[(b + i) * 3 + 1] = w1; out64[(b + i) * 3 + 2] = w2;
+        }
+        __syncwarp();
     }
 }
 
