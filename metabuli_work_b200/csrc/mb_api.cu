@@ -689,10 +689,8 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
                                                                    ctx->n_kmers, ctx->sort_t, qstart, qend));
         static bool match_attr_set = false;
         if (!match_attr_set) {
-            CK(cudaFuncSetAttribute(k_match<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
-            CK(cudaFuncSetAttribute(k_match<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
-            CK(cudaFuncSetAttribute(k_match<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
-            CK(cudaFuncSetAttribute(k_match<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
+            CK(cudaFuncSetAttribute(k_match<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
             match_attr_set = true;
         }
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
@@ -712,19 +710,18 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
             static int match_ctas = 0;
             if (!match_ctas) {
                 int per_sm = 0, sms = 148;
-                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_match<false, false>, MT_THREADS, match_smem_bytes()));
+                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_match<false>, MT_THREADS, match_smem_bytes()));
                 CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
                 static const int env_ctas = getenv("MB_MATCH_CTAS_PER_SM") ? atoi(getenv("MB_MATCH_CTAS_PER_SM")) : 0;     // tuning knob
                 if (env_ctas > 0 && env_ctas < per_sm) per_sm = env_ctas;
                 match_ctas = std::max(1, per_sm) * sms;
             }
             const unsigned grid = (unsigned) std::min<u64>(nb, (u64) match_ctas);
-            static const int buckets = getenv("MB_MATCH_LOOKUP") ? atoi(getenv("MB_MATCH_LOOKUP")) : 0;   // tuning knob: 1 = bucket index
-#define MB_LAUNCH_MATCH(R, B, ROUTE) KL(KID_MATCH, (k_match<R, B><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>( \
+#define MB_LAUNCH_MATCH(R, ROUTE) KL(KID_MATCH, (k_match<R><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>( \
                 db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo, \
                 ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, ROUTE)))
-            if (!routed) { if (buckets) MB_LAUNCH_MATCH(false, true, nullptr); else MB_LAUNCH_MATCH(false, false, nullptr); }
-            else { if (buckets) MB_LAUNCH_MATCH(true, true, ctx->route_dev.as<Route>()); else MB_LAUNCH_MATCH(true, false, ctx->route_dev.as<Route>()); }
+            if (!routed) MB_LAUNCH_MATCH(false, nullptr);
+            else MB_LAUNCH_MATCH(true, ctx->route_dev.as<Route>());
 #undef MB_LAUNCH_MATCH
             if (routed) { if (int rc = publish_sent(ctx, 1)) return rc; }
             unsigned long long total = 0;

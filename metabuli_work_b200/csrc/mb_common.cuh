@@ -98,41 +98,12 @@ MB_HD u32 sort_t_packed(u64 value) {
 MB_HD u64 sort_t(const SortT &k, u64 value) { return k.mode ? (u64) sort_t_packed(value) : (value >> 24) >> k.shift; }
 MB_HD bool sort_t_lossy(const SortT &k) { return k.mode != 0 || k.shift != 0; }
 
-// ---- bucket index of a decoded DB block (k_match) ------------------------------------------------------
-// A decoded block holds n ascending values; their amino-acid parts span [aa0, aa_last].  Instead of a binary search over
-// the whole block, a query looks its group up through MB_NBUCKET equal-width buckets of that span: bstart[b] = first
-// index whose bucket is >= b (b = 0..MB_NBUCKET), so the group of `aa` lies in [bstart[b], bstart[b+1]) — a handful of
-// entries — and a short binary search finishes.
-constexpr int MB_NBUCKET_LOG = 10;
-constexpr int MB_NBUCKET = 1 << MB_NBUCKET_LOG;
-MB_HD int bucket_shift(u64 aa0, u64 aa_last) {          // smallest shift with (aa_last - aa0) >> shift < MB_NBUCKET
-    u64 range = aa_last - aa0;
-    int sh = 0;
-    while ((range >> sh) >= (u64) MB_NBUCKET) ++sh;
-    return sh;
-}
-MB_HD u32 bucket_of(u64 aa, u64 aa0, int shift) { return (u32) ((aa - aa0) >> shift); }
-// first index in vals[lo, hi) whose amino-acid part is >= aa
+// first index in vals[lo, hi) whose amino-acid part is >= aa (k_match: lookup of a query in a decoded DB block)
 MB_HD u32 lower_bound_aa_range(const u64 *vals, u32 lo, u32 hi, u64 aa) {
     while (lo < hi) {
         const u32 mid = (lo + hi) >> 1;
         if ((vals[mid] >> 24) < aa) lo = mid + 1; else hi = mid;
     }
-    return lo;
-}
-// candidate range [lo, lo + ncand) of a query with amino-acid part aa among vals[0, proc_end)
-template <typename BS>
-MB_HD u32 bucket_lookup(const u64 *vals, const BS *bstart, u32 proc_end, u64 aa0, u64 aa_last, int shift, u64 aa, u32 &ncand) {
-    ncand = 0;
-    if (aa < aa0 || aa > aa_last) return 0;
-    const u32 b = bucket_of(aa, aa0, shift);
-    u32 lo = bstart[b], hi = bstart[b + 1];
-    if (lo > proc_end) lo = proc_end;
-    if (hi > proc_end) hi = proc_end;
-    lo = lower_bound_aa_range(vals, lo, hi, aa);
-    u32 e = lo;
-    while (e < proc_end && (vals[e] >> 24) == aa) ++e;
-    ncand = e - lo;
     return lo;
 }
 

@@ -20,9 +20,8 @@
 //   2. decodes it cooperatively: each thread assembles the deltas ending in its 10 words, a block
 //      scan of (count, 64-bit delta sum) turns them into absolute values in shared memory,
 //   3. joins its query slice, one query per thread, warps running independently (32 queries per ticket,
-//      no block barrier): the AA part is looked up through a 1024-bucket index of the decoded block (built
-//      in the same sweep that finds the group boundaries), ONE Hamming evaluation per candidate through a
-//      two-codon table in shared memory,
+//      no block barrier): binary search of the AA part in the decoded block, ONE Hamming evaluation per candidate
+//      through a two-codon table in shared memory,
 //   4. compacts matches per warp: records are staged in a per-warp shared-memory buffer and flushed with
 //      one atomic reservation and coalesced 8-byte stores when the buffer fills.
 // The kernel is persistent (one CTA per resident slot, DB blocks handed out by an atomic ticket), so the
@@ -39,7 +38,7 @@
 namespace mb {
 
 constexpr int DB_W = 2048;                 // words per block
-constexpr int DB_E = 512;                  // overhang words
+constexpr int DB_E = 256;                  // overhang words
 constexpr int DB_C = DB_W + DB_E;          // words decoded per chunk
 constexpr int MT_THREADS = 256;
 constexpr int DB_R = DB_C / MT_THREADS;    // words per thread (10: odd word stride, conflict-free)
@@ -85,7 +84,6 @@ struct MatchSmem {
     u32 qnext;                             // next 32-query ticket of the current chunk
     u32 tick[2];                           // persistent loop: DB block tickets, fetched one block ahead
     u64 qadv;
-    u16 bstart[MB_NBUCKET + 2];            // bucket index of the decoded chunk (bucket_lookup, mb_common.cuh)
 };
 
 // the part of the shared memory that lives for the whole (persistent) kernel
@@ -439,7 +437,7 @@ __device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, 
     return lo;
 }
 
-template <bool ROUTED, bool BUCKETS>
+template <bool ROUTED>
 __global__ void __launch_bounds__(MT_THREADS, 4)
 k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
         const u64 *__restrict__ qend_of, MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *block_ticket,
@@ -488,16 +486,11 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
         while (true) {
             const u32 n = decode_chunk(db, c, s);
             if (n == 0) break;
-            if (tid == 0) { s.last_start = 0; s.own_end = (int) n; s.qnext = 0; s.bstart[0] = 0; }
-            // bucket index over the amino-acid span of the chunk (bucket_lookup)
-            const u64 aa0 = s.vals[0] >> 24, aal = s.vals[n - 1] >> 24;
-            int bsh = 64 - __clzll((long long) (aal - aa0)) - MB_NBUCKET_LOG;
-            bsh = bsh > 0 ? bsh : 0;
+            if (tid == 0) { s.last_start = 0; s.own_end = (int) n; s.qnext = 0; }
             __syncthreads();
             const u64 own_limit = tile_end > c.word ? tile_end - c.word : 0;   // local word offset of the block end
             {
-                // one sweep over the group boundaries: last group start, first group that starts in a later block, and
-                // bstart[] of every bucket that begins between two neighbours
+                // one sweep over the group boundaries: last group start and first group that starts in a later block
                 int lmax = 0, lmin = (int) n;
                 for (u32 j = tid + 1; j < n; j += MT_THREADS) {
                     const u64 a = s.vals[j] >> 24, pa = s.vals[j - 1] >> 24;
@@ -505,14 +498,8 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                         lmax = (int) j;
                         // first word of k-mer j is the word after the previous terminator
                         if ((u64) s.wend[j - 1] + 1 >= own_limit && (int) j < lmin) lmin = (int) j;
-                        if (BUCKETS) {
-                            const u32 bj = bucket_of(a, aa0, bsh), bp = bucket_of(pa, aa0, bsh);
-                            for (u32 bb = bp + 1; bb <= bj; ++bb) s.bstart[bb] = (u16) j;
-                        }
                     }
                 }
-                if (BUCKETS)
-                    for (u32 bb = bucket_of(aal, aa0, bsh) + 1 + tid; bb <= (u32) MB_NBUCKET; bb += MT_THREADS) s.bstart[bb] = (u16) n;
                 lmax = __reduce_max_sync(0xFFFFFFFFu, lmax);
                 lmin = __reduce_min_sync(0xFFFFFFFFu, lmin);
                 if (lane == 0) {
@@ -558,14 +545,13 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
                 u32 lo = 0, ncand = 0;
                 if (mine) {
-                    if (BUCKETS) lo = bucket_lookup(s.vals, s.bstart, proc_end, aa0, aal, bsh, qk.value >> 24, ncand);
-                    else {
-                        const u64 aa = qk.value >> 24;
-                        lo = lower_bound_aa_range(s.vals, 0, proc_end, aa);
-                        u32 hi = lo;
-                        while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
-                        ncand = hi - lo;
-                    }
+                    // binary search of the decoded block (measured on B200 against a 1024-bucket index and against a hash
+                    // directory of the groups built per block: both cost more to build than the search they save)
+                    const u64 aa = qk.value >> 24;
+                    lo = lower_bound_aa_range(s.vals, 0, proc_end, aa);
+                    u32 hi = lo;
+                    while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
+                    ncand = hi - lo;
                 }
                 // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
                 // whose exclusive prefix of ncand is the largest one <= p

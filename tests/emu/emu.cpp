@@ -161,27 +161,4 @@ void emu_sort_t(int mode, int shift, const uint64_t *values, size_t n, uint64_t 
     for (size_t i = 0; i < n; ++i) out[i] = sort_t(st, values[i]);
 }
 
-// k_match's lookup of a query in a decoded block: bucket index built as the kernel builds it (one entry per bucket
-// transition), then bucket_lookup.  vals: n ascending values; writes lo / ncand per query.
-void emu_bucket_lookup(const uint64_t *vals, uint32_t n, uint32_t proc_end, const uint64_t *queries, size_t nq, uint32_t *lo_out,
-                       uint32_t *ncand_out) {
-    std::vector<uint16_t> bstart(MB_NBUCKET + 2, 0xFFFF);
-    const u64 aa0 = vals[0] >> 24, aal = vals[n - 1] >> 24;
-    const int bsh = bucket_shift(aa0, aal);
-    bstart[0] = 0;
-    for (u32 j = 1; j < n; ++j) {
-        const u64 a = vals[j] >> 24, pa = vals[j - 1] >> 24;
-        if (a != pa) {
-            const u32 bj = bucket_of(a, aa0, bsh), bp = bucket_of(pa, aa0, bsh);
-            for (u32 bb = bp + 1; bb <= bj; ++bb) bstart[bb] = (uint16_t) j;
-        }
-    }
-    for (u32 bb = bucket_of(aal, aa0, bsh) + 1; bb <= (u32) MB_NBUCKET; ++bb) bstart[bb] = (uint16_t) n;
-    for (size_t i = 0; i < nq; ++i) {
-        u32 nc = 0;
-        lo_out[i] = bucket_lookup((const u64 *) vals, bstart.data(), proc_end, aa0, aal, bsh, (u64) (queries[i] >> 24), nc);
-        ncand_out[i] = nc;
-    }
-}
-
 } // extern "C"

@@ -106,7 +106,6 @@ def emu_lib():
     L.emu_set_fast.argtypes = [C.c_int]
     L.emu_is_syncmer.argtypes = [vp, sz, C.c_int, vp]
     L.emu_sort_t.argtypes = [C.c_int, C.c_int, vp, sz, vp]
-    L.emu_bucket_lookup.argtypes = [vp, u32, u32, vp, sz, vp, vp]
     L.emu_fast_fallbacks.restype = C.c_long
     return L
 

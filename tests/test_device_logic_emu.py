@@ -157,42 +157,6 @@ def test_sort_key_recoded(golden, emu, case):
     db.close()
 
 
-@pytest.mark.parametrize("case", ["plain_paired", "sync_paired", "legacy_paired"])
-def test_block_bucket_lookup(golden, emu, case):
-    """k_match's bucket index of a decoded block finds exactly the amino-acid group a binary search finds, for chunks
-    cut anywhere in the database, with proc_end cutting the chunk short, and for queries outside the chunk's span."""
-    meta = golden.cases[case]
-    db = orc.Db(golden.dbdir(case))
-    p = db.params(seq_mode=meta["seq_mode"])
-    _, s1, s2 = golden.reads(case)
-    k = orc.extract(p, orc.Batch(s1, s2))
-    dbv, _ = db.decode()
-    dbv = np.ascontiguousarray(dbv)
-    rng = np.random.default_rng(11)
-    qv = np.ascontiguousarray(k["value"][rng.integers(0, len(k), 4000)])
-    for trial in range(12):
-        n = int(rng.integers(1, 2560))
-        a = int(rng.integers(0, max(1, len(dbv) - n)))
-        vals = np.ascontiguousarray(dbv[a:a + n])
-        n = len(vals)
-        proc_end = n if trial % 3 == 0 else int(rng.integers(1, n + 1))
-        # queries: random k-mers of the reads, the chunk's own values (guaranteed hits) and its two ends
-        qs = np.concatenate([qv, vals[rng.integers(0, n, 500)], vals[:1], vals[-1:], vals[:1] - np.uint64(1 << 24), vals[-1:] + np.uint64(1 << 24)])
-        qs = np.ascontiguousarray(qs)
-        lo = np.zeros(len(qs), dtype=np.uint32)
-        nc = np.zeros(len(qs), dtype=np.uint32)
-        emu.emu_bucket_lookup(_ptr(vals), n, proc_end, _ptr(qs), len(qs), _ptr(lo), _ptr(nc))
-        aa = vals[:proc_end] >> np.uint64(24)
-        qa = qs >> np.uint64(24)
-        want_lo = np.searchsorted(aa, qa, side="left")
-        want_hi = np.searchsorted(aa, qa, side="right")
-        want_n = want_hi - want_lo
-        assert np.array_equal(nc, want_n.astype(np.uint32))
-        hit = want_n > 0
-        assert np.array_equal(lo[hit], want_lo[hit].astype(np.uint32))
-    db.close()
-
-
 @pytest.mark.parametrize("s", [3, 4, 5, 6, 7])
 def test_syncmer_predicate(emu, s):
     """is_syncmer (compile-time forms for s = 4, 5, 6 and the loop) against the definition of SyncmerScanner.h:36-102:
