@@ -92,7 +92,7 @@ struct mb_ctx {
     u64 n_words = 0, n_db_kmers = 0;
     u32 n_blocks = 0;
     // taxonomy
-    DevBuf parent, depth, species_of, species_rank_of;
+    DevBuf parent, depth, species_of, species_rank_of, tax_node;
     DevBuf seg_long;                  // reads whose segment goes to k_sort_segments_long
     int32_t max_taxid = -1, node0 = 0, euk = 0;
     // batch
@@ -502,6 +502,11 @@ int mb_load_taxonomy(mb_ctx *ctx, const int32_t *parent, const int32_t *species_
     CK(cudaMemcpyAsync(ctx->depth.p, depth.data(), n * 4, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->species_of.p, species_of, n * 4, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->species_rank_of.p, species_rank_of, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    // packed (parent, depth) records for tax_lca
+    std::vector<u64> node(n);
+    for (size_t t = 0; t < n; ++t) node[t] = (u64) (u32) parent[t] | ((u64) (u32) depth[t] << 32);
+    CK(ctx->tax_node.ensure(n * 8));
+    CK(cudaMemcpyAsync(ctx->tax_node.p, node.data(), n * 8, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->max_taxid = max_taxid;
     ctx->node0 = node0_taxid;
@@ -859,6 +864,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         tv.parent = ctx->parent.as<int32_t>(); tv.depth = ctx->depth.as<int32_t>(); tv.species_of = ctx->species_of.as<int32_t>();
         tv.species_rank_of = ctx->species_rank_of.as<int32_t>(); tv.max_taxid = ctx->max_taxid; tv.node0_taxid = ctx->node0;
         tv.eukaryota = ctx->euk;
+        tv.node = ctx->tax_node.as<u64>();
         ScoreArena arena;
         arena.cap_b = (int) ((ctx->max_query_len + 3) / (u32) cfg.dna_shift + 2);
         arena.cap_c = 4 * arena.cap_b + 64;

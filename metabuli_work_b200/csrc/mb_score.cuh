@@ -401,15 +401,31 @@ MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_leng
         }
     }
     int n_tc = 0;                                   // taxCnt as a sorted array (std::map order)
-    for (int k = 0; k <= max_q; ++k) {
-        if (scr.bucket_ham[k] == 255) continue;
-        const int32_t t = scr.bucket_tax[k];
-        int p = 0;
-        while (p < n_tc && scr.tc_id[p] < t) ++p;
-        if (p < n_tc && scr.tc_id[p] == t) { ++scr.tc_cnt[p]; continue; }
-        for (int z = n_tc; z > p; --z) { scr.tc_id[z] = scr.tc_id[z - 1]; scr.tc_cnt[z] = scr.tc_cnt[z - 1]; }
-        scr.tc_id[p] = t; scr.tc_cnt[p] = 1;
-        ++n_tc;
+    {
+        // neighbouring buckets mostly carry the same taxon: runs are counted in a register and entered once (the arrays
+        // live in the per-thread scratch slice, every access is a round trip)
+        int32_t run_t = 0;
+        int run = 0;
+        for (int k = 0; k <= max_q + 1; ++k) {
+            const bool last = k > max_q;
+            int32_t t = 0;
+            if (!last) {
+                if (scr.bucket_ham[k] == 255) continue;
+                t = scr.bucket_tax[k];
+                if (run && t == run_t) { ++run; continue; }
+            }
+            if (run) {
+                int p = 0;
+                while (p < n_tc && scr.tc_id[p] < run_t) ++p;
+                if (p < n_tc && scr.tc_id[p] == run_t) scr.tc_cnt[p] += run;
+                else {
+                    for (int z = n_tc; z > p; --z) { scr.tc_id[z] = scr.tc_id[z - 1]; scr.tc_cnt[z] = scr.tc_cnt[z - 1]; }
+                    scr.tc_id[p] = run_t; scr.tc_cnt[p] = run;
+                    ++n_tc;
+                }
+            }
+            run_t = t; run = last ? 0 : 1;
+        }
     }
     r.is_classified = 1;
     r.score = best.score;

@@ -79,8 +79,14 @@ void emu_hamming_lut(const uint64_t *q, const uint64_t *t, const uint8_t *revers
 int32_t emu_lca(const int32_t *parent, const int32_t *depth, int32_t max_taxid, int32_t node0, int32_t a, int32_t b) {
     TaxView tv;
     tv.parent = parent; tv.depth = depth; tv.species_of = nullptr; tv.species_rank_of = nullptr;
-    tv.max_taxid = max_taxid; tv.node0_taxid = node0; tv.eukaryota = 0;
-    return tax_lca(tv, a, b);
+    tv.max_taxid = max_taxid; tv.node0_taxid = node0; tv.eukaryota = 0; tv.node = nullptr;
+    const int32_t plain = tax_lca(tv, a, b);
+    // the packed node table (what the device uses) must give the same answer
+    std::vector<u64> node((size_t) max_taxid + 1);
+    for (int32_t i = 0; i <= max_taxid; ++i) node[i] = (u64) (u32) parent[i] | ((u64) (u32) depth[i] << 32);
+    tv.node = node.data();
+    const int32_t packed = tax_lca(tv, a, b);
+    return plain == packed ? plain : -12345;
 }
 
 static int g_fast = 0;
@@ -102,6 +108,9 @@ int64_t emu_score(const mb_match *m, size_t n, const uint32_t *lens, uint32_t n_
     TaxView tv;
     tv.parent = parent; tv.depth = depth; tv.species_of = species_of; tv.species_rank_of = species_rank_of;
     tv.max_taxid = max_taxid; tv.node0_taxid = node0; tv.eukaryota = euk;
+    std::vector<u64> node((size_t) max_taxid + 1);
+    for (int32_t i = 0; i <= max_taxid; ++i) node[i] = (u64) (u32) parent[i] | ((u64) (u32) depth[i] << 32);
+    tv.node = node.data();
     std::vector<size_t> sb(n_reads, 0), se(n_reads, 0);
     size_t max_seg = 16;
     for (size_t i = 0; i < n;) {
