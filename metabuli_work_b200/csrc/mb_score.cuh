@@ -707,7 +707,26 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
         const int pc = (int) (sw[0] >> 24);
         u32 *pp = wp + p0 * 3;
         p0 += pc;
-        // std::sort on <= 16 elements is libstdc++'s __insertion_sort (bits/stl_algo.h)
+        // std::sort on <= 16 elements is libstdc++'s __insertion_sort (bits/stl_algo.h): a stable sort by the comparator.
+        // Up to four paths (the usual case) are not moved at all: their comparator keys (score desc, hamming asc, start
+        // desc, then the index) are ranked in registers and the list is read through the resulting order.
+        u64 ord = 0xFEDCBA9876543210ull;         // ord nibble k = index of the k-th path in sorted order
+        if (pc <= 4) {
+            u64 key[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                key[i] = ~0ull;
+                if (i < pc) {
+                    const u32 v0 = pp[i * 3], v1 = pp[i * 3 + 1];
+                    key[i] = ((((u64) (u32) (32767 - pk_score2(v1)) << 32) | ((u64) (u32) pk_ham(v1) << 16) | (u64) (0xFFFFu - (v0 & 0xFFFFu))) << 2) | (u64) i;
+                }
+            }
+            const u32 c01 = key[0] < key[1], c02 = key[0] < key[2], c03 = key[0] < key[3];
+            const u32 c12 = key[1] < key[2], c13 = key[1] < key[3], c23 = key[2] < key[3];
+            const u32 r0 = 3u - c01 - c02 - c03, r1 = c01 + 2u - c12 - c13, r2 = c02 + c12 + 1u - c23, r3 = c03 + c13 + c23;
+            ord = (1ull << (4 * r1)) | (2ull << (4 * r2)) | (3ull << (4 * r3));
+            (void) r0;
+        } else
         for (int k = 1; k < pc; ++k) {
             const u32 v0 = pp[k * 3], v1 = pp[k * 3 + 1], v2 = pp[k * 3 + 2];
             int j = k;
@@ -723,9 +742,11 @@ MB_HD int best_species_compact(const mb_match *m, int n, int query_length, const
         }
         int n_comb = 0, sum2 = 0;
         for (int k = 0; k < pc; ++k) {
-            int c_start = (int) (pp[k * 3] & 0xFFFFu), c_end = (int) (pp[k * 3] >> 16);
-            int c_score2 = pk_score2(pp[k * 3 + 1]), c_ham = pk_ham(pp[k * 3 + 1]);
-            const int c_sm = (int) (pp[k * 3 + 2] & 0xFFFFu), c_em = (int) (pp[k * 3 + 2] >> 16);
+            const int o = (int) ((ord >> (4 * k)) & 15u);
+            const u32 q0 = pp[o * 3], q1 = pp[o * 3 + 1], q2 = pp[o * 3 + 2];
+            int c_start = (int) (q0 & 0xFFFFu), c_end = (int) (q0 >> 16);
+            int c_score2 = pk_score2(q1), c_ham = pk_ham(q1);
+            const int c_sm = (int) (q2 & 0xFFFFu), c_em = (int) (q2 >> 16);
             bool rejected = false;
             for (int j = 0; j < n_comb; ++j) {
                 const int k_start = (int) (comb[j] & 0xFFFFu), k_end = (int) (comb[j] >> 16);
