@@ -119,8 +119,12 @@ __global__ void __launch_bounds__(RS_BINS) k_radix_scan_hist(u64 *__restrict__ h
 }
 
 // ---- one pass -----------------------------------------------------------------------------------
+// resident CTAs per SM the register allocation aims at: tiles of up to 48 KB fit three times into an SM
+template <typename Rec, int ITEMS>
+constexpr int radix_min_blocks() { return sizeof(Rec) * ITEMS <= 192 ? 3 : 2; }
+
 template <typename Rec, typename Key, int ITEMS, bool SEG>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, radix_min_blocks<Rec, ITEMS>())
 k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, int pass,
              const u64 *__restrict__ digit_base /*[256] exclusive*/, u64 *tile_state /*[tiles][256]*/,
              u32 *ticket, int dbg, const __grid_constant__ SegIn seg) {
