@@ -10,7 +10,7 @@ $CMD > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || { echo "pl
 cat gpurun_out/${TAG}_plain.json
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "launch list rc=$?"
-for spec in "k_match:^k_match\$:2:1" "k_extract:^k_extract:2:1" "k_radix_pass:^k_radix_pass:14:7" "k_radix_hist:^k_radix_hist:4:2" "k_sort_segments:^k_sort_segments:2:1" "k_score_fast:^k_score_fast\$:2:1" "k_score_finish:^k_score_finish\$:2:1" "k_score:^k_score\$:2:1" "k_segment_matches:^k_segment_matches:2:1" "k_match_partition:^k_match_partition:2:1"; do
+for spec in "k_match:^k_match\$:2:1" "k_extract:^k_extract:2:1" "k_radix_pass:^k_radix_pass:18:6" "k_radix_hist:^k_radix_hist:6:2" "k_sort_segments:^k_sort_segments\$:2:1" "k_score_fast:^k_score_fast\$:2:1" "k_score_finish:^k_score_finish\$:2:1" "k_score:^k_score\$:2:1" "k_segment_matches:^k_segment_matches:2:1" "k_match_partition:^k_match_partition:2:1"; do
   IFS=: read name rx skip cnt <<< "$spec"
   ncu --set full --clock-control none --import-source on -k regex:$rx -s $skip -c $cnt -f -o gpurun_out/${TAG}_${name} $CMD > gpurun_out/${TAG}_ncu_${name}.log 2>&1
   echo "$name rc=$?"
