@@ -150,6 +150,29 @@ int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint
 /* The same path in stages (each leaves its output resident on the device): */
 int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
                    uint32_t n_reads);                                   /* H2D only                      */
+/* Input pipeline on the device.  Replaces, for plain four-line FASTQ text, the two host
+ * parses of the reference: QueryIndexer::indexQueryFile (src/commons/QueryIndexer.cpp:30-147) and
+ * KmerExtractor::loadChunkOfReads over KSeqWrapper (src/commons/KmerExtractor.cpp:312-386).  text1 / text2 are raw
+ * chunks of the two FASTQ files (text2 = NULL: single-end; the second mate of every read is then empty), each starting
+ * at a record boundary.  The library uploads the text, finds the lines, checks the records ('@' / '+' markers, equal
+ * sequence and quality length, optional CR), packs the sequence lines of up to max_reads whole records (the same number
+ * from both files) exactly as mb_stage_reads expects them and leaves the batch staged.  final_chunk != 0: the text ends
+ * the file, so a last line without a newline is complete.  out->consumed1/2: bytes of each text that belong to the
+ * staged reads (the caller carries the rest over to its next chunk).  MB_E_DATA on a malformed record. */
+typedef struct {
+    uint32_t n_reads;         /* records staged                                            */
+    uint32_t reserved;
+    uint64_t consumed1, consumed2;
+    uint64_t n_bases;         /* bases of the staged batch (both mates)                    */
+} mb_fastq_index;
+int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2, size_t n2, uint32_t max_reads,
+                   int final_chunk, mb_fastq_index *out);
+/* Name span of every staged read inside text1 (offset of the first character after '@', length up to the first
+ * white space: kseq's `name`), n_reads entries each; valid after mb_stage_fastq. */
+int mb_fetch_fastq_names(mb_ctx *ctx, uint64_t *name_off, uint32_t *name_len);
+/* The staged batch as mb_stage_reads would have received it (parity tap; any pointer may be NULL). */
+int mb_fetch_staged_reads(mb_ctx *ctx, char *bases, uint64_t *offsets, uint32_t *lens);
+
 /* Overlap the host->device copy of the NEXT batch with the device work of the current one: the copy is
  * enqueued on a second stream into a second set of buffers; a following mb_stage_reads (or
  * mb_classify_batch) with the SAME arguments adopts the copied batch instead of copying again.  The

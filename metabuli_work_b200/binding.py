@@ -65,7 +65,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream",
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
-               "mb_prefetch_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
+               "mb_prefetch_reads", "mb_stage_fastq", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -121,6 +121,14 @@ _sig(_cuda, "mb_ipc_export", C.c_int, [vp, vp, vp])
 _sig(_cuda, "mb_ipc_open", C.c_int, [vp, vp, C.POINTER(vp)])
 _sig(_cuda, "mb_ipc_close", C.c_int, [vp, vp])
 _sig(_cuda, "mb_peer_attach", C.c_int, [vp, u32, u32, C.POINTER(PeerMem), vp, u32])
+class FastqIndex(C.Structure):
+    _fields_ = [("n_reads", C.c_uint32), ("reserved", C.c_uint32), ("consumed1", C.c_uint64), ("consumed2", C.c_uint64),
+                ("n_bases", C.c_uint64)]
+
+
+_sig(_cuda, "mb_stage_fastq", C.c_int, [vp, vp, sz, vp, sz, u32, C.c_int, C.POINTER(FastqIndex)])
+_sig(_cuda, "mb_fetch_fastq_names", C.c_int, [vp, vp, vp])
+_sig(_cuda, "mb_fetch_staged_reads", C.c_int, [vp, vp, vp, vp])
 _sig(_cuda, "mb_extract_kmers_routed", C.c_int, [vp, szp])
 _sig(_cuda, "mb_take_routed_kmers", C.c_int, [vp, szp])
 _sig(_cuda, "mb_match_kmers_routed", C.c_int, [vp, szp])
@@ -211,6 +219,35 @@ class Context:
         self._keep_next = (bases, offsets, lens)
         bp = bases_ptr if bases_ptr is not None else _ptr(bases)
         self._ck(_cuda.mb_prefetch_reads(self.ctx, bp, len(bases), _ptr(offsets), _ptr(lens), len(lens) // 2))
+
+    def stage_fastq(self, text1, text2=None, max_reads=0xFFFFFFFF, final=True):
+        """Raw FASTQ text (bytes / uint8 arrays) -> staged batch, parsed on the device (mb_stage_fastq).
+        Returns (n_reads, consumed1, consumed2, n_bases)."""
+        t1 = np.frombuffer(text1, dtype=np.uint8) if isinstance(text1, (bytes, bytearray)) else text1
+        t2 = None if text2 is None else (np.frombuffer(text2, dtype=np.uint8) if isinstance(text2, (bytes, bytearray)) else text2)
+        self._keep = (t1, t2)
+        idx = FastqIndex()
+        self._ck(_cuda.mb_stage_fastq(self.ctx, _ptr(t1) if len(t1) else None, len(t1),
+                                      None if t2 is None else (_ptr(t2) if len(t2) else _ptr(np.zeros(1, dtype=np.uint8))),
+                                      0 if t2 is None else len(t2), max_reads, 1 if final else 0, C.byref(idx)))
+        self.n_reads = idx.n_reads
+        return idx.n_reads, idx.consumed1, idx.consumed2, idx.n_bases
+
+    def fastq_names(self, text1):
+        """Names of the reads staged by stage_fastq, cut out of text1 through the device-computed spans."""
+        off = np.zeros(self.n_reads, dtype=np.uint64)
+        ln = np.zeros(self.n_reads, dtype=np.uint32)
+        self._ck(_cuda.mb_fetch_fastq_names(self.ctx, _ptr(off), _ptr(ln)))
+        t = bytes(text1)
+        return [t[int(o):int(o) + int(l)] for o, l in zip(off, ln)]
+
+    def staged_reads(self, n_bases):
+        bases = np.zeros(n_bases, dtype=np.uint8)
+        offsets = np.zeros(2 * self.n_reads, dtype=np.uint64)
+        lens = np.zeros(2 * self.n_reads, dtype=np.uint32)
+        self._ck(_cuda.mb_fetch_staged_reads(self.ctx, _ptr(bases) if n_bases else None, _ptr(offsets) if self.n_reads else None,
+                                             _ptr(lens) if self.n_reads else None))
+        return bases, offsets, lens
 
     def extract(self):
         n = C.c_size_t(0)

@@ -12,6 +12,7 @@
 #include "mb_match.cuh"
 #include "mb_score.cuh"
 #include "mb_segsort.cuh"
+#include "mb_fastq.cuh"
 
 #include <cuda_runtime.h>
 
@@ -93,6 +94,8 @@ struct mb_ctx {
     u32 n_blocks = 0;
     // taxonomy
     DevBuf parent, depth, species_of, species_rank_of, tax_node;
+    DevBuf fq_text[2], fq_tile_cnt, fq_tile_off, fq_lines[2], fq_src, fq_name_off, fq_name_len, fq_info, fq_sums, fq_sum_off;   // mb_stage_fastq
+    u32 fq_n_reads = 0;
     DevBuf seg_long;                  // reads whose segment goes to k_sort_segments_long
     int32_t max_taxid = -1, node0 = 0, euk = 0;
     // batch
@@ -585,6 +588,160 @@ int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_
     ctx->launches = 0;
     ctx->n_samples = 0;
     ctx->times.match_retries = 0;
+    return MB_OK;
+}
+
+// ---- input pipeline on the device: FASTQ text -> staged batch (mb_fastq.cuh) ---------------------------------
+// lines of one text: line_start[0 .. n_lines]; returns the number of COMPLETE lines (terminated, or closed by the end of
+// the file when final_chunk)
+static int fq_index_lines(mb_ctx *ctx, int f, const char *text, size_t n, int final_chunk, u64 *n_lines) {
+    *n_lines = 0;
+    CK(ctx->fq_text[f].ensure(n + 64));
+    u8 *d_text = ctx->fq_text[f].as<u8>();
+    if (n) CK(cudaMemcpyAsync(d_text, text, n, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(d_text + n, 0, 64, ctx->stream));
+    const u64 tiles = (n + FQ_TILE - 1) / FQ_TILE;
+    if (tiles > 0xFFFFFFFFull) return fail(ctx, MB_E_ARG, "FASTQ chunk too large");
+    CK(ctx->fq_tile_cnt.ensure((tiles + 1) * sizeof(u32)));
+    CK(ctx->fq_tile_off.ensure((tiles + 2) * sizeof(u64)));
+    u64 newlines = 0;
+    if (tiles) {
+        k_fq_count<<<(unsigned) tiles, FQ_THREADS, 0, ctx->stream>>>(d_text, n, ctx->fq_tile_cnt.as<u32>());
+        k_scan_counts<<<1, 1024, 0, ctx->stream>>>(ctx->fq_tile_cnt.as<u32>(), ctx->fq_tile_off.as<u64>(), (u32) tiles);
+        CK(cudaGetLastError());
+        ctx->launches += 2;
+        if (int rc = read_back(ctx, ctx->fq_tile_off.as<u64>() + tiles, &newlines)) return rc;
+    }
+    CK(ctx->fq_lines[f].ensure((newlines + 3) * sizeof(u64)));
+    CK(cudaMemsetAsync(ctx->fq_lines[f].p, 0, sizeof(u64), ctx->stream));
+    if (tiles) {
+        k_fq_lines<<<(unsigned) tiles, FQ_THREADS, 0, ctx->stream>>>(d_text, n, ctx->fq_tile_off.as<u64>(), ctx->fq_lines[f].as<u64>());
+        CK(cudaGetLastError());
+        ++ctx->launches;
+    }
+    u64 lines = newlines;
+    if (final_chunk && n && text[n - 1] != '\n') {               // the last line of the file has no newline: closed by the end
+        const u64 end = (u64) n + 1;
+        CK(cudaMemcpyAsync(ctx->fq_lines[f].as<u64>() + newlines + 1, &end, sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ++lines;
+    }
+    *n_lines = lines;
+    return MB_OK;
+}
+
+int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2, size_t n2, uint32_t max_reads, int final_chunk,
+                   mb_fastq_index *out) {
+    if (!ctx || !out || (!text1 && n1) || (!text2 && n2)) return MB_E_ARG;
+    memset(out, 0, sizeof(*out));
+    CK(cudaSetDevice(ctx->par.device));
+    ctx->have_reads = ctx->have_kmers = ctx->have_matches = ctx->have_results = false;
+    ctx->fq_n_reads = 0;
+    ctx->launches = 0;
+    ctx->n_samples = 0;
+    mark(ctx, EV_START);
+    const bool paired = text2 != nullptr;
+    u64 lines1 = 0, lines2 = 0;
+    if (int rc = fq_index_lines(ctx, 0, text1, n1, final_chunk, &lines1)) return rc;
+    if (paired) { if (int rc = fq_index_lines(ctx, 1, text2, n2, final_chunk, &lines2)) return rc; }
+    u64 nr64 = lines1 / 4;
+    if (paired) nr64 = std::min<u64>(nr64, lines2 / 4);
+    nr64 = std::min<u64>(nr64, max_reads);
+    if (nr64 + ctx->seq_base >= (1u << 29)) return fail(ctx, MB_E_ARG, "at most 2^29-1 reads per batch (29-bit sequenceID, Kmer.h:11-16)");
+    const u32 nr = (u32) nr64;
+    // bytes of each text that belong to these records
+    u64 c1 = 0, c2 = 0;
+    if (nr) {
+        if (int rc = read_back(ctx, ctx->fq_lines[0].as<u64>() + 4 * (u64) nr, &c1)) return rc;
+        if (paired) { if (int rc = read_back(ctx, ctx->fq_lines[1].as<u64>() + 4 * (u64) nr, &c2)) return rc; }
+    }
+    out->consumed1 = std::min<u64>(c1, n1);
+    out->consumed2 = std::min<u64>(c2, n2);
+    const u64 nm = 2 * (u64) nr;
+    CK(ctx->offsets.ensure(nm * sizeof(u64) + 16));
+    CK(ctx->lens.ensure(nm * sizeof(u32) + 16));
+    CK(ctx->fq_src.ensure(nm * sizeof(u64) + 16));
+    CK(ctx->fq_name_off.ensure((u64) nr * sizeof(u64) + 16));
+    CK(ctx->fq_name_len.ensure((u64) nr * sizeof(u32) + 16));
+    CK(ctx->fq_info.ensure(sizeof(FqInfo)));
+    CK(ctx->stage_info.ensure(sizeof(StageInfo)));
+    CK(cudaMemsetAsync(ctx->fq_info.p, 0, sizeof(FqInfo), ctx->stream));
+    CK(cudaMemsetAsync(ctx->stage_info.p, 0, sizeof(StageInfo), ctx->stream));
+    u64 n_bases = 0;
+    if (nr) {
+        k_fq_records<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->fq_text[0].as<u8>(), ctx->fq_lines[0].as<u64>(), nr, 0, paired ? 2 : 1,
+                                                                 ctx->lens.as<u32>(), ctx->fq_src.as<u64>(), ctx->fq_name_off.as<u64>(),
+                                                                 ctx->fq_name_len.as<u32>(), ctx->fq_info.as<FqInfo>());
+        if (paired)
+            k_fq_records<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->fq_text[1].as<u8>(), ctx->fq_lines[1].as<u64>(), nr, 1, 2,
+                                                                     ctx->lens.as<u32>(), ctx->fq_src.as<u64>(), nullptr, nullptr,
+                                                                     ctx->fq_info.as<FqInfo>());
+        // packed offsets = exclusive scan of the mate lengths
+        const u64 st = (nm + SCAN_TILE - 1) / SCAN_TILE;
+        CK(ctx->fq_sums.ensure((st + 1) * sizeof(u32)));
+        CK(ctx->fq_sum_off.ensure((st + 2) * sizeof(u64)));
+        k_scan_tile_sums<<<(unsigned) st, 256, 0, ctx->stream>>>(ctx->lens.as<u32>(), nm, ctx->fq_sums.as<u32>());
+        k_scan_counts<<<1, 1024, 0, ctx->stream>>>(ctx->fq_sums.as<u32>(), ctx->fq_sum_off.as<u64>(), (u32) st);
+        k_scan_tile_apply<<<(unsigned) st, 256, 0, ctx->stream>>>(ctx->lens.as<u32>(), nm, ctx->fq_sum_off.as<u64>(), ctx->offsets.as<u64>());
+        CK(cudaGetLastError());
+        ctx->launches += paired ? 5 : 4;
+        if (int rc = read_back(ctx, ctx->fq_sum_off.as<u64>() + st, &n_bases)) return rc;
+        FqInfo fi;
+        if (int rc = read_back(ctx, ctx->fq_info.as<FqInfo>(), &fi)) return rc;
+        if (fi.bad) {
+            char msg[160];
+            snprintf(msg, sizeof(msg), "FASTQ record %llu of this chunk is malformed (%s)", fi.bad_record,
+                     fi.bad == 1 ? "header does not start with '@'" : fi.bad == 2 ? "separator line does not start with '+'"
+                                                                                   : "sequence and quality differ in length");
+            return fail(ctx, MB_E_DATA, msg);
+        }
+    }
+    CK(ctx->bases.ensure(n_bases + 128));
+    if (nr) {
+        k_fq_pack<<<(unsigned) ((nm * 32 + 255) / 256), 256, 0, ctx->stream>>>(ctx->fq_text[0].as<u8>(), paired ? ctx->fq_text[1].as<u8>() : nullptr,
+                                                                               ctx->fq_src.as<u64>(), ctx->lens.as<u32>(), ctx->offsets.as<u64>(),
+                                                                               (u32) nm, ctx->bases.as<u8>());
+        k_validate_reads<<<(nr + 255) / 256, 256, 0, ctx->stream>>>(ctx->offsets.as<u64>(), ctx->lens.as<u32>(), nr, n_bases, ctx->par.seq_mode == 2,
+                                                                     ctx->stage_info.as<StageInfo>());
+        CK(cudaGetLastError());
+        ctx->launches += 2;
+    }
+    CK(cudaMemsetAsync(ctx->bases.as<u8>() + n_bases, 0, 128, ctx->stream));
+    mark(ctx, EV_H2D);
+    StageInfo info;
+    if (int rc = read_back(ctx, ctx->stage_info.as<StageInfo>(), &info)) return rc;
+    if (info.bad) return fail(ctx, MB_E_DATA, "internal: packed FASTQ batch failed the layout check");
+    ctx->n_bases = n_bases;
+    ctx->n_reads = nr;
+    ctx->fq_n_reads = nr;
+    ctx->kmer_bound = info.bound;
+    ctx->max_query_len = info.max_q + 8;
+    ctx->have_reads = true;
+    ctx->times.match_retries = 0;
+    out->n_reads = nr;
+    out->n_bases = n_bases;
+    return MB_OK;
+}
+
+int mb_fetch_fastq_names(mb_ctx *ctx, uint64_t *name_off, uint32_t *name_len) {
+    if (!ctx || !name_off || !name_len) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    if (ctx->fq_n_reads) {
+        CK(cudaMemcpyAsync(name_off, ctx->fq_name_off.p, (size_t) ctx->fq_n_reads * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(name_len, ctx->fq_name_len.p, (size_t) ctx->fq_n_reads * sizeof(u32), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    return MB_OK;
+}
+
+int mb_fetch_staged_reads(mb_ctx *ctx, char *bases, uint64_t *offsets, uint32_t *lens) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "no batch staged");
+    CK(cudaSetDevice(ctx->par.device));
+    if (bases && ctx->n_bases) CK(cudaMemcpyAsync(bases, ctx->bases.p, ctx->n_bases, cudaMemcpyDeviceToHost, ctx->stream));
+    if (offsets && ctx->n_reads) CK(cudaMemcpyAsync(offsets, ctx->offsets.p, (size_t) ctx->n_reads * 2 * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    if (lens && ctx->n_reads) CK(cudaMemcpyAsync(lens, ctx->lens.p, (size_t) ctx->n_reads * 2 * sizeof(u32), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }
 

@@ -386,3 +386,69 @@ def test_prefetch_overlap(golden, mb):
             clf.stage(b, o2, l)
     finally:
         clf.close()
+
+
+def _fastq_text(names, seqs, eol=b"\n", trailing=True, comment=True):
+    recs = []
+    for k, (n, s) in enumerate(zip(names, seqs)):
+        hdr = b"@" + n + ((b" extra/%d comment" % k) if comment and k % 2 == 0 else b"")
+        recs.append(hdr + eol + bytes(s) + eol + b"+" + (n if k % 3 == 0 else b"") + eol + b"I" * len(s))
+    t = eol.join(recs)
+    return t + (eol if trailing else b"")
+
+
+@pytest.mark.parametrize("variant", ["plain", "crlf", "no_trailing_newline", "single_end", "chunked"])
+def test_fastq_parsed_on_device(golden, mb, variant):
+    """mb_stage_fastq (input pipeline on the device): raw FASTQ text -> the same staged batch the host packer
+    produces (bases, offsets, lengths), the read names, whole-record chunk accounting, malformed-record errors, and the
+    same classification results as the host-parsed path."""
+    _, g1, g2 = golden.reads("plain_paired")
+    s1 = [bytes(x) for x in g1[:300]] + [b"", b"ACGTN", b"acgtacgtacgtacgtacgtacgtacgtacgt"]
+    s2 = [bytes(x) for x in g2[:300]] + [b"ACGT", b"", b"TTTTGGGGCCCCAAAATTTTGGGGCCCCAAAA"]
+    names = [b"read_%d/x" % i for i in range(len(s1))]
+    paired = variant != "single_end"
+    eol = b"\r\n" if variant == "crlf" else b"\n"
+    t1 = _fastq_text(names, s1, eol, trailing=variant != "no_trailing_newline")
+    t2 = _fastq_text(names, s2, eol, trailing=variant != "no_trailing_newline", comment=False) if paired else None
+    clf = mb.Classifier(golden.dbdir("plain_paired"), seq_mode=2 if paired else 1)
+    try:
+        want_b, want_o, want_l = mb.pack_reads(s1, s2 if paired else None)
+        clf.stage(want_b, want_o, want_l)
+        used = clf.classify_staged()
+        want_res, want_ids, want_cnt = clf.fetch(used)
+        if variant == "chunked":
+            # the texts are cut in the middle of a record: only whole records are taken and the consumed bytes say where
+            # the next chunk starts; a read limit cuts earlier
+            cut1, cut2 = len(t1) * 2 // 3, len(t2) // 2
+            n, c1, c2, nb = clf.stage_fastq(t1[:cut1], t2[:cut2], final=False)
+            assert 0 < n < len(s1) and t1[c1:c1 + 1] == b"@" and t2[c2:c2 + 1] == b"@"
+            assert t1[:c1].count(b"\n") == 4 * n and t2[:c2].count(b"\n") == 4 * n
+            b0, o0, l0 = clf.staged_reads(nb)
+            n2, d1, d2, nb2 = clf.stage_fastq(t1[c1:], t2[c2:], final=True)
+            assert n + n2 == len(s1) and c1 + d1 == len(t1) and c2 + d2 == len(t2)
+            b1, o1, l1 = clf.staged_reads(nb2)
+            assert np.array_equal(np.concatenate([b0, b1]), want_b) and np.array_equal(np.concatenate([l0, l1]), want_l)
+            assert np.array_equal(np.concatenate([o0, o1 + np.uint64(nb)]), want_o)
+            n3, e1, e2, _ = clf.stage_fastq(t1, t2, max_reads=17)
+            assert n3 == 17 and t1[:e1].count(b"\n") == 68 and t2[:e2].count(b"\n") == 68
+            return
+        n, c1, c2, nb = clf.stage_fastq(t1, t2)
+        assert n == len(s1) and c1 == len(t1) and (not paired or c2 == len(t2)) and nb == len(want_b)
+        got_b, got_o, got_l = clf.staged_reads(nb)
+        assert np.array_equal(got_l, want_l) and np.array_equal(got_o, want_o) and np.array_equal(got_b, want_b)
+        assert clf.fastq_names(t1) == names
+        used = clf.classify_staged()
+        res, ids, cnt = clf.fetch(used)
+        assert compare_results(res, ids, cnt, want_res, want_ids, want_cnt) == []
+        # malformed records are reported, not classified
+        bad = t1.replace(b"+", b"-", 1)
+        with pytest.raises(mb.MetabuliError):
+            clf.stage_fastq(bad, t2)
+        lines = t1.split(eol)
+        lines[3] = lines[3][:-1]                       # quality shorter than the sequence
+        with pytest.raises(mb.MetabuliError):
+            clf.stage_fastq(eol.join(lines), t2)
+        n0, _, _, nb0 = clf.stage_fastq(b"", b"" if paired else None)
+        assert n0 == 0 and nb0 == 0
+    finally:
+        clf.close()
