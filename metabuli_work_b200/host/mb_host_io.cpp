@@ -209,6 +209,40 @@ static bool loadBatch(FastxReader &r1, FastxReader *r2, size_t maxReads, size_t 
     return !b.names.empty();
 }
 
+// Raw text of one plain FASTQ file, read in chunks; the tail that mb_stage_fastq did not consume (an incomplete record,
+// or records beyond the batch limit) is carried over to the next chunk.
+struct RawText {
+    FILE *fp = nullptr;
+    std::vector<char> buf;
+    size_t fill = 0;
+    bool eof = false;
+    ~RawText() { if (fp) fclose(fp); }
+    bool open(const std::string &path) { fp = fopen(path.c_str(), "rb"); return fp != nullptr; }
+    void refill(size_t chunk) {
+        if (buf.size() < chunk) buf.resize(chunk);
+        while (!eof && fill < chunk) {
+            const size_t n = fread(buf.data() + fill, 1, chunk - fill, fp);
+            if (n == 0) eof = true;
+            fill += n;
+        }
+    }
+    void consume(size_t n) { memmove(buf.data(), buf.data() + n, fill - n); fill -= n; }
+};
+
+// plain (not gzip) four-line FASTQ?  Decided on the first bytes: '@' starts the file and the third line starts with '+'.
+static bool looksLikePlainFastq(const std::string &path) {
+    FILE *fp = fopen(path.c_str(), "rb");
+    if (!fp) return false;
+    char head[1 << 16];
+    const size_t n = fread(head, 1, sizeof(head), fp);
+    fclose(fp);
+    if (n < 4 || head[0] != '@') return false;
+    size_t line = 0;
+    for (size_t i = 0; i + 1 < n; ++i)
+        if (head[i] == '\n' && ++line == 2) return head[i + 1] == '+';
+    return false;
+}
+
 int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,
                 const std::string &jobId, Options opt, std::string &err) {
     using clk = std::chrono::steady_clock;
@@ -220,15 +254,75 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
               << " bytes (" << std::chrono::duration<double>(t1 - t0).count() << " s)" << std::endl;
     Reporter rep(db.taxonomy(), outDir, jobId, opt.printLineage != 0);
     if (!rep.openClassifications(err)) return 1;
-    FastxReader r1, r2;
-    if (!r1.open(inputs[0], err)) return 1;
     const bool paired = opt.seqMode == 2;
-    if (paired && !r2.open(inputs[1], err)) return 1;
     ReadBatch batch;
     std::vector<mb_read_result> res;
     std::vector<int32_t> tcId, tcCnt;
     uint64_t totalKmers = 0, totalMatches = 0;
     double gpuMs = 0;
+    // Plain FASTQ goes to the GPU as raw text (mb_stage_fastq: lines, records and packing are found on the device; the host
+    // only cuts the read names out at the spans it gets back).  FASTA, multi-line or gzip input takes the host reader.
+    const bool deviceParse = !getenv("MB_HOST_PARSE") && looksLikePlainFastq(inputs[0]) && (!paired || looksLikePlainFastq(inputs[1]));
+    if (deviceParse) {
+        RawText f1, f2;
+        if (!f1.open(inputs[0])) { err = "cannot open " + inputs[0]; return 1; }
+        if (paired && !f2.open(inputs[1])) { err = "cannot open " + inputs[1]; return 1; }
+        // a chunk holds at least one batch of short reads (~330 text bytes per 150-base record) and never less than 64 MB
+        const size_t chunk = std::max<size_t>(64u << 20, std::min<size_t>(opt.batchReads * 400, 2ull << 30));
+        std::vector<uint64_t> nameOff;
+        std::vector<uint32_t> nameLen;
+        while (true) {
+            f1.refill(chunk);
+            if (paired) f2.refill(chunk);
+            if (f1.fill == 0) break;
+            const bool last = f1.eof && (!paired || f2.eof);
+            mb_fastq_index idx;
+            int rc = mb_stage_fastq(db.ctx(), f1.buf.data(), f1.fill, paired ? f2.buf.data() : nullptr, paired ? f2.fill : 0,
+                                    (uint32_t) std::min<size_t>(opt.batchReads, 0xFFFFFFFFu), last ? 1 : 0, &idx);
+            if (rc != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
+            if (idx.n_reads == 0) {
+                if (last) break;
+                err = "FASTQ record longer than the read chunk (use a smaller --batch-reads only with short reads)";
+                return 1;
+            }
+            size_t used = 0;
+            rc = mb_classify_staged(db.ctx(), &used);
+            res.resize(idx.n_reads);
+            if (rc == MB_OK) {
+                tcId.resize(used + 1);
+                tcCnt.resize(used + 1);
+                rc = mb_fetch_results(db.ctx(), res.data(), tcId.data(), tcCnt.data(), used + 1);
+            }
+            nameOff.resize(idx.n_reads);
+            nameLen.resize(idx.n_reads);
+            if (rc == MB_OK) rc = mb_fetch_fastq_names(db.ctx(), nameOff.data(), nameLen.data());
+            if (rc != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
+            batch.clear();
+            batch.names.resize(idx.n_reads);
+            for (uint32_t i = 0; i < idx.n_reads; ++i) batch.names[i].assign(f1.buf.data() + nameOff[i], nameLen[i]);
+            mb_phase_times t;
+            mb_get_timings(db.ctx(), &t);
+            totalKmers += t.n_kmers;
+            totalMatches += t.n_matches;
+            gpuMs += t.total_ms;
+            std::cout << "Batch of " << idx.n_reads << " reads (FASTQ parsed on the GPU): " << t.n_kmers << " query k-mers, " << t.n_matches
+                      << " matches; GPU ms: parse+copy " << t.h2d_ms << " extract " << t.extract_ms << " sort " << t.sort_kmers_ms << " match "
+                      << t.match_ms << " sort " << t.sort_matches_ms << " score " << t.score_ms << std::endl;
+            rep.writeClassifications(batch, res.data(), tcId.data(), tcCnt.data());
+            f1.consume(idx.consumed1);
+            if (paired) f2.consume(idx.consumed2);
+        }
+        rep.closeClassifications();
+        if (!rep.writeReport(err)) return 1;
+        const auto t2 = clk::now();
+        std::cout << "Number of query k-mers: " << totalKmers << "\nThe number of matches: " << totalMatches << "\nNumber of sequences: "
+                  << rep.totalReads() << "\nGPU time: " << gpuMs / 1000.0 << " s\nTime for processing: "
+                  << std::chrono::duration<double>(t2 - t0).count() << " s" << std::endl;
+        return 0;
+    }
+    FastxReader r1, r2;
+    if (!r1.open(inputs[0], err)) return 1;
+    if (paired && !r2.open(inputs[1], err)) return 1;
     // long reads: bound the batch by bases as well (QueryIndexer sizes batches by k-mer count, QueryIndexer.cpp:62-67)
     const size_t maxBases = 4ull << 30;
     while (loadBatch(r1, paired ? &r2 : nullptr, opt.batchReads, maxBases, batch)) {

@@ -208,10 +208,14 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
     k, m, res, ids, cnt = orc.classify(db, p, orc.Batch(s1, s2))
     orc.write_classifications(db, os.path.join(out, "ref_classifications.tsv"), names, res, ids, cnt)
     orc.write_report(db, os.path.join(out, "ref_report.tsv"), res)
+    # (plain FASTQ is parsed on the GPU by default; MB_HOST_PARSE=1 forces the host reader that FASTA / gzip input takes)
+    subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
+                           out, "jobh", "--batch-reads", "150"], env=dict(os.environ, MB_HOST_PARSE="1"))
     for f in ("classifications.tsv", "report.tsv"):
         a = open(os.path.join(out, "job_" + f), "rb").read()
         b = open(os.path.join(out, "ref_" + f), "rb").read()
         assert a == b, f
+        assert open(os.path.join(out, "jobh_" + f), "rb").read() == b, f
     # long-read mode through the library entry point
     mb.classify_files(os.path.join(data, "long.fa"), None, golden.dbdir("sync_long"), out, "jobl", seq_mode=3)
     db2 = orc.Db(golden.dbdir("sync_long"))
