@@ -167,6 +167,14 @@ typedef struct {
 } mb_fastq_index;
 int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2, size_t n2, uint32_t max_reads,
                    int final_chunk, mb_fastq_index *out);
+/* Overlap the host->device copy of the NEXT chunk's text with the device work of the current batch: the copy is enqueued
+ * on the copy stream into a second pair of text buffers; a following mb_stage_fastq with the same pointers and sizes adopts
+ * them instead of copying.  The texts must stay untouched until that call; pinned memory (mb_alloc_host) makes the copy
+ * truly asynchronous. */
+int mb_prefetch_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2, size_t n2);
+/* Page-locked host memory for read / text buffers (cudaMallocHost); NULL on failure. */
+void *mb_alloc_host(size_t bytes);
+void mb_free_host(void *p);
 /* Name span of every staged read inside text1 (offset of the first character after '@', length up to the first
  * white space: kseq's `name`), n_reads entries each; valid after mb_stage_fastq. */
 int mb_fetch_fastq_names(mb_ctx *ctx, uint64_t *name_off, uint32_t *name_len);

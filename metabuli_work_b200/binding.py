@@ -65,7 +65,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_partition_kmers", "mb_partition_matches", "mb_get_timings", "mb_stream",
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
-               "mb_prefetch_reads", "mb_stage_fastq", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
+               "mb_prefetch_reads", "mb_stage_fastq", "mb_prefetch_fastq", "mb_alloc_host", "mb_free_host", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -127,6 +127,9 @@ class FastqIndex(C.Structure):
 
 
 _sig(_cuda, "mb_stage_fastq", C.c_int, [vp, vp, sz, vp, sz, u32, C.c_int, C.POINTER(FastqIndex)])
+_sig(_cuda, "mb_prefetch_fastq", C.c_int, [vp, vp, sz, vp, sz])
+_sig(_cuda, "mb_alloc_host", vp, [sz])
+_sig(_cuda, "mb_free_host", None, [vp])
 _sig(_cuda, "mb_fetch_fastq_names", C.c_int, [vp, vp, vp])
 _sig(_cuda, "mb_fetch_staged_reads", C.c_int, [vp, vp, vp, vp])
 _sig(_cuda, "mb_extract_kmers_routed", C.c_int, [vp, szp])
@@ -232,6 +235,13 @@ class Context:
                                       0 if t2 is None else len(t2), max_reads, 1 if final else 0, C.byref(idx)))
         self.n_reads = idx.n_reads
         return idx.n_reads, idx.consumed1, idx.consumed2, idx.n_bases
+
+    def prefetch_fastq(self, text1, text2=None):
+        """Start the host->device copy of the NEXT chunk's text on the copy stream; a later stage_fastq() with the same
+        arrays adopts it."""
+        self._keep_next = (text1, text2)
+        self._ck(_cuda.mb_prefetch_fastq(self.ctx, _ptr(text1), len(text1), None if text2 is None else _ptr(text2),
+                                         0 if text2 is None else len(text2)))
 
     def fastq_names(self, text1):
         """Names of the reads staged by stage_fastq, cut out of text1 through the device-computed spans."""

@@ -96,6 +96,11 @@ struct mb_ctx {
     DevBuf parent, depth, species_of, species_rank_of, tax_node;
     DevBuf fq_text[2], fq_tile_cnt, fq_tile_off, fq_lines[2], fq_src, fq_name_off, fq_name_len, fq_info, fq_sums, fq_sum_off;   // mb_stage_fastq
     u32 fq_n_reads = 0;
+    DevBuf fq_pf_text[2];             // text of the NEXT chunk, copied on copy_stream (mb_prefetch_fastq)
+    const void *fq_pf_host[2] = {nullptr, nullptr};
+    size_t fq_pf_n[2] = {0, 0};
+    bool fq_pf_pending = false;
+    cudaEvent_t fq_pf_done = nullptr;
     DevBuf seg_long;                  // reads whose segment goes to k_sort_segments_long
     int32_t max_taxid = -1, node0 = 0, euk = 0;
     // batch
@@ -369,6 +374,7 @@ void mb_destroy(mb_ctx *ctx) {
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     if (ctx->pf_done) cudaEventDestroy(ctx->pf_done);
+    if (ctx->fq_pf_done) cudaEventDestroy(ctx->fq_pf_done);
     if (ctx->side_stream) { cudaStreamSynchronize(ctx->side_stream); cudaStreamDestroy(ctx->side_stream); }
     if (ctx->side_fork) cudaEventDestroy(ctx->side_fork);
     if (ctx->side_join) cudaEventDestroy(ctx->side_join);
@@ -596,10 +602,19 @@ int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_
 // the file when final_chunk)
 static int fq_index_lines(mb_ctx *ctx, int f, const char *text, size_t n, int final_chunk, u64 *n_lines) {
     *n_lines = 0;
-    CK(ctx->fq_text[f].ensure(n + 64));
-    u8 *d_text = ctx->fq_text[f].as<u8>();
-    if (n) CK(cudaMemcpyAsync(d_text, text, n, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemsetAsync(d_text + n, 0, 64, ctx->stream));
+    u8 *d_text;
+    if (ctx->fq_pf_pending && ctx->fq_pf_host[f] == text && ctx->fq_pf_n[f] == n) {
+        // this text was prefetched (mb_prefetch_fastq): adopt its buffer, order the work stream behind the copy
+        ctx->fq_text[f].swap(ctx->fq_pf_text[f]);
+        ctx->fq_pf_host[f] = nullptr;
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->fq_pf_done, 0));
+        d_text = ctx->fq_text[f].as<u8>();
+    } else {
+        CK(ctx->fq_text[f].ensure(n + 64));
+        d_text = ctx->fq_text[f].as<u8>();
+        if (n) CK(cudaMemcpyAsync(d_text, text, n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemsetAsync(d_text + n, 0, 64, ctx->stream));
+    }
     const u64 tiles = (n + FQ_TILE - 1) / FQ_TILE;
     if (tiles > 0xFFFFFFFFull) return fail(ctx, MB_E_ARG, "FASTQ chunk too large");
     CK(ctx->fq_tile_cnt.ensure((tiles + 1) * sizeof(u32)));
@@ -644,6 +659,7 @@ int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2,
     u64 lines1 = 0, lines2 = 0;
     if (int rc = fq_index_lines(ctx, 0, text1, n1, final_chunk, &lines1)) return rc;
     if (paired) { if (int rc = fq_index_lines(ctx, 1, text2, n2, final_chunk, &lines2)) return rc; }
+    ctx->fq_pf_pending = false;
     u64 nr64 = lines1 / 4;
     if (paired) nr64 = std::min<u64>(nr64, lines2 / 4);
     nr64 = std::min<u64>(nr64, max_reads);
@@ -722,6 +738,39 @@ int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2,
     out->n_bases = n_bases;
     return MB_OK;
 }
+
+int mb_prefetch_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2, size_t n2) {
+    if (!ctx || (!text1 && n1) || (!text2 && n2)) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->pf_done, cudaEventDisableTiming));
+    }
+    if (!ctx->fq_pf_done) CK(cudaEventCreateWithFlags(&ctx->fq_pf_done, cudaEventDisableTiming));
+    if (ctx->fq_pf_pending) CK(cudaStreamSynchronize(ctx->copy_stream));       // an unclaimed prefetch is overwritten
+    ctx->fq_pf_pending = false;
+    const char *t[2] = {text1, text2};
+    const size_t n[2] = {n1, n2};
+    for (int f = 0; f < 2; ++f) {
+        ctx->fq_pf_host[f] = nullptr;
+        if (!t[f]) continue;
+        CK(ctx->fq_pf_text[f].ensure(n[f] + 64));
+        if (n[f]) CK(cudaMemcpyAsync(ctx->fq_pf_text[f].p, t[f], n[f], cudaMemcpyHostToDevice, ctx->copy_stream));
+        CK(cudaMemsetAsync(ctx->fq_pf_text[f].as<u8>() + n[f], 0, 64, ctx->copy_stream));
+        ctx->fq_pf_host[f] = t[f];
+        ctx->fq_pf_n[f] = n[f];
+    }
+    CK(cudaEventRecord(ctx->fq_pf_done, ctx->copy_stream));
+    ctx->fq_pf_pending = true;
+    return MB_OK;
+}
+
+void *mb_alloc_host(size_t bytes) {
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void mb_free_host(void *p) { if (p) cudaFreeHost(p); }
 
 int mb_fetch_fastq_names(mb_ctx *ctx, uint64_t *name_off, uint32_t *name_len) {
     if (!ctx || !name_off || !name_len) return MB_E_ARG;

@@ -444,6 +444,17 @@ def test_fastq_parsed_on_device(golden, mb, variant):
         used = clf.classify_staged()
         res, ids, cnt = clf.fetch(used)
         assert compare_results(res, ids, cnt, want_res, want_ids, want_cnt) == []
+        # the same text prefetched on the copy stream and adopted by the next stage call
+        a1 = np.frombuffer(t1, dtype=np.uint8).copy()
+        a2 = None if t2 is None else np.frombuffer(t2, dtype=np.uint8).copy()
+        clf.prefetch_fastq(a1, a2)
+        n, c1, c2, nb = clf.stage_fastq(a1, a2)
+        assert n == len(s1) and nb == len(want_b)
+        got_b, got_o, got_l = clf.staged_reads(nb)
+        assert np.array_equal(got_l, want_l) and np.array_equal(got_o, want_o) and np.array_equal(got_b, want_b)
+        used = clf.classify_staged()
+        res, ids, cnt = clf.fetch(used)
+        assert compare_results(res, ids, cnt, want_res, want_ids, want_cnt) == []
         # malformed records are reported, not classified
         bad = t1.replace(b"+", b"-", 1)
         with pytest.raises(mb.MetabuliError):
