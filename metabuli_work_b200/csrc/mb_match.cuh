@@ -544,13 +544,31 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 }
                 // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
                 u32 lo = 0, ncand = 0;
+                bool exact = false;                 // the candidates are copies of the query's value: distance 0, no table lookups
                 if (mine) {
                     // binary search of the decoded block (measured on B200 against a 1024-bucket index and against a hash
                     // directory of the groups built per block: both cost more to build than the search they save)
-                    const u64 aa = qk.value >> 24;
-                    lo = lower_bound_aa_range(s.vals, 0, proc_end, aa);
-                    u32 hi = lo;
-                    while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
+                    // The search is on the FULL value.  When the block holds the query's value itself, the minimum distance
+                    // of its group is 0, the filter min(2 * min, 7) = 0 keeps only distance 0, and distance 0 means the same
+                    // codon ids, i.e. the same value (the Hamming table is 0 on its diagonal only): the candidates are just
+                    // the run of equal values (35 % of the queries and 68 % of the matches of configs[1] end here, with one
+                    // or two pairs instead of the whole group).  Otherwise the candidates are the amino-acid group around
+                    // the insertion point.
+                    const u64 v = qk.value, aa = v >> 24;
+                    u32 l = 0, h = proc_end;
+                    while (l < h) {
+                        const u32 mid = (l + h) >> 1;
+                        if (s.vals[mid] < v) l = mid + 1; else h = mid;
+                    }
+                    lo = l;
+                    u32 hi = l;
+                    if (l < proc_end && s.vals[l] == v) {
+                        exact = true;
+                        do ++hi; while (hi < proc_end && s.vals[hi] == v);
+                    } else {
+                        while (lo > 0 && (s.vals[lo - 1] >> 24) == aa) --lo;
+                        while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
+                    }
                     ncand = hi - lo;
                 }
                 // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
@@ -566,7 +584,8 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 const u32 excl = incl - ncand;
                 const u32 q24 = (u32) qk.value & 0xFFFFFFu;
                 u32 *qmin = tb.qmin[warp];
-                qmin[lane] = 255;
+                qmin[lane] = exact ? 0u : 255u;
+                const u32 lo_x = lo | (exact ? 0x80000000u : 0u);
                 __syncwarp();
                 const u32 rounds = (total + 31) / 32;
                 u32 pk0 = 255, pk1 = 255;           // pairs of rounds 0 and 1 are kept for the emit pass: dd | owner << 8 | j << 16
@@ -581,13 +600,16 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                     // lanes with ncand == 0 share their prefix with the next lane: the search lands on the LAST lane
                     // with excl <= p, which is the one that owns p (its range is non-empty) when p < total
                     const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
-                    const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo, owner);
+                    const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo_x, owner);
                     const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
                     u32 dd = 255, j = 0;
                     if (p < total) {
-                        j = o_lo + (p - o_excl);
-                        dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
-                        atomicMin(&qmin[owner], dd);
+                        j = (o_lo & 0x7FFFFFFFu) + (p - o_excl);
+                        dd = 0;
+                        if (!(o_lo >> 31)) {
+                            dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
+                            atomicMin(&qmin[owner], dd);
+                        }
                     }
                     const u32 pk = dd | (owner << 8) | (j << 16);
                     if (r == 0) pk0 = pk;
@@ -608,10 +630,13 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                             if (owner + st < 32 && e <= p) owner += st;
                         }
                         const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
-                        const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo, owner);
+                        const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo_x, owner);
                         const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
                         dd = 255; j = 0;
-                        if (p < total) { j = o_lo + (p - o_excl); dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]); }
+                        if (p < total) {
+                            j = (o_lo & 0x7FFFFFFFu) + (p - o_excl);
+                            dd = (o_lo >> 31) ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
+                        }
                     }
                     const u32 mind = qmin[owner];
                     const u32 maxh = mind * 2 < 7 ? mind * 2 : 7;
