@@ -113,6 +113,30 @@ int Taxonomy::rankIndex(const char *r) {
     return it == ranks.end() ? -1 : it->second;
 }
 
+std::string Taxonomy::lineage(int32_t t) const {
+    // ExtendedShortRanks (TaxonomyWrapper.h:9-26) through findShortRank2 (TaxonomyWrapper.cpp:423-429)
+    static const std::map<std::string, std::string> shortRanks = {
+        {"subspecies", "ss"}, {"species", "s"}, {"subgenus", "sg"}, {"genus", "g"}, {"subfamily", "sf"}, {"family", "f"},
+        {"suborder", "so"}, {"order", "o"}, {"subclass", "sc"}, {"class", "c"}, {"subphylum", "sp"}, {"phylum", "p"},
+        {"subkingdom", "sk"}, {"kingdom", "k"}, {"superkingdom", "d"}, {"domain", "d"}, {"realm", "r"}};
+    const TaxNodeRec *n = node(t);
+    if (!n) return "-";
+    std::vector<const TaxNodeRec *> chain;
+    do {
+        chain.push_back(n);
+        n = node(n->parentTaxId);
+    } while (n && n->parentTaxId != n->taxId && chain.size() < 1000);
+    std::string out;
+    for (size_t i = chain.size(); i-- > 0;) {
+        const auto it = shortRanks.find(str(chain[i]->rankIdx));
+        out += it == shortRanks.end() ? "-" : it->second;
+        out += '_';
+        out += str(chain[i]->nameIdx);
+        if (i > 0) out += ';';
+    }
+    return out;
+}
+
 int32_t Taxonomy::atRank(int32_t t, const char *rank) const {
     if (t == 0 || !exists(t) || t == 1) return 0;
     const int want = rankIndex(rank);

@@ -38,6 +38,8 @@ public:
     int32_t node0TaxId() const { return nodes_.empty() ? 0 : nodes_[0].taxId; }
     // TaxonomyWrapper::getTaxIdAtRank (TaxonomyWrapper.cpp:479-498)
     int32_t atRank(int32_t t, const char *rank) const;
+    // TaxonomyWrapper::taxLineage2 (TaxonomyWrapper.cpp:431-454): "<short rank>_<name>" from below the root down to t
+    std::string lineage(int32_t t) const;
     static int rankIndex(const char *r);       // NcbiTaxonomy::findRankIndex (NcbiTaxonomy.h:52-80)
     // dense arrays for mb_load_taxonomy
     void denseParents(std::vector<int32_t> &parent, std::vector<int32_t> &speciesRankOf) const;

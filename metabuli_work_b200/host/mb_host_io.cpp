@@ -116,7 +116,7 @@ void Reporter::writeClassifications(const ReadBatch &batch, const mb_read_result
         if (r.is_classified) {
             fprintf(cls_, "1\t%s\t%d\t%d\t%s\t%s\t", batch.names[i].c_str(), tax_.original(r.classification), r.query_length, num,
                     tax_.rank(r.classification));
-            if (lineage_) fputs("-\t", cls_);    // taxLineage2 is a "next" row
+            if (lineage_) { fputs(tax_.lineage(r.classification).c_str(), cls_); fputc('\t', cls_); }   // Reporter.cpp:60-62
             for (int32_t k = r.taxcnt_begin; k < r.taxcnt_end; ++k) fprintf(cls_, "%d:%d ", tax_.original(tcId[k]), tcCnt[k]);
             fputc('\n', cls_);
         } else {

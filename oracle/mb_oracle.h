@@ -127,6 +127,8 @@ int64_t orc_score(const orc_db *db, const orc_params *p, const orc_match *sorted
                   int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap);
 
 /* ---- TSV writers (Reporter.cpp:38-83, 175-253) ---- */
+int orc_write_classifications_lineage(const orc_db *db, const char *path, const char *const *names, const orc_read_result *res,
+                                      uint32_t n_reads, const int32_t *taxcnt_id, const int32_t *taxcnt_n);
 int orc_write_classifications(const orc_db *db, const char *path, const char *const *names,
                               const orc_read_result *res, uint32_t n_reads,
                               const int32_t *taxcnt_id, const int32_t *taxcnt_n, int append);

@@ -81,6 +81,8 @@ def lib():
         L.orc_sort_matches.argtypes = [vp, sz, C.c_int]
         L.orc_score.restype = i64
         L.orc_score.argtypes = [vp, C.POINTER(Params), vp, sz, vp, u32, vp, vp, vp, sz]
+        L.orc_write_classifications_lineage.restype = C.c_int
+        L.orc_write_classifications_lineage.argtypes = [vp, C.c_char_p, C.POINTER(C.c_char_p), vp, u32, vp, vp]
         L.orc_write_classifications.restype = C.c_int
         L.orc_write_classifications.argtypes = [vp, C.c_char_p, C.POINTER(C.c_char_p), vp, u32, vp, vp, C.c_int]
         L.orc_write_report.restype = C.c_int
@@ -210,6 +212,11 @@ def write_classifications(db, path, names, res, ids, cnt, append=False):
     arr = (C.c_char_p * len(names))(*[n.encode() if isinstance(n, str) else n for n in names])
     rc = lib().orc_write_classifications(db.h, path.encode(), arr, _ptr(res), len(names), _ptr(ids), _ptr(cnt), int(append))
     assert rc == 0
+
+
+def write_classifications_lineage(db, path, names, res, ids, cnt):
+    arr = (C.c_char_p * len(names))(*[n.encode() if isinstance(n, str) else n for n in names])
+    assert lib().orc_write_classifications_lineage(db.h, path.encode(), arr, _ptr(res), len(names), _ptr(ids), _ptr(cnt)) == 0
 
 
 def write_report(db, path, res):

@@ -216,6 +216,13 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
         b = open(os.path.join(out, "ref_" + f), "rb").read()
         assert a == b, f
         assert open(os.path.join(out, "jobh_" + f), "rb").read() == b, f
+    # --lineage 1: one more column (TaxonomyWrapper::taxLineage2)
+    subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
+                           out, "jobl1", "--lineage", "1"])
+    orc.write_classifications_lineage(db, os.path.join(out, "refl1_classifications.tsv"), names, res, ids, cnt)
+    got = open(os.path.join(out, "jobl1_classifications.tsv"), "rb").read()
+    assert got == open(os.path.join(out, "refl1_classifications.tsv"), "rb").read()
+    assert b"\ts_" in got or b";s_" in got            # a species-level lineage entry is present
     # long-read mode through the library entry point
     mb.classify_files(os.path.join(data, "long.fa"), None, golden.dbdir("sync_long"), out, "jobl", seq_mode=3)
     db2 = orc.Db(golden.dbdir("sync_long"))
