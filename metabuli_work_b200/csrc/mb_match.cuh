@@ -606,6 +606,8 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                     if (p < total) {
                         j = (o_lo & 0x7FFFFFFFu) + (p - o_excl);
                         dd = 0;
+                        // the candidate's info entry (make_match reads it in the emit pass) is asked for now
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(db.info + c.kidx + j));
                         if (!(o_lo >> 31)) {
                             dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
                             atomicMin(&qmin[owner], dd);
