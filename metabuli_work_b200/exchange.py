@@ -188,7 +188,9 @@ class ShardedClassifier:
         if self.fused:
             # every window start emits at most two k-mers (one per strand): 2 x bases bounds what one rank produces; an
             # owner receives about that much too unless the query k-mers pile up in one shard (slack 1.5)
-            n_bases = int(np.asarray(lens, dtype=np.int64).sum())
+            # mates are packed back to back (mb_stage_reads checks it), so the base count is the buffer length: no pass over
+            # lens (an oracle-backed test engine hands over its own batch object instead of a byte buffer)
+            n_bases = len(bases) if hasattr(bases, "__len__") else int(np.asarray(lens, dtype=np.int64).sum())
             need = self._agree(max(3 * n_bases, 1 << 16))
             if need > self.kmer_cap:
                 self._setup(need, max(self.match_cap, self._match_cap0 or need // 2))
