@@ -67,7 +67,7 @@ struct DbView {
 
 struct DbCursor { u64 word, vbefore, kidx; };
 
-constexpr int MT_STAGE = 64;               // matches staged per warp before a flush
+constexpr int MT_STAGE = 96;               // matches staged per warp before a flush
 
 struct MatchSmem {
     __align__(16) u16 w[DB_C + 16];
