@@ -160,6 +160,15 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
         in_eff = reinterpret_cast<const Rec *>(seg.base[r]) - seg.prefix[r];
         split = r + 1 < seg.n && tile_base + TILE > seg.prefix[r + 1];
     }
+    // tiles are taken in ticket order, so the tile that a CTA starting about one machine-full of CTAs later will load is
+    // known now: ask L2 for it (that CTA's load phase then waits on L2 instead of HBM)
+    if (!SEG) {
+        constexpr u64 AHEAD = 148ull * 2;
+        const u64 pf_base = (tile_base + AHEAD * TILE) * sizeof(Rec);
+        const u64 end_bytes = n * sizeof(Rec);
+        for (u64 o = pf_base + (u64) tid * 128; o < pf_base + (u64) TILE * sizeof(Rec) && o < end_bytes; o += (u64) RS_THREADS * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(in) + o));
+    }
     // all loads first (one independent batch per thread), digits afterwards
     if (SEG && split) {
 #pragma unroll
