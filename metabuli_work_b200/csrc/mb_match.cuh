@@ -527,9 +527,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
             // of the block's range is looked up (the range is not ordered below the sorted bits, and it also holds
             // queries of the neighbouring blocks: those find no group of their amino-acid part here).  The query
             // record of the NEXT ticket is requested before the current one is processed. ----
-            u32 base = 0;
-            if (lane == 0) base = atomicAdd(&s.qnext, 32u);
-            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            u32 base = warp * 32u;
             ulonglong2 v_next = make_ulonglong2(0, 0);
             if (qcur + base + lane < qend) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qcur + base + lane));
             while (qcur + base < qend) {
@@ -537,9 +535,7 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
                 qk.value = v_next.x; qk.qinfo = v_next.y;
                 const bool mine = qcur + base + lane < qend;
                 {
-                    u32 base_n = 0;
-                    if (lane == 0) base_n = atomicAdd(&s.qnext, 32u);
-                    base = __shfl_sync(0xFFFFFFFFu, base_n, 0);
+                    base += MT_THREADS;                  // tickets are dealt round robin: warp w takes 32-query slices w, w + 8, ...
                     if (qcur + base + lane < qend) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qcur + base + lane));
                 }
                 // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
