@@ -19,8 +19,8 @@
 //   1. loads its block plus a 512-word overhang with 16-byte loads into shared memory,
 //   2. decodes it cooperatively: each thread assembles the deltas ending in its 10 words, a block
 //      scan of (count, 64-bit delta sum) turns them into absolute values in shared memory,
-//   3. joins its query slice, one query per thread, warps running independently (32 queries per ticket,
-//      no block barrier): binary search of the AA part in the decoded block, ONE Hamming evaluation per candidate
+//   3. joins its query slice, one query per thread, warps running independently (32-query slices dealt
+//      round robin to the warps, no block barrier): binary search of the AA part in the decoded block, ONE Hamming evaluation per candidate
 //      through a two-codon table in shared memory,
 //   4. compacts matches per warp: records are staged in a per-warp shared-memory buffer and flushed with
 //      one atomic reservation and coalesced 8-byte stores when the buffer fills.
