@@ -42,3 +42,20 @@ def test_taxonomy_tables_follow_reference_rules():
         sp = tax.parent[st]
         assert tax.rank[sp] == "species" and tax.species_rank_of[st] == sp and tax.species_of[st] == sp
     assert tax.species_rank_of[tax.genus[0]] == tax.genus[0]      # above species: the taxon itself (TaxonomyWrapper.cpp:479-498)
+
+
+def test_fastq_text_of_the_bench_reads():
+    """bench.py's input-pipeline leg feeds mb_stage_fastq with this text: four lines per record, fixed-width names,
+    the mate's 150 bases, '+', 150 quality characters; parsed back it must give the packed reads."""
+    import bench
+    rng = np.random.default_rng(3)
+    n = 37
+    bases = rng.choice(np.frombuffer(b"ACGTN", dtype=np.uint8), size=n * 300).astype(np.uint8)
+    for mate in (0, 1):
+        text = bytes(bench.fastq_text(bases, n, mate))
+        lines = text.split(b"\n")
+        assert lines[-1] == b"" and len(lines) == 4 * n + 1
+        for i in range(n):
+            h, s, p, q = lines[4 * i:4 * i + 4]
+            assert h == b"@r%09d" % i and p == b"+" and q == b"I" * 150
+            assert s == bytes(bases[(2 * i + mate) * 150:(2 * i + mate + 1) * 150])
