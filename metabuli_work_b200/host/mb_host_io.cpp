@@ -263,8 +263,10 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     // Plain FASTQ goes to the GPU as raw text (mb_stage_fastq: lines, records and packing are found on the device; the host
     // only cuts the read names out at the spans it gets back).  FASTA, multi-line or gzip input takes the host reader.
     const bool deviceParse = !getenv("MB_HOST_PARSE") && looksLikePlainFastq(inputs[0]) && (!paired || looksLikePlainFastq(inputs[1]));
+    bool hostFallback = false;           // the first chunk was not four-line FASTQ after all: nothing was written yet
     if (deviceParse) {
         RawText f1, f2;
+        uint64_t batchesDone = 0;
         if (!f1.open(inputs[0])) { err = "cannot open " + inputs[0]; return 1; }
         if (paired && !f2.open(inputs[1])) { err = "cannot open " + inputs[1]; return 1; }
         // a chunk holds at least one batch of short reads (~330 text bytes per 150-base record) and never less than 64 MB
@@ -279,7 +281,13 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
             mb_fastq_index idx;
             int rc = mb_stage_fastq(db.ctx(), f1.buf.data(), f1.fill, paired ? f2.buf.data() : nullptr, paired ? f2.fill : 0,
                                     (uint32_t) std::min<size_t>(opt.batchReads, 0xFFFFFFFFu), last ? 1 : 0, &idx);
+            if (rc == MB_E_DATA && batchesDone == 0) {
+                std::cout << "Input is not plain four-line FASTQ (" << mb_last_error(db.ctx()) << "): using the host reader" << std::endl;
+                hostFallback = true;
+                break;
+            }
             if (rc != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
+            ++batchesDone;
             if (idx.n_reads == 0) {
                 if (last) break;
                 err = "FASTQ record longer than the read chunk (use a smaller --batch-reads only with short reads)";
@@ -312,13 +320,15 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
             f1.consume(idx.consumed1);
             if (paired) f2.consume(idx.consumed2);
         }
-        rep.closeClassifications();
-        if (!rep.writeReport(err)) return 1;
-        const auto t2 = clk::now();
-        std::cout << "Number of query k-mers: " << totalKmers << "\nThe number of matches: " << totalMatches << "\nNumber of sequences: "
-                  << rep.totalReads() << "\nGPU time: " << gpuMs / 1000.0 << " s\nTime for processing: "
-                  << std::chrono::duration<double>(t2 - t0).count() << " s" << std::endl;
-        return 0;
+        if (!hostFallback) {
+            rep.closeClassifications();
+            if (!rep.writeReport(err)) return 1;
+            const auto t2 = clk::now();
+            std::cout << "Number of query k-mers: " << totalKmers << "\nThe number of matches: " << totalMatches << "\nNumber of sequences: "
+                      << rep.totalReads() << "\nGPU time: " << gpuMs / 1000.0 << " s\nTime for processing: "
+                      << std::chrono::duration<double>(t2 - t0).count() << " s" << std::endl;
+            return 0;
+        }
     }
     FastxReader r1, r2;
     if (!r1.open(inputs[0], err)) return 1;

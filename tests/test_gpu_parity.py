@@ -216,6 +216,23 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
         b = open(os.path.join(out, "ref_" + f), "rb").read()
         assert a == b, f
         assert open(os.path.join(out, "jobh_" + f), "rb").read() == b, f
+    # multi-line FASTQ (sequence and quality wrapped at 70 columns, after a first record that looks plain) is not what the
+    # device parser takes: the command notices on the first chunk and falls back to the host reader
+    def wrap(path_in, path_out):
+        with open(path_in, "rb") as f, open(path_out, "wb") as o:
+            lines = f.read().split(b"\n")
+            for i in range(0, len(lines) - 1, 4):
+                h, sq, p, q = lines[i:i + 4]
+                if i == 0:                          # the first record stays on four lines: the sniffing sees plain FASTQ
+                    o.write(h + b"\n" + sq + b"\n" + p + b"\n" + q + b"\n")
+                    continue
+                o.write(h + b"\n" + b"\n".join(sq[k:k + 70] for k in range(0, len(sq), 70)) + b"\n" + p + b"\n" +
+                        b"\n".join(q[k:k + 70] for k in range(0, len(q), 70)) + b"\n")
+    wrap(os.path.join(data, "reads_1.fq"), os.path.join(out, "w1.fq"))
+    wrap(os.path.join(data, "reads_2.fq"), os.path.join(out, "w2.fq"))
+    log = subprocess.check_output([mb.CLI, "classify", os.path.join(out, "w1.fq"), os.path.join(out, "w2.fq"), golden.dbdir(case), out, "jobw"])
+    assert b"using the host reader" in log
+    assert open(os.path.join(out, "jobw_classifications.tsv"), "rb").read() == open(os.path.join(out, "ref_classifications.tsv"), "rb").read()
     # --lineage 1: one more column (TaxonomyWrapper::taxLineage2)
     subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
                            out, "jobl1", "--lineage", "1"])
