@@ -251,6 +251,20 @@ int mb_take_routed_kmers(mb_ctx *ctx, size_t *n);
 int mb_match_kmers_routed(mb_ctx *ctx, size_t *n_emitted);
 int mb_take_routed_matches(mb_ctx *ctx, size_t *n);
 
+/* ---- allocation-free query k-mer sort ----
+ * No counterpart in the reference: this entry point was added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same radix kernels and the same key as mb_sort_kmers (stable, ordered by the amino-acid bits mb_params.kmer_sort_bits
+ * selects), but on caller-owned device memory: d_kmers holds n mb_kmer records and receives the sorted records, d_tmp is a
+ * second buffer of n records (both on the context's GPU, 16-byte aligned, distinct).  The sort's scratch (digit histograms,
+ * per-tile look-back states, tile ticket: about 2 MB) is a file-scope `static __device__` array that every GPU loading the
+ * library holds until exit, so the call performs no cudaMalloc / cudaFree and calls no allocating routine.
+ * Limit: n <= MB_NOALLOC_MAX_KMERS, larger n returns MB_E_CAPACITY (use mb_sort_kmers).  stream: a cudaStream_t on the
+ * context's GPU (the call is then stream-ordered and does not synchronise), or NULL = the context's stream (the call returns
+ * after the sort has finished).  The scratch is shared by every call on a GPU: calls that overlap on the GPU race. */
+#define MB_NOALLOC_MAX_KMERS (1u << 22)
+int mb_sort_kmers_noalloc(mb_ctx *ctx, void *d_kmers, void *d_tmp, size_t n, void *stream);
+
 int mb_get_timings(mb_ctx *ctx, mb_phase_times *t);
 /* Per-kernel timing of the last batch: with profiling on, every kernel launch of the hot path is
  * bracketed by a CUDA event pair on the launching stream; the table sums them per kernel. */

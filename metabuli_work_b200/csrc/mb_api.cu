@@ -1555,3 +1555,109 @@ int mb_get_kernel_times(mb_ctx *ctx, mb_kernel_time *out, size_t cap, size_t *n)
 }
 
 } // extern "C"
+
+// ---- allocation-free query k-mer sort (mb_sort_kmers_noalloc) ---------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and the same key as
+// mb_sort_kmers, but the scratch of the one-sweep radix sort — the digit histograms of every pass, the per-tile look-back
+// states and the tile ticket — lives in the file-scope device array below instead of cudaMalloc'ed buffers.  Every GPU that
+// loads the library holds the array until exit.  All calls (of every context on a device) share it and it keeps the last
+// call's contents: the parts that must start at zero are cleared on the stream before use, and two calls that overlap
+// on one GPU race on it.
+namespace {
+constexpr int NA_ITEMS = 16;                                              // records per thread, as mb_sort_kmers
+constexpr u64 NA_TILE = (u64) RS_THREADS * NA_ITEMS;
+constexpr u64 NA_MAX_TILES = (MB_NOALLOC_MAX_KMERS + NA_TILE - 1) / NA_TILE;
+struct NoallocScratch {
+    u64 hist[RS_MAX_PASSES * RS_BINS];                                    // 32 KB
+    u64 tile_state[NA_MAX_TILES * RS_BINS];                               // 2 MB at 4 Mi records
+    u32 trivial[RS_MAX_PASSES];
+    u32 ticket;
+};
+}
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoallocScratch)];
+
+namespace {
+constexpr int NA_MAX_DEVICES = 64;
+struct NoallocDev { bool ready = false; NoallocScratch *scratch = nullptr; };
+NoallocDev g_noalloc_dev[NA_MAX_DEVICES];
+
+// once per device, with that device current: the DEVICE address of the array (in host code its name is only a host-side
+// stand-in) and the shared-memory opt-in of the pass kernels (function attributes are per device)
+int noalloc_setup(mb_ctx *ctx, NoallocScratch **out) {
+    const int dev = ctx->par.device;
+    if (dev < 0 || dev >= NA_MAX_DEVICES) return fail(ctx, MB_E_ARG, "device ordinal beyond the no-alloc set-up table");
+    NoallocDev &d = g_noalloc_dev[dev];
+    if (!d.ready) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        constexpr int smem = (int) radix_pass_smem<mb_kmer, NA_ITEMS>();
+        CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKey, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKeyPacked, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        d.scratch = reinterpret_cast<NoallocScratch *>(p);
+        d.ready = true;
+    }
+    *out = d.scratch;
+    return MB_OK;
+}
+
+template <typename Key>
+int noalloc_sort(mb_ctx *ctx, cudaStream_t st, NoallocScratch *sc, mb_kmer *a, mb_kmer *b, u64 n, const Key &key, int n_passes) {
+    const u64 tiles = (n + NA_TILE - 1) / NA_TILE;
+    constexpr size_t smem = radix_pass_smem<mb_kmer, NA_ITEMS>();
+    const SegIn seg = {};
+    CK(cudaMemsetAsync(sc->hist, 0, sizeof(u64) * RS_BINS * n_passes, st));
+    CK(cudaMemsetAsync(sc->trivial, 0, sizeof(sc->trivial), st));
+    const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+    k_radix_hist<mb_kmer, Key, false><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), st>>>(a, n, key, n_passes, sc->hist, seg);
+    CK(cudaGetLastError());
+    k_radix_scan_hist<<<n_passes, RS_BINS, 0, st>>>(sc->hist, n, sc->trivial);
+    CK(cudaGetLastError());
+    for (int p = 0; p < n_passes; ++p) {
+        CK(cudaMemsetAsync(sc->tile_state, 0, tiles * RS_BINS * sizeof(u64), st));
+        CK(cudaMemsetAsync(&sc->ticket, 0, sizeof(u32), st));
+        k_radix_pass<mb_kmer, Key, NA_ITEMS, false><<<(unsigned) tiles, RS_THREADS, smem, st>>>(a, b, n, key, p, sc->hist + (size_t) p * RS_BINS,
+                                                                                              sc->tile_state, &sc->ticket, 0, seg);
+        CK(cudaGetLastError());
+        std::swap(a, b);
+    }
+    // after an odd number of passes the result sits in the caller's tmp buffer (now `a`): bring it home (now `b`)
+    if (n_passes & 1) CK(cudaMemcpyAsync(b, a, n * sizeof(mb_kmer), cudaMemcpyDeviceToDevice, st));
+    return MB_OK;
+}
+} // namespace
+
+extern "C" int mb_sort_kmers_noalloc(mb_ctx *ctx, void *d_kmers, void *d_tmp, size_t n, void *stream) {
+    if (!ctx) return MB_E_ARG;
+    if (n > (size_t) MB_NOALLOC_MAX_KMERS) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "mb_sort_kmers_noalloc: %zu k-mers exceed the fixed scratch (MB_NOALLOC_MAX_KMERS = %u); use mb_sort_kmers",
+                 n, (unsigned) MB_NOALLOC_MAX_KMERS);
+        return fail(ctx, MB_E_CAPACITY, msg);
+    }
+    if (n == 0) return MB_OK;
+    if (!d_kmers || !d_tmp || d_kmers == d_tmp || ((uintptr_t) d_kmers & 15) || ((uintptr_t) d_tmp & 15))
+        return fail(ctx, MB_E_ARG, "mb_sort_kmers_noalloc: d_kmers / d_tmp must be two distinct 16-byte aligned device buffers of n records");
+    CK(cudaSetDevice(ctx->par.device));
+    NoallocScratch *sc = nullptr;
+    if (int rc = noalloc_setup(ctx, &sc)) return rc;
+    cudaStream_t st = stream ? (cudaStream_t) stream : ctx->stream;
+    // the key of mb_sort_kmers (kmer_sort_bits; the MB_KSORT_BITS knob is honoured there and here alike)
+    const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;
+    int bits = env_bits ? env_bits : ctx->par.kmer_sort_bits;
+    if (bits == 0 || (bits == 21 && ctx->par.kmer_format != 2)) bits = ctx->par.kmer_format == 2 ? 21 : 32;
+    if (bits != 21 && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 24, 32 or 40");
+    mb_kmer *a = reinterpret_cast<mb_kmer *>(d_kmers), *b = reinterpret_cast<mb_kmer *>(d_tmp);
+    int rc;
+    if (bits == 21) {
+        KmerKeyPacked pk;
+        rc = noalloc_sort(ctx, st, sc, a, b, (u64) n, pk, 3);
+    } else {
+        KmerKey key;
+        key.first_bit = 24 + (40 - bits);
+        rc = noalloc_sort(ctx, st, sc, a, b, (u64) n, key, bits / 8);
+    }
+    if (rc) return rc;
+    if (!stream) CK(cudaStreamSynchronize(st));
+    return MB_OK;
+}
