@@ -19,7 +19,8 @@ The workload is generated on the box from a seed (bench_workload.py), written to
 Metabuli database directory and opened by the product's C++ host; it is cached under --workdir so
 the reference arm and this arm, run back to back, use byte-identical inputs.
 
-The oracle (oracle/) is used here only as the timed CPU baseline and by --check.
+The oracle (oracle/) is used here only as the timed CPU baseline / reference arm (oracle/_ref/ref_harness) and as the checker:
+by default the GPU results of the benched reads are compared with the per-read results ref_harness wrote ("check" in the line).
 """
 import argparse
 import json
@@ -56,7 +57,9 @@ def parse_args():
     ap.add_argument("--workdir", default=os.environ.get("MB_BENCH_WORKDIR", "/tmp/mb_bench"))
     ap.add_argument("--cpu-pairs", type=int, default=0, help="read pairs of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--check", action="store_true", help="compare a sample of the GPU results with the oracle")
+    ap.add_argument("--check", action="store_true", help="(kept for old command lines: the reference check is on by default)")
+    ap.add_argument("--no-check", action="store_true", help="skip the comparison of the GPU results with ref_harness' results")
+    ap.add_argument("--check-port", action="store_true", help="also compare 20000 reads with the oracle port (liborc)")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="multi-GPU: producers write into peer memory (fused) or bucket + NCCL all-to-all (nccl)")
     ap.add_argument("--no-fastq", action="store_true", help="skip the input-pipeline leg (FASTQ text parsed on the device)")
@@ -90,7 +93,6 @@ def prepare_db(a, device, rank, world):
     dbdir = os.path.join(base, "db")
     marker = os.path.join(base, "db.done")
     if rank == 0 and not os.path.exists(marker):
-        import metabuli_work_b200.binding as mb
         os.makedirs(dbdir, exist_ok=True)
         t0 = time.time()
         tax = W.Taxonomy(*taxonomy_shape(a.genomes))
@@ -108,7 +110,7 @@ def prepare_db(a, device, rank, world):
         tax.use_internal_ids(ext2int)
         codes, starts = W.make_genomes(tax, a.seed, a.len_min, a.len_max, device)
         log(f"genomes: {len(starts) - 1}, {int(starts[-1]) / 1e9:.2f} Gbp in {time.time() - t0:.1f}s")
-        db = W.build_db(mb, tax, codes, starts, device, log=log)
+        db = W.build_db(tax, codes, starts, device, log=log)
         n_words = W.write_db_dir(dbdir, db, tax)
         meta = {"genomes": len(starts) - 1, "bases": int(starts[-1]), "db_kmers": int(len(db["values"])), "db_words": int(n_words),
                 "species": len(tax.species)}
@@ -213,16 +215,24 @@ def host_threads():
 
 
 def write_sample_fastq(a, bases, n_pairs):
-    import bench_workload as W
     base = os.path.join(a.workdir, workload_key(a))
     p1, p2 = os.path.join(base, f"sample{n_pairs}_1.fq"), os.path.join(base, f"sample{n_pairs}_2.fq")
     if not (os.path.exists(p1) and os.path.exists(p2)):
-        W.write_fastq_pair(p1, p2, bases, 150, n_pairs)
+        for mate, p in ((0, p1), (1, p2)):
+            tmp = p + f".tmp{os.getpid()}"
+            fastq_text(bases[:n_pairs * 300], n_pairs, mate).tofile(tmp)
+            os.replace(tmp, p)
     return p1, p2
 
 
+def ref_results_path(a, n_pairs):
+    return os.path.join(a.workdir, workload_key(a), f"ref_p{a.pairs}_n{n_pairs}.results.tsv")
+
+
 def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
-    """-> dict(kind, cores, reads_per_s, s_per_rep, phases, sample).  Times extract+sort+match+sort+score (no file parse)."""
+    """-> dict(kind, cores, reads_per_s, s_per_rep, phases, sample, results_tsv).  The reference's own classes
+    (oracle/_ref/ref_harness) on all host cores; times extract+sort+match+sort+score (no file parse); the per-read results of
+    the first repetition are kept as results_tsv (what the default-on check compares the GPU results with)."""
     threads = host_threads()
     harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
     base = os.path.join(a.workdir, workload_key(a))
@@ -233,7 +243,8 @@ def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
             with open(os.path.join(dbdir, f), "rb") as fh:
                 while fh.read(1 << 26):
                     pass
-        cmd = [harness, dbdir, os.path.join(base, "ref_out"), "2", str(threads), p1, p2, "--reps", str(reps + skip), "--skip-reps", str(skip)]
+        prefix = ref_results_path(a, n_pairs)[:-len(".results.tsv")]
+        cmd = [harness, dbdir, prefix, "2", str(threads), p1, p2, "--reps", str(reps + skip), "--skip-reps", str(skip)]
         t0 = time.time()
         out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
         if out.returncode != 0:
@@ -246,11 +257,13 @@ def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
             raise RuntimeError("ref_harness printed no JSON line")
         ph = {k: js[k] for k in ("extract_s", "sort_kmers_s", "match_s", "sort_matches_s", "score_s")}
         s_rep = sum(ph.values())
+        whole = js["reads"] == a.pairs
         return {"kind": "reference", "cores": threads, "reads_per_s": js["reads"] / s_rep, "s_per_rep": s_rep, "phases": ph,
-                "kmers": js["kmers"], "matches": js["matches"], "wall_s": time.time() - t0,
-                "sample": f"first {js['reads']} of the {a.pairs} read pairs of rank 0 vs the full DB; reference KmerMatcher/Taxonomer "
-                          f"classes (oracle/_ref/ref_harness), {threads} OpenMP threads, mean of {reps} reps after {skip} warm-up, "
-                          f"extract+sort+match+sort+score, file parsing excluded"}
+                "kmers": js["kmers"], "matches": js["matches"], "wall_s": time.time() - t0, "reads": js["reads"],
+                "results_tsv": prefix + ".results.tsv", "same_config": whole,
+                "sample": (f"all {js['reads']} read pairs of rank 0" if whole else f"first {js['reads']} of the {a.pairs} read pairs of rank 0") +
+                          f" vs the full DB; reference KmerMatcher/Taxonomer classes (oracle/_ref/ref_harness), {threads} OpenMP threads, "
+                          f"mean of {reps} reps after {skip} warm-up, extract+sort+match+sort+score, file parsing excluded"}
     # oracle port
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
@@ -266,13 +279,38 @@ def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
     db.close()
     s_rep = float(np.mean(times[skip:]))
     return {"kind": "port", "cores": threads, "reads_per_s": n_pairs / s_rep, "s_per_rep": s_rep, "phases": {}, "wall_s": sum(times),
+            "reads": n_pairs, "results_tsv": None, "same_config": n_pairs == a.pairs,
             "sample": f"first {n_pairs} of the {a.pairs} read pairs of rank 0 vs the full DB; oracle port (oracle/liborc.so), {threads} threads"}
+
+
+def check_against_reference(tsv, h_res, h_ids, h_cnt):
+    """Default-on parity record of the benched config: the per-read results ref_harness wrote (the reference's own
+    KmerMatcher / Taxonomer on the same DB directory and reads) vs the GPU results of the same reads — internal tax ID,
+    is_classified, query length, fp32 score BITS and the taxID:count list."""
+    n = bad = 0
+    first_bad = []
+    with open(tsv) as f:
+        for i, line in enumerate(f):
+            c = line.rstrip("\n").split("\t")
+            g = h_res[i]
+            tg = "".join(f"{t}:{k} " for t, k in zip(h_ids[g["taxcnt_begin"]:g["taxcnt_end"]].tolist(), h_cnt[g["taxcnt_begin"]:g["taxcnt_end"]].tolist()))
+            ok = (int(c[0]) == int(g["is_classified"]) and int(c[2]) == int(g["classification"]) and int(c[4]) == int(g["query_length"])
+                  and int(c[5], 16) == int(np.float32(g["score"]).view(np.uint32)) and c[6] == tg)
+            n += 1
+            if not ok:
+                bad += 1
+                if len(first_bad) < 5:
+                    first_bad.append(i)
+    out = {"against": "ref_harness", "reads": n, "mismatches": bad}
+    if first_bad:
+        out["first_mismatching_reads"] = first_bad
+    return out
 
 
 def cpu_sample_pairs(a):
     if a.cpu_pairs:
         return min(a.cpu_pairs, a.pairs)
-    return min(a.pairs, 100_000)
+    return min(a.pairs, 1_000_000)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -568,15 +606,26 @@ def run_b200(a):
         except Exception as ex:  # reported, never required
             out["input_pipeline"] = {"error": str(ex)}
 
-    if rank == 0 and a.check:
-        out["check"] = check_against_oracle(a, dbdir, bases, h_res, h_ids, h_cnt, clf, mb, world)
-    if rank == 0 and not a.no_cpu_baseline and world == 1:
-        try:
-            cb = run_cpu_reference(a, dbdir, bases, cpu_sample_pairs(a), reps=1, skip=0)
-            out["cpu_baseline"] = {"value": round(cb["reads_per_s"], 1), "unit": UNIT, "cores": cb["cores"], "kind": cb["kind"],
-                                   "sample": cb["sample"], "phases_s": cb["phases"], "wall_s": round(cb["wall_s"], 1)}
-        except Exception as ex:  # the baseline is reported, never required
-            out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_threads(), "kind": "reference", "sample": f"failed: {ex}"}
+    if rank == 0:
+        n_cpu = cpu_sample_pairs(a)
+        tsv = ref_results_path(a, n_cpu)
+        if not a.no_cpu_baseline and world == 1:
+            try:
+                cb = run_cpu_reference(a, dbdir, bases, n_cpu, reps=2, skip=1)
+                out["cpu_baseline"] = {"value": round(cb["reads_per_s"], 1), "unit": UNIT, "cores": cb["cores"], "kind": cb["kind"],
+                                       "sample": cb["sample"], "same_config": cb["same_config"], "phases_s": cb["phases"],
+                                       "wall_s": round(cb["wall_s"], 1)}
+            except Exception as ex:  # the baseline is reported, never required
+                out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_threads(), "kind": "reference", "sample": f"failed: {ex}"}
+        if not a.no_check:
+            try:
+                if not os.path.exists(tsv):          # N > 1, or the baseline leg was skipped: one untimed pass of the harness
+                    run_cpu_reference(a, dbdir, bases, n_cpu, reps=1, skip=0)
+                out["check"] = check_against_reference(tsv, h_res, h_ids, h_cnt)
+            except Exception as ex:
+                out["check"] = {"against": "ref_harness", "error": str(ex)}
+        if a.check_port:
+            out["check_port"] = check_against_oracle(a, dbdir, bases, h_res, h_ids, h_cnt, clf, mb, world)
     clf.close()
     barrier()
     if rank == 0:
@@ -612,6 +661,9 @@ def check_against_oracle(a, dbdir, bases, h_res, h_ids, h_cnt, clf, mb, world):
 # the reference arm: the reference's own CPU classes on the same workload, bounded sample per step
 # ---------------------------------------------------------------------------------------------------
 def run_reference(a):
+    """The reference's own CPU implementation of the path (oracle/_ref/ref_harness: its KmerMatcher, Taxonomer, scanners and
+    ips4o sort, all host cores) on this arm's config.  Nothing of metabuli_work_b200 is imported here: the workload
+    generator is plain torch (bench_workload.py)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -635,9 +687,10 @@ def run_reference(a):
         "config": {"workload": f"configs[1]: {a.pairs} synthetic 2x150 read pairs per GPU vs {meta['genomes']}-genome synthetic syncmer DB "
                                f"({meta['db_kmers']} k-mers, {meta['species']} species), seq-mode 2, s=5",
                    "pairs_per_gpu": a.pairs, "db_kmers": meta["db_kmers"], "db_words": meta["db_words"], "genomes": meta["genomes"],
-                   "step": f"one pass of the reference hot path over a bounded sample of {n} read pairs (whole DB scanned)", "seed": a.seed},
+                   "step": f"one pass of the reference hot path over {cb['reads']} read pairs (whole DB scanned)",
+                   "same_config": cb["same_config"], "seed": a.seed},
         "cpu_baseline": {"value": round(value, 1), "unit": UNIT, "cores": cb["cores"], "kind": cb["kind"], "sample": cb["sample"],
-                         "phases_s": cb["phases"]},
+                         "same_config": cb["same_config"], "phases_s": cb["phases"]},
         "e2e": {"value": round(value, 1), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

@@ -3,7 +3,7 @@
 
 Everything is generated on the GPU box at run time from a seed (there is no network and nothing this
 large can travel): a 7-rank taxonomy, 10 000 genomes of 200-500 kb that diverge along it, the database
-(pseudo-genes -> syncmer metamers through the library's own extraction kernel -> (value, species)
+(pseudo-genes -> syncmer metamers, computed here with torch and independently of the library -> (value, species)
 de-duplication with LCA -> 15-bit delta stream + info, the on-disk format of IndexCreator.cpp:811-886),
 and Illumina-like read pairs (1 % substitutions, 2 % random pairs).  torch is used as plumbing for the
 random numbers, sorting and gathers of this SET-UP; the timed region only runs the library.
@@ -153,39 +153,103 @@ def _encode_deltas(values_sorted_u):
 FLIP = -(1 << 63)
 
 
-def build_db(mb, tax, codes, starts, device, genomes_per_chunk=400, block=1500, log=None):
-    """-> dict(values int64 tensor (uint64 bit patterns, unsigned-ascending), info int64 tensor).  K-mers come from the
-    library's extraction kernel run over the genomes as long reads; one (strand, frame) is kept per 1.5-kb
-    block, the density of a gene-finder driven build."""
-    ex = mb.RawContext(device=device.index or 0, kmer_format=2, syncmer=1, smer_len=5, seq_mode=3)
+def genetic_code_tables():
+    """codonF / codonR of the standard genetic code over ARNDCQEGHILKMFPSTWYVX with 3-bit codon ids, indexed by
+    b0 | b1 << 2 | b2 << 4 over base codes A0 C1 T2 G3: cell = aa | cid << 5 (GeneticCode.h:34-193; the reverse table is the
+    codon comp(b2) comp(b1) comp(b0), KmerScanner.h:94-98).  Built here from the TCAG table, independently of the library."""
+    alphabet = "ARNDCQEGHILKMFPSTWYVX"
+    tcag = "FFLLSSSSYYXXCCXWLLLLPPPPHHQQRRRRIIIMTTTTNNKKSSRRVVVVAAAADDEEGGGG"
+    t2c = [2, 1, 0, 3]
+    aa = np.zeros((4, 4, 4), dtype=np.int64)
+    cid = np.zeros((4, 4, 4), dtype=np.int64)
+    for a in range(4):
+        for b in range(4):
+            for c in range(4):
+                x, y, z = t2c[a], t2c[b], t2c[c]
+                aa[x, y, z] = alphabet.index(tcag[a * 16 + b * 4 + c])
+                cid[x, y, z] = z
+    cid[0, 3, 3], cid[0, 3, 0] = 4, 5          # Arg AGG, AGA
+    cid[2, 2, 3], cid[2, 2, 0] = 4, 5          # Leu TTG, TTA
+    cid[0, 3, 2], cid[0, 3, 1] = 6, 7          # Ser AGT, AGC
+    cid[2, 3, 0] = 5                           # stop TGA
+    f = np.zeros(64, dtype=np.int64)
+    r = np.zeros(64, dtype=np.int64)
+    for i in range(64):
+        b0, b1, b2 = i & 3, (i >> 2) & 3, (i >> 4) & 3
+        f[i] = aa[b0, b1, b2] | (cid[b0, b1, b2] << 5)
+        r0, r1, r2 = b2 ^ 2, b1 ^ 2, b0 ^ 2
+        r[i] = aa[r0, r1, r2] | (cid[r0, r1, r2] << 5)
+    return f, r
+
+
+def syncmer_metamers(codes, starts_rel, device, smer_len=5):
+    """Format-2 metamers (MetamerScanner::next, KmerScanner.h:82-117) of every 24-base window of the packed genomes `codes`
+    (uint8 codes on `device`) on both strands, filtered by the closed-syncmer rule of SyncmerScanner::next
+    (SyncmerScanner.h:36-102).  Pure torch (set-up plumbing); the library under test is not involved.
+    -> (value int64 [uint64 bit pattern], window start inside its genome int64, genome index int64, strand*3 + start % 3 int64)."""
+    n = codes.numel()
+    f_np, r_np = genetic_code_tables()
+    cf = torch.from_numpy(f_np).to(device)
+    cr = torch.from_numpy(r_np).to(device)
+    c = codes.to(torch.int64)
+    idx3 = c[:-2] | (c[1:-1] << 2) | (c[2:] << 4)              # codon starting at every base
+    del c
+    m = n - 23                                                  # window starts
+    st = torch.from_numpy(np.asarray(starts_rel, dtype=np.int64)).to(device)
+    p = torch.arange(m, device=device, dtype=torch.int64)
+    g = torch.searchsorted(st, p, right=True) - 1
+    # frame range of the reference (KmerExtractor.cpp:312-386, LocalUtil.h:45-59): a window of phase b = start % 3 must end
+    # inside [b, b + cov - 1], cov = L - 2 / L - 4 / L - 3 for L % 3 = 2 / 1 / 0
+    glen = st[g + 1] - st[g]
+    rem = glen % 3
+    cov = torch.where(rem == 2, glen - 2, torch.where(rem == 1, glen - 4, glen - 3))
+    rel = p - st[g]
+    inside = rel + 23 <= rel % 3 + cov - 1
+    p = rel
+    out = []
+    s = smer_len
+    last = 8 - s
+    mask = (1 << (5 * s)) - 1
+    for strand in (0, 1):
+        tab = (cr if strand else cf)[idx3]
+        aa = torch.zeros(m, dtype=torch.int64, device=device)
+        dna = torch.zeros(m, dtype=torch.int64, device=device)
+        for j in range(8):
+            cj = tab[3 * j:3 * j + m]
+            sh = j if strand else 7 - j                         # reverse strand: translation runs from the high end down
+            aa |= (cj & 31) << (5 * sh)
+            dna |= (cj >> 5) << (3 * sh)
+        del tab
+        v0 = (aa >> (5 * last)) & mask
+        vl = aa & mask
+        mid = torch.full_like(aa, 1 << 40)
+        for i in range(1, last):
+            mid = torch.minimum(mid, (aa >> (5 * (last - i))) & mask)
+        keep = inside & ((v0 <= torch.minimum(mid, vl)) | (vl < torch.minimum(mid, v0)))
+        del v0, vl, mid
+        value = (aa << 24) | dna
+        out.append((value[keep], p[keep], g[keep], p[keep] % 3 + 3 * strand))
+        del aa, dna, value, keep
+    return tuple(torch.cat([o[k] for o in out]) for k in range(4))
+
+
+def build_db(tax, codes, starts, device, genomes_per_chunk=200, block=1500, log=None):
+    """-> dict(values int64 tensor (uint64 bit patterns, unsigned-ascending), info int64 tensor).  K-mers are the syncmer
+    metamers of the genomes (syncmer_metamers above, torch only); one (strand, frame) is kept per 1.5-kb block, the density of
+    a gene-finder driven build."""
     n = len(starts) - 1
     vals, taxs = [], []
-    ascii_lut = torch.from_numpy(CODE2ASCII.copy()).to(device)
     t0 = time.time()
     for g0 in range(0, n, genomes_per_chunk):
         g1 = min(n, g0 + genomes_per_chunk)
         a, b = int(starts[g0]), int(starts[g1])
-        host = ascii_lut[codes[a:b].long()].cpu().numpy()
-        lens = np.zeros(2 * (g1 - g0), dtype=np.uint32)
-        lens[0::2] = (starts[g0 + 1:g1 + 1] - starts[g0:g1]).astype(np.uint32)
-        offs = np.zeros(2 * (g1 - g0), dtype=np.uint64)
-        offs[0::2] = (starts[g0:g1] - a).astype(np.uint64)
-        offs[1::2] = (starts[g0 + 1:g1 + 1] - a).astype(np.uint64)
-        ex.stage(host, offs, lens)
-        nk = ex.extract()
-        buf = torch.empty((nk, 2), dtype=torch.int64, device=device)
-        ex.export_kmers_device(buf.data_ptr(), nk)
-        q = buf[:, 1]
-        pos = q & 0xFFFFFFFF
-        seq = (q >> 32) & 0x1FFFFFFF
-        frame = (q >> 61) & 7
-        genome = seq - 1 + g0
+        value, pos, g_rel, frame = syncmer_metamers(codes[a:b], starts[g0:g1 + 1] - a, device)
+        genome = g_rel + g0
         chosen = ((genome * 7919 + (pos // block) * 104729) >> 3) % 6
         keep = frame == chosen
-        vals.append(buf[:, 0][keep].clone())
+        vals.append(value[keep].clone())
         taxs.append(genome[keep].clone())
-        del buf
-    ex.close()
+        del value, pos, g_rel, frame, genome, chosen, keep
     v = torch.cat(vals)
     g = torch.cat(taxs)
     del vals, taxs

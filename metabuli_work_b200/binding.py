@@ -151,6 +151,7 @@ _sig(_host, "mbh_original_taxid", i32, [vp, i32])
 _sig(_host, "mbh_rank", C.c_char_p, [vp, i32])
 _sig(_host, "mbh_db_kmers", u64, [vp])
 _sig(_host, "mbh_db_words", u64, [vp])
+_sig(_host, "mbh_write_outputs", C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, u32, C.POINTER(C.c_char_p), vp, vp, vp])
 _sig(_host, "mbh_classify_files", C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
                                             C.c_float, C.c_float, u64])
 
@@ -202,7 +203,8 @@ class Context:
 
     def set_params(self, **kw):
         p = self.params
-        for k, v in kw.items():
+        self._overrides = dict(getattr(self, "_overrides", {}), **kw)       # earlier overrides stay in force
+        for k, v in self._overrides.items():
             setattr(p, k, v)
         self._ck(_cuda.mb_set_params(self.ctx, C.byref(p)))
 
@@ -556,5 +558,17 @@ class RawContext(Context):
 def classify_files(reads1, reads2, dbdir, outdir, jobid, seq_mode=2, device=0, min_score=0.0, min_sp_score=0.0, batch_reads=0):
     rc = _host.mbh_classify_files(os.fsencode(reads1), os.fsencode(reads2 or ""), os.fsencode(dbdir), os.fsencode(outdir),
                                   jobid.encode(), seq_mode, device, min_score, min_sp_score, batch_reads)
+    if rc != 0:
+        raise MetabuliError(rc, _host.mbh_last_error().decode())
+
+
+def write_outputs(dbdir, outdir, jobid, names, res, ids, cnt, lineage=False, krona_prelude=None):
+    """The host Reporter alone (no GPU needed): classifications / report / krona files from per-read results."""
+    res = np.ascontiguousarray(res, dtype=RESULT_DT)
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+    arr = (C.c_char_p * len(names))(*[n.encode() if isinstance(n, str) else n for n in names])
+    rc = _host.mbh_write_outputs(os.fsencode(dbdir), os.fsencode(outdir), jobid.encode(), int(lineage),
+                                 os.fsencode(krona_prelude) if krona_prelude else None, len(names), arr, _ptr(res), _ptr(ids), _ptr(cnt))
     if rc != 0:
         raise MetabuliError(rc, _host.mbh_last_error().decode())

@@ -81,6 +81,7 @@ struct Options {                   // the classify flag set (src/commons/LocalPa
     int device = 0;                // --gpu (new): CUDA device ordinal
     size_t batchReads = 1u << 20;  // --batch-reads (new): reads per GPU batch
     std::string taxonomyPath;
+    std::string kronaPrelude;      // --krona-prelude (new): the static head of JOBID_krona.html (lib/mmseqs/data/resources/krona_prelude.html)
 };
 
 class Database {
@@ -135,7 +136,7 @@ private:
 // ---- output (Reporter, src/commons/Reporter.cpp:38-83,175-253) ----------------------------------------
 class Reporter {
 public:
-    Reporter(const Taxonomy &tax, const std::string &outDir, const std::string &jobId, bool lineage);
+    Reporter(const Taxonomy &tax, const std::string &outDir, const std::string &jobId, bool lineage, const std::string &kronaPrelude = "");
     bool openClassifications(std::string &err);
     void writeClassifications(const ReadBatch &batch, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt);
     void closeClassifications();
@@ -144,7 +145,7 @@ public:
     const std::unordered_map<int32_t, unsigned> &taxCounts() const { return taxCounts_; }
 private:
     const Taxonomy &tax_;
-    std::string clsPath_, reportPath_;
+    std::string clsPath_, reportPath_, kronaPath_, kronaPrelude_;
     bool lineage_;
     FILE *cls_ = nullptr;
     std::unordered_map<int32_t, unsigned> taxCounts_;

@@ -87,9 +87,11 @@ bool FastxReader::next(std::string &name, std::string &seq) {
 // ------------------------------------------------------------------------------------------------------
 // Reporter
 // ------------------------------------------------------------------------------------------------------
-Reporter::Reporter(const Taxonomy &tax, const std::string &outDir, const std::string &jobId, bool lineage)
+Reporter::Reporter(const Taxonomy &tax, const std::string &outDir, const std::string &jobId, bool lineage, const std::string &kronaPrelude)
     : tax_(tax), clsPath_(outDir + "/" + jobId + "_classifications.tsv"), reportPath_(outDir + "/" + jobId + "_report.tsv"),
-      lineage_(lineage) {}
+      kronaPath_(outDir + "/" + jobId + "_krona.html"), kronaPrelude_(kronaPrelude), lineage_(lineage) {
+    if (kronaPrelude_.empty() && getenv("METABULI_KRONA_PRELUDE")) kronaPrelude_ = getenv("METABULI_KRONA_PRELUDE");
+}
 
 bool Reporter::openClassifications(std::string &err) {
     cls_ = fopen(clsPath_.c_str(), "w");
@@ -152,6 +154,42 @@ void reportRec(FILE *fp, const Taxonomy &tax, const std::unordered_map<int32_t, 
         reportRec(fp, tax, cl, total, c, depth + 1);
     }
 }
+// escapeAttribute (lib/mmseqs/src/taxonomy/taxonomyreport.cpp:76-100)
+std::string xmlEscape(const char *s) {
+    std::string out;
+    for (; *s; ++s) {
+        switch (*s) {
+            case '&': out += "&amp;"; break;
+            case '"': out += "&quot;"; break;
+            case '\'': out += "&apos;"; break;
+            case '<': out += "&lt;"; break;
+            case '>': out += "&gt;"; break;
+            default: out += *s;
+        }
+    }
+    return out;
+}
+
+// Reporter::kronaReport (Reporter.cpp:146-173): nested <node> elements, children by clade count like the report
+void kronaRec(FILE *fp, const Taxonomy &tax, const std::unordered_map<int32_t, Clade> &cl, int32_t taxId) {
+    auto it = cl.find(taxId);
+    const unsigned cladeCount = it == cl.end() ? 0 : it->second.cladeCount;
+    if (taxId == 0) {
+        if (cladeCount > 0) fprintf(fp, "<node name=\"unclassified\"><magnitude><val>%d</val></magnitude></node>", cladeCount);
+        kronaRec(fp, tax, cl, 1);
+        return;
+    }
+    if (cladeCount == 0) return;
+    fprintf(fp, "<node name=\"%s\"><magnitude><val>%d</val></magnitude>", xmlEscape(tax.name(taxId)).c_str(), cladeCount);
+    std::vector<int32_t> children = it->second.children;
+    auto cnt = [&](int32_t t) { auto f = cl.find(t); return f == cl.end() ? 0u : f->second.cladeCount; };
+    std::sort(children.begin(), children.end(), [&](int a, int b) { return cnt(a) > cnt(b); });
+    for (int32_t c : children) {
+        if (!cl.count(c)) break;
+        kronaRec(fp, tax, cl, c);
+    }
+    fputs("</node>", fp);
+}
 } // namespace
 
 // Reporter::writeReportFile (Reporter.cpp:175-220) over NcbiTaxonomy::getCladeCounts (NcbiTaxonomy.cpp:520-545)
@@ -185,6 +223,27 @@ bool Reporter::writeReport(std::string &err) {
     fprintf(fp, "#clade_proportion\tclade_count\ttaxon_count\trank\ttaxID\tname\n");
     reportRec(fp, tax_, cl, (unsigned long) total_, 0, 0);
     fclose(fp);
+    // JOBID_krona.html (Reporter.cpp:196-219): static prelude + the clade tree.  The prelude is a 224-KB third-party
+    // resource that the reference embeds at build time; here it is read from --krona-prelude / METABULI_KRONA_PRELUDE.
+    // Without it the chart data is still written (the node tree), and the file says what is missing.
+    FILE *kf = fopen(kronaPath_.c_str(), "w");
+    if (!kf) { err = "cannot write " + kronaPath_; return false; }
+    bool havePrelude = false;
+    if (!kronaPrelude_.empty()) {
+        if (FILE *pf = fopen(kronaPrelude_.c_str(), "rb")) {
+            char buf[1 << 16];
+            size_t n;
+            while ((n = fread(buf, 1, sizeof(buf), pf)) > 0) fwrite(buf, 1, n, kf);
+            fclose(pf);
+            havePrelude = true;
+        }
+    }
+    if (!havePrelude)
+        fputs("<!-- krona prelude not supplied: pass --krona-prelude <reference>/lib/mmseqs/data/resources/krona_prelude.html -->\n", kf);
+    fprintf(kf, "<node name=\"all\"><magnitude><val>%zu</val></magnitude>", (size_t) total_);
+    kronaRec(kf, tax_, cl, 0);
+    fputs("</node></krona></div></body></html>", kf);
+    fclose(kf);
     return true;
 }
 
@@ -252,7 +311,7 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     const auto t1 = clk::now();
     std::cout << "DB resident on GPU " << opt.device << ": " << db.numKmers() << " k-mers, " << db.numWords() * 2 + db.numKmers() * 4
               << " bytes (" << std::chrono::duration<double>(t1 - t0).count() << " s)" << std::endl;
-    Reporter rep(db.taxonomy(), outDir, jobId, opt.printLineage != 0);
+    Reporter rep(db.taxonomy(), outDir, jobId, opt.printLineage != 0, opt.kronaPrelude);
     if (!rep.openClassifications(err)) return 1;
     const bool paired = opt.seqMode == 2;
     ReadBatch batch;
@@ -415,6 +474,21 @@ int mbh_classify_files(const char *reads1, const char *reads2, const char *dbdir
     in.push_back(reads1);
     if (reads2 && *reads2) in.push_back(reads2);
     return mbh::runClassify(in, dbdir, outdir, jobid, opt, g_err);
+}
+
+// The output writers alone (no GPU): per-read results in, JOBID_classifications.tsv / JOBID_report.tsv / JOBID_krona.html out,
+// exactly as runClassify writes them.  Lets the CPU test-suite compare the writers with the reference Reporter's files.
+int mbh_write_outputs(const char *dbdir, const char *outdir, const char *jobid, int lineage, const char *krona_prelude, uint32_t n_reads,
+                      const char *const *names, const mb_read_result *res, const int32_t *tc_id, const int32_t *tc_cnt) {
+    mbh::Taxonomy tax;
+    if (!tax.load(std::string(dbdir) + "/taxonomyDB", g_err)) return 1;
+    mbh::Reporter rep(tax, outdir, jobid, lineage != 0, krona_prelude ? krona_prelude : "");
+    if (!rep.openClassifications(g_err)) return 1;
+    mbh::ReadBatch batch;
+    batch.names.assign(names, names + n_reads);
+    rep.writeClassifications(batch, res, tc_id, tc_cnt);
+    rep.closeClassifications();
+    return rep.writeReport(g_err) ? 0 : 1;
 }
 
 } // extern "C"

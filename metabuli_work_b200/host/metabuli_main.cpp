@@ -4,7 +4,7 @@
 // src/commons/LocalParameters.cpp:718-740):
 //   metabuli classify [--seq-mode 1|3] <fastx> <DBDIR> <OUTDIR> <JOBID> [flags]
 //   metabuli classify  --seq-mode 2    <fastx1> <fastx2> <DBDIR> <OUTDIR> <JOBID> [flags]
-// and writes OUTDIR/JOBID_classifications.tsv and OUTDIR/JOBID_report.tsv.
+// and writes OUTDIR/JOBID_classifications.tsv, OUTDIR/JOBID_report.tsv and OUTDIR/JOBID_krona.html.
 #include "mb_host.h"
 
 #include <sys/stat.h>
@@ -22,7 +22,8 @@ static int usage() {
                  "         --hamming-margin N --taxonomy-path DIR --mask 0|1 --mask-prob F --max-ram N --match-per-kmer N\n"
                  "         --accession-level 0|1 --lineage 0|1 --validate-input 0|1 --validate-db 0|1 --syncmer 0|1\n"
                  "         --smer-len N --kmer-format 1|2 --print-log 0|1 --reduced-aa 0|1 --em 0|1\n"
-                 "         --gpu N (CUDA device) --batch-reads N (reads per GPU batch)\n";
+                 "         --gpu N (CUDA device) --batch-reads N (reads per GPU batch)\n"
+                 "         --krona-prelude FILE (static head of JOBID_krona.html: the reference's krona_prelude.html)\n";
     return 1;
 }
 
@@ -58,6 +59,7 @@ int main(int argc, char **argv) {
         else if (a == "--print-log") opt.printLog = atoi(v);
         else if (a == "--reduced-aa") opt.reducedAA = atoi(v);
         else if (a == "--em") opt.em = atoi(v);
+        else if (a == "--krona-prelude") opt.kronaPrelude = v;
         else if (a == "--gpu") opt.device = atoi(v);
         else if (a == "--batch-reads") opt.batchReads = (size_t) strtoull(v, nullptr, 10);
         else { std::cerr << "unknown option " << a << "\n"; return usage(); }

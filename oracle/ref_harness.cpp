@@ -11,19 +11,22 @@
  * The only restated piece is the ~30-line read loop of KmerExtractor (loadChunkOfReads /
  * processSequence / fillQueryKmerBuffer, KmerExtractor.cpp:312-386,442-494): KmerExtractor's
  * constructor needs MMseqs2 substitution matrices that exist only as cmake-generated headers.
- * That loop is validated by comparing this harness' per-read results with the TSV of the full
- * reference binary (tests/golden/make_golden.sh does it).
+ * (The full reference binary is not built here, so that loop is pinned only indirectly: the oracle port and the CUDA
+ * path, written from the reference text independently of this loop, produce the same k-mer multiset.)
  *
  * LocalParameters cannot be constructed without the MMseqs2 Parameters machinery (generated
  * code again), so a zeroed object is fabricated and only the fields the path reads are set.
  *
  * usage: ref_harness DBDIR OUTPREFIX SEQMODE THREADS READS1 [READS2] [--dump] [--reps N] [--skip-reps W]
- *                    [--max-reads N] [--min-score F] [--min-sp-score F]
+ *                    [--max-reads N] [--min-score F] [--min-sp-score F] [--smer-len S] [--report OUTDIR JOBID] [--lineage]
+ * --report: the reference's own Reporter (src/commons/Reporter.cpp:38-83,146-253) writes JOBID_classifications.tsv,
+ * JOBID_report.tsv and JOBID_krona.html into OUTDIR exactly as Classifier::startClassify does (Classifier.cpp:133-158).
  * (--skip-reps W: the first W of the N repetitions are warm-up and stay out of the reported means)
  * writes OUTPREFIX.results.tsv and, with --dump, OUTPREFIX.kmers.bin / OUTPREFIX.matches.bin;
  * prints one JSON line with per-phase wall times.
  */
 #include "Classifier.h"
+#include "Reporter.h"
 #include "KmerMatcher.h"
 #include "KmerScanner.h"
 #include "SyncmerScanner.h"
@@ -74,6 +77,8 @@ int main(int argc, char **argv) {
     int reps = 1, skipReps = 0;
     size_t maxReads = SIZE_MAX;
     float minScore = 0.f, minSpScore = 0.f;
+    int smerLen = 5, lineage = 0;
+    std::string reportDir, reportJob;
     for (; argi < argc; ++argi) {
         if (!strcmp(argv[argi], "--dump")) dump = true;
         else if (!strcmp(argv[argi], "--reps")) reps = atoi(argv[++argi]);
@@ -81,6 +86,9 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[argi], "--max-reads")) maxReads = strtoull(argv[++argi], nullptr, 10);
         else if (!strcmp(argv[argi], "--min-score")) minScore = (float) atof(argv[++argi]);
         else if (!strcmp(argv[argi], "--min-sp-score")) minSpScore = (float) atof(argv[++argi]);
+        else if (!strcmp(argv[argi], "--smer-len")) smerLen = atoi(argv[++argi]);
+        else if (!strcmp(argv[argi], "--lineage")) lineage = 1;
+        else if (!strcmp(argv[argi], "--report") && argi + 2 < argc) { reportDir = argv[argi + 1]; reportJob = argv[argi + 2]; argi += 2; }
     }
     if (skipReps >= reps) skipReps = reps - 1;
     omp_set_num_threads(threads);
@@ -104,7 +112,8 @@ int main(int argc, char **argv) {
     par.tieRatio = 0.95;
     par.printLog = 0;
     par.syncmer = 0;
-    par.smerLen = 5;
+    par.smerLen = smerLen;
+    par.printLineage = lineage;
     par.kmerFormat = 1;
     par.em = false;
     par.skipRedundancy = 0;
@@ -113,8 +122,8 @@ int main(int argc, char **argv) {
     par.filenames.push_back(reads1);
     if (seqMode == 2) par.filenames.push_back(reads2);
     par.filenames.push_back(dbDir);
-    par.filenames.push_back("/tmp");
-    par.filenames.push_back("harness");
+    par.filenames.push_back(reportDir.empty() ? "/tmp" : reportDir);
+    par.filenames.push_back(reportJob.empty() ? "harness" : reportJob);
 
     loadDbParameters(par, dbDir);                       /* common.cpp:88-133 */
     const int kmerFormat = par.kmerFormat;
@@ -287,6 +296,16 @@ int main(int argc, char **argv) {
                 fprintf(fr, "\n");
             }
             fclose(fr);
+            if (!reportDir.empty()) {
+                /* Classifier::startClassify's output calls (Classifier.cpp:133-158) with the counts of assignTaxonomy (:201-203) */
+                Reporter reporter(par, taxonomy);
+                reporter.openReadClassificationFile();
+                reporter.writeReadClassification(queryList);
+                reporter.closeReadClassificationFile();
+                std::unordered_map<TaxID, unsigned int> taxCounts;
+                for (size_t i = 0; i < nReads; ++i) ++taxCounts[queryList[i].classification];
+                reporter.writeReportFile((int) nReads, taxCounts, ReportType::Default);
+            }
         }
     }
     fflush(stdout);

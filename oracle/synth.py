@@ -60,7 +60,7 @@ def target_kmers(p, seq, block=1500, seed=0):
     return k["value"][keep]
 
 
-def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096, seed=7):
+def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096, seed=7, skip_redundancy=1):
     """indir: output of make_inputs.py. Returns number of DB k-mers."""
     os.makedirs(dbdir, exist_ok=True)
     subprocess.check_call([REF_MKDB, os.path.join(indir, "taxdump"), dbdir], stdout=subprocess.DEVNULL)
@@ -141,6 +141,10 @@ def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096,
     # final order (value, species, taxid): groups are already unique per (value, species)
     out_v = np.ascontiguousarray(out_v, dtype=np.uint64)
     out_t = np.ascontiguousarray(out_t, dtype=np.uint32)
+    if not skip_redundancy:
+        # old databases (Skip_redundancy 0) flag redundant k-mers in bit 31 of `info`; the matcher masks it off
+        # (KmerMatcher.cpp:204-205,381).  Every third entry is flagged here.
+        out_t[::3] |= np.uint32(1 << 31)
     rc = orc.lib().orc_write_db_files(dbdir.encode(), orc._ptr(out_v), orc._ptr(out_t), len(out_v), split_num, kmer_format)
     assert rc == 0
     with open(os.path.join(dbdir, "taxID_list"), "w") as f:
@@ -149,7 +153,8 @@ def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096,
     with open(os.path.join(dbdir, "db.parameters"), "w") as f:
         f.write("DB_name\tsynthetic\nCreation_date\t2026-01-01\n")
         f.write("Metabuli commit used to create the DB\tsynthetic\n")
-        f.write("Reduced_alphabet\t0\nAccession_level\t0\nMask_mode\t0\nMask_prob\t0.900000\nSkip_redundancy\t1\n")
+        f.write("Reduced_alphabet\t0\nAccession_level\t0\nMask_mode\t0\nMask_prob\t0.900000\n")
+        f.write(f"Skip_redundancy\t{1 if skip_redundancy else 0}\n")
         f.write(f"Syncmer\t{syncmer}\n")
         if syncmer:
             f.write(f"Syncmer_len\t{smer_len}\n")

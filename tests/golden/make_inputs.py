@@ -1,8 +1,8 @@
 #!/usr/bin/env python3
 """Seeded synthetic inputs for the golden fixtures (genomes, NCBI-style taxdump, reads).
 
-Used only by tests/golden/make_golden.sh, which feeds them to the REFERENCE `metabuli`
-binary (build + classify) and to oracle/_ref/ref_harness.  Nothing here is product code.
+Used only by tests/golden/make_golden.py / make_golden2.py, which build databases from them (oracle/synth.py) and feed
+both to oracle/_ref/ref_harness (the reference's own classes).  Nothing here is product code.
 
 Layout written under <outdir>:
   genomes/ACC_xxx.fna, fasta.list, acc2taxid.tsv, taxdump/{nodes,names,merged}.dmp,
@@ -50,6 +50,9 @@ def main():
     ap.add_argument("--genome-len", type=int, default=100_000)
     ap.add_argument("--pairs", type=int, default=2000)
     ap.add_argument("--long-reads", type=int, default=40)
+    ap.add_argument("--euk-families", type=int, default=0,
+                    help="the last N families hang under a second superkingdom named Eukaryota (Taxonomer.cpp:497-500: "
+                         "minConsCntEuk applies to their species); does not change the random stream")
     args = ap.parse_args()
     rng = np.random.default_rng(args.seed)
     out = args.outdir
@@ -59,6 +62,9 @@ def main():
     # ---- taxonomy: root(1) > Bacteria(2, superkingdom) > phylum(3) > class(4) > order(5) > families...
     nodes = [(1, 1, "no rank", "root"), (2, 1, "superkingdom", "Bacteria"), (3, 2, "phylum", "Synthphyla"),
              (4, 3, "class", "Synthclassia"), (5, 4, "order", "Synthorderales")]
+    if args.euk_families:
+        nodes += [(6, 1, "superkingdom", "Eukaryota"), (7, 6, "phylum", "Eukphyla"), (8, 7, "class", "Eukclassia"),
+                  (9, 8, "order", "Eukorderales")]
     next_id = [10]
 
     def new_node(parent, rank, name):
@@ -70,7 +76,7 @@ def main():
     genomes = []  # (accession, taxid, seq)
     root_seq = rng.integers(0, 4, size=args.genome_len, dtype=np.int64)
     for f in range(args.families):
-        fam = new_node(5, "family", f"Famaceae{f}")
+        fam = new_node(9 if f >= args.families - args.euk_families else 5, "family", f"Famaceae{f}")
         fam_seq = mutate(rng, root_seq, 0.25)
         for g in range(args.genera):
             gen = new_node(fam, "genus", f"Genus{f}{g}")

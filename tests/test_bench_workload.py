@@ -59,3 +59,21 @@ def test_fastq_text_of_the_bench_reads():
             h, s, p, q = lines[4 * i:4 * i + 4]
             assert h == b"@r%09d" % i and p == b"+" and q == b"I" * 150
             assert s == bytes(bases[(2 * i + mate) * 150:(2 * i + mate + 1) * 150])
+
+
+@pytest.mark.parametrize("L", [3000, 3001, 3002])
+def test_torch_db_kmers_equal_oracle_extraction(L):
+    """bench_workload.syncmer_metamers (torch, builds the bench DB without the library under test) yields exactly the
+    k-mer values the reference-pinned oracle extracts from the same genome read as one long read (syncmer, format 2)."""
+    import bench_workload as W
+    rng = np.random.default_rng(L)
+    codes = rng.integers(0, 4, size=2 * L, dtype=np.uint8)
+    starts = np.array([0, L, 2 * L], dtype=np.int64)
+    value, pos, g, frame = W.syncmer_metamers(torch.from_numpy(codes), starts, torch.device("cpu"))
+    got = np.sort(value.numpy().view(np.uint64))
+    p = orc.default_params(kmer_format=2, syncmer=1, smer_len=5, seq_mode=3)
+    seqs = [W.CODE2ASCII[codes[:L]].tobytes(), W.CODE2ASCII[codes[L:]].tobytes()]
+    k = orc.extract(p, orc.Batch(seqs))
+    want = np.sort(k["value"])
+    assert len(got) == len(want) and np.array_equal(got, want)
+    assert int(g.max()) == 1 and int(frame.max()) == 5

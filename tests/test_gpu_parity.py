@@ -13,7 +13,9 @@ import orc
 
 pytestmark = pytest.mark.gpu
 
-CASES = ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single"]
+CASES = ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single",
+         # round 2 (tests/golden/make_golden2.py): Eukaryota branch, redundancy-bit mask, s = 4 / 6, legacy x long reads
+         "euk_paired", "euk_long", "redund_paired", "sync4_paired", "sync6_paired", "sync4_long", "legacy_long"]
 
 
 @pytest.fixture(scope="module")
@@ -46,9 +48,11 @@ def compare_results(res_gpu, ids_gpu, cnt_gpu, res_o, ids_o, cnt_o):
     return bad
 
 
-def run_all_stages(mb, dbdir, seq_mode, s1, s2, sort_bits=0, **kw):
+def run_all_stages(mb, dbdir, seq_mode, s1, s2, sort_bits=0, smer_len=0, **kw):
     """Returns dict of GPU intermediates and the oracle's, after asserting stage-by-stage parity."""
     db = orc.Db(dbdir)
+    if smer_len:
+        kw["smer_len"] = smer_len
     p = db.params(seq_mode=seq_mode, **kw)
     batch = orc.Batch(s1, s2)
     ok, om, ores, oids, ocnt = orc.classify(db, p, batch, threads=4)
@@ -56,6 +60,8 @@ def run_all_stages(mb, dbdir, seq_mode, s1, s2, sort_bits=0, **kw):
     try:
         if sort_bits:
             clf.set_params(kmer_sort_bits=sort_bits)
+        if smer_len:
+            clf.set_params(smer_len=smer_len)            # --smer-len (the DB's Syncmer_len line is never read: common.cpp:97-127)
         # K3 tap: decode of the resident stream
         v, _ = db.decode()
         assert np.array_equal(clf.decode_db(), v)
@@ -93,7 +99,7 @@ def run_all_stages(mb, dbdir, seq_mode, s1, s2, sort_bits=0, **kw):
 def test_golden_case_all_stages(golden, mb, case):
     meta = golden.cases[case]
     _, s1, s2 = golden.reads(case)
-    res, ids, cnt = run_all_stages(mb, golden.dbdir(case), meta["seq_mode"], s1, s2)
+    res, ids, cnt = run_all_stages(mb, golden.dbdir(case), meta["seq_mode"], s1, s2, smer_len=meta.get("smer_len", 0))
     # and directly against the reference-generated fixture
     assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
 
@@ -196,26 +202,29 @@ def test_medium_random(mb, tmp_path):
 
 
 def test_cli_files_byte_identical(golden, mb, tmp_path):
-    """`metabuli classify` outputs vs the oracle's writers (Reporter.cpp:38-83,175-253) byte for byte."""
+    """`metabuli classify` outputs vs the files the REFERENCE's own Reporter wrote for the same inputs
+    (tests/golden/data/reports, made by tests/golden/make_golden2.py from oracle/_ref/ref_harness --report;
+    Reporter.cpp:38-83,146-253), byte for byte: classifications, report, Krona chart, --lineage 1."""
     case = "plain_paired"
     data = helpers.DATA
+    rep = os.path.join(data, "reports")
     out = str(tmp_path)
-    subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
-                           out, "job", "--batch-reads", "150"])
-    db = orc.Db(golden.dbdir(case))
-    p = db.params(seq_mode=2)
-    names, s1, s2 = golden.reads(case)
-    k, m, res, ids, cnt = orc.classify(db, p, orc.Batch(s1, s2))
-    orc.write_classifications(db, os.path.join(out, "ref_classifications.tsv"), names, res, ids, cnt)
-    orc.write_report(db, os.path.join(out, "ref_report.tsv"), res)
+
+    def rd(p):
+        with open(p, "rb") as f:
+            return f.read()
+    prelude = os.path.join(out, "prelude.html")
+    with open(prelude, "wb") as f:
+        f.write(b"<html><!-- stand-in for krona_prelude.html -->\n")
+    r1, r2 = os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq")
+    subprocess.check_call([mb.CLI, "classify", r1, r2, golden.dbdir(case), out, "job", "--batch-reads", "150", "--krona-prelude", prelude])
     # (plain FASTQ is parsed on the GPU by default; MB_HOST_PARSE=1 forces the host reader that FASTA / gzip input takes)
-    subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
-                           out, "jobh", "--batch-reads", "150"], env=dict(os.environ, MB_HOST_PARSE="1"))
+    subprocess.check_call([mb.CLI, "classify", r1, r2, golden.dbdir(case), out, "jobh", "--batch-reads", "150"], env=dict(os.environ, MB_HOST_PARSE="1"))
     for f in ("classifications.tsv", "report.tsv"):
-        a = open(os.path.join(out, "job_" + f), "rb").read()
-        b = open(os.path.join(out, "ref_" + f), "rb").read()
-        assert a == b, f
-        assert open(os.path.join(out, "jobh_" + f), "rb").read() == b, f
+        b = rd(os.path.join(rep, case + "_" + f))
+        assert rd(os.path.join(out, "job_" + f)) == b, f
+        assert rd(os.path.join(out, "jobh_" + f)) == b, f
+    assert rd(os.path.join(out, "job_krona.html")) == rd(prelude) + rd(os.path.join(rep, case + "_krona_tail.html"))
     # multi-line FASTQ (sequence and quality wrapped at 70 columns, after a first record that looks plain) is not what the
     # device parser takes: the command notices on the first chunk and falls back to the host reader
     def wrap(path_in, path_out):
@@ -228,26 +237,29 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
                     continue
                 o.write(h + b"\n" + b"\n".join(sq[k:k + 70] for k in range(0, len(sq), 70)) + b"\n" + p + b"\n" +
                         b"\n".join(q[k:k + 70] for k in range(0, len(q), 70)) + b"\n")
-    wrap(os.path.join(data, "reads_1.fq"), os.path.join(out, "w1.fq"))
-    wrap(os.path.join(data, "reads_2.fq"), os.path.join(out, "w2.fq"))
+    wrap(r1, os.path.join(out, "w1.fq"))
+    wrap(r2, os.path.join(out, "w2.fq"))
     log = subprocess.check_output([mb.CLI, "classify", os.path.join(out, "w1.fq"), os.path.join(out, "w2.fq"), golden.dbdir(case), out, "jobw"])
     assert b"using the host reader" in log
-    assert open(os.path.join(out, "jobw_classifications.tsv"), "rb").read() == open(os.path.join(out, "ref_classifications.tsv"), "rb").read()
+    assert rd(os.path.join(out, "jobw_classifications.tsv")) == rd(os.path.join(rep, case + "_classifications.tsv"))
     # --lineage 1: one more column (TaxonomyWrapper::taxLineage2)
-    subprocess.check_call([mb.CLI, "classify", os.path.join(data, "reads_1.fq"), os.path.join(data, "reads_2.fq"), golden.dbdir(case),
-                           out, "jobl1", "--lineage", "1"])
-    orc.write_classifications_lineage(db, os.path.join(out, "refl1_classifications.tsv"), names, res, ids, cnt)
-    got = open(os.path.join(out, "jobl1_classifications.tsv"), "rb").read()
-    assert got == open(os.path.join(out, "refl1_classifications.tsv"), "rb").read()
+    subprocess.check_call([mb.CLI, "classify", r1, r2, golden.dbdir(case), out, "jobl1", "--lineage", "1"])
+    got = rd(os.path.join(out, "jobl1_classifications.tsv"))
+    assert got == rd(os.path.join(rep, case + "_lineage_classifications.tsv"))
     assert b"\ts_" in got or b";s_" in got            # a species-level lineage entry is present
+    # the other databases / modes through the command line: Eukaryota taxonomy, redundancy bits, --smer-len, legacy x long reads
+    for c, extra in (("euk_paired", []), ("redund_paired", []), ("sync4_paired", ["--smer-len", "4"]), ("sync6_paired", ["--smer-len", "6"])):
+        subprocess.check_call([mb.CLI, "classify", r1, r2, golden.dbdir(c), out, c] + extra)
+        for f in ("classifications.tsv", "report.tsv"):
+            assert rd(os.path.join(out, c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, f)
+    for c in ("legacy_long", "euk_long"):
+        subprocess.check_call([mb.CLI, "classify", "--seq-mode", "3", os.path.join(data, "long.fa"), golden.dbdir(c), out, c])
+        for f in ("classifications.tsv", "report.tsv"):
+            assert rd(os.path.join(out, c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, f)
     # long-read mode through the library entry point
     mb.classify_files(os.path.join(data, "long.fa"), None, golden.dbdir("sync_long"), out, "jobl", seq_mode=3)
-    db2 = orc.Db(golden.dbdir("sync_long"))
-    p2 = db2.params(seq_mode=3)
-    names, s1, _ = golden.reads("sync_long")
-    k, m, res, ids, cnt = orc.classify(db2, p2, orc.Batch(s1, None))
-    orc.write_classifications(db2, os.path.join(out, "refl_classifications.tsv"), names, res, ids, cnt)
-    assert open(os.path.join(out, "jobl_classifications.tsv"), "rb").read() == open(os.path.join(out, "refl_classifications.tsv"), "rb").read()
+    assert rd(os.path.join(out, "jobl_classifications.tsv")) == rd(os.path.join(rep, "sync_long_classifications.tsv"))
+    assert rd(os.path.join(out, "jobl_report.tsv")) == rd(os.path.join(rep, "sync_long_report.tsv"))
 
 
 def test_sharded_db_matches_union(golden, mb):

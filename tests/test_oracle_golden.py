@@ -11,14 +11,16 @@ import pytest
 import helpers
 import orc
 
-CASES = ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single"]
+CASES = ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single",
+         # round 2 (tests/golden/make_golden2.py): Eukaryota branch, redundancy-bit mask, s = 4 / 6, legacy x long reads
+         "euk_paired", "euk_long", "redund_paired", "sync4_paired", "sync6_paired", "sync4_long", "legacy_long"]
 
 
 @pytest.mark.parametrize("case", CASES)
 def test_oracle_matches_reference(golden, case):
     meta = golden.cases[case]
     db = orc.Db(golden.dbdir(case))
-    p = db.params(seq_mode=meta["seq_mode"])
+    p = db.params(seq_mode=meta["seq_mode"], **({"smer_len": meta["smer_len"]} if "smer_len" in meta else {}))
     names, s1, s2 = golden.reads(case)
     assert len(names) == meta["n_reads"]
     b = orc.Batch(s1, s2)
