@@ -292,7 +292,7 @@ def shard_db(db, shard, n_shards):
         i = i + int(ch[0].item()) if len(ch) else n
         cuts.append(i)
     cuts.append(n)
-    bounds = np.array([int(v[c].item()) & 0xFFFFFFFFFFFFFFFF for c in cuts[1:-1]], dtype=np.uint64)
+    bounds = np.array([int(v[c].item()) & 0xFFFFFFFFFF000000 for c in cuts[1:-1]], dtype=np.uint64)   # amino-acid part only
     a, b = cuts[shard], cuts[shard + 1]
     words, _ = _encode_deltas(v[a:b])
     info = t[a:b].to(torch.int32).cpu().numpy().astype(np.uint32)

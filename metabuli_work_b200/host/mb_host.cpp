@@ -243,7 +243,10 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
             size_t start = (size_t) s.diffIdxOffset - 1;       // terminator word of ADkmer's delta
             while (start > 0 && !(w[start - 1] & 0x8000u)) --start;
             cutPoints.push_back({s.ADkmer, start, (size_t) s.diffIdxOffset, (size_t) s.infoIdxOffset - 1});
-            bounds_.push_back(s.ADkmer);
+            // A query is compared with EVERY DB k-mer of its amino-acid group, whatever its DNA part, and a split entry is
+            // the first DB k-mer of a group (IndexCreator.cpp:843-846): route on the amino-acid part only, so that a query of
+            // the boundary group whose DNA part is below ADkmer's still reaches the shard that holds the group.
+            bounds_.push_back(s.ADkmer & ~0xFFFFFFull);
         }
     }
     size_t wBegin = 0, wEnd = nWords, kBegin = 0, kEnd = nKmers;

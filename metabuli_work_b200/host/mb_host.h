@@ -102,7 +102,7 @@ private:
     mb_ctx *ctx_ = nullptr;
     Taxonomy tax_;
     mb_params par_;
-    std::vector<uint64_t> bounds_;     // first k-mer value of shards 1..n-1
+    std::vector<uint64_t> bounds_;     // amino-acid part (value with the 24 DNA bits cleared) of the first k-mer of shards 1..n-1
     size_t nKmers_ = 0, nWords_ = 0;
 };
 

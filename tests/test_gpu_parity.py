@@ -273,8 +273,28 @@ def test_sharded_db_matches_union(golden, mb):
     whole.extract()
     whole.sort_kmers()
     kmers = whole.kmers()
+    # queries INSIDE the boundary amino-acid groups whose DNA part is below / above the group's first DB k-mer: they are
+    # compared with the whole group (KmerMatcher.cpp:275-450), so they must be routed by their amino-acid part alone
+    probe = mb.Classifier(golden.dbdir(case), seq_mode=2, shard=1, n_shards=3)
+    b3 = probe.shard_bounds()
+    probe.close()
+    assert np.all(b3 & np.uint64(0xFFFFFF) == 0)
+    extra = np.zeros(4 * len(b3), dtype=kmers.dtype)
+    for i, bd in enumerate(b3):
+        for j, dna in enumerate((0, 1, 0x924924, 0xFFFFFF)):
+            extra[4 * i + j]["value"] = bd | np.uint64(dna)
+            extra[4 * i + j]["qinfo"] = (np.uint64(7 + i) << np.uint64(32)) | np.uint64(3 * j) | (np.uint64(j % 6) << np.uint64(61))
+    kmers = np.concatenate([kmers, extra])
+    whole.set_kmers(kmers)
+    whole.sort_kmers()
+    kmers = whole.kmers()
     whole.match()
     want = orc.sort_matches(as_orc_matches(whole.matches()))
+    db_o = orc.Db(golden.dbdir(case))
+    assert np.array_equal(want, orc.sort_matches(orc.match(db_o, db_o.params(seq_mode=2), orc.sort_kmers(kmers.view(orc.KMER_DT).copy()))))
+    db_o.close()
+    hit = np.isin(want["qinfo"], extra["qinfo"])
+    assert hit.any(), "the boundary-group probes must produce matches, or the case proves nothing"
     whole.close()
     parts = []
     total_k = 0
