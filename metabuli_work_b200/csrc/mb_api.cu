@@ -89,9 +89,12 @@ struct mb_ctx {
     std::string err;
     DevBuf tables;
     // database
-    DevBuf words, info, blocks, blk_back, blk_cnt, blk_kidx, blk_vbefore;
-    u64 n_words = 0, n_db_kmers = 0;
-    u32 n_blocks = 0;
+    DevBuf words, info, units, raw_kidx, raw_vbefore;
+    u64 n_words = 0, n_db_kmers = 0, n_raw = 0;
+    u32 n_units = 0;
+    SortT units_t{-1, 0};             // the T function the unit index was cut for (rebuilt when the sort key changes)
+    int match_ctas = 0;               // resident CTAs of k_match on this context's device (0 = not asked yet)
+    bool match_attr_set = false;
     // taxonomy
     DevBuf parent, depth, species_of, species_rank_of, tax_node;
     DevBuf fq_text[2], fq_tile_cnt, fq_tile_off, fq_lines[2], fq_src, fq_name_off, fq_name_len, fq_info, fq_sums, fq_sum_off;   // mb_stage_fastq
@@ -408,12 +411,54 @@ static DbView db_view(const mb_ctx *ctx, bool for_index) {
     return v;
 }
 
+// The T function the query sort will order by (mb_sort_kmers) for the context's current parameters.
+static SortT planned_sort_t(const mb_ctx *ctx) {
+    static const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;      // tuning knob
+    int bits = env_bits ? env_bits : ctx->par.kmer_sort_bits;
+    if (bits == 0 || (bits == 21 && ctx->par.kmer_format != 2)) bits = ctx->par.kmer_format == 2 ? 21 : 32;
+    SortT t;
+    t.mode = bits == 21 ? 1 : 0;
+    t.shift = bits == 21 ? 0 : 40 - bits;
+    return t;
+}
+
+// Cut the resident stream into units at the T-bucket starts of sort key `st` (mb_match.cuh): pass B over the raw blocks,
+// compaction of the owning blocks on the host (a load-time step over a few MB).
+static int build_units(mb_ctx *ctx, const SortT &st) {
+    const u64 n_raw = ctx->n_raw;
+    ctx->n_units = 0;
+    if (n_raw == 0) return MB_OK;
+    DevBuf raw_units;
+    CK(raw_units.ensure(n_raw * sizeof(Unit)));
+    const DbView v = db_view(ctx, true);
+    KL(-1, k_db_raw_own<<<(unsigned) ((n_raw + 7) / 8), 256, 0, ctx->stream>>>(v, n_raw, ctx->raw_kidx.as<u64>(), ctx->raw_vbefore.as<u64>(), st,
+                                                                          raw_units.as<Unit>()));
+    std::vector<Unit> ru(n_raw), units;
+    CK(cudaMemcpyAsync(ru.data(), raw_units.p, n_raw * sizeof(Unit), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    units.reserve(n_raw + 1);
+    for (u64 b = 0; b < n_raw; ++b)
+        if (ru[b].word != ~0ull) units.push_back(ru[b]);
+    if (units.empty() || units[0].word != 0 || units[0].kidx != 0) return fail(ctx, MB_E_DATA, "internal: the unit index does not start at the stream start");
+    if (units.size() > 0xFFFFFFF0ull) return fail(ctx, MB_E_ARG, "database shard too large for one context (unit index)");
+    Unit end;
+    end.word = ctx->n_words; end.vbefore = 0; end.kidx = ctx->n_db_kmers; end.t_lo = ~0ull;
+    units.push_back(end);
+    CK(ctx->units.ensure(units.size() * sizeof(Unit)));
+    CK(cudaMemcpyAsync(ctx->units.p, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_units = (u32) (units.size() - 1);
+    ctx->units_t = st;
+    return MB_OK;
+}
+
 int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint32_t *info, size_t n_kmers) {
     if (!ctx || (!diffIdx && n_words) || (!info && n_kmers)) return MB_E_ARG;
     CK(cudaSetDevice(ctx->par.device));
     ctx->n_words = 0;
     ctx->n_db_kmers = 0;
-    ctx->n_blocks = 0;
+    ctx->n_units = 0;
+    ctx->n_raw = 0;
     CK(ctx->words.ensure((n_words + DB_PAD) * sizeof(u16)));
     CK(ctx->info.ensure((n_kmers + 16) * sizeof(u32)));
     CK(cudaMemsetAsync(ctx->words.as<u16>() + n_words, 0, DB_PAD * sizeof(u16), ctx->stream));
@@ -421,45 +466,34 @@ int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint3
     CK(cudaMemcpyAsync(ctx->info.p, info, n_kmers * sizeof(u32), cudaMemcpyHostToDevice, ctx->stream));
     ctx->n_words = n_words;
     ctx->n_db_kmers = n_kmers;
-    const u32 nb = (u32) ((n_words + DB_W - 1) / DB_W);
-    ctx->n_blocks = nb;
-    if (nb == 0) { CK(cudaStreamSynchronize(ctx->stream)); return MB_OK; }
-    CK(ctx->blk_back.ensure(nb * sizeof(u32)));
-    CK(ctx->blk_cnt.ensure(nb * sizeof(u32)));
-    CK(ctx->blk_kidx.ensure(nb * sizeof(u64)));
-    CK(ctx->blk_vbefore.ensure(nb * sizeof(u64)));
-    CK(ctx->blocks.ensure(nb * sizeof(BlockIndex)));
-    DevBuf blk_sum;
-    CK(blk_sum.ensure(nb * sizeof(u64)));
+    const u64 n_raw = (n_words + UN_W - 1) / UN_W;
+    ctx->n_raw = n_raw;
+    if (n_raw == 0) { CK(cudaStreamSynchronize(ctx->stream)); return MB_OK; }
+    CK(ctx->raw_kidx.ensure(n_raw * sizeof(u64)));
+    CK(ctx->raw_vbefore.ensure(n_raw * sizeof(u64)));
+    DevBuf raw_cnt, raw_sum;
+    CK(raw_cnt.ensure(n_raw * sizeof(u32)));
+    CK(raw_sum.ensure(n_raw * sizeof(u64)));
     const DbView v = db_view(ctx, true);
-    KL(-1, k_db_block_summary<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_cnt.as<u32>(), blk_sum.as<u64>()));
-    // The scan over blocks is a load-time step on a few MB: done on the host.
-    std::vector<u32> cnt(nb);
-    std::vector<u64> sum(nb), kidx(nb), vbefore(nb);
-    CK(cudaMemcpyAsync(cnt.data(), ctx->blk_cnt.p, nb * sizeof(u32), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(sum.data(), blk_sum.p, nb * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    KL(-1, k_db_raw_summary<<<(unsigned) ((n_raw + 7) / 8), 256, 0, ctx->stream>>>(v, n_raw, raw_cnt.as<u32>(), raw_sum.as<u64>()));
+    // The scan over raw blocks is a load-time step on a few MB: done on the host.
+    std::vector<u32> cnt(n_raw);
+    std::vector<u64> sum(n_raw), kidx(n_raw), vbefore(n_raw);
+    CK(cudaMemcpyAsync(cnt.data(), raw_cnt.p, n_raw * sizeof(u32), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(sum.data(), raw_sum.p, n_raw * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    u64 k = 0, s = 0;
-    for (u32 b = 0; b < nb; ++b) { kidx[b] = k; vbefore[b] = s; k += cnt[b]; s += sum[b]; }
+    u64 k = 0, sv = 0;
+    for (u64 b = 0; b < n_raw; ++b) { kidx[b] = k; vbefore[b] = sv; k += cnt[b]; sv += sum[b]; }
     if (k != n_kmers) {
         char msg[256];
         snprintf(msg, sizeof(msg), "diffIdx holds %llu k-mers but info holds %llu entries", (unsigned long long) k, (unsigned long long) n_kmers);
-        ctx->n_words = 0; ctx->n_db_kmers = 0; ctx->n_blocks = 0;
+        ctx->n_words = 0; ctx->n_db_kmers = 0; ctx->n_raw = 0;
         return fail(ctx, MB_E_DATA, msg);
     }
-    CK(cudaMemcpyAsync(ctx->blk_kidx.p, kidx.data(), nb * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->blk_vbefore.p, vbefore.data(), nb * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
-    KL(-1, k_db_block_own<<<nb, MT_THREADS, 0, ctx->stream>>>(v, nb, ctx->blk_back.as<u32>(), ctx->blk_kidx.as<u64>(),
-                                                        ctx->blk_vbefore.as<u64>(), ctx->blocks.as<BlockIndex>()));
-    std::vector<BlockIndex> bi(nb);
-    CK(cudaMemcpyAsync(bi.data(), ctx->blocks.p, nb * sizeof(BlockIndex), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->raw_kidx.p, kidx.data(), n_raw * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->raw_vbefore.p, vbefore.data(), n_raw * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    u64 next_aa = ~0ull;                      // blocks that own nothing take the next owner's AA (empty query slice)
-    for (u32 b = nb; b-- > 0;) {
-        if (bi[b].owns) next_aa = bi[b].own_aa; else bi[b].own_aa = next_aa;
-    }
-    CK(cudaMemcpyAsync(ctx->blocks.p, bi.data(), nb * sizeof(BlockIndex), cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    if (int rc = build_units(ctx, planned_sort_t(ctx))) return rc;
     ctx->times.db_words = n_words;
     ctx->times.db_kmers = n_kmers;
     return MB_OK;
@@ -473,9 +507,10 @@ int mb_decode_db(mb_ctx *ctx, uint64_t *values_out, size_t cap, size_t *n_out) {
     if (ctx->n_db_kmers == 0) return MB_OK;
     DevBuf vals;
     CK(vals.ensure(ctx->n_db_kmers * sizeof(u64)));
-    KL(-1, k_db_decode<<<ctx->n_blocks, MT_THREADS, 0, ctx->stream>>>(db_view(ctx, true), ctx->n_blocks, ctx->blk_back.as<u32>(),
-                                                              ctx->blk_cnt.as<u32>(), ctx->blk_kidx.as<u64>(),
-                                                              ctx->blk_vbefore.as<u64>(), vals.as<u64>()));
+    const size_t smem = MT_WARPS * sizeof(WarpSmem);
+    CK(cudaFuncSetAttribute(k_db_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const unsigned grid = (unsigned) std::min<u64>(((u64) ctx->n_units + MT_WARPS - 1) / MT_WARPS, 4096);
+    KL(-1, k_db_decode<<<grid, MT_THREADS, smem, ctx->stream>>>(db_view(ctx, true), ctx->units.as<Unit>(), ctx->n_units, vals.as<u64>()));
     CK(cudaMemcpyAsync(values_out, vals.p, ctx->n_db_kmers * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
@@ -855,13 +890,10 @@ int mb_sort_kmers(mb_ctx *ctx) {
     // The join needs the queries of one DB block contiguous, not ordered (every query looks its group up in the decoded
     // block): ordering the leading `bits` of the 40 amino-acid bits takes bits/8 passes instead of 5, and for format 2
     // the re-coded 24-bit key (SortT mode 1, mb_common.cuh; kmer_sort_bits 21) resolves 5.6 residues in 3 passes.
-    static const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;      // tuning knob
-    int bits = env_bits ? env_bits : ctx->par.kmer_sort_bits;
-    if (bits == 0 || (bits == 21 && ctx->par.kmer_format != 2)) bits = ctx->par.kmer_format == 2 ? 21 : 32;
+    ctx->sort_t = planned_sort_t(ctx);
+    const bool packed = ctx->sort_t.mode == 1;
+    const int bits = packed ? 21 : 40 - ctx->sort_t.shift;
     if (bits != 21 && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 24, 32 or 40");
-    const bool packed = bits == 21;
-    ctx->sort_t.mode = packed ? 1 : 0;
-    ctx->sort_t.shift = packed ? 0 : 40 - bits;
     KmerKey key;
     key.first_bit = 24 + ctx->sort_t.shift;
     const int passes = packed ? 3 : bits / 8;
@@ -892,17 +924,19 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
     ctx->have_matches = ctx->matches_sorted = ctx->have_results = false;
     ctx->segments_valid = false;
     ctx->n_matches = 0;
-    if (ctx->n_blocks && ctx->n_kmers) {
-        const u32 nb = ctx->n_blocks;
-        CK(ctx->qstart.ensure(((size_t) nb + 1) * 2 * sizeof(u64)));
-        u64 *qstart = ctx->qstart.as<u64>(), *qend = qstart + nb + 1;
-        KL(KID_MATCH_PARTITION, k_match_partition<<<(nb + 255) / 256, 256, 0, ctx->stream>>>(ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(),
-                                                                   ctx->n_kmers, ctx->sort_t, qstart, qend));
-        static bool match_attr_set = false;
-        if (!match_attr_set) {
+    if (ctx->n_units && ctx->n_kmers) {
+        // the unit index follows the key the resident queries are ordered by
+        if (ctx->units_t.mode != ctx->sort_t.mode || ctx->units_t.shift != ctx->sort_t.shift)
+            if (int rc = build_units(ctx, ctx->sort_t)) return rc;
+        const u32 nu = ctx->n_units;
+        CK(ctx->qstart.ensure(((size_t) nu + 2) * sizeof(u64)));
+        u64 *qstart = ctx->qstart.as<u64>();
+        KL(KID_MATCH_PARTITION, k_match_partition<<<(nu + 1 + 255) / 256, 256, 0, ctx->stream>>>(ctx->units.as<Unit>(), nu, ctx->kmers_a.as<mb_kmer>(),
+                                                                   ctx->n_kmers, ctx->sort_t, qstart));
+        if (!ctx->match_attr_set) {
             CK(cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
             CK(cudaFuncSetAttribute(k_match<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) match_smem_bytes()));
-            match_attr_set = true;
+            ctx->match_attr_set = true;
         }
         size_t cap = std::max<size_t>(ctx->matches_a.cap / sizeof(mb_match), std::max<size_t>(1u << 16, ctx->n_kmers / 2));
         for (int attempt = 0; attempt < 3; ++attempt) {
@@ -917,19 +951,18 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
             mo.counter = &ctx->dcnt()->match_count; mo.error_flag = &ctx->dcnt()->error_flag; mo.route = nullptr;
             CK(cudaMemsetAsync(&ctx->dcnt()->match_ticket, 0, sizeof(u32), ctx->stream));
             if (routed) CK(cudaMemsetAsync(ctx->route.sent_m, 0, MB_MAX_RANKS * sizeof(unsigned long long), ctx->stream));
-            // persistent: as many CTAs as are resident at once (4 per SM: 55 KB shared memory, 64 registers)
-            static int match_ctas = 0;
-            if (!match_ctas) {
-                int per_sm = 0, sms = 148;
+            // persistent: as many CTAs as are resident at once (3 per SM: 66 KB of shared memory each); every warp draws units
+            if (!ctx->match_ctas) {
+                int per_sm = 0, sms = 0;
                 CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_match<false>, MT_THREADS, match_smem_bytes()));
                 CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
                 static const int env_ctas = getenv("MB_MATCH_CTAS_PER_SM") ? atoi(getenv("MB_MATCH_CTAS_PER_SM")) : 0;     // tuning knob
                 if (env_ctas > 0 && env_ctas < per_sm) per_sm = env_ctas;
-                match_ctas = std::max(1, per_sm) * sms;
+                ctx->match_ctas = std::max(1, per_sm) * std::max(1, sms);
             }
-            const unsigned grid = (unsigned) std::min<u64>(nb, (u64) match_ctas);
+            const unsigned grid = (unsigned) std::min<u64>(((u64) nu + MT_WARPS - 1) / MT_WARPS, (u64) ctx->match_ctas);
 #define MB_LAUNCH_MATCH(R, ROUTE) KL(KID_MATCH, (k_match<R><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>( \
-                db_view(ctx, false), ctx->blocks.as<BlockIndex>(), nb, ctx->kmers_a.as<mb_kmer>(), qstart, qend, mo, \
+                db_view(ctx, false), ctx->units.as<Unit>(), nu, ctx->kmers_a.as<mb_kmer>(), qstart, mo, \
                 ctx->tables.as<Tables>(), ctx->par.kmer_format, &ctx->dcnt()->match_ticket, ROUTE)))
             if (!routed) MB_LAUNCH_MATCH(false, nullptr);
             else MB_LAUNCH_MATCH(true, ctx->route_dev.as<Route>());

@@ -1,5 +1,5 @@
-// mb_match.cuh — K3+K4: block-parallel diffIdx decode feeding the amino-acid merge join with the DNA
-// Hamming filter and match compaction.
+// mb_match.cuh — K3+K4: unit-parallel diffIdx decode feeding the amino-acid join with the DNA Hamming filter and
+// match compaction.
 //
 // Replaces KmerMatcher::matchKmers (src/commons/KmerMatcher.cpp:123-481) with getNextTargetKmer
 // (KmerMatcher.h:282-297) and compareDna (KmerMatcher.cpp:1117-1146).
@@ -8,51 +8,56 @@
 // ALL DB k-mers whose amino-acid part (value >> 24) equals q's — except the very last k-mer of the
 // DB, which the `diffIdxPos != numOfDiffIdx` guards never offer (KmerMatcher.cpp:363-406) — and
 // every candidate whose codon-id Hamming sum is <= min(2*min_sum, 7) yields a Match.  The result
-// per query depends on nothing else, so the join parallelises over DB blocks.
+// per query depends on nothing else, so the join parallelises over pieces of the DB.
 //
-// B200 design.  The compressed stream stays in HBM (about 9.7 B per k-mer with `info`).  At load
-// time a block index is built: for every 2048-word block the decode cursor (word, value before,
-// k-mer ordinal) of the first amino-acid group that STARTS in the block, and that group's AA.  A
-// group is owned by the block it starts in.  Per batch, a partition kernel binary-searches the
-// sorted query list once per block (merge-path style: block b joins queries [qstart[b],
-// qstart[b+1])); blocks without queries never touch their words.  A CTA then
-//   1. loads its block plus a 512-word overhang with 16-byte loads into shared memory,
-//   2. decodes it cooperatively: each thread assembles the deltas ending in its 10 words, a block
-//      scan of (count, 64-bit delta sum) turns them into absolute values in shared memory,
-//   3. joins its query slice, one query per thread, warps running independently (32-query slices dealt
-//      round robin to the warps, no block barrier): binary search of the AA part in the decoded block, ONE Hamming evaluation per candidate
-//      through a two-codon table in shared memory,
-//   4. compacts matches per warp: records are staged in a per-warp shared-memory buffer and flushed with
-//      one atomic reservation and coalesced 8-byte stores when the buffer fills.
-// The kernel is persistent (one CTA per resident slot, DB blocks handed out by an atomic ticket), so the
-// tables are loaded into shared memory once per CTA and staged matches survive from block to block.  Tickets
-// are drawn one block ahead: while a CTA joins block b, one of its warps pulls the words, the info entries and
-// the query slice of its NEXT block into L2 (prefetch.global.L2), and the query loads of the ticket loop are
-// software-pipelined, so the join itself waits on L2, not on HBM.
-// Groups longer than the overhang are re-decoded from their own start; groups longer than a whole
-// chunk take a streaming two-pass path.  Capacity misses are counted, never written out of bounds;
-// the host grows the buffer and reruns (the reference's retry, Classifier.cpp:127-131).
+// B200 design (round 2: warp-autonomous units).  The compressed stream stays in HBM as it is on disk.  The query sort
+// orders a monotone function T of the amino-acid part (SortT, mb_common.cuh), so a T BUCKET (all k-mers with one T value)
+// is contiguous on both sides.  At load time the stream is cut into UNITS at T-bucket starts, one cut per 512-word raw
+// block (the first bucket start inside the block): a unit is a whole number of T buckets — hence of amino-acid groups —
+// of about 512 words / 240 k-mers, described by its decode cursor (first word, value before, k-mer ordinal) and its first
+// T value.  Per batch one binary search per unit (k_match_partition) finds where the unit's T range starts in the sorted
+// query array; the query slices of consecutive units are disjoint and exact, so no query is looked up twice.
+//
+// k_match is persistent and every WARP works on its own: it draws a unit ticket (one ahead), and for that unit
+//   1. waits for the unit's words, which ONE lane fetched into the warp's shared-memory buffer with a bulk asynchronous
+//      copy (cp.async.bulk + mbarrier) while the warp was still joining the previous unit (double buffer);
+//   2. decodes them: every lane assembles the deltas ending in its 20 words (two sweeps over registers loaded with five
+//      64-bit shared loads: count/sum, warp scan of (count, 64-bit sum), then absolute values), marks the amino-acid group
+//      heads in a bit mask;
+//   3. joins the unit's query slice 32 queries at a time: branch-free binary search of the query's amino-acid key in
+//      the decoded values (<= 9 steps), group end from the head bit mask, then ALL (query, candidate) pairs of the 32
+//      queries are spread evenly over the lanes (prefix sum of the group sizes), one Hamming evaluation per pair through a
+//      two-codon table in shared memory, per-query minimum by shared atomicMin, filter d <= min(2*min, 7);
+//   4. stages the surviving matches in the warp's buffer and flushes it with one atomic reservation and coalesced
+//      8-byte stores.
+// There is no block-wide barrier anywhere in the loop.  Units longer than the buffers (no bucket start for a while, or
+// many one-word deltas) are joined in several pieces, each ending on a group boundary; a single amino-acid group longer
+// than a piece takes a streaming two-pass path.  Capacity misses are counted, never written out of bounds; the host
+// grows the buffer and reruns (the reference's retry, Classifier.cpp:127-131).
 #pragma once
 #include "mb_common.cuh"
 
 namespace mb {
 
-constexpr int DB_W = 2048;                 // words per block
-constexpr int DB_E = 256;                  // overhang words
-constexpr int DB_C = DB_W + DB_E;          // words decoded per chunk
+constexpr int UN_W = 512;                  // raw block of the load-time index: at most one unit starts per raw block
 constexpr int MT_THREADS = 256;
-constexpr int DB_R = DB_C / MT_THREADS;    // words per thread (10: odd word stride, conflict-free)
-constexpr int DB_PAD = DB_C + 64;          // zero words the device stream is padded with
+constexpr int MT_WARPS = MT_THREADS / 32;
+constexpr int MT_BUF_W = 640;              // words of one word buffer (32 lanes x 20 words)
+constexpr int MT_R = MT_BUF_W / 32;        // words per lane
+constexpr int MT_CAP_W = MT_BUF_W - 8;     // words of one piece (the buffer starts at an 8-word boundary of the stream)
+constexpr int MT_CAP_K = 384;              // k-mers of one piece
+constexpr int MT_HB = MT_CAP_K / 32 + 1;   // head-bit words (one extra bit: the sentinel behind the last k-mer)
+constexpr int MT_STAGE = 64;               // matches staged per warp before a flush
+constexpr int DB_PAD = MT_BUF_W + 64;      // zero words the device stream is padded with
 
-static_assert(DB_C % MT_THREADS == 0, "chunk must divide among the threads");
+static_assert(MT_R * 2 % 8 == 0, "a lane's run must be whole 64-bit words");
 
-struct BlockIndex {      // per 2048-word block: cursor of the first AA group starting in it
-    u64 word;            // first word of that group's first k-mer
+// One unit of the load-time index (see above).  units[n_units] is a sentinel {n_words, last value, n_kmers, ~0}.
+struct Unit {
+    u64 word;            // first word of the unit's first k-mer
     u64 vbefore;         // value of the preceding k-mer (0 at the stream start)
-    u64 kidx;            // ordinal of that k-mer
-    u64 own_aa;          // its AA part; for a block that owns nothing: the next owning block's AA
-    u32 owns;            // 1 when a group starts in this block
-    u32 pad;
+    u64 kidx;            // ordinal of the unit's first k-mer
+    u64 t_lo;            // T of its first k-mer (sort_t)
 };
 
 struct DbView {
@@ -67,67 +72,96 @@ struct DbView {
 
 struct DbCursor { u64 word, vbefore, kidx; };
 
-constexpr int MT_STAGE = 96;               // matches staged per warp before a flush
-
-struct MatchSmem {
-    __align__(16) u16 w[DB_C + 16];
-    u64 vals[DB_C];
-    u16 wend[DB_C];
-    u64 scan_sum[MT_THREADS / 32];
-    u32 scan_cnt[MT_THREADS / 32];
-    u32 n;
-    int last_start;
-    int own_end;
-    u32 group_end;
-    u64 reserve_base;
-    u32 warp_tot[MT_THREADS / 32];
-    u32 qnext;                             // next 32-query ticket of the current chunk
-    u32 tick[2];                           // persistent loop: DB block tickets, fetched one block ahead
-    u64 qadv;
+// per-warp shared memory
+struct __align__(128) WarpSmem {
+    u16 w[2][MT_BUF_W];                    // word buffers (bulk-copy destinations), double buffered
+    u64 vals[MT_CAP_K];                    // decoded values of the current piece
+    u64 stage[MT_STAGE * 3];               // staged match records
+    u32 hbits[MT_HB + 3];                  // bit j: k-mer j starts an amino-acid group; bit n: sentinel
+    u32 qmin[32];                          // per query of the current 32-query slice: smallest distance in its group
+    u64 mbar[2];                           // mbarriers of the two word buffers
 };
 
-// the part of the shared memory that lives for the whole (persistent) kernel
+// the part of the shared memory that the warps share (read only after set-up)
 struct MatchTables {
     u8 lut2[4096];
     u8 lutp[4096];
-    u64 stage[MT_THREADS / 32][MT_STAGE * 3];
-    u32 fill[MT_THREADS / 32];
-    u32 qmin[MT_THREADS / 32][32];           // per query of the warp's ticket: smallest distance in its group
 };
 
-// Decode up to DB_C words starting at cursor c (which must sit on the first word of a k-mer).
-// Leaves values / terminator word offsets in shared memory, returns the number of k-mers decoded.
-__device__ __forceinline__ u32 decode_chunk(const DbView &db, const DbCursor &c, MatchSmem &s) {
-    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const u64 wbase = c.word & ~7ull;
-    const u32 pad = (u32) (c.word - wbase);
-    // 16-byte loads; the stream is zero padded so reads past n_words are harmless (no terminators)
-    const uint4 *src = reinterpret_cast<const uint4 *>(db.words + wbase);
-    uint4 *dst = reinterpret_cast<uint4 *>(s.w);
-    for (u32 i = tid; i < (DB_C + 16) / 8; i += MT_THREADS) {
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (wbase + (u64) i * 8 < db.n_words) v = __ldg(src + i);
-        dst[i] = v;
-    }
-    __syncthreads();
-    const u16 *w = s.w + pad;
-    const u32 l0 = tid * DB_R;
-    // words of an unfinished delta in front of this thread's run (at most 4 for a valid stream)
-    u32 st = l0;
-    while (st > 0 && l0 - st < 4 && !(w[st - 1] & 0x8000u)) --st;
+constexpr size_t match_smem_bytes() { return sizeof(MatchTables) + MT_WARPS * sizeof(WarpSmem); }
+
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// ---- mbarrier + bulk copy (sm_90+/sm_100: UBLKCP, SYNCS in SASS) --------------------------------------------------
+__device__ __forceinline__ u32 smem_u32(const void *p) { return (u32) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy of `bytes` (multiple of 16; both addresses 16-byte aligned), completion on `bar`
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, u32 bytes, u64 *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// One lane asks for the words of a piece that starts at stream word `word` and has `wl` words (<= MT_CAP_W): the copy
+// starts at the 8-word boundary below `word`.  Returns nothing; the warp later waits on the buffer's mbarrier.
+__device__ __forceinline__ void fetch_words(const DbView &db, WarpSmem &ws, int buf, u64 word, u32 wl) {
+    const u64 wbase = word & ~7ull;
+    const u32 pad = (u32) (word - wbase);
+    const u32 bytes = ((pad + wl + 7u) >> 3) << 4;
+    mbar_expect_tx(&ws.mbar[buf], bytes);
+    bulk_g2s(ws.w[buf], db.words + wbase, bytes, &ws.mbar[buf]);
+}
+
+// ---- warp-level decode of one piece -----------------------------------------------------------------------------
+// The piece's words lie in buf[pad, pad + wl) (buffer coordinates).  Decodes the deltas that END inside the piece
+// (getNextTargetKmer, KmerMatcher.h:282-297), leaves the first min(n_total, MT_CAP_K) absolute values in ws.vals and
+// the amino-acid group heads in ws.hbits (bit 0 is always set: a piece starts at a group start).  Returns n_total.
+// Warp-synchronous; every lane must call it.
+__device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pad, u32 wl, u64 vbefore) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 l0 = lane * MT_R, end = pad + wl;
+    // my 20 words in five 64-bit registers
+    u64 r[MT_R / 4];
+    const u64 *b64 = reinterpret_cast<const u64 *>(buf + l0);
+#pragma unroll
+    for (int i = 0; i < MT_R / 4; ++i) r[i] = b64[i];
+    if (lane < MT_HB + 3) ws.hbits[lane] = 0;
+    // words of an unfinished delta in front of my run (at most 4 for a valid stream), not before the piece start
     u64 carry = 0;
-    for (u32 k = st; k < l0; ++k) carry = (carry | w[k]) << 15;
-    // pass 1: count and sum the deltas terminating in my run (getNextTargetKmer, KmerMatcher.h:282-297)
+    if (l0 > pad && l0 < end) {
+        u32 st = l0;
+        while (st > pad && l0 - st < 4 && !(buf[st - 1] & 0x8000u)) --st;
+        for (u32 k = st; k < l0; ++k) carry = (carry | buf[k]) << 15;
+    }
+    // sweep 1: count and sum the deltas terminating in my run
     u32 cnt = 0;
     u64 sum = 0, diff = carry;
 #pragma unroll
-    for (int i = 0; i < DB_R; ++i) {
-        const u32 frag = w[l0 + i];
-        const bool in_range = c.word + l0 + i < db.n_words;
-        if ((frag & 0x8000u) && in_range) { diff |= (frag & 0x7FFFu); sum += diff; ++cnt; diff = 0; }
-        else diff = (diff | frag) << 15;
+    for (int i = 0; i < MT_R; ++i) {
+        const u32 frag = (u32) (r[i >> 2] >> (16 * (i & 3))) & 0xFFFFu;
+        const u32 idx = l0 + i;
+        const bool in = idx >= pad && idx < end;
+        if (in) {
+            if (frag & 0x8000u) { diff |= (frag & 0x7FFFu); sum += diff; ++cnt; diff = 0; }
+            else diff = (diff | frag) << 15;
+        }
     }
-    // block exclusive scan of (cnt, sum)
+    // warp inclusive scan of (cnt, sum)
     u32 icnt = cnt;
     u64 isum = sum;
 #pragma unroll
@@ -136,69 +170,77 @@ __device__ __forceinline__ u32 decode_chunk(const DbView &db, const DbCursor &c,
         const u64 ts = __shfl_up_sync(0xFFFFFFFFu, isum, d);
         if (lane >= (u32) d) { icnt += tc; isum += ts; }
     }
-    if (lane == 31) { s.scan_cnt[warp] = icnt; s.scan_sum[warp] = isum; }
-    __syncthreads();
-    u32 cbase = 0, ctot = 0;
-    u64 sbase = 0;
-#pragma unroll
-    for (int k = 0; k < MT_THREADS / 32; ++k) {
-        const u32 tc = s.scan_cnt[k];
-        const u64 ts = s.scan_sum[k];
-        if ((u32) k < warp) { cbase += tc; sbase += ts; }
-        ctot += tc;
-    }
-    u32 pos = cbase + icnt - cnt;
-    u64 run = c.vbefore + sbase + isum - sum;
-    // pass 2: absolute values
+    const u32 n_total = __shfl_sync(0xFFFFFFFFu, icnt, 31);
+    __syncwarp();                                        // hbits cleared
+    // sweep 2: absolute values and group heads
+    u32 pos = icnt - cnt;
+    const u32 pos0 = pos;
+    u64 run = vbefore + (isum - sum);
+    u32 heads = 0;                                       // bit k: my k-th k-mer is a head
     diff = carry;
 #pragma unroll
-    for (int i = 0; i < DB_R; ++i) {
-        const u32 frag = w[l0 + i];
-        const bool in_range = c.word + l0 + i < db.n_words;
-        if ((frag & 0x8000u) && in_range) {
-            diff |= (frag & 0x7FFFu);
-            run += diff;
-            s.vals[pos] = run;
-            s.wend[pos] = (u16) (l0 + i);
-            ++pos;
-            diff = 0;
-        } else diff = (diff | frag) << 15;
+    for (int i = 0; i < MT_R; ++i) {
+        const u32 frag = (u32) (r[i >> 2] >> (16 * (i & 3))) & 0xFFFFu;
+        const u32 idx = l0 + i;
+        const bool in = idx >= pad && idx < end;
+        if (in) {
+            if (frag & 0x8000u) {
+                diff |= (frag & 0x7FFFu);
+                const u64 nv = run + diff;
+                if (pos < (u32) MT_CAP_K) {
+                    ws.vals[pos] = nv;
+                    if (pos == 0 || ((nv ^ run) >> 24) != 0) heads |= 1u << (pos - pos0);
+                }
+                run = nv;
+                ++pos;
+                diff = 0;
+            } else diff = (diff | frag) << 15;
+        }
     }
-    // candidates stop at n_kmers_eff
-    u64 room = db.n_kmers_eff > c.kidx ? db.n_kmers_eff - c.kidx : 0;
-    if ((u64) ctot > room) ctot = (u32) room;
-    __syncthreads();
-    return ctot;
+    if (heads) {
+        const u32 wi = pos0 >> 5, sh = pos0 & 31;
+        atomicOr(&ws.hbits[wi], heads << sh);
+        if (sh && (heads >> (32 - sh))) atomicOr(&ws.hbits[wi + 1], heads >> (32 - sh));
+    }
+    __syncwarp();
+    return n_total;
 }
 
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-
-// One warp warms L2 with what DB block nb will touch: its words, its info entries and its query slice.  Also asks for
-// the index entries that some CTA will read `ahead` tickets from now.  Every address stays inside its allocation.
-__device__ __forceinline__ void prefetch_block(const DbView &db, const BlockIndex *__restrict__ blocks, u32 n_blocks,
-                                               const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
-                                               const u64 *__restrict__ qend_of, u32 nb, u32 ahead) {
+// index of the last group head in [0, n) (n >= 1; bit 0 is always a head).  Warp-uniform result.
+__device__ __forceinline__ u32 last_head_before(const WarpSmem &ws, u32 n) {
     const u32 lane = threadIdx.x & 31;
-    if (nb >= n_blocks) return;
-    if (lane == 0 && nb + ahead < n_blocks) { prefetch_l2(blocks + nb + ahead); prefetch_l2(qstart + nb + ahead); prefetch_l2(qend_of + nb + ahead); }
-    if (!blocks[nb].owns) return;
-    const u64 qs = qstart[nb], qe = qend_of[nb];
-    if (qs >= qe) return;
-    const u64 word = blocks[nb].word & ~7ull, kidx = blocks[nb].kidx;
-    u64 nk = DB_W / 2;
-    if (nb + 1 < n_blocks && blocks[nb + 1].owns && blocks[nb + 1].kidx > kidx) nk = blocks[nb + 1].kidx - kidx;
-    if (nk > (u64) DB_C) nk = DB_C;
-    if (kidx + nk > db.n_kmers_eff) nk = db.n_kmers_eff > kidx ? db.n_kmers_eff - kidx : 0;
-    const char *w = reinterpret_cast<const char *>(db.words + word);
-    u64 wbytes = (db.n_words + DB_PAD - word) * 2;
-    if (wbytes > (u64) (DB_C + 16) * 2) wbytes = (u64) (DB_C + 16) * 2;
-    for (u64 o = (u64) lane * 128; o < wbytes; o += 32 * 128) prefetch_l2(w + o);
-    const char *inf = reinterpret_cast<const char *>(db.info + kidx);
-    for (u64 o = (u64) lane * 128; o < nk * 4; o += 32 * 128) prefetch_l2(inf + o);
-    u64 qn = qe - qs;
-    if (qn > 8192) qn = 8192;
-    const char *qp = reinterpret_cast<const char *>(q + qs);
-    for (u64 o = (u64) lane * 128; o < qn * 16; o += 32 * 128) prefetch_l2(qp + o);
+    u32 m = 0;
+    if (lane < (u32) MT_HB) {
+        m = ws.hbits[lane];
+        const u32 lo = lane * 32;
+        if (lo >= n) m = 0;
+        else if (n - lo < 32) m &= (1u << (n - lo)) - 1u;
+    }
+    const u32 any = __ballot_sync(0xFFFFFFFFu, m != 0);
+    const int top = 31 - __clz((int) any);               // any != 0: bit 0 is set
+    const u32 mt = __shfl_sync(0xFFFFFFFFu, m, top);
+    return (u32) top * 32 + (31 - __clz((int) mt));
+}
+
+// buffer word index just behind the terminator of the piece's k-th k-mer (k >= 1), i.e. the first word of k-mer k.
+// Warp-uniform result; the piece's words lie in buf[pad, pad + wl).
+__device__ __forceinline__ u32 word_after_kmer(const u16 *buf, u32 pad, u32 wl, u32 k) {
+    const u32 lane = threadIdx.x & 31;
+    u32 seen = 0;
+    for (u32 base = pad; base < pad + wl; base += 32) {
+        const u32 idx = base + lane;
+        const bool term = idx < pad + wl && (buf[idx] & 0x8000u);
+        const u32 m = __ballot_sync(0xFFFFFFFFu, term);
+        const u32 c = (u32) __popc(m);
+        if (seen + c >= k) {
+            // the (k - seen)-th set bit of m
+            u32 mm = m;
+            for (u32 i = 1; i < k - seen; ++i) mm &= mm - 1;
+            return base + (u32) __ffs((int) mm);          // ffs is 1-based: index behind the terminator
+        }
+        seen += c;
+    }
+    return pad + wl;
 }
 
 struct MatchOut {
@@ -308,13 +350,12 @@ __device__ __forceinline__ void warp_flush(const MatchOut &mo, u64 *stage, u32 &
     __syncwarp();
 }
 
-// Warp-level emission: lane l adds `cnt` matches (entries [lo,hi) of s.vals whose distance is <= maxh; the
-// distances of the first 16 entries are cached 4 bits each in dpack).
+// Warp-level emission for the streaming path: lane l adds the entries of ws.vals[0, ge) whose distance to its query is
+// <= maxh (cnt of them).  kbase: ordinal of ws.vals[0].
 template <bool ROUTED>
-__device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, const MatchSmem &s, MatchTables &tb, const MatchOut &mo,
-                                          bool active, const mb_kmer &q, u32 lo, u32 hi, u32 maxh, u32 cnt, u64 dpack, int format,
-                                          u32 &fill) {
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__device__ __noinline__ void warp_emit_own(const DbView &db, u64 kbase, WarpSmem &ws, const MatchTables &tb, const MatchOut &mo, bool active,
+                                           const mb_kmer &q, u32 ge, u32 maxh, u32 cnt, int format, u32 &fill) {
+    const u32 lane = threadIdx.x & 31;
     u32 incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -323,126 +364,125 @@ __device__ __forceinline__ void warp_emit(const DbView &db, const DbCursor &c, c
     }
     const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
     if (total == 0) return;
-    u64 *stage = tb.stage[warp];
-    if (total > MT_STAGE) {
-        // more than the staging buffer holds (a few very long groups): reserve and write straight to HBM
-        warp_flush<ROUTED>(mo, stage, fill);
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(mo.counter, (unsigned long long) total);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (active && cnt) {
-            u64 o = base + incl - cnt;
-            for (u32 j = lo; j < hi; ++j) {
-                const u64 t = s.vals[j];
-                const u32 d = (j - lo < 16) ? (u32) (dpack >> (4 * (j - lo))) & 15u : hamming_sum_lut(tb.lut2, q.value, t);
-                if (d > maxh) continue;
-                if (ROUTED) {                                     // rare path: one reservation per record at its home
-                    u64 rec[3];
-                    make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
-                    const u32 h = route_home(*mo.route, qi_seq(rec[0]));
-                    const unsigned long long slot = atomicAdd(mo.route->sent_m + h, 1ull);
-                    if (slot < mo.route->match_cap[h]) {
-                        u64 *p = reinterpret_cast<u64 *>(mo.route->matches[h]) + slot * 3;
-                        p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
-                    }
-                } else if (o < mo.cap) {
-                    u64 rec[3];
-                    make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
-                    u64 *p = reinterpret_cast<u64 *>(mo.out + o);
-                    p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
-                }
-                ++o;
-            }
-        }
-        return;
-    }
-    if (fill + total > MT_STAGE) warp_flush<ROUTED>(mo, stage, fill);
+    // reserve and write straight to HBM (rare path: a group longer than a piece)
+    warp_flush<ROUTED>(mo, ws.stage, fill);
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(mo.counter, (unsigned long long) total);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (active && cnt) {
-        u32 o = fill + incl - cnt;
-        for (u32 j = lo; j < hi; ++j) {
-            const u64 t = s.vals[j];
-            const u32 d = (j - lo < 16) ? (u32) (dpack >> (4 * (j - lo))) & 15u : hamming_sum_lut(tb.lut2, q.value, t);
+        u64 o = base + incl - cnt;
+        for (u32 j = 0; j < ge; ++j) {
+            const u64 t = ws.vals[j];
+            const u32 d = hamming_sum_lut(tb.lut2, q.value, t);
             if (d > maxh) continue;
             u64 rec[3];
-            make_match(db, mo, tb.lutp, q, t, c.kidx + j, d, format, rec);
-            stage[o * 3] = rec[0]; stage[o * 3 + 1] = rec[1]; stage[o * 3 + 2] = rec[2];
+            make_match(db, mo, tb.lutp, q, t, kbase + j, d, format, rec);
+            if (ROUTED) {                                     // one reservation per record at its home
+                const u32 h = route_home(*mo.route, qi_seq(rec[0]));
+                const unsigned long long slot = atomicAdd(mo.route->sent_m + h, 1ull);
+                if (slot < mo.route->match_cap[h]) {
+                    u64 *p = reinterpret_cast<u64 *>(mo.route->matches[h]) + slot * 3;
+                    p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
+                }
+            } else if (o < mo.cap) {
+                u64 *p = reinterpret_cast<u64 *>(mo.out + o);
+                p[0] = rec[0]; p[1] = rec[1]; p[2] = rec[2];
+            }
             ++o;
         }
     }
-    fill += total;
-    __syncwarp();
 }
 
-// Streaming two-pass join for an amino-acid group that does not fit one chunk: for every batch of
-// 256 queries of that group the group is decoded twice from its start cursor (minimum, then emit).
+// synchronous fetch + decode of a piece at cursor g into word buffer `buf` (streaming path and follow-up pieces).
+// wl = words of the piece.  Returns n_total; *parity is the buffer's mbarrier phase (flipped here).
+__device__ __forceinline__ u32 load_piece(const DbView &db, WarpSmem &ws, int buf, u32 &parity, const DbCursor &g, u32 wl) {
+    const u32 lane = threadIdx.x & 31;
+    __syncwarp();
+    if (lane == 0) fetch_words(db, ws, buf, g.word, wl);
+    mbar_wait(&ws.mbar[buf], parity);
+    parity ^= 1u;
+    const u32 pad = (u32) (g.word & 7ull);
+    return decode_piece(ws, ws.w[buf], pad, wl, g.vbefore);
+}
+
+// Streaming two-pass join for an amino-acid group that does not fit one piece.  `c` sits on the group's first k-mer;
+// the group ends at the first k-mer with another amino-acid part, at ordinal kend or at stream word wlimit.  For every
+// 32 queries of the slice that hold queries of that group the group is decoded twice (minimum, then emit).  On return
+// `c` is the cursor of the first k-mer behind the group.
 template <bool ROUTED>
-__device__ __noinline__ void giant_group(const DbView &db, const DbCursor &c, MatchSmem &s, MatchTables &tb, const MatchOut &mo,
-                                         const mb_kmer *__restrict__ q, u64 qcur, u64 qend, u64 gaa, int format, u32 &fill) {
-    const u32 tid = threadIdx.x;
-    for (; qcur < qend; qcur += MT_THREADS) {
-        const u64 qi = qcur + tid;
+__device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend, u64 wlimit, WarpSmem &ws, const MatchTables &tb,
+                                         const MatchOut &mo, int buf, u32 &parity, const mb_kmer *__restrict__ q, u64 qs, u64 qe,
+                                         int format, u32 &fill) {
+    const u32 lane = threadIdx.x & 31;
+    // the group's amino-acid part: value of its first k-mer
+    u32 wl = (u32) (wlimit - c.word < (u64) MT_CAP_W ? wlimit - c.word : (u64) MT_CAP_W);
+    load_piece(db, ws, buf, parity, c, wl);
+    const u64 gaa = ws.vals[0] >> 24;
+    DbCursor gend = c;                                   // becomes the cursor behind the group
+    bool have_end = false;
+    for (u64 qb = qs; qb < qe || !have_end; qb += 32) {
+        const u64 qi = qb + lane;
         mb_kmer qk;
         qk.value = 0; qk.qinfo = 0;
         bool mine = false;
-        if (qi < qend) { qk = q[qi]; mine = (qk.value >> 24) == gaa; }
-        if (__syncthreads_count(mine) == 0) continue;
+        if (qi < qe) { qk = q[qi]; mine = (qk.value >> 24) == gaa; }
+        const bool any = __any_sync(0xFFFFFFFFu, mine);
+        if (!any && have_end) continue;                  // (the first pass also finds the group's end, queries or not)
         u32 mind = 255, maxh = 0;
         for (int phase = 0; phase < 2; ++phase) {
+            if (phase == 1 && !any) break;
             DbCursor g = c;
             while (true) {
-                const u32 n = decode_chunk(db, g, s);
-                if (n == 0) break;
-                if (tid == 0) s.group_end = n;
-                __syncthreads();
-                for (u32 j = tid; j < n; j += MT_THREADS)
-                    if ((s.vals[j] >> 24) != gaa) atomicMin(&s.group_end, j);
-                __syncthreads();
-                const u32 ge = s.group_end;
-                const bool finished = ge < n || (g.kidx + n == db.n_kmers_eff);
+                wl = (u32) (wlimit - g.word < (u64) MT_CAP_W ? wlimit - g.word : (u64) MT_CAP_W);
+                const u32 n_total = load_piece(db, ws, buf, parity, g, wl);
+                u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
+                if ((u64) n > kend - g.kidx) n = (u32) (kend - g.kidx);
+                if (n == 0) { if (!have_end) { gend = g; have_end = true; } break; }
+                // first entry with another amino-acid part
+                u32 ge = n;
+                for (u32 j0 = 0; j0 < n; j0 += 32) {
+                    const u32 j = j0 + lane;
+                    const u32 m = __ballot_sync(0xFFFFFFFFu, j < n && (ws.vals[j] >> 24) != gaa);
+                    if (m) { ge = j0 + (u32) __ffs((int) m) - 1; break; }
+                }
+                const bool finished = ge < n || g.kidx + n >= kend || (g.word + wl >= wlimit && n == n_total);
                 if (phase == 0) {
                     if (mine)
                         for (u32 j = 0; j < ge; ++j) {
-                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, s.vals[j]);
+                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, ws.vals[j]);
                             mind = d < mind ? d : mind;
                         }
                 } else {
                     u32 cnt = 0;
-                    u64 dpack = 0;
                     if (mine)
-                        for (u32 j = 0; j < ge; ++j) {
-                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, s.vals[j]);
-                            if (j < 16) dpack |= (u64) (d < 15 ? d : 15) << (4 * j);
-                            cnt += d <= maxh ? 1u : 0u;
-                        }
-                    warp_emit<ROUTED>(db, g, s, tb, mo, mine, qk, 0, ge, maxh, cnt, dpack, format, fill);
+                        for (u32 j = 0; j < ge; ++j) cnt += hamming_sum_lut(tb.lut2, qk.value, ws.vals[j]) <= maxh ? 1u : 0u;
+                    warp_emit_own<ROUTED>(db, g.kidx, ws, tb, mo, mine, qk, ge, maxh, cnt, format, fill);
                 }
-                __syncthreads();
-                if (finished) break;
-                const u64 nw = g.word + (u64) s.wend[n - 1] + 1;
-                const u64 nv = s.vals[n - 1];
-                __syncthreads();
-                g.word = nw; g.vbefore = nv; g.kidx += n;
+                // cursor behind the entries consumed from this piece
+                const u32 used = finished ? ge : n;
+                DbCursor nx = g;
+                if (used) {
+                    const u32 pad = (u32) (g.word & 7ull);
+                    nx.word = (g.word & ~7ull) + word_after_kmer(ws.w[buf], pad, wl, used);
+                    nx.vbefore = ws.vals[used - 1];
+                    nx.kidx = g.kidx + used;
+                }
+                __syncwarp();
+                if (finished) { if (!have_end) { gend = nx; have_end = true; } break; }
+                g = nx;
             }
             if (phase == 0) maxh = mind * 2 < 7 ? mind * 2 : 7;
         }
     }
+    c = gend;
 }
 
-// first index in q[lo, hi) whose AA part is >= aa
-__device__ __forceinline__ u64 query_lower_bound(const mb_kmer *__restrict__ q, u64 lo, u64 hi, u64 aa) {
-    while (lo < hi) {
-        const u64 mid = (lo + hi) >> 1;
-        if ((__ldg(&q[mid].value) >> 24) < aa) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
+// ---- the join kernel ---------------------------------------------------------------------------------------------
 template <bool ROUTED>
-__global__ void __launch_bounds__(MT_THREADS, 4)
-k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
-        const u64 *__restrict__ qend_of, MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *block_ticket,
-        const Route *__restrict__ route_g) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+__global__ void __launch_bounds__(MT_THREADS, 3)
+k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
+        MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *unit_ticket, const Route *__restrict__ route_g) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ Route s_route;
     MatchOut mo = mo_in;
     mo.route = nullptr;
@@ -450,9 +490,9 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
         for (u32 i = threadIdx.x; i < sizeof(Route) / 8; i += MT_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
         mo.route = &s_route;
     }
-    MatchSmem &s = *reinterpret_cast<MatchSmem *>(smem_raw);
-    MatchTables &tb = *reinterpret_cast<MatchTables *>(smem_raw + ((sizeof(MatchSmem) + 15) & ~(size_t) 15));
+    MatchTables &tb = *reinterpret_cast<MatchTables *>(smem_raw);
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    WarpSmem &ws = *reinterpret_cast<WarpSmem *>(smem_raw + sizeof(MatchTables) + (size_t) warp * sizeof(WarpSmem));
     {
         const uint4 *src2 = reinterpret_cast<const uint4 *>(tables->lut2);
         const uint4 *srcp = reinterpret_cast<const uint4 *>(tables->lutp);
@@ -460,310 +500,382 @@ k_match(DbView db, const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb
         uint4 *dp = reinterpret_cast<uint4 *>(tb.lutp);
         for (u32 i = tid; i < 4096 / 16; i += MT_THREADS) { d2[i] = __ldg(src2 + i); dp[i] = __ldg(srcp + i); }
     }
+    if (lane == 0) { mbar_init(&ws.mbar[0], 1); mbar_init(&ws.mbar[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();                                // tables, route and barriers are ready; the only block barrier
+
     u32 fill = 0;                                   // matches staged by this warp (warp-uniform)
+    u32 parity[2] = {0, 0};                         // mbarrier phases of the two word buffers
 
-    // Block tickets are drawn one block ahead: tick[it & 1] is the block of iteration `it`, tick[(it + 1) & 1] the next one
-    // (known from the start, so that it can be prefetched).  Thread 0 draws the ticket after that at the start of the
-    // iteration, keeps it in a register and publishes it in the slot of the current block just before the closing barrier.
-    if (tid == 0) { s.tick[0] = atomicAdd(block_ticket, 1u); s.tick[1] = atomicAdd(block_ticket, 1u); }
-    __syncthreads();
-    u32 b = s.tick[0];
-    for (u32 it = 0; b < n_blocks; ++it) {
-        const u32 nb = s.tick[(it + 1) & 1];
+    // The words of unit `u` go to buffer `b`.  Only units with queries are fetched; returns whether a copy was issued.
+    // (lane 0 issues; all lanes compute the same unit facts from the same loads)
+    auto unit_facts = [&](u32 u, DbCursor &c, u64 &wend, u64 &kend, u64 &qs, u64 &qe) -> bool {
+        if (u >= n_units) return false;
+        const Unit a = units[u], z = units[u + 1];
+        c.word = a.word; c.vbefore = a.vbefore; c.kidx = a.kidx;
+        wend = z.word;
+        kend = z.kidx < db.n_kmers_eff ? z.kidx : db.n_kmers_eff;
+        qs = qstart[u]; qe = qstart[u + 1];
+        return qs < qe && a.kidx < kend;
+    };
+
+    // tickets are drawn one unit ahead: `cur` is joined now, `nxt` has its words in flight
+    u32 cur = 0, nxt = 0;
+    if (lane == 0) { cur = atomicAdd(unit_ticket, 1u); nxt = atomicAdd(unit_ticket, 1u); }
+    cur = __shfl_sync(0xFFFFFFFFu, cur, 0);
+    nxt = __shfl_sync(0xFFFFFFFFu, nxt, 0);
+    DbCursor c, cn;
+    u64 wend = 0, kend = 0, qs = 0, qe = 0, wend_n = 0, kend_n = 0, qs_n = 0, qe_n = 0;
+    bool have = unit_facts(cur, c, wend, kend, qs, qe);
+    int buf = 0;
+    if (have && lane == 0) fetch_words(db, ws, buf, c.word, (u32) (wend - c.word < (u64) MT_CAP_W ? wend - c.word : (u64) MT_CAP_W));
+
+    while (cur < n_units) {
+        // next ticket + next unit's words (other buffer) + L2 warm-up of its queries and info entries
         u32 drawn = 0;
-        if (tid == 0) drawn = atomicAdd(block_ticket, 1u);
-        if (warp == MT_THREADS / 32 - 1) prefetch_block(db, blocks, n_blocks, q, qstart, qend_of, nb, gridDim.x);
-        do {
-        const BlockIndex bi = blocks[b];
-        if (!bi.owns) break;
-        const u64 qcur = qstart[b];
-        const u64 qend = qend_of[b];
-        if (qcur >= qend) break;                    // no query falls into this block's AA range
+        if (lane == 0) drawn = atomicAdd(unit_ticket, 1u);
+        const bool have_n = unit_facts(nxt, cn, wend_n, kend_n, qs_n, qe_n);
+        if (have_n) {
+            if (lane == 0) fetch_words(db, ws, buf ^ 1, cn.word, (u32) (wend_n - cn.word < (u64) MT_CAP_W ? wend_n - cn.word : (u64) MT_CAP_W));
+            u64 qn = qe_n - qs_n;
+            if (qn > 2048) qn = 2048;
+            const char *qp = reinterpret_cast<const char *>(q + qs_n);
+            for (u64 o = (u64) lane * 128; o < qn * 16; o += 32 * 128) prefetch_l2(qp + o);
+            u64 nk = kend_n - cn.kidx;
+            if (nk > (u64) MT_CAP_K) nk = MT_CAP_K;
+            const char *inf = reinterpret_cast<const char *>(db.info + cn.kidx);
+            for (u64 o = (u64) lane * 128; o < nk * 4; o += 32 * 128) prefetch_l2(inf + o);
+            if (lane == 0 && nxt + 2 * gridDim.x * MT_WARPS < n_units) { prefetch_l2(units + nxt + 2 * gridDim.x * MT_WARPS); prefetch_l2(qstart + nxt + 2 * gridDim.x * MT_WARPS); }
+        }
 
-        const u64 tile_end = (u64) (b + 1) * DB_W;  // groups starting at or after this word belong to later blocks
-        DbCursor c{bi.word, bi.vbefore, bi.kidx};
-
-        while (true) {
-            const u32 n = decode_chunk(db, c, s);
-            if (n == 0) break;
-            if (tid == 0) { s.last_start = 0; s.own_end = (int) n; s.qnext = 0; }
-            __syncthreads();
-            const u64 own_limit = tile_end > c.word ? tile_end - c.word : 0;   // local word offset of the block end
-            {
-                // one sweep over the group boundaries: last group start and first group that starts in a later block
-                int lmax = 0, lmin = (int) n;
-                for (u32 j = tid + 1; j < n; j += MT_THREADS) {
-                    const u64 a = s.vals[j] >> 24, pa = s.vals[j - 1] >> 24;
-                    if (a != pa) {
-                        lmax = (int) j;
-                        // first word of k-mer j is the word after the previous terminator
-                        if ((u64) s.wend[j - 1] + 1 >= own_limit && (int) j < lmin) lmin = (int) j;
+        if (have) {
+            bool first_piece = true;
+            while (c.kidx < kend) {
+                const u32 wl = (u32) (wend - c.word < (u64) MT_CAP_W ? wend - c.word : (u64) MT_CAP_W);
+                u32 n_total;
+                if (first_piece) {
+                    mbar_wait(&ws.mbar[buf], parity[buf]);
+                    parity[buf] ^= 1u;
+                    n_total = decode_piece(ws, ws.w[buf], (u32) (c.word & 7ull), wl, c.vbefore);
+                    first_piece = false;
+                } else {
+                    n_total = load_piece(db, ws, buf, parity[buf], c, wl);
+                }
+                u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
+                if ((u64) n > kend - c.kidx) n = (u32) (kend - c.kidx);
+                if (n == 0) break;
+                // every group of the piece is complete when the piece reaches the end of the unit (a unit is a whole number of
+                // groups) or the end of the candidates; otherwise the last group may continue and is left to the next piece
+                const bool whole = (c.word + wl >= wend && n_total <= (u32) MT_CAP_K) || c.kidx + n >= kend;
+                u32 proc = n;
+                if (!whole) {
+                    proc = last_head_before(ws, n);
+                    if (proc == 0) {
+                        giant_group<ROUTED>(db, c, kend, wend, ws, tb, mo, buf, parity[buf], q, qs, qe, format, fill);
+                        continue;
                     }
                 }
-                lmax = __reduce_max_sync(0xFFFFFFFFu, lmax);
-                lmin = __reduce_min_sync(0xFFFFFFFFu, lmin);
-                if (lane == 0) {
-                    if (lmax) atomicMax(&s.last_start, lmax);
-                    if (lmin < (int) n) atomicMin(&s.own_end, lmin);
-                }
-            }
-            __syncthreads();
-            const bool db_end = (c.kidx + n == db.n_kmers_eff);
-            u32 proc_end = db_end ? n : (u32) s.last_start;     // the last group may continue past the chunk
-            if ((u32) s.own_end < proc_end) proc_end = (u32) s.own_end;
-            const u32 own_end = (u32) s.own_end;
-
-            if (proc_end == 0) {
-                // One group fills the whole chunk and is not known to be complete: streaming path.  The
-                // group is owned (the cursor always sits on a group starting inside this block) and, being
-                // longer than a block plus overhang, it is the last one this block owns.
-                const u64 gaa = s.vals[0] >> 24;
-                __syncthreads();
-                giant_group<ROUTED>(db, c, s, tb, mo, q, qcur, qend, gaa, format, fill);
-                break;
-            }
-
-            // ---- fast path: all groups in [0, proc_end) are complete and owned.  Warps run on their own; every query
-            // of the block's range is looked up (the range is not ordered below the sorted bits, and it also holds
-            // queries of the neighbouring blocks: those find no group of their amino-acid part here).  The query
-            // record of the NEXT ticket is requested before the current one is processed. ----
-            u32 base = warp * 32u;
-            ulonglong2 v_next = make_ulonglong2(0, 0);
-            if (qcur + base + lane < qend) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qcur + base + lane));
-            while (qcur + base < qend) {
-                mb_kmer qk;
-                qk.value = v_next.x; qk.qinfo = v_next.y;
-                const bool mine = qcur + base + lane < qend;
-                {
-                    base += MT_THREADS;                  // tickets are dealt round robin: warp w takes 32-query slices w, w + 8, ...
-                    if (qcur + base + lane < qend) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qcur + base + lane));
-                }
-                // (1) every lane: candidate range [lo, lo + ncand) of its query = its amino-acid group in the block
-                u32 lo = 0, ncand = 0;
-                bool exact = false;                 // the candidates are copies of the query's value: distance 0, no table lookups
-                if (mine) {
-                    // binary search of the decoded block (measured on B200 against a 1024-bucket index and against a hash
-                    // directory of the groups built per block: both cost more to build than the search they save)
-                    // The search is on the FULL value.  When the block holds the query's value itself, the minimum distance
-                    // of its group is 0, the filter min(2 * min, 7) = 0 keeps only distance 0, and distance 0 means the same
-                    // codon ids, i.e. the same value (the Hamming table is 0 on its diagonal only): the candidates are just
-                    // the run of equal values (35 % of the queries and 68 % of the matches of configs[1] end here, with one
-                    // or two pairs instead of the whole group).  Otherwise the candidates are the amino-acid group around
-                    // the insertion point.
-                    const u64 v = qk.value, aa = v >> 24;
-                    u32 l = 0, h = proc_end;
-                    while (l < h) {
-                        const u32 mid = (l + h) >> 1;
-                        if (s.vals[mid] < v) l = mid + 1; else h = mid;
-                    }
-                    lo = l;
-                    u32 hi = l;
-                    if (l < proc_end && s.vals[l] == v) {
-                        exact = true;
-                        do ++hi; while (hi < proc_end && s.vals[hi] == v);
-                    } else {
-                        while (lo > 0 && (s.vals[lo - 1] >> 24) == aa) --lo;
-                        while (hi < proc_end && (s.vals[hi] >> 24) == aa) ++hi;
-                    }
-                    ncand = hi - lo;
-                }
-                // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
-                // whose exclusive prefix of ncand is the largest one <= p
-                u32 incl = ncand;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-                    if (lane >= (u32) d) incl += t;
-                }
-                const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-                if (total == 0) continue;
-                const u32 excl = incl - ncand;
-                const u32 q24 = (u32) qk.value & 0xFFFFFFu;
-                u32 *qmin = tb.qmin[warp];
-                qmin[lane] = exact ? 0u : 255u;
-                const u32 lo_x = lo | (exact ? 0x80000000u : 0u);
+                if (lane == 0) atomicOr(&ws.hbits[proc >> 5], 1u << (proc & 31));      // sentinel head behind the last entry
                 __syncwarp();
-                const u32 rounds = (total + 31) / 32;
-                u32 pk0 = 255, pk1 = 255;           // pairs of rounds 0 and 1 are kept for the emit pass: dd | owner << 8 | j << 16
-                for (u32 r = 0; r < rounds; ++r) {
-                    const u32 p = r * 32 + lane;
-                    u32 owner = 0;
-#pragma unroll
-                    for (int st = 16; st > 0; st >>= 1) {
-                        const u32 e = __shfl_sync(0xFFFFFFFFu, excl, (owner + st) & 31);
-                        if (owner + st < 32 && e <= p) owner += st;
-                    }
-                    // lanes with ncand == 0 share their prefix with the next lane: the search lands on the LAST lane
-                    // with excl <= p, which is the one that owns p (its range is non-empty) when p < total
-                    const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
-                    const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo_x, owner);
-                    const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
-                    u32 dd = 255, j = 0;
-                    if (p < total) {
-                        j = (o_lo & 0x7FFFFFFFu) + (p - o_excl);
-                        dd = 0;
-                        // the candidate's info entry (make_match reads it in the emit pass) is asked for now
-                        asm volatile("prefetch.global.L1 [%0];" ::"l"(db.info + c.kidx + j));
-                        if (!(o_lo >> 31)) {
-                            dd = hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
-                            atomicMin(&qmin[owner], dd);
+
+                // ---- join the query slice against ws.vals[0, proc) ----
+                const u64 key_lo = ws.vals[0] & ~0xFFFFFFull, key_hi = ws.vals[proc - 1] | 0xFFFFFFull;
+                u32 top = 1;
+                while (top * 2 <= proc) top *= 2;
+                ulonglong2 v_next = make_ulonglong2(0, 0);
+                if (qs + lane < qe) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qs + lane));
+                for (u64 qb = qs; qb < qe; qb += 32) {
+                    mb_kmer qk;
+                    qk.value = v_next.x; qk.qinfo = v_next.y;
+                    const bool mine = qb + lane < qe;
+                    if (qb + 32 + lane < qe) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qb + 32 + lane));
+                    // (1) every lane: its query's amino-acid group [lo, lo + ncand) in the piece
+                    u32 lo = 0, ncand = 0;
+                    const u64 key = qk.value & ~0xFFFFFFull;
+                    if (mine && key >= key_lo && key <= key_hi) {
+                        // branch-free lower bound: number of entries below the key
+                        u32 pos = 0;
+                        for (u32 step = top; step; step >>= 1) {
+                            const u32 nx = pos + step;
+                            if (nx <= proc && ws.vals[nx - 1] < key) pos = nx;
+                        }
+                        if (pos < proc && (ws.vals[pos] >> 24) == (key >> 24)) {
+                            // pos is the group's head; the group ends at the next head (the sentinel bounds the scan)
+                            lo = pos;
+                            u32 b = pos + 1;
+                            u32 m = ws.hbits[b >> 5] >> (b & 31);
+                            u32 hi;
+                            if (m) hi = b + (u32) __ffs((int) m) - 1;
+                            else {
+                                u32 wi = (b >> 5) + 1;
+                                while ((m = ws.hbits[wi]) == 0) ++wi;
+                                hi = wi * 32 + (u32) __ffs((int) m) - 1;
+                            }
+                            ncand = hi - lo;
                         }
                     }
-                    const u32 pk = dd | (owner << 8) | (j << 16);
-                    if (r == 0) pk0 = pk;
-                    else if (r == 1) pk1 = pk;
-                }
-                __syncwarp();
-                // (3) emit: distance <= min(2 * min, 7) (KmerMatcher.cpp:1126); one staging slot per surviving pair
-                u64 *stage = tb.stage[warp];
-                for (u32 r = 0; r < rounds; ++r) {
-                    const u32 p = r * 32 + lane;
-                    u32 owner, dd, j;
-                    if (r < 2) { const u32 pk = r == 0 ? pk0 : pk1; dd = pk & 255u; owner = (pk >> 8) & 31u; j = pk >> 16; }
-                    else {
-                        owner = 0;
+                    // (2) the warp's (query, candidate) pairs are spread evenly over the lanes: pair p belongs to the lane
+                    // whose exclusive prefix of ncand is the largest one <= p
+                    u32 incl = ncand;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                        if (lane >= (u32) d) incl += t;
+                    }
+                    const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                    if (total == 0) continue;
+                    const u32 excl = incl - ncand;
+                    const u32 q24 = (u32) qk.value & 0xFFFFFFu;
+                    ws.qmin[lane] = 255u;
+                    __syncwarp();
+                    const u32 rounds = (total + 31) / 32;
+                    u32 pk0 = 255, pk1 = 255;           // pairs of rounds 0 and 1 are kept for the emit pass: dd | owner << 8 | j << 16
+                    for (u32 r = 0; r < rounds; ++r) {
+                        const u32 p = r * 32 + lane;
+                        u32 owner = 0;
 #pragma unroll
                         for (int st = 16; st > 0; st >>= 1) {
                             const u32 e = __shfl_sync(0xFFFFFFFFu, excl, (owner + st) & 31);
                             if (owner + st < 32 && e <= p) owner += st;
                         }
+                        // lanes with ncand == 0 share their prefix with the next lane: the search lands on the LAST lane
+                        // with excl <= p, which is the one that owns p (its range is non-empty) when p < total
                         const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
-                        const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo_x, owner);
+                        const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo, owner);
                         const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
-                        dd = 255; j = 0;
+                        u32 dd = 255, j = 0;
                         if (p < total) {
-                            j = (o_lo & 0x7FFFFFFFu) + (p - o_excl);
-                            dd = (o_lo >> 31) ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, s.vals[j]);
+                            j = o_lo + (p - o_excl);
+                            // the candidate's info entry (make_match reads it in the emit pass) is asked for now
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(db.info + c.kidx + j));
+                            const u32 t24 = (u32) ws.vals[j] & 0xFFFFFFu;
+                            dd = t24 == o_q ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, (u64) t24);
+                            atomicMin(&ws.qmin[owner], dd);
                         }
+                        const u32 pk = dd | (owner << 8) | (j << 16);
+                        if (r == 0) pk0 = pk;
+                        else if (r == 1) pk1 = pk;
                     }
-                    const u32 mind = qmin[owner];
-                    const u32 maxh = mind * 2 < 7 ? mind * 2 : 7;
-                    const bool ok = p < total && dd <= maxh;
-                    const u32 okmask = __ballot_sync(0xFFFFFFFFu, ok);
-                    // the owner's full query record (value and qinfo) for the match
-                    mb_kmer oq;
-                    oq.value = __shfl_sync(0xFFFFFFFFu, qk.value, owner);
-                    oq.qinfo = __shfl_sync(0xFFFFFFFFu, qk.qinfo, owner);
-                    if (okmask == 0) continue;
-                    const u32 nok = (u32) __popc(okmask);
-                    if (fill + nok > MT_STAGE) warp_flush<ROUTED>(mo, stage, fill);
-                    if (ok) {
-                        u64 rec[3];
-                        make_match(db, mo, tb.lutp, oq, s.vals[j], c.kidx + j, dd, format, rec);
-                        const u32 o = fill + (u32) __popc(okmask & ((1u << lane) - 1u));
-                        stage[o * 3] = rec[0]; stage[o * 3 + 1] = rec[1]; stage[o * 3 + 2] = rec[2];
-                    }
-                    fill += nok;
                     __syncwarp();
+                    // (3) emit: distance <= min(2 * min, 7) (KmerMatcher.cpp:1126); one staging slot per surviving pair
+                    for (u32 r = 0; r < rounds; ++r) {
+                        const u32 p = r * 32 + lane;
+                        u32 owner, dd, j;
+                        if (r < 2) { const u32 pk = r == 0 ? pk0 : pk1; dd = pk & 255u; owner = (pk >> 8) & 31u; j = pk >> 16; }
+                        else {
+                            owner = 0;
+#pragma unroll
+                            for (int st = 16; st > 0; st >>= 1) {
+                                const u32 e = __shfl_sync(0xFFFFFFFFu, excl, (owner + st) & 31);
+                                if (owner + st < 32 && e <= p) owner += st;
+                            }
+                            const u32 o_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
+                            const u32 o_lo = __shfl_sync(0xFFFFFFFFu, lo, owner);
+                            const u32 o_q = __shfl_sync(0xFFFFFFFFu, q24, owner);
+                            dd = 255; j = 0;
+                            if (p < total) {
+                                j = o_lo + (p - o_excl);
+                                const u32 t24 = (u32) ws.vals[j] & 0xFFFFFFu;
+                                dd = t24 == o_q ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, (u64) t24);
+                            }
+                        }
+                        const u32 mind = ws.qmin[owner];
+                        const u32 maxh = mind * 2 < 7 ? mind * 2 : 7;
+                        const bool ok = p < total && dd <= maxh;
+                        const u32 okmask = __ballot_sync(0xFFFFFFFFu, ok);
+                        // the owner's full query record (value and qinfo) for the match
+                        mb_kmer oq;
+                        oq.value = __shfl_sync(0xFFFFFFFFu, qk.value, owner);
+                        oq.qinfo = __shfl_sync(0xFFFFFFFFu, qk.qinfo, owner);
+                        if (okmask == 0) continue;
+                        const u32 nok = (u32) __popc(okmask);
+                        if (fill + nok > MT_STAGE) warp_flush<ROUTED>(mo, ws.stage, fill);
+                        if (ok) {
+                            u64 rec[3];
+                            make_match(db, mo, tb.lutp, oq, ws.vals[j], c.kidx + j, dd, format, rec);
+                            const u32 o = fill + (u32) __popc(okmask & ((1u << lane) - 1u));
+                            ws.stage[o * 3] = rec[0]; ws.stage[o * 3 + 1] = rec[1]; ws.stage[o * 3 + 2] = rec[2];
+                        }
+                        fill += nok;
+                        __syncwarp();
+                    }
+                }
+                // behind the entries joined: the next piece of this unit, if any
+                if (c.kidx + proc >= kend) break;
+                {
+                    const u32 pad = (u32) (c.word & 7ull);
+                    const u64 nw = (c.word & ~7ull) + word_after_kmer(ws.w[buf], pad, wl, proc);
+                    const u64 nv = ws.vals[proc - 1];
+                    __syncwarp();
+                    c.word = nw; c.vbefore = nv; c.kidx += proc;
                 }
             }
-            __syncthreads();
-            if (proc_end >= n && db_end) break;                        // end of the stream
-            if (proc_end >= own_end) break;                            // the next group starts in a later block
-            // continue from the first group that was not processed (it starts inside this block)
-            const u64 nw = c.word + (u64) s.wend[proc_end - 1] + 1;
-            const u64 nv = s.vals[proc_end - 1];
-            __syncthreads();
-            c.word = nw; c.vbefore = nv; c.kidx += proc_end;
         }
-        } while (false);
-        if (tid == 0) s.tick[it & 1] = drawn;
-        __syncthreads();                            // this block is done with the shared arrays; the new ticket is visible
-        b = nb;
+        cur = nxt;
+        nxt = __shfl_sync(0xFFFFFFFFu, drawn, 0);
+        c = cn; wend = wend_n; kend = kend_n; qs = qs_n; qe = qe_n; have = have_n;
+        buf ^= 1;
     }
-    warp_flush<ROUTED>(mo, tb.stage[warp], fill);
+    warp_flush<ROUTED>(mo, ws.stage, fill);
 }
 
-constexpr size_t match_smem_bytes() { return ((sizeof(MatchSmem) + 15) & ~(size_t) 15) + sizeof(MatchTables); }
-
-// ---- load-time block index ---------------------------------------------------------------------------
-// pass A: per block, how many words in front of the block belong to the first k-mer ending in it, how
-// many k-mers end in it and the sum of their deltas.
-__global__ void __launch_bounds__(MT_THREADS)
-k_db_block_summary(DbView db, u32 n_blocks, u32 *__restrict__ blk_back, u32 *__restrict__ blk_cnt, u64 *__restrict__ blk_sum) {
-    __shared__ MatchSmem s;
-    __shared__ u32 s_back;
-    __shared__ u32 s_cnt;
-    const u32 b = blockIdx.x, tid = threadIdx.x;
-    if (b >= n_blocks) return;
-    const u64 w0 = (u64) b * DB_W;
-    if (tid == 0) {
-        u32 back = 0;
-        while (back < 4 && w0 > back && !(db.words[w0 - back - 1] & 0x8000u)) ++back;
-        s_back = back;
-        s_cnt = 0;
+// ---- load-time unit index ----------------------------------------------------------------------------------------
+// pass A, one warp per raw block of UN_W words: how many k-mers END in the block and the sum of their deltas.
+__global__ void __launch_bounds__(256)
+k_db_raw_summary(DbView db, u64 n_raw, u32 *__restrict__ raw_cnt, u64 *__restrict__ raw_sum) {
+    const u64 b = (u64) blockIdx.x * 8 + (threadIdx.x >> 5);
+    const u32 lane = threadIdx.x & 31;
+    if (b >= n_raw) return;
+    const u64 w0 = b * UN_W;
+    constexpr int R = UN_W / 32;
+    const u64 l0 = w0 + (u64) lane * R;
+    u64 carry = 0;
+    {
+        u64 st = l0;
+        while (st > 0 && l0 - st < 4 && st - 1 < db.n_words && !(db.words[st - 1] & 0x8000u)) --st;
+        for (u64 k = st; k < l0; ++k) carry = (carry | db.words[k]) << 15;
     }
-    __syncthreads();
-    const u32 back = s_back;
-    DbCursor c{w0 - back, 0, 0};
-    const u32 n = decode_chunk(db, c, s);
-    const u32 limit = DB_W + back;                 // local offset of the block end
-    // entries are ordered: count those whose terminator lies inside the block
-    for (u32 j = tid; j < n; j += MT_THREADS)
-        if (s.wend[j] < limit && (j + 1 == n || s.wend[j + 1] >= limit)) s_cnt = j + 1;
-    __syncthreads();
-    if (tid == 0) {
-        const u32 cnt = s_cnt;
-        blk_back[b] = back;
-        blk_cnt[b] = cnt;
-        blk_sum[b] = cnt ? s.vals[cnt - 1] : 0;
+    u32 cnt = 0;
+    u64 sum = 0, diff = carry;
+    for (int i = 0; i < R; ++i) {
+        const u64 idx = l0 + i;
+        if (idx >= db.n_words) break;
+        const u32 frag = db.words[idx];
+        if (frag & 0x8000u) { diff |= (frag & 0x7FFFu); sum += diff; ++cnt; diff = 0; }
+        else diff = (diff | frag) << 15;
     }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, d);
+        sum += __shfl_xor_sync(0xFFFFFFFFu, sum, d);
+    }
+    if (lane == 0) { raw_cnt[b] = cnt; raw_sum[b] = sum; }
 }
 
-// pass B (after the host scanned counts and sums into kidx/vbefore per block): first group starting in the block
-__global__ void __launch_bounds__(MT_THREADS)
-k_db_block_own(DbView db, u32 n_blocks, const u32 *__restrict__ blk_back, const u64 *__restrict__ blk_kidx,
-               const u64 *__restrict__ blk_vbefore, BlockIndex *__restrict__ out) {
-    __shared__ MatchSmem s;
-    __shared__ u32 s_first;
-    const u32 b = blockIdx.x, tid = threadIdx.x;
-    if (b >= n_blocks) return;
-    const u32 back = blk_back[b];
-    DbCursor c{(u64) b * DB_W - back, blk_vbefore[b], blk_kidx[b]};
-    if (tid == 0) s_first = 0xFFFFFFFFu;
-    const u32 n = decode_chunk(db, c, s);
-    const u32 lo = back, hi = DB_W + back;         // local word range of the block
-    for (u32 j = tid; j < n; j += MT_THREADS) {
-        const u32 first_word = j == 0 ? 0u : (u32) s.wend[j - 1] + 1u;
-        if (first_word < lo || first_word >= hi) continue;
-        const bool starts = (j == 0) ? (c.kidx == 0 || (s.vals[0] >> 24) != (c.vbefore >> 24))
-                                     : ((s.vals[j] >> 24) != (s.vals[j - 1] >> 24));
-        if (starts) atomicMin(&s_first, j);
+// pass B (after the host scanned counts and sums into kidx / vbefore per raw block), one warp per raw block: the first
+// k-mer that STARTS in the block and opens a new T bucket (or the stream).  out[b].t_lo = ~0 when there is none.
+__global__ void __launch_bounds__(256)
+k_db_raw_own(DbView db, u64 n_raw, const u64 *__restrict__ raw_kidx, const u64 *__restrict__ raw_vbefore, SortT st, Unit *__restrict__ out) {
+    const u64 b = (u64) blockIdx.x * 8 + (threadIdx.x >> 5);
+    const u32 lane = threadIdx.x & 31;
+    if (b >= n_raw) return;
+    const u64 w0 = b * UN_W, w1 = w0 + UN_W < db.n_words ? w0 + UN_W : db.n_words;
+    constexpr int R = UN_W / 32;
+    const u64 l0 = w0 + (u64) lane * R;
+    // deltas ENDING in my run (as in pass A), then absolute values; a k-mer's start word is the word behind the previous terminator
+    u64 carry = 0;
+    u64 first_start = l0;                    // start word of the delta that is unfinished at l0 (if any)
+    {
+        u64 s0 = l0;
+        while (s0 > 0 && l0 - s0 < 4 && s0 - 1 < db.n_words && !(db.words[s0 - 1] & 0x8000u)) --s0;
+        for (u64 k = s0; k < l0; ++k) carry = (carry | db.words[k]) << 15;
+        first_start = s0;
     }
-    __syncthreads();
-    if (tid == 0) {
-        BlockIndex bi;
-        const u32 j = s_first;
-        if (j == 0xFFFFFFFFu) { bi.word = 0; bi.vbefore = 0; bi.kidx = 0; bi.own_aa = ~0ull; bi.owns = 0; }
-        else {
-            bi.word = c.word + (j == 0 ? 0u : (u32) s.wend[j - 1] + 1u);
-            bi.vbefore = j == 0 ? c.vbefore : s.vals[j - 1];
-            bi.kidx = c.kidx + j;
-            bi.own_aa = s.vals[j] >> 24;
-            bi.owns = 1;
+    u32 cnt = 0;
+    u64 sum = 0, diff = carry;
+    for (int i = 0; i < R; ++i) {
+        const u64 idx = l0 + i;
+        if (idx >= db.n_words) break;
+        const u32 frag = db.words[idx];
+        if (frag & 0x8000u) { diff |= (frag & 0x7FFFu); sum += diff; ++cnt; diff = 0; }
+        else diff = (diff | frag) << 15;
+    }
+    u32 icnt = cnt;
+    u64 isum = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 tc = __shfl_up_sync(0xFFFFFFFFu, icnt, d);
+        const u64 ts = __shfl_up_sync(0xFFFFFFFFu, isum, d);
+        if (lane >= (u32) d) { icnt += tc; isum += ts; }
+    }
+    u64 run = raw_vbefore[b] + (isum - sum);
+    u64 ord = raw_kidx[b] + (icnt - cnt);
+    // candidates: k-mers ENDING in my run whose start word lies in [w0, w1)
+    u64 best_word = ~0ull, best_vb = 0, best_k = 0, best_t = ~0ull;
+    diff = carry;
+    u64 start = first_start;
+    for (int i = 0; i < R; ++i) {
+        const u64 idx = l0 + i;
+        if (idx >= db.n_words) break;
+        const u32 frag = db.words[idx];
+        if (frag & 0x8000u) {
+            diff |= (frag & 0x7FFFu);
+            const u64 nv = run + diff;
+            if (start >= w0 && start < w1 && best_word == ~0ull) {
+                const bool opens = ord == 0 || sort_t(st, nv) != sort_t(st, run);
+                if (opens) { best_word = start; best_vb = run; best_k = ord; best_t = sort_t(st, nv); }
+            }
+            run = nv;
+            ++ord;
+            diff = 0;
+            start = idx + 1;
+        } else diff = (diff | frag) << 15;
+    }
+    // a k-mer that starts in this block but ends in the next one: the last lane sees its start (unfinished delta at w1)
+    // and finishes it from the following words
+    if (lane == 31 && best_word == ~0ull && start < w1 && start >= w0 && w1 < db.n_words) {
+        u64 d2 = diff;
+        u64 idx = w1;
+        bool done = false;
+        for (int k = 0; k < 5 && idx < db.n_words; ++k, ++idx) {
+            const u32 frag = db.words[idx];
+            if (frag & 0x8000u) { d2 |= (frag & 0x7FFFu); done = true; break; }
+            d2 = (d2 | frag) << 15;
         }
-        bi.pad = 0;
-        out[b] = bi;
+        if (done) {
+            const u64 nv = run + d2;
+            if (ord == 0 || sort_t(st, nv) != sort_t(st, run)) { best_word = start; best_vb = run; best_k = ord; best_t = sort_t(st, nv); }
+        }
+    }
+    // lowest start word wins
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        const u64 ow = __shfl_xor_sync(0xFFFFFFFFu, best_word, d);
+        const u64 ov = __shfl_xor_sync(0xFFFFFFFFu, best_vb, d);
+        const u64 ok = __shfl_xor_sync(0xFFFFFFFFu, best_k, d);
+        const u64 ot = __shfl_xor_sync(0xFFFFFFFFu, best_t, d);
+        if (ow < best_word) { best_word = ow; best_vb = ov; best_k = ok; best_t = ot; }
+    }
+    if (lane == 0) {
+        Unit u;
+        u.word = best_word; u.vbefore = best_vb; u.kidx = best_k; u.t_lo = best_t;
+        out[b] = u;
     }
 }
 
-// plain decode of the resident stream (parity tap): values of the k-mers ending in each block
+// plain decode of the resident stream (parity tap): one warp per unit writes the values of its k-mers
 __global__ void __launch_bounds__(MT_THREADS)
-k_db_decode(DbView db, u32 n_blocks, const u32 *__restrict__ blk_back, const u32 *__restrict__ blk_cnt,
-            const u64 *__restrict__ blk_kidx, const u64 *__restrict__ blk_vbefore, u64 *__restrict__ values) {
-    __shared__ MatchSmem s;
-    const u32 b = blockIdx.x, tid = threadIdx.x;
-    if (b >= n_blocks) return;
-    DbCursor c{(u64) b * DB_W - blk_back[b], blk_vbefore[b], blk_kidx[b]};
-    decode_chunk(db, c, s);
-    const u32 cnt = blk_cnt[b];
-    for (u32 j = tid; j < cnt; j += MT_THREADS) values[c.kidx + j] = s.vals[j];
+k_db_decode(DbView db, const Unit *__restrict__ units, u32 n_units, u64 *__restrict__ values) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpSmem &ws = *reinterpret_cast<WarpSmem *>(smem_raw + (size_t) warp * sizeof(WarpSmem));
+    if (lane == 0) { mbar_init(&ws.mbar[0], 1); mbar_init(&ws.mbar[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    u32 parity = 0;
+    for (u32 u = blockIdx.x * MT_WARPS + warp; u < n_units; u += gridDim.x * MT_WARPS) {
+        DbCursor c{units[u].word, units[u].vbefore, units[u].kidx};
+        const u64 wend = units[u + 1].word, kend = units[u + 1].kidx;
+        while (c.kidx < kend) {
+            const u32 wl = (u32) (wend - c.word < (u64) MT_CAP_W ? wend - c.word : (u64) MT_CAP_W);
+            const u32 n_total = load_piece(db, ws, 0, parity, c, wl);
+            u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
+            if ((u64) n > kend - c.kidx) n = (u32) (kend - c.kidx);
+            if (n == 0) break;
+            for (u32 j = lane; j < n; j += 32) values[c.kidx + j] = ws.vals[j];
+            if (c.kidx + n >= kend) break;
+            const u32 pad = (u32) (c.word & 7ull);
+            const u64 nw = (c.word & ~7ull) + word_after_kmer(ws.w[0], pad, wl, n);
+            const u64 nv = ws.vals[n - 1];
+            __syncwarp();
+            c.word = nw; c.vbefore = nv; c.kidx += n;
+        }
+    }
 }
 
-// ---- per-batch partition: the query range a block has to look at ------------------------------------------
-// The queries are ordered by T(aa) only (SortT, mb_common.cuh: leading bits or the re-coded 24-bit key).  Block b owns the amino-acid groups [own_aa(b), own_aa(b+1)),
-// so it scans the queries with T(own_aa(b)) <= T(aa) <= T(own_aa(b+1)): the buckets at both ends are shared with the
-// neighbouring blocks, which is harmless because a query only finds its group in the block that owns it.
+// ---- per-batch partition: where each unit's T range starts in the sorted query array -----------------------------
+// The queries are ordered by T(aa) (SortT, mb_common.cuh); unit u owns the T values [t_lo(u), t_lo(u+1)), so its query
+// slice is [qstart[u], qstart[u+1]) — disjoint between units and exact.
 __device__ __forceinline__ u64 query_lower_bound_t(const mb_kmer *__restrict__ q, u64 nq, const SortT &st, u64 t) {
     u64 lo = 0, hi = nq;
     while (lo < hi) {
@@ -772,14 +884,11 @@ __device__ __forceinline__ u64 query_lower_bound_t(const mb_kmer *__restrict__ q
     }
     return lo;
 }
-__global__ void k_match_partition(const BlockIndex *__restrict__ blocks, u32 n_blocks, const mb_kmer *__restrict__ q, u64 nq, SortT st,
-                                  u64 *__restrict__ qstart, u64 *__restrict__ qend) {
-    const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= n_blocks) return;
-    if (!blocks[b].owns) { qstart[b] = 0; qend[b] = 0; return; }
-    qstart[b] = query_lower_bound_t(q, nq, st, sort_t(st, blocks[b].own_aa << 24));
-    const u64 nxt = b + 1 < n_blocks ? blocks[b + 1].own_aa : ~0ull;
-    qend[b] = nxt == ~0ull ? nq : query_lower_bound_t(q, nq, st, sort_t(st, nxt << 24) + (sort_t_lossy(st) ? 1 : 0));
+__global__ void k_match_partition(const Unit *__restrict__ units, u32 n_units, const mb_kmer *__restrict__ q, u64 nq, SortT st,
+                                  u64 *__restrict__ qstart) {
+    const u32 u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u > n_units) return;
+    qstart[u] = u == n_units ? nq : query_lower_bound_t(q, nq, st, units[u].t_lo);
 }
 
 } // namespace mb
