@@ -73,14 +73,19 @@ struct DbView {
 struct DbCursor { u64 word, vbefore, kidx; };
 
 // per-warp shared memory
+constexpr int MT_KEYS = 512;               // key array: MT_CAP_K entries padded with 0xFFFFFFFF to a power of two (bound-free search)
 struct __align__(128) WarpSmem {
     u16 w[2][MT_BUF_W];                    // word buffers (bulk-copy destinations), double buffered
-    u64 vals[MT_CAP_K];                    // decoded values of the current piece
+    u32 key[MT_KEYS];                      // amino-acid part of entry j minus aa0 (entries >= n: 0xFFFFFFFF)
+    u32 dna[MT_CAP_K];                     // low 24 bits (DNA part) of entry j
     u64 stage[MT_STAGE * 3];               // staged match records
     u32 hbits[MT_HB + 3];                  // bit j: k-mer j starts an amino-acid group; bit n: sentinel
     u32 qmin[32];                          // per query of the current 32-query slice: smallest distance in its group
     u64 mbar[2];                           // mbarriers of the two word buffers
+    u64 aa0;                               // amino-acid part of the piece's first entry
 };
+// value of entry j of the decoded piece
+__device__ __forceinline__ u64 piece_value(const WarpSmem &ws, u32 j) { return ((ws.aa0 + ws.key[j]) << 24) | ws.dna[j]; }
 
 // the part of the shared memory that the warps share (read only after set-up)
 struct MatchTables {
@@ -129,18 +134,31 @@ __device__ __forceinline__ void fetch_words(const DbView &db, WarpSmem &ws, int 
 
 // ---- warp-level decode of one piece -----------------------------------------------------------------------------
 // The piece's words lie in buf[pad, pad + wl) (buffer coordinates).  Decodes the deltas that END inside the piece
-// (getNextTargetKmer, KmerMatcher.h:282-297), leaves the first min(n_total, MT_CAP_K) absolute values in ws.vals and
-// the amino-acid group heads in ws.hbits (bit 0 is always set: a piece starts at a group start).  Returns n_total.
+// (getNextTargetKmer, KmerMatcher.h:282-297).  Of the first min(n_total, MT_CAP_K) k-mers it leaves the amino-acid part
+// relative to the first one's (ws.aa0) in ws.key, the DNA part in ws.dna and the amino-acid group heads in ws.hbits (bit 0
+// is always set: a piece starts at a group start); ws.key is padded with 0xFFFFFFFF up to MT_KEYS.  *n_fit = entries whose
+// relative amino-acid part fits 32 bits (the piece is cut before the first one that does not).  Returns n_total.
 // Warp-synchronous; every lane must call it.
-__device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pad, u32 wl, u64 vbefore) {
+__device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pad, u32 wl, u64 vbefore, u32 *n_fit) {
     const u32 lane = threadIdx.x & 31;
     const u32 l0 = lane * MT_R, end = pad + wl;
-    // my 20 words in five 64-bit registers
+    // my 20 words in five 64-bit registers; words outside the piece become zero words (no terminator, no payload), which
+    // leaves the sweeps free of range checks: leading zeros keep the empty delta empty, trailing zeros only shift a delta
+    // that nothing finishes
     u64 r[MT_R / 4];
     const u64 *b64 = reinterpret_cast<const u64 *>(buf + l0);
 #pragma unroll
     for (int i = 0; i < MT_R / 4; ++i) r[i] = b64[i];
+    if (l0 < pad || l0 + MT_R > end) {
+#pragma unroll
+        for (int i = 0; i < MT_R; ++i) {
+            const u32 idx = l0 + i;
+            if (idx < pad || idx >= end) r[i >> 2] &= ~(0xFFFFull << (16 * (i & 3)));
+        }
+    }
     if (lane < MT_HB + 3) ws.hbits[lane] = 0;
+#pragma unroll
+    for (int i = 0; i < MT_KEYS / 32; ++i) ws.key[lane + 32 * i] = 0xFFFFFFFFu;
     // words of an unfinished delta in front of my run (at most 4 for a valid stream), not before the piece start
     u64 carry = 0;
     if (l0 > pad && l0 < end) {
@@ -148,18 +166,29 @@ __device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pa
         while (st > pad && l0 - st < 4 && !(buf[st - 1] & 0x8000u)) --st;
         for (u32 k = st; k < l0; ++k) carry = (carry | buf[k]) << 15;
     }
-    // sweep 1: count and sum the deltas terminating in my run
+    // the piece's first k-mer ends within five words of its start, inside lane 0's run: its amino-acid part is the base of the keys
+    u64 aa0 = 0;
+    if (lane == 0) {
+        u64 d = 0;
+        for (u32 k = pad; k < end && k < pad + 5; ++k) {
+            const u32 frag = buf[k];
+            d = (d << 15) | (frag & 0x7FFFu);
+            if (frag & 0x8000u) break;
+        }
+        aa0 = (vbefore + d) >> 24;
+    }
+    aa0 = __shfl_sync(0xFFFFFFFFu, aa0, 0);
+    // sweep 1: count and sum the deltas terminating in my run (branch-free)
     u32 cnt = 0;
-    u64 sum = 0, diff = carry;
+    u64 sum = 0, diff = carry >> 15;                     // `carry` is kept pre-shifted; the sweeps shift on entry
 #pragma unroll
     for (int i = 0; i < MT_R; ++i) {
         const u32 frag = (u32) (r[i >> 2] >> (16 * (i & 3))) & 0xFFFFu;
-        const u32 idx = l0 + i;
-        const bool in = idx >= pad && idx < end;
-        if (in) {
-            if (frag & 0x8000u) { diff |= (frag & 0x7FFFu); sum += diff; ++cnt; diff = 0; }
-            else diff = (diff | frag) << 15;
-        }
+        const bool t = (frag & 0x8000u) != 0;
+        diff = (diff << 15) | (frag & 0x7FFFu);
+        sum += t ? diff : 0ull;
+        cnt += t ? 1u : 0u;
+        diff = t ? 0ull : diff;
     }
     // warp inclusive scan of (cnt, sum)
     u32 icnt = cnt;
@@ -171,30 +200,30 @@ __device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pa
         if (lane >= (u32) d) { icnt += tc; isum += ts; }
     }
     const u32 n_total = __shfl_sync(0xFFFFFFFFu, icnt, 31);
-    __syncwarp();                                        // hbits cleared
-    // sweep 2: absolute values and group heads
+    __syncwarp();                                        // hbits / key cleared
+    // sweep 2: keys, DNA parts and group heads of my k-mers
     u32 pos = icnt - cnt;
     const u32 pos0 = pos;
     u64 run = vbefore + (isum - sum);
     u32 heads = 0;                                       // bit k: my k-th k-mer is a head
-    diff = carry;
+    u32 fit = 0xFFFFFFFFu;                               // first of my entries whose key does not fit
+    diff = carry >> 15;
 #pragma unroll
     for (int i = 0; i < MT_R; ++i) {
         const u32 frag = (u32) (r[i >> 2] >> (16 * (i & 3))) & 0xFFFFu;
-        const u32 idx = l0 + i;
-        const bool in = idx >= pad && idx < end;
-        if (in) {
-            if (frag & 0x8000u) {
-                diff |= (frag & 0x7FFFu);
-                const u64 nv = run + diff;
-                if (pos < (u32) MT_CAP_K) {
-                    ws.vals[pos] = nv;
-                    if (pos == 0 || ((nv ^ run) >> 24) != 0) heads |= 1u << (pos - pos0);
-                }
-                run = nv;
-                ++pos;
-                diff = 0;
-            } else diff = (diff | frag) << 15;
+        diff = (diff << 15) | (frag & 0x7FFFu);
+        if (frag & 0x8000u) {
+            const u64 nv = run + diff;
+            if (pos < (u32) MT_CAP_K) {
+                const u64 rel = (nv >> 24) - aa0;
+                if (rel >= 0xFFFFFFFFull) fit = fit < pos ? fit : pos;
+                else ws.key[pos] = (u32) rel;
+                ws.dna[pos] = (u32) nv & 0xFFFFFFu;
+                if (pos == 0 || ((nv ^ run) >> 24) != 0) heads |= 1u << (pos - pos0);
+            }
+            run = nv;
+            ++pos;
+            diff = 0;
         }
     }
     if (heads) {
@@ -202,6 +231,9 @@ __device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pa
         atomicOr(&ws.hbits[wi], heads << sh);
         if (sh && (heads >> (32 - sh))) atomicOr(&ws.hbits[wi + 1], heads >> (32 - sh));
     }
+    if (lane == 0) ws.aa0 = aa0;
+    fit = __reduce_min_sync(0xFFFFFFFFu, fit);
+    *n_fit = fit;
     __syncwarp();
     return n_total;
 }
@@ -350,8 +382,8 @@ __device__ __forceinline__ void warp_flush(const MatchOut &mo, u64 *stage, u32 &
     __syncwarp();
 }
 
-// Warp-level emission for the streaming path: lane l adds the entries of ws.vals[0, ge) whose distance to its query is
-// <= maxh (cnt of them).  kbase: ordinal of ws.vals[0].
+// Warp-level emission for the streaming path: lane l adds the entries [0, ge) of the decoded piece whose distance to its
+// query is <= maxh (cnt of them).  kbase: ordinal of entry 0.
 template <bool ROUTED>
 __device__ __noinline__ void warp_emit_own(const DbView &db, u64 kbase, WarpSmem &ws, const MatchTables &tb, const MatchOut &mo, bool active,
                                            const mb_kmer &q, u32 ge, u32 maxh, u32 cnt, int format, u32 &fill) {
@@ -372,7 +404,7 @@ __device__ __noinline__ void warp_emit_own(const DbView &db, u64 kbase, WarpSmem
     if (active && cnt) {
         u64 o = base + incl - cnt;
         for (u32 j = 0; j < ge; ++j) {
-            const u64 t = ws.vals[j];
+            const u64 t = ws.dna[j];
             const u32 d = hamming_sum_lut(tb.lut2, q.value, t);
             if (d > maxh) continue;
             u64 rec[3];
@@ -393,16 +425,38 @@ __device__ __noinline__ void warp_emit_own(const DbView &db, u64 kbase, WarpSmem
     }
 }
 
-// synchronous fetch + decode of a piece at cursor g into word buffer `buf` (streaming path and follow-up pieces).
-// wl = words of the piece.  Returns n_total; *parity is the buffer's mbarrier phase (flipped here).
-__device__ __forceinline__ u32 load_piece(const DbView &db, WarpSmem &ws, int buf, u32 &parity, const DbCursor &g, u32 wl) {
+// Fetch (unless the words are already in flight) + wait + decode of the piece at cursor g in word buffer `buf`.
+// Returns n = entries of the piece that can be joined now (decoded, keys fit, candidates below kend) and sets
+// *complete = every one of them belongs to a complete amino-acid group (the piece reaches the end of the unit or of the
+// candidates).  `parity` holds the mbarrier phases of the two buffers in bits 0 and 1.
+__device__ __forceinline__ u32 open_piece(const DbView &db, WarpSmem &ws, int buf, u32 &parity, const DbCursor &g, u64 wlimit, u64 kend,
+                                          bool in_flight, u32 *wl_out, bool *complete) {
     const u32 lane = threadIdx.x & 31;
-    __syncwarp();
-    if (lane == 0) fetch_words(db, ws, buf, g.word, wl);
-    mbar_wait(&ws.mbar[buf], parity);
-    parity ^= 1u;
-    const u32 pad = (u32) (g.word & 7ull);
-    return decode_piece(ws, ws.w[buf], pad, wl, g.vbefore);
+    const u32 wl = (u32) (wlimit - g.word < (u64) MT_CAP_W ? wlimit - g.word : (u64) MT_CAP_W);
+    if (!in_flight) {
+        __syncwarp();
+        if (lane == 0) fetch_words(db, ws, buf, g.word, wl);
+    }
+    mbar_wait(&ws.mbar[buf], (parity >> buf) & 1u);
+    parity ^= 1u << buf;
+    u32 n_fit;
+    const u32 n_total = decode_piece(ws, ws.w[buf], (u32) (g.word & 7ull), wl, g.vbefore, &n_fit);
+    u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
+    bool all = g.word + wl >= wlimit && n_total <= (u32) MT_CAP_K;
+    if (n_fit < n) { n = n_fit; all = false; }
+    if ((u64) n >= kend - g.kidx) { n = (u32) (kend - g.kidx); all = true; }
+    *wl_out = wl;
+    *complete = all;
+    return n;
+}
+
+// cursor of entry `used` (>= 1) of the piece that was decoded at cursor g (wl words) in word buffer `buf`
+__device__ __forceinline__ DbCursor cursor_after(const WarpSmem &ws, int buf, const DbCursor &g, u32 wl, u32 used) {
+    DbCursor nx;
+    nx.word = (g.word & ~7ull) + word_after_kmer(ws.w[buf], (u32) (g.word & 7ull), wl, used);
+    nx.vbefore = piece_value(ws, used - 1);
+    nx.kidx = g.kidx + used;
+    return nx;
 }
 
 // Streaming two-pass join for an amino-acid group that does not fit one piece.  `c` sits on the group's first k-mer;
@@ -414,10 +468,10 @@ __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend
                                          const MatchOut &mo, int buf, u32 &parity, const mb_kmer *__restrict__ q, u64 qs, u64 qe,
                                          int format, u32 &fill) {
     const u32 lane = threadIdx.x & 31;
-    // the group's amino-acid part: value of its first k-mer
-    u32 wl = (u32) (wlimit - c.word < (u64) MT_CAP_W ? wlimit - c.word : (u64) MT_CAP_W);
-    load_piece(db, ws, buf, parity, c, wl);
-    const u64 gaa = ws.vals[0] >> 24;
+    u32 wl;
+    bool complete;
+    open_piece(db, ws, buf, parity, c, wlimit, kend, false, &wl, &complete);
+    const u64 gaa = ws.aa0;                              // the group's amino-acid part: that of its first k-mer
     DbCursor gend = c;                                   // becomes the cursor behind the group
     bool have_end = false;
     for (u64 qb = qs; qb < qe || !have_end; qb += 32) {
@@ -433,40 +487,33 @@ __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend
             if (phase == 1 && !any) break;
             DbCursor g = c;
             while (true) {
-                wl = (u32) (wlimit - g.word < (u64) MT_CAP_W ? wlimit - g.word : (u64) MT_CAP_W);
-                const u32 n_total = load_piece(db, ws, buf, parity, g, wl);
-                u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
-                if ((u64) n > kend - g.kidx) n = (u32) (kend - g.kidx);
+                const u32 n = open_piece(db, ws, buf, parity, g, wlimit, kend, false, &wl, &complete);
                 if (n == 0) { if (!have_end) { gend = g; have_end = true; } break; }
-                // first entry with another amino-acid part
+                // first entry with another amino-acid part (keys are relative to THIS piece's first entry)
+                const u64 aa_p = ws.aa0;
                 u32 ge = n;
                 for (u32 j0 = 0; j0 < n; j0 += 32) {
                     const u32 j = j0 + lane;
-                    const u32 m = __ballot_sync(0xFFFFFFFFu, j < n && (ws.vals[j] >> 24) != gaa);
+                    const u32 m = __ballot_sync(0xFFFFFFFFu, j < n && aa_p + ws.key[j] != gaa);
                     if (m) { ge = j0 + (u32) __ffs((int) m) - 1; break; }
                 }
-                const bool finished = ge < n || g.kidx + n >= kend || (g.word + wl >= wlimit && n == n_total);
+                const bool finished = ge < n || complete;
                 if (phase == 0) {
                     if (mine)
                         for (u32 j = 0; j < ge; ++j) {
-                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, ws.vals[j]);
+                            const u32 d = hamming_sum_lut(tb.lut2, qk.value, (u64) ws.dna[j]);
                             mind = d < mind ? d : mind;
                         }
                 } else {
                     u32 cnt = 0;
                     if (mine)
-                        for (u32 j = 0; j < ge; ++j) cnt += hamming_sum_lut(tb.lut2, qk.value, ws.vals[j]) <= maxh ? 1u : 0u;
+                        for (u32 j = 0; j < ge; ++j) cnt += hamming_sum_lut(tb.lut2, qk.value, (u64) ws.dna[j]) <= maxh ? 1u : 0u;
                     warp_emit_own<ROUTED>(db, g.kidx, ws, tb, mo, mine, qk, ge, maxh, cnt, format, fill);
                 }
                 // cursor behind the entries consumed from this piece
                 const u32 used = finished ? ge : n;
                 DbCursor nx = g;
-                if (used) {
-                    const u32 pad = (u32) (g.word & 7ull);
-                    nx.word = (g.word & ~7ull) + word_after_kmer(ws.w[buf], pad, wl, used);
-                    nx.vbefore = ws.vals[used - 1];
-                    nx.kidx = g.kidx + used;
-                }
+                if (used) nx = cursor_after(ws, buf, g, wl, used);
                 __syncwarp();
                 if (finished) { if (!have_end) { gend = nx; have_end = true; } break; }
                 g = nx;
@@ -480,19 +527,20 @@ __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend
 // ---- the join kernel ---------------------------------------------------------------------------------------------
 template <bool ROUTED>
 __global__ void __launch_bounds__(MT_THREADS, 3)
-k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *__restrict__ q, const u64 *__restrict__ qstart,
-        MatchOut mo_in, const Tables *__restrict__ tables, int format, u32 *unit_ticket, const Route *__restrict__ route_g) {
+k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *__restrict__ q,
+        const u64 *__restrict__ qstart, const __grid_constant__ MatchOut mo_in, const Tables *__restrict__ tables, int format,
+        u32 *unit_ticket, const Route *__restrict__ route_g) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ Route s_route;
-    MatchOut mo = mo_in;
-    mo.route = nullptr;
-    if (ROUTED) {                                   // multi-GPU: matches leave for their home rank (warp_flush_routed)
-        for (u32 i = threadIdx.x; i < sizeof(Route) / 8; i += MT_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
-        mo.route = &s_route;
-    }
+    __shared__ MatchOut s_mo;                        // routed form only: mo_in with the shared-memory copy of the route
     MatchTables &tb = *reinterpret_cast<MatchTables *>(smem_raw);
     const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpSmem &ws = *reinterpret_cast<WarpSmem *>(smem_raw + sizeof(MatchTables) + (size_t) warp * sizeof(WarpSmem));
+    if (ROUTED) {                                   // multi-GPU: matches leave for their home rank (warp_flush_routed)
+        for (u32 i = tid; i < sizeof(Route) / 8; i += MT_THREADS) reinterpret_cast<u64 *>(&s_route)[i] = reinterpret_cast<const u64 *>(route_g)[i];
+        if (tid == 0) { s_mo = mo_in; s_mo.route = &s_route; }
+    }
+    const MatchOut &mo = ROUTED ? s_mo : mo_in;
     {
         const uint4 *src2 = reinterpret_cast<const uint4 *>(tables->lut2);
         const uint4 *srcp = reinterpret_cast<const uint4 *>(tables->lutp);
@@ -505,18 +553,27 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
     __syncthreads();                                // tables, route and barriers are ready; the only block barrier
 
     u32 fill = 0;                                   // matches staged by this warp (warp-uniform)
-    u32 parity[2] = {0, 0};                         // mbarrier phases of the two word buffers
+    u32 parity = 0;                                 // mbarrier phases of the two word buffers (bits 0, 1)
 
-    // The words of unit `u` go to buffer `b`.  Only units with queries are fetched; returns whether a copy was issued.
-    // (lane 0 issues; all lanes compute the same unit facts from the same loads)
-    auto unit_facts = [&](u32 u, DbCursor &c, u64 &wend, u64 &kend, u64 &qs, u64 &qe) -> bool {
-        if (u >= n_units) return false;
-        const Unit a = units[u], z = units[u + 1];
-        c.word = a.word; c.vbefore = a.vbefore; c.kidx = a.kidx;
-        wend = z.word;
-        kend = z.kidx < db.n_kmers_eff ? z.kidx : db.n_kmers_eff;
-        qs = qstart[u]; qe = qstart[u + 1];
-        return qs < qe && a.kidx < kend;
+    // Asks for the words of unit u (buffer b) when the unit has queries and candidates; warms L2 with its query slice and
+    // info entries.  All lanes compute the same facts from the same loads; nothing is kept in registers.
+    auto prefetch_unit = [&](u32 u, int b) {
+        if (u >= n_units) return;
+        const u64 qs = qstart[u], qe = qstart[u + 1];
+        const u64 w0 = units[u].word, k0 = units[u].kidx, w1 = units[u + 1].word;
+        u64 k1 = units[u + 1].kidx;
+        if (k1 > db.n_kmers_eff) k1 = db.n_kmers_eff;
+        if (qs >= qe || k0 >= k1) return;
+        __syncwarp();
+        if (lane == 0) fetch_words(db, ws, b, w0, (u32) (w1 - w0 < (u64) MT_CAP_W ? w1 - w0 : (u64) MT_CAP_W));
+        u64 qn = qe - qs;
+        if (qn > 2048) qn = 2048;
+        const char *qp = reinterpret_cast<const char *>(q + qs);
+        for (u64 o = (u64) lane * 128; o < qn * 16; o += 32 * 128) prefetch_l2(qp + o);
+        u64 nk = k1 - k0;
+        if (nk > (u64) MT_CAP_K) nk = MT_CAP_K;
+        const char *inf = reinterpret_cast<const char *>(db.info + k0);
+        for (u64 o = (u64) lane * 128; o < nk * 4; o += 32 * 128) prefetch_l2(inf + o);
     };
 
     // tickets are drawn one unit ahead: `cur` is joined now, `nxt` has its words in flight
@@ -524,85 +581,65 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
     if (lane == 0) { cur = atomicAdd(unit_ticket, 1u); nxt = atomicAdd(unit_ticket, 1u); }
     cur = __shfl_sync(0xFFFFFFFFu, cur, 0);
     nxt = __shfl_sync(0xFFFFFFFFu, nxt, 0);
-    DbCursor c, cn;
-    u64 wend = 0, kend = 0, qs = 0, qe = 0, wend_n = 0, kend_n = 0, qs_n = 0, qe_n = 0;
-    bool have = unit_facts(cur, c, wend, kend, qs, qe);
     int buf = 0;
-    if (have && lane == 0) fetch_words(db, ws, buf, c.word, (u32) (wend - c.word < (u64) MT_CAP_W ? wend - c.word : (u64) MT_CAP_W));
+    prefetch_unit(cur, buf);
 
     while (cur < n_units) {
-        // next ticket + next unit's words (other buffer) + L2 warm-up of its queries and info entries
         u32 drawn = 0;
         if (lane == 0) drawn = atomicAdd(unit_ticket, 1u);
-        const bool have_n = unit_facts(nxt, cn, wend_n, kend_n, qs_n, qe_n);
-        if (have_n) {
-            if (lane == 0) fetch_words(db, ws, buf ^ 1, cn.word, (u32) (wend_n - cn.word < (u64) MT_CAP_W ? wend_n - cn.word : (u64) MT_CAP_W));
-            u64 qn = qe_n - qs_n;
-            if (qn > 2048) qn = 2048;
-            const char *qp = reinterpret_cast<const char *>(q + qs_n);
-            for (u64 o = (u64) lane * 128; o < qn * 16; o += 32 * 128) prefetch_l2(qp + o);
-            u64 nk = kend_n - cn.kidx;
-            if (nk > (u64) MT_CAP_K) nk = MT_CAP_K;
-            const char *inf = reinterpret_cast<const char *>(db.info + cn.kidx);
-            for (u64 o = (u64) lane * 128; o < nk * 4; o += 32 * 128) prefetch_l2(inf + o);
-            if (lane == 0 && nxt + 2 * gridDim.x * MT_WARPS < n_units) { prefetch_l2(units + nxt + 2 * gridDim.x * MT_WARPS); prefetch_l2(qstart + nxt + 2 * gridDim.x * MT_WARPS); }
-        }
+        prefetch_unit(nxt, buf ^ 1);
+        if (lane == 0 && nxt + 2 * gridDim.x * MT_WARPS < n_units) { prefetch_l2(units + nxt + 2 * gridDim.x * MT_WARPS); prefetch_l2(qstart + nxt + 2 * gridDim.x * MT_WARPS); }
 
-        if (have) {
-            bool first_piece = true;
+        // the current unit (the same facts prefetch_unit saw)
+        const u64 qs = qstart[cur], qe = qstart[cur + 1];
+        DbCursor c{units[cur].word, units[cur].vbefore, units[cur].kidx};
+        const u64 wend = units[cur + 1].word;
+        u64 kend = units[cur + 1].kidx;
+        if (kend > db.n_kmers_eff) kend = db.n_kmers_eff;
+        if (qs < qe && c.kidx < kend) {
+            bool in_flight = true;
             while (c.kidx < kend) {
-                const u32 wl = (u32) (wend - c.word < (u64) MT_CAP_W ? wend - c.word : (u64) MT_CAP_W);
-                u32 n_total;
-                if (first_piece) {
-                    mbar_wait(&ws.mbar[buf], parity[buf]);
-                    parity[buf] ^= 1u;
-                    n_total = decode_piece(ws, ws.w[buf], (u32) (c.word & 7ull), wl, c.vbefore);
-                    first_piece = false;
-                } else {
-                    n_total = load_piece(db, ws, buf, parity[buf], c, wl);
-                }
-                u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
-                if ((u64) n > kend - c.kidx) n = (u32) (kend - c.kidx);
+                u32 wl;
+                bool complete;
+                const u32 n = open_piece(db, ws, buf, parity, c, wend, kend, in_flight, &wl, &complete);
+                in_flight = false;
                 if (n == 0) break;
-                // every group of the piece is complete when the piece reaches the end of the unit (a unit is a whole number of
-                // groups) or the end of the candidates; otherwise the last group may continue and is left to the next piece
-                const bool whole = (c.word + wl >= wend && n_total <= (u32) MT_CAP_K) || c.kidx + n >= kend;
+                // a piece that does not reach the end of the unit leaves its last group, which may continue, to the next piece
                 u32 proc = n;
-                if (!whole) {
+                if (!complete) {
                     proc = last_head_before(ws, n);
                     if (proc == 0) {
-                        giant_group<ROUTED>(db, c, kend, wend, ws, tb, mo, buf, parity[buf], q, qs, qe, format, fill);
+                        giant_group<ROUTED>(db, c, kend, wend, ws, tb, mo, buf, parity, q, qs, qe, format, fill);
                         continue;
                     }
                 }
                 if (lane == 0) atomicOr(&ws.hbits[proc >> 5], 1u << (proc & 31));      // sentinel head behind the last entry
                 __syncwarp();
 
-                // ---- join the query slice against ws.vals[0, proc) ----
-                const u64 key_lo = ws.vals[0] & ~0xFFFFFFull, key_hi = ws.vals[proc - 1] | 0xFFFFFFull;
+                // ---- join the query slice against entries [0, proc) ----
+                const u64 aa0 = ws.aa0;
+                const u32 key_hi = ws.key[proc - 1];
                 u32 top = 1;
                 while (top * 2 <= proc) top *= 2;
                 ulonglong2 v_next = make_ulonglong2(0, 0);
                 if (qs + lane < qe) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qs + lane));
                 for (u64 qb = qs; qb < qe; qb += 32) {
-                    mb_kmer qk;
-                    qk.value = v_next.x; qk.qinfo = v_next.y;
+                    const u64 qvalue = v_next.x, qinfo = v_next.y;
                     const bool mine = qb + lane < qe;
                     if (qb + 32 + lane < qe) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qb + 32 + lane));
                     // (1) every lane: its query's amino-acid group [lo, lo + ncand) in the piece
                     u32 lo = 0, ncand = 0;
-                    const u64 key = qk.value & ~0xFFFFFFull;
-                    if (mine && key >= key_lo && key <= key_hi) {
-                        // branch-free lower bound: number of entries below the key
+                    const u64 rel = (qvalue >> 24) - aa0;              // (wraps to a huge value below the piece)
+                    if (mine && rel <= (u64) key_hi) {
+                        // bound-free lower bound in the padded key array: number of entries below the key
+                        const u32 key = (u32) rel;
                         u32 pos = 0;
-                        for (u32 step = top; step; step >>= 1) {
-                            const u32 nx = pos + step;
-                            if (nx <= proc && ws.vals[nx - 1] < key) pos = nx;
-                        }
-                        if (pos < proc && (ws.vals[pos] >> 24) == (key >> 24)) {
+                        for (u32 step = top; step; step >>= 1)
+                            if (ws.key[pos + step - 1] < key) pos += step;
+                        if (ws.key[pos] == key && pos < proc) {
                             // pos is the group's head; the group ends at the next head (the sentinel bounds the scan)
                             lo = pos;
-                            u32 b = pos + 1;
+                            const u32 b = pos + 1;
                             u32 m = ws.hbits[b >> 5] >> (b & 31);
                             u32 hi;
                             if (m) hi = b + (u32) __ffs((int) m) - 1;
@@ -625,7 +662,7 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
                     const u32 total = __shfl_sync(0xFFFFFFFFu, incl, 31);
                     if (total == 0) continue;
                     const u32 excl = incl - ncand;
-                    const u32 q24 = (u32) qk.value & 0xFFFFFFu;
+                    const u32 q24 = (u32) qvalue & 0xFFFFFFu;
                     ws.qmin[lane] = 255u;
                     __syncwarp();
                     const u32 rounds = (total + 31) / 32;
@@ -648,7 +685,7 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
                             j = o_lo + (p - o_excl);
                             // the candidate's info entry (make_match reads it in the emit pass) is asked for now
                             asm volatile("prefetch.global.L1 [%0];" ::"l"(db.info + c.kidx + j));
-                            const u32 t24 = (u32) ws.vals[j] & 0xFFFFFFu;
+                            const u32 t24 = ws.dna[j];
                             dd = t24 == o_q ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, (u64) t24);
                             atomicMin(&ws.qmin[owner], dd);
                         }
@@ -675,7 +712,7 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
                             dd = 255; j = 0;
                             if (p < total) {
                                 j = o_lo + (p - o_excl);
-                                const u32 t24 = (u32) ws.vals[j] & 0xFFFFFFu;
+                                const u32 t24 = ws.dna[j];
                                 dd = t24 == o_q ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, (u64) t24);
                             }
                         }
@@ -683,16 +720,16 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
                         const u32 maxh = mind * 2 < 7 ? mind * 2 : 7;
                         const bool ok = p < total && dd <= maxh;
                         const u32 okmask = __ballot_sync(0xFFFFFFFFu, ok);
-                        // the owner's full query record (value and qinfo) for the match
+                        // the owner's query record for the match (only the DNA part of its value is needed)
                         mb_kmer oq;
-                        oq.value = __shfl_sync(0xFFFFFFFFu, qk.value, owner);
-                        oq.qinfo = __shfl_sync(0xFFFFFFFFu, qk.qinfo, owner);
+                        oq.value = (u64) __shfl_sync(0xFFFFFFFFu, q24, owner);
+                        oq.qinfo = __shfl_sync(0xFFFFFFFFu, qinfo, owner);
                         if (okmask == 0) continue;
                         const u32 nok = (u32) __popc(okmask);
                         if (fill + nok > MT_STAGE) warp_flush<ROUTED>(mo, ws.stage, fill);
                         if (ok) {
                             u64 rec[3];
-                            make_match(db, mo, tb.lutp, oq, ws.vals[j], c.kidx + j, dd, format, rec);
+                            make_match(db, mo, tb.lutp, oq, (u64) ws.dna[j], c.kidx + j, dd, format, rec);
                             const u32 o = fill + (u32) __popc(okmask & ((1u << lane) - 1u));
                             ws.stage[o * 3] = rec[0]; ws.stage[o * 3 + 1] = rec[1]; ws.stage[o * 3 + 2] = rec[2];
                         }
@@ -702,18 +739,13 @@ k_match(DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *_
                 }
                 // behind the entries joined: the next piece of this unit, if any
                 if (c.kidx + proc >= kend) break;
-                {
-                    const u32 pad = (u32) (c.word & 7ull);
-                    const u64 nw = (c.word & ~7ull) + word_after_kmer(ws.w[buf], pad, wl, proc);
-                    const u64 nv = ws.vals[proc - 1];
-                    __syncwarp();
-                    c.word = nw; c.vbefore = nv; c.kidx += proc;
-                }
+                const DbCursor nx = cursor_after(ws, buf, c, wl, proc);
+                __syncwarp();
+                c = nx;
             }
         }
         cur = nxt;
         nxt = __shfl_sync(0xFFFFFFFFu, drawn, 0);
-        c = cn; wend = wend_n; kend = kend_n; qs = qs_n; qe = qe_n; have = have_n;
         buf ^= 1;
     }
     warp_flush<ROUTED>(mo, ws.stage, fill);
@@ -845,7 +877,7 @@ k_db_raw_own(DbView db, u64 n_raw, const u64 *__restrict__ raw_kidx, const u64 *
 
 // plain decode of the resident stream (parity tap): one warp per unit writes the values of its k-mers
 __global__ void __launch_bounds__(MT_THREADS)
-k_db_decode(DbView db, const Unit *__restrict__ units, u32 n_units, u64 *__restrict__ values) {
+k_db_decode(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n_units, u64 *__restrict__ values) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem &ws = *reinterpret_cast<WarpSmem *>(smem_raw + (size_t) warp * sizeof(WarpSmem));
@@ -857,18 +889,15 @@ k_db_decode(DbView db, const Unit *__restrict__ units, u32 n_units, u64 *__restr
         DbCursor c{units[u].word, units[u].vbefore, units[u].kidx};
         const u64 wend = units[u + 1].word, kend = units[u + 1].kidx;
         while (c.kidx < kend) {
-            const u32 wl = (u32) (wend - c.word < (u64) MT_CAP_W ? wend - c.word : (u64) MT_CAP_W);
-            const u32 n_total = load_piece(db, ws, 0, parity, c, wl);
-            u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
-            if ((u64) n > kend - c.kidx) n = (u32) (kend - c.kidx);
+            u32 wl;
+            bool complete;
+            const u32 n = open_piece(db, ws, 0, parity, c, wend, kend, false, &wl, &complete);
             if (n == 0) break;
-            for (u32 j = lane; j < n; j += 32) values[c.kidx + j] = ws.vals[j];
+            for (u32 j = lane; j < n; j += 32) values[c.kidx + j] = piece_value(ws, j);
             if (c.kidx + n >= kend) break;
-            const u32 pad = (u32) (c.word & 7ull);
-            const u64 nw = (c.word & ~7ull) + word_after_kmer(ws.w[0], pad, wl, n);
-            const u64 nv = ws.vals[n - 1];
+            const DbCursor nx = cursor_after(ws, 0, c, wl, n);
             __syncwarp();
-            c.word = nw; c.vbefore = nv; c.kidx += n;
+            c = nx;
         }
     }
 }

@@ -10,7 +10,7 @@ rep=gpurun_out/${TAG}.ncu-rep
 if [ -f $rep ]; then
   ncu -i $rep --page raw --csv > gpurun_out/${TAG}_raw.csv 2>/dev/null
   python scripts/ncu_show.py < gpurun_out/${TAG}_raw.csv > gpurun_out/${TAG}_summary.txt 2>&1
-  python scripts/ncu_lines.py $rep 70 > gpurun_out/${TAG}_lines.txt 2>&1
+  python scripts/ncu_lines.py $rep ${NCU_TOP:-70} > gpurun_out/${TAG}_lines.txt 2>&1
   cat gpurun_out/${TAG}_summary.txt
   head -45 gpurun_out/${TAG}_lines.txt
   rm -f $rep
