@@ -39,15 +39,27 @@
 
 namespace mb {
 
-constexpr int UN_W = 512;                  // raw block of the load-time index: at most one unit starts per raw block
+#ifndef MB_UN_W
+#define MB_UN_W 448
+#endif
+constexpr int UN_W = MB_UN_W;               // raw block of the load-time index: at most one unit starts per raw block (multiple of 32)
 constexpr int MT_THREADS = 256;
 constexpr int MT_WARPS = MT_THREADS / 32;
 constexpr int MT_BUF_W = 640;              // words of one word buffer (32 lanes x 20 words)
 constexpr int MT_R = MT_BUF_W / 32;        // words per lane
 constexpr int MT_CAP_W = MT_BUF_W - 8;     // words of one piece (the buffer starts at an 8-word boundary of the stream)
-constexpr int MT_CAP_K = 384;              // k-mers of one piece
+constexpr int MT_CAP_K = 256;              // k-mers of one piece
 constexpr int MT_HB = MT_CAP_K / 32 + 1;   // head-bit words (one extra bit: the sentinel behind the last k-mer)
-constexpr int MT_STAGE = 64;               // matches staged per warp before a flush
+#ifndef MB_MT_STAGE
+#define MB_MT_STAGE 64
+#endif
+#ifndef MB_MT_MIN_CTAS
+#define MB_MT_MIN_CTAS 4
+#endif
+#ifndef MB_MT_INFO_PF
+#define MB_MT_INFO_PF 1
+#endif
+constexpr int MT_STAGE = MB_MT_STAGE;      // matches staged per warp before a flush
 constexpr int DB_PAD = MT_BUF_W + 64;      // zero words the device stream is padded with
 
 static_assert(MT_R * 2 % 8 == 0, "a lane's run must be whole 64-bit words");
@@ -73,15 +85,16 @@ struct DbView {
 struct DbCursor { u64 word, vbefore, kidx; };
 
 // per-warp shared memory
-constexpr int MT_KEYS = 512;               // key array: MT_CAP_K entries padded with 0xFFFFFFFF to a power of two (bound-free search)
+constexpr int MT_KEYS = 256;               // key array: MT_CAP_K entries padded with 0xFFFFFFFF to a power of two (bound-free search)
+static_assert(MT_KEYS >= MT_CAP_K && (MT_KEYS & (MT_KEYS - 1)) == 0, "key array: power of two that holds a piece");
 struct __align__(128) WarpSmem {
-    u16 w[2][MT_BUF_W];                    // word buffers (bulk-copy destinations), double buffered
+    u16 w[MT_BUF_W];                       // word buffer (bulk-copy destination); free again as soon as a piece is decoded
     u32 key[MT_KEYS];                      // amino-acid part of entry j minus aa0 (entries >= n: 0xFFFFFFFF)
     u32 dna[MT_CAP_K];                     // low 24 bits (DNA part) of entry j
     u64 stage[MT_STAGE * 3];               // staged match records
     u32 hbits[MT_HB + 3];                  // bit j: k-mer j starts an amino-acid group; bit n: sentinel
     u32 qmin[32];                          // per query of the current 32-query slice: smallest distance in its group
-    u64 mbar[2];                           // mbarriers of the two word buffers
+    u64 mbar;                              // mbarrier of the word buffer
     u64 aa0;                               // amino-acid part of the piece's first entry
 };
 // value of entry j of the decoded piece
@@ -124,12 +137,13 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, u32 bytes, 
 
 // One lane asks for the words of a piece that starts at stream word `word` and has `wl` words (<= MT_CAP_W): the copy
 // starts at the 8-word boundary below `word`.  Returns nothing; the warp later waits on the buffer's mbarrier.
-__device__ __forceinline__ void fetch_words(const DbView &db, WarpSmem &ws, int buf, u64 word, u32 wl) {
+__device__ __forceinline__ void fetch_words(const DbView &db, WarpSmem &ws, u64 word, u32 wl) {
     const u64 wbase = word & ~7ull;
     const u32 pad = (u32) (word - wbase);
     const u32 bytes = ((pad + wl + 7u) >> 3) << 4;
-    mbar_expect_tx(&ws.mbar[buf], bytes);
-    bulk_g2s(ws.w[buf], db.words + wbase, bytes, &ws.mbar[buf]);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // the lanes' reads of the buffer precede the asynchronous write
+    mbar_expect_tx(&ws.mbar, bytes);
+    bulk_g2s(ws.w, db.words + wbase, bytes, &ws.mbar);
 }
 
 // ---- warp-level decode of one piece -----------------------------------------------------------------------------
@@ -428,19 +442,19 @@ __device__ __noinline__ void warp_emit_own(const DbView &db, u64 kbase, WarpSmem
 // Fetch (unless the words are already in flight) + wait + decode of the piece at cursor g in word buffer `buf`.
 // Returns n = entries of the piece that can be joined now (decoded, keys fit, candidates below kend) and sets
 // *complete = every one of them belongs to a complete amino-acid group (the piece reaches the end of the unit or of the
-// candidates).  `parity` holds the mbarrier phases of the two buffers in bits 0 and 1.
-__device__ __forceinline__ u32 open_piece(const DbView &db, WarpSmem &ws, int buf, u32 &parity, const DbCursor &g, u64 wlimit, u64 kend,
+// candidates).  `parity` is the mbarrier phase of the word buffer.
+__device__ __forceinline__ u32 open_piece(const DbView &db, WarpSmem &ws, u32 &parity, const DbCursor &g, u64 wlimit, u64 kend,
                                           bool in_flight, u32 *wl_out, bool *complete) {
     const u32 lane = threadIdx.x & 31;
     const u32 wl = (u32) (wlimit - g.word < (u64) MT_CAP_W ? wlimit - g.word : (u64) MT_CAP_W);
     if (!in_flight) {
         __syncwarp();
-        if (lane == 0) fetch_words(db, ws, buf, g.word, wl);
+        if (lane == 0) fetch_words(db, ws, g.word, wl);
     }
-    mbar_wait(&ws.mbar[buf], (parity >> buf) & 1u);
-    parity ^= 1u << buf;
+    mbar_wait(&ws.mbar, parity);
+    parity ^= 1u;
     u32 n_fit;
-    const u32 n_total = decode_piece(ws, ws.w[buf], (u32) (g.word & 7ull), wl, g.vbefore, &n_fit);
+    const u32 n_total = decode_piece(ws, ws.w, (u32) (g.word & 7ull), wl, g.vbefore, &n_fit);
     u32 n = n_total < (u32) MT_CAP_K ? n_total : (u32) MT_CAP_K;
     bool all = g.word + wl >= wlimit && n_total <= (u32) MT_CAP_K;
     if (n_fit < n) { n = n_fit; all = false; }
@@ -450,10 +464,10 @@ __device__ __forceinline__ u32 open_piece(const DbView &db, WarpSmem &ws, int bu
     return n;
 }
 
-// cursor of entry `used` (>= 1) of the piece that was decoded at cursor g (wl words) in word buffer `buf`
-__device__ __forceinline__ DbCursor cursor_after(const WarpSmem &ws, int buf, const DbCursor &g, u32 wl, u32 used) {
+// cursor of entry `used` (>= 1) of the piece that was decoded at cursor g (wl words; its words are still in the buffer)
+__device__ __forceinline__ DbCursor cursor_after(const WarpSmem &ws, const DbCursor &g, u32 wl, u32 used) {
     DbCursor nx;
-    nx.word = (g.word & ~7ull) + word_after_kmer(ws.w[buf], (u32) (g.word & 7ull), wl, used);
+    nx.word = (g.word & ~7ull) + word_after_kmer(ws.w, (u32) (g.word & 7ull), wl, used);
     nx.vbefore = piece_value(ws, used - 1);
     nx.kidx = g.kidx + used;
     return nx;
@@ -465,12 +479,12 @@ __device__ __forceinline__ DbCursor cursor_after(const WarpSmem &ws, int buf, co
 // `c` is the cursor of the first k-mer behind the group.
 template <bool ROUTED>
 __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend, u64 wlimit, WarpSmem &ws, const MatchTables &tb,
-                                         const MatchOut &mo, int buf, u32 &parity, const mb_kmer *__restrict__ q, u64 qs, u64 qe,
+                                         const MatchOut &mo, u32 &parity, const mb_kmer *__restrict__ q, u64 qs, u64 qe,
                                          int format, u32 &fill) {
     const u32 lane = threadIdx.x & 31;
     u32 wl;
     bool complete;
-    open_piece(db, ws, buf, parity, c, wlimit, kend, false, &wl, &complete);
+    open_piece(db, ws, parity, c, wlimit, kend, false, &wl, &complete);
     const u64 gaa = ws.aa0;                              // the group's amino-acid part: that of its first k-mer
     DbCursor gend = c;                                   // becomes the cursor behind the group
     bool have_end = false;
@@ -487,7 +501,7 @@ __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend
             if (phase == 1 && !any) break;
             DbCursor g = c;
             while (true) {
-                const u32 n = open_piece(db, ws, buf, parity, g, wlimit, kend, false, &wl, &complete);
+                const u32 n = open_piece(db, ws, parity, g, wlimit, kend, false, &wl, &complete);
                 if (n == 0) { if (!have_end) { gend = g; have_end = true; } break; }
                 // first entry with another amino-acid part (keys are relative to THIS piece's first entry)
                 const u64 aa_p = ws.aa0;
@@ -513,7 +527,7 @@ __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend
                 // cursor behind the entries consumed from this piece
                 const u32 used = finished ? ge : n;
                 DbCursor nx = g;
-                if (used) nx = cursor_after(ws, buf, g, wl, used);
+                if (used) nx = cursor_after(ws, g, wl, used);
                 __syncwarp();
                 if (finished) { if (!have_end) { gend = nx; have_end = true; } break; }
                 g = nx;
@@ -526,7 +540,7 @@ __device__ __noinline__ void giant_group(const DbView &db, DbCursor &c, u64 kend
 
 // ---- the join kernel ---------------------------------------------------------------------------------------------
 template <bool ROUTED>
-__global__ void __launch_bounds__(MT_THREADS, 3)
+__global__ void __launch_bounds__(MT_THREADS, MB_MT_MIN_CTAS)
 k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n_units, const mb_kmer *__restrict__ q,
         const u64 *__restrict__ qstart, const __grid_constant__ MatchOut mo_in, const Tables *__restrict__ tables, int format,
         u32 *unit_ticket, const Route *__restrict__ route_g) {
@@ -548,16 +562,16 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
         uint4 *dp = reinterpret_cast<uint4 *>(tb.lutp);
         for (u32 i = tid; i < 4096 / 16; i += MT_THREADS) { d2[i] = __ldg(src2 + i); dp[i] = __ldg(srcp + i); }
     }
-    if (lane == 0) { mbar_init(&ws.mbar[0], 1); mbar_init(&ws.mbar[1], 1); }
+    if (lane == 0) mbar_init(&ws.mbar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();                                // tables, route and barriers are ready; the only block barrier
 
     u32 fill = 0;                                   // matches staged by this warp (warp-uniform)
-    u32 parity = 0;                                 // mbarrier phases of the two word buffers (bits 0, 1)
+    u32 parity = 0;                                 // mbarrier phase of the word buffer
 
-    // Asks for the words of unit u (buffer b) when the unit has queries and candidates; warms L2 with its query slice and
-    // info entries.  All lanes compute the same facts from the same loads; nothing is kept in registers.
-    auto prefetch_unit = [&](u32 u, int b) {
+    // Asks for the words of unit u when the unit has queries and candidates; warms L2 with its query slice and info
+    // entries.  All lanes compute the same facts from the same loads; nothing is kept in registers.
+    auto prefetch_unit = [&](u32 u) {
         if (u >= n_units) return;
         const u64 qs = qstart[u], qe = qstart[u + 1];
         const u64 w0 = units[u].word, k0 = units[u].kidx, w1 = units[u + 1].word;
@@ -565,7 +579,7 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
         if (k1 > db.n_kmers_eff) k1 = db.n_kmers_eff;
         if (qs >= qe || k0 >= k1) return;
         __syncwarp();
-        if (lane == 0) fetch_words(db, ws, b, w0, (u32) (w1 - w0 < (u64) MT_CAP_W ? w1 - w0 : (u64) MT_CAP_W));
+        if (lane == 0) fetch_words(db, ws, w0, (u32) (w1 - w0 < (u64) MT_CAP_W ? w1 - w0 : (u64) MT_CAP_W));
         u64 qn = qe - qs;
         if (qn > 2048) qn = 2048;
         const char *qp = reinterpret_cast<const char *>(q + qs);
@@ -576,18 +590,18 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
         for (u64 o = (u64) lane * 128; o < nk * 4; o += 32 * 128) prefetch_l2(inf + o);
     };
 
-    // tickets are drawn one unit ahead: `cur` is joined now, `nxt` has its words in flight
+    // tickets are drawn one unit ahead: `cur` is joined now; the words of `nxt` are asked for as soon as the last piece of
+    // `cur` is decoded (the decode keeps nothing in the word buffer), so they arrive while `cur` is being joined
     u32 cur = 0, nxt = 0;
     if (lane == 0) { cur = atomicAdd(unit_ticket, 1u); nxt = atomicAdd(unit_ticket, 1u); }
     cur = __shfl_sync(0xFFFFFFFFu, cur, 0);
     nxt = __shfl_sync(0xFFFFFFFFu, nxt, 0);
-    int buf = 0;
-    prefetch_unit(cur, buf);
+    prefetch_unit(cur);
 
     while (cur < n_units) {
         u32 drawn = 0;
         if (lane == 0) drawn = atomicAdd(unit_ticket, 1u);
-        prefetch_unit(nxt, buf ^ 1);
+        bool asked = false;                          // the words of `nxt` have been asked for
         if (lane == 0 && nxt + 2 * gridDim.x * MT_WARPS < n_units) { prefetch_l2(units + nxt + 2 * gridDim.x * MT_WARPS); prefetch_l2(qstart + nxt + 2 * gridDim.x * MT_WARPS); }
 
         // the current unit (the same facts prefetch_unit saw)
@@ -601,15 +615,16 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
             while (c.kidx < kend) {
                 u32 wl;
                 bool complete;
-                const u32 n = open_piece(db, ws, buf, parity, c, wend, kend, in_flight, &wl, &complete);
+                const u32 n = open_piece(db, ws, parity, c, wend, kend, in_flight, &wl, &complete);
                 in_flight = false;
                 if (n == 0) break;
+                if (complete && !asked) { prefetch_unit(nxt); asked = true; }       // no further piece of this unit: the buffer is free
                 // a piece that does not reach the end of the unit leaves its last group, which may continue, to the next piece
                 u32 proc = n;
                 if (!complete) {
                     proc = last_head_before(ws, n);
                     if (proc == 0) {
-                        giant_group<ROUTED>(db, c, kend, wend, ws, tb, mo, buf, parity, q, qs, qe, format, fill);
+                        giant_group<ROUTED>(db, c, kend, wend, ws, tb, mo, parity, q, qs, qe, format, fill);
                         continue;
                     }
                 }
@@ -684,7 +699,7 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
                         if (p < total) {
                             j = o_lo + (p - o_excl);
                             // the candidate's info entry (make_match reads it in the emit pass) is asked for now
-                            asm volatile("prefetch.global.L1 [%0];" ::"l"(db.info + c.kidx + j));
+                            if (MB_MT_INFO_PF) asm volatile("prefetch.global.L1 [%0];" ::"l"(db.info + c.kidx + j));
                             const u32 t24 = ws.dna[j];
                             dd = t24 == o_q ? 0u : hamming_sum_lut(tb.lut2, (u64) o_q, (u64) t24);
                             atomicMin(&ws.qmin[owner], dd);
@@ -739,14 +754,14 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
                 }
                 // behind the entries joined: the next piece of this unit, if any
                 if (c.kidx + proc >= kend) break;
-                const DbCursor nx = cursor_after(ws, buf, c, wl, proc);
+                const DbCursor nx = cursor_after(ws, c, wl, proc);
                 __syncwarp();
                 c = nx;
             }
         }
+        if (!asked) prefetch_unit(nxt);
         cur = nxt;
         nxt = __shfl_sync(0xFFFFFFFFu, drawn, 0);
-        buf ^= 1;
     }
     warp_flush<ROUTED>(mo, ws.stage, fill);
 }
@@ -881,7 +896,7 @@ k_db_decode(const __grid_constant__ DbView db, const Unit *__restrict__ units, u
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem &ws = *reinterpret_cast<WarpSmem *>(smem_raw + (size_t) warp * sizeof(WarpSmem));
-    if (lane == 0) { mbar_init(&ws.mbar[0], 1); mbar_init(&ws.mbar[1], 1); }
+    if (lane == 0) mbar_init(&ws.mbar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     u32 parity = 0;
@@ -891,11 +906,11 @@ k_db_decode(const __grid_constant__ DbView db, const Unit *__restrict__ units, u
         while (c.kidx < kend) {
             u32 wl;
             bool complete;
-            const u32 n = open_piece(db, ws, 0, parity, c, wend, kend, false, &wl, &complete);
+            const u32 n = open_piece(db, ws, parity, c, wend, kend, false, &wl, &complete);
             if (n == 0) break;
             for (u32 j = lane; j < n; j += 32) values[c.kidx + j] = piece_value(ws, j);
             if (c.kidx + n >= kend) break;
-            const DbCursor nx = cursor_after(ws, 0, c, wl, n);
+            const DbCursor nx = cursor_after(ws, c, wl, n);
             __syncwarp();
             c = nx;
         }
