@@ -36,6 +36,7 @@
 // grows the buffer and reruns (the reference's retry, Classifier.cpp:127-131).
 #pragma once
 #include "mb_common.cuh"
+#include <cstddef>
 
 namespace mb {
 
@@ -90,13 +91,14 @@ static_assert(MT_KEYS >= MT_CAP_K && (MT_KEYS & (MT_KEYS - 1)) == 0, "key array:
 struct __align__(128) WarpSmem {
     u16 w[MT_BUF_W];                       // word buffer (bulk-copy destination); free again as soon as a piece is decoded
     u32 key[MT_KEYS];                      // amino-acid part of entry j minus aa0 (entries >= n: 0xFFFFFFFF)
-    u32 dna[MT_CAP_K];                     // low 24 bits (DNA part) of entry j
+    u32 dna[MT_CAP_K];                     // low 24 bits (DNA part) of entry j; directly behind `key` (decode_piece relies on it)
     u64 stage[MT_STAGE * 3];               // staged match records
     u32 hbits[MT_HB + 3];                  // bit j: k-mer j starts an amino-acid group; bit n: sentinel
     u32 qmin[32];                          // per query of the current 32-query slice: smallest distance in its group
     u64 mbar;                              // mbarrier of the word buffer
     u64 aa0;                               // amino-acid part of the piece's first entry
 };
+static_assert(offsetof(WarpSmem, dna) == offsetof(WarpSmem, key) + MT_KEYS * sizeof(u32), "dna follows key");
 // value of entry j of the decoded piece
 __device__ __forceinline__ u64 piece_value(const WarpSmem &ws, u32 j) { return ((ws.aa0 + ws.key[j]) << 24) | ws.dna[j]; }
 
@@ -170,7 +172,6 @@ __device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pa
             if (idx < pad || idx >= end) r[i >> 2] &= ~(0xFFFFull << (16 * (i & 3)));
         }
     }
-    if (lane < MT_HB + 3) ws.hbits[lane] = 0;
 #pragma unroll
     for (int i = 0; i < MT_KEYS / 32; ++i) ws.key[lane + 32 * i] = 0xFFFFFFFFu;
     // words of an unfinished delta in front of my run (at most 4 for a valid stream), not before the piece start
@@ -214,39 +215,63 @@ __device__ __forceinline__ u32 decode_piece(WarpSmem &ws, const u16 *buf, u32 pa
         if (lane >= (u32) d) { icnt += tc; isum += ts; }
     }
     const u32 n_total = __shfl_sync(0xFFFFFFFFu, icnt, 31);
-    __syncwarp();                                        // hbits / key cleared
-    // sweep 2: keys, DNA parts and group heads of my k-mers
-    u32 pos = icnt - cnt;
-    const u32 pos0 = pos;
+    __syncwarp();                                        // key array cleared
+    // sweep 2: keys and DNA parts of my k-mers.  The key is the low 32 bits of (amino-acid part - aa0); whether every key of
+    // the piece fits is checked once, on the largest one (the last k-mer decoded), below.
+    const u32 pos0 = icnt - cnt;
     u64 run = vbefore + (isum - sum);
-    u32 heads = 0;                                       // bit k: my k-th k-mer is a head
-    u32 fit = 0xFFFFFFFFu;                               // first of my entries whose key does not fit
+    u32 *kp = ws.key + pos0;                             // ws.dna lies MT_KEYS words behind ws.key
+    u32 *const kend_p = ws.key + MT_CAP_K;
+    const u32 aa0_lo = (u32) aa0;
     diff = carry >> 15;
 #pragma unroll
     for (int i = 0; i < MT_R; ++i) {
         const u32 frag = (u32) (r[i >> 2] >> (16 * (i & 3))) & 0xFFFFu;
         diff = (diff << 15) | (frag & 0x7FFFu);
         if (frag & 0x8000u) {
-            const u64 nv = run + diff;
-            if (pos < (u32) MT_CAP_K) {
-                const u64 rel = (nv >> 24) - aa0;
-                if (rel >= 0xFFFFFFFFull) fit = fit < pos ? fit : pos;
-                else ws.key[pos] = (u32) rel;
-                ws.dna[pos] = (u32) nv & 0xFFFFFFu;
-                if (pos == 0 || ((nv ^ run) >> 24) != 0) heads |= 1u << (pos - pos0);
+            run += diff;
+            if (kp < kend_p) {
+                kp[0] = (u32) (run >> 24) - aa0_lo;
+                kp[MT_KEYS] = (u32) run & 0xFFFFFFu;
             }
-            run = nv;
-            ++pos;
+            ++kp;
             diff = 0;
         }
     }
-    if (heads) {
-        const u32 wi = pos0 >> 5, sh = pos0 & 31;
-        atomicOr(&ws.hbits[wi], heads << sh);
-        if (sh && (heads >> (32 - sh))) atomicOr(&ws.hbits[wi + 1], heads >> (32 - sh));
+    // amino-acid parts relative to aa0 that do not fit 32 bits (a sparse region): the piece is cut before the first such
+    // entry.  The values are ascending, so the last k-mer any lane decoded tells whether that can happen at all.
+    u32 fit = 0xFFFFFFFFu;
+    if (__any_sync(0xFFFFFFFFu, cnt != 0 && ((run >> 24) - aa0) >= 0xFFFFFFFFull)) {
+        u32 pos = pos0;
+        u64 v = vbefore + (isum - sum);
+        diff = carry >> 15;
+        for (int i = 0; i < MT_R; ++i) {
+            const u32 frag = (u32) (r[i >> 2] >> (16 * (i & 3))) & 0xFFFFu;
+            diff = (diff << 15) | (frag & 0x7FFFu);
+            if (frag & 0x8000u) {
+                v += diff;
+                if (((v >> 24) - aa0) >= 0xFFFFFFFFull) {
+                    fit = fit < pos ? fit : pos;
+                    if (pos < (u32) MT_CAP_K) ws.key[pos] = 0xFFFFFFFFu;
+                }
+                ++pos;
+                diff = 0;
+            }
+        }
+        fit = __reduce_min_sync(0xFFFFFFFFu, fit);
     }
     if (lane == 0) ws.aa0 = aa0;
-    fit = __reduce_min_sync(0xFFFFFFFFu, fit);
+    __syncwarp();
+    // group heads: entry j opens a group when its key differs from its predecessor's; the padding (0xFFFFFFFF) behind the
+    // last entry makes the first padded slot a head too
+#pragma unroll
+    for (int i = 0; i < MT_HB; ++i) {
+        const u32 j = 32 * i + lane;
+        const u32 k = j < (u32) MT_KEYS ? ws.key[j] : 0xFFFFFFFFu;
+        const u32 kprev = j == 0 ? ~k : (j - 1 < (u32) MT_KEYS ? ws.key[j - 1] : 0xFFFFFFFFu);
+        const u32 m = __ballot_sync(0xFFFFFFFFu, k != kprev);
+        if (lane == 0) ws.hbits[i] = m;
+    }
     *n_fit = fit;
     __syncwarp();
     return n_total;
@@ -634,8 +659,6 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
                 // ---- join the query slice against entries [0, proc) ----
                 const u64 aa0 = ws.aa0;
                 const u32 key_hi = ws.key[proc - 1];
-                u32 top = 1;
-                while (top * 2 <= proc) top *= 2;
                 ulonglong2 v_next = make_ulonglong2(0, 0);
                 if (qs + lane < qe) v_next = __ldg(reinterpret_cast<const ulonglong2 *>(q + qs + lane));
                 for (u64 qb = qs; qb < qe; qb += 32) {
@@ -648,10 +671,12 @@ k_match(const __grid_constant__ DbView db, const Unit *__restrict__ units, u32 n
                     if (mine && rel <= (u64) key_hi) {
                         // bound-free lower bound in the padded key array: number of entries below the key
                         const u32 key = (u32) rel;
-                        u32 pos = 0;
-                        for (u32 step = top; step; step >>= 1)
-                            if (ws.key[pos + step - 1] < key) pos += step;
-                        if (ws.key[pos] == key && pos < proc) {
+                        const u32 *kp = ws.key;
+#pragma unroll
+                        for (int step = MT_KEYS / 2; step; step >>= 1)
+                            if (kp[step - 1] < key) kp += step;
+                        const u32 pos = (u32) (kp - ws.key);
+                        if (*kp == key && pos < proc) {
                             // pos is the group's head; the group ends at the next head (the sentinel bounds the scan)
                             lo = pos;
                             const u32 b = pos + 1;
