@@ -68,17 +68,20 @@ struct Counters {                 // device-side scalars, one allocation
     u32 slow_ticket;
     u32 finish_ticket;
     u32 fast_overflow[8];     // reads the compact scorer left to the general kernel, by reason
+    u32 lr_n_grp, lr_n_sp, lr_ticket[3];   // long-read scorer: list lengths and kernel tickets
     u32 trivial[RS_MAX_PASSES];
 };
 
 // kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
        KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SEGSORT_LONG, KID_SCORE_FAST, KID_SCORE_FINISH, KID_SCORE,
+       KID_LR_HEADS, KID_LR_PATHS, KID_LR_SPECIES, KID_LR_BEST,
        KID_COUNT };
 const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
-                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_sort_segments_long", "k_score_fast", "k_score_finish", "k_score"};
+                                          "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_sort_segments_long", "k_score_fast", "k_score_finish", "k_score",
+                                          "k_lr_heads", "k_lr_paths", "k_lr_species", "k_lr_best"};
 struct KSample { int kid; cudaEvent_t a, b; };
 
 } // namespace
@@ -133,6 +136,7 @@ struct mb_ctx {
     DevBuf seg_begin, seg_end, results, tc_id, tc_cnt, arena;
     DevBuf slow_list, best_recs;
     DevBuf sc_local, sc_paths, sc_comb, sc_linked, sc_spid, sc_spscore;   // per-match scoring scratch
+    DevBuf lr_grp_np, lr_grp_end, lr_sp_end, lr_grp_heads, lr_sp_heads;      // long-read scorer (k_lr_*)
     u64 tc_used = 0;
     DevBuf counters;
     void *pinned = nullptr;       // 256-byte pinned scratch for read-backs
@@ -1191,10 +1195,40 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
                 ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count, &ctx->dcnt()->finish_ticket, &ctx->dcnt()->error_flag));
             CK(cudaStreamWaitEvent(ctx->stream, ctx->side_join, 0));
         } else {
-            KL(KID_SCORE, k_score<<<grid, SC_THREADS, 0, ctx->stream>>>(
-                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
+            // long reads / contigs: paths per (read, species, frame) run, species scores per (read, species) run, then one
+            // thread per read (mb_score.cuh, k_lr_*)
+            if (ctx->n_matches >= 0xFFFFFFF0ull) return fail(ctx, MB_E_ARG, "too many matches in one long-read batch (use smaller batches)");
+            CK(ctx->lr_grp_np.ensure(nm * sizeof(int32_t)));
+            CK(ctx->lr_grp_end.ensure(nm * sizeof(int32_t)));
+            CK(ctx->lr_sp_end.ensure(nm * sizeof(int32_t)));
+            CK(ctx->lr_grp_heads.ensure(nm * sizeof(u32)));
+            CK(ctx->lr_sp_heads.ensure(nm * sizeof(u32)));
+            LongScratch ls;
+            ls.local = arena.local; ls.paths = arena.paths; ls.combined = arena.combined; ls.linked = arena.linked;
+            ls.grp_np = ctx->lr_grp_np.as<int32_t>(); ls.grp_end = ctx->lr_grp_end.as<int32_t>();
+            ls.sp_score = arena.sp_score; ls.sp_end = ctx->lr_sp_end.as<int32_t>();
+            ls.grp_heads = ctx->lr_grp_heads.as<u32>(); ls.sp_heads = ctx->lr_sp_heads.as<u32>();
+            ls.n_grp = &ctx->dcnt()->lr_n_grp; ls.n_sp = &ctx->dcnt()->lr_n_sp;
+            CK(cudaMemsetAsync(&ctx->dcnt()->lr_n_grp, 0, 5 * sizeof(u32), ctx->stream));
+            int sms = 0;
+            CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
+            const unsigned wide = (unsigned) std::max(1, sms) * 16;          // 16 CTAs of 128 threads per SM
+            if (ctx->n_matches) {
+                KL(KID_LR_HEADS, k_lr_heads<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
+                    ctx->matches_a.as<mb_match>(), ctx->n_matches, ls));
+                KL(KID_LR_PATHS, k_lr_paths<<<wide, SC_THREADS, 0, ctx->stream>>>(
+                    ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->seq_base, cfg, tv, ls,
+                    &ctx->dcnt()->lr_ticket[0]));
+                KL(KID_LR_SPECIES, k_lr_species<<<wide, SC_THREADS, 0, ctx->stream>>>(
+                    ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), ctx->seq_base, cfg,
+                    ls, &ctx->dcnt()->lr_ticket[1]));
+            }
+            // one warp per read at a time; an arena slice per warp
+            const unsigned best_grid = (unsigned) std::max<u64>(1, std::min<u64>((u64) grid, ((u64) nr + 3) / 4));
+            KL(KID_LR_BEST, k_lr_best<<<best_grid, SC_THREADS, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, cfg, tv, arena, ls,
                 ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
-                &ctx->dcnt()->score_ticket, &ctx->dcnt()->error_flag, nullptr, nullptr));
+                &ctx->dcnt()->lr_ticket[2], &ctx->dcnt()->error_flag));
         }
         unsigned long long used = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->tc_count, &used)) return rc;

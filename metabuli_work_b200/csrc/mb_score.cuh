@@ -1029,6 +1029,207 @@ k_score_finish(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin
         __syncwarp();
     }
 }
+
+// ---- long reads and contigs (--seq-mode 3): the general per-read functions spread over four kernels ----------------
+// A long read has thousands of matches and a contig hundreds of thousands, so one thread per read (k_score) serialises
+// what is independent: getMatchPaths works on one (species, frame) run of the read's matches at a time
+// (Taxonomer.cpp:316-408 calls it per frame), combineMatchPaths on one species.  The four kernels keep every function and
+// every order of the general scorer (scores stay bit-identical) and only change who runs them:
+//   k_lr_heads    one thread per match: lists the first match of every (read, species, frame) run and of every
+//                 (read, species) run
+//   k_lr_paths    one thread per (read, species, frame) run: match_paths -> the run's paths, left beside its matches
+//   k_lr_species  one thread per (read, species) run: gathers the paths of its frames in frame order and runs
+//                 combine_paths -> the species' score
+//   k_lr_best     one thread per read: walks its species in match order exactly as best_species does (first maximum wins,
+//                 ties within tie_ratio go to the LCA), then finish_read
+struct LongScratch {
+    PathRec *local, *paths, *combined;     // per match, as in ScoreArena
+    u8 *linked;
+    int32_t *grp_np, *grp_end;             // at a run's first match: number of paths, end of the run (index inside the read)
+    float *sp_score;                       // at a species' first match: its score, < 0 = no entry (no path, or below min_score)
+    int32_t *sp_end;                       // at a species' first match: end of its matches (index inside the read)
+    u32 *grp_heads, *sp_heads;             // lists of first matches (global match indices)
+    u32 *n_grp, *n_sp;                     // their lengths
+};
+
+__global__ void __launch_bounds__(256)
+k_lr_heads(const mb_match *__restrict__ m, u64 n, LongScratch ls) {
+    const u64 i = (u64) blockIdx.x * 256 + threadIdx.x;
+    const u32 lane = threadIdx.x & 31;
+    bool gh = false, sh = false;
+    if (i < n) {
+        const u64 q = m[i].qinfo;
+        const int32_t sp = m[i].speciesId;
+        if (i == 0) gh = sh = true;
+        else {
+            const u64 qp = m[i - 1].qinfo;
+            const int32_t spp = m[i - 1].speciesId;
+            sh = qi_seq(q) != qi_seq(qp) || sp != spp;
+            gh = sh || qi_frame(q) != qi_frame(qp);
+        }
+    }
+    // one reservation per warp and list
+    const u32 gm = __ballot_sync(0xFFFFFFFFu, gh), sm = __ballot_sync(0xFFFFFFFFu, sh);
+    u32 gbase = 0, sbase = 0;
+    if (lane == 0) {
+        if (gm) gbase = atomicAdd(ls.n_grp, (u32) __popc(gm));
+        if (sm) sbase = atomicAdd(ls.n_sp, (u32) __popc(sm));
+    }
+    gbase = __shfl_sync(0xFFFFFFFFu, gbase, 0);
+    sbase = __shfl_sync(0xFFFFFFFFu, sbase, 0);
+    if (gh) ls.grp_heads[gbase + __popc(gm & ((1u << lane) - 1u))] = (u32) i;
+    if (sh) ls.sp_heads[sbase + __popc(sm & ((1u << lane) - 1u))] = (u32) i;
+}
+
+__global__ void __launch_bounds__(SC_THREADS)
+k_lr_paths(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end, u32 seq_base,
+           ScoreCfg cfg, TaxView tax, LongScratch ls, u32 *ticket) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 total = *ls.n_grp;
+    while (true) {
+        u32 g0 = 0;
+        if (lane == 0) g0 = atomicAdd(ticket, 32u);
+        g0 = __shfl_sync(0xFFFFFFFFu, g0, 0);
+        if (g0 >= total) break;
+        if (g0 + lane < total) {
+            const u64 h = ls.grp_heads[g0 + lane];
+            const u32 r = qi_seq(m[h].qinfo) - seq_base - 1u;
+            const u64 rb = seg_begin[r], re = seg_end[r];
+            const mb_match *mr = m + rb;
+            const int fb = (int) (h - rb), n = (int) (re - rb);
+            const int32_t species = mr[fb].speciesId;
+            const u32 frame = qi_frame(mr[fb].qinfo);
+            int fe = fb + 1;
+            while (fe < n && mr[fe].speciesId == species && qi_frame(mr[fe].qinfo) == frame) ++fe;
+            int n_paths = 0;
+            if (fe - fb > 1) {
+                int min_depth = cfg.min_cons_cnt;
+                if (tax_is_ancestor(tax, tax.eukaryota, species)) min_depth = cfg.min_cons_cnt_euk;
+                ReadScratch scr;
+                scr.local = ls.local + h; scr.linked = ls.linked + h; scr.paths = ls.paths + h;
+                match_paths(mr, fb, fe, min_depth, cfg, scr, n_paths);
+            }
+            ls.grp_np[h] = n_paths;
+            ls.grp_end[h] = fe;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(SC_THREADS)
+k_lr_species(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end, const u32 *__restrict__ lens,
+             u32 seq_base, ScoreCfg cfg, LongScratch ls, u32 *ticket) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 total = *ls.n_sp;
+    while (true) {
+        u32 s0 = 0;
+        if (lane == 0) s0 = atomicAdd(ticket, 32u);
+        s0 = __shfl_sync(0xFFFFFFFFu, s0, 0);
+        if (s0 >= total) break;
+        if (s0 + lane < total) {
+            const u64 s = ls.sp_heads[s0 + lane];
+            const u32 r = qi_seq(m[s].qinfo) - seq_base - 1u;
+            const u64 rb = seg_begin[r], re = seg_end[r];
+            const mb_match *mr = m + rb;
+            const int n = (int) (re - rb);
+            const int32_t species = mr[s - rb].speciesId;
+            // the paths of the species' frames, in frame order, moved to the front of the species' slice
+            int g = (int) (s - rb), n_paths = 0;
+            PathRec *dst = ls.paths + s;
+            while (g < n && mr[g].speciesId == species) {
+                const int np = ls.grp_np[rb + g];
+                const PathRec *src = ls.paths + rb + g;
+                if (dst + n_paths != src)
+                    for (int k = 0; k < np; ++k) dst[n_paths + k] = src[k];
+                n_paths += np;
+                g = ls.grp_end[rb + g];
+            }
+            float score = -1.f;
+            if (n_paths > 0) {
+                ReadScratch scr;
+                scr.paths = dst; scr.combined = ls.combined + s;
+                const int ql = max_covered_length((int) lens[2 * r]);
+                score = combine_paths(mr, scr, n_paths, ql);
+                score = score < 1.0f ? score : 1.0f;
+                if (score < cfg.min_score) score = -1.f;
+            }
+            ls.sp_score[s] = score;
+            ls.sp_end[s] = g;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(SC_THREADS)
+k_lr_best(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end, const u32 *__restrict__ lens,
+          u32 n_reads, ScoreCfg cfg, TaxView tax, ScoreArena arena, LongScratch ls, mb_read_result *__restrict__ results,
+          int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out, u64 tc_cap, unsigned long long *tc_counter, u32 *ticket,
+          u32 *error_flag) {
+    const u32 lane = threadIdx.x & 31;
+    const u64 slot = ((u64) blockIdx.x * SC_THREADS + threadIdx.x) >> 5;      // one arena slice per WARP
+    while (true) {
+        u32 r0 = 0;
+        if (lane == 0) r0 = atomicAdd(ticket, 1u);              // reads are few and heavy: one per warp (lane 0 works)
+        r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
+        if (r0 >= n_reads) break;
+        if (lane == 0) {
+            const u32 r = r0;
+            const int ql = max_covered_length((int) lens[2 * r]);
+            const u64 b = seg_begin[r], e = seg_end[r];
+            mb_read_result res;
+            int n_tc = 0;
+            ReadScratch scr;
+            if (e > b && (e - b) < 0x7FFFFFFFull) {
+                const int n = (int) (e - b);
+                arena_carve(arena, slot, b, n, scr);
+                result_init(res, ql, n);
+                // Taxonomer::getBestSpeciesMatches (Taxonomer.cpp:316-408) over the species scores, in match order
+                BestSpecies best;
+                best.tax = 0; best.score = 0.f; best.lca = false; best.rb = 0; best.re = 0;
+                int meaningful = 0;
+                float best_sp = 0.f;
+                for (int i = 0; i < n;) {
+                    const float sc = ls.sp_score[b + i];
+                    const int ie = ls.sp_end[b + i];
+                    if (sc >= 0.f) {
+                        if (sc > 0.f) ++meaningful;
+                        if (sc > best_sp) { best_sp = sc; best.rb = i; best.re = ie; }
+                    }
+                    i = ie;
+                }
+                if (meaningful) {
+                    int n_top = 0;
+                    int32_t lca = 0, single = 0;
+                    bool have = false;
+                    const float cut = best_sp * cfg.tie_ratio;
+                    for (int i = 0; i < n;) {
+                        const float sc = ls.sp_score[b + i];
+                        const int ie = ls.sp_end[b + i];
+                        if (sc >= 0.f && sc >= cut) {
+                            const int32_t t = m[b + i].speciesId;
+                            if (n_top == 0) single = t;
+                            ++n_top;
+                            best.score += sc;
+                            if (tax_exists(tax, t)) {
+                                if (!have) { lca = t; have = true; }
+                                else lca = tax_lca_existing(tax, lca, t);
+                            }
+                        }
+                        i = ie;
+                    }
+                    if (n_top > 1) { best.lca = true; best.tax = have ? lca : 0; best.score /= (float) n_top; }
+                    else best.tax = single;
+                }
+                n_tc = finish_read(m + b, best, ql, cfg, tax, scr, res, error_flag);
+            } else {
+                if (e > b) *error_flag = 4;
+                result_init(res, ql, (int32_t) (e - b));
+            }
+            store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
+        }
+        __syncwarp();
+    }
+}
 #endif // __CUDACC__
 
 } // namespace mb
