@@ -49,10 +49,16 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--genomes", type=int, default=10000, help="genomes in the synthetic DB (configs[1]: 10k)")
-    ap.add_argument("--pairs", type=int, default=1_000_000, help="read pairs per GPU per step (configs[1]: 1M)")
-    ap.add_argument("--len-min", type=int, default=200_000)
-    ap.add_argument("--len-max", type=int, default=500_000)
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5],
+                    help="BASELINE.json configs (1-based): 2 = 1M 2x150 pairs vs 10k-genome syncmer DB (the driver's default); "
+                         "3 = GTDB-scale taxonomy (130k species), DB sharded over the GPUs; 4 = ONT-like long reads, seq-mode 3; "
+                         "5 = contigs vs non-syncmer DB (--legacy: legacy format-1 DB)")
+    ap.add_argument("--legacy", action="store_true", help="config 5: legacy format-1 database (OldMetamerScanner)")
+    ap.add_argument("--batch-reads", type=int, default=0, help="reads per library batch (0 = the config's default)")
+    ap.add_argument("--genomes", type=int, default=0, help="genomes in the synthetic DB (0 = the config's: 10k, config 3: 130k)")
+    ap.add_argument("--pairs", type=int, default=0, help="reads (pairs) per GPU per step (0 = the config's: 1M pairs / 1.25M pairs / 100k long reads / 500 contigs)")
+    ap.add_argument("--len-min", type=int, default=0)
+    ap.add_argument("--len-max", type=int, default=0)
     ap.add_argument("--seed", type=int, default=2)
     ap.add_argument("--workdir", default=os.environ.get("MB_BENCH_WORKDIR", "/tmp/mb_bench"))
     ap.add_argument("--cpu-pairs", type=int, default=0, help="read pairs of the bounded CPU sample (0 = auto)")
@@ -64,7 +70,32 @@ def parse_args():
                     help="multi-GPU: producers write into peer memory (fused) or bucket + NCCL all-to-all (nccl)")
     ap.add_argument("--no-fastq", action="store_true", help="skip the input-pipeline leg (FASTQ text parsed on the device)")
     ap.add_argument("--keep", action="store_true", help="keep the generated workload in --workdir")
-    return ap.parse_args()
+    a = ap.parse_args()
+    apply_config(a)
+    return a
+
+
+def apply_config(a):
+    """Fills in the workload of the chosen BASELINE.json config (explicit flags win)."""
+    c = {2: dict(label="configs[1]", genomes=10000, pairs=1_000_000, glen=(200_000, 500_000), kind="pairs", seq_mode=2, syncmer=1, fmt=2,
+                 rlen=(150, 150), batch=0, cpu=1_000_000),
+         3: dict(label="configs[2]", genomes=130_000, pairs=1_250_000, glen=(80_000, 160_000), kind="pairs", seq_mode=2, syncmer=1, fmt=2,
+                 rlen=(150, 150), batch=0, cpu=100_000),
+         4: dict(label="configs[3]", genomes=10000, pairs=100_000, glen=(200_000, 500_000), kind="long", seq_mode=3, syncmer=1, fmt=2,
+                 rlen=(5_000, 20_000), batch=50_000, cpu=5_000),
+         5: dict(label="configs[4]", genomes=10000, pairs=500, glen=(200_000, 500_000), kind="contigs", seq_mode=3, syncmer=0,
+                 fmt=1 if a.legacy else 2, rlen=(50_000, 500_000), batch=0, cpu=50)}[a.config]
+    a.label = c["label"]
+    a.genomes = a.genomes or c["genomes"]
+    a.pairs = a.pairs or c["pairs"]
+    a.len_min = a.len_min or c["glen"][0]
+    a.len_max = a.len_max or c["glen"][1]
+    a.kind, a.seq_mode, a.syncmer, a.kmer_format, a.rlen = c["kind"], c["seq_mode"], c["syncmer"], c["fmt"], c["rlen"]
+    a.batch_reads = a.batch_reads or c["batch"] or a.pairs
+    if not a.cpu_pairs:
+        a.cpu_pairs = min(a.pairs, c["cpu"])
+    a.metric = {"pairs": METRIC, "long": "classified reads/sec (ONT-like long reads 5-20 kb, 5% errors, seq-mode 3, syncmer DB)",
+                "contigs": "classified reads/sec (contigs 50-500 kb, seq-mode 3, non-syncmer DB" + (", legacy format 1)" if a.legacy else ")")}[a.kind]
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -72,6 +103,8 @@ def parse_args():
 # ---------------------------------------------------------------------------------------------------
 def taxonomy_shape(n_genomes):
     """families x genera x species x strains with F*G*S*T == n_genomes (10k -> 10 x 10 x 10 x 10)."""
+    if n_genomes >= 100_000:                  # GTDB-scale: one genome per species (129,671 species in GTDB R226)
+        return 50, 52, n_genomes // 2600, 1
     if n_genomes >= 10000:
         return 10, 10, 10, n_genomes // 1000
     if n_genomes >= 1000:
@@ -82,7 +115,7 @@ def taxonomy_shape(n_genomes):
 
 
 def workload_key(a):
-    return f"g{a.genomes}_l{a.len_min}-{a.len_max}_s{a.seed}"
+    return f"g{a.genomes}_l{a.len_min}-{a.len_max}_s{a.seed}" + ("" if (a.syncmer, a.kmer_format) == (1, 2) else f"_syn{a.syncmer}_f{a.kmer_format}")
 
 
 def prepare_db(a, device, rank, world):
@@ -110,8 +143,8 @@ def prepare_db(a, device, rank, world):
         tax.use_internal_ids(ext2int)
         codes, starts = W.make_genomes(tax, a.seed, a.len_min, a.len_max, device)
         log(f"genomes: {len(starts) - 1}, {int(starts[-1]) / 1e9:.2f} Gbp in {time.time() - t0:.1f}s")
-        db = W.build_db(tax, codes, starts, device, log=log)
-        n_words = W.write_db_dir(dbdir, db, tax)
+        db = W.build_db(tax, codes, starts, device, log=log, syncmer=bool(a.syncmer), kmer_format=a.kmer_format)
+        n_words = W.write_db_dir(dbdir, db, tax, syncmer=a.syncmer, kmer_format=a.kmer_format)
         meta = {"genomes": len(starts) - 1, "bases": int(starts[-1]), "db_kmers": int(len(db["values"])), "db_words": int(n_words),
                 "species": len(tax.species)}
         with open(os.path.join(base, "db.json"), "w") as f:
@@ -132,22 +165,41 @@ def prepare_reads(a, device, rank):
     """Reads of home rank `rank` (cached as .npy): bases uint8 ASCII, offsets u64[2n], lens u32[2n]."""
     import bench_workload as W
     base = os.path.join(a.workdir, workload_key(a))
-    path = os.path.join(base, f"reads_p{a.pairs}_r{rank}.npy")
-    if os.path.exists(path):
+    tag = f"{a.kind}_p{a.pairs}_r{rank}"
+    path = os.path.join(base, f"reads_{tag}.npy")
+    n = a.pairs
+    if os.path.exists(path) and (a.kind == "pairs" or os.path.exists(path[:-4] + "_lens.npy")):
         bases = np.load(path)
+        rl = None if a.kind == "pairs" else np.load(path[:-4] + "_lens.npy")
     else:
         import torch
         tax = W.Taxonomy(*taxonomy_shape(a.genomes))
         codes, starts = W.make_genomes(tax, a.seed, a.len_min, a.len_max, device)
-        bases, _, _, _ = W.make_reads(codes, starts, a.pairs, a.seed * 1000 + 17 + rank, device)
+        if a.kind == "pairs":
+            bases, _, _, _ = W.make_reads(codes, starts, n, a.seed * 1000 + 17 + rank, device)
+            rl = None
+        else:
+            err = dict(sub=0.02, ins=0.01, dele=0.02) if a.kind == "long" else dict(sub=0.001, ins=0.0, dele=0.0)
+            bases, _, lens = W.make_long_reads(codes, starts, n, a.seed * 1000 + 29 + rank, device, a.rlen[0], a.rlen[1],
+                                               chunk=2000 if a.kind == "long" else 50, **err)
+            rl = lens[0::2].copy()
         del codes
         torch.cuda.empty_cache()
         tmp = path + f".tmp{os.getpid()}.npy"
         np.save(tmp, bases)
         os.replace(tmp, path)
-    n = a.pairs
-    offsets = np.arange(2 * n, dtype=np.uint64) * np.uint64(150)
-    lens = np.full(2 * n, 150, dtype=np.uint32)
+        if rl is not None:
+            np.save(path[:-4] + "_lens.npy", rl)
+    if a.kind == "pairs":
+        offsets = np.arange(2 * n, dtype=np.uint64) * np.uint64(150)
+        lens = np.full(2 * n, 150, dtype=np.uint32)
+    else:
+        lens = np.zeros(2 * n, dtype=np.uint32)
+        lens[0::2] = rl
+        ends = np.cumsum(rl.astype(np.uint64))
+        offsets = np.zeros(2 * n, dtype=np.uint64)
+        offsets[0::2][1:] = ends[:-1]
+        offsets[1::2] = ends
     return bases, offsets, lens
 
 
@@ -214,37 +266,47 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def write_sample_fastq(a, bases, n_pairs):
+def write_sample_files(a, bases, offsets, lens, n_reads):
+    """The first n_reads reads of rank 0 as files for ref_harness: two FASTQ files (pairs) or one FASTA file (long reads)."""
+    import bench_workload as W
     base = os.path.join(a.workdir, workload_key(a))
-    p1, p2 = os.path.join(base, f"sample{n_pairs}_1.fq"), os.path.join(base, f"sample{n_pairs}_2.fq")
-    if not (os.path.exists(p1) and os.path.exists(p2)):
-        for mate, p in ((0, p1), (1, p2)):
-            tmp = p + f".tmp{os.getpid()}"
-            fastq_text(bases[:n_pairs * 300], n_pairs, mate).tofile(tmp)
-            os.replace(tmp, p)
-    return p1, p2
+    if a.kind == "pairs":
+        p1, p2 = os.path.join(base, f"sample{n_reads}_1.fq"), os.path.join(base, f"sample{n_reads}_2.fq")
+        if not (os.path.exists(p1) and os.path.exists(p2)):
+            for mate, p in ((0, p1), (1, p2)):
+                tmp = p + f".tmp{os.getpid()}"
+                fastq_text(bases[:n_reads * 300], n_reads, mate).tofile(tmp)
+                os.replace(tmp, p)
+        return [p1, p2]
+    p = os.path.join(base, f"sample_{a.kind}_p{a.pairs}_{n_reads}.fa")
+    if not os.path.exists(p):
+        tmp = p + f".tmp{os.getpid()}"
+        W.write_fasta(tmp, bases, offsets, lens, n_reads)
+        os.replace(tmp, p)
+    return [p]
 
 
 def ref_results_path(a, n_pairs):
-    return os.path.join(a.workdir, workload_key(a), f"ref_p{a.pairs}_n{n_pairs}.results.tsv")
+    return os.path.join(a.workdir, workload_key(a), f"ref_{a.kind}_p{a.pairs}_n{n_pairs}.results.tsv")
 
 
-def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
+def run_cpu_reference(a, dbdir, reads, n_pairs, reps, skip):
     """-> dict(kind, cores, reads_per_s, s_per_rep, phases, sample, results_tsv).  The reference's own classes
     (oracle/_ref/ref_harness) on all host cores; times extract+sort+match+sort+score (no file parse); the per-read results of
     the first repetition are kept as results_tsv (what the default-on check compares the GPU results with)."""
     threads = host_threads()
     harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
     base = os.path.join(a.workdir, workload_key(a))
+    bases, offsets, lens = reads
     if os.path.exists(harness):
-        p1, p2 = write_sample_fastq(a, bases, n_pairs)
+        files = write_sample_files(a, bases, offsets, lens, n_pairs)
         # warm the page cache for the DB files the matcher re-reads on every call
         for f in ("diffIdx", "info"):
             with open(os.path.join(dbdir, f), "rb") as fh:
                 while fh.read(1 << 26):
                     pass
         prefix = ref_results_path(a, n_pairs)[:-len(".results.tsv")]
-        cmd = [harness, dbdir, prefix, "2", str(threads), p1, p2, "--reps", str(reps + skip), "--skip-reps", str(skip)]
+        cmd = [harness, dbdir, prefix, str(a.seq_mode), str(threads)] + files + ["--reps", str(reps + skip), "--skip-reps", str(skip)]
         t0 = time.time()
         out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
         if out.returncode != 0:
@@ -261,16 +323,17 @@ def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
         return {"kind": "reference", "cores": threads, "reads_per_s": js["reads"] / s_rep, "s_per_rep": s_rep, "phases": ph,
                 "kmers": js["kmers"], "matches": js["matches"], "wall_s": time.time() - t0, "reads": js["reads"],
                 "results_tsv": prefix + ".results.tsv", "same_config": whole,
-                "sample": (f"all {js['reads']} read pairs of rank 0" if whole else f"first {js['reads']} of the {a.pairs} read pairs of rank 0") +
+                "sample": (f"all {js['reads']} reads ({a.kind}) of rank 0" if whole else f"first {js['reads']} of the {a.pairs} reads ({a.kind}) of rank 0") +
                           f" vs the full DB; reference KmerMatcher/Taxonomer classes (oracle/_ref/ref_harness), {threads} OpenMP threads, "
                           f"mean of {reps} reps after {skip} warm-up, extract+sort+match+sort+score, file parsing excluded"}
     # oracle port
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
     db = orc.Db(dbdir)
-    p = db.params(seq_mode=2, threads=threads)
-    b = bases[:n_pairs * 300].reshape(n_pairs, 2, 150)
-    batch = orc.Batch([x[0].tobytes() for x in b], [x[1].tobytes() for x in b])
+    p = db.params(seq_mode=a.seq_mode, threads=threads)
+    m1 = [bases[int(offsets[2 * i]):int(offsets[2 * i]) + int(lens[2 * i])].tobytes() for i in range(n_pairs)]
+    m2 = [bases[int(offsets[2 * i + 1]):int(offsets[2 * i + 1]) + int(lens[2 * i + 1])].tobytes() for i in range(n_pairs)] if a.kind == "pairs" else None
+    batch = orc.Batch(m1, m2)
     times = []
     for r in range(reps + skip):
         t0 = time.time()
@@ -283,7 +346,7 @@ def run_cpu_reference(a, dbdir, bases, n_pairs, reps, skip):
             "sample": f"first {n_pairs} of the {a.pairs} read pairs of rank 0 vs the full DB; oracle port (oracle/liborc.so), {threads} threads"}
 
 
-def check_against_reference(tsv, h_res, h_ids, h_cnt):
+def check_against_reference(tsv, h_res, h_ids, h_cnt, limit=None):
     """Default-on parity record of the benched config: the per-read results ref_harness wrote (the reference's own
     KmerMatcher / Taxonomer on the same DB directory and reads) vs the GPU results of the same reads — internal tax ID,
     is_classified, query length, fp32 score BITS and the taxID:count list."""
@@ -291,6 +354,8 @@ def check_against_reference(tsv, h_res, h_ids, h_cnt):
     first_bad = []
     with open(tsv) as f:
         for i, line in enumerate(f):
+            if limit is not None and i >= limit:
+                break
             c = line.rstrip("\n").split("\t")
             g = h_res[i]
             tg = "".join(f"{t}:{k} " for t, k in zip(h_ids[g["taxcnt_begin"]:g["taxcnt_end"]].tolist(), h_cnt[g["taxcnt_begin"]:g["taxcnt_end"]].tolist()))
@@ -307,10 +372,16 @@ def check_against_reference(tsv, h_res, h_ids, h_cnt):
     return out
 
 
+def workload_text(a, meta):
+    what = {"pairs": f"{a.pairs} synthetic 2x150 read pairs", "long": f"{a.pairs} synthetic ONT-like long reads ({a.rlen[0]}-{a.rlen[1]} nt, 5% errors)",
+            "contigs": f"{a.pairs} synthetic contigs ({a.rlen[0]}-{a.rlen[1]} nt, 0.1% substitutions)"}[a.kind]
+    dbk = ("syncmer" if a.syncmer else "non-syncmer") + (" legacy format-1" if a.kmer_format == 1 else "")
+    return (f"{a.label}: {what} per GPU vs {meta['genomes']}-genome synthetic {dbk} DB ({meta['db_kmers']} k-mers, {meta['species']} species), "
+            f"seq-mode {a.seq_mode}" + (", s=5" if a.syncmer else ""))
+
+
 def cpu_sample_pairs(a):
-    if a.cpu_pairs:
-        return min(a.cpu_pairs, a.pairs)
-    return min(a.pairs, 1_000_000)
+    return min(a.cpu_pairs, a.pairs)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -444,10 +515,28 @@ def run_b200(a):
     bases, offsets, lens = prepare_reads(a, device, rank)
     n_pairs = a.pairs
     t0 = time.time()
-    clf = mb.Classifier(dbdir, device=local, seq_mode=2, shard=rank, n_shards=world)
+    clf = mb.Classifier(dbdir, device=local, seq_mode=a.seq_mode, shard=rank, n_shards=world)
     log(f"rank {rank}: shard {rank}/{world} resident ({clf.db_kmers()} k-mers, {clf.db_words()} words) in {time.time() - t0:.1f}s")
     clf.set_profile(True)
     sharded = ShardedClassifier(DeviceEngine(clf, device), clf.shard_bounds(), n_pairs, rank, world, fused=a.exchange == "fused") if world > 1 else None
+
+    # Library batches: the whole step in one batch (configs 2, 3, 5), or several (config 4: 100k long reads hold a billion
+    # k-mers; the reference splits such inputs as well, QueryIndexer.cpp:62-67).  With several batches every batch is staged
+    # from pinned host memory inside the timed region of BOTH legs.
+    multi = a.batch_reads < n_pairs
+    if multi and world > 1:
+        raise SystemExit("configs with several batches per step run on one GPU")
+    batches = []
+    if multi:
+        for s0 in range(0, n_pairs, a.batch_reads):
+            s1 = min(n_pairs, s0 + a.batch_reads)
+            b0 = int(offsets[2 * s0])
+            b1 = int(offsets[2 * s1 - 1]) + int(lens[2 * s1 - 1])
+            tb = torch.from_numpy(bases[b0:b1].copy()).pin_memory()
+            to = torch.from_numpy((offsets[2 * s0:2 * s1] - np.uint64(b0)).view(np.int64).copy()).pin_memory()
+            tl = torch.from_numpy(lens[2 * s0:2 * s1].view(np.int32).copy()).pin_memory()
+            batches.append({"n": s1 - s0, "tb": tb, "b": tb.numpy(), "o": to.numpy().view(np.uint64), "l": tl.numpy().view(np.uint32),
+                            "keep": (to, tl)})
 
     # pinned host buffers (inputs and results of the end-to-end leg)
     pin_bases = torch.from_numpy(bases).pin_memory()
@@ -457,7 +546,7 @@ def run_b200(a):
     h_off = pin_off.numpy().view(np.uint64)
     h_len = pin_len.numpy().view(np.uint32)
     pin_res = torch.zeros(n_pairs * mb.RESULT_DT.itemsize, dtype=torch.uint8).pin_memory()
-    tc_cap = 8 * n_pairs
+    tc_cap = 8 * n_pairs if a.kind == "pairs" else max(64 * n_pairs, 1 << 22)      # (internal taxID, count) entries of one step
     pin_ids = torch.zeros(tc_cap, dtype=torch.int32).pin_memory()
     pin_cnt = torch.zeros(tc_cap, dtype=torch.int32).pin_memory()
     h_res = pin_res.numpy().view(mb.RESULT_DT)
@@ -479,8 +568,23 @@ def run_b200(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    step_counts = {}
+
     def staged_step():
-        return sharded.classify_staged() if sharded else clf.classify_staged()
+        if not multi:
+            return sharded.classify_staged() if sharded else clf.classify_staged()
+        used = 0
+        step_counts.clear()
+        for bt in batches:
+            clf.stage(bt["b"], bt["o"], bt["l"], bases_ptr=bt["tb"].data_ptr())
+            used += clf.classify_staged()
+            t = clf.timings()
+            for k in ("n_bases", "n_kmers", "n_matches", "n_reads", "kernel_launches"):
+                step_counts[k] = step_counts.get(k, 0) + t[k]
+            for k, (ms, n) in clf.kernel_times().items():
+                a_ms, a_n = step_counts.setdefault("kt", {}).get(k, (0.0, 0))
+                step_counts["kt"][k] = (a_ms + ms, a_n + n)
+        return used
 
     # end-to-end step: the reads of the step come from pinned host memory, the results go back to host memory.  Two
     # pinned input buffers alternate, and the copy of the NEXT step's reads (mb_prefetch_reads, second stream) overlaps
@@ -490,7 +594,24 @@ def run_b200(a):
     pin_in.append((pb2, pb2.numpy(), po2.numpy().view(np.uint64), pl2.numpy().view(np.uint32)))
     e2e_i = [0]
 
+    def e2e_step_multi():
+        used = 0
+        for i, bt in enumerate(batches):
+            nx = batches[(i + 1) % len(batches)]
+            clf.stage(bt["b"], bt["o"], bt["l"], bases_ptr=bt["tb"].data_ptr())
+            clf.prefetch(nx["b"], nx["o"], nx["l"], bases_ptr=nx["tb"].data_ptr())
+            u = clf.classify_staged()
+            if "res" not in bt or len(bt["ids"]) < u:
+                bt["res"] = np.zeros(bt["n"], dtype=mb.RESULT_DT)
+                bt["ids"] = np.zeros(max(2 * u, 1024), dtype=np.int32)
+                bt["cnt"] = np.zeros(max(2 * u, 1024), dtype=np.int32)
+            clf.fetch_into(bt["res"], bt["ids"], bt["cnt"])
+            used += u
+        return used
+
     def e2e_step():
+        if multi:
+            return e2e_step_multi()
         cur = pin_in[e2e_i[0] & 1]
         nxt = pin_in[(e2e_i[0] + 1) & 1]
         e2e_i[0] += 1
@@ -508,7 +629,7 @@ def run_b200(a):
     # ---- device-resident leg: reads staged once, K passes of the device stages ----
     if sharded:
         sharded.stage(h_bases, h_off, h_len, bases_ptr=pin_bases.data_ptr())
-    else:
+    elif not multi:
         clf.stage(h_bases, h_off, h_len, bases_ptr=pin_bases.data_ptr())
     for _ in range(a.warmup):
         staged_step()
@@ -524,6 +645,9 @@ def run_b200(a):
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
     t_step = clf.timings()
     ktimes = clf.kernel_times()
+    if multi:                                  # counts and kernel times of the whole step = sums over its batches
+        t_step = dict(t_step, **{k: v for k, v in step_counts.items() if k != "kt"})
+        ktimes = step_counts["kt"]
     launches_per_step = t_step["kernel_launches"]
     stats = dict(sharded.stats) if sharded else {}
 
@@ -541,7 +665,11 @@ def run_b200(a):
     wall_e2e = time.perf_counter() - w0
     ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), wall_e2e * 1e3))
     clocks = sampler.stop()
-    classified = int(h_res["is_classified"].sum())
+    if multi:
+        classified = int(sum(int(bt["res"]["is_classified"].sum()) for bt in batches))
+        h_res, h_ids, h_cnt = batches[0]["res"], batches[0]["ids"], batches[0]["cnt"]     # what the check compares: the first batch
+    else:
+        classified = int(h_res["is_classified"].sum())
     t_e2e = clf.timings()
 
     ms_step = ms_total / a.steps
@@ -576,11 +704,11 @@ def run_b200(a):
         match_phase = None
 
     out = {
-        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "metric": a.metric, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
         "data": "synthetic",
-        "config": {"workload": f"configs[1]: {n_pairs} synthetic 2x150 read pairs per GPU vs {meta['genomes']}-genome synthetic syncmer DB "
-                               f"({meta['db_kmers']} k-mers, {meta['species']} species), seq-mode 2, s=5",
+        "config": {"workload": workload_text(a, meta),
+                   "batches_per_step": max(1, len(batches)),
                    "pairs_per_gpu": n_pairs, "db_kmers": meta["db_kmers"], "db_words": meta["db_words"], "genomes": meta["genomes"],
                    "db_sharding": f"{world} k-mer-range shard(s), one per GPU" if world > 1 else "whole DB on one GPU",
                    "exchange": (a.exchange if world > 1 else None),
@@ -600,7 +728,7 @@ def run_b200(a):
     }
 
     # ---- input pipeline: the same reads as raw FASTQ text, parsed and packed on the device ----
-    if world == 1 and not a.no_fastq:
+    if world == 1 and not a.no_fastq and a.kind == "pairs" and not multi:
         try:
             out["input_pipeline"] = fastq_leg(a, torch, clf, bases, n_pairs, h_res, h_ids, h_cnt, stream)
         except Exception as ex:  # reported, never required
@@ -611,7 +739,7 @@ def run_b200(a):
         tsv = ref_results_path(a, n_cpu)
         if not a.no_cpu_baseline and world == 1:
             try:
-                cb = run_cpu_reference(a, dbdir, bases, n_cpu, reps=2, skip=1)
+                cb = run_cpu_reference(a, dbdir, (bases, offsets, lens), n_cpu, reps=2, skip=1)
                 out["cpu_baseline"] = {"value": round(cb["reads_per_s"], 1), "unit": UNIT, "cores": cb["cores"], "kind": cb["kind"],
                                        "sample": cb["sample"], "same_config": cb["same_config"], "phases_s": cb["phases"],
                                        "wall_s": round(cb["wall_s"], 1)}
@@ -620,8 +748,8 @@ def run_b200(a):
         if not a.no_check:
             try:
                 if not os.path.exists(tsv):          # N > 1, or the baseline leg was skipped: one untimed pass of the harness
-                    run_cpu_reference(a, dbdir, bases, n_cpu, reps=1, skip=0)
-                out["check"] = check_against_reference(tsv, h_res, h_ids, h_cnt)
+                    run_cpu_reference(a, dbdir, (bases, offsets, lens), n_cpu, reps=1, skip=0)
+                out["check"] = check_against_reference(tsv, h_res, h_ids, h_cnt, limit=len(h_res))
             except Exception as ex:
                 out["check"] = {"against": "ref_harness", "error": str(ex)}
         if a.check_port:
@@ -676,16 +804,15 @@ def run_reference(a):
     if device is not None:
         torch.cuda.set_device(device)
     dbdir, meta = prepare_db(a, device, 0, 1)
-    bases, _, _ = prepare_reads(a, device, 0)
+    reads = prepare_reads(a, device, 0)
     n = cpu_sample_pairs(a)
-    cb = run_cpu_reference(a, dbdir, bases, n, reps=a.steps, skip=a.warmup)
+    cb = run_cpu_reference(a, dbdir, reads, n, reps=a.steps, skip=a.warmup)
     value = cb["reads_per_s"]
     out = {
-        "impl": "reference", "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "impl": "reference", "metric": a.metric, "value": round(value, 1), "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": round(cb["s_per_rep"] * 1e3, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": f"configs[1]: {a.pairs} synthetic 2x150 read pairs per GPU vs {meta['genomes']}-genome synthetic syncmer DB "
-                               f"({meta['db_kmers']} k-mers, {meta['species']} species), seq-mode 2, s=5",
+        "config": {"workload": workload_text(a, meta),
                    "pairs_per_gpu": a.pairs, "db_kmers": meta["db_kmers"], "db_words": meta["db_words"], "genomes": meta["genomes"],
                    "step": f"one pass of the reference hot path over {cb['reads']} read pairs (whole DB scanned)",
                    "same_config": cb["same_config"], "seed": a.seed},

@@ -182,7 +182,7 @@ def genetic_code_tables():
     return f, r
 
 
-def syncmer_metamers(codes, starts_rel, device, smer_len=5):
+def syncmer_metamers(codes, starts_rel, device, smer_len=5, syncmer=True, kmer_format=2):
     """Format-2 metamers (MetamerScanner::next, KmerScanner.h:82-117) of every 24-base window of the packed genomes `codes`
     (uint8 codes on `device`) on both strands, filtered by the closed-syncmer rule of SyncmerScanner::next
     (SyncmerScanner.h:36-102).  Pure torch (set-up plumbing); the library under test is not involved.
@@ -214,26 +214,38 @@ def syncmer_metamers(codes, starts_rel, device, smer_len=5):
         tab = (cr if strand else cf)[idx3]
         aa = torch.zeros(m, dtype=torch.int64, device=device)
         dna = torch.zeros(m, dtype=torch.int64, device=device)
-        for j in range(8):
-            cj = tab[3 * j:3 * j + m]
-            sh = j if strand else 7 - j                         # reverse strand: translation runs from the high end down
-            aa |= (cj & 31) << (5 * sh)
-            dna |= (cj >> 5) << (3 * sh)
+        if kmer_format == 2:
+            for j in range(8):
+                cj = tab[3 * j:3 * j + m]
+                sh = j if strand else 7 - j                     # reverse strand: translation runs from the high end down
+                aa |= (cj & 31) << (5 * sh)
+                dna |= (cj >> 5) << (3 * sh)
+        else:
+            # legacy format 1 (OldMetamerScanner::next, KmerScanner.h:137-181): codons consumed from the far end, amino-acid
+            # part a base-21 number; forward strand: highest stored codon most significant, reverse strand: lowest
+            order = range(8) if strand else range(7, -1, -1)
+            for j in order:
+                cj = tab[3 * j:3 * j + m]
+                aa = aa * 21 + (cj & 31)
+                dna = (dna << 3) | (cj >> 5)
         del tab
-        v0 = (aa >> (5 * last)) & mask
-        vl = aa & mask
-        mid = torch.full_like(aa, 1 << 40)
-        for i in range(1, last):
-            mid = torch.minimum(mid, (aa >> (5 * (last - i))) & mask)
-        keep = inside & ((v0 <= torch.minimum(mid, vl)) | (vl < torch.minimum(mid, v0)))
-        del v0, vl, mid
+        if syncmer:
+            v0 = (aa >> (5 * last)) & mask
+            vl = aa & mask
+            mid = torch.full_like(aa, 1 << 40)
+            for i in range(1, last):
+                mid = torch.minimum(mid, (aa >> (5 * (last - i))) & mask)
+            keep = inside & ((v0 <= torch.minimum(mid, vl)) | (vl < torch.minimum(mid, v0)))
+            del v0, vl, mid
+        else:
+            keep = inside
         value = (aa << 24) | dna
         out.append((value[keep], p[keep], g[keep], p[keep] % 3 + 3 * strand))
         del aa, dna, value, keep
     return tuple(torch.cat([o[k] for o in out]) for k in range(4))
 
 
-def build_db(tax, codes, starts, device, genomes_per_chunk=200, block=1500, log=None):
+def build_db(tax, codes, starts, device, genomes_per_chunk=200, block=1500, log=None, syncmer=True, kmer_format=2):
     """-> dict(values int64 tensor (uint64 bit patterns, unsigned-ascending), info int64 tensor).  K-mers are the syncmer
     metamers of the genomes (syncmer_metamers above, torch only); one (strand, frame) is kept per 1.5-kb block, the density of
     a gene-finder driven build."""
@@ -243,7 +255,7 @@ def build_db(tax, codes, starts, device, genomes_per_chunk=200, block=1500, log=
     for g0 in range(0, n, genomes_per_chunk):
         g1 = min(n, g0 + genomes_per_chunk)
         a, b = int(starts[g0]), int(starts[g1])
-        value, pos, g_rel, frame = syncmer_metamers(codes[a:b], starts[g0:g1 + 1] - a, device)
+        value, pos, g_rel, frame = syncmer_metamers(codes[a:b], starts[g0:g1 + 1] - a, device, syncmer=syncmer, kmer_format=kmer_format)
         genome = g_rel + g0
         chosen = ((genome * 7919 + (pos // block) * 104729) >> 3) % 6
         keep = frame == chosen
@@ -347,7 +359,7 @@ def write_taxdump(tax, outdir):
     open(f"{outdir}/merged.dmp", "w").close()
 
 
-def write_db_dir(dbdir, db, tax, split_num=4096, syncmer=1, smer_len=5):
+def write_db_dir(dbdir, db, tax, split_num=4096, syncmer=1, smer_len=5, kmer_format=2):
     """Writes diffIdx / info / split / taxID_list / db.parameters of a Metabuli database directory (taxonomyDB comes
     from ref_mkdb).  Format: IndexCreator::writeTargetFilesAndSplits + getDiffIdx (IndexCreator.cpp:811-886) and
     writeDbParameters (:1245-1266)."""
@@ -393,5 +405,77 @@ def write_db_dir(dbdir, db, tax, split_num=4096, syncmer=1, smer_len=5):
         f.write(f"Syncmer\t{syncmer}\n")
         if syncmer:
             f.write(f"Syncmer_len\t{smer_len}\n")
-        f.write("Kmer_format\t2\n")
+        if kmer_format != 1:             # legacy databases carry no Kmer_format line (classify.cpp:13, updateDB.cpp:16)
+            f.write(f"Kmer_format\t{kmer_format}\n")
     return len(words)
+
+
+def make_long_reads(codes, starts, n_reads, seed, device, len_min, len_max, sub=0.02, ins=0.01, dele=0.02, chunk=2000):
+    """ONT-like reads (BASELINE.json configs[3]: sub / ins / del in the ratio 2:1:2) or contigs (sub only): fragments of
+    random genomes, errors applied per base, half of them reverse-complemented.
+    -> (bases uint8 numpy ASCII, offsets uint64[2n] with an empty second mate, lens uint32[2n])."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    n = len(starts) - 1
+    st = torch.from_numpy(np.asarray(starts, dtype=np.int64)).to(device)
+    ascii_lut = torch.from_numpy(CODE2ASCII.copy()).to(device)
+    out_bases, out_lens = [], []
+    for c0 in range(0, n_reads, chunk):
+        c = min(chunk, n_reads - c0)
+        g = torch.randint(0, n, (c,), generator=gen, device=device)
+        glen = st[g + 1] - st[g]
+        L = torch.randint(len_min, len_max + 1, (c,), generator=gen, device=device)
+        L = torch.minimum(L, glen - 1)
+        off = (torch.rand(c, generator=gen, device=device, dtype=torch.float64) * (glen - L).double()).long()
+        rstart = torch.zeros(c + 1, dtype=torch.int64, device=device)
+        rstart[1:] = torch.cumsum(L, 0)
+        tot = int(rstart[-1].item())
+        rid = torch.repeat_interleave(torch.arange(c, device=device), L)
+        pos = torch.arange(tot, device=device) - rstart[rid]
+        src = codes[st[g][rid] + off[rid] + pos]
+        r = torch.rand(tot, generator=gen, device=device)
+        is_sub = r < sub
+        is_ins = (r >= sub) & (r < sub + ins)
+        is_del = (r >= sub + ins) & (r < sub + ins + dele)
+        shift = torch.randint(1, 4, (tot,), generator=gen, device=device, dtype=torch.uint8)
+        src = torch.where(is_sub, (src + shift) & 3, src)
+        cnt = (~is_del).to(torch.int64) + is_ins.to(torch.int64)
+        opos = torch.cumsum(cnt, 0) - cnt
+        ototal = int((opos[-1] + cnt[-1]).item()) if tot else 0
+        out = torch.zeros(ototal, dtype=torch.uint8, device=device)
+        keep = ~is_del
+        out[opos[keep]] = src[keep]
+        extra = torch.randint(0, 4, (int(is_ins.sum().item()),), generator=gen, device=device, dtype=torch.uint8)
+        out[opos[is_ins] + 1] = extra
+        # new read boundaries
+        csum = torch.zeros(tot + 1, dtype=torch.int64, device=device)
+        csum[1:] = torch.cumsum(cnt, 0)
+        nstart = csum[rstart]
+        nlen = nstart[1:] - nstart[:-1]
+        # reverse complement of half of the reads
+        flip = torch.rand(c, generator=gen, device=device) < 0.5
+        orid = torch.repeat_interleave(torch.arange(c, device=device), nlen)
+        p = torch.arange(ototal, device=device)
+        rel = p - nstart[orid]
+        srcp = torch.where(flip[orid], nstart[orid] + nlen[orid] - 1 - rel, p)
+        out = out[srcp] ^ (flip[orid].to(torch.uint8) * 2)
+        out_bases.append(ascii_lut[out.long()].cpu().numpy())
+        out_lens.append(nlen.cpu().numpy())
+    bases = np.concatenate(out_bases) if out_bases else np.zeros(0, dtype=np.uint8)
+    rl = np.concatenate(out_lens).astype(np.uint32)
+    lens = np.zeros(2 * n_reads, dtype=np.uint32)
+    lens[0::2] = rl
+    offsets = np.zeros(2 * n_reads, dtype=np.uint64)
+    ends = np.cumsum(rl.astype(np.uint64))
+    offsets[0::2][1:] = ends[:-1]
+    offsets[1::2] = ends
+    return bases, offsets, lens
+
+
+def write_fasta(path, bases, offsets, lens, n_reads):
+    with open(path, "wb") as f:
+        for i in range(n_reads):
+            o, l = int(offsets[2 * i]), int(lens[2 * i])
+            f.write(b">r%09d\n" % i)
+            f.write(bases[o:o + l].tobytes())
+            f.write(b"\n")

@@ -55,6 +55,7 @@ struct Counters {                 // device-side scalars, one allocation
     unsigned long long match_count;
     unsigned long long tc_count;
     unsigned long long kmer_count;
+    unsigned long long slow_matches;     // matches of the reads listed for the general scorer (compact scratch offsets)
     u32 error_flag;
     u32 max_seg;
     u32 score_ticket;
@@ -134,7 +135,8 @@ struct mb_ctx {
     DevBuf qstart, matches_a, matches_b;
     u64 n_matches = 0;
     DevBuf seg_begin, seg_end, results, tc_id, tc_cnt, arena;
-    DevBuf slow_list, best_recs;
+    DevBuf slow_list, slow_off, best_recs;
+    bool score_full_scratch = false;  // the compact scratch of the general scorer was too small once: size it by the batch
     DevBuf sc_local, sc_paths, sc_comb, sc_linked, sc_spid, sc_spscore;   // per-match scoring scratch
     DevBuf lr_grp_np, lr_grp_end, lr_sp_end, lr_grp_heads, lr_sp_heads;      // long-read scorer (k_lr_*)
     u64 tc_used = 0;
@@ -1125,13 +1127,19 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         CK(ctx->arena.ensure((size_t) (grid + slow_grid) * SC_THREADS * arena.slice_bytes));
         arena.base = ctx->arena.as<unsigned char>();
         const size_t nm = std::max<size_t>(ctx->n_matches, 1);
-        CK(ctx->sc_local.ensure(nm * sizeof(PathRec)));
-        CK(ctx->sc_paths.ensure(nm * sizeof(PathRec)));
-        CK(ctx->sc_comb.ensure(nm * sizeof(PathRec)));
-        CK(ctx->sc_linked.ensure(nm));
-        CK(ctx->sc_spid.ensure(nm * sizeof(int32_t)));
-        CK(ctx->sc_spscore.ensure(nm * sizeof(float)));
-        arena.local = ctx->sc_local.as<PathRec>(); arena.paths = ctx->sc_paths.as<PathRec>(); arena.combined = ctx->sc_comb.as<PathRec>();
+        // Per-match scratch.  Long reads: every match may carry a path; `combined` (species phase) reuses `local` (paths
+        // phase).  Short reads: only the few reads the streaming scorer leaves over use it, at compact offsets — an eighth of
+        // the batch is reserved, and the whole batch once that has proved too small (error 6 below).
+        const bool long_mode = ctx->par.seq_mode == 3;
+        const size_t sc_cap = (long_mode || ctx->score_full_scratch) ? nm : std::min<size_t>(nm, std::max<size_t>(nm / 8, 1u << 20));
+        CK(ctx->sc_local.ensure(sc_cap * sizeof(PathRec)));
+        CK(ctx->sc_paths.ensure(sc_cap * sizeof(PathRec)));
+        if (!long_mode) CK(ctx->sc_comb.ensure(sc_cap * sizeof(PathRec)));
+        CK(ctx->sc_linked.ensure(sc_cap));
+        if (!long_mode) CK(ctx->sc_spid.ensure(sc_cap * sizeof(int32_t)));
+        CK(ctx->sc_spscore.ensure(sc_cap * sizeof(float)));
+        arena.local = ctx->sc_local.as<PathRec>(); arena.paths = ctx->sc_paths.as<PathRec>();
+        arena.combined = long_mode ? arena.local : ctx->sc_comb.as<PathRec>();
         arena.linked = ctx->sc_linked.as<u8>(); arena.sp_id = ctx->sc_spid.as<int32_t>(); arena.sp_score = ctx->sc_spscore.as<float>();
         ScoreArena arena_slow = arena;
         arena_slow.base = arena.base + (size_t) grid * SC_THREADS * arena.slice_bytes;
@@ -1142,6 +1150,8 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         if (ctx->par.seq_mode != 3) {
             // short reads: streaming scorer first; what it cannot hold goes to the general kernel through slow_list
             CK(ctx->slow_list.ensure((size_t) nr * sizeof(u32)));
+            CK(ctx->slow_off.ensure((size_t) nr * sizeof(u64)));
+            CK(cudaMemsetAsync(&ctx->dcnt()->slow_matches, 0, sizeof(unsigned long long), ctx->stream));
             CK(ctx->best_recs.ensure((size_t) nr * sizeof(BestRec)));
             CK(cudaMemsetAsync(&ctx->dcnt()->slow_count, 0, 11 * sizeof(u32), ctx->stream));
             const size_t fast_smem = (size_t) SC_THREADS * SC_GSTRIDE * sizeof(u32);
@@ -1170,7 +1180,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
             KL(KID_SCORE_FAST, k_score_fast<<<fast_grid, SC_THREADS, fast_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv,
                 ctx->best_recs.as<BestRec>(), &ctx->dcnt()->score_ticket, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count,
-                ctx->dcnt()->fast_overflow));
+                ctx->dcnt()->fast_overflow, ctx->slow_off.as<u64>(), &ctx->dcnt()->slow_matches));
             if (!ctx->side_stream) {
                 CK(cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking));
                 CK(cudaEventCreateWithFlags(&ctx->side_fork, cudaEventDisableTiming));
@@ -1187,7 +1197,8 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
             KL_ON(KID_SCORE, slow_stream, k_score<<<slow_grid, SC_THREADS, 0, slow_stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena_slow,
                 ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
-                &ctx->dcnt()->slow_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count));
+                &ctx->dcnt()->slow_ticket, &ctx->dcnt()->error_flag, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count,
+                ctx->slow_off.as<u64>(), (u64) sc_cap));
             CK(cudaEventRecord(ctx->side_join, slow_stream));
             KL(KID_SCORE_FINISH, k_score_finish<<<grid, SC_THREADS, fin_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv, arena,
@@ -1215,7 +1226,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
             const unsigned wide = (unsigned) std::max(1, sms) * 16;          // 16 CTAs of 128 threads per SM
             if (ctx->n_matches) {
                 KL(KID_LR_HEADS, k_lr_heads<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
-                    ctx->matches_a.as<mb_match>(), ctx->n_matches, ls));
+                    ctx->matches_a.as<mb_match>(), ctx->n_matches, ls, 3 * cfg.max_codon_shift));
                 KL(KID_LR_PATHS, k_lr_paths<<<wide, SC_THREADS, 0, ctx->stream>>>(
                     ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->seq_base, cfg, tv, ls,
                     &ctx->dcnt()->lr_ticket[0]));
@@ -1223,8 +1234,8 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
                     ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), ctx->seq_base, cfg,
                     ls, &ctx->dcnt()->lr_ticket[1]));
             }
-            // one warp per read at a time; an arena slice per warp
-            const unsigned best_grid = (unsigned) std::max<u64>(1, std::min<u64>((u64) grid, ((u64) nr + 3) / 4));
+            // one thread block per read at a time; an arena slice per block
+            const unsigned best_grid = (unsigned) std::max<u64>(1, std::min<u64>((u64) grid * SC_THREADS, std::min<u64>((u64) nr, (u64) wide)));
             KL(KID_LR_BEST, k_lr_best<<<best_grid, SC_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, cfg, tv, arena, ls,
                 ctx->results.as<mb_read_result>(), ctx->tc_id.as<int32_t>(), ctx->tc_cnt.as<int32_t>(), (u64) tc_cap, &ctx->dcnt()->tc_count,
@@ -1241,6 +1252,10 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         }
         u32 flag = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->error_flag, &flag)) return rc;
+        if (flag == 6 && !ctx->score_full_scratch) {       // the leftover reads hold more matches than the compact scratch: redo with all of it
+            ctx->score_full_scratch = true;
+            return mb_score_reads(ctx, taxcnt_used);
+        }
         if (flag) {
             char msg[128];
             snprintf(msg, sizeof(msg), "scoring kernel reported internal error %u", flag);

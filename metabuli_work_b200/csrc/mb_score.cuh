@@ -367,8 +367,10 @@ MB_HD BestSpecies best_species(const mb_match *m, int b, int e, int query_length
 
 // Everything of Taxonomer::chooseBestTaxon after getBestSpeciesMatches.  Returns the number of taxCnt entries left
 // in scr.tc_id / scr.tc_cnt.
+// buckets_ready: scr.bucket_ham / scr.bucket_tax were already filled (fill_buckets_warp); n_tc_ready >= 0: so was the taxCnt
+// list scr.tc_id / scr.tc_cnt (count_taxa_warp), with that many entries.
 MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_length, const ScoreCfg &cfg, const TaxView &tax,
-                      ReadScratch &scr, mb_read_result &r, u32 *error_flag) {
+                      ReadScratch &scr, mb_read_result &r, u32 *error_flag, bool buckets_ready = false, int n_tc_ready = -1) {
     // Taxonomer::chooseBestTaxon (Taxonomer.cpp:130-202), em == false
     if (best.score == 0.f || best.score < cfg.min_score) { r.score = best.score; return 0; }
     if (best.lca) { r.is_classified = 1; r.classification = best.tax; r.score = best.score; return 0; }
@@ -376,6 +378,7 @@ MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_leng
     // filterRedundantMatches (Taxonomer.cpp:205-241)
     const int max_q = (query_length + 3) / cfg.dna_shift;
     if (max_q + 1 > scr.cap_b) { *error_flag = 2; return 0; }
+    if (!buckets_ready) {
     for (int k = 0; k <= max_q; ++k) { scr.bucket_ham[k] = 255; scr.bucket_tax[k] = 0; }
     {
         // the record of the next match is requested while the current one is bucketed (one thread per read: every load
@@ -400,8 +403,10 @@ MB_HD int finish_read(const mb_match *m, const BestSpecies &best, int query_leng
             }
         }
     }
+    }
     int n_tc = 0;                                   // taxCnt as a sorted array (std::map order)
-    {
+    if (n_tc_ready >= 0) n_tc = n_tc_ready;
+    else {
         // neighbouring buckets mostly carry the same taxon: runs are counted in a register and entered once (the arrays
         // live in the per-thread scratch slice, every access is a round trip)
         int32_t run_t = 0;
@@ -905,7 +910,7 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
         const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, ScoreArena arena,
         mb_read_result *__restrict__ results, int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out,
         u64 tc_cap, unsigned long long *tc_counter, u32 *ticket, u32 *error_flag, const u32 *__restrict__ list,
-        const u32 *__restrict__ list_count) {
+        const u32 *__restrict__ list_count, const u64 *__restrict__ list_off, u64 scratch_cap) {
     const u32 lane = threadIdx.x & 31;
     const u64 slot = (u64) blockIdx.x * SC_THREADS + threadIdx.x;
     const u32 total = list ? *list_count : n_reads;
@@ -926,11 +931,14 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
             mb_read_result res;
             int n_tc = 0;
             ReadScratch scr;
-            if (e > b && (e - b) < 0x7FFFFFFFull) {
-                arena_carve(arena, slot, b, (int) (e - b), scr);
+            // per-match scratch: a listed read got a compact offset when it was listed (k_score_fast), so that the scratch
+            // is sized by the matches of the listed reads and not by the whole batch
+            const u64 first = list ? list_off[r0 + lane] : b;
+            if (e > b && (e - b) < 0x7FFFFFFFull && first + (e - b) <= scratch_cap) {
+                arena_carve(arena, slot, first, (int) (e - b), scr);
                 n_tc = score_read(m + b, 0, (int) (e - b), ql, cfg, tax, scr, res, error_flag);
             } else {
-                if (e > b) *error_flag = 4;
+                if (e > b) *error_flag = first + (e - b) > scratch_cap ? 6 : 4;
                 result_init(res, ql, (int32_t) (e - b));
             }
             store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
@@ -952,7 +960,8 @@ struct BestRec {
 __global__ void __launch_bounds__(SC_THREADS)
 k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const u64 *__restrict__ seg_end,
              const u32 *__restrict__ lens, u32 n_reads, int paired, ScoreCfg cfg, TaxView tax, BestRec *__restrict__ best_out,
-             u32 *ticket, u32 *__restrict__ list, u32 *list_count, u32 *overflow_reasons) {
+             u32 *ticket, u32 *__restrict__ list, u32 *list_count, u32 *overflow_reasons, u64 *__restrict__ list_off,
+             unsigned long long *slow_matches) {
     extern __shared__ u32 sc_state[];            // SC_THREADS slices of SC_GSTRIDE words
     u32 wp[SC_PWORDS];                           // path / species lists of this thread's read (local memory)
     const u32 lane = threadIdx.x & 31;
@@ -973,7 +982,9 @@ k_score_fast(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, 
                 const int why = (e - b) < 0x7FFFFFFFull ? best_species_compact(m + b, (int) (e - b), ql, cfg, tax, sc_state + threadIdx.x * SC_GSTRIDE, wp, best) : 6;
                 if (why) {
                     rec.state = 0;
-                    list[atomicAdd(list_count, 1u)] = r;
+                    const u32 li = atomicAdd(list_count, 1u);
+                    list[li] = r;
+                    list_off[li] = atomicAdd(slow_matches, (unsigned long long) (e - b));
                     atomicAdd(overflow_reasons + (why > 7 ? 7 : why), 1u);
                 } else {
                     rec.tax = best.tax; rec.score = best.score; rec.range = (u32) best.rb | ((u32) best.re << 16);
@@ -1035,13 +1046,142 @@ k_score_finish(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin
 // what is independent: getMatchPaths works on one (species, frame) run of the read's matches at a time
 // (Taxonomer.cpp:316-408 calls it per frame), combineMatchPaths on one species.  The four kernels keep every function and
 // every order of the general scorer (scores stay bit-identical) and only change who runs them:
-//   k_lr_heads    one thread per match: lists the first match of every (read, species, frame) run and of every
-//                 (read, species) run
-//   k_lr_paths    one thread per (read, species, frame) run: match_paths -> the run's paths, left beside its matches
+//   k_lr_heads    one thread per match: lists the first match of every piece of a (read, species, frame) run (runs are cut
+//                 where no link is possible) and of every (read, species) run
+//   k_lr_paths    one thread per piece: match_paths -> the piece's paths, left beside its matches
 //   k_lr_species  one thread per (read, species) run: gathers the paths of its frames in frame order and runs
 //                 combine_paths -> the species' score
 //   k_lr_best     one thread per read: walks its species in match order exactly as best_species does (first maximum wins,
 //                 ties within tie_ratio go to the LCA), then finish_read
+// filterRedundantMatches' bucket phase (Taxonomer.cpp:205-241) by a whole thread block: per position bucket the smallest
+// Hamming distance (atomicMin), then the LCA of the targets at that distance (compare-and-swap fold).  LCA is associative
+// and commutative, so the fold order does not matter and the buckets equal the sequential ones.  `ham32` is a cap_b-word
+// scratch array.  Every thread of the block calls it with the same arguments.
+__device__ __forceinline__ void fill_buckets_block(const mb_match *m, int rb, int re, int max_q, const ScoreCfg &cfg, const TaxView &tax,
+                                                   ReadScratch &scr, u32 *ham32) {
+    const int tid = (int) threadIdx.x, nt = (int) blockDim.x;
+    for (int k = tid; k <= max_q; k += nt) { ham32[k] = 255u; scr.bucket_tax[k] = -1; }
+    __syncthreads();
+    const u64 *mw = reinterpret_cast<const u64 *>(m);
+    for (int i = rb + tid; i < re; i += nt) {
+        const u32 pos_i = qi_pos(mw[(u64) i * 3]);
+        const int qd = (int) (cfg.dna_shift == 3 ? pos_i / 3u : cfg.dna_shift == 9 ? pos_i / 9u : pos_i / (u32) cfg.dna_shift);
+        if (qd <= max_q) atomicMin(&ham32[qd], (u32) (mw[(u64) i * 3 + 2] >> 48) & 255u);
+    }
+    __syncthreads();
+    for (int i = rb + tid; i < re; i += nt) {
+        const u32 pos_i = qi_pos(mw[(u64) i * 3]);
+        const int qd = (int) (cfg.dna_shift == 3 ? pos_i / 3u : cfg.dna_shift == 9 ? pos_i / 9u : pos_i / (u32) cfg.dna_shift);
+        if (qd > max_q) continue;
+        const u32 h = (u32) (mw[(u64) i * 3 + 2] >> 48) & 255u;
+        if (h != ham32[qd]) continue;
+        const int32_t target = (int32_t) (u32) mw[(u64) i * 3 + 1];
+        int32_t old = scr.bucket_tax[qd];
+        while (true) {
+            const int32_t nw = old < 0 ? target : (old == target ? old : tax_lca(tax, old, target));
+            if (nw == old) break;
+            const int32_t seen = atomicCAS(&scr.bucket_tax[qd], old, nw);
+            if (seen == old) break;
+            old = seen;
+        }
+    }
+    __syncthreads();
+    for (int k = tid; k <= max_q; k += nt) {
+        const u32 h = ham32[k];
+        scr.bucket_ham[k] = (u8) h;
+        if (h == 255u) scr.bucket_tax[k] = 0;
+    }
+    __syncthreads();
+}
+
+// The taxCnt list of filterRedundantMatches (one count per non-empty bucket, ascending taxID = std::map order) by a whole
+// warp: 32 buckets at a time, equal taxa of the window grouped with match_any, one sorted insert per distinct taxon of the
+// window (neighbouring buckets mostly share their taxon).  Every lane returns the same n_tc.  Warp-synchronous.
+__device__ __forceinline__ int count_taxa_warp(int max_q, ReadScratch &scr) {
+    const int lane = (int) (threadIdx.x & 31);
+    int n_tc = 0;
+    for (int k0 = 0; k0 <= max_q; k0 += 32) {
+        const int k = k0 + lane;
+        const bool valid = k <= max_q && scr.bucket_ham[k] != 255;
+        const int32_t t = valid ? scr.bucket_tax[k] : 0;
+        u32 todo = __ballot_sync(0xFFFFFFFFu, valid);
+        while (todo) {
+            const int leader = __ffs((int) todo) - 1;
+            const int32_t lt = __shfl_sync(0xFFFFFFFFu, t, leader);
+            const u32 same = __ballot_sync(0xFFFFFFFFu, valid && t == lt) & todo;
+            const int cnt = __popc(same);
+            todo &= ~same;
+            // sorted insert of (lt, cnt): all lanes follow the same control flow, lane 0 writes
+            int p = 0;
+            while (p < n_tc && scr.tc_id[p] < lt) ++p;
+            if (p < n_tc && scr.tc_id[p] == lt) { if (lane == 0) scr.tc_cnt[p] += cnt; }
+            else {
+                if (lane == 0) {
+                    for (int z = n_tc; z > p; --z) { scr.tc_id[z] = scr.tc_id[z - 1]; scr.tc_cnt[z] = scr.tc_cnt[z - 1]; }
+                    scr.tc_id[p] = lt; scr.tc_cnt[p] = cnt;
+                }
+                ++n_tc;
+            }
+            __syncwarp();
+        }
+    }
+    return n_tc;
+}
+
+// combine_paths by a whole warp, for species with many paths (contigs): the paths are sorted by lane 0 exactly as
+// combine_paths does; the greedy pass keeps its order (candidates one after another, each checked against the accepted
+// paths in acceptance order) but the 32 lanes look at 32 accepted paths at a time and only the first one that overlaps the
+// candidate is handled, after which the scan resumes behind it with the trimmed candidate — the same sequence of trims and
+// rejections as the sequential loop, since accepted paths that do not overlap leave the candidate unchanged.
+// Warp-synchronous; every lane calls it with the same arguments and gets the same result.
+__device__ __noinline__ float combine_paths_warp(const mb_match *m, PathRec *paths, PathRec *comb, int n_paths, int read_length) {
+    const int lane = (int) (threadIdx.x & 31);
+    if (lane == 0) path_sort(paths, paths + n_paths);
+    __syncwarp();
+    int n_comb = 0;
+    float score = 0.f;
+    for (int i = 0; i < n_paths; ++i) {
+        PathRec cand = paths[i];
+        bool rejected = false;
+        int j = 0;
+        while (j < n_comb) {
+            const int jj = j + lane;
+            bool ov = false;
+            if (jj < n_comb) {
+                const int ks = comb[jj].start, ke = comb[jj].end;
+                ov = !(cand.end < ks || ke < cand.start);
+            }
+            const u32 mask = __ballot_sync(0xFFFFFFFFu, ov);
+            if (!mask) { j += 32; continue; }
+            const int hit = j + (__ffs((int) mask) - 1);
+            const PathRec kept = comb[hit];
+            const int lo = cand.start > kept.start ? cand.start : kept.start;
+            const int hi = cand.end < kept.end ? cand.end : kept.end;
+            const int overlap = hi - lo + 1;
+            if (overlap == cand.end - cand.start + 1 || overlap >= 24) { rejected = true; break; }
+            if (cand.start < kept.start) {
+                cand.end = kept.start - 1;
+                int h = cand.ham - right_part_ham(m[cand.em], overlap / 3);
+                cand.ham = h > 0 ? h : 0;
+                cand.score = cand.score - right_part_score(m[cand.em], overlap / 3) - (float) (overlap % 3);
+            } else {
+                cand.start = kept.end + 1;
+                int h = cand.ham - left_part_ham(m[cand.sm], overlap / 3);
+                cand.ham = h > 0 ? h : 0;
+                cand.score = cand.score - left_part_score(m[cand.sm], overlap / 3) - (float) (overlap % 3);
+            }
+            j = hit + 1;
+        }
+        if (!rejected) {
+            if (lane == 0) comb[n_comb] = cand;
+            ++n_comb;
+            score += cand.score;
+        }
+        __syncwarp();
+    }
+    return score / (float) read_length;
+}
+
 struct LongScratch {
     PathRec *local, *paths, *combined;     // per match, as in ScoreArena
     u8 *linked;
@@ -1053,7 +1193,7 @@ struct LongScratch {
 };
 
 __global__ void __launch_bounds__(256)
-k_lr_heads(const mb_match *__restrict__ m, u64 n, LongScratch ls) {
+k_lr_heads(const mb_match *__restrict__ m, u64 n, LongScratch ls, int max_gap) {
     const u64 i = (u64) blockIdx.x * 256 + threadIdx.x;
     const u32 lane = threadIdx.x & 31;
     bool gh = false, sh = false;
@@ -1065,7 +1205,10 @@ k_lr_heads(const mb_match *__restrict__ m, u64 n, LongScratch ls) {
             const u64 qp = m[i - 1].qinfo;
             const int32_t spp = m[i - 1].speciesId;
             sh = qi_seq(q) != qi_seq(qp) || sp != spp;
-            gh = sh || qi_frame(q) != qi_frame(qp);
+            // a (read, species, frame) run is cut wherever two neighbouring positions are too far apart to be linked
+            // (getMatchPaths only links position groups up to maxCodonShift codons apart, Taxonomer.cpp:530-560): the
+            // pieces are independent and emit their paths in the same order as the whole run would
+            gh = sh || qi_frame(q) != qi_frame(qp) || (int) (qi_pos(q) - qi_pos(qp)) > max_gap;
         }
     }
     // one reservation per warp and list
@@ -1099,10 +1242,17 @@ k_lr_paths(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, co
             const int fb = (int) (h - rb), n = (int) (re - rb);
             const int32_t species = mr[fb].speciesId;
             const u32 frame = qi_frame(mr[fb].qinfo);
+            const int max_gap = 3 * cfg.max_codon_shift;
             int fe = fb + 1;
-            while (fe < n && mr[fe].speciesId == species && qi_frame(mr[fe].qinfo) == frame) ++fe;
+            while (fe < n && mr[fe].speciesId == species && qi_frame(mr[fe].qinfo) == frame &&
+                   (int) (qi_pos(mr[fe].qinfo) - qi_pos(mr[fe - 1].qinfo)) <= max_gap) ++fe;
+            // getBestSpeciesMatches skips a (species, frame) run of a single match (Taxonomer.cpp:340-350): a piece of one
+            // match is scored only when its run has more
+            const bool run_has_more = fe - fb > 1 ||
+                                      (fb > 0 && mr[fb - 1].speciesId == species && qi_frame(mr[fb - 1].qinfo) == frame) ||
+                                      (fe < n && mr[fe].speciesId == species && qi_frame(mr[fe].qinfo) == frame);
             int n_paths = 0;
-            if (fe - fb > 1) {
+            if (run_has_more) {
                 int min_depth = cfg.min_cons_cnt;
                 if (tax_is_ancestor(tax, tax.eukaryota, species)) min_depth = cfg.min_cons_cnt_euk;
                 ReadScratch scr;
@@ -1126,6 +1276,9 @@ k_lr_species(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, 
         if (lane == 0) s0 = atomicAdd(ticket, 32u);
         s0 = __shfl_sync(0xFFFFFFFFu, s0, 0);
         if (s0 >= total) break;
+        u64 sp_start = 0, rb_mine = 0;
+        int sp_stop = 0, np_mine = 0, ql_mine = 1;
+        bool active = false;
         if (s0 + lane < total) {
             const u64 s = ls.sp_heads[s0 + lane];
             const u32 r = qi_seq(m[s].qinfo) - seq_base - 1u;
@@ -1144,17 +1297,35 @@ k_lr_species(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, 
                 n_paths += np;
                 g = ls.grp_end[rb + g];
             }
-            float score = -1.f;
-            if (n_paths > 0) {
-                ReadScratch scr;
-                scr.paths = dst; scr.combined = ls.combined + s;
-                const int ql = max_covered_length((int) lens[2 * r]);
-                score = combine_paths(mr, scr, n_paths, ql);
+            sp_start = s; sp_stop = g; np_mine = n_paths; rb_mine = rb;
+            ql_mine = max_covered_length((int) lens[2 * r]);
+            active = true;
+        }
+        // species with few paths: every lane combines its own; species with many: the whole warp, one after another
+        constexpr int LR_WARP_PATHS = 48;
+        float score = -1.f;
+        if (active && np_mine > 0 && np_mine <= LR_WARP_PATHS) {
+            ReadScratch scr;
+            scr.paths = ls.paths + sp_start; scr.combined = ls.combined + sp_start;
+            score = combine_paths(m + rb_mine, scr, np_mine, ql_mine);
+        }
+        __syncwarp();                                    // the gathered paths of every lane are visible to the warp
+        u32 big = __ballot_sync(0xFFFFFFFFu, active && np_mine > LR_WARP_PATHS);
+        while (big) {
+            const int src = __ffs((int) big) - 1;
+            big &= big - 1;
+            const u64 s_b = __shfl_sync(0xFFFFFFFFu, sp_start, src), rb_b = __shfl_sync(0xFFFFFFFFu, rb_mine, src);
+            const int np_b = __shfl_sync(0xFFFFFFFFu, np_mine, src), ql_b = __shfl_sync(0xFFFFFFFFu, ql_mine, src);
+            const float sc = combine_paths_warp(m + rb_b, ls.paths + s_b, ls.combined + s_b, np_b, ql_b);
+            if ((int) lane == src) score = sc;
+        }
+        if (active) {
+            if (np_mine > 0) {
                 score = score < 1.0f ? score : 1.0f;
                 if (score < cfg.min_score) score = -1.f;
             }
-            ls.sp_score[s] = score;
-            ls.sp_end[s] = g;
+            ls.sp_score[sp_start] = score;
+            ls.sp_end[sp_start] = sp_stop;
         }
         __syncwarp();
     }
@@ -1165,27 +1336,31 @@ k_lr_best(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, con
           u32 n_reads, ScoreCfg cfg, TaxView tax, ScoreArena arena, LongScratch ls, mb_read_result *__restrict__ results,
           int32_t *__restrict__ tc_id_out, int32_t *__restrict__ tc_cnt_out, u64 tc_cap, unsigned long long *tc_counter, u32 *ticket,
           u32 *error_flag) {
-    const u32 lane = threadIdx.x & 31;
-    const u64 slot = ((u64) blockIdx.x * SC_THREADS + threadIdx.x) >> 5;      // one arena slice per WARP
+    // one thread BLOCK per read at a time (reads are few and heavy); thread 0 does what is sequential, the block fills the
+    // redundancy buckets, warp 0 counts the taxa; one arena slice per block
+    __shared__ u32 s_r;
+    __shared__ BestSpecies s_best;
+    __shared__ int s_need, s_ntc;
+    const u32 tid = threadIdx.x;
+    const u64 slot = blockIdx.x;
     while (true) {
-        u32 r0 = 0;
-        if (lane == 0) r0 = atomicAdd(ticket, 1u);              // reads are few and heavy: one per warp (lane 0 works)
-        r0 = __shfl_sync(0xFFFFFFFFu, r0, 0);
-        if (r0 >= n_reads) break;
-        if (lane == 0) {
-            const u32 r = r0;
-            const int ql = max_covered_length((int) lens[2 * r]);
-            const u64 b = seg_begin[r], e = seg_end[r];
-            mb_read_result res;
-            int n_tc = 0;
-            ReadScratch scr;
-            if (e > b && (e - b) < 0x7FFFFFFFull) {
-                const int n = (int) (e - b);
-                arena_carve(arena, slot, b, n, scr);
-                result_init(res, ql, n);
+        __syncthreads();
+        if (tid == 0) s_r = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const u32 r = s_r;
+        if (r >= n_reads) break;
+        const int ql = max_covered_length((int) lens[2 * r]);
+        const u64 b = seg_begin[r], e = seg_end[r];
+        const bool usable = e > b && (e - b) < 0x7FFFFFFFull;
+        const int n = usable ? (int) (e - b) : 0;
+        const int max_q = (ql + 3) / cfg.dna_shift;
+        ReadScratch scr;
+        arena_carve(arena, slot, b, n, scr);
+        if (tid == 0) {
+            BestSpecies best;
+            best.tax = 0; best.score = 0.f; best.lca = false; best.rb = 0; best.re = 0;
+            if (usable) {
                 // Taxonomer::getBestSpeciesMatches (Taxonomer.cpp:316-408) over the species scores, in match order
-                BestSpecies best;
-                best.tax = 0; best.score = 0.f; best.lca = false; best.rb = 0; best.re = 0;
                 int meaningful = 0;
                 float best_sp = 0.f;
                 for (int i = 0; i < n;) {
@@ -1220,14 +1395,33 @@ k_lr_best(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, con
                     if (n_top > 1) { best.lca = true; best.tax = have ? lca : 0; best.score /= (float) n_top; }
                     else best.tax = single;
                 }
-                n_tc = finish_read(m + b, best, ql, cfg, tax, scr, res, error_flag);
+            }
+            s_best = best;
+            s_need = usable && !(best.score == 0.f || best.score < cfg.min_score) && !best.lca && max_q + 1 <= scr.cap_b;
+            s_ntc = -1;
+        }
+        __syncthreads();
+        if (s_need) {
+            fill_buckets_block(m + b, s_best.rb, s_best.re, max_q, cfg, tax, scr, reinterpret_cast<u32 *>(scr.cl_id));
+            if (tid < 32) {
+                const int n_tc_w = count_taxa_warp(max_q, scr);
+                if (tid == 0) s_ntc = n_tc_w;
+            }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            mb_read_result res;
+            int n_tc = 0;
+            if (usable) {
+                result_init(res, ql, n);
+                const BestSpecies best = s_best;
+                n_tc = finish_read(m + b, best, ql, cfg, tax, scr, res, error_flag, s_need != 0, s_ntc);
             } else {
                 if (e > b) *error_flag = 4;
                 result_init(res, ql, (int32_t) (e - b));
             }
             store_result(res, n_tc, scr, r, results, tc_id_out, tc_cnt_out, tc_cap, tc_counter, error_flag);
         }
-        __syncwarp();
     }
 }
 #endif // __CUDACC__
