@@ -681,6 +681,8 @@ def run_b200(a):
     # ---- roofline of the dominant kernel of the step (per-launch CUDA-event times of the last timed step) ----
     peak, peak_src = measured_peak()
     alg = algorithmic_bytes(t_step)
+    if multi:                                  # the counts are sums over the step's batches: per launch = per batch
+        alg = {k: v // len(batches) for k, v in alg.items()}
     table = {}
     for k, (ms, n) in ktimes.items():
         if n == 0:
