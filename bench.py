@@ -79,7 +79,7 @@ def apply_config(a):
     """Fills in the workload of the chosen BASELINE.json config (explicit flags win)."""
     c = {2: dict(label="configs[1]", genomes=10000, pairs=1_000_000, glen=(200_000, 500_000), kind="pairs", seq_mode=2, syncmer=1, fmt=2,
                  rlen=(150, 150), batch=0, cpu=1_000_000),
-         3: dict(label="configs[2]", genomes=130_000, pairs=1_250_000, glen=(80_000, 160_000), kind="pairs", seq_mode=2, syncmer=1, fmt=2,
+         3: dict(label="configs[2]", genomes=130_000, pairs=1_250_000, glen=(40_000, 80_000), kind="pairs", seq_mode=2, syncmer=1, fmt=2,
                  rlen=(150, 150), batch=0, cpu=100_000),
          4: dict(label="configs[3]", genomes=10000, pairs=100_000, glen=(200_000, 500_000), kind="long", seq_mode=3, syncmer=1, fmt=2,
                  rlen=(5_000, 20_000), batch=50_000, cpu=5_000),
@@ -144,12 +144,15 @@ def prepare_db(a, device, rank, world):
         codes, starts = W.make_genomes(tax, a.seed, a.len_min, a.len_max, device)
         log(f"genomes: {len(starts) - 1}, {int(starts[-1]) / 1e9:.2f} Gbp in {time.time() - t0:.1f}s")
         db = W.build_db(tax, codes, starts, device, log=log, syncmer=bool(a.syncmer), kmer_format=a.kmer_format)
+        n_bases = int(starts[-1])
+        del codes
+        torch.cuda.empty_cache()
         n_words = W.write_db_dir(dbdir, db, tax, syncmer=a.syncmer, kmer_format=a.kmer_format)
-        meta = {"genomes": len(starts) - 1, "bases": int(starts[-1]), "db_kmers": int(len(db["values"])), "db_words": int(n_words),
+        meta = {"genomes": len(starts) - 1, "bases": n_bases, "db_kmers": int(len(db["values"])), "db_words": int(n_words),
                 "species": len(tax.species)}
         with open(os.path.join(base, "db.json"), "w") as f:
             json.dump(meta, f)
-        del db, codes
+        del db
         torch.cuda.empty_cache()
         open(marker, "w").close()
         log(f"database written to {dbdir} in {time.time() - t0:.1f}s: {meta}")

@@ -250,7 +250,7 @@ def build_db(tax, codes, starts, device, genomes_per_chunk=200, block=1500, log=
     metamers of the genomes (syncmer_metamers above, torch only); one (strand, frame) is kept per 1.5-kb block, the density of
     a gene-finder driven build."""
     n = len(starts) - 1
-    vals, taxs = [], []
+    vals, taxs = [[] for _ in range(8)], [[] for _ in range(8)]
     t0 = time.time()
     for g0 in range(0, n, genomes_per_chunk):
         g1 = min(n, g0 + genomes_per_chunk)
@@ -259,31 +259,47 @@ def build_db(tax, codes, starts, device, genomes_per_chunk=200, block=1500, log=
         genome = g_rel + g0
         chosen = ((genome * 7919 + (pos // block) * 104729) >> 3) % 6
         keep = frame == chosen
-        vals.append(value[keep].clone())
-        taxs.append(genome[keep].clone())
-        del value, pos, g_rel, frame, genome, chosen, keep
-    v = torch.cat(vals)
-    g = torch.cat(taxs)
-    del vals, taxs
-    gtax = torch.from_numpy(tax.genome_tax).to(device)[g]
-    gsp = torch.from_numpy(tax.genome_species).to(device)[g]
-    del g
-    # order (value unsigned, species, taxid): Kmer.h:77-87
-    o1 = torch.argsort(gsp * (1 << 24) + gtax, stable=True)
-    v, gtax, gsp = v[o1], gtax[o1], gsp[o1]
-    o2 = torch.argsort(v ^ FLIP, stable=True)
-    v, gtax, gsp = v[o2], gtax[o2], gsp[o2]
-    del o1, o2
-    # one entry per (value, species); tax id = LCA of the group's tax ids = the strain if unique, else the species
-    first = torch.ones(len(v), dtype=torch.bool, device=device)
-    first[1:] = (v[1:] != v[:-1]) | (gsp[1:] != gsp[:-1])
-    gid = torch.cumsum(first.to(torch.int64), 0) - 1
-    ng = int(gid[-1].item()) + 1
-    tmin = torch.full((ng,), 1 << 40, dtype=torch.int64, device=device).scatter_reduce_(0, gid, gtax, "amin")
-    tmax = torch.zeros(ng, dtype=torch.int64, device=device).scatter_reduce_(0, gid, gtax, "amax")
-    out_v = v[first]
-    out_sp = gsp[first]
-    out_t = torch.where(tmin == tmax, tmin, out_sp)
+        vk, gk = value[keep], genome[keep]
+        tb = (vk >> 61) & 7                              # value range (top three bits): sorted separately below
+        for bucket in range(8):
+            mb_ = tb == bucket
+            vals[bucket].append(vk[mb_].clone())
+            taxs[bucket].append(gk[mb_].to(torch.int32))
+        del value, pos, g_rel, frame, genome, chosen, keep, vk, gk, tb
+    gtax_of = torch.from_numpy(tax.genome_tax).to(device)
+    gsp_of = torch.from_numpy(tax.genome_species).to(device)
+    # sorted and de-duplicated in eight value ranges (top three bits), one after another: torch sorts (and masks) at most
+    # 2^31 - 1 elements at a time, and a GTDB-scale build has more k-mers than that before the de-duplication
+    outs_v, outs_t = [], []
+    for bucket in range(8):
+        if not vals[bucket] or sum(len(x) for x in vals[bucket]) == 0:
+            continue
+        v = torch.cat(vals[bucket])
+        g = torch.cat(taxs[bucket]).long()
+        vals[bucket], taxs[bucket] = None, None
+        gtax = gtax_of[g]
+        gsp = gsp_of[g]
+        del g
+        # order (value unsigned, species, taxid): Kmer.h:77-87
+        o1 = torch.argsort(gsp * (1 << 24) + gtax, stable=True)
+        v, gtax, gsp = v[o1], gtax[o1], gsp[o1]
+        o2 = torch.argsort(v ^ FLIP, stable=True)
+        v, gtax, gsp = v[o2], gtax[o2], gsp[o2]
+        del o1, o2
+        # one entry per (value, species); tax id = LCA of the group's tax ids = the strain if unique, else the species
+        first = torch.ones(len(v), dtype=torch.bool, device=device)
+        first[1:] = (v[1:] != v[:-1]) | (gsp[1:] != gsp[:-1])
+        gid = torch.cumsum(first.to(torch.int64), 0) - 1
+        ng = int(gid[-1].item()) + 1
+        tmin = torch.full((ng,), 1 << 40, dtype=torch.int64, device=device).scatter_reduce_(0, gid, gtax, "amin")
+        tmax = torch.zeros(ng, dtype=torch.int64, device=device).scatter_reduce_(0, gid, gtax, "amax")
+        o_sp = gsp[first]
+        outs_v.append(v[first])
+        outs_t.append(torch.where(tmin == tmax, tmin, o_sp))
+        del v, gtax, gsp, first, gid, tmin, tmax, o_sp
+    out_v = torch.cat(outs_v)
+    out_t = torch.cat(outs_t)
+    del outs_v, outs_t
     if log:
         log(f"db: {len(out_v)} k-mers from {n} genomes in {time.time() - t0:.1f}s")
     return {"values": out_v, "info": out_t}

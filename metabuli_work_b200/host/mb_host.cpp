@@ -2,6 +2,9 @@
 // the reference tree.
 #include "mb_host.h"
 
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
 #include <algorithm>
@@ -217,11 +220,25 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     const std::string taxPath = opt.taxonomyPath.empty() ? dir + "/taxonomyDB" : opt.taxonomyPath + "/taxonomyDB";
     if (!tax_.load(taxPath, err)) return false;
 
-    std::vector<char> words, info, splitBytes;
-    if (!readFile(dir + "/diffIdx", words, err) || !readFile(dir + "/info", info, err) || !readFile(dir + "/split", splitBytes, err)) return false;
-    const uint16_t *w = reinterpret_cast<const uint16_t *>(words.data());
-    const uint32_t *inf = reinterpret_cast<const uint32_t *>(info.data());
-    const size_t nWords = words.size() / 2, nKmers = info.size() / 4;
+    // Only the shard's byte ranges of diffIdx / info are read (a rank of an 8-GPU run touches an eighth of the files); the
+    // split table is small and read whole.
+    std::vector<char> splitBytes;
+    if (!readFile(dir + "/split", splitBytes, err)) return false;
+    struct stat stW, stI;
+    if (stat((dir + "/diffIdx").c_str(), &stW) != 0 || stat((dir + "/info").c_str(), &stI) != 0) { err = "cannot stat diffIdx / info in " + dir; return false; }
+    const size_t nWords = (size_t) stW.st_size / 2, nKmers = (size_t) stI.st_size / 4;
+    const int fdW = ::open((dir + "/diffIdx").c_str(), O_RDONLY), fdI = ::open((dir + "/info").c_str(), O_RDONLY);
+    if (fdW < 0 || fdI < 0) { if (fdW >= 0) ::close(fdW); if (fdI >= 0) ::close(fdI); err = "cannot open diffIdx / info in " + dir; return false; }
+    struct Closer { int a, b; ~Closer() { ::close(a); ::close(b); } } closer{fdW, fdI};
+    auto preadAll = [&](int fd, void *dst, size_t bytes, size_t off) -> bool {
+        char *p = static_cast<char *>(dst);
+        while (bytes) {
+            const ssize_t got = ::pread(fd, p, bytes, (off_t) off);
+            if (got <= 0) return false;
+            p += got; off += (size_t) got; bytes -= (size_t) got;
+        }
+        return true;
+    };
     const mb_split *splits = reinterpret_cast<const mb_split *>(splitBytes.data());
     const size_t nSplits = splitBytes.size() / sizeof(mb_split);
 
@@ -240,8 +257,13 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
         for (int g = 1; g < nShards; ++g) {
             const mb_split &s = cuts[(size_t) g * cuts.size() / (size_t) nShards];
             if (s.diffIdxOffset == 0 || s.diffIdxOffset > nWords || s.infoIdxOffset == 0) { err = "split entry out of range"; return false; }
+            // the words in front of the boundary: a delta has at most five
+            const size_t lookFrom = s.diffIdxOffset >= 6 ? (size_t) s.diffIdxOffset - 6 : 0;
+            uint16_t look[6] = {0, 0, 0, 0, 0, 0};
+            const size_t nLook = (size_t) s.diffIdxOffset - lookFrom;
+            if (!preadAll(fdW, look, nLook * 2, lookFrom * 2)) { err = "short read on " + dir + "/diffIdx"; return false; }
             size_t start = (size_t) s.diffIdxOffset - 1;       // terminator word of ADkmer's delta
-            while (start > 0 && !(w[start - 1] & 0x8000u)) --start;
+            while (start > lookFrom && !(look[start - 1 - lookFrom] & 0x8000u)) --start;
             cutPoints.push_back({s.ADkmer, start, (size_t) s.diffIdxOffset, (size_t) s.infoIdxOffset - 1});
             // A query is compared with EVERY DB k-mer of its amino-acid group, whatever its DNA part, and a split entry is
             // the first DB k-mer of a group (IndexCreator.cpp:843-846): route on the amino-acid part only, so that a query of
@@ -251,6 +273,8 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     }
     size_t wBegin = 0, wEnd = nWords, kBegin = 0, kEnd = nKmers;
     std::vector<uint16_t> shardWords;
+    std::vector<uint32_t> shardInfo;
+    size_t prefix = 0;
     if (nShards > 1) {
         if (shard > 0) { wBegin = cutPoints[shard - 1].wordAfter; kBegin = cutPoints[shard - 1].kIndex; }
         if (shard + 1 < nShards) { wEnd = cutPoints[shard].wordStart; kEnd = cutPoints[shard].kIndex; }
@@ -265,8 +289,12 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
             while (v) { tmp[idx--] = (uint16_t) (v & 0x7FFFu); v >>= 15; }
             for (int k = idx + 1; k <= 4; ++k) shardWords.push_back(tmp[k]);
         }
-        shardWords.insert(shardWords.end(), w + wBegin, w + wEnd);
+        prefix = shardWords.size();
     }
+    shardWords.resize(prefix + (wEnd - wBegin));
+    shardInfo.resize(kEnd - kBegin);
+    if (!preadAll(fdW, shardWords.data() + prefix, (wEnd - wBegin) * 2, wBegin * 2)) { err = "short read on " + dir + "/diffIdx"; return false; }
+    if (!preadAll(fdI, shardInfo.data(), (kEnd - kBegin) * 4, kBegin * 4)) { err = "short read on " + dir + "/info"; return false; }
 
     mb_default_params(&par_);
     par_.device = opt.device;
@@ -313,12 +341,10 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
         err = mb_last_error(ctx_);
         return false;
     }
-    int rc;
-    if (nShards > 1) rc = mb_load_db(ctx_, shardWords.data(), shardWords.size(), inf + kBegin, kEnd - kBegin);
-    else rc = mb_load_db(ctx_, w, nWords, inf, nKmers);
+    const int rc = mb_load_db(ctx_, shardWords.data(), shardWords.size(), shardInfo.data(), shardInfo.size());
     if (rc != MB_OK) { err = mb_last_error(ctx_); return false; }
     nKmers_ = kEnd - kBegin;
-    nWords_ = nShards > 1 ? shardWords.size() : nWords;
+    nWords_ = shardWords.size();
     return true;
 }
 
