@@ -172,6 +172,10 @@ int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2,
  * them instead of copying.  The texts must stay untouched until that call; pinned memory (mb_alloc_host) makes the copy
  * truly asynchronous. */
 int mb_prefetch_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2, size_t n2);
+/* Device memory of the context's GPU right now (cudaMemGetInfo), for sizing batches: the reference sizes its query
+ * splits from --max-ram and bytesPerKmer = 16 + matchPerKmer * 32 (QueryIndexer::indexQueryFile,
+ * src/commons/QueryIndexer.cpp:62-67); a host on top of this library does the same against free HBM. */
+int mb_mem_info(mb_ctx *ctx, size_t *free_bytes, size_t *total_bytes);
 /* Page-locked host memory for read / text buffers (cudaMallocHost); NULL on failure. */
 void *mb_alloc_host(size_t bytes);
 void mb_free_host(void *p);

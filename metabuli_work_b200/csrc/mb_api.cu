@@ -97,8 +97,12 @@ struct mb_ctx {
     u64 n_words = 0, n_db_kmers = 0, n_raw = 0;
     u32 n_units = 0;
     SortT units_t{-1, 0};             // the T function the unit index was cut for (rebuilt when the sort key changes)
-    int match_ctas = 0;               // resident CTAs of k_match on this context's device (0 = not asked yet)
-    bool match_attr_set = false;
+    // per-context (= per-device) launch facts: function attributes and occupancy are per device, so nothing of this is static
+    int sms = 0;                      // multiprocessors of the context's device
+    int match_ctas = 0;               // resident CTAs of k_match (0 = not asked yet)
+    int seg_ctas = 0, fast_ctas = 0;
+    bool match_attr_set = false, ex_attr_set = false, fast_attr_set = false;
+    unsigned radix_attr_mask = 0;     // bit per radix instantiation whose shared-memory opt-in was done (radix_slot<>)
     // taxonomy
     DevBuf parent, depth, species_of, species_rank_of, tax_node;
     DevBuf fq_text[2], fq_tile_cnt, fq_tile_off, fq_lines[2], fq_src, fq_name_off, fq_name_len, fq_info, fq_sums, fq_sum_off;   // mb_stage_fastq
@@ -225,6 +229,11 @@ static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
 }
 
 // ---- radix sort driver --------------------------------------------------------------------------------
+// one bit of mb_ctx::radix_attr_mask per instantiation of the pass kernel (numbered in order of first use, process wide)
+static int g_radix_slots = 0;
+template <typename Rec, typename Key, int ITEMS>
+static int radix_slot() { static const int slot = g_radix_slots++; return slot; }
+
 template <typename Rec, typename Key, int ITEMS>
 static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, int n_passes, int kid_base, SegIn *seg_in = nullptr) {
     // seg_in (n > 0): the records lie in the regions of a peer receive buffer, outside the ping-pong pair; the histogram
@@ -251,7 +260,7 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     CK(ctx->tile_state.ensure(tiles * RS_BINS * sizeof(u64)));
     CK(cudaMemsetAsync(ctx->hist.p, 0, sizeof(u64) * RS_BINS * n_passes, ctx->stream));
     CK(cudaMemsetAsync(&ctx->dcnt()->trivial, 0, sizeof(u32) * RS_MAX_PASSES, ctx->stream));
-    const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+    const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, (u64) ctx->sms * 8);
     if (seg.n)
         KL(kid_base + 0, k_radix_hist<Rec, Key, true><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), ctx->stream>>>(
             a.as<Rec>(), n, key, n_passes, ctx->hist.as<u64>(), seg));
@@ -261,11 +270,11 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     KL(kid_base + 1, k_radix_scan_hist<<<n_passes, RS_BINS, 0, ctx->stream>>>(ctx->hist.as<u64>(), n, ctx->dcnt()->trivial));
     constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
     static const int radix_dbg = getenv("MB_RADIX_DBG") ? atoi(getenv("MB_RADIX_DBG")) : 0;     // timing experiments only
-    static bool attr_set = false;
-    if (!attr_set) {
+    const unsigned slot_bit = 1u << (radix_slot<Rec, Key, ITEMS>() & 31);
+    if (!(ctx->radix_attr_mask & slot_bit)) {
         CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        attr_set = true;
+        ctx->radix_attr_mask |= slot_bit;
     }
     for (int p = 0; p < n_passes; ++p) {
         CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * RS_BINS * sizeof(u64), ctx->stream));
@@ -357,6 +366,7 @@ mb_ctx *mb_create(const mb_params *p) {
     memset(&ctx->times, 0, sizeof(ctx->times));
     for (int i = 0; i < EV_COUNT; ++i) ctx->ev_set[i] = false;
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, p->device) == cudaSuccess && ctx->sms > 0;
     for (int i = 0; ok && i < EV_COUNT; ++i) ok = cudaEventCreate(&ctx->ev[i]) == cudaSuccess;
     ok = ok && cudaHostAlloc(&ctx->pinned, 256, cudaHostAllocDefault) == cudaSuccess;
     ok = ok && ctx->tables.ensure(sizeof(Tables)) == cudaSuccess && ctx->counters.ensure(sizeof(Counters)) == cudaSuccess;
@@ -806,6 +816,13 @@ int mb_prefetch_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *tex
     return MB_OK;
 }
 
+int mb_mem_info(mb_ctx *ctx, size_t *free_bytes, size_t *total_bytes) {
+    if (!ctx || !free_bytes || !total_bytes) return MB_E_ARG;
+    CK(cudaSetDevice(ctx->par.device));
+    CK(cudaMemGetInfo(free_bytes, total_bytes));
+    return MB_OK;
+}
+
 void *mb_alloc_host(size_t bytes) {
     void *p = nullptr;
     if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
@@ -856,13 +873,12 @@ static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
         else CK(cudaMemsetAsync(ctx->route.sent_k, 0, MB_MAX_RANKS * sizeof(unsigned long long), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->kmer_count, 0, sizeof(unsigned long long), ctx->stream));
         KL(KID_TILE_MATE, k_tile_first_mate<<<(n_tiles + 1 + 255) / 256, 256, 0, ctx->stream>>>(a, n_tiles, ctx->tile_mate.as<u32>()));
-        static bool ex_attr = false;
-        if (!ex_attr) {
+        if (!ctx->ex_attr_set) {
             CK(cudaFuncSetAttribute(k_extract<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
             CK(cudaFuncSetAttribute(k_extract<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
             CK(cudaFuncSetAttribute(k_extract<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
             CK(cudaFuncSetAttribute(k_extract<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) extract_smem_bytes()));
-            ex_attr = true;
+            ctx->ex_attr_set = true;
         }
         mb_kmer *out = routed ? nullptr : ctx->kmers_a.as<mb_kmer>();
         const Route *rt = routed ? ctx->route_dev.as<Route>() : nullptr;
@@ -959,12 +975,11 @@ static int match_impl(mb_ctx *ctx, size_t *n_matches, const bool routed) {
             if (routed) CK(cudaMemsetAsync(ctx->route.sent_m, 0, MB_MAX_RANKS * sizeof(unsigned long long), ctx->stream));
             // persistent: as many CTAs as are resident at once (3 per SM: 66 KB of shared memory each); every warp draws units
             if (!ctx->match_ctas) {
-                int per_sm = 0, sms = 0;
+                int per_sm = 0;
                 CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_match<false>, MT_THREADS, match_smem_bytes()));
-                CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
                 static const int env_ctas = getenv("MB_MATCH_CTAS_PER_SM") ? atoi(getenv("MB_MATCH_CTAS_PER_SM")) : 0;     // tuning knob
                 if (env_ctas > 0 && env_ctas < per_sm) per_sm = env_ctas;
-                ctx->match_ctas = std::max(1, per_sm) * std::max(1, sms);
+                ctx->match_ctas = std::max(1, per_sm) * ctx->sms;
             }
             const unsigned grid = (unsigned) std::min<u64>(((u64) nu + MT_WARPS - 1) / MT_WARPS, (u64) ctx->match_ctas);
 #define MB_LAUNCH_MATCH(R, ROUTE) KL(KID_MATCH, (k_match<R><<<grid, MT_THREADS, match_smem_bytes(), ctx->stream>>>( \
@@ -1047,15 +1062,13 @@ int mb_sort_matches(mb_ctx *ctx) {
         CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
         CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 4 * sizeof(u32), ctx->stream));
         CK(ctx->seg_long.ensure((size_t) ctx->n_reads * sizeof(u32)));
-        static int seg_ctas = 0;
-        if (!seg_ctas) {
+        if (!ctx->seg_ctas) {
             CK(cudaFuncSetAttribute(k_sort_segments_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
-            int per_sm = 0, sms = 148;
+            int per_sm = 0;
             CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sort_segments<true>, SS_THREADS, 0));
-            CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
-            seg_ctas = std::max(1, per_sm) * sms;
+            ctx->seg_ctas = std::max(1, per_sm) * ctx->sms;
         }
-        const unsigned grid = (unsigned) std::min<u64>((u64) seg_ctas, ((u64) ctx->n_reads + 63) / 64);
+        const unsigned grid = (unsigned) std::min<u64>((u64) ctx->seg_ctas, ((u64) ctx->n_reads + 63) / 64);
         if (sk.total_bits() <= 55)
             KL(KID_SEGSORT, k_sort_segments<true><<<grid, SS_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
@@ -1065,7 +1078,7 @@ int mb_sort_matches(mb_ctx *ctx) {
                 ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
                 &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
         // segments of 513..1024 matches (rare with short reads): shared-memory network, one warp each
-        KL(KID_SEGSORT_LONG, k_sort_segments_long<<<148, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
+        KL(KID_SEGSORT_LONG, k_sort_segments_long<<<(unsigned) ctx->sms, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
             ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), sk,
             &ctx->dcnt()->seg_long_ticket, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
         u32 too_long = 0;
@@ -1116,14 +1129,14 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
         arena.slice_bytes = arena_slice_bytes(arena.cap_b, arena.cap_c);
         // one thread per read; resident threads fill the machine, bounded by a 4-GB arena of per-thread slices
         const u64 budget = 4ull << 30;
-        u64 resident = 148ull * 2048;
-        if (const char *ev = getenv("MB_SCORE_THREADS_PER_SM")) resident = 148ull * (u64) std::max(128, atoi(ev));   // tuning knob
+        u64 resident = (u64) ctx->sms * 2048;
+        if (const char *ev = getenv("MB_SCORE_THREADS_PER_SM")) resident = (u64) ctx->sms * (u64) std::max(128, atoi(ev));   // tuning knob
         u64 threads = std::min<u64>(resident, std::max<u64>(budget / arena.slice_bytes, SC_THREADS));
         threads = std::min<u64>(threads, (u64) nr + SC_THREADS);
         const unsigned grid = (unsigned) std::max<u64>(1, threads / SC_THREADS);
         // short reads: the leftover scorer runs beside k_score_finish on a second stream, with its own slices behind the
         // first `grid` blocks' worth
-        const unsigned slow_grid = std::min<unsigned>(grid, 148u * 8);
+        const unsigned slow_grid = std::min<unsigned>(grid, (unsigned) ctx->sms * 8);
         CK(ctx->arena.ensure((size_t) (grid + slow_grid) * SC_THREADS * arena.slice_bytes));
         arena.base = ctx->arena.as<unsigned char>();
         const size_t nm = std::max<size_t>(ctx->n_matches, 1);
@@ -1160,23 +1173,20 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
             bucket_stride |= 1;
             const size_t fin_smem = (size_t) SC_THREADS * bucket_stride * sizeof(u32);
             if (fin_smem > 200 * 1024) return fail(ctx, MB_E_ARG, "reads too long for seq-mode 1/2 scoring: use --seq-mode 3");
-            static bool fast_attr = false;
-            if (!fast_attr) {
+            if (!ctx->fast_attr_set) {
                 CK(cudaFuncSetAttribute(k_score_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) fast_smem));
                 CK(cudaFuncSetAttribute(k_score_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-                fast_attr = true;
+                ctx->fast_attr_set = true;
             }
             // persistent: every resident slot (the DP state is 100 B of shared memory per thread; registers set the limit)
-            static int fast_ctas = 0;
-            if (!fast_ctas) {
-                int per_sm = 0, sms = 148;
+            if (!ctx->fast_ctas) {
+                int per_sm = 0;
                 CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast, SC_THREADS, fast_smem));
-                CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
                 static const int env_ctas = getenv("MB_SCORE_CTAS_PER_SM") ? atoi(getenv("MB_SCORE_CTAS_PER_SM")) : 0;      // tuning knob
                 if (env_ctas > 0 && env_ctas < per_sm) per_sm = env_ctas;
-                fast_ctas = std::max(1, per_sm) * sms;
+                ctx->fast_ctas = std::max(1, per_sm) * ctx->sms;
             }
-            const unsigned fast_grid = (unsigned) std::min<u64>((u64) fast_ctas, ((u64) nr + SC_THREADS - 1) / SC_THREADS);
+            const unsigned fast_grid = (unsigned) std::min<u64>((u64) ctx->fast_ctas, ((u64) nr + SC_THREADS - 1) / SC_THREADS);
             KL(KID_SCORE_FAST, k_score_fast<<<fast_grid, SC_THREADS, fast_smem, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->lens.as<u32>(), nr, paired, cfg, tv,
                 ctx->best_recs.as<BestRec>(), &ctx->dcnt()->score_ticket, ctx->slow_list.as<u32>(), &ctx->dcnt()->slow_count,
@@ -1221,9 +1231,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
             ls.grp_heads = ctx->lr_grp_heads.as<u32>(); ls.sp_heads = ctx->lr_sp_heads.as<u32>();
             ls.n_grp = &ctx->dcnt()->lr_n_grp; ls.n_sp = &ctx->dcnt()->lr_n_sp;
             CK(cudaMemsetAsync(&ctx->dcnt()->lr_n_grp, 0, 5 * sizeof(u32), ctx->stream));
-            int sms = 0;
-            CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->par.device));
-            const unsigned wide = (unsigned) std::max(1, sms) * 16;          // 16 CTAs of 128 threads per SM
+            const unsigned wide = (unsigned) ctx->sms * 16;          // 16 CTAs of 128 threads per SM
             if (ctx->n_matches) {
                 KL(KID_LR_HEADS, k_lr_heads<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(
                     ctx->matches_a.as<mb_match>(), ctx->n_matches, ls, 3 * cfg.max_codon_shift));
@@ -1690,7 +1698,7 @@ int noalloc_sort(mb_ctx *ctx, cudaStream_t st, NoallocScratch *sc, mb_kmer *a, m
     const SegIn seg = {};
     CK(cudaMemsetAsync(sc->hist, 0, sizeof(u64) * RS_BINS * n_passes, st));
     CK(cudaMemsetAsync(sc->trivial, 0, sizeof(sc->trivial), st));
-    const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+    const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, (u64) ctx->sms * 8);
     k_radix_hist<mb_kmer, Key, false><<<(unsigned) hist_ctas, RS_THREADS, n_passes * RS_BINS * sizeof(u32), st>>>(a, n, key, n_passes, sc->hist, seg);
     CK(cudaGetLastError());
     k_radix_scan_hist<<<n_passes, RS_BINS, 0, st>>>(sc->hist, n, sc->trivial);

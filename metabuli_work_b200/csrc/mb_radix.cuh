@@ -163,7 +163,7 @@ k_radix_pass(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, 
     // tiles are taken in ticket order, so the tile that a CTA starting about one machine-full of CTAs later will load is
     // known now: ask L2 for it (that CTA's load phase then waits on L2 instead of HBM)
     if (!SEG) {
-        constexpr u64 AHEAD = 148ull * 1;
+        constexpr u64 AHEAD = 148ull;                // tiles: about one machine-full of CTAs ahead on a B200 (a prefetch distance, not a grid size)
         const u64 pf_base = (tile_base + AHEAD * TILE) * sizeof(Rec);
         const u64 end_bytes = n * sizeof(Rec);
         for (u64 o = pf_base + (u64) tid * 128; o < pf_base + (u64) TILE * sizeof(Rec) && o < end_bytes; o += (u64) RS_THREADS * 128)

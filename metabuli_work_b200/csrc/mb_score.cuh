@@ -515,7 +515,10 @@ constexpr int SF_P = 16;     // paths per species: the size up to which std::sor
 // collects the paths of every species, (2) one loop over the species that have paths sorts and combines them.
 constexpr int SC_G = 4;                          // matches per (species, frame, position) group
 constexpr int SC_NP = 40;                        // paths per read
-constexpr int SC_NS = 16;                        // species with paths per read
+#ifndef MB_SC_NS
+#define MB_SC_NS 16
+#endif
+constexpr int SC_NS = MB_SC_NS;                  // species with paths per read
 constexpr int SC_GWORDS = 2 * SC_G * 3;          // DP state `w`: 2 groups x SC_G entries x 3 words (shared memory on the device)
 constexpr int SC_GSTRIDE = SC_GWORDS + 1;        // odd: lanes touching the same word hit different banks
 constexpr int SC_W_SPEC = SC_NP * 3;             // path list `wp`: SC_NP paths x 3 words, then SC_NS species x 2 words:
@@ -916,7 +919,9 @@ k_score(const mb_match *__restrict__ m, const u64 *__restrict__ seg_begin, const
     const u32 total = list ? *list_count : n_reads;
     // Left-over reads are few and heavy, and the general form diverges completely between lanes: one read per WARP
     // (lane 0 works) finishes them sooner than 32 per warp.  The full-batch form takes 32 consecutive reads per warp.
-    const u32 per_ticket = list ? 1u : 32u;
+    // ... unless there are so many that every warp gets 32 anyway (a database with dozens of species per genus leaves a
+    // large share of the reads over): then lanes that idle cost more than divergence does
+    const u32 per_ticket = (list && total < 32u * gridDim.x * (SC_THREADS / 32)) ? 1u : 32u;
     while (true) {
         u32 r0 = 0;
         if (lane == 0) r0 = atomicAdd(ticket, per_ticket);

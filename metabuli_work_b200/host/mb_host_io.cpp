@@ -311,6 +311,19 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     const auto t1 = clk::now();
     std::cout << "DB resident on GPU " << opt.device << ": " << db.numKmers() << " k-mers, " << db.numWords() * 2 + db.numKmers() * 4
               << " bytes (" << std::chrono::duration<double>(t1 - t0).count() << " s)" << std::endl;
+    // Batch size from the memory that is left (QueryIndexer::indexQueryFile sizes its splits the same way from --max-ram,
+    // QueryIndexer.cpp:62-67: bytes per k-mer slot = k-mer record(s) + matchPerKmer match records).  Per slot here: two
+    // 16-byte k-mer buffers, and per expected match two 24-byte match buffers plus the scorer's per-match scratch
+    // (85 bytes with long reads, an eighth of 93 bytes with short reads).  --max-ram (GB) caps the budget like it caps the
+    // reference's host memory.
+    size_t freeB = 0, totalB = 0;
+    if (mb_mem_info(db.ctx(), &freeB, &totalB) != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
+    const size_t budget = std::min<size_t>((size_t) (0.9 * (double) freeB), (size_t) std::max(1, opt.ramUsage) << 30);
+    const size_t slotBytes = 32 + (size_t) std::max(1, opt.matchPerKmer) * (48 + (opt.seqMode == 3 ? 85 : 12));
+    const size_t maxSlots = std::max<size_t>(budget / slotBytes, 1u << 20);
+    const size_t maxBatchBases = maxSlots / 2;          // about two k-mer slots per base (six frames, one per codon)
+    std::cout << "Batch budget: " << (budget >> 20) << " MiB of HBM (" << (freeB >> 20) << " MiB free), at most " << maxBatchBases
+              << " bases per batch" << std::endl;
     Reporter rep(db.taxonomy(), outDir, jobId, opt.printLineage != 0, opt.kronaPrelude);
     if (!rep.openClassifications(err)) return 1;
     const bool paired = opt.seqMode == 2;
@@ -329,7 +342,9 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
         if (!f1.open(inputs[0])) { err = "cannot open " + inputs[0]; return 1; }
         if (paired && !f2.open(inputs[1])) { err = "cannot open " + inputs[1]; return 1; }
         // a chunk holds at least one batch of short reads (~330 text bytes per 150-base record) and never less than 64 MB
-        const size_t chunk = std::max<size_t>(64u << 20, std::min<size_t>(opt.batchReads * 400, 2ull << 30));
+        // ... and holds no more bases than the batch budget allows (FASTQ text is a little over twice its bases)
+        const size_t chunk = std::min<size_t>(std::max<size_t>(64u << 20, std::min<size_t>(opt.batchReads * 400, 2ull << 30)),
+                                              std::max<size_t>(maxBatchBases * 2 + (1u << 20), 4u << 20));
         std::vector<uint64_t> nameOff;
         std::vector<uint32_t> nameLen;
         while (true) {
@@ -393,7 +408,7 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     if (!r1.open(inputs[0], err)) return 1;
     if (paired && !r2.open(inputs[1], err)) return 1;
     // long reads: bound the batch by bases as well (QueryIndexer sizes batches by k-mer count, QueryIndexer.cpp:62-67)
-    const size_t maxBases = 4ull << 30;
+    const size_t maxBases = std::min<size_t>(4ull << 30, maxBatchBases);
     while (loadBatch(r1, paired ? &r2 : nullptr, opt.batchReads, maxBases, batch)) {
         res.resize(batch.nReads());
         size_t used = 0;
