@@ -248,6 +248,10 @@ int mb_peer_alloc(mb_ctx *ctx, size_t kmer_cap, size_t match_cap, mb_peer_mem *o
 int mb_ipc_export(mb_ctx *ctx, const void *dptr, unsigned char handle[64]);
 int mb_ipc_open(mb_ctx *ctx, const unsigned char handle[64], void **dptr);
 int mb_ipc_close(mb_ctx *ctx, void *dptr);
+/* One process driving several GPUs (the C++ host's --gpus N): lets the context's GPU store into the memory of
+ * `peer_device` (cudaDeviceEnablePeerAccess; a no-op for the context's own device or when access is already on).  With it
+ * the mb_peer_mem pointers of the other contexts can be passed to mb_peer_attach as they are — no CUDA IPC. */
+int mb_enable_peer_access(mb_ctx *ctx, int peer_device);
 int mb_peer_attach(mb_ctx *ctx, uint32_t rank, uint32_t n_ranks, const mb_peer_mem *peers, const uint64_t *bounds,
                    uint32_t reads_per_rank);
 int mb_extract_kmers_routed(mb_ctx *ctx, size_t *n_emitted);

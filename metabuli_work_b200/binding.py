@@ -67,7 +67,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
                "mb_prefetch_reads", "mb_stage_fastq", "mb_prefetch_fastq", "mb_alloc_host", "mb_free_host", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches",
-               "mb_sort_kmers_noalloc", "mb_mem_info"]
+               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -116,6 +116,7 @@ _sig(_cuda, "mb_partition_kmers", C.c_int, [vp, vp, C.c_int, vp])
 _sig(_cuda, "mb_partition_matches", C.c_int, [vp, u32, C.c_int, vp])
 _sig(_cuda, "mb_get_timings", C.c_int, [vp, C.POINTER(PhaseTimes)])
 _sig(_cuda, "mb_mem_info", C.c_int, [vp, szp, szp])
+_sig(_cuda, "mb_enable_peer_access", C.c_int, [vp, C.c_int])
 _sig(_cuda, "mb_sort_kmers_noalloc", C.c_int, [vp, vp, vp, sz, vp])
 _sig(_cuda, "mb_stream", vp, [vp])
 _sig(_cuda, "mb_set_profile", C.c_int, [vp, C.c_int])

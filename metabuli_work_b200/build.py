@@ -38,15 +38,15 @@ def build(force=False, verbose=False):
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         subprocess.check_call(cmd)
-    host_src = [os.path.join(HOST, "mb_host.cpp"), os.path.join(HOST, "mb_host_io.cpp")]
+    host_src = [os.path.join(HOST, "mb_host.cpp"), os.path.join(HOST, "mb_host_io.cpp"), os.path.join(HOST, "mb_host_multi.cpp")]
     host_all = host_src + [os.path.join(HOST, "mb_host.h"), inc]
     rpath = "-Wl,-rpath,$ORIGIN"
     if force or _newer(LIB_HOST, host_all + [LIB_CUDA]):
         subprocess.check_call([CXX, "-O2", "-std=gnu++17", "-fPIC", "-shared", "-Wall", "-o", LIB_HOST] + host_src +
-                              ["-L" + PKG, "-lmetabuli_b200", "-lz", rpath])
+                              ["-L" + PKG, "-lmetabuli_b200", "-lz", "-lpthread", rpath])
     if force or _newer(CLI, host_all + [os.path.join(HOST, "metabuli_main.cpp"), LIB_CUDA]):
         subprocess.check_call([CXX, "-O2", "-std=gnu++17", "-Wall", "-o", CLI, os.path.join(HOST, "metabuli_main.cpp")] + host_src +
-                              ["-L" + PKG, "-lmetabuli_b200", "-lz", rpath])
+                              ["-L" + PKG, "-lmetabuli_b200", "-lz", "-lpthread", rpath])
     return LIB_CUDA, LIB_HOST, CLI
 
 

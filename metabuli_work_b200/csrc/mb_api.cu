@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -230,7 +231,7 @@ static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
 
 // ---- radix sort driver --------------------------------------------------------------------------------
 // one bit of mb_ctx::radix_attr_mask per instantiation of the pass kernel (numbered in order of first use, process wide)
-static int g_radix_slots = 0;
+static std::atomic<int> g_radix_slots{0};
 template <typename Rec, typename Key, int ITEMS>
 static int radix_slot() { static const int slot = g_radix_slots++; return slot; }
 
@@ -1485,6 +1486,19 @@ int mb_ipc_close(mb_ctx *ctx, void *dptr) {
     CK(cudaSetDevice(ctx->par.device));
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaIpcCloseMemHandle(dptr));
+    return MB_OK;
+}
+
+int mb_enable_peer_access(mb_ctx *ctx, int peer_device) {
+    if (!ctx) return MB_E_ARG;
+    if (peer_device == ctx->par.device) return MB_OK;
+    CK(cudaSetDevice(ctx->par.device));
+    int can = 0;
+    CK(cudaDeviceCanAccessPeer(&can, ctx->par.device, peer_device));
+    if (!can) return fail(ctx, MB_E_ARG, "the GPUs cannot access each other's memory (no NVLink / PCIe peer path)");
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return MB_OK; }
+    CK(e);
     return MB_OK;
 }
 

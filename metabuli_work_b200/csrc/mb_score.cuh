@@ -516,7 +516,7 @@ constexpr int SF_P = 16;     // paths per species: the size up to which std::sor
 constexpr int SC_G = 4;                          // matches per (species, frame, position) group
 constexpr int SC_NP = 40;                        // paths per read
 #ifndef MB_SC_NS
-#define MB_SC_NS 16
+#define MB_SC_NS 32
 #endif
 constexpr int SC_NS = MB_SC_NS;                  // species with paths per read
 constexpr int SC_GWORDS = 2 * SC_G * 3;          // DP state `w`: 2 groups x SC_G entries x 3 words (shared memory on the device)

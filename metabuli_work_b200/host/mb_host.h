@@ -79,6 +79,7 @@ struct Options {                   // the classify flag set (src/commons/LocalPa
     int reducedAA = 0;
     int em = 0;
     int device = 0;                // --gpu (new): CUDA device ordinal
+    std::vector<int> devices;      // --gpus N / --gpu-list a,b,...: (new) more than one entry = one DB shard per listed GPU, reads split over them
     size_t batchReads = 1u << 20;  // --batch-reads (new): reads per GPU batch
     std::string taxonomyPath;
     std::string kronaPrelude;      // --krona-prelude (new): the static head of JOBID_krona.html (lib/mmseqs/data/resources/krona_prelude.html)
@@ -139,6 +140,7 @@ public:
     Reporter(const Taxonomy &tax, const std::string &outDir, const std::string &jobId, bool lineage, const std::string &kronaPrelude = "");
     bool openClassifications(std::string &err);
     void writeClassifications(const ReadBatch &batch, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt);
+    void writeClassifications(const std::string *names, uint32_t n, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt);
     void closeClassifications();
     bool writeReport(std::string &err);
     uint64_t totalReads() const { return total_; }
@@ -152,7 +154,9 @@ private:
     uint64_t total_ = 0;
 };
 
-// whole `classify` run: returns process exit code
+// whole `classify` run: returns process exit code (opt.devices with more than one entry: runClassifyMulti)
+int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,
+                     const std::string &jobId, Options opt, std::string &err);
 int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,
                 const std::string &jobId, Options opt, std::string &err);
 

@@ -109,20 +109,25 @@ bool Reporter::openClassifications(std::string &err) {
 static inline int formatScore(char *buf, size_t n, float score) { return snprintf(buf, n, "%g", (double) score); }
 
 void Reporter::writeClassifications(const ReadBatch &batch, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt) {
+    writeClassifications(batch.names.data(), batch.nReads(), res, tcId, tcCnt);
+}
+
+void Reporter::writeClassifications(const std::string *names, uint32_t nReads, const mb_read_result *res, const int32_t *tcId,
+                                    const int32_t *tcCnt) {
     char num[64];
-    for (uint32_t i = 0; i < batch.nReads(); ++i) {
+    for (uint32_t i = 0; i < nReads; ++i) {
         const mb_read_result &r = res[i];
         ++taxCounts_[r.classification];          // Classifier.cpp:201-203
         ++total_;
         formatScore(num, sizeof(num), r.score);
         if (r.is_classified) {
-            fprintf(cls_, "1\t%s\t%d\t%d\t%s\t%s\t", batch.names[i].c_str(), tax_.original(r.classification), r.query_length, num,
+            fprintf(cls_, "1\t%s\t%d\t%d\t%s\t%s\t", names[i].c_str(), tax_.original(r.classification), r.query_length, num,
                     tax_.rank(r.classification));
             if (lineage_) { fputs(tax_.lineage(r.classification).c_str(), cls_); fputc('\t', cls_); }   // Reporter.cpp:60-62
             for (int32_t k = r.taxcnt_begin; k < r.taxcnt_end; ++k) fprintf(cls_, "%d:%d ", tax_.original(tcId[k]), tcCnt[k]);
             fputc('\n', cls_);
         } else {
-            fprintf(cls_, "0\t%s\t%d\t%d\t%s\t-\t", batch.names[i].c_str(), tax_.original(r.classification), r.query_length, num);
+            fprintf(cls_, "0\t%s\t%d\t%d\t%s\t-\t", names[i].c_str(), tax_.original(r.classification), r.query_length, num);
             if (lineage_) fputs("-\t", cls_);
             fputs("-\t\n", cls_);
         }
@@ -304,6 +309,8 @@ static bool looksLikePlainFastq(const std::string &path) {
 
 int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,
                 const std::string &jobId, Options opt, std::string &err) {
+    if (opt.devices.size() > 1) return runClassifyMulti(inputs, dbDir, outDir, jobId, opt, err);
+    if (opt.devices.size() == 1) opt.device = opt.devices[0];
     using clk = std::chrono::steady_clock;
     const auto t0 = clk::now();
     Database db;

@@ -22,7 +22,8 @@ static int usage() {
                  "         --hamming-margin N --taxonomy-path DIR --mask 0|1 --mask-prob F --max-ram N --match-per-kmer N\n"
                  "         --accession-level 0|1 --lineage 0|1 --validate-input 0|1 --validate-db 0|1 --syncmer 0|1\n"
                  "         --smer-len N --kmer-format 1|2 --print-log 0|1 --reduced-aa 0|1 --em 0|1\n"
-                 "         --gpu N (CUDA device) --batch-reads N (reads per GPU batch)\n"
+                 "         --gpu N (CUDA device) --batch-reads N (reads per batch)\n"
+                 "         --gpus N | --gpu-list a,b,... (DB sharded by k-mer range over the listed GPUs, reads split over them)\n"
                  "         --krona-prelude FILE (static head of JOBID_krona.html: the reference's krona_prelude.html)\n";
     return 1;
 }
@@ -61,6 +62,8 @@ int main(int argc, char **argv) {
         else if (a == "--em") opt.em = atoi(v);
         else if (a == "--krona-prelude") opt.kronaPrelude = v;
         else if (a == "--gpu") opt.device = atoi(v);
+        else if (a == "--gpus") { opt.devices.clear(); for (int g = 0; g < atoi(v); ++g) opt.devices.push_back(g); }
+        else if (a == "--gpu-list") { opt.devices.clear(); for (const char *q = v; *q;) { opt.devices.push_back(atoi(q)); while (*q && *q != ',') ++q; if (*q) ++q; } }
         else if (a == "--batch-reads") opt.batchReads = (size_t) strtoull(v, nullptr, 10);
         else { std::cerr << "unknown option " << a << "\n"; return usage(); }
     }

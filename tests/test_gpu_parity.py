@@ -256,6 +256,14 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
         subprocess.check_call([mb.CLI, "classify", "--seq-mode", "3", os.path.join(data, "long.fa"), golden.dbdir(c), out, c])
         for f in ("classifications.tsv", "report.tsv"):
             assert rd(os.path.join(out, c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, f)
+    # several GPUs in one process (host/mb_host_multi.cpp): DB shards per context, reads split over them, k-mers and matches
+    # exchanged through peer stores.  Listing device 0 more than once runs the same code on one GPU.
+    for c, mode, gl, extra in (("plain_paired", 2, "0,0", ["--batch-reads", "150"]), ("sync_paired", 2, "0,0,0", []),
+                               ("legacy_long", 3, "0,0", []), ("euk_paired", 2, "0,0,0,0", ["--batch-reads", "97"])):
+        inp = [r1, r2] if mode == 2 else ["--seq-mode", "3", os.path.join(data, "long.fa")]
+        subprocess.check_call([mb.CLI, "classify"] + inp + [golden.dbdir(c), out, "mg_" + c, "--gpu-list", gl] + extra)
+        for f in ("classifications.tsv", "report.tsv"):
+            assert rd(os.path.join(out, "mg_" + c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, gl, f)
     # long-read mode through the library entry point
     mb.classify_files(os.path.join(data, "long.fa"), None, golden.dbdir("sync_long"), out, "jobl", seq_mode=3)
     assert rd(os.path.join(out, "jobl_classifications.tsv")) == rd(os.path.join(rep, "sync_long_classifications.tsv"))
