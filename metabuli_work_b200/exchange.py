@@ -156,7 +156,7 @@ class ShardedClassifier:
     """One per rank.  `engine` holds shard `rank` of the database; `bounds` are the first k-mer values of shards
     1..world-1 (binding.Classifier.shard_bounds())."""
 
-    def __init__(self, engine, bounds, reads_per_rank, rank=None, world=None, group=None, fused=False, match_cap=None):
+    def __init__(self, engine, bounds, reads_per_rank, rank=None, world=None, group=None, fused=False, match_cap=None, kmer_cap=None):
         self.e = engine
         self.group = group
         self.rank = dist.get_rank(group) if rank is None else rank
@@ -168,6 +168,7 @@ class ShardedClassifier:
         self.fused = bool(fused)
         self.kmer_cap = self.match_cap = 0
         self._match_cap0 = match_cap          # initial match receive capacity (records); default: half the k-mer capacity
+        self._kmer_cap0 = kmer_cap            # initial k-mer receive capacity (records); default: 3 x the bases of the batch
         self.regrows = 0
 
     def _agree(self, value=0):
@@ -191,7 +192,7 @@ class ShardedClassifier:
             # mates are packed back to back (mb_stage_reads checks it), so the base count is the buffer length: no pass over
             # lens (an oracle-backed test engine hands over its own batch object instead of a byte buffer)
             n_bases = len(bases) if hasattr(bases, "__len__") else int(np.asarray(lens, dtype=np.int64).sum())
-            need = self._agree(max(3 * n_bases, 1 << 16))
+            need = self._agree(self._kmer_cap0 if self._kmer_cap0 and not self.kmer_cap else max(3 * n_bases, 1 << 16))
             if need > self.kmer_cap:
                 self._setup(need, max(self.match_cap, self._match_cap0 or need // 2))
 
@@ -228,11 +229,18 @@ class ShardedClassifier:
         e = self.e
         t = [time.perf_counter()]
         lap = lambda: t.append(time.perf_counter())
-        n_local = e.extract_routed(); lap()                 # k-mers land in their owners' receive buffers
-        self._agree(); lap()                                # every producer is done
-        n_owned, over = e.take_kmers()
-        if self._agree(over):
-            raise RuntimeError("k-mer receive buffer overflow: query k-mers pile up in one shard beyond the 1.5x slack")
+        while True:
+            n_local = e.extract_routed(); lap()             # k-mers land in their owners' receive buffers
+            self._agree(); lap()                            # every producer is done
+            n_owned, over = e.take_kmers()
+            need = self._agree(n_owned if over else 0)      # (on overflow the count is the capacity that would have sufficed)
+            if not need:
+                break
+            # query k-mers piled up in one shard beyond the slack (low-complexity or contaminated samples against an
+            # equal-count split): everyone re-allocates with the worst demand and the extraction is redone, as on the match side
+            del t[-2:]
+            self.regrows += 1
+            self._setup(need + need // 4, self.match_cap)
         e.sort_kmers()
         while True:
             n_matches_owner = e.match_routed(); lap()       # matches land in their home ranks' receive buffers

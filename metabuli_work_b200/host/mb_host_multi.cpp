@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstdlib>
 #include <chrono>
 #include <condition_variable>
 #include <cstring>
@@ -50,6 +51,7 @@ struct Shared {
     std::vector<mb_peer_mem> peers;
     size_t kmerCap = 0, matchCap = 0;
     std::atomic<unsigned long long> need{0};
+    std::atomic<int> regrows{0};
     std::mutex errMu;
     std::string err;
     void fail(const std::string &e) { std::lock_guard<std::mutex> lk(errMu); if (err.empty()) err = e; }
@@ -100,16 +102,30 @@ static void runBatch(Worker &w, Shared &sh, Barrier &bar, const ReadBatch &batch
         mb_stage_reads(ctx, batch.bases.data() + b0, (size_t) (b1 - b0), w.offsets.data(), w.lens.data(), w.count) != MB_OK) return die("stage");
     // receive capacity: a rank emits at most two k-mers per base; an owner gets about as many unless the queries pile up in
     // one shard (slack 1.5), as in the torch.distributed driver (exchange.py)
-    atomicMax(sh.need, std::max<unsigned long long>(3ull * (b1 - b0), 1ull << 16));
+    // MB_EXCHANGE_CAP0 (test knob): first receive capacity in records, so that small inputs reach the regrow paths below
+    static const unsigned long long cap0 = getenv("MB_EXCHANGE_CAP0") ? strtoull(getenv("MB_EXCHANGE_CAP0"), nullptr, 10) : 0;
+    atomicMax(sh.need, cap0 && !sh.kmerCap ? cap0 : std::max<unsigned long long>(3ull * (b1 - b0), 1ull << 16));
     if (!bar.wait()) return;
     const size_t needK = (size_t) sh.need.load();
     if (!bar.wait()) return;                               // everybody has read `need`
     if (w.rank == 0) sh.need.store(0);
     if (needK > sh.kmerCap && !setupPeers(w, sh, bar, needK, std::max(sh.matchCap, needK / 2))) return;
     size_t got = 0;
-    if (mb_extract_kmers_routed(ctx, &got) != MB_OK) return die("extract");
-    if (!bar.wait()) return;                               // every producer is done
-    if (mb_take_routed_kmers(ctx, &got) != MB_OK) return die("k-mer exchange");
+    while (true) {
+        if (mb_extract_kmers_routed(ctx, &got) != MB_OK) return die("extract");
+        if (!bar.wait()) return;                           // every producer is done
+        const int rc = mb_take_routed_kmers(ctx, &got);
+        if (rc != MB_OK && rc != MB_E_CAPACITY) return die("k-mer exchange");
+        if (rc == MB_E_CAPACITY) atomicMax(sh.need, got);
+        if (!bar.wait()) return;
+        const size_t needMore = (size_t) sh.need.load();
+        if (!bar.wait()) return;
+        if (w.rank == 0) sh.need.store(0);
+        if (!needMore) break;
+        // the query k-mers pile up in one shard beyond the slack: everybody re-allocates with the worst demand, extraction is redone
+        if (w.rank == 0) ++sh.regrows;
+        if (!setupPeers(w, sh, bar, needMore + needMore / 4, sh.matchCap)) return;
+    }
     w.nKmers = got;
     if (mb_sort_kmers(ctx) != MB_OK) return die("sort");
     while (true) {
@@ -127,6 +143,7 @@ static void runBatch(Worker &w, Shared &sh, Barrier &bar, const ReadBatch &batch
         if (!needM) break;
         // some GPU received more matches than its buffer holds: everybody re-allocates and the join is redone (the sorted
         // k-mers are still resident)
+        if (w.rank == 0) ++sh.regrows;
         if (!setupPeers(w, sh, bar, sh.kmerCap, needM + needM / 4)) return;
     }
     size_t used = 0;
@@ -224,6 +241,7 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
     }
     rep.closeClassifications();
     if (!rep.writeReport(err)) return 1;
+    if (sh.regrows.load()) std::cout << "Exchange receive buffers regrown " << sh.regrows.load() << " time(s)" << std::endl;
     std::cout << "Number of query k-mers: " << totalKmers << "\nThe number of matches: " << totalMatches << "\nNumber of sequences: "
               << rep.totalReads() << "\nTime for processing: " << std::chrono::duration<double>(clk::now() - t0).count() << " s" << std::endl;
     return 0;

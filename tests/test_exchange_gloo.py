@@ -133,7 +133,7 @@ def _worker(rank, world, port, dbdir, s1, s2, seq_mode, bounds, per_rank, outdir
         a, b = rank * per_rank, min(len(s1), (rank + 1) * per_rank)
         batch = orc.Batch(s1[a:b], None if s2 is None else s2[a:b])
         eng = OracleEngine(dbdir, seq_mode)
-        sc = ShardedClassifier(eng, bounds, per_rank, fused=fused, match_cap=16 if fused else None)
+        sc = ShardedClassifier(eng, bounds, per_rank, fused=fused, match_cap=16 if fused else None, kmer_cap=64 if fused else None)
         sc.stage(batch, None, batch.len)
         used = sc.classify_staged()
         res, ids, cnt = sc.fetch(used)
@@ -187,4 +187,4 @@ def test_sharded_equals_single(golden, tmp_path, case, world, fused):
     assert st[:, 2].sum() == st[:, 3].sum() == len(m)          # every match came home
     assert (st[:, 1] > 0).all()                                # the shards really split the work
     if fused:
-        assert (st[:, 4] >= 1).all()                           # the 16-record match buffer overflowed and was regrown
+        assert (st[:, 4] >= 2).all()                           # the 64-record k-mer and the 16-record match buffers both overflowed and were regrown

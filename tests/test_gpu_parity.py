@@ -264,6 +264,12 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
         subprocess.check_call([mb.CLI, "classify"] + inp + [golden.dbdir(c), out, "mg_" + c, "--gpu-list", gl] + extra)
         for f in ("classifications.tsv", "report.tsv"):
             assert rd(os.path.join(out, "mg_" + c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, gl, f)
+    # receive buffers that start far too small: both exchanges overflow, everybody re-allocates and the step is redone
+    log = subprocess.run([mb.CLI, "classify", r1, r2, golden.dbdir("sync_paired"), out, "mg_small", "--gpu-list", "0,0,0"],
+                         env=dict(os.environ, MB_EXCHANGE_CAP0="64"), check=True, capture_output=True, text=True)
+    assert "regrown" in log.stdout + log.stderr
+    for f in ("classifications.tsv", "report.tsv"):
+        assert rd(os.path.join(out, "mg_small_" + f)) == rd(os.path.join(rep, "sync_paired_" + f)), f
     # long-read mode through the library entry point
     mb.classify_files(os.path.join(data, "long.fa"), None, golden.dbdir("sync_long"), out, "jobl", seq_mode=3)
     assert rd(os.path.join(out, "jobl_classifications.tsv")) == rd(os.path.join(rep, "sync_long_classifications.tsv"))
