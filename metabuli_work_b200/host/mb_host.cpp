@@ -14,9 +14,39 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <memory>
 #include <sstream>
+#include <thread>
 
 namespace mbh {
+
+// pread of one byte range by several threads (page-cache copies and NVMe queues both want more than one reader)
+bool preadParallel(int fd, void *dst, size_t bytes, size_t off, int threads) {
+    const size_t minPiece = 8u << 20;
+    const int n = (int) std::max<size_t>(1, std::min<size_t>((size_t) std::max(1, threads), bytes / minPiece));
+    std::vector<char> ok((size_t) n, 1);
+    auto piece = [&](int t) {
+        size_t b = bytes * (size_t) t / (size_t) n, e = bytes * (size_t) (t + 1) / (size_t) n;
+        char *p = static_cast<char *>(dst) + b;
+        while (b < e) {
+            const ssize_t got = ::pread(fd, p, e - b, (off_t) (off + b));
+            if (got <= 0) { ok[(size_t) t] = 0; return; }
+            p += got; b += (size_t) got;
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < n; ++t) th.emplace_back(piece, t);
+    piece(0);
+    for (auto &x : th) x.join();
+    for (char c : ok) if (!c) return false;
+    return true;
+}
+
+int ioThreads(const Options &opt) {
+    if (opt.threads > 1) return opt.threads;
+    const unsigned hw = std::thread::hardware_concurrency();
+    return (int) std::min<unsigned>(std::max<unsigned>(hw, 1), 16);
+}
 
 // ------------------------------------------------------------------------------------------------------
 // taxonomyDB
@@ -217,8 +247,15 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     if (opt.em) { err = "--em is outside this path"; return false; }
     if (opt.maskMode) { err = "--mask 1 (tantan masking) is not implemented on this path yet"; return false; }
 
+    using clk = std::chrono::steady_clock;
+    const bool timing = getenv("MB_TIMING") != nullptr;        // where the load time goes, on stderr
+    const auto tStart = clk::now();
+    auto lap = [&](const char *what) {
+        if (timing) fprintf(stderr, "[db open] %-22s at %.3f s\n", what, std::chrono::duration<double>(clk::now() - tStart).count());
+    };
     const std::string taxPath = opt.taxonomyPath.empty() ? dir + "/taxonomyDB" : opt.taxonomyPath + "/taxonomyDB";
     if (!tax_.load(taxPath, err)) return false;
+    lap("taxonomy file parsed");
 
     // Only the shard's byte ranges of diffIdx / info are read (a rank of an 8-GPU run touches an eighth of the files); the
     // split table is small and read whole.
@@ -272,9 +309,7 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
         }
     }
     size_t wBegin = 0, wEnd = nWords, kBegin = 0, kEnd = nKmers;
-    std::vector<uint16_t> shardWords;
-    std::vector<uint32_t> shardInfo;
-    size_t prefix = 0;
+    std::vector<uint16_t> head;        // the shard's first k-mer re-encoded (shards > 0)
     if (nShards > 1) {
         if (shard > 0) { wBegin = cutPoints[shard - 1].wordAfter; kBegin = cutPoints[shard - 1].kIndex; }
         if (shard + 1 < nShards) { wEnd = cutPoints[shard].wordStart; kEnd = cutPoints[shard].kIndex; }
@@ -287,14 +322,22 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
             tmp[4] = (uint16_t) (0x8000u | (v & 0x7FFFu));
             v >>= 15;
             while (v) { tmp[idx--] = (uint16_t) (v & 0x7FFFu); v >>= 15; }
-            for (int k = idx + 1; k <= 4; ++k) shardWords.push_back(tmp[k]);
+            for (int k = idx + 1; k <= 4; ++k) head.push_back(tmp[k]);
         }
-        prefix = shardWords.size();
     }
-    shardWords.resize(prefix + (wEnd - wBegin));
-    shardInfo.resize(kEnd - kBegin);
-    if (!preadAll(fdW, shardWords.data() + prefix, (wEnd - wBegin) * 2, wBegin * 2)) { err = "short read on " + dir + "/diffIdx"; return false; }
-    if (!preadAll(fdI, shardInfo.data(), (kEnd - kBegin) * 4, kBegin * 4)) { err = "short read on " + dir + "/info"; return false; }
+    // The two big reads go on while this thread creates the CUDA context and prepares the taxonomy: buffers are not
+    // value-initialised (a 2 GB memset would cost as much as the read) and each file is read by several threads.
+    const size_t prefix = head.size(), nShardWords = prefix + (wEnd - wBegin), nShardKmers = kEnd - kBegin;
+    std::unique_ptr<uint16_t[]> shardWords(new uint16_t[nShardWords + 1]);
+    std::unique_ptr<uint32_t[]> shardInfo(new uint32_t[nShardKmers + 1]);
+    std::copy(head.begin(), head.end(), shardWords.get());
+    const int ioT = ioThreads(opt);
+    bool readOk = true;
+    std::thread fileReader([&] {
+        readOk = preadParallel(fdW, shardWords.get() + prefix, (wEnd - wBegin) * 2, wBegin * 2, ioT) &&
+                 preadParallel(fdI, shardInfo.get(), nShardKmers * 4, kBegin * 4, ioT);
+    });
+    struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{fileReader};
 
     mb_default_params(&par_);
     par_.device = opt.device;
@@ -312,6 +355,7 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     par_.last_shard = (shard + 1 == nShards) ? 1 : 0;
     ctx_ = mb_create(&par_);
     if (!ctx_) { err = mb_global_error(); return false; }
+    lap("GPU context created");
 
     // taxonomy tables; taxId2speciesId as KmerMatcher::loadTaxIdList builds it (KmerMatcher.cpp:56-120)
     std::vector<int32_t> parent, speciesRankOf, speciesOf((size_t) tax_.maxTaxId() + 1, 0);
@@ -341,10 +385,15 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
         err = mb_last_error(ctx_);
         return false;
     }
-    const int rc = mb_load_db(ctx_, shardWords.data(), shardWords.size(), shardInfo.data(), shardInfo.size());
+    lap("taxonomy resident");
+    fileReader.join();
+    lap("diffIdx / info read");
+    if (!readOk) { err = "short read on diffIdx / info in " + dir; return false; }
+    const int rc = mb_load_db(ctx_, shardWords.get(), nShardWords, shardInfo.get(), nShardKmers);
     if (rc != MB_OK) { err = mb_last_error(ctx_); return false; }
-    nKmers_ = kEnd - kBegin;
-    nWords_ = shardWords.size();
+    lap("DB resident, units cut");
+    nKmers_ = nShardKmers;
+    nWords_ = nShardWords;
     return true;
 }
 

@@ -85,6 +85,9 @@ struct Options {                   // the classify flag set (src/commons/LocalPa
     std::string kronaPrelude;      // --krona-prelude (new): the static head of JOBID_krona.html (lib/mmseqs/data/resources/krona_prelude.html)
 };
 
+bool preadParallel(int fd, void *dst, size_t bytes, size_t off, int threads);
+int ioThreads(const Options &opt);     // --threads when given, else the host's cores (at most 16): file reads and output formatting
+
 class Database {
 public:
     ~Database();
@@ -135,12 +138,21 @@ private:
 };
 
 // ---- output (Reporter, src/commons/Reporter.cpp:38-83,175-253) ----------------------------------------
+struct NameView {                  // read names either as strings or as spans of a FASTQ text (mb_fetch_fastq_names)
+    const std::string *names;
+    const char *text;
+    const uint64_t *off;
+    const uint32_t *len;
+};
+
 class Reporter {
 public:
     Reporter(const Taxonomy &tax, const std::string &outDir, const std::string &jobId, bool lineage, const std::string &kronaPrelude = "");
     bool openClassifications(std::string &err);
     void writeClassifications(const ReadBatch &batch, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt);
     void writeClassifications(const std::string *names, uint32_t n, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt);
+    void writeClassifications(const NameView &names, uint32_t n, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt);
+    void setThreads(int t) { threads_ = t; }      // lines are formatted by this many threads (the file is written by the caller's)
     void closeClassifications();
     bool writeReport(std::string &err);
     uint64_t totalReads() const { return total_; }
@@ -152,6 +164,10 @@ private:
     FILE *cls_ = nullptr;
     std::unordered_map<int32_t, unsigned> taxCounts_;
     uint64_t total_ = 0;
+    int threads_ = 1;
+    std::vector<std::string> parts_;
+    void formatSlice(const NameView &nv, uint32_t begin, uint32_t end, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt,
+                     std::string &out) const;
 };
 
 // whole `classify` run: returns process exit code (opt.devices with more than one entry: runClassifyMulti)

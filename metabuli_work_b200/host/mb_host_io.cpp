@@ -3,12 +3,21 @@
 
 #include <zlib.h>
 
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <iostream>
+#include <mutex>
 #include <sstream>
+#include <thread>
 
 namespace mbh {
 
@@ -108,30 +117,78 @@ bool Reporter::openClassifications(std::string &err) {
 // std::ostream << float with default flags prints like printf("%g") (precision 6)
 static inline int formatScore(char *buf, size_t n, float score) { return snprintf(buf, n, "%g", (double) score); }
 
+static inline void appendInt(std::string &s, long long v) {     // what "%d" prints
+    char b[24];
+    int i = 24;
+    const bool neg = v < 0;
+    unsigned long long u = neg ? 0ull - (unsigned long long) v : (unsigned long long) v;
+    do { b[--i] = (char) ('0' + u % 10); u /= 10; } while (u);
+    if (neg) b[--i] = '-';
+    s.append(b + i, (size_t) (24 - i));
+}
+
 void Reporter::writeClassifications(const ReadBatch &batch, const mb_read_result *res, const int32_t *tcId, const int32_t *tcCnt) {
     writeClassifications(batch.names.data(), batch.nReads(), res, tcId, tcCnt);
 }
 
 void Reporter::writeClassifications(const std::string *names, uint32_t nReads, const mb_read_result *res, const int32_t *tcId,
                                     const int32_t *tcCnt) {
+    writeClassifications(NameView{names, nullptr, nullptr, nullptr}, nReads, res, tcId, tcCnt);
+}
+
+// One line per read (Reporter::writeReadClassification, Reporter.cpp:38-83).  The lines of a slice of reads are put together
+// in memory, slices by several threads; the file and the per-taxon counters are touched by the calling thread only.
+void Reporter::formatSlice(const NameView &nv, uint32_t begin, uint32_t end, const mb_read_result *res, const int32_t *tcId,
+                           const int32_t *tcCnt, std::string &out) const {
     char num[64];
-    for (uint32_t i = 0; i < nReads; ++i) {
+    out.clear();
+    out.reserve((size_t) (end - begin) * 96);
+    for (uint32_t i = begin; i < end; ++i) {
         const mb_read_result &r = res[i];
-        ++taxCounts_[r.classification];          // Classifier.cpp:201-203
-        ++total_;
-        formatScore(num, sizeof(num), r.score);
+        const int nNum = formatScore(num, sizeof(num), r.score);
+        out.append(r.is_classified ? "1\t" : "0\t", 2);
+        if (nv.names) out.append(nv.names[i]);
+        else out.append(nv.text + nv.off[i], nv.len[i]);
+        out.push_back('\t');
+        appendInt(out, tax_.original(r.classification));
+        out.push_back('\t');
+        appendInt(out, r.query_length);
+        out.push_back('\t');
+        out.append(num, (size_t) nNum);
+        out.push_back('\t');
         if (r.is_classified) {
-            fprintf(cls_, "1\t%s\t%d\t%d\t%s\t%s\t", names[i].c_str(), tax_.original(r.classification), r.query_length, num,
-                    tax_.rank(r.classification));
-            if (lineage_) { fputs(tax_.lineage(r.classification).c_str(), cls_); fputc('\t', cls_); }   // Reporter.cpp:60-62
-            for (int32_t k = r.taxcnt_begin; k < r.taxcnt_end; ++k) fprintf(cls_, "%d:%d ", tax_.original(tcId[k]), tcCnt[k]);
-            fputc('\n', cls_);
+            out.append(tax_.rank(r.classification));
+            out.push_back('\t');
+            if (lineage_) { out.append(tax_.lineage(r.classification)); out.push_back('\t'); }   // Reporter.cpp:60-62
+            for (int32_t k = r.taxcnt_begin; k < r.taxcnt_end; ++k) {
+                appendInt(out, tax_.original(tcId[k]));
+                out.push_back(':');
+                appendInt(out, tcCnt[k]);
+                out.push_back(' ');
+            }
+            out.push_back('\n');
         } else {
-            fprintf(cls_, "0\t%s\t%d\t%d\t%s\t-\t", names[i].c_str(), tax_.original(r.classification), r.query_length, num);
-            if (lineage_) fputs("-\t", cls_);
-            fputs("-\t\n", cls_);
+            out.append(lineage_ ? "-\t-\t-\t\n" : "-\t-\t\n");
         }
     }
+}
+
+void Reporter::writeClassifications(const NameView &nv, uint32_t nReads, const mb_read_result *res, const int32_t *tcId,
+                                    const int32_t *tcCnt) {
+    const uint32_t perThread = 1u << 14;
+    const int T = (int) std::max<uint32_t>(1, std::min<uint32_t>((uint32_t) std::max(1, threads_), (nReads + perThread - 1) / perThread));
+    if (parts_.size() < (size_t) T) parts_.resize((size_t) T);
+    auto slice = [&](int t) {
+        const uint32_t b = (uint32_t) ((uint64_t) nReads * (uint64_t) t / (uint64_t) T), e = (uint32_t) ((uint64_t) nReads * (uint64_t) (t + 1) / (uint64_t) T);
+        formatSlice(nv, b, e, res, tcId, tcCnt, parts_[(size_t) t]);
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; ++t) th.emplace_back(slice, t);
+    slice(0);
+    for (uint32_t i = 0; i < nReads; ++i) ++taxCounts_[res[i].classification];          // Classifier.cpp:201-203
+    total_ += nReads;
+    for (auto &x : th) x.join();
+    for (int t = 0; t < T; ++t) fwrite(parts_[(size_t) t].data(), 1, parts_[(size_t) t].size(), cls_);
 }
 
 void Reporter::closeClassifications() { if (cls_) { fclose(cls_); cls_ = nullptr; } }
@@ -273,38 +330,83 @@ static bool loadBatch(FastxReader &r1, FastxReader *r2, size_t maxReads, size_t 
     return !b.names.empty();
 }
 
-// Raw text of one plain FASTQ file, read in chunks; the tail that mb_stage_fastq did not consume (an incomplete record,
-// or records beyond the batch limit) is carried over to the next chunk.
-struct RawText {
-    FILE *fp = nullptr;
-    std::vector<char> buf;
-    size_t fill = 0;
-    bool eof = false;
-    ~RawText() { if (fp) fclose(fp); }
-    bool open(const std::string &path) { fp = fopen(path.c_str(), "rb"); return fp != nullptr; }
-    void refill(size_t chunk) {
-        if (buf.size() < chunk) buf.resize(chunk);
-        while (!eof && fill < chunk) {
-            const size_t n = fread(buf.data() + fill, 1, chunk - fill, fp);
-            if (n == 0) eof = true;
-            fill += n;
-        }
+// ---- the three stages of the batch loop run on their own threads: a reader fills text / read buffers, the calling thread
+// drives the GPU, a writer formats and writes the classification lines.  Buffers circulate through bounded queues. ----------
+template <class T> class Channel {
+public:
+    void push(T v) { { std::lock_guard<std::mutex> lk(mu_); q_.push_back(std::move(v)); } cv_.notify_all(); }
+    bool pop(T &out) {                       // false: closed and drained
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return !q_.empty() || closed_; });
+        if (q_.empty()) return false;
+        out = std::move(q_.front());
+        q_.pop_front();
+        return true;
     }
-    void consume(size_t n) { memmove(buf.data(), buf.data() + n, fill - n); fill -= n; }
+    void close() { { std::lock_guard<std::mutex> lk(mu_); closed_ = true; } cv_.notify_all(); }
+    void closeAndDrop() { { std::lock_guard<std::mutex> lk(mu_); closed_ = true; q_.clear(); } cv_.notify_all(); }
+private:
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<T> q_;
+    bool closed_ = false;
 };
 
-// plain (not gzip) four-line FASTQ?  Decided on the first bytes: '@' starts the file and the third line starts with '+'.
-static bool looksLikePlainFastq(const std::string &path) {
+// Text of one plain FASTQ file for one batch.  The reader thread preads a chunk behind `reserve` free bytes; the tail the
+// previous batch did not consume (an incomplete record, or records beyond its mate's) is copied in front of it.
+struct TextBuf {
+    char *pin = nullptr;               // page-locked (mb_alloc_host) when the driver gives it, else malloc
+    size_t cap = 0;
+    bool pinned = false;
+    std::vector<char> spill;           // a chunk or tail that outgrew the fixed buffer (a record longer than a chunk)
+    char *base = nullptr;
+    size_t start = 0, fill = 0;
+    bool eof = false;
+    char *data() const { return base + start; }
+    void prepend(const char *src, size_t n) {
+        if (n <= start) { memcpy(base + start - n, src, n); start -= n; fill += n; return; }
+        std::vector<char> nb(n + fill + 64);
+        memcpy(nb.data(), src, n);
+        memcpy(nb.data() + n, data(), fill);
+        spill.swap(nb);
+        base = spill.data();
+        start = 0;
+        fill += n;
+    }
+};
+
+struct BatchSlot {
+    TextBuf f[2];                      // device-parse path
+    ReadBatch batch;                   // host-reader path
+    uint32_t nReads = 0;
+    std::vector<mb_read_result> res;
+    std::vector<int32_t> tcId, tcCnt;
+    std::vector<uint64_t> nameOff;
+    std::vector<uint32_t> nameLen;
+};
+
+// plain (not gzip) four-line FASTQ in a regular file?  Decided on the first bytes: '@' starts the file and the third line
+// starts with '+'.  bytesPerRecord: average over the records of the first 64 KB.
+static bool looksLikePlainFastq(const std::string &path, size_t &bytesPerRecord, size_t &fileSize) {
+    struct stat st;
+    if (stat(path.c_str(), &st) != 0 || !S_ISREG(st.st_mode)) return false;
+    fileSize = (size_t) st.st_size;
     FILE *fp = fopen(path.c_str(), "rb");
     if (!fp) return false;
-    char head[1 << 16];
+    static char head[1 << 16];
     const size_t n = fread(head, 1, sizeof(head), fp);
     fclose(fp);
     if (n < 4 || head[0] != '@') return false;
-    size_t line = 0;
-    for (size_t i = 0; i + 1 < n; ++i)
-        if (head[i] == '\n' && ++line == 2) return head[i + 1] == '+';
-    return false;
+    size_t line = 0, lastRecordEnd = 0;
+    bool plus = false;
+    for (size_t i = 0; i < n; ++i)
+        if (head[i] == '\n') {
+            ++line;
+            if (line == 2) plus = i + 1 < n && head[i + 1] == '+';
+            if (line % 4 == 0) lastRecordEnd = i + 1;
+        }
+    bytesPerRecord = line >= 4 ? (lastRecordEnd + line / 4 - 1) / (line / 4) : n;
+    return plus;
 }
 
 int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,
@@ -313,8 +415,93 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     if (opt.devices.size() == 1) opt.device = opt.devices[0];
     using clk = std::chrono::steady_clock;
     const auto t0 = clk::now();
+    const bool paired = opt.seqMode == 2;
+    const int nFiles = paired ? 2 : 1;
+    const int ioT = ioThreads(opt);
+    constexpr int kSlots = 3;
+    BatchSlot slots[kSlots];
+    Channel<int> freeSlots, filled, toWrite;
+    for (int i = 0; i < kSlots; ++i) freeSlots.push(i);
+
+    // Plain FASTQ goes to the GPU as raw text (mb_stage_fastq: lines, records and packing are found on the device; the host
+    // only cuts the read names out at the spans it gets back).  FASTA, multi-line or gzip input takes the host reader.
+    size_t bpr[2] = {0, 0}, fileSize[2] = {0, 0};
+    const bool deviceParse = !getenv("MB_HOST_PARSE") && looksLikePlainFastq(inputs[0], bpr[0], fileSize[0]) &&
+                             (!paired || looksLikePlainFastq(inputs[1], bpr[1], fileSize[1]));
+    // A chunk holds about --batch-reads records; the batch is bounded by the chunk's bytes, not by a record count, so that
+    // what a batch leaves over is an incomplete record and not a pile of whole ones.
+    std::atomic<size_t> chunkWant[2];
+    size_t reserve[2] = {0, 0};
+    for (int f = 0; f < nFiles; ++f) {
+        // MB_CHUNK_MB (tuning knob) caps the chunk.  Page-locking costs time in proportion to the buffer size and, while the
+        // database is being copied to the device, slows that copy down: measured on B200 with 8M pairs, 128 MB chunks (about
+        // 400k short read pairs per batch) finish in 2.6 s, 330 MB chunks in 3.2-4.5 s.
+        static const size_t chunkCap = (getenv("MB_CHUNK_MB") ? (size_t) atoll(getenv("MB_CHUNK_MB")) : (size_t) 128) << 20;
+        chunkWant[f] = std::min<size_t>(std::max<size_t>(opt.batchReads * bpr[f] + 4096, 64u << 10), chunkCap);
+        reserve[f] = std::max<size_t>(64u << 10, chunkWant[f] / 8);
+    }
+    std::atomic<bool> readerFailed{false};
+    std::string readerErr;
+    const bool timing = getenv("MB_TIMING") != nullptr;      // busy seconds of the three stages, on stderr
+    double readBusy = 0, writeBusy = 0, gpuBusy = 0, pinBusy = 0;
+    auto secondsSince = [](clk::time_point t) { return std::chrono::duration<double>(clk::now() - t).count(); };
+    std::thread reader;
+    if (deviceParse) {
+        // starts before the database is resident: page-locking the buffers and reading the first chunk overlap the DB load
+        reader = std::thread([&] {
+            int fd[2] = {-1, -1};
+            size_t pos[2] = {0, 0};
+            for (int f = 0; f < nFiles; ++f) {
+                fd[f] = ::open(inputs[(size_t) f].c_str(), O_RDONLY);
+                if (fd[f] < 0) { readerErr = "cannot open " + inputs[(size_t) f]; readerFailed = true; }
+            }
+            int si;
+            while (!readerFailed && freeSlots.pop(si)) {
+                const auto tr = clk::now();
+                bool allEof = true;
+                for (int f = 0; f < nFiles; ++f) {
+                    TextBuf &tb = slots[si].f[f];
+                    const size_t want = std::min<size_t>(chunkWant[f], fileSize[f] - pos[f]);
+                    if (!tb.pin) {       // first use of this slot (a file that fits one chunk never touches the other slots)
+                        tb.cap = reserve[f] + std::min<size_t>(chunkWant[f], fileSize[f]) + 64;
+                        const auto tp = clk::now();
+                        tb.pin = static_cast<char *>(mb_alloc_host(tb.cap));
+                        pinBusy += secondsSince(tp);
+                        tb.pinned = tb.pin != nullptr;
+                        if (!tb.pin) tb.pin = static_cast<char *>(malloc(tb.cap));
+                        if (!tb.pin) { readerErr = "out of host memory for the read buffers"; readerFailed = true; break; }
+                    }
+                    if (reserve[f] + want + 64 <= tb.cap) tb.base = tb.pin;
+                    else { tb.spill.resize(reserve[f] + want + 64); tb.base = tb.spill.data(); }
+                    tb.start = reserve[f];
+                    tb.fill = want;
+                    if (want && !preadParallel(fd[f], tb.data(), want, pos[f], ioT)) { readerErr = "short read on " + inputs[(size_t) f]; readerFailed = true; }
+                    pos[f] += want;
+                    tb.eof = pos[f] >= fileSize[f];
+                    allEof = allEof && tb.eof;
+                }
+                readBusy += secondsSince(tr);
+                filled.push(si);
+                if (allEof) break;
+            }
+            filled.close();
+            for (int f = 0; f < nFiles; ++f) if (fd[f] >= 0) ::close(fd[f]);
+        });
+    }
+    auto stopReader = [&] {
+        freeSlots.closeAndDrop();
+        if (reader.joinable()) reader.join();
+    };
+    auto freeText = [&] {
+        for (BatchSlot &s : slots)
+            for (TextBuf &tb : s.f) {
+                if (tb.pin) { if (tb.pinned) mb_free_host(tb.pin); else free(tb.pin); }
+                tb.pin = nullptr;
+            }
+    };
+
     Database db;
-    if (!db.open(dbDir, opt, 0, 1, err)) return 1;
+    if (!db.open(dbDir, opt, 0, 1, err)) { stopReader(); freeText(); return 1; }
     const auto t1 = clk::now();
     std::cout << "DB resident on GPU " << opt.device << ": " << db.numKmers() << " k-mers, " << db.numWords() * 2 + db.numKmers() * 4
               << " bytes (" << std::chrono::duration<double>(t1 - t0).count() << " s)" << std::endl;
@@ -324,120 +511,159 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     // (85 bytes with long reads, an eighth of 93 bytes with short reads).  --max-ram (GB) caps the budget like it caps the
     // reference's host memory.
     size_t freeB = 0, totalB = 0;
-    if (mb_mem_info(db.ctx(), &freeB, &totalB) != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
+    if (mb_mem_info(db.ctx(), &freeB, &totalB) != MB_OK) { err = mb_last_error(db.ctx()); stopReader(); freeText(); return 1; }
     const size_t budget = std::min<size_t>((size_t) (0.9 * (double) freeB), (size_t) std::max(1, opt.ramUsage) << 30);
     const size_t slotBytes = 32 + (size_t) std::max(1, opt.matchPerKmer) * (48 + (opt.seqMode == 3 ? 85 : 12));
     const size_t maxSlots = std::max<size_t>(budget / slotBytes, 1u << 20);
     const size_t maxBatchBases = maxSlots / 2;          // about two k-mer slots per base (six frames, one per codon)
     std::cout << "Batch budget: " << (budget >> 20) << " MiB of HBM (" << (freeB >> 20) << " MiB free), at most " << maxBatchBases
               << " bases per batch" << std::endl;
+    // FASTQ text is a little over twice its bases: later chunks respect the budget (the first ones are already on their way)
+    const size_t chunkMax = std::max<size_t>(maxBatchBases * 2 / (size_t) nFiles + (1u << 20), 4u << 20);
+    for (int f = 0; f < nFiles; ++f) if (chunkWant[f] > chunkMax) chunkWant[f] = chunkMax;
+
     Reporter rep(db.taxonomy(), outDir, jobId, opt.printLineage != 0, opt.kronaPrelude);
-    if (!rep.openClassifications(err)) return 1;
-    const bool paired = opt.seqMode == 2;
-    ReadBatch batch;
-    std::vector<mb_read_result> res;
-    std::vector<int32_t> tcId, tcCnt;
+    rep.setThreads(ioT);
+    if (!rep.openClassifications(err)) { stopReader(); freeText(); return 1; }
     uint64_t totalKmers = 0, totalMatches = 0;
     double gpuMs = 0;
-    // Plain FASTQ goes to the GPU as raw text (mb_stage_fastq: lines, records and packing are found on the device; the host
-    // only cuts the read names out at the spans it gets back).  FASTA, multi-line or gzip input takes the host reader.
-    const bool deviceParse = !getenv("MB_HOST_PARSE") && looksLikePlainFastq(inputs[0]) && (!paired || looksLikePlainFastq(inputs[1]));
-    bool hostFallback = false;           // the first chunk was not four-line FASTQ after all: nothing was written yet
-    if (deviceParse) {
-        RawText f1, f2;
-        uint64_t batchesDone = 0;
-        if (!f1.open(inputs[0])) { err = "cannot open " + inputs[0]; return 1; }
-        if (paired && !f2.open(inputs[1])) { err = "cannot open " + inputs[1]; return 1; }
-        // a chunk holds at least one batch of short reads (~330 text bytes per 150-base record) and never less than 64 MB
-        // ... and holds no more bases than the batch budget allows (FASTQ text is a little over twice its bases)
-        const size_t chunk = std::min<size_t>(std::max<size_t>(64u << 20, std::min<size_t>(opt.batchReads * 400, 2ull << 30)),
-                                              std::max<size_t>(maxBatchBases * 2 + (1u << 20), 4u << 20));
-        std::vector<uint64_t> nameOff;
-        std::vector<uint32_t> nameLen;
-        while (true) {
-            f1.refill(chunk);
-            if (paired) f2.refill(chunk);
-            if (f1.fill == 0) break;
-            const bool last = f1.eof && (!paired || f2.eof);
-            mb_fastq_index idx;
-            int rc = mb_stage_fastq(db.ctx(), f1.buf.data(), f1.fill, paired ? f2.buf.data() : nullptr, paired ? f2.fill : 0,
-                                    (uint32_t) std::min<size_t>(opt.batchReads, 0xFFFFFFFFu), last ? 1 : 0, &idx);
-            if (rc == MB_E_DATA && batchesDone == 0) {
-                std::cout << "Input is not plain four-line FASTQ (" << mb_last_error(db.ctx()) << "): using the host reader" << std::endl;
-                hostFallback = true;
-                break;
-            }
-            if (rc != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
-            ++batchesDone;
-            if (idx.n_reads == 0) {
-                if (last) break;
-                err = "FASTQ record longer than the read chunk (use a smaller --batch-reads only with short reads)";
-                return 1;
-            }
-            size_t used = 0;
-            rc = mb_classify_staged(db.ctx(), &used);
-            res.resize(idx.n_reads);
-            if (rc == MB_OK) {
-                tcId.resize(used + 1);
-                tcCnt.resize(used + 1);
-                rc = mb_fetch_results(db.ctx(), res.data(), tcId.data(), tcCnt.data(), used + 1);
-            }
-            nameOff.resize(idx.n_reads);
-            nameLen.resize(idx.n_reads);
-            if (rc == MB_OK) rc = mb_fetch_fastq_names(db.ctx(), nameOff.data(), nameLen.data());
-            if (rc != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
-            batch.clear();
-            batch.names.resize(idx.n_reads);
-            for (uint32_t i = 0; i < idx.n_reads; ++i) batch.names[i].assign(f1.buf.data() + nameOff[i], nameLen[i]);
-            mb_phase_times t;
-            mb_get_timings(db.ctx(), &t);
-            totalKmers += t.n_kmers;
-            totalMatches += t.n_matches;
-            gpuMs += t.total_ms;
-            std::cout << "Batch of " << idx.n_reads << " reads (FASTQ parsed on the GPU): " << t.n_kmers << " query k-mers, " << t.n_matches
-                      << " matches; GPU ms: parse+copy " << t.h2d_ms << " extract " << t.extract_ms << " sort " << t.sort_kmers_ms << " match "
-                      << t.match_ms << " sort " << t.sort_matches_ms << " score " << t.score_ms << std::endl;
-            rep.writeClassifications(batch, res.data(), tcId.data(), tcCnt.data());
-            f1.consume(idx.consumed1);
-            if (paired) f2.consume(idx.consumed2);
+    // the writer: formats a finished batch and hands its buffers back to the reader
+    bool namesFromText = deviceParse;
+    Channel<int> freeHost;               // host-reader path: its own queue of free slots
+    Channel<int> *freeCh = &freeSlots;
+    std::thread writer([&] {
+        int si;
+        while (toWrite.pop(si)) {
+            BatchSlot &s = slots[si];
+            const auto tw = clk::now();
+            if (namesFromText) rep.writeClassifications(NameView{nullptr, s.f[0].data(), s.nameOff.data(), s.nameLen.data()}, s.nReads,
+                                                        s.res.data(), s.tcId.data(), s.tcCnt.data());
+            else rep.writeClassifications(s.batch, s.res.data(), s.tcId.data(), s.tcCnt.data());
+            writeBusy += secondsSince(tw);
+            freeCh->push(si);
         }
-        if (!hostFallback) {
-            rep.closeClassifications();
-            if (!rep.writeReport(err)) return 1;
-            const auto t2 = clk::now();
-            std::cout << "Number of query k-mers: " << totalKmers << "\nThe number of matches: " << totalMatches << "\nNumber of sequences: "
-                      << rep.totalReads() << "\nGPU time: " << gpuMs / 1000.0 << " s\nTime for processing: "
-                      << std::chrono::duration<double>(t2 - t0).count() << " s" << std::endl;
-            return 0;
-        }
-    }
-    FastxReader r1, r2;
-    if (!r1.open(inputs[0], err)) return 1;
-    if (paired && !r2.open(inputs[1], err)) return 1;
-    // long reads: bound the batch by bases as well (QueryIndexer sizes batches by k-mer count, QueryIndexer.cpp:62-67)
-    const size_t maxBases = std::min<size_t>(4ull << 30, maxBatchBases);
-    while (loadBatch(r1, paired ? &r2 : nullptr, opt.batchReads, maxBases, batch)) {
-        res.resize(batch.nReads());
+    });
+    auto stopAll = [&] {
+        toWrite.close();
+        if (writer.joinable()) writer.join();
+        stopReader();
+        freeText();
+    };
+    auto classifyAndFetch = [&](BatchSlot &s, uint32_t nReads) -> bool {
         size_t used = 0;
-        int rc = mb_stage_reads(db.ctx(), batch.bases.data(), batch.bases.size(), batch.offsets.data(), batch.lens.data(), batch.nReads());
-        if (rc == MB_OK) rc = mb_classify_staged(db.ctx(), &used);
+        int rc = mb_classify_staged(db.ctx(), &used);
+        s.nReads = nReads;
+        s.res.resize(nReads);
         if (rc == MB_OK) {
-            tcId.resize(used + 1);
-            tcCnt.resize(used + 1);
-            rc = mb_fetch_results(db.ctx(), res.data(), tcId.data(), tcCnt.data(), used + 1);
+            s.tcId.resize(used + 1);
+            s.tcCnt.resize(used + 1);
+            rc = mb_fetch_results(db.ctx(), s.res.data(), s.tcId.data(), s.tcCnt.data(), used + 1);
         }
-        if (rc != MB_OK) { err = mb_last_error(db.ctx()); return 1; }
+        if (rc != MB_OK) { err = mb_last_error(db.ctx()); return false; }
         mb_phase_times t;
         mb_get_timings(db.ctx(), &t);
         totalKmers += t.n_kmers;
         totalMatches += t.n_matches;
         gpuMs += t.total_ms;
-        std::cout << "Batch of " << batch.nReads() << " reads: " << t.n_kmers << " query k-mers, " << t.n_matches << " matches; GPU ms: extract "
-                  << t.extract_ms << " sort " << t.sort_kmers_ms << " match " << t.match_ms << " sort " << t.sort_matches_ms << " score "
-                  << t.score_ms << std::endl;
-        rep.writeClassifications(batch, res.data(), tcId.data(), tcCnt.data());
+        std::cout << "Batch of " << nReads << " reads" << (namesFromText ? " (FASTQ parsed on the GPU)" : "") << ": " << t.n_kmers
+                  << " query k-mers, " << t.n_matches << " matches; GPU ms: " << (namesFromText ? "parse+copy " : "copy ") << t.h2d_ms
+                  << " extract " << t.extract_ms << " sort " << t.sort_kmers_ms << " match " << t.match_ms << " sort " << t.sort_matches_ms
+                  << " score " << t.score_ms << std::endl;
+        return true;
+    };
+
+    bool hostFallback = false;           // the first chunk was not four-line FASTQ after all: nothing was written yet
+    if (deviceParse) {
+        uint64_t batchesDone = 0;
+        int cur = -1;
+        bool ok = filled.pop(cur);
+        while (ok) {
+            BatchSlot &s = slots[cur];
+            const bool last = s.f[0].eof && (!paired || s.f[1].eof);
+            if (s.f[0].fill == 0) break;
+            mb_fastq_index idx;
+            const auto tg = clk::now();
+            int rc = mb_stage_fastq(db.ctx(), s.f[0].data(), s.f[0].fill, paired ? s.f[1].data() : nullptr, paired ? s.f[1].fill : 0,
+                                    (1u << 29) - 2, last ? 1 : 0, &idx);
+            if (rc == MB_E_DATA && batchesDone == 0) {
+                std::cout << "Input is not plain four-line FASTQ (" << mb_last_error(db.ctx()) << "): using the host reader" << std::endl;
+                hostFallback = true;
+                break;
+            }
+            if (rc != MB_OK) { err = mb_last_error(db.ctx()); stopAll(); return 1; }
+            ++batchesDone;
+            if (idx.n_reads == 0 && last) break;
+            int nxt = -1;
+            if (!last) {
+                // the next chunk is (being) read: what this batch left over goes in front of it, and its copy to the device
+                // overlaps this batch's device work
+                if (!filled.pop(nxt) || readerFailed) { err = readerFailed ? readerErr : "reader stopped early"; stopAll(); return 1; }
+                BatchSlot &nx = slots[nxt];
+                nx.f[0].prepend(s.f[0].data() + idx.consumed1, s.f[0].fill - idx.consumed1);
+                if (paired) nx.f[1].prepend(s.f[1].data() + idx.consumed2, s.f[1].fill - idx.consumed2);
+                if (idx.n_reads == 0) {
+                    // not one whole record in the chunk: read twice as much from now on
+                    for (int f = 0; f < nFiles; ++f) {
+                        const size_t w = chunkWant[f];
+                        if (w >= chunkMax) { err = "FASTQ record longer than a batch may be (--max-ram / free GPU memory)"; stopAll(); return 1; }
+                        chunkWant[f] = std::min(chunkMax, 2 * w);
+                    }
+                } else if (mb_prefetch_fastq(db.ctx(), nx.f[0].data(), nx.f[0].fill, paired ? nx.f[1].data() : nullptr, paired ? nx.f[1].fill : 0) != MB_OK) {
+                    err = mb_last_error(db.ctx()); stopAll(); return 1;
+                }
+            }
+            if (idx.n_reads) {
+                s.nameOff.resize(idx.n_reads);
+                s.nameLen.resize(idx.n_reads);
+                if (!classifyAndFetch(s, idx.n_reads)) { stopAll(); return 1; }
+                if (mb_fetch_fastq_names(db.ctx(), s.nameOff.data(), s.nameLen.data()) != MB_OK) { err = mb_last_error(db.ctx()); stopAll(); return 1; }
+                toWrite.push(cur);
+            } else freeSlots.push(cur);
+            gpuBusy += secondsSince(tg);
+            if (last) break;
+            cur = nxt;
+        }
+        if (readerFailed) { err = readerErr; stopAll(); return 1; }
     }
+    if (!deviceParse || hostFallback) {
+        if (hostFallback) stopReader();      // nothing was written yet; the writer stays
+        namesFromText = false;
+        freeCh = &freeHost;
+        for (int i = 0; i < kSlots; ++i) freeHost.push(i);
+        // long reads: bound the batch by bases as well (QueryIndexer sizes batches by k-mer count, QueryIndexer.cpp:62-67)
+        const size_t maxBases = std::min<size_t>(4ull << 30, maxBatchBases);
+        Channel<int> parsed;
+        std::atomic<bool> openFailed{false};
+        std::thread hostReader([&] {
+            FastxReader r1, r2;
+            if (!r1.open(inputs[0], readerErr) || (paired && !r2.open(inputs[1], readerErr))) { openFailed = true; parsed.close(); return; }
+            int si;
+            while (freeHost.pop(si)) {
+                if (!loadBatch(r1, paired ? &r2 : nullptr, opt.batchReads, maxBases, slots[si].batch)) break;
+                parsed.push(si);
+            }
+            parsed.close();
+        });
+        int cur;
+        bool failed = false;
+        while (!failed && parsed.pop(cur)) {
+            BatchSlot &s = slots[cur];
+            const ReadBatch &b = s.batch;
+            if (mb_stage_reads(db.ctx(), b.bases.data(), b.bases.size(), b.offsets.data(), b.lens.data(), b.nReads()) != MB_OK) {
+                err = mb_last_error(db.ctx());
+                failed = true;
+            } else if (!classifyAndFetch(s, b.nReads())) failed = true;
+            else toWrite.push(cur);
+        }
+        freeHost.closeAndDrop();
+        hostReader.join();
+        if (openFailed) { err = readerErr; failed = true; }
+        if (failed) { stopAll(); return 1; }
+    }
+    stopAll();
     rep.closeClassifications();
+    if (timing) fprintf(stderr, "[classify] busy seconds: reader %.3f (page-locking %.3f), GPU calls (incl. waiting for the reader) %.3f, writer %.3f; batches done at %.3f s\n",
+                        readBusy, pinBusy, gpuBusy, writeBusy, secondsSince(t0));
     if (!rep.writeReport(err)) return 1;
     const auto t2 = clk::now();
     std::cout << "Number of query k-mers: " << totalKmers << "\nThe number of matches: " << totalMatches << "\nNumber of sequences: "

@@ -218,6 +218,7 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
     const size_t maxBatchBases = std::max<size_t>(budget / slotBytes, 1u << 20) / 2 * (size_t) n;
     const Taxonomy &tax = workers[0].db->taxonomy();
     Reporter rep(tax, outDir, jobId, opt.printLineage != 0, opt.kronaPrelude);
+    rep.setThreads(ioThreads(opt));
     if (!rep.openClassifications(err)) return 1;
     const bool paired = opt.seqMode == 2;
     FastxReader r1, r2;

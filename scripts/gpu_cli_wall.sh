@@ -13,6 +13,8 @@ for run in 1 2; do
   tail -1 gpurun_out/${TAG}_g1.log
 done
 grep -E "Time for processing|GPU time|Batch budget" gpurun_out/${TAG}_g1.log
+MB_TIMING=1 $CLI classify $W/sample1000000_1.fq $W/sample1000000_2.fq $W/db $OUT g1b --batch-reads 200000 > gpurun_out/${TAG}_g1b.log 2>&1; grep -E "db open|Time for processing" gpurun_out/${TAG}_g1b.log
+cmp $OUT/g1_classifications.tsv $OUT/g1b_classifications.tsv && cmp $OUT/g1_report.tsv $OUT/g1b_report.tsv && echo "--batch-reads 200000 == one batch"
 MB_HOST_PARSE=1 $CLI classify $W/sample1000000_1.fq $W/sample1000000_2.fq $W/db $OUT g1h > gpurun_out/${TAG}_g1h.log 2>&1; grep -E "Time for processing" gpurun_out/${TAG}_g1h.log
 cmp $OUT/g1_classifications.tsv $OUT/g1h_classifications.tsv && echo "host-parse == device-parse"
 if [ "$N" -gt 1 ]; then
