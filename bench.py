@@ -405,7 +405,7 @@ def algorithmic_bytes(t, sizeof_match=24):
         "k_radix_hist<kmer>": 16 * nk,
         "k_radix_scan_hist<kmer>": 5 * 256 * 16,
         "k_radix_pass<kmer>": 32 * nk,                            # one read + one write of the records
-        "k_match_partition": 8 * (dbw // 2048 + 1),
+        "k_match_partition": 40 * (dbw // 448 + 1),          # a 32-byte unit read + an 8-byte slice start written per unit (<= one per 448 words)
         "k_match": 2 * dbw + 4 * dbk + 16 * nk + sizeof_match * nm,   # stream + info + queries + matches
         "k_radix_hist<match>": sizeof_match * nm,
         "k_radix_scan_hist<match>": 16 * 256 * 16,

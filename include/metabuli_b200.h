@@ -113,9 +113,10 @@ int         mb_set_params(mb_ctx *ctx, const mb_params *p);  /* device / last_sh
 
 /* ---- database (replaces the per-call fopen/fread/mmap of KmerMatcher::matchKmers, KmerMatcher.cpp:127-271) ----
  * diffIdx: uint16 delta stream (IndexCreator.cpp:868-886); info: one uint32 per k-mer; splits: the
- * `split` file.  The library keeps the compressed stream resident in HBM and builds a block index
- * (k-mer ordinal + value before every 2048-word block, anchored on the stream start) so that every
- * block decodes independently.  A SHARD (multi-GPU) is passed as a self-contained stream: the host
+ * `split` file.  The library keeps the compressed stream resident in HBM and builds a unit index
+ * (the stream cut every 448 words where a new value of the query sort key starts; per unit: first word,
+ * value before, k-mer ordinal, key) so that every unit decodes independently and owns an exact slice of
+ * the sorted queries.  A SHARD (multi-GPU) is passed as a self-contained stream: the host
  * cuts the DB at `split` entries and re-encodes the shard's first k-mer as a delta from 0
  * (INTEGRATION.md), so the library never needs to know where a shard came from. */
 int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint32_t *info, size_t n_kmers);

@@ -3,7 +3,7 @@
 # usage: bash scripts/gpu_prof_one.sh <tag> <kernel regex> [launches to skip] [launches to capture] [env assignments...]
 TAG=$1; RX=$2; SKIP=${3:-2}; CNT=${4:-1}; shift 4
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-check $BENCH_EXTRA"
 env "$@" ncu --set full --clock-control none --import-source on -k regex:$RX -s $SKIP -c $CNT -f -o gpurun_out/${TAG} $CMD > gpurun_out/${TAG}_ncu.log 2>&1
 echo "ncu rc=$?"
 rep=gpurun_out/${TAG}.ncu-rep
