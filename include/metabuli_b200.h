@@ -78,7 +78,9 @@ typedef struct {
                                  sixth, 24 bits in all.  0 = default (21 for format 2, 32 for format 1).
                                  The join only needs the queries of a DB block to be contiguous, not ordered, so
                                  fewer bits = fewer radix passes; blocks re-check the full amino-acid part.        */
-    int32_t reserved[2];
+    int32_t mask_mode;        /* --mask (0): 1 = tantan low-complexity masking of every mate before extraction
+                                 (SeqIterator::maskLowComplexityRegions, SeqIterator.cpp:154-177)              */
+    float   mask_prob;        /* --mask-prob (0.9): bases whose repeat probability reaches it become 'N'       */
 } mb_params;
 
 /* Per-read result: the fields of Query (src/commons/common.h:95-128) that reach the outputs. */
@@ -151,6 +153,12 @@ int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint
 /* The same path in stages (each leaves its output resident on the device): */
 int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
                    uint32_t n_reads);                                   /* H2D only                      */
+/* --mask 1 on the staged batch, in place.  Replaces SeqIterator::maskLowComplexityRegions
+ * (src/commons/SeqIterator.cpp:154-177: tantan::maskSequences with maxRepeatOffset 50, repeatProb 0.005, repeatEndProb
+ * 0.05, decay 0.9, no gaps) as KmerExtractor::processSequence applies it to every mate (KmerExtractor.cpp:328-335).
+ * mb_extract_kmers / mb_classify_* call it themselves when mb_params.mask_mode is 1; the explicit call is the parity tap
+ * (mb_fetch_staged_reads then returns the masked bases).  Idempotent per staged batch. */
+int mb_mask_reads(mb_ctx *ctx);
 /* Input pipeline on the device.  Replaces, for plain four-line FASTQ text, the two host
  * parses of the reference: QueryIndexer::indexQueryFile (src/commons/QueryIndexer.cpp:30-147) and
  * KmerExtractor::loadChunkOfReads over KSeqWrapper (src/commons/KmerExtractor.cpp:312-386).  text1 / text2 are raw

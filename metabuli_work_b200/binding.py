@@ -33,7 +33,7 @@ class Params(C.Structure):
                 ("seq_mode", C.c_int32), ("min_cons_cnt", C.c_int32), ("min_cons_cnt_euk", C.c_int32),
                 ("min_score", C.c_float), ("min_sp_score", C.c_float), ("tie_ratio", C.c_float),
                 ("skip_redundancy", C.c_int32), ("accession_level", C.c_int32), ("last_shard", C.c_int32),
-                ("kmer_sort_bits", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("kmer_sort_bits", C.c_int32), ("mask_mode", C.c_int32), ("mask_prob", C.c_float)]
 
 
 class PhaseTimes(C.Structure):
@@ -67,7 +67,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
                "mb_prefetch_reads", "mb_stage_fastq", "mb_prefetch_fastq", "mb_alloc_host", "mb_free_host", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches",
-               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access"]
+               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access", "mb_mask_reads"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -137,6 +137,7 @@ _sig(_cuda, "mb_alloc_host", vp, [sz])
 _sig(_cuda, "mb_free_host", None, [vp])
 _sig(_cuda, "mb_fetch_fastq_names", C.c_int, [vp, vp, vp])
 _sig(_cuda, "mb_fetch_staged_reads", C.c_int, [vp, vp, vp, vp])
+_sig(_cuda, "mb_mask_reads", C.c_int, [vp])
 _sig(_cuda, "mb_extract_kmers_routed", C.c_int, [vp, szp])
 _sig(_cuda, "mb_take_routed_kmers", C.c_int, [vp, szp])
 _sig(_cuda, "mb_match_kmers_routed", C.c_int, [vp, szp])
@@ -265,6 +266,10 @@ class Context:
         self._ck(_cuda.mb_fetch_staged_reads(self.ctx, _ptr(bases) if n_bases else None, _ptr(offsets) if self.n_reads else None,
                                              _ptr(lens) if self.n_reads else None))
         return bases, offsets, lens
+
+    def mask_reads(self):
+        """--mask 1 on the staged batch (tap; extract() applies it itself when mask_mode is set)."""
+        self._ck(_cuda.mb_mask_reads(self.ctx))
 
     def extract(self):
         n = C.c_size_t(0)

@@ -6,6 +6,8 @@
 // Everything runs on one CUDA stream; the only host synchronisations per batch are four 8-byte
 // read-backs (k-mer count, match count, longest per-read match list, taxCnt size) that size the next
 // launch.  There is no CPU fallback anywhere in this file.
+#include <cmath>
+
 #include "mb_common.cuh"
 #include "mb_extract.cuh"
 #include "mb_radix.cuh"
@@ -13,6 +15,7 @@
 #include "mb_score.cuh"
 #include "mb_segsort.cuh"
 #include "mb_fastq.cuh"
+#include "mb_mask.cuh"
 
 #include <cuda_runtime.h>
 
@@ -77,13 +80,13 @@ struct Counters {                 // device-side scalars, one allocation
 // kernels of this library, for the per-kernel timing table (mb_get_kernel_times)
 enum { KID_TILE_MATE, KID_EXTRACT_COUNT, KID_EXTRACT_SCAN, KID_EXTRACT_WRITE, KID_KSORT_HIST, KID_KSORT_SCAN, KID_KSORT_PASS,
        KID_MATCH_PARTITION, KID_MATCH, KID_MSORT_HIST, KID_MSORT_SCAN, KID_MSORT_PASS, KID_SEGMENT, KID_SEGMENT_MAX, KID_SEGSORT, KID_SEGSORT_LONG, KID_SCORE_FAST, KID_SCORE_FINISH, KID_SCORE,
-       KID_LR_HEADS, KID_LR_PATHS, KID_LR_SPECIES, KID_LR_BEST,
+       KID_LR_HEADS, KID_LR_PATHS, KID_LR_SPECIES, KID_LR_BEST, KID_MASK,
        KID_COUNT };
 const char *const KID_NAMES[KID_COUNT] = {"k_tile_first_mate", "k_extract<count>", "k_scan_counts", "k_extract",
                                           "k_radix_hist<kmer>", "k_radix_scan_hist<kmer>", "k_radix_pass<kmer>",
                                           "k_match_partition", "k_match", "k_radix_hist<match>", "k_radix_scan_hist<match>",
                                           "k_radix_pass<match>", "k_segment_matches", "k_segment_max", "k_sort_segments", "k_sort_segments_long", "k_score_fast", "k_score_finish", "k_score",
-                                          "k_lr_heads", "k_lr_paths", "k_lr_species", "k_lr_best"};
+                                          "k_lr_heads", "k_lr_paths", "k_lr_species", "k_lr_best", "k_mask_mates"};
 struct KSample { int kid; cudaEvent_t a, b; };
 
 } // namespace
@@ -154,6 +157,8 @@ struct mb_ctx {
     bool profile = false;             // mb_set_profile: bracket every kernel launch with an event pair
     std::vector<KSample> samples;     // event pairs of the current batch
     size_t n_samples = 0;
+    bool reads_masked = false;         // --mask 1 has been applied to the staged bases
+    DevBuf mask_probs, mask_scales;
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
     bool segments_valid = false;      // seg_begin/seg_end describe matches_a
     // multi-GPU routing (mb_peer_*): this context's receive side and the routing table of all ranks
@@ -334,6 +339,7 @@ void mb_default_params(mb_params *p) {
     p->device = 0; p->kmer_format = 1; p->syncmer = 0; p->smer_len = 5; p->seq_mode = 2;
     p->min_cons_cnt = 4; p->min_cons_cnt_euk = 9; p->min_score = 0.f; p->min_sp_score = 0.f; p->tie_ratio = 0.95f;
     p->skip_redundancy = 0; p->accession_level = 0; p->last_shard = 1;
+    p->mask_mode = 0; p->mask_prob = 0.9f;
 }
 
 const char *mb_global_error(void) { return g_global_err.c_str(); }
@@ -348,6 +354,8 @@ static int check_params(const mb_params *p, std::string &err) {
     }
     if (p->kmer_sort_bits == 21 && p->kmer_format != 2) { err = "kmer_sort_bits 21 (re-coded key) needs kmer_format 2"; return MB_E_ARG; }
     if (p->accession_level != 0) { err = "accession_level != 0 is not on this path"; return MB_E_ARG; }
+    if (p->mask_mode != 0 && p->mask_mode != 1) { err = "mask_mode must be 0 or 1"; return MB_E_ARG; }
+    if (p->mask_mode && !(p->mask_prob > 0.f && p->mask_prob <= 1.f)) { err = "mask_prob must be in (0, 1]"; return MB_E_ARG; }
     return MB_OK;
 }
 
@@ -643,6 +651,7 @@ int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_
     ctx->kmer_bound = info.bound;
     ctx->max_query_len = info.max_q + 8;
     ctx->have_reads = true;
+    ctx->reads_masked = false;
     ctx->launches = 0;
     ctx->n_samples = 0;
     ctx->times.match_retries = 0;
@@ -785,6 +794,7 @@ int mb_stage_fastq(mb_ctx *ctx, const char *text1, size_t n1, const char *text2,
     ctx->kmer_bound = info.bound;
     ctx->max_query_len = info.max_q + 8;
     ctx->have_reads = true;
+    ctx->reads_masked = false;
     ctx->times.match_retries = 0;
     out->n_reads = nr;
     out->n_bases = n_bases;
@@ -853,6 +863,41 @@ int mb_fetch_staged_reads(mb_ctx *ctx, char *bases, uint64_t *offsets, uint32_t 
     return MB_OK;
 }
 
+// --mask 1 (mb_mask.cuh): every mate of the staged batch masked in place, once per batch
+static int mask_impl(mb_ctx *ctx) {
+    if (ctx->reads_masked || !ctx->n_reads || !ctx->n_bases) { ctx->reads_masked = true; return MB_OK; }
+    // Tantan::Tantan (lib/mmseqs/lib/tantan/tantan.cpp:81-135) for the arguments of SeqIterator.cpp:161-170; the two
+    // likelihood ratios are what ProbabilityMatrix(NucleotideMatrix("nucleotide.out", 1.0, 0.0)) holds at run time
+    // (dumped from the reference classes: tests/golden/data/mask_lr.bin, checked by the tests)
+    MaskModel M;
+    const double repeatProb = 0.005, repeatEndProb = 0.05, decay = 0.9;
+    M.b2b = 1 - repeatProb;
+    M.f2b = repeatEndProb;
+    M.f2f0 = 1 - repeatEndProb;
+    M.lr_match = 0x1.c6a258ad6ec6ep+1;
+    M.lr_mismatch = 0x1.31f371483f33ap-3;
+    M.min_prob = (double) ctx->par.mask_prob;
+    double p = repeatProb * ((1 - decay) / (1 - std::pow(decay, MK_OFF)));     // firstRepeatOffsetProb, tantan.cpp:26-31
+    for (int i = 0; i < MK_OFF; ++i) { M.b2f[i] = p; p *= decay; }
+    const u32 n_mates = ctx->n_reads * 2;
+    CK(ctx->mask_probs.ensure((ctx->n_bases + 16) * sizeof(float)));
+    CK(ctx->mask_scales.ensure(((ctx->n_bases >> 4) + n_mates + 2) * sizeof(double)));
+    KL(KID_MASK, k_mask_mates<<<(n_mates + MK_THREADS - 1) / MK_THREADS, MK_THREADS, 0, ctx->stream>>>(
+                     ctx->bases.as<u8>(), ctx->offsets.as<u64>(), ctx->lens.as<u32>(), n_mates, M, ctx->mask_probs.as<float>(),
+                     ctx->mask_scales.as<double>()));
+    ctx->reads_masked = true;
+    return MB_OK;
+}
+
+int mb_mask_reads(mb_ctx *ctx) {
+    if (!ctx) return MB_E_ARG;
+    if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "mb_stage_reads first");
+    CK(cudaSetDevice(ctx->par.device));
+    if (int rc = mask_impl(ctx)) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
 static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
     if (!ctx) return MB_E_ARG;
     if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "mb_stage_reads first");
@@ -864,6 +909,7 @@ static int extract_impl(mb_ctx *ctx, size_t *n_kmers, const bool routed) {
     ctx->n_samples = 0;               // the per-kernel table covers one pass of the device stages
     ctx->launches = 0;
     const u32 n_tiles = (u32) ((ctx->n_bases + EX_TILE - 1) / EX_TILE);
+    if (ctx->par.mask_mode) { if (int rc = mask_impl(ctx)) return rc; }
     if (n_tiles && ctx->n_reads) {
         ExtractArgs a;
         a.bases = ctx->bases.as<u8>(); a.n_bases = ctx->n_bases; a.offsets = ctx->offsets.as<u64>(); a.lens = ctx->lens.as<u32>();

@@ -245,7 +245,6 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     if (opt.reducedAA) { err = "reduced amino-acid alphabet databases are outside this path (ReducedKmerMatcher)"; return false; }
     if (opt.accessionLevel != 0) { err = "accession-level classification is outside this path"; return false; }
     if (opt.em) { err = "--em is outside this path"; return false; }
-    if (opt.maskMode) { err = "--mask 1 (tantan masking) is not implemented on this path yet"; return false; }
 
     using clk = std::chrono::steady_clock;
     const bool timing = getenv("MB_TIMING") != nullptr;        // where the load time goes, on stderr
@@ -352,6 +351,8 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     par_.tie_ratio = opt.tieRatio;
     par_.skip_redundancy = skipRedundancy;
     par_.accession_level = 0;
+    par_.mask_mode = opt.maskMode ? 1 : 0;          // KmerExtractor.cpp:37-38,328-335
+    par_.mask_prob = opt.maskProb;
     par_.last_shard = (shard + 1 == nShards) ? 1 : 0;
     ctx_ = mb_create(&par_);
     if (!ctx_) { err = mb_global_error(); return false; }

@@ -413,3 +413,4 @@ int32_t orc_tax_at_rank(const orc_db *db, int32_t t, const char *rank) { return 
 #include "orc_match.inc"
 #include "orc_score.inc"
 #include "orc_io.inc"
+#include "orc_mask.inc"

@@ -89,6 +89,9 @@ def lib():
         L.orc_write_report.argtypes = [vp, C.c_char_p, vp, u32]
         L.orc_write_db_files.restype = C.c_int
         L.orc_write_db_files.argtypes = [C.c_char_p, vp, vp, sz, C.c_int, C.c_int]
+        L.orc_mask_sequences.argtypes = [vp, vp, vp, u32, C.c_float, vp]
+        L.orc_mask_lr.restype = C.c_double
+        L.orc_mask_lr.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -157,6 +160,16 @@ class Batch:
                 pos += len(s)
         self.seqs = np.frombuffer(b"".join(chunks) + b"\0" * 8, dtype=np.uint8).copy()
         self.off, self.len = off, ln
+
+
+def mask(batch, mask_prob=0.9, want_probs=False):
+    """--mask 1: the batch with every mate masked (tantan), optionally the per-base repeat probabilities."""
+    import copy
+    out = copy.copy(batch)
+    out.seqs = batch.seqs.copy()
+    probs = np.zeros(len(out.seqs), dtype=np.float32) if want_probs else None
+    lib().orc_mask_sequences(_ptr(out.seqs), _ptr(out.off), _ptr(out.len), 2 * batch.n, mask_prob, _ptr(probs) if want_probs else None)
+    return (out, probs) if want_probs else out
 
 
 def extract(p, batch):

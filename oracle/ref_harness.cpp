@@ -8,17 +8,21 @@
  *   Taxonomer::chooseBestTaxon                                         (Taxonomer.cpp:130)
  *   TaxonomyWrapper / loadTaxonomy / loadDbParameters                  (common.cpp:50-133)
  *   KSeqWrapper (FASTA/FASTQ parsing)
- * The only restated piece is the ~30-line read loop of KmerExtractor (loadChunkOfReads /
- * processSequence / fillQueryKmerBuffer, KmerExtractor.cpp:312-386,442-494): KmerExtractor's
- * constructor needs MMseqs2 substitution matrices that exist only as cmake-generated headers.
- * (The full reference binary is not built here, so that loop is pinned only indirectly: the oracle port and the CUDA
- * path, written from the reference text independently of this loop, produce the same k-mer multiset.)
+ * Extraction has two forms.  --ref-extractor runs the reference's own QueryIndexer::indexQueryFile and
+ * KmerExtractor::extractQueryKmers (incl. --mask 1: SeqIterator::maskLowComplexityRegions / tantan) the way
+ * Classifier::startClassify drives them; the nucleotide matrix its constructor needs is handed over as
+ * "nucleotide.out:DATA" from a header generated out of lib/mmseqs/data/nucleotide.out.  It parses the files inside the
+ * timed extraction, so the timing runs (bench.py) use the default form instead: the ~30-line read loop of KmerExtractor
+ * (loadChunkOfReads / processSequence / fillQueryKmerBuffer, KmerExtractor.cpp:312-386,442-494) restated below over
+ * reads parsed up front.  tests/golden/make_golden2.py checks on every fixture case that both forms give the same
+ * k-mer buffer.
  *
  * LocalParameters cannot be constructed without the MMseqs2 Parameters machinery (generated
  * code again), so a zeroed object is fabricated and only the fields the path reads are set.
  *
  * usage: ref_harness DBDIR OUTPREFIX SEQMODE THREADS READS1 [READS2] [--dump] [--reps N] [--skip-reps W]
  *                    [--max-reads N] [--min-score F] [--min-sp-score F] [--smer-len S] [--report OUTDIR JOBID] [--lineage]
+ *                    [--ref-extractor] [--mask 0|1] [--mask-prob P] [--dump-masked FILE]
  * --report: the reference's own Reporter (src/commons/Reporter.cpp:38-83,146-253) writes JOBID_classifications.tsv,
  * JOBID_report.tsv and JOBID_krona.html into OUTDIR exactly as Classifier::startClassify does (Classifier.cpp:133-158).
  * (--skip-reps W: the first W of the N repetitions are warm-up and stay out of the reported means)
@@ -26,6 +30,9 @@
  * prints one JSON line with per-phase wall times.
  */
 #include "Classifier.h"
+#include "KmerExtractor.h"
+#include "NucleotideMatrix.h"
+#include "QueryIndexer.h"
 #include "Reporter.h"
 #include "KmerMatcher.h"
 #include "KmerScanner.h"
@@ -43,6 +50,8 @@
 #include <new>
 #include <omp.h>
 
+#include "nucleotide_out.h"   /* oracle/_ref/gen: lib/mmseqs/data/nucleotide.out as a C array (the reference's cmake embeds it the same way) */
+
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -57,12 +66,34 @@ static LocalParameters *fabricate_parameters() {
     new (&par->taxonomyPath) std::string();
     new (&par->dbName) std::string();
     new (&par->dbDate) std::string();
+    /* BaseMatrix::unserialize accepts "NAME.out:DATA" (SubstitutionMatrix.cpp:13-20): the matrix text travels in the name */
+    new (&par->scoringMatrixFile) MultiParam<NuclAA<std::string>>(NuclAA<std::string>(
+        "blosum62.out", std::string("nucleotide.out:") + std::string((const char *) nucleotide_out, nucleotide_out_len)));
     return par;
 }
 
 struct Mate { std::string seq; };
 
+/* --dump-lr FILE: the 5x5 likelihood-ratio matrix tantan gets (ProbabilityMatrix over NucleotideMatrix, BaseMatrix.h:83-96),
+ * the letter codes (aa2num) and the mask code, as the reference computes them at run time */
+static int dump_lr(const char *path) {
+    LocalParameters &par = *fabricate_parameters();
+    NucleotideMatrix subMat(par.scoringMatrixFile.values.nucleotide().c_str(), 1.0, 0.0);
+    ProbabilityMatrix pm(subMat);
+    FILE *f = fopen(path, "wb");
+    if (!f) return 1;
+    for (int i = 0; i < subMat.alphabetSize; ++i) fwrite(pm.probMatrixPointers[i], sizeof(double), subMat.alphabetSize, f);
+    unsigned char codes[256];
+    for (int c = 0; c < 256; ++c) codes[c] = (unsigned char) subMat.aa2num[c];
+    fwrite(codes, 1, 256, f);
+    fwrite(pm.hardMaskTable, 1, 1, f);
+    fclose(f);
+    printf("alphabet %d\n", subMat.alphabetSize);
+    return 0;
+}
+
 int main(int argc, char **argv) {
+    if (argc == 3 && !strcmp(argv[1], "--dump-lr")) return dump_lr(argv[2]);
     if (argc < 6) {
         fprintf(stderr, "usage: %s DBDIR OUTPREFIX SEQMODE THREADS READS1 [READS2] [--dump] [--reps N] [--max-reads N]\n", argv[0]);
         return 2;
@@ -79,7 +110,15 @@ int main(int argc, char **argv) {
     float minScore = 0.f, minSpScore = 0.f;
     int smerLen = 5, lineage = 0;
     std::string reportDir, reportJob;
+    bool refExtractor = false;
+    std::string dumpMasked;          /* file: SeqIterator::maskLowComplexityRegions of every mate, one line each */
+    int maskMode = 0;
+    float maskProb = 0.9f;
     for (; argi < argc; ++argi) {
+        if (!strcmp(argv[argi], "--ref-extractor")) { refExtractor = true; continue; }
+        if (!strcmp(argv[argi], "--mask")) { maskMode = atoi(argv[++argi]); continue; }
+        if (!strcmp(argv[argi], "--mask-prob")) { maskProb = (float) atof(argv[++argi]); continue; }
+        if (!strcmp(argv[argi], "--dump-masked")) { dumpMasked = argv[++argi]; continue; }
         if (!strcmp(argv[argi], "--dump")) dump = true;
         else if (!strcmp(argv[argi], "--reps")) reps = atoi(argv[++argi]);
         else if (!strcmp(argv[argi], "--skip-reps")) skipReps = atoi(argv[++argi]);
@@ -105,8 +144,8 @@ int main(int argc, char **argv) {
     par.ramUsage = 128;
     par.minConsCnt = 4;
     par.minConsCntEuk = 9;
-    par.maskMode = 0;
-    par.maskProb = 0.9;
+    par.maskMode = maskMode;
+    par.maskProb = maskProb;
     par.matchPerKmer = 4;
     par.accessionLevel = 0;
     par.tieRatio = 0.95;
@@ -153,6 +192,20 @@ int main(int argc, char **argv) {
     }
     const size_t nReads = queryList.size();
     double tParse = now_s() - t0;
+    if (!dumpMasked.empty()) {
+        NucleotideMatrix subMat(par.scoringMatrixFile.values.nucleotide().c_str(), 1.0, 0.0);
+        ProbabilityMatrix probMatrix(subMat);
+        FILE *fm = fopen(dumpMasked.c_str(), "w");
+        std::vector<char> masked;
+        for (size_t i = 0; i < nReads; ++i)
+            for (int mate = 0; mate < (seqMode == 2 ? 2 : 1); ++mate) {
+                const std::string &s = mate == 0 ? seq1[i] : seq2[i];
+                masked.assign(s.size() + 1, 0);
+                SeqIterator::maskLowComplexityRegions((const unsigned char *) s.c_str(), (unsigned char *) masked.data(), probMatrix, maskProb, &subMat);
+                fprintf(fm, "%s\n", masked.data());
+            }
+        fclose(fm);
+    }
 
     double tExtract = 0, tSortK = 0, tMatch = 0, tSortM = 0, tScore = 0;
     size_t nKmers = 0, nMatches = 0;
@@ -160,9 +213,34 @@ int main(int argc, char **argv) {
     Buffer<Match> matchBuffer(16);
     for (int rep = 0; rep < reps; ++rep) {
         if (rep == skipReps) tExtract = tSortK = tMatch = tSortM = tScore = 0;   /* warm-up repetitions end here */
+        size_t slots = 0;
+        if (refExtractor) {
+            /* the reference's own QueryIndexer + KmerExtractor, driven as Classifier::startClassify drives them
+             * (Classifier.cpp:57-112): index the files, one split, extract (+ mask) and sort inside extractQueryKmers */
+            t0 = now_s();
+            QueryIndexer indexer(par);
+            indexer.setBytesPerKmer(par.matchPerKmer);
+            indexer.indexQueryFile(0);
+            const std::vector<QuerySplit> &splits = indexer.getQuerySplits();
+            if (splits.size() != 1) { fprintf(stderr, "--ref-extractor: %zu query splits, expected 1\n", splits.size()); return 3; }
+            static KmerExtractor *extractor = new KmerExtractor(par, geneticCode, kmerFormat);
+            std::vector<std::string> names(nReads);
+            for (size_t i = 0; i < nReads; ++i) names[i] = queryList[i].name;
+            queryList.clear();
+            queryList.resize(splits[0].end - splits[0].start);
+            if (queryList.size() != nReads) { fprintf(stderr, "--ref-extractor: read count differs\n"); return 3; }
+            kmerBuffer.reallocateMemory(splits[0].kmerCnt);
+            kmerBuffer.init();
+            KSeqWrapper *k1 = KSeqFactory(reads1.c_str());
+            KSeqWrapper *k2 = seqMode == 2 ? KSeqFactory(reads2.c_str()) : nullptr;
+            extractor->extractQueryKmers(kmerBuffer, queryList, splits[0], par, k1, k2);
+            delete k1;
+            delete k2;
+            slots = kmerBuffer.startIndexOfReserve;
+            tExtract += now_s() - t0;
+        } else {
         /* ---- extraction: KmerExtractor.cpp:442-494 (lengths, empties), :312-386 (six frames) ---- */
         t0 = now_s();
-        size_t slots = 0;
         std::vector<size_t> slotStart(nReads + 1);
         std::vector<char> skip(nReads, 0);
         for (size_t i = 0; i < nReads; ++i) {
@@ -219,6 +297,7 @@ int main(int argc, char **argv) {
         t0 = now_s();
         SORT_PARALLEL(kmerBuffer.buffer, kmerBuffer.buffer + kmerBuffer.startIndexOfReserve, Kmer::compareQueryKmer);
         tSortK += now_s() - t0;
+        }
 
         /* ---- match (retry with a larger buffer on overflow, Classifier.cpp:127-131) ---- */
         t0 = now_s();

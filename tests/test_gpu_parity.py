@@ -104,6 +104,54 @@ def test_golden_case_all_stages(golden, mb, case):
     assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
 
 
+@pytest.mark.parametrize("case", ["mask_paired", "mask_paired_p05", "mask_long"])
+def test_mask_on_device(golden, mb, tmp_path, case):
+    """--mask 1 (csrc/mb_mask.cuh): the masked batch is byte-identical to what the reference's
+    SeqIterator::maskLowComplexityRegions produced (tests/golden/data/<case>.masked.txt, written by ref_harness), the
+    stages that follow give the reference's results, and `metabuli classify --mask 1` writes the reference's files."""
+    meta = golden.cases[case]
+    _, s1, s2 = golden.reads(case)
+    want = open(os.path.join(helpers.DATA, case + ".masked.txt"), "rb").read().split(b"\n")[:-1]
+    bases, offsets, lens = mb.pack_reads(s1, s2)
+    clf = mb.Classifier(golden.dbdir(case), seq_mode=meta["seq_mode"])
+    try:
+        clf.set_params(mask_mode=1, mask_prob=meta["mask_prob"])
+        clf.stage(bases, offsets, lens)
+        clf.mask_reads()
+        clf.mask_reads()                                    # idempotent per staged batch
+        gb, go, gl = clf.staged_reads(len(bases))
+        got = [bytes(gb[int(o):int(o) + int(l)]) for o, l in zip(go, gl)]
+        if s2 is None:
+            got = got[0::2]
+        assert got == want
+        # the oracle's restatement agrees too (same bytes), then the rest of the path on the masked batch
+        ob = orc.mask(orc.Batch(s1, s2), meta["mask_prob"])
+        assert bytes(ob.seqs[:len(bases)]) == bytes(gb)
+        n = clf.extract()
+        assert n == meta["n_kmers"]
+        assert helpers.digest(canon_k(clf.kmers())) == meta["kmers_sha256"]
+        clf.sort_kmers()
+        assert clf.match() == meta["n_matches"]
+        clf.sort_matches()
+        assert helpers.digest(as_orc_matches(clf.matches())) == meta["matches_sha256"]
+        res, ids, cnt = clf.fetch(clf.score())
+        assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
+        # one call from host buffers: masking happens inside
+        res2, ids2, cnt2 = clf.classify(bases, offsets, lens)
+        assert helpers.check_results_against_golden(golden.results(case), res2, ids2, cnt2) == []
+    finally:
+        clf.close()
+    # the command line, device parser and host reader
+    out = str(tmp_path)
+    rep = os.path.join(helpers.DATA, "reports")
+    files = [os.path.join(helpers.DATA, f) for f in meta["reads"]]
+    flags = ["--seq-mode", str(meta["seq_mode"]), "--mask", "1", "--mask-prob", str(meta["mask_prob"])]
+    for job, env in ((case, {}), (case + "_h", {"MB_HOST_PARSE": "1"})):
+        subprocess.check_call([mb.CLI, "classify"] + flags + files + [golden.dbdir(case), out, job], env=dict(os.environ, **env))
+        for f in ("classifications.tsv", "report.tsv"):
+            assert open(os.path.join(out, job + "_" + f), "rb").read() == open(os.path.join(rep, case + "_" + f), "rb").read(), (job, f)
+
+
 @pytest.mark.parametrize("bits", [24, 32, 40])
 def test_kmer_sort_bits(golden, mb, bits):
     """The join result does not depend on how many leading amino-acid bits the query sort orders."""

@@ -33,6 +33,55 @@ def test_oracle_matches_reference(golden, case):
     db.close()
 
 
+MASK_CASES = ["mask_paired", "mask_paired_p05", "mask_long"]
+
+
+def _mates(b):
+    return [bytes(b.seqs[int(o):int(o) + int(l)]).decode("latin-1") for o, l in zip(b.off, b.len)]
+
+
+@pytest.mark.parametrize("case", MASK_CASES)
+def test_oracle_mask_matches_reference(golden, case):
+    """--mask 1 (tests/golden/make_golden3.py): the masked mates equal what the reference's
+    SeqIterator::maskLowComplexityRegions wrote (SeqIterator.cpp:154-177), and the masked batch classifies like the
+    reference's own KmerExtractor (with masking) + KmerMatcher + Taxonomer did."""
+    meta = golden.cases[case]
+    names, s1, s2 = golden.reads(case)
+    b = orc.Batch(s1, s2)
+    masked, probs = orc.mask(b, meta["mask_prob"], want_probs=True)
+    want = open(helpers.DATA + "/" + case + ".masked.txt").read().split("\n")[:-1]
+    got = [m for i, m in enumerate(_mates(masked)) if s2 is not None or i % 2 == 0]
+    assert got == want
+    assert sum(m.count("N") for m in got) > sum(m.count("N") for m in _mates(b))     # the case masks something
+    assert float(probs.max()) <= 1.0 and float(probs.min()) >= 0.0
+    db = orc.Db(golden.dbdir(case))
+    p = db.params(seq_mode=meta["seq_mode"])
+    k, m, res, ids, cnt = orc.classify(db, p, masked, threads=2)
+    assert helpers.digest(k) == meta["kmers_sha256"] and helpers.digest(m) == meta["matches_sha256"]
+    assert helpers.check_results_against_golden(golden.results(case), res, ids, cnt) == []
+    db.close()
+
+
+def test_mask_likelihood_ratios_are_the_reference_matrix():
+    """mask_lr.bin = ref_harness --dump-lr: ProbabilityMatrix(NucleotideMatrix("nucleotide.out")) and aa2num as the
+    reference computes them at run time; the oracle (and csrc/mb_mask.cuh) hold the two values and the letter map."""
+    raw = open(helpers.DATA + "/mask_lr.bin", "rb").read()
+    lr = np.frombuffer(raw[:200], dtype=np.float64).reshape(5, 5)
+    codes = np.frombuffer(raw[200:456], dtype=np.uint8)
+    assert raw[456] == 4
+    match, mismatch = orc.lib().orc_mask_lr(1), orc.lib().orc_mask_lr(0)
+    for i in range(5):
+        for j in range(5):
+            assert lr[i, j] == (match if i == j and i < 4 else mismatch)
+    # letter map: mask a one-letter read with every byte value; 'N' comes back exactly for code 4
+    for c in range(1, 256):
+        if c in (10, 13):
+            continue
+        b = orc.Batch([bytes([c]) * 3])
+        out = _mates(orc.mask(b, 1.0))[0]
+        assert (out == "NNN") == (codes[c] == 4), c        # (byte 255 keeps code 0: the reference's mapping loop stops at 254)
+
+
 def test_oracle_thread_invariance(golden):
     """KmerMatcher splits the query list per thread (KmerMatcher.cpp:166-194); the result must not depend on it."""
     case = "plain_paired"
