@@ -64,6 +64,7 @@ def parse_args():
     ap.add_argument("--cpu-pairs", type=int, default=0, help="read pairs of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--check", action="store_true", help="(kept for old command lines: the reference check is on by default)")
+    ap.add_argument("--mask", action="store_true", help="--mask 1: tantan low-complexity masking of the reads before extraction (k_mask_mates)")
     ap.add_argument("--no-check", action="store_true", help="skip the comparison of the GPU results with ref_harness' results")
     ap.add_argument("--check-port", action="store_true", help="also compare 20000 reads with the oracle port (liborc)")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
@@ -290,7 +291,7 @@ def write_sample_files(a, bases, offsets, lens, n_reads):
 
 
 def ref_results_path(a, n_pairs):
-    return os.path.join(a.workdir, workload_key(a), f"ref_{a.kind}_p{a.pairs}_n{n_pairs}.results.tsv")
+    return os.path.join(a.workdir, workload_key(a), f"ref_{a.kind}_p{a.pairs}_n{n_pairs}{'_mask' if a.mask else ''}.results.tsv")
 
 
 def run_cpu_reference(a, dbdir, reads, n_pairs, reps, skip):
@@ -310,6 +311,8 @@ def run_cpu_reference(a, dbdir, reads, n_pairs, reps, skip):
                     pass
         prefix = ref_results_path(a, n_pairs)[:-len(".results.tsv")]
         cmd = [harness, dbdir, prefix, str(a.seq_mode), str(threads)] + files + ["--reps", str(reps + skip), "--skip-reps", str(skip)]
+        if a.mask:      # masking lives in the reference's own KmerExtractor (which parses the files inside the timed extraction)
+            cmd += ["--mask", "1", "--ref-extractor"]
         t0 = time.time()
         out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
         if out.returncode != 0:
@@ -380,7 +383,7 @@ def workload_text(a, meta):
             "contigs": f"{a.pairs} synthetic contigs ({a.rlen[0]}-{a.rlen[1]} nt, 0.1% substitutions)"}[a.kind]
     dbk = ("syncmer" if a.syncmer else "non-syncmer") + (" legacy format-1" if a.kmer_format == 1 else "")
     return (f"{a.label}: {what} per GPU vs {meta['genomes']}-genome synthetic {dbk} DB ({meta['db_kmers']} k-mers, {meta['species']} species), "
-            f"seq-mode {a.seq_mode}" + (", s=5" if a.syncmer else ""))
+            f"seq-mode {a.seq_mode}" + (", s=5" if a.syncmer else "") + (", --mask 1" if a.mask else ""))
 
 
 def cpu_sample_pairs(a):
@@ -399,6 +402,7 @@ def algorithmic_bytes(t, sizeof_match=24):
         "k_extract<count>": nb,                                   # 1 B/base read
         "k_scan_counts": 12 * (nb // 2048 + 1),
         "k_extract": nb + 16 * nk,                                # bases read + 16 B/k-mer written (single pass)
+        "k_mask_mates": 3 * nb + 8 * nb + nb // 2,               # bases twice read + once written, a float per base written + read, scales
         "k_sort_segments": 2 * sizeof_match * nm,                 # one read + one write of the grouped matches
         "k_score_fast": sizeof_match * nm + 16 * nr,
         "k_score_finish": sizeof_match * nm // 2 + 48 * nr,       # the best species' matches (about half) + results
@@ -521,6 +525,8 @@ def run_b200(a):
     clf = mb.Classifier(dbdir, device=local, seq_mode=a.seq_mode, shard=rank, n_shards=world)
     log(f"rank {rank}: shard {rank}/{world} resident ({clf.db_kmers()} k-mers, {clf.db_words()} words) in {time.time() - t0:.1f}s")
     clf.set_profile(True)
+    if a.mask:
+        clf.set_params(mask_mode=1, mask_prob=0.9)
     sharded = ShardedClassifier(DeviceEngine(clf, device), clf.shard_bounds(), n_pairs, rank, world, fused=a.exchange == "fused") if world > 1 else None
 
     # Library batches: the whole step in one batch (configs 2, 3, 5), or several (config 4: 100k long reads hold a billion
