@@ -131,8 +131,10 @@ def main():
         out = os.path.join(work, "rep_" + name)
         os.makedirs(out, exist_ok=True)
         run(base + ["--report", out, "plain"])
+        run(base + ["--report", out, "lineage", "--lineage"])
         for f in ("classifications.tsv", "report.tsv"):
             shutil.copy(os.path.join(out, "plain_" + f), os.path.join(rep, name + "_" + f))
+        shutil.copy(os.path.join(out, "lineage_classifications.tsv"), os.path.join(rep, name + "_lineage_classifications.tsv"))
         krona = open(os.path.join(out, "plain_krona.html"), "rb").read()
         with open(os.path.join(rep, name + "_krona_tail.html"), "wb") as f:
             f.write(krona[prelude_len:])

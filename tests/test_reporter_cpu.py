@@ -45,7 +45,8 @@ def test_every_case_has_reference_reports(golden):
 
 
 @pytest.mark.parametrize("case", ["plain_paired", "sync_paired", "legacy_paired", "plain_long", "sync_long", "plain_single",
-                                  "euk_paired", "euk_long", "redund_paired", "sync4_paired", "sync6_paired", "sync4_long", "legacy_long"])
+                                  "euk_paired", "euk_long", "redund_paired", "sync4_paired", "sync6_paired", "sync4_long", "legacy_long",
+                                  "mask_paired", "mask_paired_p05", "mask_long"])
 def test_host_writers_equal_reference_reporter(golden, mb, tmp_path, case):
     rows = golden.results(case)
     res, ids, cnt = results_from_golden(mb, rows)
