@@ -585,3 +585,23 @@ def test_fastq_parsed_on_device(golden, mb, variant):
         assert n0 == 0 and nb0 == 0
     finally:
         clf.close()
+
+
+@pytest.mark.parametrize("extra", [[], ["--mask"]])
+def test_config1_sized_run_equals_reference_classes(tmp_path, extra):
+    """BASELINE configs[0] at its stated size (100 genomes x 200 kb, 100 000 read pairs) through the whole product path
+    (DB directory written in the on-disk format, C++ host, CUDA stages) and through the reference's own classes
+    (oracle/_ref/ref_harness: KmerMatcher, Taxonomer, ips4o sort; with --mask also its KmerExtractor + tantan) on the
+    same files: every read's is_classified, taxID, query length, fp32 score bits and taxID:count list must agree."""
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.exists(os.path.join(root, "oracle", "_ref", "ref_harness")):
+        pytest.skip("oracle/_ref/ref_harness was not built (it is compiled where /root/reference exists and travels with the repo)")
+    cmd = [sys.executable, os.path.join(root, "bench.py"), "--genomes", "100", "--pairs", "100000", "--len-min", "200000", "--len-max", "200000",
+           "--steps", "1", "--warmup", "3", "--no-fastq", "--workdir", str(tmp_path)] + extra
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, cwd=root)
+    assert out.returncode == 0, out.stderr[-3000:]
+    line = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+    assert line["check"] == {"against": "ref_harness", "reads": 100000, "mismatches": 0}
+    assert line["counts"]["classified"] > 90000 and line["gpu_launches"] > 0
+    assert line["cpu_baseline"]["kind"] == "reference" and line["cpu_baseline"]["same_config"] is True
