@@ -153,6 +153,19 @@ int mb_classify_batch(mb_ctx *ctx, const char *bases, size_t n_bases, const uint
 /* The same path in stages (each leaves its output resident on the device): */
 int mb_stage_reads(mb_ctx *ctx, const char *bases, size_t n_bases, const uint64_t *offsets, const uint32_t *lens,
                    uint32_t n_reads);                                   /* H2D only                      */
+/* DB-build inner loop.  Replaces, for one buffer of n target k-mers
+ * {value, taxId, speciesId} (internal ids, any order), the three steps of IndexCreator::createIndex between extraction
+ * and the files (src/commons/IndexCreator.cpp:262-280):
+ *   SORT_PARALLEL(buffer, Kmer::compareTargetKmer)         src/commons/Kmer.h:77-87
+ *   IndexCreator::filterKmers<FilterMode::DB_CREATION>     src/commons/IndexCreator.h:475-615 (equal (value, speciesId):
+ *                                                          one k-mer, taxId = LCA of the duplicates' taxa)
+ *   IndexCreator::writeTargetFilesAndSplits / getDiffIdx   src/commons/IndexCreator.cpp:811-886
+ * Outputs are the contents of the diffIdx, info and split files: diffIdx_out[cap_words], info_out[cap_kmers],
+ * splits_out[split_num] (may be NULL).  *n_words / *n_kmers always receive the sizes; MB_E_CAPACITY when a buffer is too
+ * small (n_kmers <= n, n_words <= 5 * n_kmers).  Needs mb_load_taxonomy (for the LCA); touches no staged batch. */
+int mb_build_index(mb_ctx *ctx, const uint64_t *values, const int32_t *taxids, const int32_t *species, size_t n, int split_num,
+                   uint16_t *diffIdx_out, size_t cap_words, size_t *n_words, uint32_t *info_out, size_t cap_kmers, size_t *n_kmers,
+                   mb_split *splits_out);
 /* --mask 1 on the staged batch, in place.  Replaces SeqIterator::maskLowComplexityRegions
  * (src/commons/SeqIterator.cpp:154-177: tantan::maskSequences with maxRepeatOffset 50, repeatProb 0.005, repeatEndProb
  * 0.05, decay 0.9, no gaps) as KmerExtractor::processSequence applies it to every mate (KmerExtractor.cpp:328-335).

@@ -67,7 +67,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
                "mb_prefetch_reads", "mb_stage_fastq", "mb_prefetch_fastq", "mb_alloc_host", "mb_free_host", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches",
-               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access", "mb_mask_reads"]
+               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access", "mb_mask_reads", "mb_build_index"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -138,6 +138,8 @@ _sig(_cuda, "mb_free_host", None, [vp])
 _sig(_cuda, "mb_fetch_fastq_names", C.c_int, [vp, vp, vp])
 _sig(_cuda, "mb_fetch_staged_reads", C.c_int, [vp, vp, vp, vp])
 _sig(_cuda, "mb_mask_reads", C.c_int, [vp])
+_sig(_cuda, "mb_build_index", C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_int, vp, C.c_size_t, C.POINTER(C.c_size_t), vp, C.c_size_t,
+                                          C.POINTER(C.c_size_t), vp])
 _sig(_cuda, "mb_extract_kmers_routed", C.c_int, [vp, szp])
 _sig(_cuda, "mb_take_routed_kmers", C.c_int, [vp, szp])
 _sig(_cuda, "mb_match_kmers_routed", C.c_int, [vp, szp])
@@ -266,6 +268,20 @@ class Context:
         self._ck(_cuda.mb_fetch_staged_reads(self.ctx, _ptr(bases) if n_bases else None, _ptr(offsets) if self.n_reads else None,
                                              _ptr(lens) if self.n_reads else None))
         return bases, offsets, lens
+
+    def build_index(self, values, taxids, species, split_num=4096):
+        """DB-build inner loop -> (diffIdx words u16, info u32, split table as a (split_num, 3) u64 array)."""
+        v = np.ascontiguousarray(values, dtype=np.uint64)
+        t = np.ascontiguousarray(taxids, dtype=np.int32)
+        s = np.ascontiguousarray(species, dtype=np.int32)
+        n = len(v)
+        words = np.zeros(5 * n + 8, dtype=np.uint16)
+        info = np.zeros(n + 8, dtype=np.uint32)
+        splits = np.zeros((split_num, 3), dtype=np.uint64)
+        nw, nk = C.c_size_t(0), C.c_size_t(0)
+        self._ck(_cuda.mb_build_index(self.ctx, _ptr(v), _ptr(t), _ptr(s), n, split_num, _ptr(words), len(words), C.byref(nw), _ptr(info),
+                                      len(info), C.byref(nk), _ptr(splits)))
+        return words[:nw.value].copy(), info[:nk.value].copy(), splits
 
     def mask_reads(self):
         """--mask 1 on the staged batch (tap; extract() applies it itself when mask_mode is set)."""

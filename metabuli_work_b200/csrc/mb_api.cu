@@ -16,6 +16,7 @@
 #include "mb_segsort.cuh"
 #include "mb_fastq.cuh"
 #include "mb_mask.cuh"
+#include "mb_build.cuh"
 
 #include <cuda_runtime.h>
 
@@ -894,6 +895,97 @@ int mb_mask_reads(mb_ctx *ctx) {
     if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "mb_stage_reads first");
     CK(cudaSetDevice(ctx->par.device));
     if (int rc = mask_impl(ctx)) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+// exclusive scan of u32 -> u64 (offsets[n] = total) with the three scan kernels of the FASTQ parser
+static int scan_u32(mb_ctx *ctx, const u32 *v, u64 n, u64 *out, DevBuf &sums, DevBuf &sum_off, u64 *total) {
+    const u64 st = (n + SCAN_TILE - 1) / SCAN_TILE;
+    CK(sums.ensure((st + 1) * sizeof(u32)));
+    CK(sum_off.ensure((st + 2) * sizeof(u64)));
+    k_scan_tile_sums<<<(unsigned) st, 256, 0, ctx->stream>>>(v, n, sums.as<u32>());
+    k_scan_counts<<<1, 1024, 0, ctx->stream>>>(sums.as<u32>(), sum_off.as<u64>(), (u32) st);
+    k_scan_tile_apply<<<(unsigned) st, 256, 0, ctx->stream>>>(v, n, sum_off.as<u64>(), out);
+    CK(cudaGetLastError());
+    ctx->launches += 3;
+    return read_back(ctx, sum_off.as<u64>() + st, total);
+}
+
+int mb_build_index(mb_ctx *ctx, const uint64_t *values, const int32_t *taxids, const int32_t *species, size_t n, int split_num,
+                   uint16_t *diffIdx_out, size_t cap_words, size_t *n_words, uint32_t *info_out, size_t cap_kmers, size_t *n_kmers,
+                   mb_split *splits_out) {
+    if (!ctx || !values || !taxids || !species || !n_words || !n_kmers) return MB_E_ARG;
+    if (split_num < 2) return fail(ctx, MB_E_ARG, "split_num must be at least 2");
+    if (!ctx->parent.p) return fail(ctx, MB_E_ARG, "mb_load_taxonomy first (the duplicates' taxa are folded with LCA)");
+    if (n >= (1ull << 32) * SCAN_TILE) return fail(ctx, MB_E_ARG, "too many records for one buffer");
+    CK(cudaSetDevice(ctx->par.device));
+    *n_words = *n_kmers = 0;
+    if (splits_out) memset(splits_out, 0, sizeof(mb_split) * (size_t) split_num);
+    if (n == 0) return MB_OK;
+    DevBuf in_v, in_t, in_s, rec_a, rec_b, head, pos, out_v, out_t, cnt, woff, words, sums, sum_off, probes;
+    CK(in_v.ensure(n * 8)); CK(in_t.ensure(n * 4)); CK(in_s.ensure(n * 4));
+    CK(cudaMemcpyAsync(in_v.p, values, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(in_t.p, taxids, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(in_s.p, species, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(rec_a.ensure((n + 1) * sizeof(mb_kmer)));
+    const unsigned g = (unsigned) ((n + 255) / 256);
+    KL(-100, k_build_pack<<<g, 256, 0, ctx->stream>>>(in_v.as<u64>(), in_t.as<int32_t>(), in_s.as<int32_t>(), n, rec_a.as<mb_kmer>()));
+    // compareTargetKmer orders by (value, speciesId, taxId); the taxId order inside a run of duplicates does not reach the
+    // output (the run keeps its value and species, and LCA does not depend on the order), so (value, speciesId) is sorted
+    TargetKey key;
+    int sp_bits = 1;
+    while ((1ll << sp_bits) <= (long long) ctx->max_taxid) ++sp_bits;
+    key.sp_passes = (sp_bits + 7) / 8;
+    if (int rc = radix_sort<mb_kmer, TargetKey, 16>(ctx, rec_a, rec_b, n, key, key.sp_passes + 8, -100)) return rc;
+    CK(head.ensure(n * sizeof(u32)));
+    CK(pos.ensure((n + 1) * sizeof(u64)));
+    KL(-100, k_build_heads<<<g, 256, 0, ctx->stream>>>(rec_a.as<mb_kmer>(), n, head.as<u32>()));
+    u64 uniq = 0;
+    if (int rc = scan_u32(ctx, head.as<u32>(), n, pos.as<u64>(), sums, sum_off, &uniq)) return rc;
+    *n_kmers = (size_t) uniq;
+    TaxView tv;
+    tv.parent = ctx->parent.as<int32_t>(); tv.depth = ctx->depth.as<int32_t>(); tv.species_of = ctx->species_of.as<int32_t>();
+    tv.species_rank_of = ctx->species_rank_of.as<int32_t>(); tv.max_taxid = ctx->max_taxid; tv.node0_taxid = ctx->node0;
+    tv.eukaryota = ctx->euk;
+    tv.node = ctx->tax_node.as<u64>();
+    CK(out_v.ensure((uniq + 1) * 8)); CK(out_t.ensure((uniq + 1) * 4));
+    KL(-100, k_build_reduce<<<g, 256, 0, ctx->stream>>>(rec_a.as<mb_kmer>(), n, head.as<u32>(), pos.as<u64>(), tv, out_v.as<u64>(), out_t.as<u32>()));
+    const unsigned gu = (unsigned) ((uniq + 255) / 256);
+    CK(cnt.ensure(uniq * sizeof(u32)));
+    CK(woff.ensure((uniq + 2) * sizeof(u64)));
+    KL(-100, k_build_wordcount<<<gu, 256, 0, ctx->stream>>>(out_v.as<u64>(), uniq, cnt.as<u32>()));
+    u64 nw = 0;
+    if (int rc = scan_u32(ctx, cnt.as<u32>(), uniq, woff.as<u64>(), sums, sum_off, &nw)) return rc;
+    CK(cudaMemcpyAsync(woff.as<u64>() + uniq, &nw, sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));     // woff[uniq] = total
+    *n_words = (size_t) nw;
+    if (uniq > cap_kmers || nw > cap_words) return fail(ctx, MB_E_CAPACITY, "output buffers too small (sizes returned in n_words / n_kmers)");
+    if (!diffIdx_out || !info_out) return fail(ctx, MB_E_ARG, "null output");
+    CK(words.ensure((nw + 8) * sizeof(u16)));
+    KL(-100, k_build_encode<<<gu, 256, 0, ctx->stream>>>(out_v.as<u64>(), uniq, woff.as<u64>(), words.as<u16>()));
+    CK(cudaMemcpyAsync(diffIdx_out, words.p, nw * sizeof(u16), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(info_out, out_t.p, uniq * sizeof(u32), cudaMemcpyDeviceToHost, ctx->stream));
+    if (splits_out) {
+        const u64 size_of_split = uniq / (u64) (split_num - 1);
+        CK(probes.ensure((size_t) split_num * sizeof(SplitProbe)));
+        KL(-100, k_build_splits<<<(split_num + 255) / 256, 256, 0, ctx->stream>>>(out_v.as<u64>(), uniq, woff.as<u64>(), size_of_split, split_num,
+                                                                                   probes.as<SplitProbe>()));
+        std::vector<SplitProbe> pr((size_t) split_num);
+        CK(cudaMemcpyAsync(pr.data(), probes.p, pr.size() * sizeof(SplitProbe), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        // the reference's state machine has ONE pending flag: a threshold reached before the previous one found its
+        // amino-acid change merges with it, so equal answers of consecutive thresholds are one split
+        int idx = 1;
+        u64 last_j = ~0ull;
+        for (int os = 1; os < split_num; ++os) {
+            if (pr[(size_t) os].j == ~0ull || pr[(size_t) os].j == last_j) continue;
+            last_j = pr[(size_t) os].j;
+            splits_out[idx].ADkmer = pr[(size_t) os].adkmer;
+            splits_out[idx].diffIdxOffset = pr[(size_t) os].words_through;
+            splits_out[idx].infoIdxOffset = pr[(size_t) os].j + 1;
+            ++idx;
+        }
+    }
     CK(cudaStreamSynchronize(ctx->stream));
     return MB_OK;
 }

@@ -414,3 +414,4 @@ int32_t orc_tax_at_rank(const orc_db *db, int32_t t, const char *rank) { return 
 #include "orc_score.inc"
 #include "orc_io.inc"
 #include "orc_mask.inc"
+#include "orc_build.inc"

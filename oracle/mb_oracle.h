@@ -139,6 +139,11 @@ int orc_write_report(const orc_db *db, const char *path, const orc_read_result *
 int orc_write_db_files(const char *dbdir, const uint64_t *values, const uint32_t *taxids, size_t n,
                        int split_num, int kmer_format);
 
+/* ---- DB-build inner loop (orc_build.inc): sort, (value, species) duplicates folded with LCA, diffIdx / info / split written.
+ * db supplies the taxonomy (any directory with a taxonomyDB opened by orc_db_open).  Returns the number of DB k-mers. */
+int64_t orc_build_index(const orc_db *db, const uint64_t *values, const int32_t *taxids, const int32_t *species, size_t n,
+                        int split_num, int kmer_format, const char *dbdir);
+
 /* ---- --mask 1: tantan low-complexity masking of every mate in place (orc_mask.inc) ----
  * seqs: packed bases; mate m at off[m], len[m] characters; probs_out (may be NULL): repeat probability per base. */
 void orc_mask_sequences(char *seqs, const uint64_t *off, const uint32_t *len, uint32_t n_mates, float mask_prob, float *probs_out);

@@ -89,6 +89,8 @@ def lib():
         L.orc_write_report.argtypes = [vp, C.c_char_p, vp, u32]
         L.orc_write_db_files.restype = C.c_int
         L.orc_write_db_files.argtypes = [C.c_char_p, vp, vp, sz, C.c_int, C.c_int]
+        L.orc_build_index.restype = i64
+        L.orc_build_index.argtypes = [vp, vp, vp, vp, sz, C.c_int, C.c_int, C.c_char_p]
         L.orc_mask_sequences.argtypes = [vp, vp, vp, u32, C.c_float, vp]
         L.orc_mask_lr.restype = C.c_double
         L.orc_mask_lr.argtypes = [C.c_int]
@@ -160,6 +162,17 @@ class Batch:
                 pos += len(s)
         self.seqs = np.frombuffer(b"".join(chunks) + b"\0" * 8, dtype=np.uint8).copy()
         self.off, self.len = off, ln
+
+
+def build_index(db, values, taxids, species, dbdir, split_num=4096, kmer_format=2):
+    """DB-build inner loop: writes dbdir/{diffIdx,info,split}; -> number of DB k-mers."""
+    v = np.ascontiguousarray(values, dtype=np.uint64)
+    t = np.ascontiguousarray(taxids, dtype=np.int32)
+    s = np.ascontiguousarray(species, dtype=np.int32)
+    os.makedirs(dbdir, exist_ok=True)
+    n = lib().orc_build_index(db.h, _ptr(v), _ptr(t), _ptr(s), len(v), split_num, kmer_format, dbdir.encode())
+    assert n >= 0
+    return int(n)
 
 
 def mask(batch, mask_prob=0.9, want_probs=False):

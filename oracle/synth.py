@@ -60,8 +60,10 @@ def target_kmers(p, seq, block=1500, seed=0):
     return k["value"][keep]
 
 
-def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096, seed=7, skip_redundancy=1):
-    """indir: output of make_inputs.py. Returns number of DB k-mers."""
+def target_records(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, seed=7, max_genomes=None):
+    """The raw target k-mers of the genomes under indir as IndexCreator's buffer holds them before the sort: value, external
+    tax id, internal tax id, internal species id per k-mer (+ the genomes' tax ids, the external->internal map and an lca
+    function over external ids).  dbdir receives taxonomyDB / tax_map.tsv (ref_mkdb)."""
     os.makedirs(dbdir, exist_ok=True)
     subprocess.check_call([REF_MKDB, os.path.join(indir, "taxdump"), dbdir], stdout=subprocess.DEVNULL)
     ext2int = {}
@@ -103,6 +105,8 @@ def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096,
     genome_tax = []
     with open(os.path.join(indir, "fasta.list")) as f:
         paths = [l.strip() for l in f if l.strip()]
+    if max_genomes:
+        paths = paths[:max_genomes]
     for gi, path in enumerate(paths):
         acc = os.path.basename(path).split(".")[0]
         t = acc2tax[acc]
@@ -122,6 +126,12 @@ def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096,
     s_int = dict(zip(uniq_s.tolist(), to_int(uniq_s).tolist()))
     ti = np.array([t_int[x] for x in uniq_t])[np.searchsorted(uniq_t, t)]
     si = np.array([s_int[x] for x in uniq_s])[np.searchsorted(uniq_s, s)]
+    return v, t, ti, si, genome_tax, ext2int, lca
+
+
+def build_db(indir, dbdir, syncmer=0, kmer_format=2, smer_len=5, split_num=4096, seed=7, skip_redundancy=1):
+    """indir: output of make_inputs.py. Returns number of DB k-mers."""
+    v, t, ti, si, genome_tax, ext2int, lca = target_records(indir, dbdir, syncmer, kmer_format, smer_len, seed)
     order = np.lexsort((ti, si, v))
     v, t, ti, si = v[order], t[order], ti[order], si[order]
     # group by (value, species): one entry each, tax id = LCA of the group's tax ids

@@ -136,3 +136,15 @@ def dense_taxonomy(db):
         depth[t] = d
     node0 = 1
     return parent, depth, species_of, species_rank_of, mx, node0, L.orc_tax_eukaryota(db.h)
+
+
+def build_edge_records(taxid, species):
+    """Target records that stress the DB writer: values far apart (five-word deltas), and one amino-acid group so large that
+    several split thresholds fall inside it (the reference's writer has one pending flag: they share a split).  taxid /
+    species: the committed build_input columns, sampled for plausible taxa.  Deterministic."""
+    rng = np.random.default_rng(5)
+    big = rng.integers(0, 1 << 63, 5000, dtype=np.uint64) << np.uint64(1)
+    grp = (np.uint64(0x123456789A) << np.uint64(24)) | rng.integers(0, 1 << 24, 20000, dtype=np.uint64)
+    vv = np.concatenate([big, grp])
+    pick = rng.integers(0, len(taxid), len(vv))
+    return vv, np.ascontiguousarray(taxid[pick]), np.ascontiguousarray(species[pick])

@@ -152,6 +152,51 @@ def test_mask_on_device(golden, mb, tmp_path, case):
             assert open(os.path.join(out, job + "_" + f), "rb").read() == open(os.path.join(rep, case + "_" + f), "rb").read(), (job, f)
 
 
+@pytest.mark.parametrize("splits", [64, 4096])
+def test_build_index_on_device(golden, mb, tmp_path, splits):
+    """DB-build inner loop (csrc/mb_build.cuh, mb_build_index): diffIdx / info / split for the committed target records are
+    the files the REFERENCE's own sort + filterKmers<DB_CREATION> + writeTargetFilesAndSplits wrote (digests from
+    oracle/_ref/ref_buildidx, tests/golden/make_golden4.py), and equal the oracle's byte for byte; edge cases: one record,
+    all records equal, fewer k-mers than splits."""
+    import hashlib
+    import json
+    want = json.load(open(os.path.join(helpers.DATA, "build_digests.json")))[f"splits{splits}"]
+    rec = np.load(os.path.join(helpers.DATA, "build_input.npz"))
+    clf = mb.Classifier(golden.dbdir("plain_paired"), seq_mode=2)
+    db = orc.Db(golden.dbdir("plain_paired"))
+    try:
+        words, info, spl = clf.build_index(rec["value"], rec["taxid"], rec["species"], split_num=splits)
+        assert len(info) == want["db_kmers"] and 2 * len(words) == want["diffIdx_bytes"]
+        assert hashlib.sha256(words.tobytes()).hexdigest() == want["diffIdx_sha256"]
+        assert hashlib.sha256(info.tobytes()).hexdigest() == want["info_sha256"]
+        assert hashlib.sha256(spl.tobytes()).hexdigest() == want["split_sha256"]
+
+        def same_as_oracle(v, t, s, k, tag):
+            d = str(tmp_path / tag)
+            n = orc.build_index(db, v, t, s, d, split_num=k)
+            w, i, sp = clf.build_index(v, t, s, split_num=k)
+            assert len(i) == n, tag
+            assert w.tobytes() == open(d + "/diffIdx", "rb").read(), tag
+            assert i.tobytes() == open(d + "/info", "rb").read(), tag
+            assert sp.tobytes() == open(d + "/split", "rb").read(), tag
+        v, t, s = rec["value"], rec["taxid"], rec["species"]
+        same_as_oracle(v[:1], t[:1], s[:1], splits, "one")
+        same_as_oracle(np.repeat(v[:1], 1000), t[:1000], np.repeat(s[:1], 1000), splits, "all_equal")
+        same_as_oracle(v[:40], t[:40], s[:40], splits, "few")
+        # values far apart (five-word deltas) and a giant amino-acid group swallowing several split thresholds: the digests
+        # are the reference's (13 of the 63 split entries are used: thresholds inside the giant group share one)
+        ev, et, es = helpers.build_edge_records(t, s)
+        same_as_oracle(ev, et, es, 64, "wide_and_giant")
+        w, i, sp = clf.build_index(ev, et, es, split_num=64)
+        edge = json.load(open(os.path.join(helpers.DATA, "build_digests.json")))["edge_splits64"]
+        assert (hashlib.sha256(w.tobytes()).hexdigest(), hashlib.sha256(i.tobytes()).hexdigest(), hashlib.sha256(sp.tobytes()).hexdigest()) == \
+            (edge["diffIdx_sha256"], edge["info_sha256"], edge["split_sha256"])
+        assert int((sp[:, 0] != 0).sum()) == edge["used_split_entries"]
+    finally:
+        clf.close()
+        db.close()
+
+
 @pytest.mark.parametrize("bits", [24, 32, 40])
 def test_kmer_sort_bits(golden, mb, bits):
     """The join result does not depend on how many leading amino-acid bits the query sort orders."""

@@ -82,6 +82,48 @@ def test_mask_likelihood_ratios_are_the_reference_matrix():
         assert (out == "NNN") == (codes[c] == 4), c        # (byte 255 keeps code 0: the reference's mapping loop stops at 254)
 
 
+def _sha(b):
+    import hashlib
+    return hashlib.sha256(bytes(b)).hexdigest()
+
+
+@pytest.mark.parametrize("splits", [64, 4096])
+def test_oracle_build_index_matches_reference(golden, tmp_path, splits):
+    """DB-build inner loop (tests/golden/make_golden4.py): the files the oracle writes for the committed target records
+    equal the files written by the REFERENCE's own sort + IndexCreator::filterKmers<DB_CREATION> +
+    IndexCreator::writeTargetFilesAndSplits (oracle/_ref/ref_buildidx), by digest; the split table with 64 entries byte
+    for byte."""
+    import json
+    want = json.load(open(helpers.DATA + "/build_digests.json"))
+    rec = np.load(helpers.DATA + "/build_input.npz")
+    assert len(rec["value"]) == want["records"]
+    db = orc.Db(golden.dbdir("plain_paired"))
+    n = orc.build_index(db, rec["value"], rec["taxid"], rec["species"], str(tmp_path), split_num=splits)
+    db.close()
+    w = want[f"splits{splits}"]
+    assert n == w["db_kmers"]
+    for f in ("diffIdx", "info", "split"):
+        assert _sha(open(tmp_path / f, "rb").read()) == w[f + "_sha256"], f
+    if splits == 64:
+        assert open(tmp_path / "split", "rb").read() == open(helpers.DATA + "/build_split64.bin", "rb").read()
+    if splits == 64:
+        ev, et, es = helpers.build_edge_records(rec["taxid"], rec["species"])
+        db = orc.Db(golden.dbdir("plain_paired"))
+        d = str(tmp_path / "edge")
+        assert orc.build_index(db, ev, et, es, d, split_num=64) == want["edge_splits64"]["db_kmers"]
+        db.close()
+        for f in ("diffIdx", "info", "split"):
+            assert _sha(open(d + "/" + f, "rb").read()) == want["edge_splits64"][f + "_sha256"], ("edge", f)
+    # the built files are a database: decoding gives a sorted stream of n k-mers
+    import shutil
+    for f in ("taxonomyDB", "taxID_list", "db.parameters"):
+        shutil.copy(golden.dbdir("plain_paired") + "/" + f, tmp_path / f)
+    built = orc.Db(str(tmp_path))
+    v, t = built.decode()
+    assert len(v) == n and np.all(v[1:] >= v[:-1])
+    built.close()
+
+
 def test_oracle_thread_invariance(golden):
     """KmerMatcher splits the query list per thread (KmerMatcher.cpp:166-194); the result must not depend on it."""
     case = "plain_paired"
