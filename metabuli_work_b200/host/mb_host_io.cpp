@@ -385,17 +385,28 @@ struct BatchSlot {
     std::vector<uint32_t> nameLen;
 };
 
-// plain (not gzip) four-line FASTQ in a regular file?  Decided on the first bytes: '@' starts the file and the third line
-// starts with '+'.  bytesPerRecord: average over the records of the first 64 KB.
-static bool looksLikePlainFastq(const std::string &path, size_t &bytesPerRecord, size_t &fileSize) {
+// Four-line FASTQ in a regular file, plain or gzip?  Decided on the first (decompressed) bytes: '@' starts the file and the
+// third line starts with '+'.  bytesPerRecord: average over the records of the first 64 KB of text.
+static bool looksLikeFastq(const std::string &path, size_t &bytesPerRecord, size_t &fileSize, bool &gz) {
     struct stat st;
     if (stat(path.c_str(), &st) != 0 || !S_ISREG(st.st_mode)) return false;
     fileSize = (size_t) st.st_size;
-    FILE *fp = fopen(path.c_str(), "rb");
-    if (!fp) return false;
     static char head[1 << 16];
-    const size_t n = fread(head, 1, sizeof(head), fp);
-    fclose(fp);
+    size_t n = 0;
+    {
+        FILE *fp = fopen(path.c_str(), "rb");
+        if (!fp) return false;
+        n = fread(head, 1, sizeof(head), fp);
+        fclose(fp);
+    }
+    gz = n >= 2 && (unsigned char) head[0] == 0x1f && (unsigned char) head[1] == 0x8b;
+    if (gz) {
+        gzFile g = gzopen(path.c_str(), "rb");
+        if (!g) return false;
+        const int got = gzread(g, head, sizeof(head));
+        gzclose(g);
+        n = got > 0 ? (size_t) got : 0;
+    }
     if (n < 4 || head[0] != '@') return false;
     size_t line = 0, lastRecordEnd = 0;
     bool plus = false;
@@ -424,10 +435,13 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     for (int i = 0; i < kSlots; ++i) freeSlots.push(i);
 
     // Plain FASTQ goes to the GPU as raw text (mb_stage_fastq: lines, records and packing are found on the device; the host
-    // only cuts the read names out at the spans it gets back).  FASTA, multi-line or gzip input takes the host reader.
+    // only cuts the read names out at the spans it gets back).  Gzip files are inflated by the reader threads (zlib, one
+    // thread per file: a gzip stream cannot be inflated in parallel) and their TEXT takes the same road.  FASTA and
+    // multi-line FASTQ take the host reader.
     size_t bpr[2] = {0, 0}, fileSize[2] = {0, 0};
-    const bool deviceParse = !getenv("MB_HOST_PARSE") && looksLikePlainFastq(inputs[0], bpr[0], fileSize[0]) &&
-                             (!paired || looksLikePlainFastq(inputs[1], bpr[1], fileSize[1]));
+    bool isGz[2] = {false, false};
+    const bool deviceParse = !getenv("MB_HOST_PARSE") && looksLikeFastq(inputs[0], bpr[0], fileSize[0], isGz[0]) &&
+                             (!paired || looksLikeFastq(inputs[1], bpr[1], fileSize[1], isGz[1]));
     // A chunk holds about --batch-reads records; the batch is bounded by the chunk's bytes, not by a record count, so that
     // what a batch leaves over is an incomplete record and not a pile of whole ones.
     std::atomic<size_t> chunkWant[2];
@@ -450,42 +464,68 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
         // starts before the database is resident: page-locking the buffers and reading the first chunk overlap the DB load
         reader = std::thread([&] {
             int fd[2] = {-1, -1};
+            gzFile gzf[2] = {nullptr, nullptr};
             size_t pos[2] = {0, 0};
+            bool srcEof[2] = {false, false};
             for (int f = 0; f < nFiles; ++f) {
-                fd[f] = ::open(inputs[(size_t) f].c_str(), O_RDONLY);
-                if (fd[f] < 0) { readerErr = "cannot open " + inputs[(size_t) f]; readerFailed = true; }
+                if (isGz[f]) {
+                    gzf[f] = gzopen(inputs[(size_t) f].c_str(), "rb");
+                    if (gzf[f]) gzbuffer(gzf[f], 1u << 20);
+                } else fd[f] = ::open(inputs[(size_t) f].c_str(), O_RDONLY);
+                if (fd[f] < 0 && !gzf[f]) { readerErr = "cannot open " + inputs[(size_t) f]; readerFailed = true; }
             }
+            // one file's share of a slot: `want` bytes of text behind the reserve (plain: pread by several threads; gzip: inflate)
+            auto fillOne = [&](int si, int f) {
+                TextBuf &tb = slots[si].f[f];
+                const size_t want = isGz[f] ? (srcEof[f] ? 0 : (size_t) chunkWant[f]) : std::min<size_t>(chunkWant[f], fileSize[f] - pos[f]);
+                if (!tb.pin) {       // first use of this slot (a file that fits one chunk never touches the other slots)
+                    tb.cap = reserve[f] + (isGz[f] ? (size_t) chunkWant[f] : std::min<size_t>(chunkWant[f], fileSize[f])) + 64;
+                    const auto tp = clk::now();
+                    tb.pin = static_cast<char *>(mb_alloc_host(tb.cap));
+                    if (f == 0) pinBusy += secondsSince(tp);
+                    tb.pinned = tb.pin != nullptr;
+                    if (!tb.pin) tb.pin = static_cast<char *>(malloc(tb.cap));
+                    if (!tb.pin) { if (!readerFailed.exchange(true)) readerErr = "out of host memory for the read buffers"; return; }
+                }
+                if (reserve[f] + want + 64 <= tb.cap) tb.base = tb.pin;
+                else { tb.spill.resize(reserve[f] + want + 64); tb.base = tb.spill.data(); }
+                tb.start = reserve[f];
+                size_t got = 0;
+                if (isGz[f]) {
+                    while (got < want) {
+                        const int r = gzread(gzf[f], tb.data() + got, (unsigned) std::min<size_t>(want - got, 1u << 30));
+                        if (r < 0) { if (!readerFailed.exchange(true)) readerErr = "gzip error in " + inputs[(size_t) f]; return; }
+                        if (r == 0) { srcEof[f] = true; break; }
+                        got += (size_t) r;
+                    }
+                    if (!srcEof[f] && gzeof(gzf[f])) srcEof[f] = true;
+                } else {
+                    got = want;
+                    if (want && !preadParallel(fd[f], tb.data(), want, pos[f], ioT)) { if (!readerFailed.exchange(true)) readerErr = "short read on " + inputs[(size_t) f]; return; }
+                    srcEof[f] = pos[f] + want >= fileSize[f];
+                }
+                pos[f] += got;
+                tb.fill = got;
+                tb.eof = srcEof[f];
+            };
             int si;
             while (!readerFailed && freeSlots.pop(si)) {
                 const auto tr = clk::now();
-                bool allEof = true;
-                for (int f = 0; f < nFiles; ++f) {
-                    TextBuf &tb = slots[si].f[f];
-                    const size_t want = std::min<size_t>(chunkWant[f], fileSize[f] - pos[f]);
-                    if (!tb.pin) {       // first use of this slot (a file that fits one chunk never touches the other slots)
-                        tb.cap = reserve[f] + std::min<size_t>(chunkWant[f], fileSize[f]) + 64;
-                        const auto tp = clk::now();
-                        tb.pin = static_cast<char *>(mb_alloc_host(tb.cap));
-                        pinBusy += secondsSince(tp);
-                        tb.pinned = tb.pin != nullptr;
-                        if (!tb.pin) tb.pin = static_cast<char *>(malloc(tb.cap));
-                        if (!tb.pin) { readerErr = "out of host memory for the read buffers"; readerFailed = true; break; }
-                    }
-                    if (reserve[f] + want + 64 <= tb.cap) tb.base = tb.pin;
-                    else { tb.spill.resize(reserve[f] + want + 64); tb.base = tb.spill.data(); }
-                    tb.start = reserve[f];
-                    tb.fill = want;
-                    if (want && !preadParallel(fd[f], tb.data(), want, pos[f], ioT)) { readerErr = "short read on " + inputs[(size_t) f]; readerFailed = true; }
-                    pos[f] += want;
-                    tb.eof = pos[f] >= fileSize[f];
-                    allEof = allEof && tb.eof;
+                if (nFiles == 2 && (isGz[0] || isGz[1])) {      // the two inflations run side by side
+                    std::thread second(fillOne, si, 1);
+                    fillOne(si, 0);
+                    second.join();
+                } else {
+                    for (int f = 0; f < nFiles; ++f) fillOne(si, f);
                 }
+                bool allEof = true;
+                for (int f = 0; f < nFiles; ++f) allEof = allEof && slots[si].f[f].eof;
                 readBusy += secondsSince(tr);
                 filled.push(si);
-                if (allEof) break;
+                if (allEof || readerFailed) break;
             }
             filled.close();
-            for (int f = 0; f < nFiles; ++f) if (fd[f] >= 0) ::close(fd[f]);
+            for (int f = 0; f < nFiles; ++f) { if (fd[f] >= 0) ::close(fd[f]); if (gzf[f]) gzclose(gzf[f]); }
         });
     }
     auto stopReader = [&] {

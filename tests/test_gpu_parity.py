@@ -349,6 +349,21 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
         subprocess.check_call([mb.CLI, "classify", "--seq-mode", "3", os.path.join(data, "long.fa"), golden.dbdir(c), out, c])
         for f in ("classifications.tsv", "report.tsv"):
             assert rd(os.path.join(out, c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, f)
+    # gzip input: inflated by the reader threads, the text parsed on the device like a plain file (several chunks), and
+    # through the host reader
+    import gzip
+    gz = []
+    for src in (r1, r2):
+        dst = os.path.join(out, os.path.basename(src) + ".gz")
+        with open(src, "rb") as fi, gzip.open(dst, "wb") as fo:
+            fo.write(fi.read())
+        gz.append(dst)
+    for job, env, extra in (("gz", {}, []), ("gz_chunks", {}, ["--batch-reads", "150"]), ("gz_host", {"MB_HOST_PARSE": "1"}, [])):
+        log = subprocess.run([mb.CLI, "classify"] + gz + [golden.dbdir(case), out, job] + extra, env=dict(os.environ, **env), check=True,
+                             capture_output=True, text=True).stdout
+        assert ("parsed on the GPU" in log) == (job != "gz_host")
+        for f in ("classifications.tsv", "report.tsv"):
+            assert rd(os.path.join(out, job + "_" + f)) == rd(os.path.join(rep, case + "_" + f)), (job, f)
     # several GPUs in one process (host/mb_host_multi.cpp): DB shards per context, reads split over them, k-mers and matches
     # exchanged through peer stores.  Listing device 0 more than once runs the same code on one GPU.
     for c, mode, gl, extra in (("plain_paired", 2, "0,0", ["--batch-reads", "150"]), ("sync_paired", 2, "0,0,0", []),
