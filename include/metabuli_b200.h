@@ -75,7 +75,10 @@ typedef struct {
                                  offers the final DB k-mer as a candidate, KmerMatcher.cpp:363-406) */
     int32_t kmer_sort_bits;   /* leading amino-acid bits the query k-mer sort orders: 24, 32 or 40; 21 (format 2 only) =
                                  the re-coded key: five leading residues as a base-21 number plus two bits of the
-                                 sixth, 24 bits in all.  0 = default (21 for format 2, 32 for format 1).
+                                 sixth, 24 bits in all (three passes); 31 (format 2 only) = seven residues as a base-21
+                                 number plus one bit of the eighth, 32 bits (four passes).  0 = default (format 2: 21,
+                                 or 31 when the resident database stream has more than four words per query k-mer of the
+                                 first large batch; format 1: 32).
                                  The join only needs the queries of a DB block to be contiguous, not ordered, so
                                  fewer bits = fewer radix passes; blocks re-check the full amino-acid part.        */
     int32_t mask_mode;        /* --mask (0): 1 = tantan low-complexity masking of every mate before extraction

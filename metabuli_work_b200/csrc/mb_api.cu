@@ -159,6 +159,7 @@ struct mb_ctx {
     std::vector<KSample> samples;     // event pairs of the current batch
     size_t n_samples = 0;
     bool reads_masked = false;         // --mask 1 has been applied to the staged bases
+    bool fine_key = false, key_decided = false;    // seven-residue sort key: decided by the first large batch after mb_load_db
     DevBuf mask_probs, mask_scales;
     DevBuf read_order, order_hist;     // short-read scorers: reads by match count
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
@@ -351,10 +352,11 @@ static int check_params(const mb_params *p, std::string &err) {
     if (p->kmer_format != 1 && p->kmer_format != 2) { err = "kmer_format must be 1 or 2"; return MB_E_ARG; }
     if (p->seq_mode < 1 || p->seq_mode > 3) { err = "seq_mode must be 1, 2 or 3"; return MB_E_ARG; }
     if (p->syncmer && (p->smer_len < 1 || p->smer_len > 7)) { err = "smer_len must be in 1..7"; return MB_E_ARG; }
-    if (p->kmer_sort_bits != 0 && p->kmer_sort_bits != 21 && p->kmer_sort_bits != 24 && p->kmer_sort_bits != 32 && p->kmer_sort_bits != 40) {
-        err = "kmer_sort_bits must be 0, 21, 24, 32 or 40"; return MB_E_ARG;
+    if (p->kmer_sort_bits != 0 && p->kmer_sort_bits != 21 && p->kmer_sort_bits != 31 && p->kmer_sort_bits != 24 && p->kmer_sort_bits != 32 &&
+        p->kmer_sort_bits != 40) {
+        err = "kmer_sort_bits must be 0, 21, 31, 24, 32 or 40"; return MB_E_ARG;
     }
-    if (p->kmer_sort_bits == 21 && p->kmer_format != 2) { err = "kmer_sort_bits 21 (re-coded key) needs kmer_format 2"; return MB_E_ARG; }
+    if ((p->kmer_sort_bits == 21 || p->kmer_sort_bits == 31) && p->kmer_format != 2) { err = "kmer_sort_bits 21 / 31 (re-coded keys) need kmer_format 2"; return MB_E_ARG; }
     if (p->accession_level != 0) { err = "accession_level != 0 is not on this path"; return MB_E_ARG; }
     if (p->mask_mode != 0 && p->mask_mode != 1) { err = "mask_mode must be 0 or 1"; return MB_E_ARG; }
     if (p->mask_mode && !(p->mask_prob > 0.f && p->mask_prob <= 1.f)) { err = "mask_prob must be in (0, 1]"; return MB_E_ARG; }
@@ -442,10 +444,15 @@ static DbView db_view(const mb_ctx *ctx, bool for_index) {
 static SortT planned_sort_t(const mb_ctx *ctx) {
     static const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;      // tuning knob
     int bits = env_bits ? env_bits : ctx->par.kmer_sort_bits;
-    if (bits == 0 || (bits == 21 && ctx->par.kmer_format != 2)) bits = ctx->par.kmer_format == 2 ? 21 : 32;
+    if ((bits == 21 || bits == 31) && ctx->par.kmer_format != 2) bits = 0;
+    // default: format 2 takes a re-coded key — five residues (three passes), or seven (four passes) when the database
+    // stream is long against the batch (fine_key, below): the better the queries are ordered, the faster the join runs
+    // (measured: k_match 33.0 -> 25.1 ms at configs[2] with 1.32 G DB k-mers for 3.4 ms of extra pass, step 94.9 -> 90.3 ms;
+    // 8.85 -> 7.85 ms at configs[1], where the extra pass costs 2.8 ms and the five-residue key stays)
+    if (bits == 0) bits = ctx->par.kmer_format == 2 ? (ctx->fine_key ? 31 : 21) : 32;
     SortT t;
-    t.mode = bits == 21 ? 1 : 0;
-    t.shift = bits == 21 ? 0 : 40 - bits;
+    t.mode = bits == 21 ? 1 : bits == 31 ? 2 : 0;
+    t.shift = t.mode ? 0 : 40 - bits;
     return t;
 }
 
@@ -520,6 +527,7 @@ int mb_load_db(mb_ctx *ctx, const uint16_t *diffIdx, size_t n_words, const uint3
     CK(cudaMemcpyAsync(ctx->raw_kidx.p, kidx.data(), n_raw * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->raw_vbefore.p, vbefore.data(), n_raw * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    ctx->fine_key = ctx->key_decided = false;
     if (int rc = build_units(ctx, planned_sort_t(ctx))) return rc;
     ctx->times.db_words = n_words;
     ctx->times.db_kmers = n_kmers;
@@ -1052,20 +1060,31 @@ int mb_sort_kmers(mb_ctx *ctx) {
     // The join needs the queries of one DB block contiguous, not ordered (every query looks its group up in the decoded
     // block): ordering the leading `bits` of the 40 amino-acid bits takes bits/8 passes instead of 5, and for format 2
     // the re-coded 24-bit key (SortT mode 1, mb_common.cuh; kmer_sort_bits 21) resolves 5.6 residues in 3 passes.
+    // the first batch of at least a million k-mers after mb_load_db decides the default key for this database (kept, so
+    // that the unit index is not rebuilt from batch to batch): seven residues when the DB stream has more than four words
+    // per query k-mer
+    if (!ctx->key_decided && ctx->n_kmers >= (1u << 20)) {
+        ctx->key_decided = true;
+        ctx->fine_key = ctx->n_words > 4 * ctx->n_kmers;
+    }
     ctx->sort_t = planned_sort_t(ctx);
-    const bool packed = ctx->sort_t.mode == 1;
-    const int bits = packed ? 21 : 40 - ctx->sort_t.shift;
-    if (bits != 21 && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 24, 32 or 40");
+    const int mode = ctx->sort_t.mode;
+    const int bits = mode ? 0 : 40 - ctx->sort_t.shift;
+    if (!mode && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 31, 24, 32 or 40");
     KmerKey key;
     key.first_bit = 24 + ctx->sort_t.shift;
-    const int passes = packed ? 3 : bits / 8;
+    const int passes = mode == 1 ? 3 : mode == 2 ? 4 : bits / 8;
     static const int k_items = getenv("MB_KSORT_ITEMS") ? atoi(getenv("MB_KSORT_ITEMS")) : 16;     // tuning knob
     int rc = 0;
-    if (packed) {
+    if (mode == 1) {
         KmerKeyPacked pk;
         if (k_items == 8) rc = radix_sort<mb_kmer, KmerKeyPacked, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
         else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKeyPacked, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
         else rc = radix_sort<mb_kmer, KmerKeyPacked, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
+    }
+    else if (mode == 2) {
+        KmerKeyPacked7 pk;
+        rc = radix_sort<mb_kmer, KmerKeyPacked7, 16>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, pk, passes, KID_KSORT_HIST, &ctx->kmers_seg);
     }
     else if (k_items == 8) rc = radix_sort<mb_kmer, KmerKey, 8>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
     else if (k_items == 12) rc = radix_sort<mb_kmer, KmerKey, 12>(ctx, ctx->kmers_a, ctx->kmers_b, ctx->n_kmers, key, passes, KID_KSORT_HIST, &ctx->kmers_seg);
@@ -1853,6 +1872,7 @@ int noalloc_setup(mb_ctx *ctx, NoallocScratch **out) {
         constexpr int smem = (int) radix_pass_smem<mb_kmer, NA_ITEMS>();
         CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKey, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKeyPacked, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKeyPacked7, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         d.scratch = reinterpret_cast<NoallocScratch *>(p);
         d.ready = true;
     }
@@ -1901,19 +1921,21 @@ extern "C" int mb_sort_kmers_noalloc(mb_ctx *ctx, void *d_kmers, void *d_tmp, si
     NoallocScratch *sc = nullptr;
     if (int rc = noalloc_setup(ctx, &sc)) return rc;
     cudaStream_t st = stream ? (cudaStream_t) stream : ctx->stream;
-    // the key of mb_sort_kmers (kmer_sort_bits; the MB_KSORT_BITS knob is honoured there and here alike)
-    const int env_bits = getenv("MB_KSORT_BITS") ? atoi(getenv("MB_KSORT_BITS")) : 0;
-    int bits = env_bits ? env_bits : ctx->par.kmer_sort_bits;
-    if (bits == 0 || (bits == 21 && ctx->par.kmer_format != 2)) bits = ctx->par.kmer_format == 2 ? 21 : 32;
-    if (bits != 21 && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 24, 32 or 40");
+    // the key of mb_sort_kmers (kmer_sort_bits, database size; the MB_KSORT_BITS knob is honoured there and here alike)
+    const SortT plan = planned_sort_t(ctx);
+    const int bits = plan.mode ? 0 : 40 - plan.shift;
+    if (!plan.mode && bits != 24 && bits != 32 && bits != 40) return fail(ctx, MB_E_ARG, "MB_KSORT_BITS must be 21, 31, 24, 32 or 40");
     mb_kmer *a = reinterpret_cast<mb_kmer *>(d_kmers), *b = reinterpret_cast<mb_kmer *>(d_tmp);
     int rc;
-    if (bits == 21) {
+    if (plan.mode == 1) {
         KmerKeyPacked pk;
         rc = noalloc_sort(ctx, st, sc, a, b, (u64) n, pk, 3);
+    } else if (plan.mode == 2) {
+        KmerKeyPacked7 pk;
+        rc = noalloc_sort(ctx, st, sc, a, b, (u64) n, pk, 4);
     } else {
         KmerKey key;
-        key.first_bit = 24 + (40 - bits);
+        key.first_bit = 24 + plan.shift;
         rc = noalloc_sort(ctx, st, sc, a, b, (u64) n, key, bits / 8);
     }
     if (rc) return rc;

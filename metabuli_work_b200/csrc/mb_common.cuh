@@ -95,7 +95,23 @@ MB_HD u32 sort_t_packed(u64 value) {
     t = t * 21u + ((hi >> 7) & 31u);
     return (t << 2) | ((((hi >> 2) & 31u) * 49u) >> 8);
 }
-MB_HD u64 sort_t(const SortT &k, u64 value) { return k.mode ? (u64) sort_t_packed(value) : (value >> 24) >> k.shift; }
+// mode 2: all seven leading residues as a base-21 number (21^7 < 2^31) plus one bit of the eighth: a 32-bit key — four
+// passes — that resolves 7.3 residues (the raw leading 32 bits resolve 6.4).  Chosen for large databases, where a coarser
+// key leaves T buckets that span several units of the DB stream and the join walks a unit's queries once per piece.
+MB_HD u32 sort_t_packed7(u64 value) {
+    const u64 aa = value >> 24;                  // 8 x 5 bits, first residue most significant
+    u32 t = (u32) (aa >> 35) & 31u;
+    t = t * 21u + ((u32) (aa >> 30) & 31u);
+    t = t * 21u + ((u32) (aa >> 25) & 31u);
+    t = t * 21u + ((u32) (aa >> 20) & 31u);
+    t = t * 21u + ((u32) (aa >> 15) & 31u);
+    t = t * 21u + ((u32) (aa >> 10) & 31u);
+    t = t * 21u + ((u32) (aa >> 5) & 31u);
+    return (t << 1) | (u32) (((u32) aa & 31u) >= 11u);
+}
+MB_HD u64 sort_t(const SortT &k, u64 value) {
+    return k.mode == 1 ? (u64) sort_t_packed(value) : k.mode == 2 ? (u64) sort_t_packed7(value) : (value >> 24) >> k.shift;
+}
 MB_HD bool sort_t_lossy(const SortT &k) { return k.mode != 0 || k.shift != 0; }
 
 // first index in vals[lo, hi) whose amino-acid part is >= aa (k_match: lookup of a query in a decoded DB block)

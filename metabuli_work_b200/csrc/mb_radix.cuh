@@ -33,6 +33,10 @@ struct KmerKeyPacked {      // digits of the 24-bit re-coded key sort_t_packed (
     __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const { return (sort_t_packed(r.value) >> (8 * pass)) & 255u; }
 };
 
+struct KmerKeyPacked7 {     // digits of the 32-bit re-coded key sort_t_packed7 (seven residues), format 2 only
+    __device__ __forceinline__ u32 digit(const mb_kmer &r, int pass) const { return (sort_t_packed7(r.value) >> (8 * pass)) & 255u; }
+};
+
 struct KmerOwnerKey {       // multi-GPU bucketing: owner shard = number of bounds <= value
     u64 bounds[8];
     int n_bounds;

@@ -49,6 +49,12 @@ def kmer_sort_key(values, sort_bits, kmer_format):
     values = np.asarray(values, dtype=np.uint64)
     if not sort_bits:
         sort_bits = 21 if kmer_format == 2 else 32
+    if sort_bits == 31:                  # seven residues base 21, one bit of the eighth (sort_t_packed7)
+        aa = values >> np.uint64(24)
+        t = (aa >> np.uint64(35)) & np.uint64(31)
+        for sh in (30, 25, 20, 15, 10, 5):
+            t = t * np.uint64(21) + ((aa >> np.uint64(sh)) & np.uint64(31))
+        return (t << np.uint64(1)) | ((aa & np.uint64(31)) >= np.uint64(11)).astype(np.uint64)
     if sort_bits != 21:
         return values >> np.uint64(24 + 40 - sort_bits)
     hi = (values >> np.uint64(32)).astype(np.uint64)

@@ -197,7 +197,7 @@ def test_build_index_on_device(golden, mb, tmp_path, splits):
         db.close()
 
 
-@pytest.mark.parametrize("bits", [24, 32, 40])
+@pytest.mark.parametrize("bits", [24, 31, 32, 40])
 def test_kmer_sort_bits(golden, mb, bits):
     """The join result does not depend on how many leading amino-acid bits the query sort orders."""
     _, s1, s2 = golden.reads("sync_paired")
