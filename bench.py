@@ -659,6 +659,14 @@ def run_b200(a):
         ktimes = step_counts["kt"]
     launches_per_step = t_step["kernel_launches"]
     stats = dict(sharded.stats) if sharded else {}
+    if sharded and world > 1:
+        # every rank's wall-clock split and leftover-scorer load of the last timed step: where an imbalance comes from
+        import torch.distributed as dist
+        mine = dict(stats["phases_ms"], k_match=round(ktimes.get("k_match", (0, 0))[0], 2), k_score=round(ktimes.get("k_score", (0, 0))[0], 2),
+                    k_sort_segments=round(ktimes.get("k_sort_segments", (0, 0))[0], 2), kmers_owned=stats["kmers_owned"], matches_owned=stats["matches_owned"])
+        allr = [None] * world
+        dist.all_gather_object(allr, mine)
+        stats["by_rank"] = allr
 
     # ---- end-to-end leg: host buffers in, host results out, every step ----
     for _ in range(max(1, a.warmup // 2)):

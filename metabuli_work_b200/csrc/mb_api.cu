@@ -61,6 +61,7 @@ struct Counters {                 // device-side scalars, one allocation
     unsigned long long tc_count;
     unsigned long long kmer_count;
     unsigned long long slow_matches;     // matches of the reads listed for the general scorer (compact scratch offsets)
+    unsigned long long seg_huge_words;   // key scratch the segments beyond SS_CAP need (k_sort_segments_huge)
     u32 error_flag;
     u32 max_seg;
     u32 score_ticket;
@@ -162,6 +163,7 @@ struct mb_ctx {
     bool fine_key = false, key_decided = false;    // seven-residue sort key: decided by the first large batch after mb_load_db
     DevBuf mask_probs, mask_scales;
     DevBuf read_order, order_hist;     // short-read scorers: reads by match count
+    DevBuf seg_huge, seg_huge_keys, seg_huge_idx;      // segments beyond SS_CAP: list and (key, index) scratch
     bool have_reads = false, have_kmers = false, kmers_sorted = false, have_matches = false, matches_sorted = false, have_results = false;
     bool segments_valid = false;      // seg_begin/seg_end describe matches_a
     // multi-GPU routing (mb_peer_*): this context's receive side and the routing table of all ranks
@@ -1220,7 +1222,9 @@ int mb_sort_matches(mb_ctx *ctx) {
         if (int rc = compute_segments(ctx)) return rc;
         CK(ctx->matches_b.ensure(ctx->n_matches * sizeof(mb_match)));
         CK(cudaMemsetAsync(&ctx->dcnt()->seg_ticket, 0, 4 * sizeof(u32), ctx->stream));
+        CK(cudaMemsetAsync(&ctx->dcnt()->seg_huge_words, 0, sizeof(unsigned long long), ctx->stream));
         CK(ctx->seg_long.ensure((size_t) ctx->n_reads * sizeof(u32)));
+        CK(ctx->seg_huge.ensure((size_t) SS_HUGE_MAX * sizeof(HugeSeg)));
         if (!ctx->seg_ctas) {
             CK(cudaFuncSetAttribute(k_sort_segments_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) segsort_smem_bytes()));
             int per_sm = 0;
@@ -1231,20 +1235,36 @@ int mb_sort_matches(mb_ctx *ctx) {
         if (sk.total_bits() <= 55)
             KL(KID_SEGSORT, k_sort_segments<true><<<grid, SS_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
-                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
+                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count,
+                ctx->seg_huge.as<HugeSeg>(), &ctx->dcnt()->seg_huge_words));
         else
             KL(KID_SEGSORT, k_sort_segments<false><<<grid, SS_THREADS, 0, ctx->stream>>>(
                 ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), ctx->n_reads, sk,
-                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
+                &ctx->dcnt()->seg_ticket, &ctx->dcnt()->seg_too_long, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count,
+                ctx->seg_huge.as<HugeSeg>(), &ctx->dcnt()->seg_huge_words));
         // segments of 513..1024 matches (rare with short reads): shared-memory network, one warp each
         KL(KID_SEGSORT_LONG, k_sort_segments_long<<<(unsigned) ctx->sms, SS_THREADS, segsort_smem_bytes(), ctx->stream>>>(
             ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), sk,
             &ctx->dcnt()->seg_long_ticket, ctx->seg_long.as<u32>(), &ctx->dcnt()->seg_long_count));
         u32 too_long = 0;
         if (int rc = read_back(ctx, &ctx->dcnt()->seg_too_long, &too_long)) return rc;
-        std::swap(ctx->matches_a.p, ctx->matches_b.p);
-        std::swap(ctx->matches_a.cap, ctx->matches_b.cap);
-        done = too_long == 0;      // otherwise some read has more matches than a segment buffer: fall through
+        if (too_long && too_long <= SS_HUGE_MAX) {
+            // a few reads with more than SS_CAP matches: one CTA each over a slice of global key scratch
+            unsigned long long words = 0;
+            if (int rc = read_back(ctx, &ctx->dcnt()->seg_huge_words, &words)) return rc;
+            CK(ctx->seg_huge_keys.ensure((size_t) words * sizeof(u64)));
+            CK(ctx->seg_huge_idx.ensure((size_t) words * sizeof(u32)));
+            KL(KID_SEGSORT_LONG, k_sort_segments_huge<<<std::min<unsigned>(too_long, (unsigned) ctx->sms * 4), SS_THREADS, 0, ctx->stream>>>(
+                ctx->matches_a.as<mb_match>(), ctx->matches_b.as<mb_match>(), ctx->seg_begin.as<u64>(), ctx->seg_end.as<u64>(), sk,
+                ctx->seg_huge.as<HugeSeg>(), too_long, ctx->seg_huge_keys.as<u64>(), ctx->seg_huge_idx.as<u32>()));
+            too_long = 0;
+        }
+        done = too_long == 0;      // otherwise more reads beyond SS_CAP than the list holds: the full-key sort below, from the
+                                   // untouched input (the segments beyond SS_CAP were not copied)
+        if (done) {
+            std::swap(ctx->matches_a.p, ctx->matches_b.p);
+            std::swap(ctx->matches_a.cap, ctx->matches_b.cap);
+        }
     }
     if (!done) {
         ctx->segments_valid = false;

@@ -10,6 +10,8 @@ namespace mb {
 constexpr int SS_THREADS = 256;
 constexpr int SS_WARPS = SS_THREADS / 32;
 constexpr int SS_CAP = 1024;                    // longest segment the shared-memory path takes
+constexpr u32 SS_HUGE_MAX = 1u << 16;           // segments beyond SS_CAP that are sorted one CTA each (more: full radix sort)
+struct HugeSeg { u32 read, n_pad; unsigned long long off; };
 
 struct MatchSeqKey {                            // radix digit = byte `pass` of the batch-local read index
     u32 seq_base;
@@ -141,12 +143,13 @@ constexpr size_t segsort_smem_bytes() { return (size_t) SS_WARPS * SS_CAP * (siz
 // One warp per read segment [seg_begin[r], seg_end[r]) of `in` (grouped by read); sorted records go to the same
 // range of `out`.  Segments of up to 512 records are sorted in registers here; those of 513..SS_CAP are appended to
 // `long_list` for k_sort_segments_long (keeping this kernel free of shared memory: 3 CTAs per SM instead of 2);
-// longer ones are copied unsorted and counted in *too_long (the host then takes the full radix path).
+// longer ones are listed in `huge` with a slice of key scratch each (k_sort_segments_huge sorts them one CTA each); when
+// there are more than SS_HUGE_MAX of them they are only counted and the host takes the full radix path.
 template <bool PACKED>
 __global__ void __launch_bounds__(SS_THREADS, 3)
 k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, const u64 *__restrict__ seg_begin,
                 const u64 *__restrict__ seg_end, u32 n_reads, SegKey sk, u32 *ticket, u32 *too_long, u32 *__restrict__ long_list,
-                u32 *long_count) {
+                u32 *long_count, HugeSeg *__restrict__ huge, unsigned long long *huge_words) {
     const u32 lane = threadIdx.x & 31;
     const u64 *in64 = reinterpret_cast<const u64 *>(in);
     u64 *out64 = reinterpret_cast<u64 *>(out);
@@ -170,8 +173,16 @@ k_sort_segments(const mb_match *__restrict__ in, mb_match *__restrict__ out, con
             const u32 n = (u32) (e - b);
             if (n == 0) continue;
             if (n > SS_CAP) {
-                if (lane == 0) atomicAdd(too_long, 1u);
-                for (u64 i = lane; i < (u64) n * 3; i += 32) out64[b * 3 + i] = in64[b * 3 + i];
+                if (lane == 0) {
+                    const u32 slot = atomicAdd(too_long, 1u);
+                    if (slot < SS_HUGE_MAX) {
+                        u32 n_pad = 2048;
+                        while (n_pad < n) n_pad <<= 1;
+                        huge[slot].read = r;
+                        huge[slot].n_pad = n_pad;
+                        huge[slot].off = atomicAdd(huge_words, (unsigned long long) n_pad);
+                    }
+                }
                 continue;
             }
             if (n <= 32) { sort_segment_regs<1, PACKED>(in64, out64, b, n, sk); continue; }
@@ -235,6 +246,54 @@ k_sort_segments_long(const mb_match *__restrict__ in, mb_match *__restrict__ out
             out64[(b + i) * 3] = w0; out64[(b + i) * 3 + 1] = w1; out64[(b + i) * 3 + 2] = w2;
         }
         __syncwarp();
+    }
+}
+
+// Segments of more than SS_CAP records (a short read that hits very many species): one CTA each, bitonic network over
+// (key, index) pairs in a global scratch slice (L2 resident), then the gather.  Rare; before this kernel existed ONE such
+// read sent the whole batch through the full-key radix sort (8+ passes: 53 ms at configs[2] on the ranks that had one).
+__global__ void __launch_bounds__(SS_THREADS)
+k_sort_segments_huge(const mb_match *__restrict__ in, mb_match *__restrict__ out, const u64 *__restrict__ seg_begin,
+                     const u64 *__restrict__ seg_end, SegKey sk, const HugeSeg *__restrict__ huge, u32 n_huge, u64 *__restrict__ keys_all,
+                     u32 *__restrict__ idx_all) {
+    const u64 *in64 = reinterpret_cast<const u64 *>(in);
+    u64 *out64 = reinterpret_cast<u64 *>(out);
+    for (u32 h = blockIdx.x; h < n_huge; h += gridDim.x) {
+        const HugeSeg hs = huge[h];
+        const u64 b = seg_begin[hs.read];
+        const u32 n = (u32) (seg_end[hs.read] - b), n_pad = hs.n_pad;
+        u64 *keys = keys_all + hs.off;
+        u32 *idx = idx_all + hs.off;
+        for (u32 i = threadIdx.x; i < n_pad; i += SS_THREADS) {
+            u64 k = ~0ull;
+            if (i < n) {
+                const u64 w0 = __ldg(in64 + (b + i) * 3), w1 = __ldg(in64 + (b + i) * 3 + 1), w2 = __ldg(in64 + (b + i) * 3 + 2);
+                k = sk.key(w0, (u32) (w1 >> 32), (u32) w2, (u32) (w2 >> 48));
+            }
+            keys[i] = k;
+            idx[i] = i;
+        }
+        __syncthreads();
+        for (u32 kk = 2; kk <= n_pad; kk <<= 1) {
+            for (u32 j = kk >> 1; j > 0; j >>= 1) {
+                for (u32 tt = threadIdx.x; tt < n_pad / 2; tt += SS_THREADS) {
+                    const u32 i = ((tt & ~(j - 1)) << 1) | (tt & (j - 1));
+                    const u32 p = i | j;
+                    const u64 a = keys[i], c = keys[p];
+                    const u32 ia = idx[i], ic = idx[p];
+                    const bool up = (i & kk) == 0;
+                    const bool a_gt = a > c || (a == c && ia > ic);
+                    if (a_gt == up) { keys[i] = c; keys[p] = a; idx[i] = ic; idx[p] = ia; }
+                }
+                __syncthreads();
+            }
+        }
+        for (u32 i = threadIdx.x; i < n; i += SS_THREADS) {
+            const u64 s = b + idx[i];
+            const u64 w0 = __ldg(in64 + s * 3), w1 = __ldg(in64 + s * 3 + 1), w2 = __ldg(in64 + s * 3 + 2);
+            out64[(b + i) * 3] = w0; out64[(b + i) * 3 + 1] = w1; out64[(b + i) * 3 + 2] = w2;
+        }
+        __syncthreads();
     }
 }
 

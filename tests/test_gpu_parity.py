@@ -276,6 +276,48 @@ def test_skewed_groups(golden, mb, tmp_path):
     run_all_stages(mb, dbdir, 2, s1[:200], s2[:200])
 
 
+def test_reads_with_thousands_of_matches(golden, mb, tmp_path):
+    """Short reads whose match lists exceed every in-kernel segment buffer (> 1024 matches: k_sort_segments_huge, one CTA per
+    such read) next to ordinary reads: the k-mers of three read pairs are in the DB under every species of the fixture taxonomy."""
+    rng = np.random.default_rng(12)
+    src_db = orc.Db(golden.dbdir("plain_paired"))
+    base_v, base_t = src_db.decode()
+    src_db.close()
+    taxa = np.unique(base_t)
+    _, s1, s2 = golden.reads("plain_paired")
+    p = orc.default_params(kmer_format=2, seq_mode=2)
+    hot = orc.extract(p, orc.Batch([s1[3], s1[40], s1[77]], [s2[3], s2[40], s2[77]]))["value"]
+    hot = np.unique(hot)
+    # a database holds a value once per SPECIES (IndexCreator::filterKmers): the added taxa belong to different species
+    src_db = orc.Db(golden.dbdir("plain_paired"))
+    by_species = {}
+    for x in taxa.tolist():
+        by_species.setdefault(int(orc.lib().orc_tax_species_of(src_db.h, int(x))), int(x))
+    src_db.close()
+    by_species.pop(0, None)
+    chosen = np.array(sorted(by_species.values()), dtype=np.uint32)
+    assert len(chosen) >= 8
+    extra_v = np.repeat(hot, len(chosen))
+    extra_t = np.tile(chosen, len(hot)).astype(np.uint32)
+    # (the base DB's own entries for these values would repeat a species: drop them)
+    base_keep = ~np.isin(base_v, hot)
+    base_v, base_t = base_v[base_keep], base_t[base_keep]
+    v = np.concatenate([base_v, extra_v])
+    t = np.concatenate([base_t.astype(np.uint32), extra_t])
+    order = np.lexsort((t, v))
+    v, t = v[order], t[order]
+    keep = np.ones(len(v), dtype=bool)
+    keep[1:] = (v[1:] != v[:-1]) | (t[1:] != t[:-1])
+    dbdir = _craft_db(golden, str(tmp_path / "hot"), v[keep], t[keep])
+    db = orc.Db(dbdir)
+    k, m, res, ids, cnt = orc.classify(db, db.params(seq_mode=2), orc.Batch(s1[:120], s2[:120]), threads=4)
+    db.close()
+    seq = (m["qinfo"] >> np.uint64(32)) & np.uint64((1 << 29) - 1)
+    per_read = np.bincount(seq.astype(np.int64))
+    assert per_read.max() > 2048 and (per_read > 1024).sum() >= 3          # the case really has huge segments
+    run_all_stages(mb, dbdir, 2, s1[:120], s2[:120])
+
+
 def test_medium_random(mb, tmp_path):
     """A larger seeded case built on the box: 54 genomes x 60 kb, 20k pairs + long reads (multi-tile sort,
     hundreds of DB blocks), plain and syncmer."""
