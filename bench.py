@@ -69,6 +69,8 @@ def parse_args():
     ap.add_argument("--check-port", action="store_true", help="also compare 20000 reads with the oracle port (liborc)")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="multi-GPU: producers write into peer memory (fused) or bucket + NCCL all-to-all (nccl)")
+    ap.add_argument("--no-rebalance", action="store_true", help="multi-GPU: keep the equal-count DB shards (default: after the warm-up the "
+                    "shard boundaries are moved so that the owner-side time (k-mer sort + join) is equal, and the shards reloaded)")
     ap.add_argument("--no-fastq", action="store_true", help="skip the input-pipeline leg (FASTQ text parsed on the device)")
     ap.add_argument("--keep", action="store_true", help="keep the generated workload in --workdir")
     a = ap.parse_args()
@@ -642,6 +644,35 @@ def run_b200(a):
         clf.stage(h_bases, h_off, h_len, bases_ptr=pin_bases.data_ptr())
     for _ in range(a.warmup):
         staged_step()
+    # Equal k-mer counts per shard are not equal work (shards that begin with six-codon amino acids have larger groups:
+    # 21-40 ms of join per shard at configs[2]).  The owner-side wall time of the warm-up (k-mer sort + join) is gathered,
+    # the boundaries are moved along the split table so that it comes out equal (piecewise-constant density), and every
+    # rank reloads its shard; at most two rounds.
+    cut_fractions, rebalance_log = None, []
+    if sharded and not a.no_rebalance:
+        import torch.distributed as dist
+        for _round in range(2):
+            t_own = [None] * world
+            dist.all_gather_object(t_own, float(sharded.stats["phases_ms"]["sort_match"]))
+            rebalance_log.append([round(x, 2) for x in t_own])
+            if max(t_own) <= float(os.environ.get("MB_REBALANCE_THRESHOLD", "1.06")) * (sum(t_own) / world):     # (test knob: 0 forces a round)
+                break
+            cut_fractions = mb.rebalanced_cuts(t_own, cut_fractions)
+            sharded.close()
+            del sharded
+            clf.close()
+            barrier()
+            clf = mb.Classifier(dbdir, device=local, seq_mode=a.seq_mode, shard=rank, n_shards=world, cut_fractions=cut_fractions)
+            clf.set_profile(True)
+            if a.mask:
+                clf.set_params(mask_mode=1, mask_prob=0.9)
+            stream = torch.cuda.ExternalStream(clf.stream(), device=device)      # the timing events go on the new context's stream
+            sharded = ShardedClassifier(DeviceEngine(clf, device), clf.shard_bounds(), n_pairs, rank, world, fused=a.exchange == "fused")
+            sharded.stage(h_bases, h_off, h_len, bases_ptr=pin_bases.data_ptr())
+            for _ in range(a.warmup):
+                staged_step()
+        if cut_fractions is not None:
+            log(f"rank {rank}: shards re-balanced, boundaries at {[round(float(x), 4) for x in cut_fractions]}; owner-side ms per round {rebalance_log}")
     sampler = ClockSampler(local)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -729,7 +760,9 @@ def run_b200(a):
         "config": {"workload": workload_text(a, meta),
                    "batches_per_step": max(1, len(batches)),
                    "pairs_per_gpu": n_pairs, "db_kmers": meta["db_kmers"], "db_words": meta["db_words"], "genomes": meta["genomes"],
-                   "db_sharding": f"{world} k-mer-range shard(s), one per GPU" if world > 1 else "whole DB on one GPU",
+                   "db_sharding": (f"{world} k-mer-range shard(s), one per GPU" + (f"; boundaries moved to equalise the owner-side time "
+                                   f"(fractions of the split table {[round(float(x), 4) for x in cut_fractions]}, owner-side ms per "
+                                   f"round {rebalance_log})" if cut_fractions is not None else "")) if world > 1 else "whole DB on one GPU",
                    "exchange": (a.exchange if world > 1 else None),
                    "l2": "inputs larger than L2 (k-mer buffer and DB stream are GBs vs 126 MB L2); no flush needed",
                    "seed": a.seed},

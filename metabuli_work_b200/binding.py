@@ -147,6 +147,8 @@ _sig(_cuda, "mb_take_routed_matches", C.c_int, [vp, szp])
 
 _sig(_host, "mbh_last_error", C.c_char_p, [])
 _sig(_host, "mbh_open", vp, [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int])
+_sig(_host, "mbh_open_cuts", vp, [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, vp])
+_sig(_host, "mbh_rebalanced_cuts", None, [vp, C.c_int, vp, vp])
 _sig(_host, "mbh_close", None, [vp])
 _sig(_host, "mbh_ctx", vp, [vp])
 _sig(_host, "mbh_params", None, [vp, C.POINTER(Params)])
@@ -171,6 +173,15 @@ def _ptr(a):
     if a is None:
         return None
     return a.ctypes.data_as(C.c_void_p)
+
+
+def rebalanced_cuts(times, current=None):
+    """Shard boundaries (fractions of the split table) that equalise the measured per-shard times."""
+    t = np.ascontiguousarray(times, dtype=np.float64)
+    cur = None if current is None else np.ascontiguousarray(current, dtype=np.float64)
+    out = np.zeros(len(t) - 1, dtype=np.float64)
+    _host.mbh_rebalanced_cuts(_ptr(t), len(t), _ptr(cur) if cur is not None else None, _ptr(out))
+    return out
 
 
 def pack_reads(mates1, mates2=None):
@@ -504,8 +515,13 @@ class Classifier(Context):
     """A database directory opened through the C++ host library (host/mb_host.h): parses taxonomyDB,
     taxID_list, db.parameters, cuts the shard and makes everything resident on the GPU."""
 
-    def __init__(self, dbdir, device=0, seq_mode=2, min_score=0.0, min_sp_score=0.0, shard=0, n_shards=1):
-        self.h = _host.mbh_open(os.fsencode(dbdir), device, seq_mode, min_score, min_sp_score, shard, n_shards)
+    def __init__(self, dbdir, device=0, seq_mode=2, min_score=0.0, min_sp_score=0.0, shard=0, n_shards=1, cut_fractions=None):
+        if cut_fractions is not None:
+            self._cuts = np.ascontiguousarray(cut_fractions, dtype=np.float64)
+            assert len(self._cuts) == n_shards - 1
+            self.h = _host.mbh_open_cuts(os.fsencode(dbdir), device, seq_mode, min_score, min_sp_score, shard, n_shards, _ptr(self._cuts))
+        else:
+            self.h = _host.mbh_open(os.fsencode(dbdir), device, seq_mode, min_score, min_sp_score, shard, n_shards)
         if not self.h:
             raise MetabuliError(-1, _host.mbh_last_error().decode())
         self.ctx = _host.mbh_ctx(self.h)

@@ -178,6 +178,11 @@ class ShardedClassifier:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         return int(t.item())
 
+    def close(self):
+        """Unmap the peers' buffers (collective): call on every rank before the engines' contexts are destroyed."""
+        if self.fused and hasattr(self.e, "peer_teardown"):
+            self.e.peer_teardown(self.group)
+
     def _setup(self, kmer_cap, match_cap):
         self.kmer_cap, self.match_cap = int(kmer_cap), int(match_cap)
         self.e.peer_setup(self.group, self.rank, self.world, self.bounds, self.reads_per_rank, self.kmer_cap, self.match_cap)

@@ -42,6 +42,26 @@ bool preadParallel(int fd, void *dst, size_t bytes, size_t off, int threads) {
     return true;
 }
 
+std::vector<double> rebalancedCuts(const std::vector<double> &t, const double *frac) {
+    const size_t n = t.size();
+    std::vector<double> edge(n + 1, 0.0), out;
+    for (size_t g = 1; g < n; ++g) edge[g] = frac ? frac[g - 1] : (double) g / (double) n;
+    edge[n] = 1.0;
+    double total = 0;
+    for (double x : t) total += x;
+    if (n < 2 || total <= 0) return out;
+    // piecewise-constant work density t[g] / width[g]; the new boundaries cut its integral into n equal parts
+    size_t g = 0;
+    double done = 0;                      // work before shard g
+    for (size_t k = 1; k < n; ++k) {
+        const double want = total * (double) k / (double) n;
+        while (g + 1 < n && done + t[g] < want) { done += t[g]; ++g; }
+        const double within = t[g] > 0 ? (want - done) / t[g] : 0.0;
+        out.push_back(edge[g] + within * (edge[g + 1] - edge[g]));
+    }
+    return out;
+}
+
 int ioThreads(const Options &opt) {
     if (opt.threads > 1) return opt.threads;
     const unsigned hw = std::thread::hardware_concurrency();
@@ -229,7 +249,7 @@ static DbParameters readDbParameters(const std::string &dir) {
 
 Database::~Database() { if (ctx_) mb_destroy(ctx_); }
 
-bool Database::open(const std::string &dir, Options &opt, int shard, int nShards, std::string &err) {
+bool Database::open(const std::string &dir, Options &opt, int shard, int nShards, std::string &err, const double *cutFrac) {
     // loadDbParameters (common.cpp:88-133): DB-side values win where the reference lets them
     const DbParameters dp = readDbParameters(dir);
     int skipRedundancy = 0;
@@ -290,8 +310,17 @@ bool Database::open(const std::string &dir, Options &opt, int shard, int nShards
     bounds_.clear();
     if (nShards > 1) {
         if ((size_t) nShards > cuts.size()) { err = "more shards than usable split entries"; return false; }
+        size_t prevCut = 0;
         for (int g = 1; g < nShards; ++g) {
-            const mb_split &s = cuts[(size_t) g * cuts.size() / (size_t) nShards];
+            size_t at = (size_t) g * cuts.size() / (size_t) nShards;
+            if (cutFrac) {
+                at = (size_t) std::llround(cutFrac[g - 1] * (double) cuts.size());
+                // strictly increasing, inside the table
+                const size_t lo = prevCut + 1, hi = cuts.size() - (size_t) (nShards - g);
+                at = std::min(std::max(at, lo), hi);
+            }
+            prevCut = at;
+            const mb_split &s = cuts[at];
             if (s.diffIdxOffset == 0 || s.diffIdxOffset > nWords || s.infoIdxOffset == 0) { err = "split entry out of range"; return false; }
             // the words in front of the boundary: a delta has at most five
             const size_t lookFrom = s.diffIdxOffset >= 6 ? (size_t) s.diffIdxOffset - 6 : 0;

@@ -94,7 +94,9 @@ public:
     // Reads diffIdx/info/split/taxonomyDB/taxID_list/db.parameters, applies the DB-side parameter
     // overrides to `opt`, creates the GPU context and makes DB + taxonomy resident.
     // shard/nShards cut the DB at `split` boundaries (multi-GPU).
-    bool open(const std::string &dir, Options &opt, int shard, int nShards, std::string &err);
+    // cutFrac (nShards - 1 values in (0, 1), increasing; may be null): where the shard boundaries lie along the usable split
+    // entries — null means equal k-mer counts (g / nShards).  Used to re-balance shards by measured join time.
+    bool open(const std::string &dir, Options &opt, int shard, int nShards, std::string &err, const double *cutFrac = nullptr);
     mb_ctx *ctx() const { return ctx_; }
     const Taxonomy &taxonomy() const { return tax_; }
     const mb_params &params() const { return par_; }
@@ -171,6 +173,10 @@ private:
 };
 
 // whole `classify` run: returns process exit code (opt.devices with more than one entry: runClassifyMulti)
+// new shard boundaries (fractions along the split table) that equalise the measured per-shard times, assuming a shard's work
+// is spread evenly over its range; frac: the nShards - 1 current boundaries (null = equal counts)
+std::vector<double> rebalancedCuts(const std::vector<double> &timePerShard, const double *frac);
+
 int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,
                      const std::string &jobId, Options opt, std::string &err);
 int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir, const std::string &outDir,

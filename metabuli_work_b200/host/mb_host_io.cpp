@@ -739,6 +739,23 @@ mbh_db *mbh_open(const char *dbdir, int device, int seq_mode, float min_score, f
     if (!h->db.open(dbdir, h->opt, shard, n_shards, g_err)) { delete h; return nullptr; }
     return h;
 }
+// the same with shard boundaries at given fractions of the split table (n_shards - 1 values; re-balancing by join time)
+mbh_db *mbh_open_cuts(const char *dbdir, int device, int seq_mode, float min_score, float min_sp_score, int shard, int n_shards,
+                      const double *cut_frac) {
+    mbh_db *h = new mbh_db();
+    h->opt.device = device;
+    h->opt.seqMode = seq_mode;
+    h->opt.minScore = min_score;
+    h->opt.minSpScore = min_sp_score;
+    if (!h->db.open(dbdir, h->opt, shard, n_shards, g_err, cut_frac)) { delete h; return nullptr; }
+    return h;
+}
+// new boundaries from the per-shard times (out: n_shards - 1 values); cur may be NULL (equal counts)
+void mbh_rebalanced_cuts(const double *time_per_shard, int n_shards, const double *cur, double *out) {
+    std::vector<double> t(time_per_shard, time_per_shard + n_shards);
+    const std::vector<double> r = mbh::rebalancedCuts(t, cur);
+    for (size_t i = 0; i < r.size(); ++i) out[i] = r[i];
+}
 void mbh_close(mbh_db *h) { delete h; }
 mb_ctx *mbh_ctx(mbh_db *h) { return h->db.ctx(); }
 void mbh_params(mbh_db *h, mb_params *out) { *out = h->db.params(); }
