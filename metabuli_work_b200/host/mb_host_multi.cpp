@@ -182,8 +182,9 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
     sh.n = n;
     sh.peers.resize(n);
     std::vector<Worker> workers(n);
-    {
-        // the shards are opened side by side: each thread reads its own byte ranges of diffIdx / info
+    // (re)opens all shards side by side: each thread reads its own byte ranges of diffIdx / info.  frac: shard boundaries as
+    // fractions of the split table (null: equal k-mer counts)
+    auto openShards = [&](const double *frac) -> bool {
         std::vector<std::thread> th;
         std::vector<std::string> errs(n);
         std::vector<Options> opts(n, opt);
@@ -191,16 +192,21 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
             workers[g].rank = g;
             workers[g].db.reset(new Database());
             opts[g].device = opt.devices[g];
-            th.emplace_back([&, g] { if (!workers[g].db->open(dbDir, opts[g], g, n, errs[g])) workers[g].db.reset(); });
+            th.emplace_back([&, g] { if (!workers[g].db->open(dbDir, opts[g], g, n, errs[g], frac)) workers[g].db.reset(); });
         }
         for (auto &t : th) t.join();
-        for (int g = 0; g < n; ++g) if (!workers[g].db) { err = "GPU " + std::to_string(opt.devices[g]) + ": " + errs[g]; return 1; }
+        for (int g = 0; g < n; ++g) if (!workers[g].db) { err = "GPU " + std::to_string(opt.devices[g]) + ": " + errs[g]; return false; }
+        const std::vector<int> devices = opt.devices;
         opt = opts[0];                                     // DB-side parameter overrides (the same on every shard)
-    }
-    for (int g = 0; g < n; ++g)
-        for (int h = 0; h < n; ++h)
-            if (mb_enable_peer_access(workers[g].db->ctx(), opt.devices[h]) != MB_OK) { err = mb_last_error(workers[g].db->ctx()); return 1; }
-    sh.bounds = workers[0].db->shardBounds();
+        opt.devices = devices;
+        for (int g = 0; g < n; ++g)
+            for (int h = 0; h < n; ++h)
+                if (mb_enable_peer_access(workers[g].db->ctx(), opt.devices[h]) != MB_OK) { err = mb_last_error(workers[g].db->ctx()); return false; }
+        sh.bounds = workers[0].db->shardBounds();
+        sh.kmerCap = sh.matchCap = 0;                      // the receive sides belong to the old contexts: set up again
+        return true;
+    };
+    if (!openShards(nullptr)) return 1;
     sh.readsPerRank = (uint32_t) ((opt.batchReads + (size_t) n - 1) / (size_t) n);
     size_t dbKmers = 0, dbBytes = 0;
     for (auto &w : workers) { dbKmers += w.db->numKmers(); dbBytes += w.db->numWords() * 2 + w.db->numKmers() * 4; }
@@ -216,7 +222,7 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
     const size_t budget = std::min<size_t>((size_t) (0.9 * (double) freeMin), (size_t) std::max(1, opt.ramUsage) << 30);
     const size_t slotBytes = 32 + (size_t) std::max(1, opt.matchPerKmer) * (48 + (opt.seqMode == 3 ? 85 : 12)) + 16 + 24 * (size_t) std::max(1, opt.matchPerKmer) / 2;
     const size_t maxBatchBases = std::max<size_t>(budget / slotBytes, 1u << 20) / 2 * (size_t) n;
-    const Taxonomy &tax = workers[0].db->taxonomy();
+    const Taxonomy tax = workers[0].db->taxonomy();          // a copy: the shards may be reloaded (re-balancing) while the Reporter lives
     Reporter rep(tax, outDir, jobId, opt.printLineage != 0, opt.kronaPrelude);
     rep.setThreads(ioThreads(opt));
     if (!rep.openClassifications(err)) return 1;
@@ -226,6 +232,8 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
     if (paired && !r2.open(inputs[1], err)) return 1;
     ReadBatch batch;
     uint64_t totalKmers = 0, totalMatches = 0;
+    int rebalanceRounds = 0;
+    std::vector<double> cutFrac;
     while (loadBatchMulti(r1, paired ? &r2 : nullptr, opt.batchReads, std::min<size_t>(4ull << 30, maxBatchBases), batch)) {
         Barrier bar(n);
         std::vector<std::thread> th;
@@ -239,6 +247,30 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
         }
         totalKmers += bk; totalMatches += bm;
         std::cout << "Batch of " << batch.nReads() << " reads on " << n << " GPUs: " << bk << " query k-mers, " << bm << " matches" << std::endl;
+        // Equal k-mer counts per shard are not equal work: after each of the first two large batches the
+        // owners' times (k-mer sort + join) decide whether the shard boundaries move and the shards are reloaded.
+        static const size_t minReads = getenv("MB_REBALANCE_MIN_READS") ? (size_t) atoll(getenv("MB_REBALANCE_MIN_READS")) : 100000;
+        static const double threshold = getenv("MB_REBALANCE_THRESHOLD") ? atof(getenv("MB_REBALANCE_THRESHOLD")) : 1.06;
+        if (rebalanceRounds < 2 && batch.nReads() >= minReads) {
+            std::vector<double> t(n);
+            double mean = 0, worst = 0;
+            for (int g = 0; g < n; ++g) {
+                mb_phase_times pt;
+                mb_get_timings(workers[g].db->ctx(), &pt);
+                t[g] = (double) pt.sort_kmers_ms + (double) pt.match_ms;
+                mean += t[g] / n;
+                worst = std::max(worst, t[g]);
+            }
+            ++rebalanceRounds;
+            if (worst > threshold * mean) {
+                const std::vector<double> moved = rebalancedCuts(t, cutFrac.empty() ? nullptr : cutFrac.data());
+                if (moved.size() == (size_t) n - 1) {
+                    cutFrac = moved;
+                    if (!openShards(cutFrac.data())) return 1;
+                    std::cout << "DB shards re-balanced by owner time (slowest " << worst << " ms, mean " << mean << " ms)" << std::endl;
+                }
+            } else rebalanceRounds = 2;
+        }
     }
     rep.closeClassifications();
     if (!rep.writeReport(err)) return 1;

@@ -414,6 +414,13 @@ def test_cli_files_byte_identical(golden, mb, tmp_path):
         subprocess.check_call([mb.CLI, "classify"] + inp + [golden.dbdir(c), out, "mg_" + c, "--gpu-list", gl] + extra)
         for f in ("classifications.tsv", "report.tsv"):
             assert rd(os.path.join(out, "mg_" + c + "_" + f)) == rd(os.path.join(rep, c + "_" + f)), (c, gl, f)
+    # shard re-balancing forced after every batch (thresholds lowered through the test knobs): the shards are reloaded with
+    # moved boundaries in the middle of the run and the output must not change
+    log = subprocess.run([mb.CLI, "classify", r1, r2, golden.dbdir("sync_paired"), out, "mg_rebal", "--gpu-list", "0,0,0", "--batch-reads", "97"],
+                         env=dict(os.environ, MB_REBALANCE_MIN_READS="1", MB_REBALANCE_THRESHOLD="0"), check=True, capture_output=True, text=True)
+    assert "re-balanced" in log.stdout
+    for f in ("classifications.tsv", "report.tsv"):
+        assert rd(os.path.join(out, "mg_rebal_" + f)) == rd(os.path.join(rep, "sync_paired_" + f)), f
     # receive buffers that start far too small: both exchanges overflow, everybody re-allocates and the step is redone
     log = subprocess.run([mb.CLI, "classify", r1, r2, golden.dbdir("sync_paired"), out, "mg_small", "--gpu-list", "0,0,0"],
                          env=dict(os.environ, MB_EXCHANGE_CAP0="64"), check=True, capture_output=True, text=True)
