@@ -67,3 +67,25 @@ def test_pack_reads_layout(mb):
     assert bytes(b) == b"ACGTTTCCCGG"
     assert list(l) == [4, 2, 0, 3, 2, 0]
     assert list(o) == [0, 4, 6, 6, 9, 11]
+
+
+def test_rebalanced_cuts():
+    """Shard boundaries that equalise measured per-shard times (host/mb_host.cpp rebalancedCuts): equal times keep equal
+    shards, a slow shard shrinks, the new boundaries cut the piecewise-constant work density into equal parts."""
+    import numpy as np
+    import metabuli_work_b200.binding as mb
+    assert np.allclose(mb.rebalanced_cuts([3.0, 3.0, 3.0, 3.0]), [0.25, 0.5, 0.75])
+    c = mb.rebalanced_cuts([2.0, 1.0])
+    assert np.allclose(c, [0.375])                       # half of the work (1.5) lies at 3/4 of the first shard
+    # second round from moved boundaries: density 2/0.375 and 1/0.625 ... the cut keeps equalising
+    c2 = mb.rebalanced_cuts([1.5, 1.5], c)
+    assert np.allclose(c2, c)
+    t = np.array([40.0, 39, 21, 28, 31, 29, 35, 24])
+    cuts = mb.rebalanced_cuts(t)
+    assert len(cuts) == 7 and np.all(np.diff(cuts) > 0) and 0 < cuts[0] and cuts[-1] < 1
+    # work in each new shard under the model = total / 8
+    edges = np.concatenate([[0], cuts, [1]])
+    old = np.linspace(0, 1, 9)
+    dens = t / np.diff(old)
+    work = [sum(dens[g] * max(0.0, min(b, old[g + 1]) - max(a, old[g])) for g in range(8)) for a, b in zip(edges[:-1], edges[1:])]
+    assert np.allclose(work, t.sum() / 8)
