@@ -1268,8 +1268,15 @@ int mb_sort_matches(mb_ctx *ctx) {
     }
     if (!done) {
         ctx->segments_valid = false;
-        const int passes = (key.total_bits() + 7) / 8;
-        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, key, passes, KID_MSORT_HIST, &ctx->matches_seg)) return rc;
+        // full compareMatches key (long reads, contigs): the 24 DNA bits stay out of the radix passes — records that tie above
+        // them are a handful at most and are ordered in place afterwards (10 -> 7 passes at configs[3])
+        static const bool whole_key = getenv("MB_MSORT_WHOLE_KEY") != nullptr;          // tuning knob: the 24 DNA bits as passes too
+        MatchKey mk = key;
+        mk.skip_bits = whole_key ? 0 : 24;
+        const int passes = (mk.total_bits() - mk.skip_bits + 7) / 8;
+        if (int rc = radix_sort<mb_match, MatchKey, 8>(ctx, ctx->matches_a, ctx->matches_b, ctx->n_matches, mk, passes, KID_MSORT_HIST, &ctx->matches_seg)) return rc;
+        if (mk.skip_bits && ctx->n_matches)
+            KL(KID_SEGSORT_LONG, k_fix_dna_ties<<<(unsigned) ((ctx->n_matches + 255) / 256), 256, 0, ctx->stream>>>(ctx->matches_a.as<mb_match>(), ctx->n_matches, mk));
     }
     mark(ctx, EV_SORTM);
     ctx->matches_sorted = true;

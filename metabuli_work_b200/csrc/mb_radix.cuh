@@ -61,9 +61,30 @@ struct MatchKey {
         k = (k << 24) | (m.dnaEncoding & 0xFFFFFFu);
         return k;
     }
-    __device__ __forceinline__ u32 digit(const mb_match &m, int pass) const { return (u32) (key(m) >> (8 * pass)) & 255u; }
+    int skip_bits = 0;     // 24: the radix passes leave the DNA bits out; k_fix_dna_ties orders the (short) runs that tie above them
+    __device__ __forceinline__ u32 digit(const mb_match &m, int pass) const { return (u32) (key(m) >> (skip_bits + 8 * pass)) & 255u; }
     int total_bits() const { return 24 + 3 + pos_bits + 3 + sp_bits + seq_bits; }
 };
+
+// After a full-key sort without the 24 DNA bits: records that agree in everything above them form runs (same read, species,
+// frame, position and Hamming sum: a handful of DB k-mers at most); the first record of a run orders it by the DNA bits with
+// an insertion sort in place.  Three radix passes over every record become one read of the keys.
+__global__ void __launch_bounds__(256) k_fix_dna_ties(mb_match *__restrict__ m, u64 n, MatchKey key) {
+    const u64 i = (u64) blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const unsigned __int128 hi = key.key(m[i]) >> 24;
+    if (i && (key.key(m[i - 1]) >> 24) == hi) return;          // not the head of its run
+    u64 e = i + 1;
+    while (e < n && (key.key(m[e]) >> 24) == hi) ++e;
+    if (e - i < 2) return;
+    for (u64 a = i + 1; a < e; ++a) {
+        const mb_match x = m[a];
+        const u32 dx = x.dnaEncoding & 0xFFFFFFu;
+        u64 b = a;
+        while (b > i && (m[b - 1].dnaEncoding & 0xFFFFFFu) > dx) { m[b] = m[b - 1]; --b; }
+        if (b != a) m[b] = x;
+    }
+}
 
 struct MatchHomeKey {       // multi-GPU: home rank of a match = (sequenceID-1) / reads_per_rank
     u32 reads_per_rank;

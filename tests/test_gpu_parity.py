@@ -318,6 +318,37 @@ def test_reads_with_thousands_of_matches(golden, mb, tmp_path):
     run_all_stages(mb, dbdir, 2, s1[:120], s2[:120])
 
 
+def test_long_read_sort_orders_dna_ties(golden, mb):
+    """--seq-mode 3 sorts the full compareMatches key; the radix passes leave the 24 DNA bits out and k_fix_dna_ties orders
+    the runs that agree above them.  Real matches, each repeated up to six times with other DNA bits (so that nearly every
+    record sits in such a run), shuffled: the order must equal compareMatches' (KmerMatcher.cpp:1149-1166)."""
+    _, sl, _ = golden.reads("plain_long")
+    bases, offsets, lens = mb.pack_reads(sl, None)
+    clf = mb.Classifier(golden.dbdir("plain_long"), seq_mode=3)
+    try:
+        clf.stage(bases, offsets, lens)
+        clf.extract()
+        clf.sort_kmers()
+        clf.match()
+        m = clf.matches()
+        rng = np.random.default_rng(21)
+        parts = [m]
+        for k in range(5):
+            c = m[rng.random(len(m)) < 0.6].copy()
+            c["dnaEncoding"] = rng.integers(0, 1 << 24, len(c), dtype=np.uint32)
+            parts.append(c)
+        big = np.concatenate(parts)
+        big = big[rng.permutation(len(big))]
+        clf.set_matches(big)
+        clf.sort_matches()
+        got = as_orc_matches(clf.matches())
+        want = orc.sort_matches(as_orc_matches(big))
+        assert len(got) == len(want) > 3 * len(m)
+        assert np.array_equal(got, want)
+    finally:
+        clf.close()
+
+
 def test_medium_random(mb, tmp_path):
     """A larger seeded case built on the box: 54 genomes x 60 kb, 20k pairs + long reads (multi-tile sort,
     hundreds of DB blocks), plain and syncmer."""
