@@ -223,6 +223,13 @@ int mb_match_kmers(mb_ctx *ctx, size_t *n_matches);                     /* KmerM
 int mb_sort_matches(mb_ctx *ctx);                                       /* KmerMatcher.cpp:1071-1078     */
 int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used);                   /* Classifier.cpp:166-208        */
 int mb_fetch_results(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap);
+/* The same copy without waiting for it: enqueued on the copy stream behind the scoring, so the caller can stage and run the
+ * next batch while the results travel (page-locked host arrays for a truly asynchronous copy).  The host arrays are valid
+ * after mb_fetch_wait; one transfer is in flight at a time, and the next mb_score_reads waits for it before it writes the
+ * result arrays again.  (The reference writes its results on the thread that computed them, Classifier.cpp:133-150; this
+ * is the overlap its OpenMP batch loop cannot have.) */
+int mb_fetch_results_async(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap);
+int mb_fetch_wait(mb_ctx *ctx);
 /* all device stages back to back on staged reads (no host copies) */
 int mb_classify_staged(mb_ctx *ctx, size_t *taxcnt_used);
 

@@ -67,7 +67,7 @@ ABI_SYMBOLS = ["mb_default_params", "mb_create", "mb_destroy", "mb_last_error", 
                "mb_export_kmers_device", "mb_export_matches_device", "mb_set_read_id_base", "mb_set_profile",
                "mb_get_kernel_times", "mb_peer_alloc", "mb_ipc_export", "mb_ipc_open", "mb_ipc_close", "mb_peer_attach",
                "mb_prefetch_reads", "mb_stage_fastq", "mb_prefetch_fastq", "mb_alloc_host", "mb_free_host", "mb_fetch_fastq_names", "mb_fetch_staged_reads", "mb_extract_kmers_routed", "mb_take_routed_kmers", "mb_match_kmers_routed", "mb_take_routed_matches",
-               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access", "mb_mask_reads", "mb_build_index"]
+               "mb_sort_kmers_noalloc", "mb_mem_info", "mb_enable_peer_access", "mb_mask_reads", "mb_build_index", "mb_fetch_results_async", "mb_fetch_wait"]
 
 _cuda = C.CDLL(LIB_CUDA, mode=C.RTLD_GLOBAL)
 _host = C.CDLL(LIB_HOST)
@@ -138,6 +138,8 @@ _sig(_cuda, "mb_free_host", None, [vp])
 _sig(_cuda, "mb_fetch_fastq_names", C.c_int, [vp, vp, vp])
 _sig(_cuda, "mb_fetch_staged_reads", C.c_int, [vp, vp, vp, vp])
 _sig(_cuda, "mb_mask_reads", C.c_int, [vp])
+_sig(_cuda, "mb_fetch_results_async", C.c_int, [vp, vp, vp, vp, C.c_size_t])
+_sig(_cuda, "mb_fetch_wait", C.c_int, [vp])
 _sig(_cuda, "mb_build_index", C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_int, vp, C.c_size_t, C.POINTER(C.c_size_t), vp, C.c_size_t,
                                           C.POINTER(C.c_size_t), vp])
 _sig(_cuda, "mb_extract_kmers_routed", C.c_int, [vp, szp])
@@ -334,6 +336,13 @@ class Context:
     def fetch_into(self, res, ids, cnt):
         """mb_fetch_results into caller-owned (e.g. pinned) arrays."""
         self._ck(_cuda.mb_fetch_results(self.ctx, _ptr(res), _ptr(ids), _ptr(cnt), len(ids)))
+
+    def fetch_async(self, res, ids, cnt):
+        """mb_fetch_results_async into caller-owned (page-locked) arrays; fetch_wait() before they are read."""
+        self._ck(_cuda.mb_fetch_results_async(self.ctx, _ptr(res), _ptr(ids), _ptr(cnt), len(ids)))
+
+    def fetch_wait(self):
+        self._ck(_cuda.mb_fetch_wait(self.ctx))
 
     def kmers(self):
         n = C.c_size_t(0)

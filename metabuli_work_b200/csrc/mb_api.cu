@@ -126,6 +126,8 @@ struct mb_ctx {
     DevBuf pf_bases, pf_offsets, pf_lens, pf_info;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t pf_done = nullptr;
+    cudaEvent_t fetch_ready = nullptr, fetch_done = nullptr;   // mb_fetch_results_async: scoring finished / results on the host
+    bool fetch_pending = false;
     cudaStream_t side_stream = nullptr;          // the leftover scorer runs beside k_score_finish
     cudaEvent_t side_fork = nullptr, side_join = nullptr;
     bool pf_pending = false;
@@ -408,6 +410,8 @@ void mb_destroy(mb_ctx *ctx) {
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     if (ctx->pf_done) cudaEventDestroy(ctx->pf_done);
+    if (ctx->fetch_done) { cudaEventSynchronize(ctx->fetch_done); cudaEventDestroy(ctx->fetch_done); }
+    if (ctx->fetch_ready) cudaEventDestroy(ctx->fetch_ready);
     if (ctx->fq_pf_done) cudaEventDestroy(ctx->fq_pf_done);
     if (ctx->side_stream) { cudaStreamSynchronize(ctx->side_stream); cudaStreamDestroy(ctx->side_stream); }
     if (ctx->side_fork) cudaEventDestroy(ctx->side_fork);
@@ -1288,6 +1292,9 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
     if (!ctx->have_matches || !ctx->matches_sorted) return fail(ctx, MB_E_ARG, "sorted matches required");
     if (!ctx->have_reads) return fail(ctx, MB_E_ARG, "reads must be staged (lengths are needed)");
     CK(cudaSetDevice(ctx->par.device));
+    // results of the previous batch still on their way to the host (mb_fetch_results_async): they leave before the result
+    // arrays are written again (the copy was enqueued a whole batch ago, so this does not wait in practice)
+    if (ctx->fetch_pending) { CK(cudaEventSynchronize(ctx->fetch_done)); ctx->fetch_pending = false; }
     const u32 nr = ctx->n_reads;
     ctx->tc_used = 0;
     if (nr) {
@@ -1491,6 +1498,43 @@ int mb_fetch_results(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, i
     }
     mark(ctx, EV_D2H);
     CK(cudaStreamSynchronize(ctx->stream));
+    return MB_OK;
+}
+
+// The device->host copy of the results on the copy stream: the caller goes on with the next batch (stage, extract, sort,
+// join) while the results travel; mb_fetch_wait before the host arrays are read.
+int mb_fetch_results_async(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap) {
+    if (!ctx || (!results && ctx->n_reads)) return MB_E_ARG;
+    if (!ctx->have_results) return fail(ctx, MB_E_ARG, "no results resident");
+    if (taxcnt_cap < ctx->tc_used) return fail(ctx, MB_E_CAPACITY, "taxcnt arrays too small");
+    CK(cudaSetDevice(ctx->par.device));
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->pf_done, cudaEventDisableTiming));
+    }
+    if (!ctx->fetch_done) {
+        CK(cudaEventCreateWithFlags(&ctx->fetch_ready, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->fetch_done, cudaEventDisableTiming));
+    }
+    if (ctx->fetch_pending) CK(cudaEventSynchronize(ctx->fetch_done));         // one transfer in flight at a time
+    CK(cudaEventRecord(ctx->fetch_ready, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->fetch_ready, 0));
+    if (ctx->n_reads) CK(cudaMemcpyAsync(results, ctx->results.p, (size_t) ctx->n_reads * sizeof(mb_read_result), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (ctx->tc_used) {
+        CK(cudaMemcpyAsync(taxcnt_id, ctx->tc_id.p, ctx->tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->copy_stream));
+        CK(cudaMemcpyAsync(taxcnt_n, ctx->tc_cnt.p, ctx->tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    }
+    CK(cudaEventRecord(ctx->fetch_done, ctx->copy_stream));
+    ctx->fetch_pending = true;
+    return MB_OK;
+}
+int mb_fetch_wait(mb_ctx *ctx) {
+    if (!ctx) return MB_E_ARG;
+    if (ctx->fetch_pending) {
+        CK(cudaSetDevice(ctx->par.device));
+        CK(cudaEventSynchronize(ctx->fetch_done));
+        ctx->fetch_pending = false;
+    }
     return MB_OK;
 }
 

@@ -349,6 +349,40 @@ def test_long_read_sort_orders_dna_ties(golden, mb):
         clf.close()
 
 
+def test_async_result_fetch(golden, mb):
+    """mb_fetch_results_async / mb_fetch_wait: the same arrays as mb_fetch_results, also when the next batch is started
+    before the wait (its scoring must not overwrite results that are still travelling)."""
+    import torch
+    _, s1, s2 = golden.reads("sync_paired")
+    half = len(s1) // 2
+    a = mb.pack_reads(s1[:half], s2[:half])
+    b = mb.pack_reads(s1[half:], s2[half:])
+    clf = mb.Classifier(golden.dbdir("sync_paired"), seq_mode=2)
+    try:
+        def pinned(n, dt):
+            t = torch.zeros(n * np.dtype(dt).itemsize, dtype=torch.uint8).pin_memory()
+            return t, t.numpy().view(dt)
+        want = []
+        for bases, offsets, lens in (a, b):
+            res, ids, cnt = clf.classify(bases, offsets, lens)
+            want.append((res.copy(), ids.copy(), cnt.copy()))
+        keep, got = [], []
+        for bases, offsets, lens in (a, b):
+            clf.stage(bases, offsets, lens)
+            used = clf.classify_staged()
+            tr, res = pinned(len(lens) // 2, mb.RESULT_DT)
+            ti, ids = pinned(used + 1, np.int32)
+            tc, cnt = pinned(used + 1, np.int32)
+            keep.append((tr, ti, tc))
+            clf.fetch_async(res, ids, cnt)              # no wait: the next batch starts while these travel
+            got.append((res, ids, cnt, used))
+        clf.fetch_wait()
+        for (wr, wi, wc), (res, ids, cnt, used) in zip(want, got):
+            assert compare_results(res, ids, cnt, wr, wi, wc) == []
+    finally:
+        clf.close()
+
+
 def test_medium_random(mb, tmp_path):
     """A larger seeded case built on the box: 54 genomes x 60 kb, 20k pairs + long reads (multi-tile sort,
     hundreds of DB blocks), plain and syncmer."""
