@@ -623,12 +623,29 @@ def run_b200(a):
             used += u
         return used
 
+    e2e_host = {"stage": 0.0, "prefetch": 0.0, "classify": 0.0, "fetch": 0.0, "n": 0}     # MB_BENCH_HOST_TIMES=1: host seconds per call
+
     def e2e_step():
         if multi:
             return e2e_step_multi()
         cur = pin_in[e2e_i[0] & 1]
         nxt = pin_in[(e2e_i[0] + 1) & 1]
         e2e_i[0] += 1
+        if os.environ.get("MB_BENCH_HOST_TIMES") and not sharded:
+            t0 = time.perf_counter()
+            clf.stage(cur[1], cur[2], cur[3], bases_ptr=cur[0].data_ptr())
+            t1 = time.perf_counter()
+            clf.prefetch(nxt[1], nxt[2], nxt[3], bases_ptr=nxt[0].data_ptr())
+            t2 = time.perf_counter()
+            used = clf.classify_staged()
+            t3 = time.perf_counter()
+            clf.fetch_wait()
+            clf.fetch_async(*res_sets[e2e_i[0] & 1])
+            t4 = time.perf_counter()
+            for k, v in (("stage", t1 - t0), ("prefetch", t2 - t1), ("classify", t3 - t2), ("fetch", t4 - t3)):
+                e2e_host[k] += v
+            e2e_host["n"] += 1
+            return used
         if sharded:
             sharded.stage(cur[1], cur[2], cur[3], bases_ptr=cur[0].data_ptr())
             clf.prefetch(nxt[1], nxt[2], nxt[3], bases_ptr=nxt[0].data_ptr())
@@ -713,6 +730,8 @@ def run_b200(a):
     for _ in range(a.steps):
         used = e2e_step()
     clf.fetch_wait()                                       # the last step's results are on the host: inside the timed region
+    if e2e_host["n"]:
+        log("e2e host ms per step: " + ", ".join(f"{k} {1e3 * v / e2e_host['n']:.3f}" for k, v in e2e_host.items() if k != "n"))
     e1.record(stream)
     barrier()
     wall_e2e = time.perf_counter() - w0

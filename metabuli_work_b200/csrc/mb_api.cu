@@ -6,6 +6,7 @@
 // Everything runs on one CUDA stream; the only host synchronisations per batch are four 8-byte
 // read-backs (k-mer count, match count, longest per-read match list, taxCnt size) that size the next
 // launch.  There is no CPU fallback anywhere in this file.
+#include <chrono>
 #include <cmath>
 
 #include "mb_common.cuh"
@@ -233,9 +234,22 @@ static void mark(mb_ctx *ctx, int ev) {
     ctx->ev_set[ev] = true;
 }
 
+__global__ void k_read_back(u32 *__restrict__ host_dst, const u32 *__restrict__ src, u32 n_words) {
+    if (threadIdx.x < n_words) host_dst[threadIdx.x] = src[threadIdx.x];
+    __threadfence_system();
+}
+
 template <class T>
 static int read_back(mb_ctx *ctx, const T *dptr, T *out) {
-    CK(cudaMemcpyAsync(ctx->pinned, dptr, sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    // A few bytes from the device, synchronously.  Not a cudaMemcpy: a device->host memcpy queues on the DMA engine behind a
+    // result transfer that mb_fetch_results_async has in flight (0.9 ms at configs[1], measured in mb_stage_reads); a
+    // one-warp kernel writes the words straight into the page-locked host buffer instead (unified addressing).
+    if constexpr (sizeof(T) % 4 == 0 && sizeof(T) <= 256) {
+        k_read_back<<<1, 64, 0, ctx->stream>>>(reinterpret_cast<u32 *>(ctx->pinned), reinterpret_cast<const u32 *>(dptr), (u32) (sizeof(T) / 4));
+        CK(cudaGetLastError());
+    } else {
+        CK(cudaMemcpyAsync(ctx->pinned, dptr, sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    }
     CK(cudaStreamSynchronize(ctx->stream));
     memcpy(out, ctx->pinned, sizeof(T));
     return MB_OK;
@@ -385,7 +399,7 @@ mb_ctx *mb_create(const mb_params *p) {
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
     ok = ok && cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, p->device) == cudaSuccess && ctx->sms > 0;
     for (int i = 0; ok && i < EV_COUNT; ++i) ok = cudaEventCreate(&ctx->ev[i]) == cudaSuccess;
-    ok = ok && cudaHostAlloc(&ctx->pinned, 256, cudaHostAllocDefault) == cudaSuccess;
+    ok = ok && cudaHostAlloc(&ctx->pinned, 256, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess;
     ok = ok && ctx->tables.ensure(sizeof(Tables)) == cudaSuccess && ctx->counters.ensure(sizeof(Counters)) == cudaSuccess;
     if (ok) {
         Tables t;
