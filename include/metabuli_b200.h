@@ -226,7 +226,9 @@ int mb_fetch_results(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, i
 /* The same copy without waiting for it: enqueued on the copy stream behind the scoring, so the caller can stage and run the
  * next batch while the results travel (page-locked host arrays for a truly asynchronous copy).  The host arrays are valid
  * after mb_fetch_wait; one transfer is in flight at a time, and the next mb_score_reads waits for it before it writes the
- * result arrays again.  (The reference writes its results on the thread that computed them, Classifier.cpp:133-150; this
+ * result arrays again.  The results stay fetchable after the NEXT batch has been staged and extracted (only its scoring
+ * overwrites them): starting the transfer after the next batch's mb_extract_kmers keeps it off the host link while the
+ * staging and extraction read their counts.  (The reference writes its results on the thread that computed them, Classifier.cpp:133-150; this
  * is the overlap its OpenMP batch loop cannot have.) */
 int mb_fetch_results_async(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap);
 int mb_fetch_wait(mb_ctx *ctx);

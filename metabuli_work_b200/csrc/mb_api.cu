@@ -129,6 +129,9 @@ struct mb_ctx {
     cudaEvent_t pf_done = nullptr;
     cudaEvent_t fetch_ready = nullptr, fetch_done = nullptr;   // mb_fetch_results_async: scoring finished / results on the host
     bool fetch_pending = false;
+    bool res_valid = false;            // the result arrays hold a scored batch (until the next mb_score_reads starts): what
+    u32 res_n_reads = 0;               // mb_fetch_results_async copies, also after the NEXT batch has been staged
+    u64 res_tc_used = 0;
     cudaStream_t side_stream = nullptr;          // the leftover scorer runs beside k_score_finish
     cudaEvent_t side_fork = nullptr, side_join = nullptr;
     bool pf_pending = false;
@@ -1309,6 +1312,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
     // results of the previous batch still on their way to the host (mb_fetch_results_async): they leave before the result
     // arrays are written again (the copy was enqueued a whole batch ago, so this does not wait in practice)
     if (ctx->fetch_pending) { CK(cudaEventSynchronize(ctx->fetch_done)); ctx->fetch_pending = false; }
+    ctx->res_valid = false;
     const u32 nr = ctx->n_reads;
     ctx->tc_used = 0;
     if (nr) {
@@ -1496,6 +1500,7 @@ int mb_score_reads(mb_ctx *ctx, size_t *taxcnt_used) {
     }
     mark(ctx, EV_SCORE);
     ctx->have_results = true;
+    ctx->res_valid = true; ctx->res_n_reads = ctx->n_reads; ctx->res_tc_used = ctx->tc_used;
     if (taxcnt_used) *taxcnt_used = ctx->tc_used;
     return MB_OK;
 }
@@ -1518,9 +1523,11 @@ int mb_fetch_results(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, i
 // The device->host copy of the results on the copy stream: the caller goes on with the next batch (stage, extract, sort,
 // join) while the results travel; mb_fetch_wait before the host arrays are read.
 int mb_fetch_results_async(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt_id, int32_t *taxcnt_n, size_t taxcnt_cap) {
-    if (!ctx || (!results && ctx->n_reads)) return MB_E_ARG;
-    if (!ctx->have_results) return fail(ctx, MB_E_ARG, "no results resident");
-    if (taxcnt_cap < ctx->tc_used) return fail(ctx, MB_E_CAPACITY, "taxcnt arrays too small");
+    if (!ctx || (!results && ctx->res_n_reads)) return MB_E_ARG;
+    // the last scored batch: still resident after the next batch has been staged and extracted (only the next scoring
+    // overwrites it), so the transfer can be started wherever it disturbs the next batch least
+    if (!ctx->res_valid) return fail(ctx, MB_E_ARG, "no results resident");
+    if (taxcnt_cap < ctx->res_tc_used) return fail(ctx, MB_E_CAPACITY, "taxcnt arrays too small");
     CK(cudaSetDevice(ctx->par.device));
     if (!ctx->copy_stream) {
         CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -1533,10 +1540,10 @@ int mb_fetch_results_async(mb_ctx *ctx, mb_read_result *results, int32_t *taxcnt
     if (ctx->fetch_pending) CK(cudaEventSynchronize(ctx->fetch_done));         // one transfer in flight at a time
     CK(cudaEventRecord(ctx->fetch_ready, ctx->stream));
     CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->fetch_ready, 0));
-    if (ctx->n_reads) CK(cudaMemcpyAsync(results, ctx->results.p, (size_t) ctx->n_reads * sizeof(mb_read_result), cudaMemcpyDeviceToHost, ctx->copy_stream));
-    if (ctx->tc_used) {
-        CK(cudaMemcpyAsync(taxcnt_id, ctx->tc_id.p, ctx->tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->copy_stream));
-        CK(cudaMemcpyAsync(taxcnt_n, ctx->tc_cnt.p, ctx->tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (ctx->res_n_reads) CK(cudaMemcpyAsync(results, ctx->results.p, (size_t) ctx->res_n_reads * sizeof(mb_read_result), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (ctx->res_tc_used) {
+        CK(cudaMemcpyAsync(taxcnt_id, ctx->tc_id.p, ctx->res_tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->copy_stream));
+        CK(cudaMemcpyAsync(taxcnt_n, ctx->tc_cnt.p, ctx->res_tc_used * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->copy_stream));
     }
     CK(cudaEventRecord(ctx->fetch_done, ctx->copy_stream));
     ctx->fetch_pending = true;
