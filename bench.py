@@ -690,7 +690,10 @@ def run_b200(a):
             rebalance_log.append([round(x, 2) for x in t_own])
             if max(t_own) <= float(os.environ.get("MB_REBALANCE_THRESHOLD", "1.06")) * (sum(t_own) / world):     # (test knob: 0 forces a round)
                 break
-            cut_fractions = mb.rebalanced_cuts(t_own, cut_fractions)
+            moved = mb.rebalanced_cuts(t_own, cut_fractions)
+            if not np.all(np.diff(np.concatenate([[0.0], moved, [1.0]])) > 1e-4):      # degenerate times: keep the shards as they are
+                break
+            cut_fractions = moved
             sharded.close()
             del sharded
             clf.close()

@@ -264,7 +264,9 @@ int runClassifyMulti(const std::vector<std::string> &inputs, const std::string &
             ++rebalanceRounds;
             if (worst > threshold * mean) {
                 const std::vector<double> moved = rebalancedCuts(t, cutFrac.empty() ? nullptr : cutFrac.data());
-                if (moved.size() == (size_t) n - 1) {
+                bool sane = moved.size() == (size_t) n - 1;
+                for (size_t i = 0; sane && i < moved.size(); ++i) sane = moved[i] > (i ? moved[i - 1] : 0.0) + 1e-4 && moved[i] < 1.0 - 1e-4;
+                if (sane) {
                     cutFrac = moved;
                     if (!openShards(cutFrac.data())) return 1;
                     std::cout << "DB shards re-balanced by owner time (slowest " << worst << " ms, mean " << mean << " ms)" << std::endl;
