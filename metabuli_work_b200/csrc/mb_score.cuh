@@ -1178,10 +1178,43 @@ __device__ __forceinline__ int count_taxa_warp(int max_q, ReadScratch &scr) {
 // candidate is handled, after which the scan resumes behind it with the trimmed candidate — the same sequence of trims and
 // rejections as the sequential loop, since accepted paths that do not overlap leave the candidate unchanged.
 // Warp-synchronous; every lane calls it with the same arguments and gets the same result.
+// The sort of combineMatchPaths for a species with many paths, by the whole warp.  std::sort's result is unique when no
+// two paths tie under the comparator; then ANY correct sort reproduces it.  So: a copy of the paths is sorted with a
+// bitonic network in global memory (all exchanges ascending, the virtual padding beyond n stays in place), ties are looked
+// for among neighbours, and only if there is one the untouched original goes through the literal introsort (path_sort)
+// on one lane as before.  (Profile at configs[4]: the one-lane sort was 55 % of k_lr_species.)
+__device__ __forceinline__ void warp_sort_paths(PathRec *paths, PathRec *tmp, int n) {
+    const int lane = (int) (threadIdx.x & 31);
+    for (int i = lane; i < n; i += 32) tmp[i] = paths[i];
+    __syncwarp();
+    int n_pad = 1;
+    while (n_pad < n) n_pad <<= 1;
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = lane; t < n_pad / 2; t += 32) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int p = j == (k >> 1) ? (i ^ (k - 1)) : (i | j);        // first step of a merge: flip partner
+                if (p < n && p > i) {
+                    const PathRec a = tmp[i], b = tmp[p];
+                    if (path_before(b, a)) { tmp[i] = b; tmp[p] = a; }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    bool tie = false;
+    for (int i = lane; i + 1 < n; i += 32) tie = tie || !path_before(tmp[i], tmp[i + 1]);
+    if (__any_sync(0xFFFFFFFFu, tie)) {
+        if (lane == 0) path_sort(paths, paths + n);
+    } else {
+        for (int i = lane; i < n; i += 32) paths[i] = tmp[i];
+    }
+    __syncwarp();
+}
+
 __device__ __noinline__ float combine_paths_warp(const mb_match *m, PathRec *paths, PathRec *comb, int n_paths, int read_length) {
     const int lane = (int) (threadIdx.x & 31);
-    if (lane == 0) path_sort(paths, paths + n_paths);
-    __syncwarp();
+    warp_sort_paths(paths, comb, n_paths);
     int n_comb = 0;
     float score = 0.f;
     for (int i = 0; i < n_paths; ++i) {
