@@ -10,6 +10,9 @@
 #include <cmath>
 
 #include "mb_common.cuh"
+#ifndef MB_RADIX_V2_DEFAULT
+#define MB_RADIX_V2_DEFAULT true
+#endif
 #include "mb_extract.cuh"
 #include "mb_radix.cuh"
 #include "mb_match.cuh"
@@ -285,9 +288,14 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     if (seg.n) CK(a.ensure(n * sizeof(Rec)));
     constexpr u64 TILE = (u64) RS_THREADS * ITEMS;
     const u64 tiles = (n + TILE - 1) / TILE;
+    // the pass with the tile kept in shared memory (k_radix_pass2: half the items per thread)
+    constexpr bool HAS_V2 = ITEMS % 2 == 0 && ITEMS >= 8;
+    constexpr int ITEMS2 = HAS_V2 ? ITEMS / 2 : ITEMS;
+    constexpr u64 TILE2 = (u64) R2_THREADS * ITEMS2;
+    const u64 tiles2 = (n + TILE2 - 1) / TILE2;
     CK(b.ensure(n * sizeof(Rec)));
     CK(ctx->hist.ensure(sizeof(u64) * RS_BINS * RS_MAX_PASSES));
-    CK(ctx->tile_state.ensure(tiles * RS_BINS * sizeof(u64)));
+    CK(ctx->tile_state.ensure(std::max(tiles, tiles2) * RS_BINS * sizeof(u64)));
     CK(cudaMemsetAsync(ctx->hist.p, 0, sizeof(u64) * RS_BINS * n_passes, ctx->stream));
     CK(cudaMemsetAsync(&ctx->dcnt()->trivial, 0, sizeof(u32) * RS_MAX_PASSES, ctx->stream));
     const u64 hist_ctas = std::min<u64>((n + RS_THREADS - 1) / RS_THREADS, (u64) ctx->sms * 8);
@@ -301,14 +309,36 @@ static int radix_sort(mb_ctx *ctx, DevBuf &a, DevBuf &b, u64 n, const Key &key, 
     constexpr size_t smem = radix_pass_smem<Rec, ITEMS>();
     static const int radix_dbg = getenv("MB_RADIX_DBG") ? atoi(getenv("MB_RADIX_DBG")) : 0;     // timing experiments only
     const unsigned slot_bit = 1u << (radix_slot<Rec, Key, ITEMS>() & 31);
+    static const bool radix_v2 = getenv("MB_RADIX_V2") ? atoi(getenv("MB_RADIX_V2")) != 0 : MB_RADIX_V2_DEFAULT;
     if (!(ctx->radix_attr_mask & slot_bit)) {
         CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         CK(cudaFuncSetAttribute(k_radix_pass<Rec, Key, ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        if constexpr (HAS_V2) {
+            CK(cudaFuncSetAttribute(k_radix_pass2<Rec, Key, ITEMS2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) radix_pass2_smem<Rec, ITEMS2>()));
+            CK(cudaFuncSetAttribute(k_radix_pass2<Rec, Key, ITEMS2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) radix_pass2_smem<Rec, ITEMS2>()));
+        }
         ctx->radix_attr_mask |= slot_bit;
     }
     for (int p = 0; p < n_passes; ++p) {
-        CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * RS_BINS * sizeof(u64), ctx->stream));
+        const bool v2 = HAS_V2 && radix_v2 && !radix_dbg;
+        CK(cudaMemsetAsync(ctx->tile_state.p, 0, (v2 ? tiles2 : tiles) * RS_BINS * sizeof(u64), ctx->stream));
         CK(cudaMemsetAsync(&ctx->dcnt()->radix_ticket, 0, sizeof(u32), ctx->stream));
+        if constexpr (HAS_V2) {
+            if (v2) {
+                if (seg.n)
+                    KL(kid_base + 2, k_radix_pass2<Rec, Key, ITEMS2, true><<<(unsigned) tiles2, R2_THREADS, radix_pass2_smem<Rec, ITEMS2>(), ctx->stream>>>(
+                        a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
+                        &ctx->dcnt()->radix_ticket, seg));
+                else
+                    KL(kid_base + 2, k_radix_pass2<Rec, Key, ITEMS2, false><<<(unsigned) tiles2, R2_THREADS, radix_pass2_smem<Rec, ITEMS2>(), ctx->stream>>>(
+                        a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
+                        &ctx->dcnt()->radix_ticket, seg));
+                seg.n = 0;
+                std::swap(a.p, b.p);
+                std::swap(a.cap, b.cap);
+                continue;
+            }
+        }
         if (seg.n)
             KL(kid_base + 2, k_radix_pass<Rec, Key, ITEMS, true><<<(unsigned) tiles, RS_THREADS, smem, ctx->stream>>>(
                 a.as<Rec>(), b.as<Rec>(), n, key, p, ctx->hist.as<u64>() + (size_t) p * RS_BINS, ctx->tile_state.as<u64>(),
@@ -1935,8 +1965,8 @@ int mb_get_kernel_times(mb_ctx *ctx, mb_kernel_time *out, size_t cap, size_t *n)
 // call's contents: the parts that must start at zero are cleared on the stream before use, and two calls that overlap
 // on one GPU race on it.
 namespace {
-constexpr int NA_ITEMS = 16;                                              // records per thread, as mb_sort_kmers
-constexpr u64 NA_TILE = (u64) RS_THREADS * NA_ITEMS;
+constexpr int NA_ITEMS2 = 8;                                              // records per thread of k_radix_pass2, as mb_sort_kmers
+constexpr u64 NA_TILE = (u64) R2_THREADS * NA_ITEMS2;
 constexpr u64 NA_MAX_TILES = (MB_NOALLOC_MAX_KMERS + NA_TILE - 1) / NA_TILE;
 struct NoallocScratch {
     u64 hist[RS_MAX_PASSES * RS_BINS];                                    // 32 KB
@@ -1961,10 +1991,10 @@ int noalloc_setup(mb_ctx *ctx, NoallocScratch **out) {
     if (!d.ready) {
         void *p = nullptr;
         CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
-        constexpr int smem = (int) radix_pass_smem<mb_kmer, NA_ITEMS>();
-        CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKey, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKeyPacked, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        CK(cudaFuncSetAttribute(k_radix_pass<mb_kmer, KmerKeyPacked7, NA_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        constexpr int smem = (int) radix_pass2_smem<mb_kmer, NA_ITEMS2>();
+        CK(cudaFuncSetAttribute(k_radix_pass2<mb_kmer, KmerKey, NA_ITEMS2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CK(cudaFuncSetAttribute(k_radix_pass2<mb_kmer, KmerKeyPacked, NA_ITEMS2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CK(cudaFuncSetAttribute(k_radix_pass2<mb_kmer, KmerKeyPacked7, NA_ITEMS2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         d.scratch = reinterpret_cast<NoallocScratch *>(p);
         d.ready = true;
     }
@@ -1975,7 +2005,7 @@ int noalloc_setup(mb_ctx *ctx, NoallocScratch **out) {
 template <typename Key>
 int noalloc_sort(mb_ctx *ctx, cudaStream_t st, NoallocScratch *sc, mb_kmer *a, mb_kmer *b, u64 n, const Key &key, int n_passes) {
     const u64 tiles = (n + NA_TILE - 1) / NA_TILE;
-    constexpr size_t smem = radix_pass_smem<mb_kmer, NA_ITEMS>();
+    constexpr size_t smem = radix_pass2_smem<mb_kmer, NA_ITEMS2>();
     const SegIn seg = {};
     CK(cudaMemsetAsync(sc->hist, 0, sizeof(u64) * RS_BINS * n_passes, st));
     CK(cudaMemsetAsync(sc->trivial, 0, sizeof(sc->trivial), st));
@@ -1987,8 +2017,8 @@ int noalloc_sort(mb_ctx *ctx, cudaStream_t st, NoallocScratch *sc, mb_kmer *a, m
     for (int p = 0; p < n_passes; ++p) {
         CK(cudaMemsetAsync(sc->tile_state, 0, tiles * RS_BINS * sizeof(u64), st));
         CK(cudaMemsetAsync(&sc->ticket, 0, sizeof(u32), st));
-        k_radix_pass<mb_kmer, Key, NA_ITEMS, false><<<(unsigned) tiles, RS_THREADS, smem, st>>>(a, b, n, key, p, sc->hist + (size_t) p * RS_BINS,
-                                                                                              sc->tile_state, &sc->ticket, 0, seg);
+        k_radix_pass2<mb_kmer, Key, NA_ITEMS2, false><<<(unsigned) tiles, R2_THREADS, smem, st>>>(a, b, n, key, p, sc->hist + (size_t) p * RS_BINS,
+                                                                                                sc->tile_state, &sc->ticket, seg);
         CK(cudaGetLastError());
         std::swap(a, b);
     }

@@ -340,4 +340,247 @@ constexpr size_t radix_pass_smem() {
     return sizeof(Rec) * RS_THREADS * ITEMS + sizeof(u32) * (RS_WARPS * RS_BINS + RS_BINS) + sizeof(u64) * RS_BINS + RS_THREADS * ITEMS;
 }
 
+
+// ---- one pass, second form: the tile stays in shared memory ------------------------------------------------
+// k_radix_pass keeps a thread's records in registers (126 of them: 16 warps per SM, and every warp issues on half of its
+// cycles while it waits on its own ballots and shared-memory atomics).  Here the tile is brought in by ONE bulk copy
+// (cp.async.bulk global -> shared, completion on an mbarrier) and never enters the register file: a thread reads the
+// keys of its items from shared memory, ranks them (same stable warp multisplit), and the tile leaves through a
+// permutation — slot p of the digit-ordered tile holds (digit << 16 | source index) — so that 512 threads x 2 CTAs
+// = 32 warps per SM fit (<= 64 registers), twice the warps to cover the same latencies.  Tiles are as large as before
+// (same look-back chain, same tile_state).  Whole tiles only take the bulk copy; the last, partial tile is copied by the
+// threads, and so are tiles that straddle two regions of a segmented input (peer receive regions) or start off a 16-byte
+// boundary there.
+#ifndef MB_R2_THREADS
+#define MB_R2_THREADS 512
+#endif
+#ifndef MB_R2_LB
+#define MB_R2_LB 6
+#endif
+
+constexpr int R2_THREADS = MB_R2_THREADS;  // 512 x 2 CTAs or 256 x 4 CTAs per SM
+constexpr int R2_WARPS = R2_THREADS / 32;
+constexpr int R2_LB = MB_R2_LB;            // predecessors read per look-back round (independent loads)
+constexpr u32 R2_PAD = 0x100u;              // digit of a padding slot of the partial tile (bit 8 keeps it apart from digit 0)
+
+// peers &= lanes whose digit agrees with mine in bit BIT (whole warp converged)
+template <int BIT>
+__device__ __forceinline__ void peers_bit(u32 &peers, u32 d) {
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 ".reg .b32 m, t;\n"
+                 "and.b32 t, %1, %2;\n"
+                 "setp.ne.u32 p, t, 0;\n"
+                 "vote.sync.ballot.b32 m, p, 0xffffffff;\n"
+                 "@!p not.b32 m, m;\n"
+                 "and.b32 %0, %0, m;\n"
+                 "}\n" : "+r"(peers) : "r"(d), "n"(1 << BIT));
+}
+
+template <typename Rec, int ITEMS>
+constexpr size_t radix_pass2_smem() {
+    return sizeof(Rec) * R2_THREADS * ITEMS + sizeof(u64) * RS_BINS + sizeof(u32) * R2_THREADS * ITEMS +
+           sizeof(u32) * R2_WARPS * RS_BINS;
+}
+
+template <typename Rec, typename Key, int ITEMS, bool SEG>
+__global__ void __launch_bounds__(R2_THREADS, 1024 / R2_THREADS)
+k_radix_pass2(const Rec *__restrict__ in, Rec *__restrict__ out, u64 n, Key key, int pass,
+              const u64 *__restrict__ digit_base /*[256] exclusive*/, u64 *tile_state /*[tiles][256]*/, u32 *ticket,
+              const __grid_constant__ SegIn seg) {
+    constexpr int TILE = R2_THREADS * ITEMS;
+    constexpr u32 W = sizeof(Rec) / 8;
+    static_assert(sizeof(Rec) % 8 == 0 && (sizeof(Rec) * TILE) % 16 == 0 && TILE <= 65536, "tile: whole 16-byte units, 16-bit indices");
+    extern __shared__ __align__(128) unsigned char s_raw[];
+    Rec *s_rec = reinterpret_cast<Rec *>(s_raw);                                   // TILE records, in input order
+    u64 *s_gbase = reinterpret_cast<u64 *>(s_raw + sizeof(Rec) * TILE);            // [256]
+    u32 *s_perm = reinterpret_cast<u32 *>(s_gbase + RS_BINS);                      // [TILE] digit << 16 | source index
+    u32 *s_whist = s_perm + TILE;                                                  // [R2_WARPS][256]
+    __shared__ u32 s_tile;
+    __shared__ u32 s_scan[RS_BINS / 32];
+    __shared__ u32 s_cnt[RS_BINS];
+    __shared__ __align__(8) u64 s_mbar;
+
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        s_tile = atomicAdd(ticket, 1u);
+        mbar_init(&s_mbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = tid; i < R2_WARPS * RS_BINS / 4; i += R2_THREADS) reinterpret_cast<uint4 *>(s_whist)[i] = make_uint4(0, 0, 0, 0);
+    if (tid < RS_BINS) s_cnt[tid] = 0;
+    __syncthreads();
+    const u32 tile = s_tile;
+    const u64 tile_base = (u64) tile * TILE;
+    const u32 valid = (u32) (n - tile_base < (u64) TILE ? n - tile_base : (u64) TILE);
+    const bool full = valid == (u32) TILE;
+    // SEG: the input lies in a few regions (SegIn); a tile inside one region reads through one rebased pointer
+    const Rec *src = in + tile_base;
+    bool split = false;
+    if (SEG) {
+        u32 r = 0;
+        while (r + 1 < seg.n && tile_base >= seg.prefix[r + 1]) ++r;
+        src = reinterpret_cast<const Rec *>(seg.base[r]) + (tile_base - seg.prefix[r]);
+        split = r + 1 < seg.n && tile_base + valid > seg.prefix[r + 1];
+    }
+    // the bulk copy wants a whole tile at a 16-byte boundary (24-byte records inside a region start at one every other time)
+    const bool bulk = full && !split && (reinterpret_cast<size_t>(src) & 15) == 0;
+    if (bulk) {
+        if (tid == 0) {
+            constexpr u32 BYTES = (u32) (sizeof(Rec) * TILE), CHUNK = 16384;
+            mbar_expect_tx(&s_mbar, BYTES);
+            const char *srcb = reinterpret_cast<const char *>(src);
+            for (u32 o = 0; o < BYTES; o += CHUNK) bulk_g2s(s_raw + o, srcb + o, BYTES - o < CHUNK ? BYTES - o : CHUNK, &s_mbar);
+        }
+    } else if (SEG && split) {
+        for (u32 i = tid; i < valid; i += R2_THREADS) s_rec[i] = *seg_ptr(seg, in, tile_base + i);
+    } else {
+        const u64 *in_w = reinterpret_cast<const u64 *>(src);
+        u64 *s_w = reinterpret_cast<u64 *>(s_rec);
+        for (u32 wi = tid; wi < valid * W; wi += R2_THREADS) s_w[wi] = in_w[wi];
+    }
+    if (!SEG) {   // the tile a CTA starting about one machine-full of CTAs later will ask for: into L2 now
+        constexpr u64 AHEAD = 148ull * 4096 / TILE;
+        constexpr u32 TILE_BYTES = (u32) (sizeof(Rec) * TILE);
+        const u64 pf_base = (tile_base + AHEAD * TILE) * sizeof(Rec);
+        const u64 end_bytes = n * sizeof(Rec);
+        if (pf_base + TILE_BYTES <= end_bytes) {
+#pragma unroll
+            for (u32 o = 0; o < TILE_BYTES; o += R2_THREADS * 128)
+                if (o + tid * 128 < TILE_BYTES) prefetch_l2(reinterpret_cast<const char *>(in) + pf_base + o + tid * 128);
+        }
+    }
+    if (bulk) mbar_wait(&s_mbar, 0);
+    else __syncthreads();
+
+    // digits of my items (warp-striped: item j of lane l is tile record warp*32*ITEMS + j*32 + l)
+    u32 dig[ITEMS];
+    u32 rank[ITEMS];
+    const u32 wbase = warp * 32 * ITEMS;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u32 idx = wbase + (u32) j * 32 + lane;
+        dig[j] = (full || idx < valid) ? key.digit(s_rec[idx], pass) : R2_PAD;
+    }
+    // early counts: the tile's digit histogram is published BEFORE the ranking (successors look back at it), and the
+    // positions of the digits in the digit-ordered tile are scanned now, off the critical path
+    volatile u64 *state = tile_state;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j)
+        if (dig[j] != R2_PAD) atomicAdd(&s_cnt[dig[j]], 1u);
+    __syncthreads();
+    u32 cnt_d = 0, incl_c = 0;
+    if (tid < RS_BINS) {
+        cnt_d = s_cnt[tid];
+        state[(u64) tile * RS_BINS + tid] = (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | cnt_d;
+        incl_c = cnt_d;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl_c, o);
+            if (lane >= (u32) o) incl_c += t;
+        }
+        if (lane == 31) s_scan[warp] = incl_c;
+    }
+
+    // stable ranking inside the warp, items ordered by (j, lane) == memory order
+    u32 *wh = s_whist + warp * RS_BINS;
+    const u32 lt = (1u << lane) - 1u;
+    // Three sweeps, so that nothing waits on a shared-memory atomic it has just issued: (1) per item the lanes holding
+    // the same digit — one ballot per digit bit (test, vote, conditional complement, and); (2) the first lane of every
+    // group advances the warp's running count of the digit (one predicated atomic per item, issued back to back: they
+    // reach shared memory in program order); (3) the old count travels to the group, plus the lane's rank in it.
+    u32 peers[ITEMS];
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u32 d = dig[j];
+        u32 p = 0xFFFFFFFFu;
+        peers_bit<0>(p, d); peers_bit<1>(p, d); peers_bit<2>(p, d); peers_bit<3>(p, d);
+        peers_bit<4>(p, d); peers_bit<5>(p, d); peers_bit<6>(p, d); peers_bit<7>(p, d);
+        if (!full) peers_bit<8>(p, d);               // (block-uniform) padding slots only ever match each other
+        peers[j] = p;
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u32 d = dig[j];
+        const u32 first = (d != R2_PAD && (peers[j] & lt) == 0u) ? 1u : 0u;
+        u32 pre = 0;
+        asm volatile("{\n"
+                     ".reg .pred p;\n"
+                     "setp.ne.u32 p, %3, 0;\n"
+                     "@p atom.shared.add.u32 %0, [%1], %2;\n"
+                     "}\n" : "+r"(pre) : "r"(smem_u32(wh + (d & 255u))), "r"((u32) __popc(peers[j])), "r"(first) : "memory");
+        rank[j] = pre;
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const int leader = __ffs(peers[j]) - 1;
+        rank[j] = __shfl_sync(0xFFFFFFFFu, rank[j], leader) + __popc(peers[j] & lt);
+    }
+    __syncthreads();
+
+    // per digit (thread == digit): where each warp's run of the digit starts in the digit-ordered tile, look-back
+    if (tid < RS_BINS) {
+        const u32 d = tid;
+        u32 start = incl_c - cnt_d;
+#pragma unroll
+        for (int w = 0; w < RS_BINS / 32; ++w) if ((u32) w < warp) start += s_scan[w];
+        u32 run = start;
+#pragma unroll
+        for (int w = 0; w < R2_WARPS; ++w) {
+            const u32 t = s_whist[w * RS_BINS + d];
+            s_whist[w * RS_BINS + d] = run;
+            run += t;
+        }
+        u64 excl = 0;
+        if (tile > 0) {
+            long long p = (long long) tile - 1;
+            bool done = false;
+            while (!done) {
+                u64 v[R2_LB];
+#pragma unroll
+                for (int k = 0; k < R2_LB; ++k) { v[k] = 2ull << 62; if (p - k >= 0) v[k] = state[(u64) (p - k) * RS_BINS + d]; }
+#pragma unroll
+                for (int k = 0; k < R2_LB; ++k) {
+                    if (done) break;
+                    if ((v[k] >> 62) == 0) break;        // not published yet: reload from here
+                    excl += v[k] & RS_VALUE_MASK;
+                    --p;
+                    if (v[k] & RS_FLAG_INC) done = true;
+                }
+            }
+            state[(u64) tile * RS_BINS + d] = RS_FLAG_INC | (excl + cnt_d);
+        }
+        s_gbase[d] = digit_base[d] + excl - start;       // out index = s_gbase[digit] + slot in the digit-ordered tile
+    }
+    __syncthreads();
+
+    // the permutation: slot of every item in the digit-ordered tile
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const u32 d = dig[j];
+        if (d != R2_PAD) {
+            const u32 pos = s_whist[warp * RS_BINS + d] + rank[j];
+            s_perm[pos] = (d << 16) | (wbase + (u32) j * 32 + lane);
+        }
+    }
+    __syncthreads();
+    if constexpr (sizeof(Rec) == 16) {
+        for (u32 i = tid; i < valid; i += R2_THREADS) {
+            const u32 pk = s_perm[i];
+            Rec r;
+            rec_load(r, s_rec + (pk & 0xFFFFu));
+            rec_store(out + s_gbase[pk >> 16] + i, r);
+        }
+    } else {
+        // other record sizes leave word by word: consecutive lanes write consecutive 8-byte words of a run
+        const u64 *s_w = reinterpret_cast<const u64 *>(s_rec);
+        u64 *out_w = reinterpret_cast<u64 *>(out);
+        for (u32 wi = tid; wi < valid * W; wi += R2_THREADS) {
+            const u32 r = wi / W, c = wi - r * W;
+            const u32 pk = s_perm[r];
+            out_w[(s_gbase[pk >> 16] + r) * W + c] = s_w[(pk & 0xFFFFu) * W + c];
+        }
+    }
+}
+
 } // namespace mb
