@@ -70,6 +70,27 @@ def test_noalloc_sort_matches_sort_kmers(mb, fmt, bits):
         ctx.close()
 
 
+@pytest.mark.parametrize("fmt,bits", [(2, 0), (2, 31), (2, 40), (1, 0)])
+def test_sort_is_the_stable_sort_by_key_at_tile_edges(mb, fmt, bits):
+    """mb_sort_kmers and mb_sort_kmers_noalloc against numpy's stable sort by the same key (tests/helpers.kmer_sort_key), at
+    sizes around the radix pass' 4096-record tile: one record, a partial tile, exactly one tile (the bulk-copy path), one
+    more, several tiles and a partial one.  Equal keys are common, so a rank that is not stable shows."""
+    import helpers
+    rng = np.random.default_rng(1000 + 10 * fmt + bits)
+    ctx = mb.RawContext(kmer_format=fmt, kmer_sort_bits=bits)
+    try:
+        for n in (1, 31, 4095, 4096, 4097, 8192, 3 * 4096 + 5, 40 * 4096 + 777):
+            k = _random_kmers(mb, rng, n, fmt)
+            key = helpers.kmer_sort_key(k["value"], bits, fmt)
+            expect = k[np.argsort(key, kind="stable")]
+            got = _sort_existing(ctx, k)
+            assert got.tobytes() == expect.tobytes(), (n, "mb_sort_kmers")
+            got = _sort_noalloc(mb, ctx, k)
+            assert got.tobytes() == expect.tobytes(), (n, "mb_sort_kmers_noalloc")
+    finally:
+        ctx.close()
+
+
 def test_noalloc_limits(mb):
     import torch
     ctx = mb.RawContext(kmer_format=2)
