@@ -391,19 +391,21 @@ static bool looksLikeFastq(const std::string &path, size_t &bytesPerRecord, size
     struct stat st;
     if (stat(path.c_str(), &st) != 0 || !S_ISREG(st.st_mode)) return false;
     fileSize = (size_t) st.st_size;
-    static char head[1 << 16];
+    std::vector<char> headBuf(1 << 16);
+    char *const head = headBuf.data();
+    const size_t headCap = headBuf.size();
     size_t n = 0;
     {
         FILE *fp = fopen(path.c_str(), "rb");
         if (!fp) return false;
-        n = fread(head, 1, sizeof(head), fp);
+        n = fread(head, 1, headCap, fp);
         fclose(fp);
     }
     gz = n >= 2 && (unsigned char) head[0] == 0x1f && (unsigned char) head[1] == 0x8b;
     if (gz) {
         gzFile g = gzopen(path.c_str(), "rb");
         if (!g) return false;
-        const int got = gzread(g, head, sizeof(head));
+        const int got = gzread(g, head, (unsigned) headCap);
         gzclose(g);
         n = got > 0 ? (size_t) got : 0;
     }
@@ -456,6 +458,12 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
     }
     std::atomic<bool> readerFailed{false};
     std::string readerErr;
+    std::mutex readerErrMu;
+    // first failure wins; the message is complete before the flag shows (two inflating threads may fail at once)
+    auto readerFail = [&](const std::string &msg) {
+        std::lock_guard<std::mutex> lk(readerErrMu);
+        if (!readerFailed) { readerErr = msg; readerFailed = true; }
+    };
     const bool timing = getenv("MB_TIMING") != nullptr;      // busy seconds of the three stages, on stderr
     double readBusy = 0, writeBusy = 0, gpuBusy = 0, pinBusy = 0;
     auto secondsSince = [](clk::time_point t) { return std::chrono::duration<double>(clk::now() - t).count(); };
@@ -472,7 +480,7 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
                     gzf[f] = gzopen(inputs[(size_t) f].c_str(), "rb");
                     if (gzf[f]) gzbuffer(gzf[f], 1u << 20);
                 } else fd[f] = ::open(inputs[(size_t) f].c_str(), O_RDONLY);
-                if (fd[f] < 0 && !gzf[f]) { readerErr = "cannot open " + inputs[(size_t) f]; readerFailed = true; }
+                if (fd[f] < 0 && !gzf[f]) readerFail("cannot open " + inputs[(size_t) f]);
             }
             // one file's share of a slot: `want` bytes of text behind the reserve (plain: pread by several threads; gzip: inflate)
             auto fillOne = [&](int si, int f) {
@@ -485,7 +493,7 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
                     if (f == 0) pinBusy += secondsSince(tp);
                     tb.pinned = tb.pin != nullptr;
                     if (!tb.pin) tb.pin = static_cast<char *>(malloc(tb.cap));
-                    if (!tb.pin) { if (!readerFailed.exchange(true)) readerErr = "out of host memory for the read buffers"; return; }
+                    if (!tb.pin) { readerFail("out of host memory for the read buffers"); return; }
                 }
                 if (reserve[f] + want + 64 <= tb.cap) tb.base = tb.pin;
                 else { tb.spill.resize(reserve[f] + want + 64); tb.base = tb.spill.data(); }
@@ -494,14 +502,14 @@ int runClassify(const std::vector<std::string> &inputs, const std::string &dbDir
                 if (isGz[f]) {
                     while (got < want) {
                         const int r = gzread(gzf[f], tb.data() + got, (unsigned) std::min<size_t>(want - got, 1u << 30));
-                        if (r < 0) { if (!readerFailed.exchange(true)) readerErr = "gzip error in " + inputs[(size_t) f]; return; }
+                        if (r < 0) { readerFail("gzip error in " + inputs[(size_t) f]); return; }
                         if (r == 0) { srcEof[f] = true; break; }
                         got += (size_t) r;
                     }
                     if (!srcEof[f] && gzeof(gzf[f])) srcEof[f] = true;
                 } else {
                     got = want;
-                    if (want && !preadParallel(fd[f], tb.data(), want, pos[f], ioT)) { if (!readerFailed.exchange(true)) readerErr = "short read on " + inputs[(size_t) f]; return; }
+                    if (want && !preadParallel(fd[f], tb.data(), want, pos[f], ioT)) { readerFail("short read on " + inputs[(size_t) f]); return; }
                     srcEof[f] = pos[f] + want >= fileSize[f];
                 }
                 pos[f] += got;
