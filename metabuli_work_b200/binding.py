@@ -161,6 +161,8 @@ _sig(_host, "mbh_rank", C.c_char_p, [vp, i32])
 _sig(_host, "mbh_db_kmers", u64, [vp])
 _sig(_host, "mbh_db_words", u64, [vp])
 _sig(_host, "mbh_write_outputs", C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, u32, C.POINTER(C.c_char_p), vp, vp, vp])
+_sig(_host, "mbh_read_fastx", C.c_int, [C.c_char_p, C.c_char_p, u64, u64, vp, u64, vp, vp, u64, vp, u64, C.POINTER(u32), C.POINTER(u64),
+                                        C.POINTER(u64)])
 _sig(_host, "mbh_classify_files", C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
                                             C.c_float, C.c_float, u64])
 
@@ -184,6 +186,29 @@ def rebalanced_cuts(times, current=None):
     out = np.zeros(len(t) - 1, dtype=np.float64)
     _host.mbh_rebalanced_cuts(_ptr(t), len(t), _ptr(cur) if cur is not None else None, _ptr(out))
     return out
+
+
+def host_read_fastx(path1, path2=None, max_reads=1 << 62, max_bases=1 << 62):
+    """The C++ host reader on its own (no GPU): first batch of the file(s) -> (names, bases uint8[], offsets uint64[2n],
+    lens uint32[2n]) in the layout of mb_stage_reads (the second mate of a single-end read has length 0)."""
+    n_reads, n_bases, names_len = u32(0), u64(0), u64(0)
+    cap_b, cap_r, cap_n = 1 << 16, 1 << 10, 1 << 14
+    while True:
+        bases = np.zeros(cap_b, dtype=np.uint8)
+        offsets = np.zeros(2 * cap_r, dtype=np.uint64)
+        lens = np.zeros(2 * cap_r, dtype=np.uint32)
+        names = np.zeros(cap_n, dtype=np.uint8)
+        rc = _host.mbh_read_fastx(os.fsencode(path1), os.fsencode(path2) if path2 else None, int(max_reads), int(max_bases),
+                                  _ptr(bases), cap_b, _ptr(offsets), _ptr(lens), cap_r, _ptr(names), cap_n,
+                                  C.byref(n_reads), C.byref(n_bases), C.byref(names_len))
+        if rc == 2:
+            cap_b, cap_r, cap_n = max(cap_b, n_bases.value), max(cap_r, n_reads.value), max(cap_n, names_len.value)
+            continue
+        if rc != 0:
+            raise MetabuliError(rc, _host.mbh_last_error().decode())
+        n = n_reads.value
+        nm = names[:names_len.value].tobytes().decode().split("\n")[:n]
+        return nm, bases[:n_bases.value].copy(), offsets[:2 * n].copy(), lens[:2 * n].copy()
 
 
 def pack_reads(mates1, mates2=None):

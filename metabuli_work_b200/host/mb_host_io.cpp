@@ -789,6 +789,30 @@ int mbh_classify_files(const char *reads1, const char *reads2, const char *dbdir
     return mbh::runClassify(in, dbdir, outdir, jobid, opt, g_err);
 }
 
+// The host reader alone (no GPU): the first batch runClassify's host path would stage from these files — at most max_reads
+// reads and, checked before every read, max_bases bases — in the packed layout of mb_stage_reads; names joined by '\n'.
+// Returns 0, 1 (error, mbh_last_error) or 2 (a caller's array is too small; the needed sizes are in the out arguments).
+int mbh_read_fastx(const char *reads1, const char *reads2, uint64_t max_reads, uint64_t max_bases, char *bases, uint64_t bases_cap,
+                   uint64_t *offsets, uint32_t *lens, uint64_t reads_cap, char *names, uint64_t names_cap, uint32_t *n_reads,
+                   uint64_t *n_bases, uint64_t *names_len) {
+    mbh::FastxReader r1, r2;
+    const bool paired = reads2 && *reads2;
+    if (!r1.open(reads1, g_err) || (paired && !r2.open(reads2, g_err))) return 1;
+    mbh::ReadBatch b;
+    mbh::loadBatch(r1, paired ? &r2 : nullptr, (size_t) max_reads, (size_t) max_bases, b);
+    size_t nl = 0;
+    for (const std::string &n : b.names) nl += n.size() + 1;
+    *n_reads = b.nReads();
+    *n_bases = b.bases.size();
+    *names_len = nl;
+    if (b.bases.size() > bases_cap || b.nReads() > reads_cap || nl > names_cap) return 2;
+    if (!b.bases.empty()) memcpy(bases, b.bases.data(), b.bases.size());
+    for (size_t i = 0; i < b.offsets.size(); ++i) { offsets[i] = b.offsets[i]; lens[i] = b.lens[i]; }
+    char *w = names;
+    for (const std::string &n : b.names) { memcpy(w, n.data(), n.size()); w += n.size(); *w++ = '\n'; }
+    return 0;
+}
+
 // The output writers alone (no GPU): per-read results in, JOBID_classifications.tsv / JOBID_report.tsv / JOBID_krona.html out,
 // exactly as runClassify writes them.  Lets the CPU test-suite compare the writers with the reference Reporter's files.
 int mbh_write_outputs(const char *dbdir, const char *outdir, const char *jobid, int lineage, const char *krona_prelude, uint32_t n_reads,
